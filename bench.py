@@ -1,0 +1,282 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the particle-parallel inference path.
+
+Workload (BASELINE.json configs[1], SURVEY 8(d) D2 "C2"): Bayesian logistic
+regression, D = 16 weights, N = 10^4 synthetic observations, 65 536 particles
+per GPU, program `(resimulation_mh default one 160)` (10 sweeps) per step.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]
+  python bench.py --impl reference ...     # CPU arm: oracle on all host cores
+
+One JSON line on rank 0.  `value` = particle-site MH transitions/s with the
+particle state resident in HBM (device-timed, max over ranks); `e2e` = the same
+metric through the public host-buffer API (forget + observe(X, y) H2D +
+incorporate + resimulation_mh + D2H of node counts and log weights, per step).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "particle-site MH transitions/sec"
+UNIT = "transitions/s"
+
+
+def make_data(N, D):
+    # X ~ N(0,1) (seed 0), w* ~ N(0,1) (seed 1), y ~ Bernoulli(logistic(x.w*)) (seed 2)
+    X = np.random.default_rng(0).normal(size=(N, D))
+    w_true = np.random.default_rng(1).normal(size=D)
+    y = (np.random.default_rng(2).random(N) < 1.0 / (1.0 + np.exp(-X @ w_true))).astype(np.uint8)
+    return np.ascontiguousarray(X), y
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks/throttle reasons DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_baseline(X, y, D, N, T, seconds_target=12.0):
+    """Oracle (CPU restatement of the Lite algorithm) on all host cores, bounded sample."""
+    import oracle
+    oracle.build()
+    L = oracle.lib()
+    cores = os.cpu_count() or 1
+
+    def run(Ps, Ts):
+        w = np.ascontiguousarray(np.random.default_rng(3).normal(size=(D, Ps)))
+        t0 = time.perf_counter()
+        L.orc_blr_mh(oracle._ptr(w), oracle._ptr(X), oracle._ptr(y), oracle.I32(D), oracle.I64(N), oracle.I64(Ps),
+                     oracle.I64(0), oracle.F64(0.0), oracle.F64(1.0), oracle.U64(1), oracle.U32(0), oracle.I32(Ts),
+                     oracle.I32(-1), None, None)
+        return time.perf_counter() - t0
+
+    Ts = min(T, 16)
+    dt = run(cores, Ts)                      # calibration: one particle per core
+    per = dt / Ts                            # seconds per transition per core-slot
+    Ps = int(max(cores, min(4096, (seconds_target / max(per * Ts, 1e-9)) * cores)))
+    Ps -= Ps % cores
+    dt = run(Ps, Ts)
+    return {"value": Ps * Ts / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d particles x %d transitions of the same N=%d, D=%d workload, OpenMP over particles, %.1f s"
+                      % (Ps, Ts, N, D, dt)}, dt
+
+
+def run_reference(args, X, y, D, N, T):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    vals, last = [], None
+    for i in range(args.warmup + args.steps):
+        cb, dt = cpu_baseline(X, y, D, N, T, seconds_target=4.0)
+        if i >= args.warmup:
+            vals.append((cb, dt))
+    tot_t = sum(dt for _, dt in vals)
+    value = float(np.mean([cb["value"] for cb, _ in vals]))
+    cb = dict(vals[-1][0]); cb["value"] = value
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(len(vals), 1),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "C2 Bayesian logistic regression, single-site resimulation_mh (default one)",
+                   "particles_per_gpu": args.particles, "observations": N, "D": D, "transitions_per_step": T},
+        "cpu_baseline": cb,
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "obs_loglik_evals_per_sec": value * N,
+        "note": "reference Lite/Puma cannot run here (python2 / GSL / Boost absent); this arm times the oracle "
+                "(C restatement of the Lite algorithm: full vector_dot + log_odds_flip recompute per proposal)",
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--particles", type=int, default=65536, help="particles per GPU")
+    ap.add_argument("--obs", type=int, default=10000)
+    ap.add_argument("--dim", type=int, default=16)
+    ap.add_argument("--transitions", type=int, default=160)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    D, N, T, P = args.dim, args.obs, args.transitions, args.particles
+    X, y = make_data(N, D)
+
+    if args.impl == "reference":
+        run_reference(args, X, y, D, N, T)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import venturecxx_b200 as vb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    W = max(args.warmup, 3)
+
+    ts = vb.B200TraceSet(vb.LogisticRegressionModel(D, N), P, seed=1234, device=local, particle_base=rank * P)
+    stream = torch.cuda.Stream()          # a real (non-default) stream shared by torch events and the library
+    torch.cuda.set_stream(stream)
+    ts.use_stream(stream.cuda_stream)
+    ts.observe(X, y)
+    ts.incorporate()
+    from venturecxx_b200 import _lib
+
+    def step_resident():
+        # state resident in HBM, no host outputs: exactly one kernel launch
+        _lib.call("vk_mh", ts._h, 0, _lib.BLOCK_ONE, T, None, None)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # L2 note: the per-particle logit rows total P*N*8 B = 5.2 GB >> 126 MB L2; Xs (1.3 MB) is meant to be L2 resident.
+    for _ in range(W):
+        step_resident()
+    acc0 = np.empty(P, dtype=np.int64)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step_resident()
+    ev1.record(stream)
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    # accept rate of one extra (untimed) step, for the algorithmic-bytes formula
+    _lib.call("vk_mh", ts._h, 0, _lib.BLOCK_ONE, T, None, _lib.ptr(acc0))
+    a_rate = float(acc0.mean()) / T
+
+    # ---- end to end through the public API with host buffers ------------
+    Xp = torch.from_numpy(X).pin_memory().numpy()
+    yp = torch.from_numpy(y).pin_memory().numpy()
+
+    def step_e2e():
+        ts.forget_observations()
+        ts.observe(Xp, yp)                       # H2D: N*D*8 + N bytes
+        ts.incorporate()                         # D2H: P*8 (increments)
+        nodes = ts.primitive_infer(["resimulation_mh", "default", "one", T])   # D2H: P*8
+        return nodes
+
+    step_e2e()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_e2e()
+    e1.record(stream)
+    barrier()
+    ms_e2e = max(e0.elapsed_time(e1), 1e3 * (time.perf_counter() - t0))
+
+    t_ms = torch.tensor([ms, ms_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = [float(v) for v in t_ms.tolist()]
+
+    if rank == 0:
+        total_tr = float(P) * world * T * args.steps
+        value = total_tr / (ms * 1e-3)
+        e2e_value = total_tr / (ms_e2e * 1e-3)
+        peak, peak_src = load_peaks()
+        # N*s*(1+a) + 2s bytes per particle-transition (s = 8)
+        bytes_per_tr = N * 8.0 * (1.0 + a_rate) + 16.0
+        launch_s = ms * 1e-3 / args.steps
+        achieved = bytes_per_tr * P * T / launch_s / 1e9
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C2 Bayesian logistic regression, single-site resimulation_mh (default one)",
+                       "particles_per_gpu": P, "observations": N, "D": D, "transitions_per_step": T,
+                       "l2": "inputs larger than L2 (logit rows %.1f GB per GPU)" % (P * N * 8 / 1e9)},
+            "obs_loglik_evals_per_sec": value * N,
+            "accept_rate": a_rate,
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+                    "h2d_bytes_per_step": int(X.nbytes + y.nbytes), "d2h_bytes_per_step": int(3 * P * 8)},
+            "gpu_launches": args.steps,
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "blr_mh_kernel<true>",
+                         "note": "algorithmic bytes per SURVEY 8(d) D4 = N*8*(1+a)+16 per particle-transition; "
+                                 "the kernel keeps the logit row in shared memory for all transitions of a launch, so "
+                                 "real DRAM traffic is ~2*8N B per particle per launch and the kernel is fp64-ALU bound"},
+        }
+        if not args.no_cpu_baseline and world == 1:
+            cb, _ = cpu_baseline(X, y, D, N, T)
+            out["cpu_baseline"] = cb
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

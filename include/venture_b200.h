@@ -1,0 +1,233 @@
+/*
+ * venture_b200.h -- C ABI of the B200-native particle-parallel inference path
+ * for Venture (probcomp/Venturecxx).
+ *
+ * One `vk_particles` handle is one device-resident batch of P weighted traces
+ * ("particles") of ONE fixed-structure model, laid out structure-of-arrays in
+ * HBM.  It replaces, for that batch, what the reference reaches through
+ *   TraceSet.traces.map('<method>')        python/lib/engine/trace_set.py:148-164
+ * i.e. the per-trace backend methods exported by Puma's Boost.Python module
+ *   backend/new_cxx/src/pytrace.cxx:330-366
+ * and by the Lite trace
+ *   backend/lite/trace.py:422-448 (makeConsistent), :509-520 (primitive_infer,
+ *   log_likelihood_at, log_joint_at), :522-530 (likelihood_weight)
+ * plus the TraceSet-level weight bookkeeping and resampling
+ *   python/lib/engine/trace_set.py:202-235, 287-294
+ *   backend/lite/utils.py:70-91, 152-180.
+ *
+ * Conventions
+ *   - every entry point returns 0 on success and a nonzero VK_E* code on
+ *     failure; vk_last_error() then holds a message (thread-local).  The
+ *     Python shim raises it as VentureException("evaluation", msg), the way
+ *     pytrace.cxx:236-242,331-332 translates Puma's C++ exceptions.
+ *   - plain pointers and sizes only.  Pointers named *_host are host memory
+ *     (pageable or pinned); copies are issued on the handle's stream and the
+ *     call returns after the stream has drained, so results are ready.
+ *   - the handle owns all device memory.  One caller at a time per handle
+ *     (the reference engine is single-threaded per TraceSet).
+ *   - arithmetic is IEEE double (the reference is double everywhere).
+ *   - there is NO CPU fallback: without a CUDA device every compute call
+ *     fails with VK_ECUDA.
+ */
+#ifndef VENTURE_B200_H
+#define VENTURE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct vk_particles vk_particles;
+
+enum vk_status {
+  VK_OK = 0,
+  VK_EINVAL = 1,      /* bad argument  -> VentureException("invalid_argument") */
+  VK_ECUDA = 2,       /* CUDA runtime / launch failure                        */
+  VK_EUNSUPPORTED = 3,/* operation not defined for this model kind            */
+  VK_ESTATE = 4       /* call sequence error (e.g. infer before observe)      */
+};
+
+enum vk_model_kind {
+  VK_MODEL_NORMAL_NORMAL = 1, /* x ~ normal(mu0,s0); observe normal(x,s) = y_k          */
+  VK_MODEL_BLR = 2,           /* w_j ~ normal(mu0,s0); observe log_odds_flip(w.x_i)=y_i */
+  VK_MODEL_HMM = 3,           /* examples/hmm.vnt:31-60                                 */
+  VK_MODEL_LDA = 4            /* examples/lda.vnt:18-41                                 */
+};
+
+/* block argument of an infer command (backend/lite/infer/dispatch.py:86-107) */
+#define VK_BLOCK_ONE  (-1)  /* a uniformly chosen block per transition */
+#define VK_BLOCK_ALL  (-2)  /* all blocks of the scope as one proposal  */
+#define VK_BLOCK_EACH (-3)  /* every block in order, one proposal each  */
+
+enum vk_resample_mode {
+  VK_RESAMPLE_MULTINOMIAL = 0, /* trace_set.py:209-219 (i.i.d. categorical draws) */
+  VK_RESAMPLE_SYSTEMATIC = 1   /* one uniform, stratified positions (k+u)/P       */
+};
+
+/* ---- library ---------------------------------------------------------- */
+const char *vk_last_error(void);
+int vk_version(void);
+int vk_device_count(int *n_out);
+
+/* ---- construction (replaces Backend.trace_constructor()(seed) for P traces:
+ *      python/lib/shortcuts/__init__.py:90-149, trace_set.py:38-48) --------- */
+int vk_create_normal_normal(int64_t n_particles, uint64_t seed, int device,
+                            double prior_mu, double prior_sigma,
+                            double obs_sigma, int64_t max_obs,
+                            vk_particles **out);
+/* X rows are D doubles; capacity n_obs_capacity observations. */
+int vk_create_blr(int64_t n_particles, uint64_t seed, int device, int32_t D,
+                  int64_t n_obs_capacity, double prior_mu, double prior_sigma,
+                  vk_particles **out);
+/* trans: n_trans_rows x S row-major, emit: S x O row-major (unnormalised
+ * categorical weights, normalised per call like lite/utils.py:101-118);
+ * state(1) = init_state (1-based, hmm.vnt:55-60); T_max = history length. */
+int vk_create_hmm(int64_t n_particles, uint64_t seed, int device, int32_t S,
+                  int32_t O, int32_t n_trans_rows, const double *trans_host,
+                  const double *emit_host, int32_t init_state, int32_t T_max,
+                  vk_particles **out);
+/* tokens are observed later with vk_lda_observe; doc d holds at most
+ * max_tokens_per_doc tokens.  Hyperpriors alpha ~ gamma(hyper_shape, hyper_rate). */
+int vk_create_lda(int64_t n_particles, uint64_t seed, int device, int32_t K,
+                  int32_t V, int32_t n_docs, int32_t max_tokens,
+                  double hyper_shape, double hyper_rate, vk_particles **out);
+int vk_destroy(vk_particles *h);
+
+int vk_kind(const vk_particles *h);
+int64_t vk_num_particles(const vk_particles *h);
+/* has_own_prng / set_seed / get_seed  (lite/trace.py:89-92, trace_set.py) */
+int vk_set_seed(vk_particles *h, uint64_t seed);
+int vk_get_seed(const vk_particles *h, uint64_t *seed_out);
+/* RNG step counter: every infer-level operation consumes one or more steps
+ * of the counter-based Philox stream (DESIGN.md "RNG contract"). */
+int vk_get_step(const vk_particles *h, uint32_t *step_out);
+int vk_set_step(vk_particles *h, uint32_t step);
+/* global index of this batch's particle 0 when the particle set is sharded
+ * over several GPUs (streams are addressed by GLOBAL particle index, so
+ * results do not depend on the GPU count). */
+int vk_set_particle_base(vk_particles *h, int64_t base);
+/* TraceSet.reset_to_prior (trace_set.py:199-200): resimulate every latent
+ * from its prior; weights untouched.  Also the initial `assume` simulation:
+ * call once after vk_create_* (and after vk_set_particle_base). */
+int vk_reset_to_prior(vk_particles *h);
+/* run on a caller-provided CUDA stream (cudaStream_t passed as void*),
+ * e.g. torch.cuda.current_stream().cuda_stream; NULL = the handle's own. */
+int vk_set_stream(vk_particles *h, void *cuda_stream);
+int vk_synchronize(vk_particles *h);
+
+/* ---- observe (engine.observe -> trace.observe; values are shared by all
+ *      particles; they stay "unpropagated" until vk_make_consistent,
+ *      lite/trace.py:415-448) -------------------------------------------- */
+int vk_nn_observe(vk_particles *h, const double *y_host, int64_t n);
+int vk_blr_observe(vk_particles *h, const double *X_rows_host,
+                   const uint8_t *y_host, int64_t n);
+int vk_hmm_observe(vk_particles *h, int32_t symbol /* 1-based */);
+int vk_lda_observe(vk_particles *h, const int32_t *doc_host,
+                   const int32_t *word_host, int64_t n);
+
+/* engine.forget of every observe directive (trace_set.py:157-161 ->
+ * lite/trace.py:483-493 unobserve): drops all observations; returns per
+ * particle the weight unconstrain() reports (sum of their logDensity);
+ * log weights are NOT changed, as in the reference. out may be NULL. */
+int vk_forget_observations(vk_particles *h, double *weights_out_host);
+
+/* ---- weights (trace_set.py:287-294; engine/inference.py:218-234) ------- */
+/* TraceSet.incorporate: lw[p] += makeConsistent()[p]; increments optionally
+ * copied out (host, P doubles; may be NULL). NaN increment -> -inf. */
+int vk_make_consistent(vk_particles *h, double *increments_out_host);
+/* TraceSet.likelihood_weight: resimulate all latents from the prior,
+ * lw[p] := sum_obs logDensity (overwrite). */
+int vk_likelihood_weight(vk_particles *h);
+int vk_get_log_weights(vk_particles *h, double *out_host);
+int vk_set_log_weights(vk_particles *h, const double *in_host);
+int vk_increment_log_weights(vk_particles *h, const double *in_host);
+/* lite/utils.py:70-91 over the particle log-weights. */
+int vk_logsumexp(vk_particles *h, double *out_host);
+/* lite/utils.py:159-168 (all -inf -> zeros). */
+int vk_normalized_probs(vk_particles *h, double *out_host);
+/* stand-alone logsumexp of a host array (n may be 0 -> -inf). */
+int vk_logsumexp_array(const double *in_host, int64_t n, int device,
+                       double *out_host);
+
+/* ---- resample (trace_set.py:202-235, utils.py:93-104,152-157,170-180) ---
+ * Draw n_new ancestors proportional to exp(lw); copy ancestor state; all new
+ * weights = logsumexp(lw) - log(n_new).  n_new must equal P in this version.
+ * uniforms_host: NULL = draw from the handle's Philox stream; otherwise 1
+ * (systematic) or n_new (multinomial) uniforms in [0,1) to use instead.
+ * ancestors_out_host: NULL or n_new int32. */
+int vk_resample(vk_particles *h, int64_t n_new, int mode,
+                const double *uniforms_host, int32_t *ancestors_out_host);
+
+/* ---- inference (infer/dispatch.py:130-136, mh.py:59-113,167-208) --------
+ * K single-site resimulation-MH transitions per particle.  scope 0 =
+ * "default".  block = VK_BLOCK_ONE / VK_BLOCK_EACH / a block index.
+ * mean_nodes_out_host: NULL or P doubles = transloop's return value
+ * (mean #affected nodes per transition, dispatch.py:109-120).
+ * accepted_out_host: NULL or P int64 accept counters (profiling analogue of
+ * mh.py:98-111). */
+int vk_mh(vk_particles *h, int32_t scope, int32_t block, int32_t transitions,
+          double *mean_nodes_out_host, int64_t *accepted_out_host);
+
+/* infer/subsampled_mh.py:76-171 (BLR model only).  stats_out_host: NULL or
+ * 3*P doubles per call = (accepted transitions, mean local sections visited
+ * per transition, last t statistic). */
+int vk_subsampled_mh(vk_particles *h, int32_t scope, int32_t block,
+                     int64_t Nbatch, int32_t k0, double epsilon,
+                     int32_t use_delta_kernels, double delta_sigma,
+                     int32_t update_values, int32_t transitions,
+                     double *stats_out_host);
+
+/* infer/dispatch.py:331-361 -- non-mutating. out_host: P doubles. */
+int vk_log_likelihood_at(vk_particles *h, int32_t scope, int32_t block,
+                         double *out_host);
+int vk_log_joint_at(vk_particles *h, int32_t scope, int32_t block,
+                    double *out_host);
+
+/* ---- state access (extractValue / parity-test injection) ----------------
+ * site ids are model specific (DESIGN.md "site tables"); values are doubles
+ * (integers are converted), P per site. */
+int vk_num_sites(const vk_particles *h, int64_t *n_out);
+int vk_read_site(vk_particles *h, int64_t site, double *out_host);
+int vk_write_site(vk_particles *h, int64_t site, const double *in_host);
+/* after vk_write_site: recompute derived caches (logits, counts). */
+int vk_refresh(vk_particles *h);
+/* numBlocksInScope("default")  (lite/trace.py) */
+int vk_num_blocks(const vk_particles *h, int32_t scope, int64_t *n_out);
+
+/* ---- raw device buffers, for NCCL plumbing in the host layer ------------
+ * which: 0 = log weights (P doubles), 1.. = model state arrays.
+ * Returns device pointer, element size, rows (per-particle stride semantics
+ * in DESIGN.md).  The pointers stay valid until the next resample. */
+int vk_device_buffer(vk_particles *h, int32_t which, void **dev_ptr_out,
+                     int64_t *n_bytes_out);
+
+/* Multi-GPU resampling helpers: fixed-point weight mass of
+ * this shard relative to a caller-supplied global max, and ancestor search
+ * against a caller-supplied global offset/total.  See distributed.py. */
+int vk_shard_weight_max(vk_particles *h, double *max_out_host);
+int vk_shard_weight_mass(vk_particles *h, double global_max, int32_t frac_bits,
+                         uint64_t *mass_out_host);
+
+/* ---- SP plugin surface, batched (backend/lite/psp.py:32-318:
+ *      simulate(args) / logDensity(value,args)) ---------------------------
+ * params_host: n x n_params row-major.  For vector-valued SPs (dirichlet)
+ * values are n x dim.  Draws use Philox(seed, particle=i, step). */
+enum vk_sp_id {
+  VK_SP_NORMAL = 1, VK_SP_GAMMA = 2, VK_SP_BETA = 3, VK_SP_FLIP = 4,
+  VK_SP_LOG_FLIP = 5, VK_SP_LOG_ODDS_FLIP = 6, VK_SP_CATEGORICAL = 7,
+  VK_SP_LOG_CATEGORICAL = 8, VK_SP_DIRICHLET = 9, VK_SP_SYM_DIRICHLET = 10,
+  VK_SP_SYM_DIR_CAT = 11, VK_SP_BETA_BERNOULLI = 12
+};
+int vk_sp_simulate(int32_t sp, const double *params_host, int32_t n_params,
+                   int64_t n, int32_t dim, uint64_t seed, uint32_t step,
+                   int device, double *values_out_host);
+int vk_sp_log_density(int32_t sp, const double *values_host,
+                      const double *params_host, int32_t n_params, int64_t n,
+                      int32_t dim, int device, double *out_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VENTURE_B200_H */

@@ -1,0 +1,554 @@
+/*
+ * oracle.c -- CPU restatement (plain C, fp64) of the reference's particle
+ * inference path.  TEST INFRASTRUCTURE ONLY: imported by tests/, by
+ * __graft_entry__.smoke() and by bench.py's cpu_baseline / --impl reference
+ * legs as the checker and the timed CPU baseline; never by the product path.
+ *
+ * Each function cites the reference code it follows (paths relative to
+ * /root/reference).  The reference draws from numpy RandomState / Python
+ * random (backend/lite/trace.py:89-92), which cannot be reproduced on a GPU;
+ * the oracle therefore consumes the SAME counter-based Philox4x32-10 streams
+ * as the CUDA path (DESIGN.md "RNG contract": key = seed, counter =
+ * (particle, step, draw>>1)), so that whole chains can be compared value by
+ * value.  Everything else -- which draws happen, in which order, the weight
+ * accounting of detach/regen, the accept rule, the +-inf policies -- follows
+ * Lite.  Where Lite delegates to scipy (gamma/beta logpdf, gammaln, betaln,
+ * t.cdf) the closed forms are restated here and pinned against scipy and
+ * against the reference's own functions in tests/ (see oracle/lite_semantics.py
+ * and tests/golden/).
+ *
+ * Pinning status: logsumexp, logistic family, sequentialTest, categorical /
+ * dirichlet / dir-cat densities, normal logDensity are pinned against the
+ * reference's own golden vectors and against the reference functions executed
+ * here (tests/golden/make_golden.py).  gamma/beta logDensity values are pinned
+ * against scipy only (the reference tests only integrate / KS them).
+ * Resampling ancestors: the reference is multinomial via numpy; parity there is
+ * defined against THIS restatement ("parity unpinned" vs the reference for
+ * ancestor indices, distributional tests only).
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define HALF_LOG2PI 0.91893853320467274178
+typedef unsigned __int128 u128;
+
+/* ------------------------------------------------------------------ RNG */
+typedef struct { uint32_t k0, k1, p0, p1, step, d; uint32_t b[4]; } orc_stream;
+
+static void philox(uint32_t c[4], uint32_t k0, uint32_t k1) {
+  for (int r = 0; r < 10; ++r) {
+    uint64_t m0 = (uint64_t)0xD2511F53u * c[0];
+    uint64_t m1 = (uint64_t)0xCD9E8D57u * c[2];
+    uint32_t n0 = (uint32_t)(m1 >> 32) ^ c[1] ^ k0;
+    uint32_t n2 = (uint32_t)(m0 >> 32) ^ c[3] ^ k1;
+    c[0] = n0; c[1] = (uint32_t)m1; c[2] = n2; c[3] = (uint32_t)m0;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+}
+static void st_init(orc_stream *s, uint64_t seed, uint64_t particle, uint32_t step) {
+  s->k0 = (uint32_t)seed; s->k1 = (uint32_t)(seed >> 32);
+  s->p0 = (uint32_t)particle; s->p1 = (uint32_t)(particle >> 32);
+  s->step = step; s->d = 0;
+}
+static void st_fill(orc_stream *s) {
+  s->b[0] = s->p0; s->b[1] = s->p1; s->b[2] = s->step; s->b[3] = s->d >> 1;
+  philox(s->b, s->k0, s->k1);
+}
+static double st_uniform(orc_stream *s) {
+  if ((s->d & 1u) == 0u) st_fill(s);
+  uint32_t w = (s->d & 1u) * 2u;
+  uint64_t x = (((uint64_t)s->b[w] << 32) | s->b[w + 1]) >> 11;
+  s->d++;
+  return ((double)x + 0.5) * (1.0 / 9007199254740992.0);
+}
+static void st_seek(orc_stream *s, uint32_t d) { s->d = d; if (d & 1u) st_fill(s); }
+
+void orc_uniforms(uint64_t seed, uint64_t particle, uint32_t step, int n, double *out) {
+  orc_stream s; st_init(&s, seed, particle, step);
+  for (int i = 0; i < n; ++i) out[i] = st_uniform(&s);
+}
+
+/* -------------------------------------------------- lite/utils.py maths */
+/* utils.py:60-61 */
+static double vlog(double x) { return x == 0 ? -INFINITY : log(x); }
+static double vlog1p(double x) { return x == -1 ? -INFINITY : log1p(x); }
+/* utils.py:257-268 */
+double orc_log_logistic(double x) { return x <= -37 ? x : -log1p(exp(-x)); }
+/* utils.py:189-203 */
+double orc_logistic(double x) { return x <= -37 ? exp(x) : 1 / (1 + exp(-x)); }
+static double logit(double p) { return log(p / (1 - p)); }
+
+/* utils.py:70-91 */
+double orc_logsumexp(const double *a, int64_t n) {
+  if (n == 0) return -INFINITY;
+  double m = -INFINITY, mn = INFINITY; int has_nan = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    if (a[i] != a[i]) has_nan = 1;
+    else { if (a[i] > m) m = a[i]; if (a[i] < mn) mn = a[i]; }
+  }
+  if (has_nan) return NAN;
+  if (isinf(m) && mn != -m) return m;
+  if (isinf(m)) return NAN;
+  double s = 0;
+  for (int64_t i = 0; i < n; ++i) s += exp(a[i] - m);
+  return m + log(s);
+}
+/* utils.py:159-168 */
+void orc_normalized_probs(const double *a, int64_t n, double *out) {
+  double m = -INFINITY;
+  for (int64_t i = 0; i < n; ++i) if (a[i] > m) m = a[i];
+  if (!(m > -INFINITY)) { for (int64_t i = 0; i < n; ++i) out[i] = 0; return; }
+  double s = 0;
+  for (int64_t i = 0; i < n; ++i) { out[i] = exp(a[i] - m); s += out[i]; }
+  for (int64_t i = 0; i < n; ++i) out[i] /= s;
+}
+
+/* ------------------------------------------------------- SP primitives */
+/* continuous.py:319-323 */
+static double normal_logpdf(double x, double mu, double sigma) {
+  double dev = x - mu;
+  return -log(sigma) - HALF_LOG2PI - (0.5 * dev * dev / (sigma * sigma));
+}
+static double std_normal(orc_stream *r) {
+  double u1 = st_uniform(r), u2 = st_uniform(r);
+  return sqrt(-2.0 * log(u1)) * cos(6.283185307179586476925 * u2);
+}
+static double normal_sim(orc_stream *r, double mu, double sigma) { return mu + sigma * std_normal(r); }
+
+/* continuous.py:1166-1167 -> scipy.stats.gamma.logpdf(x, a, scale=1/b) */
+static double gamma_logpdf(double x, double a, double b) {
+  if (x < 0) return -INFINITY;
+  double y = x * b, t;
+  if (a == 1) t = 0;
+  else if (y == 0) t = a > 1 ? -INFINITY : INFINITY;
+  else t = (a - 1) * log(y);
+  return t - y - lgamma(a) + log(b);
+}
+/* continuous.py:1163-1164 np_rng.gamma(shape, scale=1/b): Marsaglia-Tsang */
+static double std_gamma(orc_stream *r, double a) {
+  double boost = 1;
+  if (a < 1) { double u = st_uniform(r); boost = pow(u, 1 / a); a += 1; }
+  double d = a - 1.0 / 3.0, c = 1 / sqrt(9 * d);
+  for (;;) {
+    double x = std_normal(r), v = 1 + c * x;
+    if (v <= 0) continue;
+    v = v * v * v;
+    double u = st_uniform(r);
+    if (log(u) < 0.5 * x * x + d - d * v + d * log(v)) return d * v * boost;
+  }
+}
+static double gamma_sim(orc_stream *r, double a, double b) { return std_gamma(r, a) / b; }
+
+static double betaln(double a, double b) { return lgamma(a) + lgamma(b) - lgamma(a + b); }
+/* continuous.py:858-859 -> scipy.stats.beta.logpdf */
+static double beta_logpdf(double x, double a, double b) {
+  if (x < 0 || x > 1) return -INFINITY;
+  double t1 = (b - 1 == 0) ? 0 : (b - 1) * log1p(-x);
+  double t2 = (a - 1 == 0) ? 0 : (a - 1) * log(x);
+  return t1 + t2 - betaln(a, b);
+}
+/* continuous.py:731-856 */
+static double beta_sim(orc_stream *r, double a, double b) {
+  if (a == 0 && b == 0) return st_uniform(r) < 0.5 ? 0 : 1;
+  if (a == 0) return 1;
+  if (b == 0) return 0;
+  if (fmin(a, b) < 1e-300) return st_uniform(r) < a / (a + b) ? 0 : 1;
+  if (1 < a || 1 < b) { double G = std_gamma(r, a), H = std_gamma(r, b); return G / (G + H); }
+  for (;;) {
+    double u = st_uniform(r), v = st_uniform(r);
+    double x = pow(u, 1 / a), y = pow(v, 1 / b);
+    if (1 < x + y) continue;
+    if (0 < x + y) return x / (x + y);
+    double lx = log(u) / a, ly = log(v) / b, lm = fmax(lx, ly);
+    lx -= lm; ly -= lm;
+    return exp(lx - log(exp(lx) + exp(ly)));
+  }
+}
+/* utils.py:93-118 */
+static double categorical_logpmf(int val, const double *ps, int n) {
+  double denom = 0;
+  for (int i = 0; i < n; ++i) denom += ps[i];
+  if (val < 0 || val >= n) return -INFINITY;
+  double p = denom > 0 ? ps[val] / denom : 1.0 / n;
+  return p == 0 ? -INFINITY : log(p);
+}
+static int categorical_sim(orc_stream *r, const double *ps, int n) {
+  double denom = 0;
+  for (int i = 0; i < n; ++i) denom += ps[i];
+  double u = st_uniform(r);
+  if (!(denom > 0)) { int k = (int)(u * n); return k < n ? k : n - 1; }
+  double t = u * denom, acc = 0; int last = 0;
+  for (int i = 0; i < n; ++i) { if (ps[i] > 0) last = i; acc += ps[i]; if (t < acc) return i; }
+  return last;
+}
+/* utils.py:182-184 */
+static double log_categorical_logpmf(int val, const double *lps, int n) {
+  if (val < 0 || val >= n) return -INFINITY;
+  return orc_logsumexp(&lps[val], 1) - orc_logsumexp(lps, n);
+}
+/* utils.py:137-141 */
+static double dirichlet_logpdf(const double *theta, const double *alpha, int n) {
+  double sa = 0, sl = 0, dot = 0;
+  for (int i = 0; i < n; ++i) { sa += alpha[i]; sl += lgamma(alpha[i]); dot += (alpha[i] - 1) * log(theta[i]); }
+  return lgamma(sa) - sl + dot;
+}
+static void dirichlet_sim(orc_stream *r, const double *alpha, int n, double *out) {
+  double s = 0;
+  for (int i = 0; i < n; ++i) { out[i] = std_gamma(r, alpha[i]); s += out[i]; }
+  for (int i = 0; i < n; ++i) out[i] /= s;
+}
+
+enum { SP_NORMAL = 1, SP_GAMMA, SP_BETA, SP_FLIP, SP_LOG_FLIP, SP_LOG_ODDS_FLIP, SP_CATEGORICAL,
+       SP_LOG_CATEGORICAL, SP_DIRICHLET, SP_SYM_DIRICHLET, SP_SYM_DIR_CAT, SP_BETA_BERNOULLI };
+
+/* batched PSP.simulate: value i drawn from Philox(seed, particle=i, step) */
+int orc_sp_simulate(int sp, const double *params, int n_params, int64_t n, int dim, uint64_t seed,
+                    uint32_t step, double *out) {
+  for (int64_t i = 0; i < n; ++i) {
+    const double *q = params + i * n_params;
+    orc_stream r; st_init(&r, seed, (uint64_t)i, step);
+    switch (sp) {
+      case SP_NORMAL: out[i] = normal_sim(&r, q[0], q[1]); break;
+      case SP_GAMMA: out[i] = gamma_sim(&r, q[0], q[1]); break;
+      case SP_BETA: out[i] = beta_sim(&r, q[0], q[1]); break;
+      case SP_FLIP: out[i] = st_uniform(&r) < q[0]; break;                 /* discrete.py:56-59 */
+      case SP_LOG_FLIP: out[i] = log(st_uniform(&r)) < q[0]; break;        /* discrete.py:106-108 */
+      case SP_LOG_ODDS_FLIP: out[i] = logit(st_uniform(&r)) < q[0]; break; /* discrete.py:144-146 */
+      case SP_CATEGORICAL: out[i] = categorical_sim(&r, q, n_params); break;
+      case SP_LOG_CATEGORICAL: {                                           /* utils.py:170-180 */
+        double m = -INFINITY; double tmp[1024];
+        if (n_params > 1024) return 1;
+        for (int k = 0; k < n_params; ++k) if (q[k] > m) m = q[k];
+        for (int k = 0; k < n_params; ++k) tmp[k] = m > -INFINITY ? exp(q[k] - m) : 0;
+        out[i] = categorical_sim(&r, tmp, n_params); break; }
+      case SP_DIRICHLET: dirichlet_sim(&r, q, dim, out + i * dim); break;
+      case SP_SYM_DIRICHLET: {
+        double al[1024]; if (dim > 1024) return 1;
+        for (int k = 0; k < dim; ++k) al[k] = q[0];
+        dirichlet_sim(&r, al, dim, out + i * dim); break; }
+      case SP_SYM_DIR_CAT: {  /* dirichlet.py:164-166: index ~ (alpha + counts); params = alpha, counts[dim] */
+        double wts[1024]; if (dim > 1024) return 1;
+        for (int k = 0; k < dim; ++k) wts[k] = q[0] + q[1 + k];
+        out[i] = categorical_sim(&r, wts, dim); break; }
+      case SP_BETA_BERNOULLI: {  /* discrete.py:440-443; params = a, b, yes, no */
+        double w = (q[0] + q[2]) / (q[0] + q[2] + q[1] + q[3]);
+        out[i] = st_uniform(&r) < w; break; }
+      default: return 1;
+    }
+  }
+  return 0;
+}
+
+int orc_sp_log_density(int sp, const double *values, const double *params, int n_params, int64_t n,
+                       int dim, double *out) {
+  for (int64_t i = 0; i < n; ++i) {
+    const double *q = params + i * n_params;
+    double v = values[dim > 1 && (sp == SP_DIRICHLET || sp == SP_SYM_DIRICHLET) ? i * dim : i];
+    switch (sp) {
+      case SP_NORMAL: out[i] = normal_logpdf(v, q[0], q[1]); break;
+      case SP_GAMMA: out[i] = gamma_logpdf(v, q[0], q[1]); break;
+      case SP_BETA: out[i] = beta_logpdf(v, q[0], q[1]); break;
+      case SP_FLIP: out[i] = v != 0 ? vlog(q[0]) : vlog1p(-q[0]); break;               /* discrete.py:61-67 */
+      case SP_LOG_FLIP: out[i] = v != 0 ? q[0] : vlog1p(-exp(q[0])); break;           /* discrete.py:110-113 */
+      case SP_LOG_ODDS_FLIP: out[i] = orc_log_logistic(v != 0 ? q[0] : -q[0]); break; /* discrete.py:148-150 */
+      case SP_CATEGORICAL: out[i] = categorical_logpmf((int)v, q, n_params); break;
+      case SP_LOG_CATEGORICAL: out[i] = log_categorical_logpmf((int)v, q, n_params); break;
+      case SP_DIRICHLET: out[i] = dirichlet_logpdf(values + i * dim, q, dim); break;
+      case SP_SYM_DIRICHLET: {
+        double al[1024]; if (dim > 1024) return 1;
+        for (int k = 0; k < dim; ++k) al[k] = q[0];
+        out[i] = dirichlet_logpdf(values + i * dim, al, dim); break; }
+      case SP_SYM_DIR_CAT: {  /* dirichlet.py:168-173 */
+        double tot = 0; int idx = (int)v;
+        for (int k = 0; k < dim; ++k) tot += q[1 + k];
+        out[i] = log((q[1 + idx] + q[0]) / (tot + q[0] * dim)); break; }
+      case SP_BETA_BERNOULLI: {  /* discrete.py:445-451 */
+        double w = (q[0] + q[2]) / (q[0] + q[2] + q[1] + q[3]);
+        out[i] = v != 0 ? log(w) : log1p(-w); break; }
+      default: return 1;
+    }
+  }
+  return 0;
+}
+
+/* dirichlet.py:192-201 CDirCatOutputPSP.logDensityOfData, symmetric alpha */
+double orc_sym_dircat_log_density_of_data(const double *counts, int n, double alpha) {
+  double N = 0;
+  for (int i = 0; i < n; ++i) N += counts[i];
+  double A = alpha * n;
+  double term1 = lgamma(A) - lgamma(N + A), term2 = 0;
+  for (int i = 0; i < n; ++i) term2 += lgamma(alpha + counts[i]) - lgamma(alpha);
+  return term1 + term2;
+}
+/* discrete.py:453-459 */
+double orc_beta_bernoulli_log_density_of_data(double a, double b, double yes, double no) {
+  return betaln(yes + a, no + b) - betaln(a, b);
+}
+
+/* ----------------------------------------------------------- resampling */
+/* Fixed-point weights: q_i = rint(exp(lw_i - max) * 2^S).  All -inf -> all 1
+ * (utils.py:93-99,176-180: "equally impossible").  NaN -> 0. */
+int orc_frac_bits(int64_t P_total) {
+  int lg = 0;
+  while (((int64_t)1 << lg) < P_total) ++lg;
+  int S = 62 - lg;
+  return S > 52 ? 52 : S;
+}
+void orc_fixed_cdf(const double *lw, int64_t n, double m, int frac_bits, uint64_t *cdf) {
+  double scale = ldexp(1.0, frac_bits);
+  uint64_t run = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    uint64_t q;
+    if (!(m > -INFINITY)) q = 1;
+    else { double d = lw[i] - m; q = (d != d) ? 0 : (uint64_t)nearbyint(exp(d) * scale); }
+    run += q; cdf[i] = run;
+  }
+}
+static int64_t upper_bound(const uint64_t *cdf, int64_t n, uint64_t thr) {
+  int64_t lo = 0, hi = n - 1;
+  while (lo < hi) { int64_t mid = (lo + hi) >> 1; if (cdf[mid] > thr) hi = mid; else lo = mid + 1; }
+  return lo;
+}
+/* trace_set.py:209-219 (_resample_traces): mode 0 multinomial (one uniform
+ * per child, stream (seed, particle=k, step)); mode 1 systematic (one uniform,
+ * stream (seed, GLOBAL, step)). uniforms may override the stream draws. */
+void orc_ancestors(const double *lw, int64_t n, int64_t n_new, int mode, uint64_t seed, uint32_t step,
+                   const double *uniforms, int32_t *anc) {
+  double m = -INFINITY;
+  for (int64_t i = 0; i < n; ++i) if (lw[i] == lw[i] && lw[i] > m) m = lw[i];
+  uint64_t *cdf = (uint64_t *)malloc((size_t)n * sizeof(uint64_t));
+  orc_fixed_cdf(lw, n, m, orc_frac_bits(n), cdf);
+  uint64_t total = cdf[n - 1];
+  double u_sys = 0;
+  if (mode == 1) {
+    if (uniforms) u_sys = uniforms[0];
+    else { orc_stream r; st_init(&r, seed, 0xFFFFFFFFFFFFFFFFull, step); u_sys = st_uniform(&r); }
+  }
+  for (int64_t k = 0; k < n_new; ++k) {
+    uint64_t thr;
+    if (mode == 1) {
+      uint64_t U0 = (uint64_t)(u_sys * 4294967296.0);
+      if (U0 > 0xFFFFFFFFull) U0 = 0xFFFFFFFFull;
+      u128 num = ((((u128)(uint64_t)k) << 32) | U0) * (u128)total;
+      u128 den = ((u128)(uint64_t)n_new) << 32;
+      thr = (uint64_t)(num / den);
+    } else {
+      double u;
+      if (uniforms) u = uniforms[k];
+      else { orc_stream r; st_init(&r, seed, (uint64_t)k, step); u = st_uniform(&r); }
+      uint64_t U = (uint64_t)(u * 9007199254740992.0);
+      if (U > 9007199254740991ull) U = 9007199254740991ull;
+      thr = (uint64_t)(((u128)U * (u128)total) >> 53);
+    }
+    anc[k] = (int32_t)upper_bound(cdf, n, thr);
+  }
+  free(cdf);
+}
+
+/* mh.py:187-208 */
+static double mh_log_alpha(double rho, double xi) {
+  if (rho == -INFINITY && xi == -INFINITY) return INFINITY;
+  if (rho == INFINITY && xi == INFINITY) return -INFINITY;
+  return xi - rho;
+}
+
+/* ------------------------------------------------- C1: normal-normal */
+static double nn_absorb(const double *y, int64_t k0, int64_t k1, double x, double s) {
+  double w = 0;  /* regen.py:120-127 absorb: weight += logDensity(obs | x) */
+  for (int64_t k = k0; k < k1; ++k) w += normal_logpdf(y[k], x, s);
+  return w;
+}
+/* lite/trace.py:522-530 */
+void orc_nn_likelihood_weight(double *x, double *lw, const double *y, int64_t n_obs, int64_t P,
+                              int64_t p_base, double mu0, double s0, double s, uint64_t seed, uint32_t step) {
+#pragma omp parallel for schedule(static)
+  for (int64_t p = 0; p < P; ++p) {
+    orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step);
+    x[p] = normal_sim(&r, mu0, s0);
+    if (lw) lw[p] = nn_absorb(y, 0, n_obs, x[p], s);
+  }
+}
+/* lite/trace.py:422-448 */
+void orc_nn_make_consistent(const double *x, double *lw, double *incr, const double *y, int64_t k0,
+                            int64_t k1, int64_t P, double s) {
+#pragma omp parallel for schedule(static)
+  for (int64_t p = 0; p < P; ++p) {
+    double w = nn_absorb(y, k0, k1, x[p], s);
+    if (w != w) w = -INFINITY;
+    if (incr) incr[p] = w;
+    lw[p] += w;
+  }
+}
+/* infer/mh.py:59-113 with MHOperator (:187-208); K transitions */
+void orc_nn_mh(double *x, const double *y, int64_t n_obs, int64_t P, int64_t p_base, double mu0, double s0,
+               double s, uint64_t seed, uint32_t step0, int K, int64_t *acc) {
+#pragma omp parallel for schedule(static)
+  for (int64_t p = 0; p < P; ++p) {
+    int64_t a = 0;
+    for (int t = 0; t < K; ++t) {
+      orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step0 + (uint32_t)t);
+      (void)st_uniform(&r);                       /* sampleBlock: a single block */
+      double logu = log(st_uniform(&r));          /* mh.py:85 */
+      double rho = nn_absorb(y, 0, n_obs, x[p], s);      /* detachAndExtract */
+      double xn = normal_sim(&r, mu0, s0);               /* regen: simulate from prior */
+      double xi = nn_absorb(y, 0, n_obs, xn, s);
+      double alpha = mh_log_alpha(rho, xi);
+      if (logu < alpha) { x[p] = xn; ++a; }
+    }
+    if (acc) acc[p] = a;
+  }
+}
+void orc_nn_log_likelihood_at(const double *x, const double *y, int64_t n_obs, int64_t P, double mu0,
+                              double s0, double s, int joint, double *out) {
+  for (int64_t p = 0; p < P; ++p) {
+    double v = nn_absorb(y, 0, n_obs, x[p], s);
+    if (joint) v += normal_logpdf(x[p], mu0, s0);
+    out[p] = v;
+  }
+}
+
+/* ------------------------------------------- C2: logistic regression */
+/* w[D][P] particle-minor; X[N][D] row-major; y[N] bytes.
+ * eta_i = vector_dot(w, x_i) (vectors.py:159-177); obs density
+ * log_logistic(y ? eta : -eta) (discrete.py:148-150). */
+static double blr_eta(const double *wp, const double *xi, int D) {
+  double e = 0;
+  for (int j = 0; j < D; ++j) e += wp[j] * xi[j];
+  return e;
+}
+static double blr_loglik_range(const double *wp, const double *X, const uint8_t *y, int D, int64_t i0, int64_t i1) {
+  double acc = 0;
+  for (int64_t i = i0; i < i1; ++i) {
+    double e = blr_eta(wp, X + i * D, D);
+    acc += orc_log_logistic(y[i] ? e : -e);
+  }
+  return acc;
+}
+void orc_blr_log_likelihood(const double *w, const double *X, const uint8_t *y, int D, int64_t i0, int64_t i1,
+                            int64_t P, double *out) {
+#pragma omp parallel for schedule(static)
+  for (int64_t p = 0; p < P; ++p) {
+    double wp[256];
+    for (int j = 0; j < D; ++j) wp[j] = w[(int64_t)j * P + p];
+    out[p] = blr_loglik_range(wp, X, y, D, i0, i1);
+  }
+}
+/* likelihood_weight / reset_to_prior: site j uses draws 2j, 2j+1 */
+void orc_blr_prior(double *w, int D, int64_t P, int64_t p_base, double mu0, double s0, uint64_t seed, uint32_t step) {
+#pragma omp parallel for schedule(static)
+  for (int64_t p = 0; p < P; ++p)
+    for (int j = 0; j < D; ++j) {
+      orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step); st_seek(&r, 2u * (uint32_t)j);
+      w[(int64_t)j * P + p] = normal_sim(&r, mu0, s0);
+    }
+}
+/* block_mode: -1 one, -3 each, -2 all, >=0 fixed site. n_steps proposals. */
+void orc_blr_mh(double *w, const double *X, const uint8_t *y, int D, int64_t N, int64_t P, int64_t p_base,
+                double mu0, double s0, uint64_t seed, uint32_t step0, int n_steps, int block_mode,
+                int64_t *acc, double *ll_out) {
+#pragma omp parallel for schedule(dynamic, 1)
+  for (int64_t p = 0; p < P; ++p) {
+    double wp[256], wn[256];
+    for (int j = 0; j < D; ++j) wp[j] = w[(int64_t)j * P + p];
+    double *eta = (double *)malloc((size_t)N * sizeof(double));
+    for (int64_t i = 0; i < N; ++i) eta[i] = blr_eta(wp, X + i * D, D);
+    int64_t a = 0;
+    for (int t = 0; t < n_steps; ++t) {
+      orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step0 + (uint32_t)t);
+      double u_sel = st_uniform(&r);
+      double logu = log(st_uniform(&r));
+      /* detach: rho = sum of the absorbing children's logDensity at the cached dots */
+      double rho = 0;
+      for (int64_t i = 0; i < N; ++i) rho += orc_log_logistic(y[i] ? eta[i] : -eta[i]);
+      memcpy(wn, wp, sizeof(double) * (size_t)D);
+      if (block_mode == -2) {
+        for (int j = 0; j < D; ++j) { st_seek(&r, 2u + 2u * (uint32_t)j); wn[j] = normal_sim(&r, mu0, s0); }
+      } else {
+        int j;
+        if (block_mode == -1) { j = (int)(u_sel * D); if (j >= D) j = D - 1; }  /* trace.py:320 sampleBlock */
+        else if (block_mode == -3) j = t % D;
+        else j = block_mode;
+        wn[j] = normal_sim(&r, mu0, s0);
+      }
+      /* regen: every vector_dot node recomputed, every flip absorbs */
+      double xi = 0;
+      for (int64_t i = 0; i < N; ++i) { double e = blr_eta(wn, X + i * D, D); xi += orc_log_logistic(y[i] ? e : -e); }
+      if (logu < mh_log_alpha(rho, xi)) {
+        memcpy(wp, wn, sizeof(double) * (size_t)D);
+        for (int64_t i = 0; i < N; ++i) eta[i] = blr_eta(wp, X + i * D, D);
+        ++a;
+      }
+    }
+    for (int j = 0; j < D; ++j) w[(int64_t)j * P + p] = wp[j];
+    if (acc) acc[p] = a;
+    if (ll_out) { double v = 0; for (int64_t i = 0; i < N; ++i) v += orc_log_logistic(y[i] ? eta[i] : -eta[i]); ll_out[p] = v; }
+    free(eta);
+  }
+}
+
+/* ------------------------------------------------ subsampled MH pieces */
+/* regularised incomplete beta I_x(a,b) (continued fraction, modified Lentz);
+ * stands in for scipy.stats.t.cdf (infer/subsampled_mh.py:161). */
+static double betacf(double a, double b, double x) {
+  const double TINY = 1e-300, EPS = 1e-16;
+  double qab = a + b, qap = a + 1, qam = a - 1, c = 1, d = 1 - qab * x / qap;
+  if (fabs(d) < TINY) d = TINY;
+  d = 1 / d;
+  double h = d;
+  for (int m = 1; m <= 10000; ++m) {
+    int m2 = 2 * m;
+    double aa = m * (b - m) * x / ((qam + m2) * (a + m2));
+    d = 1 + aa * d; if (fabs(d) < TINY) d = TINY;
+    c = 1 + aa / c; if (fabs(c) < TINY) c = TINY;
+    d = 1 / d; h *= d * c;
+    aa = -(a + m) * (qab + m) * x / ((a + m2) * (qap + m2));
+    d = 1 + aa * d; if (fabs(d) < TINY) d = TINY;
+    c = 1 + aa / c; if (fabs(c) < TINY) c = TINY;
+    d = 1 / d;
+    double del = d * c;
+    h *= del;
+    if (fabs(del - 1) < EPS) break;
+  }
+  return h;
+}
+static double betainc(double a, double b, double x) {
+  if (x <= 0) return 0;
+  if (x >= 1) return 1;
+  double bt = exp(lgamma(a + b) - lgamma(a) - lgamma(b) + a * log(x) + b * log1p(-x));
+  if (x < (a + 1) / (a + b + 2)) return bt * betacf(a, b, x) / a;
+  return 1 - bt * betacf(b, a, 1 - x) / b;
+}
+double orc_student_t_cdf(double t, double df) {
+  if (t != t) return NAN;
+  if (isinf(t)) return t > 0 ? 1 : 0;
+  double x = df / (df + t * t);
+  double tail = 0.5 * betainc(0.5 * df, 0.5, x);
+  return t > 0 ? 1 - tail : tail;
+}
+
+/* infer/subsampled_mh.py:118-171 sequentialTest, with fun_dllh(i) = dllh[i].
+ * Returns accept; *n_out = sections consumed; *tstat_out as in :170. */
+int orc_sequential_test(double mu_0, int k0, double Nbatch, double N, double epsilon, const double *dllh,
+                        double *n_out, double *tstat_out) {
+  double mx = 0, mx2 = 0, k = 0, n = 0, cum = 0, cum2 = 0, tstat = 0;
+  int have_t = 0, accept = -1;
+  while (n < N) {
+    double n_start = n, n_end = fmin(n + Nbatch, N);
+    for (int64_t i = (int64_t)n_start; i < (int64_t)n_end; ++i) { cum += dllh[i]; cum2 += dllh[i] * dllh[i]; }
+    k += 1; n = n_end; mx = cum / n_end; mx2 = cum2 / n_end;
+    if (k < k0 && n < N) continue;
+    if (n == N) { accept = mx >= mu_0; break; }
+    double sx = sqrt((1 - (n - 1) / (N - 1)) * (mx2 - mx * mx) / (n - 1));
+    double q;
+    if (sx == 0) q = mx >= mu_0 ? 1 : 0;
+    else { tstat = (mx - mu_0) / sx; have_t = 1; q = orc_student_t_cdf(tstat, n - 1); }
+    if (q < epsilon) { accept = 0; break; }
+    else if (q > 1 - epsilon) { accept = 1; break; }
+  }
+  *n_out = n;
+  /* :170  tstat if tstat else (+inf if accept else -inf); python truthiness: 0.0 counts as "no" */
+  *tstat_out = (have_t && tstat != 0) ? tstat : (accept ? INFINITY : -INFINITY);
+  return accept;
+}

@@ -1,0 +1,108 @@
+"""GPU parity: logsumexp / normalised probs / resampling vs the oracle.
+Reference semantics: backend/lite/utils.py:70-118,152-180; trace_set.py:202-235."""
+import ctypes
+import math
+
+import numpy as np
+import pytest
+
+import venturecxx_b200 as vb
+from venturecxx_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+
+
+def gpu_lse(a):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    out = ctypes.c_double()
+    _lib.call("vk_logsumexp_array", _lib.ptr(a) if a.size else None, a.size, 0, ctypes.byref(out))
+    return out.value
+
+
+def test_logsumexp_reference_vectors():
+    # test/unit/test_explog.py:86-100
+    inf, nan = float("inf"), float("nan")
+    assert abs(gpu_lse(np.arange(1000.0)) - 999.4586751453871) / 999.4586751453871 < 1e-15
+    assert gpu_lse([]) == -inf
+    assert gpu_lse([-1000.0]) == -1000.0
+    assert gpu_lse([-1000.0, -1000.0]) == -1000.0 + math.log(2.0)
+    assert abs(gpu_lse([0.0, 0.0]) - math.log(2.0)) / math.log(2.0) < 1e-15
+    assert gpu_lse([-inf, 1]) == 1
+    assert gpu_lse([-inf, -inf]) == -inf
+    assert gpu_lse([inf, inf]) == inf
+    assert math.isnan(gpu_lse([-inf, inf]))
+    assert math.isnan(gpu_lse([nan, inf]))
+    assert math.isnan(gpu_lse([nan, -3]))
+
+
+@pytest.mark.parametrize("n", [1, 31, 1000, 4097, 1 << 18])
+def test_logsumexp_vs_oracle(orc, n):
+    rng = np.random.default_rng(n)
+    a = rng.normal(-50, 30, n)
+    ref = orc.logsumexp(a)
+    assert abs(gpu_lse(a) - ref) <= 1e-12 * abs(ref)
+
+
+def make_ts(P, seed=7):
+    return vb.B200TraceSet(vb.NormalNormalModel(), P, seed=seed)
+
+
+@pytest.mark.parametrize("P", [1, 5, 1000, 2049, 1 << 16])
+@pytest.mark.parametrize("mode", ["systematic", "multinomial"])
+def test_resample_ancestors_bit_exact(orc, P, mode):
+    rng = np.random.default_rng(P)
+    ts = make_ts(P)
+    lw = rng.normal(0, 3, P)
+    if P > 4:
+        lw[1] = -np.inf
+    ts.set_particle_log_weights(lw)
+    x_before = ts.read_site(0)
+    step = ts.rng_step
+    anc = ts.resample(P, mode=mode, return_ancestors=True)
+    ref = orc.ancestors(lw, P, 1 if mode == "systematic" else 0, seed=7, step=step)
+    assert np.array_equal(anc, ref)
+    if mode == "systematic":
+        assert np.all(np.diff(anc) >= 0)
+    # ancestor state copied, weights evened out (utils.py:152-157)
+    assert np.array_equal(ts.read_site(0), x_before[anc])
+    lse = orc.logsumexp(lw)
+    np.testing.assert_allclose(ts.log_weights, np.full(P, lse - math.log(P)), rtol=1e-12)
+    if P > 4:
+        assert 1 not in set(anc.tolist())
+
+
+def test_resample_given_uniforms(orc):
+    P = 1000
+    rng = np.random.default_rng(3)
+    lw = rng.normal(0, 2, P)
+    ts = make_ts(P)
+    ts.set_particle_log_weights(lw)
+    anc = ts.resample(P, mode="systematic", uniforms=[0.25], return_ancestors=True)
+    assert np.array_equal(anc, orc.ancestors(lw, P, 1, uniforms=[0.25]))
+    ts.set_particle_log_weights(lw)
+    u = rng.random(P)
+    anc = ts.resample(P, mode="multinomial", uniforms=u, return_ancestors=True)
+    assert np.array_equal(anc, orc.ancestors(lw, P, 0, uniforms=u))
+
+
+def test_resample_all_impossible_is_uniform(orc):
+    # utils.py:93-99,176-180: all -inf => every parent equally likely
+    P = 512
+    ts = make_ts(P)
+    ts.set_particle_log_weights(np.full(P, -np.inf))
+    anc = ts.resample(P, mode="systematic", return_ancestors=True)
+    assert np.array_equal(anc, np.arange(P))
+    assert np.all(ts.log_weights == -np.inf)
+
+
+def test_normalized_probs(orc):
+    P = 777
+    rng = np.random.default_rng(5)
+    lw = rng.normal(0, 5, P)
+    lw[3] = -np.inf
+    ts = make_ts(P)
+    ts.set_particle_log_weights(lw)
+    np.testing.assert_allclose(ts.particle_normalized_probs(), orc.normalized_probs(lw), rtol=1e-12)
+    ts.set_particle_log_weights(np.full(P, -np.inf))
+    assert np.all(ts.particle_normalized_probs() == 0)
+    assert ts.logsumexp() == -np.inf

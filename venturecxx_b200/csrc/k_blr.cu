@@ -1,0 +1,402 @@
+// Configs C2/C5: Bayesian logistic regression
+//   assume w_j = normal(mu0, s0)  (j < D);  assume w = array(w_0 .. w_{D-1})
+//   observe log_odds_flip(vector_dot(w, x_i)) = y_i          (i < N)
+// Site program derived from the reference's scaffold rules:
+//   scaffold(w_j): DRG {w_j, its lookup, the array node, N lookups of w,
+//                  N vector_dot nodes}; absorbing {N log_odds_flip nodes}.
+//   rho = sum_i log_logistic(+-eta_i)         (detach.py:72-83, discrete.py:148-150)
+//   xi  = sum_i log_logistic(+-eta'_i), eta'_i = eta_i + (w'_j - w_j) x_ij
+//                                             (regen.py:120-127, utils.py:257-268)
+//   accept iff log u < xi - rho               (infer/mh.py:84-89, 187-208)
+//
+// HBM layout
+//   Xs  [D][Ncap]  signed features  s_i * x_ij  (s_i = +1 iff y_i) -- shared by
+//                  all particles, 1.3 MB at C2 => L2 resident
+//   w   [D][P]     particle-minor weights
+//   eta [P][Ncap]  particle-major signed logits  s_i * (w . x_i)  (the cache
+//                  that replaces the N vector_dot nodes of every trace)
+//   ll  [P]        current sum_i log_logistic(eta_i) (= rho of the next proposal)
+//
+// Kernel mapping: ONE CTA PER PARTICLE, persistent over particles.  The CTA
+// stages its 8N-byte logit row in shared memory ONCE, runs all K transitions
+// of the launch on chip (each transition streams one 8N-byte Xs column from
+// L2), and writes the row back once.  Algorithmic HBM traffic per launch is
+// therefore 2*8N B per particle instead of 8N(1+a) per transition; the
+// kernel is fp64-ALU bound (exp + log1p per observation), see DESIGN.md.
+#include "vk_common.cuh"
+#include "sp_math.cuh"
+
+namespace vk {
+
+struct BLRParams { double mu0, s0; int D; int64_t N, Ncap; };
+
+__device__ __forceinline__ double blr_log_alpha(double rho, double xi) {
+  if (rho == -INFINITY && xi == -INFINITY) return INFINITY;   // mh.py:190-197
+  if (rho == INFINITY && xi == INFINITY) return -INFINITY;    // mh.py:198-206
+  return xi - rho;
+}
+
+// eta_i = sum_j w_j Xs[j][i] for i in [i0,i1); returns this thread's partial
+// sum of log_logistic(eta_i).  w in shared memory.
+__device__ __forceinline__ double blr_fill_eta(double *__restrict__ eta_row,
+                                               const double *__restrict__ Xs, const double *w_sh,
+                                               int D, int64_t Ncap, int64_t i0, int64_t i1) {
+  double acc = 0.0;
+  for (int64_t i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+    double e = 0.0;
+    for (int j = 0; j < D; ++j) e = fma(w_sh[j], __ldg(&Xs[(int64_t)j * Ncap + i]), e);
+    eta_row[i] = e;
+    acc += log_logistic(e);
+  }
+  return acc;
+}
+
+// mode 0: reset_to_prior (w ~ prior, eta/ll over propagated obs, weights untouched)
+// mode 1: likelihood_weight (as 0 and lw := ll)            lite/trace.py:522-530
+// mode 2: refresh (keep w; recompute eta and ll)
+// mode 3: make_consistent over [n_prop, N): eta for new obs, incr, lw += incr, ll += incr
+__global__ void __launch_bounds__(256)
+blr_all_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restrict__ ll,
+               double *__restrict__ lw, double *__restrict__ incr,
+               const double *__restrict__ Xs, BLRParams prm, int64_t n_prop, int64_t P,
+               int64_t p_base, uint64_t seed, uint32_t step, int mode) {
+  extern __shared__ double smem[];
+  double *w_sh = smem;            // D
+  double *red = smem + prm.D;     // 33
+  for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
+    __syncthreads();
+    if ((int)threadIdx.x < prm.D) {
+      int j = threadIdx.x;
+      double v;
+      if (mode <= 1) {
+        Stream r(seed, (uint64_t)(p_base + p), step);
+        r.seek(2u * (uint32_t)j);
+        v = normal_sim(r, prm.mu0, prm.s0);
+        w[(int64_t)j * P + p] = v;
+      } else {
+        v = w[(int64_t)j * P + p];
+      }
+      w_sh[j] = v;
+    }
+    __syncthreads();
+    int64_t i0 = (mode == 3) ? n_prop : 0;
+    int64_t i1 = (mode == 3) ? prm.N : n_prop;
+    double part = blr_fill_eta(eta + p * prm.Ncap, Xs, w_sh, prm.D, prm.Ncap, i0, i1);
+    double tot = block_sum(part, red);
+    if (threadIdx.x == 0) {
+      if (mode == 3) {
+        double inc = tot;
+        if (inc != inc) inc = -INFINITY;  // lite/trace.py:438-448
+        if (incr) incr[p] = inc;
+        lw[p] += inc;
+        ll[p] += tot;
+      } else {
+        ll[p] = tot;
+        if (mode == 1) lw[p] = tot;
+      }
+    }
+  }
+}
+
+// K resimulation-MH transitions per particle, eta row staged in shared memory
+// (SMEM=true) or streamed from global memory every transition (SMEM=false,
+// rows too large for shared memory).
+// block_mode: VK_BLOCK_ONE (uniform site per transition), VK_BLOCK_EACH
+// (site = t mod D), or a fixed site index >= 0.
+template <bool SMEM>
+__global__ void __launch_bounds__(256)
+blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restrict__ ll,
+              const double *__restrict__ Xs, BLRParams prm, int64_t P, int64_t p_base,
+              uint64_t seed, uint32_t step0, int n_prop_steps, int block_mode,
+              long long *__restrict__ acc_out) {
+  extern __shared__ double smem[];
+  double *w_sh = smem;                 // D (padded to even)
+  double *red = w_sh + ((prm.D + 1) & ~1);  // 34
+  double *eta_sh = red + 34;           // N (SMEM only)
+  const int64_t N = prm.N;
+  for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
+    __syncthreads();
+    double *eta_g = eta + p * prm.Ncap;
+    if ((int)threadIdx.x < prm.D) w_sh[threadIdx.x] = w[(int64_t)threadIdx.x * P + p];
+    if (SMEM) {
+      // Ncap is even and rows are 16-byte aligned: 16-byte vector copies
+      const double2 *src = reinterpret_cast<const double2 *>(eta_g);
+      double2 *dst = reinterpret_cast<double2 *>(eta_sh);
+      for (int64_t i = threadIdx.x; i < (N + 1) / 2; i += blockDim.x) dst[i] = src[i];
+    }
+    double *e_cur = SMEM ? eta_sh : eta_g;
+    double rho = ll[p];
+    long long acc = 0;
+    bool dirty = false;
+    __syncthreads();
+    for (int t = 0; t < n_prop_steps; ++t) {
+      // every thread derives the same proposal from the particle's stream
+      Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)t);
+      double u_sel = r.uniform();
+      double u_acc = r.uniform();
+      int j;
+      if (block_mode == VK_BLOCK_ONE) { j = (int)(u_sel * (double)prm.D); if (j >= prm.D) j = prm.D - 1; }
+      else if (block_mode == VK_BLOCK_EACH) j = t % prm.D;
+      else j = block_mode;
+      double w_new = normal_sim(r, prm.mu0, prm.s0);
+      double delta = w_new - w_sh[j];
+      const double *xcol = Xs + (int64_t)j * prm.Ncap;
+      double part = 0.0;
+      for (int64_t i = threadIdx.x; i < N; i += blockDim.x)
+        part += log_logistic(fma(delta, __ldg(&xcol[i]), e_cur[i]));
+      double xi = block_sum(part, red);
+      double alpha = blr_log_alpha(rho, xi);
+      if (log(u_acc) < alpha) {   // uniform across the CTA
+        for (int64_t i = threadIdx.x; i < N; i += blockDim.x)
+          e_cur[i] = fma(delta, __ldg(&xcol[i]), e_cur[i]);
+        __syncthreads();
+        if (threadIdx.x == 0) w_sh[j] = w_new;
+        rho = xi; ++acc; dirty = true;
+        __syncthreads();
+      }
+    }
+    if (dirty) {
+      if (SMEM) {
+        const double2 *src = reinterpret_cast<const double2 *>(eta_sh);
+        double2 *dst = reinterpret_cast<double2 *>(eta_g);
+        for (int64_t i = threadIdx.x; i < (N + 1) / 2; i += blockDim.x) dst[i] = src[i];
+      }
+      if ((int)threadIdx.x < prm.D) w[(int64_t)threadIdx.x * P + p] = w_sh[threadIdx.x];
+      if (threadIdx.x == 0) ll[p] = rho;
+    }
+    if (acc_out && threadIdx.x == 0) acc_out[p] = acc;
+  }
+}
+
+// block = all: joint proposal of every weight from the prior (one scaffold
+// with D principal nodes).  eta' is recomputed into a scratch row.
+__global__ void __launch_bounds__(256)
+blr_mh_all_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restrict__ ll,
+                  const double *__restrict__ Xs, BLRParams prm, int64_t P, int64_t p_base,
+                  uint64_t seed, uint32_t step0, int K, long long *__restrict__ acc_out) {
+  extern __shared__ double smem[];
+  double *w_sh = smem;                       // D
+  double *red = w_sh + ((prm.D + 1) & ~1);   // 34
+  const int64_t N = prm.N;
+  for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
+    double rho = ll[p];
+    long long acc = 0;
+    for (int t = 0; t < K; ++t) {
+      __syncthreads();
+      Stream r0(seed, (uint64_t)(p_base + p), step0 + (uint32_t)t);
+      (void)r0.uniform();
+      double u_acc = r0.uniform();
+      if ((int)threadIdx.x < prm.D) {
+        Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)t);
+        r.seek(2u + 2u * threadIdx.x);
+        w_sh[threadIdx.x] = normal_sim(r, prm.mu0, prm.s0);
+      }
+      __syncthreads();
+      double part = 0.0;
+      for (int64_t i = threadIdx.x; i < N; i += blockDim.x) {
+        double e = 0.0;
+        for (int j = 0; j < prm.D; ++j) e = fma(w_sh[j], __ldg(&Xs[(int64_t)j * prm.Ncap + i]), e);
+        part += log_logistic(e);
+      }
+      double xi = block_sum(part, red);
+      double alpha = blr_log_alpha(rho, xi);
+      if (log(u_acc) < alpha) {
+        double *eta_g = eta + p * prm.Ncap;
+        for (int64_t i = threadIdx.x; i < N; i += blockDim.x) {
+          double e = 0.0;
+          for (int j = 0; j < prm.D; ++j) e = fma(w_sh[j], __ldg(&Xs[(int64_t)j * prm.Ncap + i]), e);
+          eta_g[i] = e;
+        }
+        if ((int)threadIdx.x < prm.D) w[(int64_t)threadIdx.x * P + p] = w_sh[threadIdx.x];
+        rho = xi; ++acc;
+      }
+    }
+    if (threadIdx.x == 0) { ll[p] = rho; if (acc_out) acc_out[p] = acc; }
+  }
+}
+
+// log_likelihood_at / log_joint_at: recompute from the logit cache (non-mutating)
+__global__ void __launch_bounds__(256)
+blr_loglik_at_kernel(const double *__restrict__ w, const double *__restrict__ eta,
+                     BLRParams prm, int64_t P, int joint_block, double *__restrict__ out) {
+  __shared__ double red[34];
+  for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
+    const double *e = eta + p * prm.Ncap;
+    double part = 0.0;
+    for (int64_t i = threadIdx.x; i < prm.N; i += blockDim.x) part += log_logistic(e[i]);
+    double tot = block_sum(part, red);
+    if (threadIdx.x == 0) {
+      // joint: + prior density of the principal node(s) (dispatch.py:345-361)
+      if (joint_block == VK_BLOCK_ALL) {
+        for (int j = 0; j < prm.D; ++j) tot += normal_logpdf(w[(int64_t)j * P + p], prm.mu0, prm.s0);
+      } else if (joint_block >= 0) {
+        tot += normal_logpdf(w[(int64_t)joint_block * P + p], prm.mu0, prm.s0);
+      }
+      out[p] = tot;
+    }
+  }
+}
+
+__global__ void blr_sign_features_kernel(const double *__restrict__ Xrows, const uint8_t *__restrict__ y,
+                                         double *__restrict__ Xs, int D, int64_t Ncap, int64_t i_base,
+                                         int64_t n) {
+  int64_t total = n * D;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (int64_t)gridDim.x * blockDim.x) {
+    int64_t i = t / D; int j = (int)(t - i * D);
+    double s = y[i] ? 1.0 : -1.0;
+    Xs[(int64_t)j * Ncap + i_base + i] = s * Xrows[t];
+  }
+}
+
+__global__ void blr_fill_const_kernel(double *out, int64_t n, double v) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = v;
+}
+
+struct BLRModel : Model {
+  BLRParams prm;
+  int64_t n_prop = 0;
+  DevBuf<double> Xs, wa, wb, etaa, etab, lla, llb;
+  DevBuf<uint8_t> y;
+  double *w = nullptr, *w_alt = nullptr, *eta = nullptr, *eta_alt = nullptr, *ll = nullptr, *ll_alt = nullptr;
+  int smem_limit = 0;
+
+  BLRModel(vk_particles *h_, int D, int64_t Ncap, double mu0, double s0) : Model(h_) {
+    VK_REQUIRE(D >= 1 && D <= 256, VK_EINVAL, "blr: D must be in [1,256]");
+    VK_REQUIRE(Ncap >= 1, VK_EINVAL, "blr: observation capacity must be positive");
+    prm.mu0 = mu0; prm.s0 = s0; prm.D = D; prm.N = 0; prm.Ncap = (Ncap + 1) & ~(int64_t)1;
+    Xs.alloc((size_t)D * prm.Ncap);
+    y.alloc((size_t)prm.Ncap);
+    wa.alloc((size_t)D * h->P);
+    etaa.alloc((size_t)h->P * prm.Ncap);
+    lla.alloc((size_t)h->P);
+    w = wa.p; eta = etaa.p; ll = lla.p;
+    VK_CUDA(cudaMemsetAsync(w, 0, wa.bytes(), h->stream));
+    VK_CUDA(cudaMemsetAsync(ll, 0, lla.bytes(), h->stream));
+    VK_CUDA(cudaDeviceGetAttribute(&smem_limit, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+    VK_CUDA(cudaFuncSetAttribute(blr_mh_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_limit));
+  }
+  void observe(const double *X_rows_host, const uint8_t *y_host, int64_t n) {
+    VK_REQUIRE(prm.N + n <= prm.Ncap, VK_EINVAL, "blr: observation capacity exceeded");
+    DevBuf<double> stage; stage.alloc((size_t)n * prm.D);
+    VK_CUDA(cudaMemcpyAsync(stage.p, X_rows_host, stage.bytes(), cudaMemcpyHostToDevice, h->stream));
+    VK_CUDA(cudaMemcpyAsync(y.p + prm.N, y_host, (size_t)n, cudaMemcpyHostToDevice, h->stream));
+    blr_sign_features_kernel<<<grid_for(n * prm.D, 256, h->sm_count, 8), 256, 0, h->stream>>>(
+        stage.p, y.p + prm.N, Xs.p, prm.D, prm.Ncap, prm.N, n);
+    VK_CUDA(cudaGetLastError());
+    VK_CUDA(cudaStreamSynchronize(h->stream));
+    prm.N += n;
+  }
+  int grid_particles(int ctas_per_sm) const {
+    int64_t cap = (int64_t)h->sm_count * ctas_per_sm;
+    return (int)(h->P < cap ? h->P : cap);
+  }
+  void launch_all(int mode, double *incr_dev, uint32_t step) {
+    size_t sm = (size_t)(prm.D + 34) * sizeof(double);
+    blr_all_kernel<<<grid_particles(8), 256, sm, h->stream>>>(w, eta, ll, h->lw.p, incr_dev, Xs.p, prm,
+                                                              n_prop, h->P, h->p_base, h->seed, step, mode);
+    VK_CUDA(cudaGetLastError());
+  }
+  void reset_to_prior() override { launch_all(0, nullptr, h->next_step()); }
+  void likelihood_weight() override {
+    n_prop = prm.N;
+    launch_all(1, nullptr, h->next_step());
+  }
+  void refresh() override { launch_all(2, nullptr, 0); }
+  void make_consistent(double *incr_dev) override {
+    if (n_prop == prm.N) {
+      if (incr_dev) VK_CUDA(cudaMemsetAsync(incr_dev, 0, (size_t)h->P * sizeof(double), h->stream));
+      return;
+    }
+    launch_all(3, incr_dev, 0);
+    n_prop = prm.N;
+  }
+  void mh(int scope, int block, int K, double *mean_nodes_dev, long long *acc_dev) override {
+    VK_REQUIRE(scope == 0, VK_EINVAL, "blr: only the default scope exists");
+    VK_REQUIRE(block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || block == VK_BLOCK_ALL ||
+                   (block >= 0 && block < prm.D), VK_EINVAL, "blr: bad block");
+    VK_REQUIRE(n_prop == prm.N, VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
+    double nodes = 0.0;
+    if (K > 0) {
+      if (block == VK_BLOCK_ALL) {
+        uint32_t step0 = h->next_step((uint32_t)K);
+        size_t sm = (size_t)(((prm.D + 1) & ~1) + 34) * sizeof(double);
+        blr_mh_all_kernel<<<grid_particles(8), 256, sm, h->stream>>>(w, eta, ll, Xs.p, prm, h->P, h->p_base,
+                                                                     h->seed, step0, K, acc_dev);
+        nodes = (double)(prm.D * 2 + 1 + 2 * prm.N);
+      } else {
+        int n_steps = (block == VK_BLOCK_EACH) ? K * prm.D : K;
+        uint32_t step0 = h->next_step((uint32_t)n_steps);
+        size_t base = (size_t)(((prm.D + 1) & ~1) + 34) * sizeof(double);
+        size_t need = base + (size_t)((prm.N + 1) & ~(int64_t)1) * sizeof(double);
+        if (need <= (size_t)smem_limit) {
+          int per_sm = (int)((size_t)(227 * 1024) / (need + 1024));
+          if (per_sm < 1) per_sm = 1;
+          if (per_sm > 8) per_sm = 8;
+          blr_mh_kernel<true><<<grid_particles(per_sm), 256, need, h->stream>>>(
+              w, eta, ll, Xs.p, prm, h->P, h->p_base, h->seed, step0, n_steps, block, acc_dev);
+        } else {
+          blr_mh_kernel<false><<<grid_particles(8), 256, base, h->stream>>>(
+              w, eta, ll, Xs.p, prm, h->P, h->p_base, h->seed, step0, n_steps, block, acc_dev);
+        }
+        // |DRG| of scaffold(w_j) = w_j + lookup + array + N lookups + N dots;
+        // 'each' sums D proposals per transition (dispatch.py:122-128)
+        nodes = (double)(3 + 2 * prm.N) * (block == VK_BLOCK_EACH ? prm.D : 1);
+      }
+      VK_CUDA(cudaGetLastError());
+    }
+    if (mean_nodes_dev) {
+      blr_fill_const_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, nodes);
+      VK_CUDA(cudaGetLastError());
+    }
+  }
+  void log_likelihood_at(int scope, int block, bool joint, double *out_dev) override {
+    VK_REQUIRE(scope == 0, VK_EINVAL, "blr: only the default scope exists");
+    VK_REQUIRE(block == VK_BLOCK_ALL || (block >= 0 && block < prm.D), VK_EINVAL,
+               "log_likelihood_at: block must be all or a site index");
+    BLRParams q = prm; q.N = n_prop;
+    blr_loglik_at_kernel<<<grid_particles(8), 256, 0, h->stream>>>(w, eta, q, h->P, joint ? block : -100, out_dev);
+    VK_CUDA(cudaGetLastError());
+  }
+  void forget_observations(double *w_dev) override {
+    if (w_dev) log_likelihood_at(0, VK_BLOCK_ALL, false, w_dev);
+    prm.N = 0; n_prop = 0;
+    VK_CUDA(cudaMemsetAsync(ll, 0, (size_t)h->P * sizeof(double), h->stream));
+  }
+  int64_t num_sites() const override { return prm.D; }
+  int64_t num_blocks(int) const override { return prm.D; }
+  void read_site(int64_t site, double *out_dev) override {
+    VK_REQUIRE(site >= 0 && site < prm.D, VK_EINVAL, "blr: site out of range");
+    VK_CUDA(cudaMemcpyAsync(out_dev, w + site * h->P, (size_t)h->P * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  }
+  void write_site(int64_t site, const double *in_dev) override {
+    VK_REQUIRE(site >= 0 && site < prm.D, VK_EINVAL, "blr: site out of range");
+    VK_CUDA(cudaMemcpyAsync(w + site * h->P, in_dev, (size_t)h->P * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  }
+  std::vector<StateArray> state_arrays() override {
+    // back buffers are allocated on first resample (eta doubles the footprint)
+    if (!wb.p) { wb.alloc(wa.n); etab.alloc(etaa.n); llb.alloc(lla.n); w_alt = wb.p; eta_alt = etab.p; ll_alt = llb.p; }
+    StateArray a{(void **)&w, (void **)&w_alt, 0, (size_t)prm.D, 8};
+    StateArray b{(void **)&eta, (void **)&eta_alt, (size_t)prm.Ncap * 8, 0, 0};
+    StateArray c{(void **)&ll, (void **)&ll_alt, 0, 1, 8};
+    return {a, b, c};
+  }
+  int device_buffer(int which, void **p, int64_t *bytes) override {
+    if (which == 1) { *p = w; *bytes = (int64_t)wa.bytes(); return VK_OK; }
+    if (which == 2) { *p = eta; *bytes = (int64_t)etaa.bytes(); return VK_OK; }
+    if (which == 3) { *p = ll; *bytes = (int64_t)lla.bytes(); return VK_OK; }
+    if (which == 4) { *p = Xs.p; *bytes = (int64_t)Xs.bytes(); return VK_OK; }
+    return VK_EINVAL;
+  }
+};
+
+Model *make_blr(vk_particles *h, int D, int64_t Ncap, double mu0, double s0) {
+  return new BLRModel(h, D, Ncap, mu0, s0);
+}
+void blr_observe(Model *m, const double *X_rows_host, const uint8_t *y_host, int64_t n) {
+  static_cast<BLRModel *>(m)->observe(X_rows_host, y_host, n);
+}
+
+}  // namespace vk

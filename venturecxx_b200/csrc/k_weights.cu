@@ -1,0 +1,480 @@
+// Weight kernels: logsumexp, normalised probabilities, fixed-point prefix
+// scan, ancestor search (systematic / multinomial) and ancestor gather.
+//
+// Reference semantics restated (paths under /root/reference):
+//   backend/lite/utils.py:70-91    logsumexp (max-shift; +-inf / NaN policy)
+//   backend/lite/utils.py:93-99    normalizeList (non-positive sum -> uniform)
+//   backend/lite/utils.py:152-157  log_domain_even_out
+//   backend/lite/utils.py:159-180  logWeightsToNormalizedDirect, sampleLogCategorical
+//   python/lib/engine/trace_set.py:202-235  resample / _resample_traces
+//
+// B200 mapping: all kernels are HBM streaming passes over P doubles with
+// grid-stride loops sized to a multiple of the SM count; block partials are
+// combined by the last block to finish (no second launch, deterministic
+// order).  The CDF is a 64-bit FIXED-POINT prefix sum so that ancestor
+// indices do not depend on the association order of a parallel scan, on the
+// GPU count, or on the platform's rounding: exact integers everywhere.
+#include "vk_common.cuh"
+#include "weights.cuh"
+#include "models.cuh"
+
+namespace vk {
+
+// red layout (doubles): [0]=max [1]=min [2]=nan flag [3]=sum exp [4]=lse
+// [8 ..] per-block partials (3 per block)
+static const int RED_PART = 8;
+
+__global__ void __launch_bounds__(256)
+lse_pass1_kernel(const double *__restrict__ a, int64_t n, double *red, unsigned int *counter) {
+  __shared__ double sh[3][32];
+  double mx = -INFINITY, mn = INFINITY, nanf = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    double v = a[i];
+    if (v != v) nanf = 1.0;
+    else { mx = fmax(mx, v); mn = fmin(mn, v); }
+  }
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
+  if (lane == 0) { sh[0][w] = mx; sh[1][w] = mn; sh[2][w] = nanf; }
+  __syncthreads();
+  if (w == 0) {
+    int nw = blockDim.x >> 5;
+    mx = lane < nw ? sh[0][lane] : -INFINITY;
+    mn = lane < nw ? sh[1][lane] : INFINITY;
+    nanf = lane < nw ? sh[2][lane] : 0.0;
+    mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
+    if (lane == 0) {
+      red[RED_PART + 3 * blockIdx.x + 0] = mx;
+      red[RED_PART + 3 * blockIdx.x + 1] = mn;
+      red[RED_PART + 3 * blockIdx.x + 2] = nanf;
+    }
+  }
+  __shared__ bool last;
+  __threadfence();
+  if (threadIdx.x == 0) last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (last && w == 0) {
+    __threadfence();
+    mx = -INFINITY; mn = INFINITY; nanf = 0.0;
+    for (int b = lane; b < (int)gridDim.x; b += 32) {
+      mx = fmax(mx, red[RED_PART + 3 * b + 0]);
+      mn = fmin(mn, red[RED_PART + 3 * b + 1]);
+      nanf = fmax(nanf, red[RED_PART + 3 * b + 2]);
+    }
+    mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
+    if (lane == 0) { red[0] = mx; red[1] = mn; red[2] = nanf; *counter = 0; }
+  }
+}
+
+// sum exp(a - m) with per-thread accumulation, block tree, last-block finish.
+__global__ void __launch_bounds__(256)
+lse_pass2_kernel(const double *__restrict__ a, int64_t n, double *red, unsigned int *counter) {
+  __shared__ double sh[33];
+  const double m = red[0];
+  double s = 0.0;
+  // if m is +-inf the sum is not used (edge-case branch below) -> skip work
+  if (!isinf(m)) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x)
+      s += exp(a[i] - m);
+  }
+  s = block_sum(s, sh);
+  if (threadIdx.x == 0) red[RED_PART + blockIdx.x] = s;
+  __shared__ bool last;
+  __threadfence();
+  if (threadIdx.x == 0) last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (last) {
+    __threadfence();
+    double t = 0.0;
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) t += red[RED_PART + b];
+    t = block_sum(t, sh);
+    if (threadIdx.x == 0) {
+      double mn = red[1], nanf = red[2], lse;
+      // utils.py:77-91
+      if (n == 0) lse = -INFINITY;
+      else if (nanf != 0.0) lse = NAN;
+      else if (isinf(m) && mn != -m) lse = m;
+      else if (isinf(m)) lse = NAN;          // +inf and -inf both present
+      else lse = m + log(t);
+      red[3] = t; red[4] = lse; *counter = 0;
+    }
+  }
+}
+
+void device_logsumexp(const double *a, int64_t n, double *red, unsigned int *counter,
+                      int sm_count, cudaStream_t st) {
+  int grid = grid_for(n, 256, sm_count, 4);
+  lse_pass1_kernel<<<grid, 256, 0, st>>>(a, n, red, counter);
+  lse_pass2_kernel<<<grid, 256, 0, st>>>(a, n, red, counter + 1);
+  VK_CUDA(cudaGetLastError());
+}
+
+// utils.py:159-168: all -inf -> zeros; else exp(lg - max) normalised
+// (normalizeList: sum <= 0 -> uniform, cannot happen when max is finite).
+__global__ void normalized_probs_kernel(const double *__restrict__ a, int64_t n,
+                                        const double *__restrict__ red, double *out) {
+  const double m = red[0], s = red[3];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    double v;
+    if (!(m > -INFINITY)) v = 0.0;
+    else v = exp(a[i] - m) / s;
+    out[i] = v;
+  }
+}
+
+// ---- fixed-point weights ---------------------------------------------------
+// q_i = rint(exp(lw_i - m) * 2^S); NaN or -inf -> 0; all -inf (m = -inf) -> 1
+// for everybody (normalizeList's "equally impossible").
+__device__ __forceinline__ uint64_t fixed_weight(double lw, double m, double scale) {
+  if (!(m > -INFINITY)) return 1ull;
+  double d = lw - m;
+  if (!(d == d)) return 0ull;
+  return __double2ull_rn(exp(d) * scale);
+}
+
+static const int SCAN_THREADS = 256;
+static const int SCAN_ITEMS = 8;
+static const int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+__device__ __forceinline__ uint64_t warp_scan_incl(uint64_t v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint64_t t = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += t;
+  }
+  return v;
+}
+
+// pass A: per-tile totals
+__global__ void __launch_bounds__(SCAN_THREADS)
+fixed_tile_sums_kernel(const double *__restrict__ lw, int64_t n, double m_in,
+                       const double *__restrict__ red, double scale, uint64_t *tile_sums) {
+  __shared__ uint64_t sh[32];
+  const double m = red ? red[0] : m_in;
+  int64_t base = (int64_t)blockIdx.x * SCAN_TILE;
+  uint64_t s = 0;
+#pragma unroll
+  for (int j = 0; j < SCAN_ITEMS; ++j) {
+    int64_t i = base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+    if (i < n) s += fixed_weight(lw[i], m, scale);
+  }
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) sh[w] = s;
+  __syncthreads();
+  if (w == 0) {
+    s = lane < (SCAN_THREADS >> 5) ? sh[lane] : 0ull;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) tile_sums[blockIdx.x] = s;
+  }
+}
+
+// pass B: exclusive scan of the tile totals by one block; total -> tile_sums[n_tiles]
+__global__ void __launch_bounds__(1024)
+scan_tile_sums_kernel(uint64_t *tile_sums, int n_tiles) {
+  __shared__ uint64_t sh[32];
+  __shared__ uint64_t carry_sh;
+  if (threadIdx.x == 0) carry_sh = 0;
+  __syncthreads();
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int b0 = 0; b0 < n_tiles; b0 += 1024) {
+    int b = b0 + threadIdx.x;
+    uint64_t v = b < n_tiles ? tile_sums[b] : 0ull;
+    uint64_t inc = warp_scan_incl(v, lane);
+    if (lane == 31) sh[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+      uint64_t t = sh[lane];
+      t = warp_scan_incl(t, lane);
+      sh[lane] = t;
+    }
+    __syncthreads();
+    uint64_t woff = w > 0 ? sh[w - 1] : 0ull;
+    uint64_t carry = carry_sh;
+    uint64_t excl = carry + woff + inc - v;
+    if (b < n_tiles) tile_sums[b] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry_sh = carry + woff + inc;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) tile_sums[n_tiles] = carry_sh;
+}
+
+// pass C: inclusive CDF. Element order inside a tile is blocked per thread
+// (thread t owns items t*8 .. t*8+7) so the prefix is over natural index order.
+__global__ void __launch_bounds__(SCAN_THREADS)
+fixed_cdf_kernel(const double *__restrict__ lw, int64_t n, double m_in,
+                 const double *__restrict__ red, double scale,
+                 const uint64_t *__restrict__ tile_sums, uint64_t *__restrict__ cdf) {
+  __shared__ uint64_t sh[32];
+  const double m = red ? red[0] : m_in;
+  int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+  uint64_t q[SCAN_ITEMS];
+  uint64_t s = 0;
+#pragma unroll
+  for (int j = 0; j < SCAN_ITEMS; ++j) {
+    int64_t i = base + j;
+    q[j] = i < n ? fixed_weight(lw[i], m, scale) : 0ull;
+    s += q[j];
+  }
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint64_t inc = warp_scan_incl(s, lane);
+  if (lane == 31) sh[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    uint64_t t = lane < (SCAN_THREADS >> 5) ? sh[lane] : 0ull;
+    t = warp_scan_incl(t, lane);
+    sh[lane] = t;
+  }
+  __syncthreads();
+  uint64_t run = tile_sums[blockIdx.x] + (w > 0 ? sh[w - 1] : 0ull) + inc - s;
+#pragma unroll
+  for (int j = 0; j < SCAN_ITEMS; ++j) {
+    int64_t i = base + j;
+    run += q[j];
+    if (i < n) cdf[i] = run;
+  }
+}
+
+// smallest i in [0,n) with cdf[i] > thr  (thr < cdf[n-1] guaranteed)
+__device__ __forceinline__ int64_t upper_bound_u64(const uint64_t *__restrict__ cdf, int64_t n,
+                                                   uint64_t thr) {
+  int64_t lo = 0, hi = n - 1;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (cdf[mid] > thr) hi = mid; else lo = mid + 1;
+  }
+  return lo;
+}
+
+// Ancestor search. `total` = W = mass of ALL shards, `offset` = mass of the
+// shards before this one (0 on one GPU).  Child k of n_new (global index
+// k_base + local thread) gets threshold
+//   systematic : floor(((k<<32) + U0) * W / (n_new<<32)),  U0 = floor(u*2^32)
+//   multinomial: floor(U_k * W / 2^53),                    U_k = floor(u_k*2^53)
+// and ancestor = first local i with offset + cdf[i] > thr.  Children whose
+// threshold lies outside this shard's [offset, offset + cdf[n-1]) get -1.
+__global__ void ancestor_search_kernel(const uint64_t *__restrict__ cdf, int64_t n,
+                                       uint64_t offset, uint64_t total,
+                                       int64_t n_new, int64_t k_begin, int64_t k_count,
+                                       int mode, uint64_t seed, uint32_t step,
+                                       const double *__restrict__ uniforms,
+                                       int32_t *__restrict__ anc_out) {
+  uint64_t shard_mass = cdf[n - 1];
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < k_count;
+       t += (int64_t)gridDim.x * blockDim.x) {
+    int64_t k = k_begin + t;
+    uint64_t thr;
+    if (mode == VK_RESAMPLE_SYSTEMATIC) {
+      double u;
+      if (uniforms) u = uniforms[0];
+      else { Stream r(seed, GLOBAL_PARTICLE, step); u = r.uniform(); }
+      uint64_t U0 = (uint64_t)(u * 4294967296.0);
+      if (U0 > 0xFFFFFFFFull) U0 = 0xFFFFFFFFull;
+      unsigned __int128 num = (((unsigned __int128)(uint64_t)k << 32) | U0) * (unsigned __int128)total;
+      unsigned __int128 den = (unsigned __int128)(uint64_t)n_new << 32;
+      thr = (uint64_t)(num / den);
+    } else {
+      double u;
+      if (uniforms) u = uniforms[k];
+      else { Stream r(seed, (uint64_t)k, step); u = r.uniform(); }
+      uint64_t U = (uint64_t)(u * 9007199254740992.0);
+      if (U > 9007199254740991ull) U = 9007199254740991ull;
+      thr = (uint64_t)(((unsigned __int128)U * (unsigned __int128)total) >> 53);
+    }
+    int32_t a = -1;
+    if (thr >= offset && thr - offset < shard_mass)
+      a = (int32_t)upper_bound_u64(cdf, n, thr - offset);
+    anc_out[t] = a;
+  }
+}
+
+// ---- ancestor gather --------------------------------------------------------
+// particle-major rows of row_bytes (multiple of 16): 16-byte units
+__global__ void gather_rows16_kernel(const uint4 *__restrict__ in, uint4 *__restrict__ out,
+                                     const int32_t *__restrict__ anc, int64_t n_new,
+                                     int64_t units_per_row) {
+  int64_t total = n_new * units_per_row;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (int64_t)gridDim.x * blockDim.x) {
+    int64_t k = t / units_per_row, c = t - k * units_per_row;
+    out[t] = in[(int64_t)anc[k] * units_per_row + c];
+  }
+}
+// generic byte rows (row_bytes not a multiple of 16)
+__global__ void gather_rows1_kernel(const unsigned char *__restrict__ in,
+                                    unsigned char *__restrict__ out,
+                                    const int32_t *__restrict__ anc, int64_t n_new,
+                                    int64_t row_bytes) {
+  int64_t total = n_new * row_bytes;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (int64_t)gridDim.x * blockDim.x) {
+    int64_t k = t / row_bytes, c = t - k * row_bytes;
+    out[t] = in[(int64_t)anc[k] * row_bytes + c];
+  }
+}
+// particle-minor SoA: n_rows rows of P elements
+template <typename T>
+__global__ void gather_soa_kernel(const T *__restrict__ in, T *__restrict__ out,
+                                  const int32_t *__restrict__ anc, int64_t P_old,
+                                  int64_t n_new, int64_t n_rows) {
+  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n_new;
+       k += (int64_t)gridDim.x * blockDim.x) {
+    int64_t a = anc[k];
+    for (int64_t r = 0; r < n_rows; ++r) out[r * n_new + k] = in[r * P_old + a];
+  }
+}
+
+__global__ void fill_kernel(double *out, int64_t n, const double *red, double log_n_new) {
+  double v = red[4] - log_n_new;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = v;
+}
+
+int frac_bits_for(int64_t P_total) {
+  int lg = 0;
+  while (((int64_t)1 << lg) < P_total) ++lg;
+  int S = 62 - lg;
+  return S > 52 ? 52 : S;
+}
+
+void build_fixed_cdf(vk_particles *h, const double *red_or_null, double m, int frac_bits) {
+  cudaStream_t st = h->stream;
+  int64_t P = h->P;
+  int n_tiles = (int)((P + SCAN_TILE - 1) / SCAN_TILE);
+  if (h->red_u.n < (size_t)n_tiles + 1) h->red_u.alloc((size_t)n_tiles + 1);
+  double scale = ldexp(1.0, frac_bits);
+  fixed_tile_sums_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, m, red_or_null, scale, h->red_u.p);
+  scan_tile_sums_kernel<<<1, 1024, 0, st>>>(h->red_u.p, n_tiles);
+  fixed_cdf_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, m, red_or_null, scale, h->red_u.p, h->cdf.p);
+  VK_CUDA(cudaGetLastError());
+}
+
+void gather_state(vk_particles *h, const int32_t *anc_dev, int64_t n_new) {
+  cudaStream_t st = h->stream;
+  std::vector<StateArray> arrs = h->model->state_arrays();
+  for (auto &a : arrs) {
+    if (a.elem_bytes == 0) {
+      if (a.row_bytes % 16 == 0) {
+        int64_t units = (int64_t)(a.row_bytes / 16);
+        int grid = grid_for(n_new * units, 256, h->sm_count, 8);
+        gather_rows16_kernel<<<grid, 256, 0, st>>>((const uint4 *)*a.cur, (uint4 *)*a.alt, anc_dev, n_new, units);
+      } else {
+        int grid = grid_for(n_new * (int64_t)a.row_bytes, 256, h->sm_count, 8);
+        gather_rows1_kernel<<<grid, 256, 0, st>>>((const unsigned char *)*a.cur, (unsigned char *)*a.alt, anc_dev, n_new, (int64_t)a.row_bytes);
+      }
+    } else {
+      int grid = grid_for(n_new, 256, h->sm_count, 8);
+      if (a.elem_bytes == 8)
+        gather_soa_kernel<uint64_t><<<grid, 256, 0, st>>>((const uint64_t *)*a.cur, (uint64_t *)*a.alt, anc_dev, h->P, n_new, (int64_t)a.n_rows);
+      else if (a.elem_bytes == 4)
+        gather_soa_kernel<uint32_t><<<grid, 256, 0, st>>>((const uint32_t *)*a.cur, (uint32_t *)*a.alt, anc_dev, h->P, n_new, (int64_t)a.n_rows);
+      else if (a.elem_bytes == 1)
+        gather_soa_kernel<uint8_t><<<grid, 256, 0, st>>>((const uint8_t *)*a.cur, (uint8_t *)*a.alt, anc_dev, h->P, n_new, (int64_t)a.n_rows);
+      else
+        throw Error(VK_EINVAL, "unsupported SoA element size");
+    }
+    void *t = *a.cur; *a.cur = *a.alt; *a.alt = t;
+  }
+  VK_CUDA(cudaGetLastError());
+}
+
+// Whole single-GPU resample: LSE -> fixed CDF -> ancestors -> gather -> even weights.
+void resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms_dev) {
+  VK_REQUIRE(n_new == h->P, VK_EUNSUPPORTED, "resample: n_new must equal the particle count in this version");
+  VK_REQUIRE(mode == VK_RESAMPLE_MULTINOMIAL || mode == VK_RESAMPLE_SYSTEMATIC, VK_EINVAL, "resample: bad mode");
+  cudaStream_t st = h->stream;
+  int64_t P = h->P;
+  uint32_t step = h->next_step();
+  device_logsumexp(h->lw.p, P, h->red.p, h->counters.p, h->sm_count, st);
+  int S = frac_bits_for(P);
+  build_fixed_cdf(h, h->red.p, 0.0, S);
+  int grid = grid_for(n_new, 256, h->sm_count, 8);
+  launch_ancestor_search_single(h, n_new, mode, step, uniforms_dev, grid);
+  gather_state(h, h->anc.p, n_new);
+  fill_kernel<<<grid_for(n_new, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, n_new, h->red.p, log((double)n_new));
+  VK_CUDA(cudaGetLastError());
+  h->model->after_resample();
+}
+
+// single-shard variant: total read from cdf[n-1] on the device
+__global__ void ancestor_search_single_kernel(const uint64_t *__restrict__ cdf, int64_t n,
+                                              int64_t n_new, int mode, uint64_t seed,
+                                              uint32_t step, const double *__restrict__ uniforms,
+                                              int32_t *__restrict__ anc_out) {
+  const uint64_t total = cdf[n - 1];
+  double u_sys = 0.0;
+  if (mode == VK_RESAMPLE_SYSTEMATIC) {
+    if (uniforms) u_sys = uniforms[0];
+    else { Stream r(seed, GLOBAL_PARTICLE, step); u_sys = r.uniform(); }
+  }
+  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n_new;
+       k += (int64_t)gridDim.x * blockDim.x) {
+    uint64_t thr;
+    if (mode == VK_RESAMPLE_SYSTEMATIC) {
+      uint64_t U0 = (uint64_t)(u_sys * 4294967296.0);
+      if (U0 > 0xFFFFFFFFull) U0 = 0xFFFFFFFFull;
+      unsigned __int128 num = (((unsigned __int128)(uint64_t)k << 32) | U0) * (unsigned __int128)total;
+      unsigned __int128 den = (unsigned __int128)(uint64_t)n_new << 32;
+      thr = (uint64_t)(num / den);
+    } else {
+      double u;
+      if (uniforms) u = uniforms[k];
+      else { Stream r(seed, (uint64_t)k, step); u = r.uniform(); }
+      uint64_t U = (uint64_t)(u * 9007199254740992.0);
+      if (U > 9007199254740991ull) U = 9007199254740991ull;
+      thr = (uint64_t)(((unsigned __int128)U * (unsigned __int128)total) >> 53);
+    }
+    anc_out[k] = (int32_t)upper_bound_u64(cdf, n, thr);
+  }
+}
+
+void launch_ancestor_search_single(vk_particles *h, int64_t n_new, int mode, uint32_t step,
+                                   const double *uniforms_dev, int grid) {
+  ancestor_search_single_kernel<<<grid, 256, 0, h->stream>>>(h->cdf.p, h->P, n_new, mode, h->seed,
+                                                             step, uniforms_dev, h->anc.p);
+  VK_CUDA(cudaGetLastError());
+}
+
+__global__ void fill_value_kernel(double *out, int64_t n, double v) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = v;
+}
+void launch_fill_even_weights(vk_particles *h, int64_t n, double lse, double log_n_new) {
+  fill_value_kernel<<<grid_for(n, 256, h->sm_count, 4), 256, 0, h->stream>>>(h->lw.p, n, lse - log_n_new);
+  VK_CUDA(cudaGetLastError());
+}
+
+__global__ void axpy_kernel(double *y, const double *x, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    y[i] += x[i];
+}
+void launch_axpy(vk_particles *h, double *y, const double *x, int64_t n) {
+  axpy_kernel<<<grid_for(n, 256, h->sm_count, 4), 256, 0, h->stream>>>(y, x, n);
+  VK_CUDA(cudaGetLastError());
+}
+
+void launch_normalized_probs(vk_particles *h, double *out_dev) {
+  device_logsumexp(h->lw.p, h->P, h->red.p, h->counters.p, h->sm_count, h->stream);
+  normalized_probs_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(h->lw.p, h->P, h->red.p, out_dev);
+  VK_CUDA(cudaGetLastError());
+}
+
+void launch_ancestor_search_shard(vk_particles *h, uint64_t offset, uint64_t total, int64_t n_new,
+                                  int64_t k_begin, int64_t k_count, int mode, uint32_t step,
+                                  const double *uniforms_dev, int32_t *anc_out_dev) {
+  if (k_count <= 0) return;
+  ancestor_search_kernel<<<grid_for(k_count, 256, h->sm_count, 8), 256, 0, h->stream>>>(
+      h->cdf.p, h->P, offset, total, n_new, k_begin, k_count, mode, h->seed, step, uniforms_dev, anc_out_dev);
+  VK_CUDA(cudaGetLastError());
+}
+
+}  // namespace vk

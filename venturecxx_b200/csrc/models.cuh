@@ -1,0 +1,21 @@
+// Factories and model-specific entry points behind the C ABI.
+#pragma once
+#include "vk_common.cuh"
+
+namespace vk {
+Model *make_normal_normal(vk_particles *h, double mu0, double s0, double s, int64_t max_obs);
+void normal_normal_observe(Model *m, const double *y_host, int64_t n);
+
+Model *make_blr(vk_particles *h, int D, int64_t Ncap, double mu0, double s0);
+void blr_observe(Model *m, const double *X_rows_host, const uint8_t *y_host, int64_t n);
+
+Model *make_hmm(vk_particles *h, int S, int O, int n_trans_rows, const double *trans_host,
+                const double *emit_host, int init_state, int T_max);
+void hmm_observe(Model *m, int symbol);
+
+Model *make_lda(vk_particles *h, int K, int V, int n_docs, int max_tokens, double hyper_shape,
+                double hyper_rate);
+void lda_observe(Model *m, const int32_t *doc_host, const int32_t *word_host, int64_t n);
+
+void launch_axpy(vk_particles *h, double *y, const double *x, int64_t n);  // y += x
+}  // namespace vk

@@ -1,0 +1,361 @@
+// extern "C" entry points of include/venture_b200.h: handle management,
+// host<->device staging, and dispatch into the per-model site kernels.
+#include <string.h>
+#include <cmath>
+#include "vk_common.cuh"
+#include "weights.cuh"
+#include "models.cuh"
+
+namespace vk {
+static thread_local std::string g_last_error;
+void set_last_error(const std::string &m) { g_last_error = m; }
+}  // namespace vk
+
+using namespace vk;
+
+#define VK_TRY try {
+#define VK_CATCH                                                              \
+  }                                                                           \
+  catch (const vk::Error &e) { vk::set_last_error(e.what()); return e.code; } \
+  catch (const std::exception &e) { vk::set_last_error(e.what()); return VK_ECUDA; } \
+  return VK_OK;
+
+static void check_handle(const vk_particles *h) {
+  if (!h || !h->model) throw Error(VK_EINVAL, "null or destroyed vk_particles handle");
+}
+static void use_device(const vk_particles *h) { VK_CUDA(cudaSetDevice(h->device)); }
+
+// temporary device staging buffer of P doubles copied to the host on scope exit
+struct HostOut {
+  vk_particles *h; double *host; DevBuf<double> dev; size_t n;
+  HostOut(vk_particles *h_, double *host_, size_t n_) : h(h_), host(host_), n(n_) { if (host) dev.alloc(n); }
+  double *ptr() { return host ? dev.p : nullptr; }
+  void finish() {
+    if (host) VK_CUDA(cudaMemcpyAsync(host, dev.p, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    VK_CUDA(cudaStreamSynchronize(h->stream));
+  }
+};
+
+static vk_particles *new_handle(int kind, int64_t P, uint64_t seed, int device) {
+  VK_REQUIRE(P >= 1 && P <= ((int64_t)1 << 30), VK_EINVAL, "n_particles must be in [1, 2^30]");
+  int n_dev = 0;
+  cudaError_t e = cudaGetDeviceCount(&n_dev);
+  if (e != cudaSuccess || n_dev == 0)
+    throw Error(VK_ECUDA, std::string("no CUDA device available (this library has no CPU fallback): ") +
+                              cudaGetErrorString(e));
+  VK_REQUIRE(device >= 0 && device < n_dev, VK_EINVAL, "device index out of range");
+  VK_CUDA(cudaSetDevice(device));
+  vk_particles *h = new vk_particles();
+  try {
+    h->kind = kind; h->device = device; h->P = P; h->seed = seed;
+    VK_CUDA(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device));
+    VK_CUDA(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    h->stream = h->own_stream;
+    h->lw.alloc((size_t)P);
+    h->scratch_d.alloc((size_t)P);
+    h->cdf.alloc((size_t)P);
+    h->anc.alloc((size_t)P);
+    h->red.alloc((size_t)(8 + 3 * h->sm_count * 8 + 64));
+    h->counters.alloc(8);
+    VK_CUDA(cudaMemsetAsync(h->lw.p, 0, h->lw.bytes(), h->stream));
+    VK_CUDA(cudaMemsetAsync(h->counters.p, 0, h->counters.bytes(), h->stream));
+  } catch (...) { delete h; throw; }
+  return h;
+}
+static void finish_create(vk_particles *h, vk_particles **out) {
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  *out = h;
+}
+
+extern "C" {
+
+const char *vk_last_error(void) { return vk::g_last_error.c_str(); }
+int vk_version(void) { return 100; }
+int vk_device_count(int *n_out) {
+  VK_TRY
+  VK_REQUIRE(n_out, VK_EINVAL, "n_out is NULL");
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) { n = 0; cudaGetLastError(); }
+  *n_out = n;
+  VK_CATCH
+}
+
+int vk_create_normal_normal(int64_t P, uint64_t seed, int device, double prior_mu, double prior_sigma,
+                            double obs_sigma, int64_t max_obs, vk_particles **out) {
+  VK_TRY
+  VK_REQUIRE(out, VK_EINVAL, "out is NULL");
+  VK_REQUIRE(prior_sigma > 0 && obs_sigma > 0, VK_EINVAL, "normal: sigma must be positive");
+  vk_particles *h = new_handle(VK_MODEL_NORMAL_NORMAL, P, seed, device);
+  try { h->model = make_normal_normal(h, prior_mu, prior_sigma, obs_sigma, max_obs); }
+  catch (...) { cudaStreamDestroy(h->own_stream); delete h; throw; }
+  finish_create(h, out);
+  VK_CATCH
+}
+
+int vk_create_blr(int64_t P, uint64_t seed, int device, int32_t D, int64_t n_obs_capacity,
+                  double prior_mu, double prior_sigma, vk_particles **out) {
+  VK_TRY
+  VK_REQUIRE(out, VK_EINVAL, "out is NULL");
+  VK_REQUIRE(prior_sigma > 0, VK_EINVAL, "normal: sigma must be positive");
+  vk_particles *h = new_handle(VK_MODEL_BLR, P, seed, device);
+  try { h->model = make_blr(h, D, n_obs_capacity, prior_mu, prior_sigma); }
+  catch (...) { cudaStreamDestroy(h->own_stream); delete h; throw; }
+  finish_create(h, out);
+  VK_CATCH
+}
+
+int vk_create_hmm(int64_t P, uint64_t seed, int device, int32_t S, int32_t O, int32_t n_trans_rows,
+                  const double *trans_host, const double *emit_host, int32_t init_state, int32_t T_max,
+                  vk_particles **out) {
+  VK_TRY
+  VK_REQUIRE(out && trans_host && emit_host, VK_EINVAL, "NULL argument");
+  vk_particles *h = new_handle(VK_MODEL_HMM, P, seed, device);
+  try { h->model = make_hmm(h, S, O, n_trans_rows, trans_host, emit_host, init_state, T_max); }
+  catch (...) { cudaStreamDestroy(h->own_stream); delete h; throw; }
+  finish_create(h, out);
+  VK_CATCH
+}
+
+int vk_create_lda(int64_t P, uint64_t seed, int device, int32_t K, int32_t V, int32_t n_docs,
+                  int32_t max_tokens, double hyper_shape, double hyper_rate, vk_particles **out) {
+  VK_TRY
+  VK_REQUIRE(out, VK_EINVAL, "out is NULL");
+  vk_particles *h = new_handle(VK_MODEL_LDA, P, seed, device);
+  try { h->model = make_lda(h, K, V, n_docs, max_tokens, hyper_shape, hyper_rate); }
+  catch (...) { cudaStreamDestroy(h->own_stream); delete h; throw; }
+  finish_create(h, out);
+  VK_CATCH
+}
+
+int vk_destroy(vk_particles *h) {
+  VK_TRY
+  if (!h) return VK_OK;
+  cudaSetDevice(h->device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  delete h->model; h->model = nullptr;
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  delete h;
+  VK_CATCH
+}
+
+int vk_kind(const vk_particles *h) { return h ? h->kind : 0; }
+int64_t vk_num_particles(const vk_particles *h) { return h ? h->P : 0; }
+int vk_set_seed(vk_particles *h, uint64_t seed) { VK_TRY check_handle(h); h->seed = seed; h->step = 0; VK_CATCH }
+int vk_get_seed(const vk_particles *h, uint64_t *seed_out) { VK_TRY check_handle(h); VK_REQUIRE(seed_out, VK_EINVAL, "NULL"); *seed_out = h->seed; VK_CATCH }
+int vk_get_step(const vk_particles *h, uint32_t *step_out) { VK_TRY check_handle(h); VK_REQUIRE(step_out, VK_EINVAL, "NULL"); *step_out = h->step; VK_CATCH }
+int vk_set_step(vk_particles *h, uint32_t step) { VK_TRY check_handle(h); h->step = step; VK_CATCH }
+int vk_set_particle_base(vk_particles *h, int64_t base) { VK_TRY check_handle(h); VK_REQUIRE(base >= 0, VK_EINVAL, "negative base"); h->p_base = base; VK_CATCH }
+int vk_set_stream(vk_particles *h, void *cuda_stream) {
+  VK_TRY
+  check_handle(h); use_device(h);
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  h->stream = cuda_stream ? (cudaStream_t)cuda_stream : h->own_stream;
+  VK_CATCH
+}
+int vk_synchronize(vk_particles *h) { VK_TRY check_handle(h); use_device(h); VK_CUDA(cudaStreamSynchronize(h->stream)); VK_CATCH }
+
+int vk_reset_to_prior(vk_particles *h) {
+  VK_TRY check_handle(h); use_device(h);
+  h->model->reset_to_prior();
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+
+int vk_nn_observe(vk_particles *h, const double *y_host, int64_t n) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(h->kind == VK_MODEL_NORMAL_NORMAL, VK_EUNSUPPORTED, "vk_nn_observe: not a normal-normal batch");
+  VK_REQUIRE(n >= 0 && (y_host || n == 0), VK_EINVAL, "bad observation buffer");
+  if (n) normal_normal_observe(h->model, y_host, n);
+  VK_CATCH
+}
+int vk_blr_observe(vk_particles *h, const double *X_rows_host, const uint8_t *y_host, int64_t n) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(h->kind == VK_MODEL_BLR, VK_EUNSUPPORTED, "vk_blr_observe: not a BLR batch");
+  VK_REQUIRE(n >= 0 && ((X_rows_host && y_host) || n == 0), VK_EINVAL, "bad observation buffers");
+  if (n) blr_observe(h->model, X_rows_host, y_host, n);
+  VK_CATCH
+}
+int vk_hmm_observe(vk_particles *h, int32_t symbol) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(h->kind == VK_MODEL_HMM, VK_EUNSUPPORTED, "vk_hmm_observe: not an HMM batch");
+  hmm_observe(h->model, symbol);
+  VK_CATCH
+}
+int vk_lda_observe(vk_particles *h, const int32_t *doc_host, const int32_t *word_host, int64_t n) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(h->kind == VK_MODEL_LDA, VK_EUNSUPPORTED, "vk_lda_observe: not an LDA batch");
+  VK_REQUIRE(n >= 0 && ((doc_host && word_host) || n == 0), VK_EINVAL, "bad observation buffers");
+  if (n) lda_observe(h->model, doc_host, word_host, n);
+  VK_CATCH
+}
+
+int vk_forget_observations(vk_particles *h, double *weights_out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  HostOut o(h, weights_out_host, (size_t)h->P);
+  h->model->forget_observations(o.ptr());
+  o.finish();
+  VK_CATCH
+}
+int vk_make_consistent(vk_particles *h, double *increments_out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  HostOut o(h, increments_out_host, (size_t)h->P);
+  h->model->make_consistent(o.ptr());
+  o.finish();
+  VK_CATCH
+}
+int vk_likelihood_weight(vk_particles *h) {
+  VK_TRY check_handle(h); use_device(h);
+  h->model->likelihood_weight();
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_get_log_weights(vk_particles *h, double *out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(out_host, VK_EINVAL, "out_host is NULL");
+  VK_CUDA(cudaMemcpyAsync(out_host, h->lw.p, h->lw.bytes(), cudaMemcpyDeviceToHost, h->stream));
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_set_log_weights(vk_particles *h, const double *in_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(in_host, VK_EINVAL, "in_host is NULL");
+  VK_CUDA(cudaMemcpyAsync(h->lw.p, in_host, h->lw.bytes(), cudaMemcpyHostToDevice, h->stream));
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_increment_log_weights(vk_particles *h, const double *in_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(in_host, VK_EINVAL, "in_host is NULL");
+  VK_CUDA(cudaMemcpyAsync(h->scratch_d.p, in_host, h->lw.bytes(), cudaMemcpyHostToDevice, h->stream));
+  launch_axpy(h, h->lw.p, h->scratch_d.p, h->P);
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_logsumexp(vk_particles *h, double *out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(out_host, VK_EINVAL, "out_host is NULL");
+  device_logsumexp(h->lw.p, h->P, h->red.p, h->counters.p, h->sm_count, h->stream);
+  VK_CUDA(cudaMemcpyAsync(out_host, h->red.p + 4, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_normalized_probs(vk_particles *h, double *out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(out_host, VK_EINVAL, "out_host is NULL");
+  launch_normalized_probs(h, h->scratch_d.p);
+  VK_CUDA(cudaMemcpyAsync(out_host, h->scratch_d.p, h->lw.bytes(), cudaMemcpyDeviceToHost, h->stream));
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_logsumexp_array(const double *in_host, int64_t n, int device, double *out_host) {
+  VK_TRY
+  VK_REQUIRE(out_host && n >= 0 && (in_host || n == 0), VK_EINVAL, "bad arguments");
+  int n_dev = 0;
+  cudaError_t e = cudaGetDeviceCount(&n_dev);
+  if (e != cudaSuccess || n_dev == 0) throw Error(VK_ECUDA, "no CUDA device available (no CPU fallback)");
+  VK_CUDA(cudaSetDevice(device));
+  int sm = 148;
+  VK_CUDA(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, device));
+  DevBuf<double> a, red; DevBuf<unsigned int> ctr;
+  a.alloc((size_t)(n > 0 ? n : 1)); red.alloc((size_t)(8 + 3 * sm * 8 + 64)); ctr.alloc(8);
+  VK_CUDA(cudaMemset(ctr.p, 0, ctr.bytes()));
+  if (n) VK_CUDA(cudaMemcpy(a.p, in_host, (size_t)n * sizeof(double), cudaMemcpyHostToDevice));
+  device_logsumexp(a.p, n, red.p, ctr.p, sm, 0);
+  VK_CUDA(cudaMemcpy(out_host, red.p + 4, sizeof(double), cudaMemcpyDeviceToHost));
+  VK_CATCH
+}
+
+int vk_resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms_host,
+                int32_t *ancestors_out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  DevBuf<double> u;
+  if (uniforms_host) {
+    size_t n = mode == VK_RESAMPLE_SYSTEMATIC ? 1 : (size_t)n_new;
+    u.alloc(n);
+    VK_CUDA(cudaMemcpyAsync(u.p, uniforms_host, n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  }
+  resample(h, n_new, mode, uniforms_host ? u.p : nullptr);
+  if (ancestors_out_host)
+    VK_CUDA(cudaMemcpyAsync(ancestors_out_host, h->anc.p, (size_t)n_new * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+  // trace_set.py:207: resample ends with incorporate()
+  h->model->make_consistent(nullptr);
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+
+int vk_mh(vk_particles *h, int32_t scope, int32_t block, int32_t transitions, double *mean_nodes_out_host,
+          int64_t *accepted_out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(transitions >= 0, VK_EINVAL, "transitions must be >= 0");
+  HostOut o(h, mean_nodes_out_host, (size_t)h->P);
+  DevBuf<long long> acc;
+  if (accepted_out_host) acc.alloc((size_t)h->P);
+  if (accepted_out_host && transitions == 0) VK_CUDA(cudaMemsetAsync(acc.p, 0, acc.bytes(), h->stream));
+  h->model->mh(scope, block, transitions, o.ptr(), accepted_out_host ? acc.p : nullptr);
+  if (accepted_out_host)
+    VK_CUDA(cudaMemcpyAsync(accepted_out_host, acc.p, acc.bytes(), cudaMemcpyDeviceToHost, h->stream));
+  o.finish();
+  VK_CATCH
+}
+
+int vk_subsampled_mh(vk_particles *h, int32_t scope, int32_t block, int64_t Nbatch, int32_t k0,
+                     double epsilon, int32_t use_delta_kernels, double delta_sigma, int32_t update_values,
+                     int32_t transitions, double *stats_out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(transitions >= 0 && Nbatch >= 1 && k0 >= 0, VK_EINVAL, "bad subsampled_mh arguments");
+  HostOut o(h, stats_out_host, (size_t)h->P * 3);
+  h->model->subsampled_mh(scope, block, Nbatch, k0, epsilon, use_delta_kernels, delta_sigma, update_values,
+                          transitions, o.ptr());
+  o.finish();
+  VK_CATCH
+}
+
+int vk_log_likelihood_at(vk_particles *h, int32_t scope, int32_t block, double *out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(out_host, VK_EINVAL, "out_host is NULL");
+  HostOut o(h, out_host, (size_t)h->P);
+  h->model->log_likelihood_at(scope, block, false, o.ptr());
+  o.finish();
+  VK_CATCH
+}
+int vk_log_joint_at(vk_particles *h, int32_t scope, int32_t block, double *out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(out_host, VK_EINVAL, "out_host is NULL");
+  HostOut o(h, out_host, (size_t)h->P);
+  h->model->log_likelihood_at(scope, block, true, o.ptr());
+  o.finish();
+  VK_CATCH
+}
+
+int vk_num_sites(const vk_particles *h, int64_t *n_out) { VK_TRY check_handle(h); VK_REQUIRE(n_out, VK_EINVAL, "NULL"); *n_out = h->model->num_sites(); VK_CATCH }
+int vk_num_blocks(const vk_particles *h, int32_t scope, int64_t *n_out) { VK_TRY check_handle(h); VK_REQUIRE(n_out, VK_EINVAL, "NULL"); *n_out = h->model->num_blocks(scope); VK_CATCH }
+int vk_read_site(vk_particles *h, int64_t site, double *out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(out_host, VK_EINVAL, "out_host is NULL");
+  HostOut o(h, out_host, (size_t)h->P);
+  h->model->read_site(site, o.ptr());
+  o.finish();
+  VK_CATCH
+}
+int vk_write_site(vk_particles *h, int64_t site, const double *in_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(in_host, VK_EINVAL, "in_host is NULL");
+  VK_CUDA(cudaMemcpyAsync(h->scratch_d.p, in_host, (size_t)h->P * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  h->model->write_site(site, h->scratch_d.p);
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_refresh(vk_particles *h) { VK_TRY check_handle(h); use_device(h); h->model->refresh(); VK_CUDA(cudaStreamSynchronize(h->stream)); VK_CATCH }
+
+int vk_device_buffer(vk_particles *h, int32_t which, void **dev_ptr_out, int64_t *n_bytes_out) {
+  VK_TRY check_handle(h);
+  VK_REQUIRE(dev_ptr_out && n_bytes_out, VK_EINVAL, "NULL");
+  if (which == 0) { *dev_ptr_out = h->lw.p; *n_bytes_out = (int64_t)h->lw.bytes(); }
+  else if (which == -1) { *dev_ptr_out = h->anc.p; *n_bytes_out = (int64_t)h->anc.bytes(); }
+  else if (which == -2) { *dev_ptr_out = h->cdf.p; *n_bytes_out = (int64_t)h->cdf.bytes(); }
+  else { int rc = h->model->device_buffer(which, dev_ptr_out, n_bytes_out); if (rc) throw Error(rc, "no such device buffer"); }
+  VK_CATCH
+}
+
+}  // extern "C"

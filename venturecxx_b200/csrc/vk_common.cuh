@@ -1,0 +1,159 @@
+// Shared host/device plumbing of the C-ABI library: error convention,
+// the particle-batch handle, device buffers, warp/block reductions.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include "../../include/venture_b200.h"
+#include "philox.cuh"
+
+namespace vk {
+
+struct Error : std::runtime_error {
+  int code;
+  Error(int c, const std::string &m) : std::runtime_error(m), code(c) {}
+};
+
+void set_last_error(const std::string &m);
+
+#define VK_CUDA(expr)                                                        \
+  do {                                                                       \
+    cudaError_t _e = (expr);                                                 \
+    if (_e != cudaSuccess) {                                                 \
+      char _b[512];                                                          \
+      snprintf(_b, sizeof _b, "CUDA error %s at %s:%d: %s",                  \
+               cudaGetErrorName(_e), __FILE__, __LINE__,                     \
+               cudaGetErrorString(_e));                                      \
+      throw vk::Error(VK_ECUDA, _b);                                         \
+    }                                                                        \
+  } while (0)
+
+#define VK_REQUIRE(cond, code, msg)                                          \
+  do {                                                                       \
+    if (!(cond)) throw vk::Error((code), (msg));                             \
+  } while (0)
+
+// RAII device array
+template <typename T>
+struct DevBuf {
+  T *p = nullptr;
+  size_t n = 0;
+  DevBuf() {}
+  DevBuf(const DevBuf &) = delete;
+  DevBuf &operator=(const DevBuf &) = delete;
+  ~DevBuf() { release(); }
+  void alloc(size_t count) {
+    release();
+    n = count;
+    if (count) VK_CUDA(cudaMalloc((void **)&p, count * sizeof(T)));
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+  void swap(DevBuf &o) { std::swap(p, o.p); std::swap(n, o.n); }
+  size_t bytes() const { return n * sizeof(T); }
+};
+
+// one state array that must follow its particle through resampling
+struct StateArray {
+  void **cur;        // address of the live device pointer
+  void **alt;        // address of the back buffer pointer (same size)
+  size_t row_bytes;  // bytes per particle when particle-major (rows)
+  size_t n_rows;     // SoA: number of particle-minor rows of elem_bytes each
+  size_t elem_bytes; // SoA element size (particle-minor layout); 0 => particle-major rows
+};
+
+struct Model;
+
+}  // namespace vk
+
+// The opaque handle of include/venture_b200.h.
+struct vk_particles {
+  int kind = 0;
+  int device = 0;
+  int sm_count = 148;
+  int64_t P = 0;
+  int64_t p_base = 0;   // global index of local particle 0 (multi-GPU sharding)
+  uint64_t seed = 0;
+  uint32_t step = 0;
+  cudaStream_t stream = nullptr;
+  cudaStream_t own_stream = nullptr;
+  vk::DevBuf<double> lw;        // log weights, P
+  vk::DevBuf<double> scratch_d; // P doubles (increments, probs)
+  vk::DevBuf<uint64_t> cdf;     // fixed-point inclusive weight prefix sums, P
+  vk::DevBuf<int32_t> anc;      // ancestors, P
+  vk::DevBuf<double> red;       // small reduction scratch
+  vk::DevBuf<uint64_t> red_u;   // scan block sums
+  vk::DevBuf<unsigned int> counters;
+  vk::Model *model = nullptr;
+  uint32_t next_step(uint32_t n = 1) { uint32_t s = step; step += n; return s; }
+};
+
+namespace vk {
+
+// Per-model-kind behaviour behind the C ABI.
+struct Model {
+  vk_particles *h;
+  explicit Model(vk_particles *h_) : h(h_) {}
+  virtual ~Model() {}
+  virtual void make_consistent(double *incr_dev) = 0;   // adds to h->lw, writes increments
+  virtual void likelihood_weight() = 0;                 // overwrites h->lw
+  virtual void reset_to_prior() = 0;                    // resimulate latents, weights untouched
+  virtual void mh(int scope, int block, int K, double *mean_nodes_dev, long long *acc_dev) = 0;
+  virtual void log_likelihood_at(int scope, int block, bool joint, double *out_dev) {
+    throw Error(VK_EUNSUPPORTED, "log_likelihood_at/log_joint_at not defined for this model");
+  }
+  virtual void subsampled_mh(int scope, int block, int64_t Nbatch, int k0, double eps,
+                             int use_delta, double delta_sigma, int update_values, int K,
+                             double *stats_dev) {
+    throw Error(VK_EUNSUPPORTED, "subsampled_mh is defined for the BLR model only");
+  }
+  virtual void forget_observations(double *w_dev) { throw Error(VK_EUNSUPPORTED, "forget not defined for this model"); }
+  virtual int64_t num_sites() const = 0;
+  virtual int64_t num_blocks(int scope) const = 0;
+  virtual void read_site(int64_t site, double *out_dev) = 0;
+  virtual void write_site(int64_t site, const double *in_dev) = 0;
+  virtual void refresh() {}
+  // arrays gathered by ancestor index on resample; after the gather the model
+  // swaps cur/alt itself via StateArray.
+  virtual std::vector<StateArray> state_arrays() = 0;
+  virtual void after_resample() {}
+  virtual int device_buffer(int which, void **p, int64_t *bytes) { return VK_EINVAL; }
+};
+
+// ---- device helpers -------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// block-wide sum, result valid in every thread. `sh` holds >= 33 doubles.
+__device__ __forceinline__ double block_sum(double v, double *sh) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  __syncthreads();  // protect sh from a previous use
+  if (lane == 0) sh[w] = v;
+  __syncthreads();
+  double t = (lane < nw) ? sh[lane] : 0.0;
+  t = warp_sum(t);
+  return t;
+}
+
+inline int grid_for(int64_t n, int threads, int sm_count, int ctas_per_sm) {
+  int64_t need = (n + threads - 1) / threads;
+  int64_t cap = (int64_t)sm_count * ctas_per_sm;
+  if (need < 1) need = 1;
+  return (int)(need < cap ? need : cap);
+}
+
+}  // namespace vk

@@ -1,0 +1,19 @@
+// Host-side entry points of k_weights.cu (see that file for semantics).
+#pragma once
+#include "vk_common.cuh"
+
+namespace vk {
+void device_logsumexp(const double *a, int64_t n, double *red, unsigned int *counter,
+                      int sm_count, cudaStream_t st);
+int frac_bits_for(int64_t P_total);
+void build_fixed_cdf(vk_particles *h, const double *red_or_null, double m, int frac_bits);
+void gather_state(vk_particles *h, const int32_t *anc_dev, int64_t n_new);
+void resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms_dev);
+void launch_normalized_probs(vk_particles *h, double *out_dev);
+void launch_ancestor_search_single(vk_particles *h, int64_t n_new, int mode, uint32_t step,
+                                   const double *uniforms_dev, int grid);
+void launch_ancestor_search_shard(vk_particles *h, uint64_t offset, uint64_t total, int64_t n_new,
+                                  int64_t k_begin, int64_t k_count, int mode, uint32_t step,
+                                  const double *uniforms_dev, int32_t *anc_out_dev);
+void launch_fill_even_weights(vk_particles *h, int64_t n, double lse, double log_n_new);
+}  // namespace vk

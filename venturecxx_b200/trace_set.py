@@ -1,0 +1,247 @@
+"""B200TraceSet: the device-resident stand-in for the reference's TraceSet
+(python/lib/engine/trace_set.py:36-414) over N traces of one compiled model.
+
+Method names, argument meaning and return shapes follow the reference:
+  likelihood_weight   trace_set.py:287-288   (overwrites log_weights)
+  incorporate         trace_set.py:290-294   (adds makeConsistent increments)
+  resample            trace_set.py:202-207   (+ systematic mode)
+  primitive_infer     trace_set.py:339-340 -> backend/lite/infer/dispatch.py:130-306
+  log_likelihood_at / log_joint_at           dispatch.py:331-361
+  reset_to_prior      trace_set.py:199-200
+Where the reference returns a list with one entry per trace (traces.map), a
+numpy array of length P is returned.
+"""
+import ctypes
+
+import numpy as np
+
+from . import _lib
+from .exception import VentureException
+
+_BLOCKS = {"one": _lib.BLOCK_ONE, "all": _lib.BLOCK_ALL, "each": _lib.BLOCK_EACH}
+
+
+def _unbox(v):
+    """Accept stack dicts {"type":..,"value":..} (python/lib/value/dicts.py) or raw values."""
+    if isinstance(v, dict) and "value" in v:
+        return v["value"]
+    return v
+
+
+class B200TraceSet(object):
+    def __init__(self, model, n_particles, seed=1, device=0, particle_base=0):
+        self.model = model
+        self.device = int(device)
+        self._h = model._create(int(n_particles), int(seed), self.device)
+        self.n_particles = int(n_particles)
+        if particle_base:
+            _lib.call("vk_set_particle_base", self._h, int(particle_base))
+        # `assume` simulates every latent from its prior (regen.py eval)
+        _lib.call("vk_reset_to_prior", self._h)
+
+    # -- lifetime --------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            _lib.load().vk_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def use_stream(self, cuda_stream):
+        """Run on a caller stream (e.g. torch.cuda.current_stream().cuda_stream)."""
+        _lib.call("vk_set_stream", self._h, ctypes.c_void_p(cuda_stream))
+
+    def synchronize(self):
+        _lib.call("vk_synchronize", self._h)
+
+    # -- seeds (trace_set.py has_own_prng/set_seed) ------------------------
+    def set_seed(self, seed):
+        _lib.call("vk_set_seed", self._h, int(seed))
+
+    def get_seed(self):
+        s = ctypes.c_uint64()
+        _lib.call("vk_get_seed", self._h, ctypes.byref(s))
+        return s.value
+
+    @property
+    def rng_step(self):
+        s = ctypes.c_uint32()
+        _lib.call("vk_get_step", self._h, ctypes.byref(s))
+        return s.value
+
+    @rng_step.setter
+    def rng_step(self, v):
+        _lib.call("vk_set_step", self._h, int(v))
+
+    # -- model building ----------------------------------------------------
+    def observe(self, *args):
+        """engine.observe -> TraceSet.observe (trace_set.py:154-155): values stay
+        unpropagated until incorporate()."""
+        self.model._observe(self._h, *args)
+
+    def forget_observations(self):
+        """engine.forget of every observation (trace_set.py:157-161): returns the
+        per-particle weights unconstrain() reports; log_weights unchanged."""
+        out = self._out()
+        _lib.call("vk_forget_observations", self._h, _lib.ptr(out))
+        return out
+
+    def reset_to_prior(self):
+        _lib.call("vk_reset_to_prior", self._h)
+
+    # -- weights -----------------------------------------------------------
+    def _out(self, n=None, dtype=np.float64):
+        return np.empty(self.n_particles if n is None else n, dtype=dtype)
+
+    @property
+    def log_weights(self):
+        out = self._out()
+        _lib.call("vk_get_log_weights", self._h, _lib.ptr(out))
+        return out
+
+    @log_weights.setter
+    def log_weights(self, values):
+        self.set_particle_log_weights(values)
+
+    def particle_log_weights(self):           # engine/inference.py:229-230
+        return self.log_weights
+
+    def set_particle_log_weights(self, values):   # engine/inference.py:232-234
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        if v.shape != (self.n_particles,):
+            raise VentureException("invalid_argument", "expected %d log weights" % self.n_particles)
+        _lib.call("vk_set_log_weights", self._h, _lib.ptr(v))
+
+    def increment_particle_log_weights(self, values):
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        if v.shape != (self.n_particles,):
+            raise VentureException("invalid_argument", "expected %d log weights" % self.n_particles)
+        _lib.call("vk_increment_log_weights", self._h, _lib.ptr(v))
+
+    def equalize_particle_log_weights(self):      # utils.log_domain_even_out
+        lse = self.logsumexp()
+        self.set_particle_log_weights(np.full(self.n_particles, lse - np.log(self.n_particles)))
+
+    def particle_normalized_probs(self):          # utils.logWeightsToNormalizedDirect
+        out = self._out()
+        _lib.call("vk_normalized_probs", self._h, _lib.ptr(out))
+        return out
+
+    def logsumexp(self):
+        out = ctypes.c_double()
+        _lib.call("vk_logsumexp", self._h, ctypes.byref(out))
+        return out.value
+
+    def likelihood_weight(self):
+        _lib.call("vk_likelihood_weight", self._h)
+
+    def incorporate(self):
+        out = self._out()
+        _lib.call("vk_make_consistent", self._h, _lib.ptr(out))
+        return out
+
+    def resample(self, P=None, mode="multinomial", uniforms=None, return_ancestors=False):
+        """trace_set.py:202-207.  mode: "multinomial" (reference semantics) or
+        "systematic".  `uniforms` overrides the stream draws (parity tests)."""
+        P = self.n_particles if P is None else int(P)
+        m = {"multinomial": _lib.RESAMPLE_MULTINOMIAL, "systematic": _lib.RESAMPLE_SYSTEMATIC,
+             "sequential": _lib.RESAMPLE_MULTINOMIAL}.get(mode)
+        if m is None:
+            raise VentureException("invalid_argument", "unknown resample mode %r" % (mode,))
+        u = None if uniforms is None else np.ascontiguousarray(np.atleast_1d(uniforms), dtype=np.float64)
+        anc = np.empty(P, dtype=np.int32) if return_ancestors else None
+        _lib.call("vk_resample", self._h, P, m, _lib.ptr(u), _lib.ptr(anc))
+        return anc
+
+    # -- inference ---------------------------------------------------------
+    def _scope_block(self, scope, block):
+        scope, block = _unbox(scope), _unbox(block)
+        if scope not in ("default", 0):
+            raise VentureException("invalid_argument", "only the default scope is compiled: %r" % (scope,))
+        if isinstance(block, str):
+            if block not in _BLOCKS:
+                raise VentureException("invalid_argument", "unknown block %r" % (block,))
+            return 0, _BLOCKS[block]
+        return 0, int(block)
+
+    def primitive_infer(self, exp):
+        """exp = [operator, scope, block, ...extra..., transitions]
+        (backend/lite/infer/dispatch.py:50-107, 130-161)."""
+        exp = [_unbox(e) for e in exp]
+        op = exp[0]
+        if op in ("resimulation_mh", "mh"):
+            if len(exp) != 4:
+                raise VentureException("invalid_argument", "%s takes (scope block transitions)" % op)
+            return self.resimulation_mh(exp[1], exp[2], exp[3])
+        if op == "subsampled_mh":
+            if len(exp) != 10:
+                raise VentureException(
+                    "invalid_argument",
+                    "subsampled_mh takes (scope block Nbatch k0 epsilon useDeltaKernels deltaKernelArgs "
+                    "updateValues transitions)")
+            return self.subsampled_mh(*exp[1:])
+        raise VentureException("invalid_argument", "operator %r is not on the B200 path" % (op,))
+
+    def resimulation_mh(self, scope, block, transitions, return_accepts=False):
+        s, b = self._scope_block(scope, block)
+        out = self._out()
+        acc = self._out(dtype=np.int64) if return_accepts else None
+        _lib.call("vk_mh", self._h, s, b, int(transitions), _lib.ptr(out), _lib.ptr(acc))
+        return (out, acc) if return_accepts else out
+
+    mh = resimulation_mh
+
+    def subsampled_mh(self, scope, block, Nbatch, k0, epsilon, useDeltaKernels, deltaKernelArgs,
+                      updateValues, transitions):
+        s, b = self._scope_block(scope, block)
+        stats = np.empty((self.n_particles, 3))
+        _lib.call("vk_subsampled_mh", self._h, s, b, int(Nbatch), int(k0), float(epsilon),
+                  int(bool(useDeltaKernels)), float(deltaKernelArgs or 0.0), int(bool(updateValues)),
+                  int(transitions), _lib.ptr(stats))
+        return stats
+
+    def log_likelihood_at(self, scope, block):
+        s, b = self._scope_block(scope, block)
+        out = self._out()
+        _lib.call("vk_log_likelihood_at", self._h, s, b, _lib.ptr(out))
+        return out
+
+    def log_joint_at(self, scope, block):
+        s, b = self._scope_block(scope, block)
+        out = self._out()
+        _lib.call("vk_log_joint_at", self._h, s, b, _lib.ptr(out))
+        return out
+
+    # -- state access --------------------------------------------------------
+    def numBlocksInScope(self, scope="default"):
+        n = ctypes.c_int64()
+        _lib.call("vk_num_blocks", self._h, 0, ctypes.byref(n))
+        return n.value
+
+    def num_sites(self):
+        n = ctypes.c_int64()
+        _lib.call("vk_num_sites", self._h, ctypes.byref(n))
+        return n.value
+
+    def read_site(self, site):
+        out = self._out()
+        _lib.call("vk_read_site", self._h, int(site), _lib.ptr(out))
+        return out
+
+    def write_site(self, site, values):
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        if v.shape != (self.n_particles,):
+            raise VentureException("invalid_argument", "expected %d values" % self.n_particles)
+        _lib.call("vk_write_site", self._h, int(site), _lib.ptr(v))
+
+    def refresh(self):
+        _lib.call("vk_refresh", self._h)
+
+    def device_buffer(self, which):
+        p, n = ctypes.c_void_p(), ctypes.c_int64()
+        _lib.call("vk_device_buffer", self._h, int(which), ctypes.byref(p), ctypes.byref(n))
+        return p.value, n.value

@@ -552,3 +552,152 @@ int orc_sequential_test(double mu_0, int k0, double Nbatch, double N, double eps
   *tstat_out = (have_t && tstat != 0) ? tstat : (accept ? INFINITY : -INFINITY);
   return accept;
 }
+
+/* ---------------------------------------------------------- C3: HMM */
+/* examples/hmm.vnt:31-60.  hist[P][Tpad] bytes, 1-based states; trans n_rows x S,
+ * emit S x O.  One filter step = transition draw (regen eval of the new mem
+ * family, prior proposal) + emission weight (trace.py:422-448, utils.py:106-118). */
+void orc_hmm_step(uint8_t *hist, int Tpad, int t, double *lw, double *incr, const double *trans, const double *emit,
+                  int S, int O, int init, int symbol, int64_t P, int64_t p_base, uint64_t seed, uint32_t step) {
+#pragma omp parallel for schedule(static)
+  for (int64_t p = 0; p < P; ++p) {
+    int s;
+    if (t == 0) s = init;
+    else {
+      orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step);
+      s = 1 + categorical_sim(&r, trans + (hist[p * Tpad + t - 1] - 1) * S, S);
+    }
+    hist[p * Tpad + t] = (uint8_t)s;
+    double w = categorical_logpmf(symbol - 1, emit + (s - 1) * O, O);
+    if (w != w) w = -INFINITY;
+    lw[p] += w;
+    if (incr) incr[p] = w;
+  }
+}
+void orc_hmm_prior(uint8_t *hist, int Tpad, int T, double *lw, const double *trans, const double *emit, int S, int O,
+                   int init, const int32_t *symbols, int64_t P, int64_t p_base, uint64_t seed, uint32_t step) {
+  for (int64_t p = 0; p < P; ++p) {
+    orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step);
+    int s = init; double w = 0;
+    for (int t = 0; t < T; ++t) {
+      if (t > 0) s = 1 + categorical_sim(&r, trans + (s - 1) * S, S);
+      hist[p * Tpad + t] = (uint8_t)s;
+      w += categorical_logpmf(symbols[t] - 1, emit + (s - 1) * O, O);
+    }
+    if (lw) lw[p] = w;
+  }
+}
+/* single-site MH on state(t), t = block+1 (0-based time), blocks = state(2..T) */
+void orc_hmm_mh(uint8_t *hist, int Tpad, int T, const double *trans, const double *emit, int S, int O,
+                const int32_t *symbols, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps,
+                int block_mode, int64_t *acc) {
+  int nb = T - 1;
+  for (int64_t p = 0; p < P; ++p) {
+    uint8_t *h = hist + p * Tpad; int64_t a = 0;
+    for (int k = 0; k < n_steps; ++k) {
+      orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
+      double u_sel = st_uniform(&r), logu = log(st_uniform(&r));
+      int b;
+      if (block_mode == -1) { b = (int)(u_sel * nb); if (b >= nb) b = nb - 1; }
+      else if (block_mode == -3) b = k % nb; else b = block_mode;
+      int t = b + 1, prev = h[t - 1], old = h[t], nxt = (t + 1 < T) ? h[t + 1] : 0;
+      /* detach: absorbing children = obs_t and state(t+1) */
+      double rho = categorical_logpmf(symbols[t] - 1, emit + (old - 1) * O, O);
+      if (nxt) rho += categorical_logpmf(nxt - 1, trans + (old - 1) * S, S);
+      int s = 1 + categorical_sim(&r, trans + (prev - 1) * S, S);
+      double xi = categorical_logpmf(symbols[t] - 1, emit + (s - 1) * O, O);
+      if (nxt) xi += categorical_logpmf(nxt - 1, trans + (s - 1) * S, S);
+      if (logu < mh_log_alpha(rho, xi)) { h[t] = (uint8_t)s; ++a; }
+    }
+    if (acc) acc[p] = a;
+  }
+}
+
+/* ---------------------------------------------------------- C4: LDA */
+/* examples/lda.vnt:18-41, collapsed makers.  Per particle p (particle-major):
+ * alpha[p][2], nk[p][K], ndk[p][n_docs*K], nkw[p][K*V] (int32 here), z[p][max_tok]. */
+typedef struct { int K, V, n_docs, max_tok; double a, b; } orc_lda;
+
+/* dirichlet.py:164-166 with the order-independent arithmetic of the product:
+ * first k with u*(N + K alpha) < C_k + (k+1) alpha */
+static int lda_sample_topic(const int32_t *row, int K, double alpha, double u) {
+  int tot = 0;
+  for (int k = 0; k < K; ++k) tot += row[k];
+  double t = u * ((double)tot + (double)K * alpha);
+  int c = 0;
+  for (int k = 0; k < K; ++k) { c += row[k]; if (t < (double)c + (double)(k + 1) * alpha) return k; }
+  return K - 1;
+}
+/* dirichlet.py:168-173 */
+static double dircat_logpmf(double c, double alpha, double N, double A) { return log((c + alpha) / (N + A)); }
+/* dirichlet.py:192-201 summed over tables */
+static double lda_aaa(const int32_t *counts, int n_tab, int n_cell, double alpha) {
+  double A = alpha * n_cell, acc = 0;
+  for (int t = 0; t < n_tab; ++t) {
+    double N = 0;
+    for (int i = 0; i < n_cell; ++i) N += counts[t * n_cell + i];
+    acc += lgamma(A) - lgamma(N + A);
+    for (int i = 0; i < n_cell; ++i) { int c = counts[t * n_cell + i]; if (c) acc += lgamma(alpha + c) - lgamma(alpha); }
+  }
+  return acc;
+}
+/* mode 0 make_consistent [t0,t1); 1 likelihood_weight; 2 reset_to_prior */
+void orc_lda_seq(double *alpha, int32_t *nk, int32_t *ndk, int32_t *nkw, uint8_t *z, const orc_lda *L,
+                 const int32_t *doc, const int32_t *word, int t0, int t1, double *lw, double *incr, int64_t P,
+                 int64_t p_base, uint64_t seed, uint32_t step, int mode) {
+  int K = L->K, V = L->V;
+  for (int64_t p = 0; p < P; ++p) {
+    double *al = alpha + p * 2; int32_t *NK = nk + p * K, *NDK = ndk + p * (int64_t)L->n_docs * K, *NKW = nkw + p * (int64_t)K * V;
+    uint8_t *Z = z + p * L->max_tok;
+    orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step);
+    if (mode >= 1) {
+      al[0] = gamma_sim(&r, L->a, L->b); al[1] = gamma_sim(&r, L->a, L->b);
+      memset(NK, 0, sizeof(int32_t) * K); memset(NDK, 0, sizeof(int32_t) * (size_t)L->n_docs * K);
+      memset(NKW, 0, sizeof(int32_t) * (size_t)K * V);
+    }
+    double wsum = 0;
+    for (int i = t0; i < t1; ++i) {
+      int d = doc[i], w = word[i];
+      int zi = lda_sample_topic(NDK + d * K, K, al[0], st_uniform(&r));
+      wsum += dircat_logpmf(NKW[(int64_t)zi * V + w], al[1], NK[zi], al[1] * V);
+      Z[i] = (uint8_t)zi; NDK[d * K + zi]++; NKW[(int64_t)zi * V + w]++; NK[zi]++;
+    }
+    if (mode == 0) { if (wsum != wsum) wsum = -INFINITY; if (incr) incr[p] = wsum; lw[p] += wsum; }
+    else if (mode == 1) lw[p] = wsum;
+  }
+}
+void orc_lda_mh(double *alpha, int32_t *nk, int32_t *ndk, int32_t *nkw, uint8_t *z, const orc_lda *L,
+                const int32_t *doc, const int32_t *word, int n_tok, int64_t P, int64_t p_base, uint64_t seed,
+                uint32_t step0, int n_steps, int block_mode, int64_t *acc) {
+  int K = L->K, V = L->V, nb = 2 + n_tok;
+#pragma omp parallel for schedule(dynamic, 1)
+  for (int64_t p = 0; p < P; ++p) {
+    double *al = alpha + p * 2; int32_t *NK = nk + p * K, *NDK = ndk + p * (int64_t)L->n_docs * K, *NKW = nkw + p * (int64_t)K * V;
+    uint8_t *Z = z + p * L->max_tok; int64_t a = 0;
+    for (int k = 0; k < n_steps; ++k) {
+      orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
+      double u_sel = st_uniform(&r), logu = log(st_uniform(&r));
+      int b;
+      if (block_mode == -1) { b = (int)(u_sel * nb); if (b >= nb) b = nb - 1; }
+      else if (block_mode == -3) b = k % nb; else b = block_mode;
+      if (b < 2) {
+        /* AAA: DeterministicMakerAAALKernel weight = sum logDensityOfData (lkernel.py:158-171) */
+        double a_new = gamma_sim(&r, L->a, L->b), rho, xi;
+        if (b == 0) { rho = lda_aaa(NDK, L->n_docs, K, al[0]); xi = lda_aaa(NDK, L->n_docs, K, a_new); }
+        else { rho = lda_aaa(NKW, K, V, al[1]); xi = lda_aaa(NKW, K, V, a_new); }
+        if (logu < mh_log_alpha(rho, xi)) { al[b] = a_new; ++a; }
+      } else {
+        int i = b - 2, d = doc[i], w = word[i], zo = Z[i];
+        /* detach: unconstrain + unincorporate token and z (detach.py:52-65,165-201) */
+        NKW[(int64_t)zo * V + w]--; NK[zo]--; NDK[d * K + zo]--;
+        double rho = dircat_logpmf(NKW[(int64_t)zo * V + w], al[1], NK[zo], al[1] * V);
+        int zn = lda_sample_topic(NDK + d * K, K, al[0], st_uniform(&r));
+        double xi = dircat_logpmf(NKW[(int64_t)zn * V + w], al[1], NK[zn], al[1] * V);
+        int zf = zo;
+        if (logu < mh_log_alpha(rho, xi)) { zf = zn; ++a; }
+        Z[i] = (uint8_t)zf; NKW[(int64_t)zf * V + w]++; NK[zf]++; NDK[d * K + zf]++;
+      }
+    }
+    if (acc) acc[p] = a;
+  }
+}

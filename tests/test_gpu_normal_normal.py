@@ -87,7 +87,9 @@ def test_posterior_normal_12_sqrt_half():
     ts = vb.B200TraceSet(vb.NormalNormalModel(10.0, 1.0, 1.0), P, seed=5)
     ts.observe([14.0])
     ts.incorporate()
-    ts.primitive_infer(["resimulation_mh", "default", "one", 40])
+    # independence sampler from the prior: sup(posterior/prior) ~ 77, so the chain
+    # needs ~10^3 transitions to forget its start ((1-1/77)^1500 ~ 3e-9)
+    ts.primitive_infer(["resimulation_mh", "default", "one", 1500])
     x = ts.read_site(0)
     assert st.kstest(x, st.norm(loc=12, scale=np.sqrt(0.5)).cdf).pvalue > 1e-5
 

@@ -1,0 +1,297 @@
+// Config C3: the HMM of examples/hmm.vnt:31-60 as a particle filter.
+//   state(1) = init;  state(t) ~ categorical(T[state(t-1)-1], [1..S])
+//   observe categorical(E[state(t)-1], [1..O]) = d_t
+// Reference flow per time step (hmm.vnt:66-92, SURVEY App. A "C3"):
+//   observe   -> evaluating state(t) SIMULATES the transition from the prior
+//                (regen.py eval of a new mem family), the emission node waits
+//                as an unpropagated observation            lite/trace.py:415-420
+//   incorporate -> lw += log E[s_t][d_t]                    lite/trace.py:422-448,
+//                                                          utils.py:106-118
+//   resample  -> k_weights.cu
+// Here the transition draw and the emission weight are ONE kernel (the draw
+// is deferred from observe to incorporate; nothing can read the state in
+// between).  Layout: cur[P] int32 (state at the newest time), hist[P][Tpad]
+// uint8 rows (the whole mem table of `state`, which the reference copies with
+// the trace on resample).  One thread per particle; HBM-bound:
+// 4+4 B cur, 1 B hist, 8+8 B lw per particle-step.
+#include "vk_common.cuh"
+#include "sp_math.cuh"
+
+namespace vk {
+
+static const int HMM_MAX_S = 32;
+
+struct HMMTables {
+  int S, O, n_rows, init;
+  const double *trans;  // n_rows x S
+  const double *emit;   // S x O
+};
+
+// propagate one time step and weight by the emission
+__global__ void __launch_bounds__(256)
+hmm_step_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, int t /*0-based*/,
+                double *__restrict__ lw, double *__restrict__ incr, HMMTables tb, int symbol /*1-based*/,
+                int64_t P, int64_t p_base, uint64_t seed, uint32_t step, int accumulate_incr) {
+  extern __shared__ double sh[];
+  double *tr = sh;                       // n_rows*S
+  double *em = sh + tb.n_rows * tb.S;    // S*O
+  for (int i = threadIdx.x; i < tb.n_rows * tb.S; i += blockDim.x) tr[i] = tb.trans[i];
+  for (int i = threadIdx.x; i < tb.S * tb.O; i += blockDim.x) em[i] = tb.emit[i];
+  __syncthreads();
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    int s;
+    if (t == 0) {
+      s = tb.init;  // hmm.vnt:57-59: (if (<= t 1) 1 ...)
+    } else {
+      Stream r(seed, (uint64_t)(p_base + p), step);
+      int prev = cur[p];
+      s = 1 + categorical_sim(r, tr + (prev - 1) * tb.S, tb.S, 1);
+    }
+    cur[p] = s;
+    hist[p * Tpad + t] = (uint8_t)s;
+    double w = categorical_logpmf(symbol - 1, em + (s - 1) * tb.O, tb.O, 1);
+    if (w != w) w = -INFINITY;
+    lw[p] += w;
+    if (incr) incr[p] = accumulate_incr ? incr[p] + w : w;
+  }
+}
+
+// likelihood_weight: resimulate states 2..t from the prior, lw := sum_t log E
+__global__ void __launch_bounds__(256)
+hmm_lw_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, int T,
+              double *__restrict__ lw, HMMTables tb, const int32_t *__restrict__ symbols, int64_t P,
+              int64_t p_base, uint64_t seed, uint32_t step, int write_lw) {
+  extern __shared__ double sh[];
+  double *tr = sh;
+  double *em = sh + tb.n_rows * tb.S;
+  for (int i = threadIdx.x; i < tb.n_rows * tb.S; i += blockDim.x) tr[i] = tb.trans[i];
+  for (int i = threadIdx.x; i < tb.S * tb.O; i += blockDim.x) em[i] = tb.emit[i];
+  __syncthreads();
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    Stream r(seed, (uint64_t)(p_base + p), step);
+    int s = tb.init;
+    double w = 0.0;
+    for (int t = 0; t < T; ++t) {
+      if (t > 0) s = 1 + categorical_sim(r, tr + (s - 1) * tb.S, tb.S, 1);
+      hist[p * Tpad + t] = (uint8_t)s;
+      w += categorical_logpmf(symbols[t] - 1, em + (s - 1) * tb.O, tb.O, 1);
+    }
+    if (T > 0) cur[p] = s;
+    if (write_lw) lw[p] = w;
+  }
+}
+
+// single-site resimulation MH over the state sequence (scope default: one
+// block per random choice = state(2..T)).  scaffold(state(t)): DRG {state(t)},
+// absorbing {state(t+1) (its categorical parameter row changes), obs_t}.
+__global__ void __launch_bounds__(256)
+hmm_mh_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, int T, HMMTables tb,
+              const int32_t *__restrict__ symbols, int64_t P, int64_t p_base, uint64_t seed,
+              uint32_t step0, int n_steps, int block_mode, long long *__restrict__ acc_out) {
+  extern __shared__ double sh[];
+  double *tr = sh;
+  double *em = sh + tb.n_rows * tb.S;
+  for (int i = threadIdx.x; i < tb.n_rows * tb.S; i += blockDim.x) tr[i] = tb.trans[i];
+  for (int i = threadIdx.x; i < tb.S * tb.O; i += blockDim.x) em[i] = tb.emit[i];
+  __syncthreads();
+  const int nb = T - 1;  // blocks: state(2..T)
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    uint8_t *h = hist + p * Tpad;
+    long long acc = 0;
+    for (int k = 0; k < n_steps; ++k) {
+      Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
+      double u_sel = r.uniform();
+      double logu = log(r.uniform());
+      int b;
+      if (block_mode == VK_BLOCK_ONE) { b = (int)(u_sel * (double)nb); if (b >= nb) b = nb - 1; }
+      else if (block_mode == VK_BLOCK_EACH) b = k % nb;
+      else b = block_mode;
+      int t = b + 1;  // 0-based time index of the site
+      int prev = h[t - 1], old = h[t];
+      int nxt = (t + 1 < T) ? h[t + 1] : 0;
+      double rho = categorical_logpmf(symbols[t] - 1, em + (old - 1) * tb.O, tb.O, 1);
+      if (nxt) rho += categorical_logpmf(nxt - 1, tr + (old - 1) * tb.S, tb.S, 1);
+      int s = 1 + categorical_sim(r, tr + (prev - 1) * tb.S, tb.S, 1);
+      double xi = categorical_logpmf(symbols[t] - 1, em + (s - 1) * tb.O, tb.O, 1);
+      if (nxt) xi += categorical_logpmf(nxt - 1, tr + (s - 1) * tb.S, tb.S, 1);
+      double alpha;
+      if (rho == -INFINITY && xi == -INFINITY) alpha = INFINITY;
+      else if (rho == INFINITY && xi == INFINITY) alpha = -INFINITY;
+      else alpha = xi - rho;
+      if (logu < alpha) { h[t] = (uint8_t)s; ++acc; }
+    }
+    if (T > 0) cur[p] = h[T - 1];
+    if (acc_out) acc_out[p] = acc;
+  }
+}
+
+__global__ void hmm_loglik_kernel(const uint8_t *__restrict__ hist, int Tpad, int T, HMMTables tb,
+                                  const int32_t *__restrict__ symbols, int64_t P, int joint,
+                                  double *__restrict__ out) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    const uint8_t *h = hist + p * Tpad;
+    double w = 0.0;
+    for (int t = 0; t < T; ++t) {
+      w += categorical_logpmf(symbols[t] - 1, tb.emit + (h[t] - 1) * tb.O, tb.O, 1);
+      if (joint && t > 0) w += categorical_logpmf(h[t] - 1, tb.trans + (h[t - 1] - 1) * tb.S, tb.S, 1);
+    }
+    out[p] = w;
+  }
+}
+
+__global__ void hmm_read_kernel(const uint8_t *__restrict__ hist, int Tpad, int t, int64_t P, double *out) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x)
+    out[p] = (double)hist[p * Tpad + t];
+}
+__global__ void hmm_write_kernel(uint8_t *__restrict__ hist, int32_t *__restrict__ cur, int Tpad, int t,
+                                 int is_last, int64_t P, const double *in) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    int s = (int)in[p];
+    hist[p * Tpad + t] = (uint8_t)s;
+    if (is_last) cur[p] = s;
+  }
+}
+__global__ void hmm_fill_kernel(double *out, int64_t n, double v) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = v;
+}
+
+struct HMMModel : Model {
+  HMMTables tb;
+  int T_max, Tpad, T = 0 /*propagated time steps*/;
+  std::vector<int32_t> symbols_host;   // all observed symbols (propagated first, then pending)
+  DevBuf<double> trans, emit;
+  DevBuf<int32_t> symbols, cura, curb;
+  DevBuf<uint8_t> hista, histb;
+  int32_t *cur = nullptr, *cur_alt = nullptr;
+  uint8_t *hist = nullptr, *hist_alt = nullptr;
+  size_t smem;
+
+  HMMModel(vk_particles *h_, int S, int O, int n_rows, const double *trans_host, const double *emit_host,
+           int init, int T_max_) : Model(h_), T_max(T_max_) {
+    VK_REQUIRE(S >= 1 && S <= HMM_MAX_S && O >= 1 && O <= 255, VK_EINVAL, "hmm: S must be in [1,32], O in [1,255]");
+    VK_REQUIRE(n_rows >= S, VK_EINVAL, "hmm: transition matrix needs at least S rows");
+    VK_REQUIRE(init >= 1 && init <= S, VK_EINVAL, "hmm: init_state out of range");
+    VK_REQUIRE(T_max >= 1 && T_max <= 4096, VK_EINVAL, "hmm: T_max must be in [1,4096]");
+    tb.S = S; tb.O = O; tb.n_rows = n_rows; tb.init = init;
+    trans.alloc((size_t)n_rows * S); emit.alloc((size_t)S * O);
+    VK_CUDA(cudaMemcpyAsync(trans.p, trans_host, trans.bytes(), cudaMemcpyHostToDevice, h->stream));
+    VK_CUDA(cudaMemcpyAsync(emit.p, emit_host, emit.bytes(), cudaMemcpyHostToDevice, h->stream));
+    tb.trans = trans.p; tb.emit = emit.p;
+    Tpad = (T_max + 15) & ~15;
+    symbols.alloc((size_t)T_max);
+    cura.alloc((size_t)h->P); curb.alloc((size_t)h->P);
+    hista.alloc((size_t)h->P * Tpad); histb.alloc((size_t)h->P * Tpad);
+    cur = cura.p; cur_alt = curb.p; hist = hista.p; hist_alt = histb.p;
+    VK_CUDA(cudaMemsetAsync(cur, 0, cura.bytes(), h->stream));
+    VK_CUDA(cudaMemsetAsync(hist, 0, hista.bytes(), h->stream));
+    VK_CUDA(cudaMemsetAsync(hist_alt, 0, histb.bytes(), h->stream));
+    smem = (size_t)(n_rows * S + S * O) * sizeof(double);
+  }
+  int grid() const { return grid_for(h->P, 256, h->sm_count, 8); }
+  void observe(int symbol) {
+    VK_REQUIRE(symbol >= 1 && symbol <= tb.O, VK_EINVAL, "hmm: observed symbol out of range");
+    VK_REQUIRE((int)symbols_host.size() < T_max, VK_EINVAL, "hmm: history capacity (T_max) exceeded");
+    symbols_host.push_back(symbol);
+  }
+  void upload_symbols() {
+    if (!symbols_host.empty())
+      VK_CUDA(cudaMemcpyAsync(symbols.p, symbols_host.data(), symbols_host.size() * sizeof(int32_t),
+                              cudaMemcpyHostToDevice, h->stream));
+  }
+  void make_consistent(double *incr_dev) override {
+    int n = (int)symbols_host.size();
+    if (T == n) {
+      if (incr_dev) VK_CUDA(cudaMemsetAsync(incr_dev, 0, (size_t)h->P * sizeof(double), h->stream));
+      return;
+    }
+    bool first = true;
+    for (; T < n; ++T) {
+      uint32_t step = h->next_step();
+      hmm_step_kernel<<<grid(), 256, smem, h->stream>>>(cur, hist, Tpad, T, h->lw.p, incr_dev, tb, symbols_host[T],
+                                                        h->P, h->p_base, h->seed, step, first ? 0 : 1);
+      first = false;
+    }
+    VK_CUDA(cudaGetLastError());
+  }
+  void run_prior(bool write_lw) {
+    T = (int)symbols_host.size();
+    upload_symbols();
+    uint32_t step = h->next_step();
+    hmm_lw_kernel<<<grid(), 256, smem, h->stream>>>(cur, hist, Tpad, T, h->lw.p, tb, symbols.p, h->P, h->p_base,
+                                                    h->seed, step, write_lw ? 1 : 0);
+    VK_CUDA(cudaGetLastError());
+    VK_CUDA(cudaStreamSynchronize(h->stream));  // symbols_host stays valid for the async copy
+  }
+  void likelihood_weight() override { run_prior(true); }
+  void reset_to_prior() override { run_prior(false); }
+  void mh(int scope, int block, int K, double *mean_nodes_dev, long long *acc_dev) override {
+    VK_REQUIRE(scope == 0, VK_EINVAL, "hmm: only the default scope exists");
+    VK_REQUIRE(T == (int)symbols_host.size(), VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
+    int nb = T - 1;
+    VK_REQUIRE(block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || (block >= 0 && block < nb), VK_EINVAL, "hmm: bad block");
+    double nodes = 0.0;
+    if (K > 0 && nb > 0) {  // zero-entropy scope performs no transitions (dispatch.py:55-56)
+      int n_steps = block == VK_BLOCK_EACH ? K * nb : K;
+      uint32_t step0 = h->next_step((uint32_t)n_steps);
+      upload_symbols();
+      hmm_mh_kernel<<<grid(), 256, smem, h->stream>>>(cur, hist, Tpad, T, tb, symbols.p, h->P, h->p_base, h->seed,
+                                                      step0, n_steps, block, acc_dev);
+      VK_CUDA(cudaGetLastError());
+      VK_CUDA(cudaStreamSynchronize(h->stream));
+      // DRG of state(t): the transition application's request + output nodes and the
+      // lookups that consume the state; reported as a per-model constant
+      nodes = 1.0 * (block == VK_BLOCK_EACH ? nb : 1);
+    } else if (acc_dev) {
+      VK_CUDA(cudaMemsetAsync(acc_dev, 0, (size_t)h->P * sizeof(long long), h->stream));
+    }
+    if (mean_nodes_dev) hmm_fill_kernel<<<grid(), 256, 0, h->stream>>>(mean_nodes_dev, h->P, nodes);
+  }
+  void log_likelihood_at(int scope, int block, bool joint, double *out_dev) override {
+    VK_REQUIRE(scope == 0, VK_EINVAL, "hmm: only the default scope exists");
+    VK_REQUIRE(block == VK_BLOCK_ALL, VK_EUNSUPPORTED, "hmm: log_likelihood_at is compiled for block all");
+    upload_symbols();
+    hmm_loglik_kernel<<<grid(), 256, 0, h->stream>>>(hist, Tpad, T, tb, symbols.p, h->P, joint ? 1 : 0, out_dev);
+    VK_CUDA(cudaGetLastError());
+    VK_CUDA(cudaStreamSynchronize(h->stream));
+  }
+  void forget_observations(double *w_dev) override {
+    if (w_dev) log_likelihood_at(0, VK_BLOCK_ALL, false, w_dev);
+    symbols_host.clear(); T = 0;
+  }
+  int64_t num_sites() const override { return T; }
+  int64_t num_blocks(int) const override { return T > 1 ? T - 1 : 0; }
+  void read_site(int64_t site, double *out_dev) override {
+    VK_REQUIRE(site >= 0 && site < T, VK_EINVAL, "hmm: site (0-based time index) out of range");
+    hmm_read_kernel<<<grid(), 256, 0, h->stream>>>(hist, Tpad, (int)site, h->P, out_dev);
+  }
+  void write_site(int64_t site, const double *in_dev) override {
+    VK_REQUIRE(site >= 0 && site < T, VK_EINVAL, "hmm: site (0-based time index) out of range");
+    hmm_write_kernel<<<grid(), 256, 0, h->stream>>>(hist, cur, Tpad, (int)site, site == T - 1, h->P, in_dev);
+  }
+  std::vector<StateArray> state_arrays() override {
+    StateArray a{(void **)&cur, (void **)&cur_alt, 0, 1, 4};
+    StateArray b{(void **)&hist, (void **)&hist_alt, (size_t)Tpad, 0, 0};
+    return {a, b};
+  }
+  int device_buffer(int which, void **p, int64_t *bytes) override {
+    if (which == 1) { *p = cur; *bytes = (int64_t)cura.bytes(); return VK_OK; }
+    if (which == 2) { *p = hist; *bytes = (int64_t)hista.bytes(); return VK_OK; }
+    return VK_EINVAL;
+  }
+};
+
+Model *make_hmm(vk_particles *h, int S, int O, int n_trans_rows, const double *trans_host,
+                const double *emit_host, int init_state, int T_max) {
+  return new HMMModel(h, S, O, n_trans_rows, trans_host, emit_host, init_state, T_max);
+}
+void hmm_observe(Model *m, int symbol) { static_cast<HMMModel *>(m)->observe(symbol); }
+
+}  // namespace vk

@@ -1,0 +1,401 @@
+// Config C4: LDA with collapsed symmetric-Dirichlet/categorical makers
+// (examples/lda.vnt:18-41):
+//   alpha_document_topic ~ gamma(a,b); alpha_topic_word ~ gamma(a,b)
+//   doc(d)   = make_sym_dir_cat(alpha_document_topic, K)
+//   topic(k) = make_sym_dir_cat(alpha_topic_word, V)
+//   word(d,pos) = ((topic ((doc d))));   observe word(d,pos) = w
+// Site programs (SURVEY App. A "C4"), default scope, blocks in creation order:
+//   block 0: alpha_document_topic, block 1: alpha_topic_word  -- AAA sites:
+//     rho/xi = sum over made SPs of CDirCatOutputPSP.logDensityOfData
+//     (lkernel.py:158-171, dirichlet.py:192-201); proposal from the gamma prior
+//   block 2+i: z_i = ((doc d_i)) of token i:
+//     detach: unconstrain the token, rho = log((n_{z,w}^- + aw)/(n_z^- + V aw))
+//             (detach.py:52-65, dirichlet.py:168-173), unincorporate token and z
+//     regen : z' ~ (n_{d,k}^- + ad) (dirichlet.py:164-166), re-constrain the token,
+//             xi = log((n_{z',w}^- + aw)/(n_{z'}^- + V aw))   (regen.py:68-88)
+//
+// State: ONE ROW PER PARTICLE in HBM (particle-major, 16-byte aligned)
+//   [alpha_d, alpha_w : 2 x f64][n_k : K x u32][n_dk : n_docs*K x u16]
+//   [n_kw : K*V x u16][z : max_tokens x u8]
+// Kernel mapping: one warp (= one CTA) per particle.  The whole row is staged
+// in shared memory (38 KB at C4: 5-6 resident particles per SM), the launch's
+// transitions run on chip -- the chain of one particle is inherently
+// sequential, lanes parallelise the K-way topic scan and the lgamma sums of
+// the alpha sites -- and the row is written back once.  Latency-bound, not
+// HBM-bound; see DESIGN.md.
+#include "vk_common.cuh"
+#include "sp_math.cuh"
+
+namespace vk {
+
+struct LDALayout {
+  int K, V, n_docs, max_tokens;
+  size_t off_nk, off_ndk, off_nkw, off_z, row_bytes;
+  double hyper_a, hyper_b;
+};
+
+struct LDARow {
+  double *alpha; uint32_t *nk; uint16_t *ndk; uint16_t *nkw; uint8_t *z;
+  __device__ LDARow(unsigned char *base, const LDALayout &L)
+      : alpha((double *)base), nk((uint32_t *)(base + L.off_nk)), ndk((uint16_t *)(base + L.off_ndk)),
+        nkw((uint16_t *)(base + L.off_nkw)), z(base + L.off_z) {}
+};
+
+__device__ __forceinline__ int warp_scan_incl_i(int v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += t; }
+  return v;
+}
+__device__ __forceinline__ int warp_sum_i(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// z ~ (counts_k + alpha): first k with u*(N + K alpha) < C_k + (k+1) alpha, C = exact
+// integer prefix counts (dirichlet.py:164-166; order-independent arithmetic).
+__device__ __forceinline__ int lda_sample_topic(const uint16_t *row, int K, double alpha, double u, int lane) {
+  int tot = 0;
+  for (int b = 0; b < K; b += 32) { int k = b + lane; tot += (k < K) ? (int)row[k] : 0; }
+  tot = warp_sum_i(tot);
+  double t = u * ((double)tot + (double)K * alpha);
+  int carry = 0;
+  for (int b = 0; b < K; b += 32) {
+    int k = b + lane;
+    int c = (k < K) ? (int)row[k] : 0;
+    int incl = warp_scan_incl_i(c, lane) + carry;
+    double cum = (double)incl + (double)(k + 1) * alpha;
+    unsigned m = __ballot_sync(0xffffffffu, (k < K) && (t < cum));
+    if (m) return b + __ffs(m) - 1;
+    carry = __shfl_sync(0xffffffffu, incl, 31);
+  }
+  return K - 1;
+}
+
+// sum over tables of logDensityOfData(counts; alpha): n_tab tables of n_cell cells
+// (dirichlet.py:192-201).  totals[t] = N of table t (nullptr: derive from `fixed_tot`).
+__device__ double lda_aaa_weight(const uint16_t *counts, int n_tab, int n_cell, const uint32_t *totals,
+                                 const int32_t *fixed_tot, double alpha, int lane) {
+  double A = alpha * (double)n_cell;
+  double lgA = lgamma(A), lga = lgamma(alpha);
+  double acc = 0.0;
+  for (int t = lane; t < n_tab; t += 32) {
+    double N = totals ? (double)totals[t] : (double)fixed_tot[t];
+    acc += lgA - lgamma(N + A);
+  }
+  int64_t cells = (int64_t)n_tab * n_cell;
+  for (int64_t i = lane; i < cells; i += 32) {
+    int c = counts[i];
+    if (c) acc += lgamma(alpha + (double)c) - lga;
+  }
+  return warp_sum(acc);
+}
+
+// mode 0: make_consistent over tokens [t0,t1): z ~ prior predictive, weight by the word, incorporate
+// mode 1: likelihood_weight: alphas ~ prior, counts cleared, tokens [0,t1) as mode 0, lw := sum
+// mode 2: reset_to_prior: as 1 but weights untouched
+// mode 3: refresh: recount from z (after write_site)
+__global__ void __launch_bounds__(32)
+lda_seq_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__restrict__ doc,
+               const int32_t *__restrict__ word, int t0, int t1, double *__restrict__ lw,
+               double *__restrict__ incr, int64_t P, int64_t p_base, uint64_t seed, uint32_t step, int mode) {
+  const int lane = threadIdx.x;
+  for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
+    LDARow R(rows + p * L.row_bytes, L);
+    Stream r(seed, (uint64_t)(p_base + p), step);
+    if (mode == 1 || mode == 2) {
+      double ad = gamma_sim(r, L.hyper_a, L.hyper_b);
+      double aw = gamma_sim(r, L.hyper_a, L.hyper_b);
+      if (lane == 0) { R.alpha[0] = ad; R.alpha[1] = aw; }
+    }
+    if (mode >= 1) {
+      for (int i = lane; i < L.K; i += 32) R.nk[i] = 0;
+      for (int i = lane; i < L.n_docs * L.K; i += 32) R.ndk[i] = 0;
+      for (int64_t i = lane; i < (int64_t)L.K * L.V; i += 32) R.nkw[i] = 0;
+    }
+    __syncwarp();
+    double ad = R.alpha[0], aw = R.alpha[1];
+    double wsum = 0.0;
+    for (int i = t0; i < t1; ++i) {
+      int d = doc[i], w = word[i];
+      int zi;
+      if (mode == 3) zi = R.z[i];
+      else zi = lda_sample_topic(R.ndk + d * L.K, L.K, ad, r.uniform(), lane);
+      if (lane == 0) {
+        wsum += dircat_logpmf((double)R.nkw[(int64_t)zi * L.V + w], aw, (double)R.nk[zi], aw * (double)L.V);
+        R.z[i] = (uint8_t)zi;
+        R.ndk[d * L.K + zi] += 1; R.nkw[(int64_t)zi * L.V + w] += 1; R.nk[zi] += 1;
+      }
+      __syncwarp();
+    }
+    if (lane == 0) {
+      if (mode == 0) {
+        if (wsum != wsum) wsum = -INFINITY;
+        if (incr) incr[p] = wsum;
+        lw[p] += wsum;
+      } else if (mode == 1) lw[p] = wsum;
+    }
+  }
+}
+
+// K resimulation-MH transitions per particle on the staged row.
+__global__ void __launch_bounds__(32)
+lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__restrict__ doc,
+              const int32_t *__restrict__ word, const int32_t *__restrict__ doclen, int n_tok,
+              int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int block_mode,
+              int stage, long long *__restrict__ acc_out) {
+  extern __shared__ uint4 smem_u4[];
+  const int lane = threadIdx.x;
+  const int nb = 2 + n_tok;
+  for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
+    unsigned char *grow = rows + p * L.row_bytes;
+    unsigned char *base = grow;
+    if (stage) {
+      const uint4 *src = (const uint4 *)grow;
+      for (size_t i = lane; i < L.row_bytes / 16; i += 32) smem_u4[i] = src[i];
+      base = (unsigned char *)smem_u4;
+      __syncwarp();
+    }
+    LDARow R(base, L);
+    long long acc = 0;
+    for (int k = 0; k < n_steps; ++k) {
+      Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
+      double u_sel = r.uniform();
+      double logu = log(r.uniform());
+      int b;
+      if (block_mode == VK_BLOCK_ONE) { b = (int)(u_sel * (double)nb); if (b >= nb) b = nb - 1; }
+      else if (block_mode == VK_BLOCK_EACH) b = k % nb;
+      else b = block_mode;
+      if (b < 2) {
+        // AAA site: alpha' from the gamma prior (no proposal weight), rho/xi = marginal
+        // likelihood of every made SP's counts under the old/new concentration
+        double a_old = R.alpha[b];
+        double a_new = gamma_sim(r, L.hyper_a, L.hyper_b);
+        double rho, xi;
+        if (b == 0) {
+          rho = lda_aaa_weight(R.ndk, L.n_docs, L.K, nullptr, doclen, a_old, lane);
+          xi = lda_aaa_weight(R.ndk, L.n_docs, L.K, nullptr, doclen, a_new, lane);
+        } else {
+          rho = lda_aaa_weight(R.nkw, L.K, L.V, R.nk, nullptr, a_old, lane);
+          xi = lda_aaa_weight(R.nkw, L.K, L.V, R.nk, nullptr, a_new, lane);
+        }
+        double alpha = (rho == -INFINITY && xi == -INFINITY) ? INFINITY
+                       : (rho == INFINITY && xi == INFINITY) ? -INFINITY : xi - rho;
+        if (logu < alpha) { if (lane == 0) R.alpha[b] = a_new; ++acc; }
+        __syncwarp();
+      } else {
+        int i = b - 2;
+        int d = doc[i], w = word[i];
+        int zo = R.z[i];
+        double ad = R.alpha[0], aw = R.alpha[1];
+        double Aw = aw * (double)L.V;
+        int64_t co = (int64_t)zo * L.V + w;
+        // counts with this token (and its z) removed
+        double rho = dircat_logpmf((double)((int)R.nkw[co] - 1), aw, (double)((int)R.nk[zo] - 1), Aw);
+        __syncwarp();
+        if (lane == 0) { R.nkw[co] -= 1; R.nk[zo] -= 1; R.ndk[d * L.K + zo] -= 1; }
+        __syncwarp();
+        int zn = lda_sample_topic(R.ndk + d * L.K, L.K, ad, r.uniform(), lane);
+        int64_t cn = (int64_t)zn * L.V + w;
+        double xi = dircat_logpmf((double)R.nkw[cn], aw, (double)R.nk[zn], Aw);
+        double alpha = (rho == -INFINITY && xi == -INFINITY) ? INFINITY
+                       : (rho == INFINITY && xi == INFINITY) ? -INFINITY : xi - rho;
+        int zf = (logu < alpha) ? zn : zo;
+        if (logu < alpha) ++acc;
+        __syncwarp();
+        if (lane == 0) {
+          R.z[i] = (uint8_t)zf;
+          R.nkw[(int64_t)zf * L.V + w] += 1; R.nk[zf] += 1; R.ndk[d * L.K + zf] += 1;
+        }
+        __syncwarp();
+      }
+    }
+    if (stage) {
+      uint4 *dst = (uint4 *)grow;
+      for (size_t i = lane; i < L.row_bytes / 16; i += 32) dst[i] = smem_u4[i];
+      __syncwarp();
+    }
+    if (acc_out && lane == 0) acc_out[p] = acc;
+  }
+}
+
+// log_likelihood_at(default, all): sum over tokens of the sequential predictive
+// is NOT what the reference computes; it sums each token's logDensity given all
+// other counts removed one at a time.  Compiled here for block = a z site or an
+// alpha site (the scaffold's border weights).
+__global__ void __launch_bounds__(32)
+lda_loglik_site_kernel(const unsigned char *__restrict__ rows, LDALayout L, const int32_t *__restrict__ doc,
+                       const int32_t *__restrict__ word, const int32_t *__restrict__ doclen, int block,
+                       int joint, int64_t P, double *__restrict__ out) {
+  const int lane = threadIdx.x;
+  for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
+    LDARow R(const_cast<unsigned char *>(rows) + p * L.row_bytes, L);
+    double v;
+    if (block == 0) {
+      v = lda_aaa_weight(R.ndk, L.n_docs, L.K, nullptr, doclen, R.alpha[0], lane);
+      if (joint) v += gamma_logpdf(R.alpha[0], L.hyper_a, L.hyper_b);
+    } else if (block == 1) {
+      v = lda_aaa_weight(R.nkw, L.K, L.V, R.nk, nullptr, R.alpha[1], lane);
+      if (joint) v += gamma_logpdf(R.alpha[1], L.hyper_a, L.hyper_b);
+    } else {
+      int i = block - 2, d = doc[i], w = word[i], zo = R.z[i];
+      double aw = R.alpha[1];
+      v = dircat_logpmf((double)((int)R.nkw[(int64_t)zo * L.V + w] - 1), aw, (double)((int)R.nk[zo] - 1),
+                        aw * (double)L.V);
+      if (joint) {
+        int nd = 0;
+        for (int k = 0; k < L.K; ++k) nd += R.ndk[d * L.K + k];
+        v += dircat_logpmf((double)((int)R.ndk[d * L.K + zo] - 1), R.alpha[0], (double)(nd - 1),
+                           R.alpha[0] * (double)L.K);
+      }
+    }
+    if (lane == 0) out[p] = v;
+  }
+}
+
+__global__ void lda_read_kernel(const unsigned char *__restrict__ rows, LDALayout L, int64_t site, int64_t P,
+                                double *out) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    const unsigned char *b = rows + p * L.row_bytes;
+    out[p] = site < 2 ? ((const double *)b)[site] : (double)b[L.off_z + (site - 2)];
+  }
+}
+__global__ void lda_write_kernel(unsigned char *__restrict__ rows, LDALayout L, int64_t site, int64_t P,
+                                 const double *in) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    unsigned char *b = rows + p * L.row_bytes;
+    if (site < 2) ((double *)b)[site] = in[p];
+    else b[L.off_z + (site - 2)] = (uint8_t)in[p];
+  }
+}
+__global__ void lda_fill_kernel(double *out, int64_t n, double v) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = v;
+}
+
+struct LDAModel : Model {
+  LDALayout L;
+  int n_tok = 0, n_prop = 0;
+  std::vector<int32_t> doc_host, word_host, doclen_host;
+  DevBuf<int32_t> doc, word, doclen;
+  DevBuf<unsigned char> rowsa, rowsb;
+  unsigned char *rows = nullptr, *rows_alt = nullptr;
+  int smem_limit = 0;
+
+  LDAModel(vk_particles *h_, int K, int V, int n_docs, int max_tokens, double a, double b) : Model(h_) {
+    VK_REQUIRE(K >= 1 && K <= 255, VK_EINVAL, "lda: n_topics must be in [1,255]");
+    VK_REQUIRE(V >= 1 && n_docs >= 1, VK_EINVAL, "lda: vocab_size and n_docs must be positive");
+    VK_REQUIRE(max_tokens >= 1 && max_tokens <= 65535, VK_EINVAL, "lda: max_tokens must be in [1,65535] (u16 counts)");
+    VK_REQUIRE(a > 0 && b > 0, VK_EINVAL, "gamma: shape and rate must be positive");
+    L.K = K; L.V = V; L.n_docs = n_docs; L.max_tokens = max_tokens; L.hyper_a = a; L.hyper_b = b;
+    size_t o = 16;
+    L.off_nk = o; o += (size_t)K * 4;
+    L.off_ndk = o; o += (size_t)n_docs * K * 2;
+    L.off_nkw = o; o += (size_t)K * V * 2;
+    L.off_z = o; o += (size_t)max_tokens;
+    L.row_bytes = (o + 15) & ~(size_t)15;
+    doc.alloc((size_t)max_tokens); word.alloc((size_t)max_tokens); doclen.alloc((size_t)n_docs);
+    doclen_host.assign((size_t)n_docs, 0);
+    rowsa.alloc((size_t)h->P * L.row_bytes);
+    rows = rowsa.p;
+    VK_CUDA(cudaMemsetAsync(rows, 0, rowsa.bytes(), h->stream));
+    VK_CUDA(cudaDeviceGetAttribute(&smem_limit, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+    VK_CUDA(cudaFuncSetAttribute(lda_mh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_limit));
+  }
+  int grid_p(int per_sm) const {
+    int64_t cap = (int64_t)h->sm_count * per_sm;
+    return (int)(h->P < cap ? h->P : cap);
+  }
+  void observe(const int32_t *d, const int32_t *w, int64_t n) {
+    VK_REQUIRE(n_tok + n <= L.max_tokens, VK_EINVAL, "lda: token capacity exceeded");
+    for (int64_t i = 0; i < n; ++i) {
+      VK_REQUIRE(d[i] >= 0 && d[i] < L.n_docs && w[i] >= 0 && w[i] < L.V, VK_EINVAL, "lda: doc/word id out of range");
+    }
+    for (int64_t i = 0; i < n; ++i) { doc_host.push_back(d[i]); word_host.push_back(w[i]); doclen_host[d[i]]++; }
+    VK_CUDA(cudaMemcpyAsync(doc.p + n_tok, d, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+    VK_CUDA(cudaMemcpyAsync(word.p + n_tok, w, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+    VK_CUDA(cudaMemcpyAsync(doclen.p, doclen_host.data(), doclen_host.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    VK_CUDA(cudaStreamSynchronize(h->stream));
+    n_tok += (int)n;
+  }
+  void seq(int mode, int t0, int t1, double *incr_dev, uint32_t step) {
+    lda_seq_kernel<<<grid_p(16), 32, 0, h->stream>>>(rows, L, doc.p, word.p, t0, t1, h->lw.p, incr_dev, h->P,
+                                                     h->p_base, h->seed, step, mode);
+    VK_CUDA(cudaGetLastError());
+  }
+  void make_consistent(double *incr_dev) override {
+    if (n_prop == n_tok) {
+      if (incr_dev) VK_CUDA(cudaMemsetAsync(incr_dev, 0, (size_t)h->P * sizeof(double), h->stream));
+      return;
+    }
+    seq(0, n_prop, n_tok, incr_dev, h->next_step());
+    n_prop = n_tok;
+  }
+  void likelihood_weight() override { n_prop = n_tok; seq(1, 0, n_tok, nullptr, h->next_step()); }
+  void reset_to_prior() override { seq(2, 0, n_prop, nullptr, h->next_step()); }
+  void refresh() override { seq(3, 0, n_prop, nullptr, 0); }
+  void mh(int scope, int block, int K, double *mean_nodes_dev, long long *acc_dev) override {
+    VK_REQUIRE(scope == 0, VK_EINVAL, "lda: only the default scope exists");
+    VK_REQUIRE(n_prop == n_tok, VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
+    int nb = 2 + n_tok;
+    VK_REQUIRE(block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || (block >= 0 && block < nb), VK_EINVAL, "lda: bad block");
+    if (K > 0) {
+      int n_steps = block == VK_BLOCK_EACH ? K * nb : K;
+      uint32_t step0 = h->next_step((uint32_t)n_steps);
+      int stage = L.row_bytes <= (size_t)smem_limit ? 1 : 0;
+      size_t sm = stage ? L.row_bytes : 0;
+      int per_sm = stage ? (int)((size_t)(227 * 1024) / (L.row_bytes + 1024)) : 16;
+      if (per_sm < 1) per_sm = 1;
+      if (per_sm > 32) per_sm = 32;
+      lda_mh_kernel<<<grid_p(per_sm), 32, sm, h->stream>>>(rows, L, doc.p, word.p, doclen.p, n_tok, h->P, h->p_base,
+                                                           h->seed, step0, n_steps, block, stage, acc_dev);
+      VK_CUDA(cudaGetLastError());
+    } else if (acc_dev) {
+      VK_CUDA(cudaMemsetAsync(acc_dev, 0, (size_t)h->P * sizeof(long long), h->stream));
+    }
+    if (mean_nodes_dev) {
+      // z site: DRG {z, request + output of (topic z), the token application} = 4
+      double nodes = K > 0 ? 4.0 * (block == VK_BLOCK_EACH ? nb : 1) : 0.0;
+      lda_fill_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, nodes);
+      VK_CUDA(cudaGetLastError());
+    }
+  }
+  void log_likelihood_at(int scope, int block, bool joint, double *out_dev) override {
+    VK_REQUIRE(scope == 0, VK_EINVAL, "lda: only the default scope exists");
+    VK_REQUIRE(block >= 0 && block < 2 + n_prop, VK_EUNSUPPORTED, "lda: log_likelihood_at needs a block index");
+    lda_loglik_site_kernel<<<grid_p(16), 32, 0, h->stream>>>(rows, L, doc.p, word.p, doclen.p, block, joint ? 1 : 0,
+                                                             h->P, out_dev);
+    VK_CUDA(cudaGetLastError());
+  }
+  int64_t num_sites() const override { return 2 + n_prop; }
+  int64_t num_blocks(int) const override { return 2 + n_prop; }
+  void read_site(int64_t site, double *out_dev) override {
+    VK_REQUIRE(site >= 0 && site < 2 + n_prop, VK_EINVAL, "lda: site out of range");
+    lda_read_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(rows, L, site, h->P, out_dev);
+  }
+  void write_site(int64_t site, const double *in_dev) override {
+    VK_REQUIRE(site >= 0 && site < 2 + n_prop, VK_EINVAL, "lda: site out of range");
+    lda_write_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(rows, L, site, h->P, in_dev);
+  }
+  std::vector<StateArray> state_arrays() override {
+    if (!rowsb.p) { rowsb.alloc(rowsa.n); rows_alt = rowsb.p; }
+    StateArray a{(void **)&rows, (void **)&rows_alt, L.row_bytes, 0, 0};
+    return {a};
+  }
+  int device_buffer(int which, void **p, int64_t *bytes) override {
+    if (which == 1) { *p = rows; *bytes = (int64_t)rowsa.bytes(); return VK_OK; }
+    return VK_EINVAL;
+  }
+};
+
+Model *make_lda(vk_particles *h, int K, int V, int n_docs, int max_tokens, double a, double b) {
+  return new LDAModel(h, K, V, n_docs, max_tokens, a, b);
+}
+void lda_observe(Model *m, const int32_t *d, const int32_t *w, int64_t n) {
+  static_cast<LDAModel *>(m)->observe(d, w, n);
+}
+
+}  // namespace vk

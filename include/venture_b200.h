@@ -203,12 +203,47 @@ int vk_num_blocks(const vk_particles *h, int32_t scope, int64_t *n_out);
 int vk_device_buffer(vk_particles *h, int32_t which, void **dev_ptr_out,
                      int64_t *n_bytes_out);
 
-/* Multi-GPU resampling helpers: fixed-point weight mass of
- * this shard relative to a caller-supplied global max, and ancestor search
- * against a caller-supplied global offset/total.  See distributed.py. */
+/* ---- multi-GPU plumbing ------------------------------------
+ * One process per GPU owns one vk_particles shard; the host layer
+ * (venturecxx_b200/distributed.py) moves the few scalars and the packed
+ * ancestor rows with NCCL (torch.distributed).  Pointers named *_dev are
+ * device pointers supplied by the caller (e.g. torch tensors' data_ptr).
+ *
+ * Sharded resample (E2): local max -> allreduce(max) -> local fixed-point CDF
+ * against the GLOBAL max -> allgather(mass) -> ancestor search for the children
+ * whose threshold falls in this shard's mass interval -> pack rows ->
+ * all_to_all -> unpack into slots. */
 int vk_shard_weight_max(vk_particles *h, double *max_out_host);
-int vk_shard_weight_mass(vk_particles *h, double global_max, int32_t frac_bits,
-                         uint64_t *mass_out_host);
+int vk_shard_build_cdf(vk_particles *h, double global_max, int32_t frac_bits,
+                       uint64_t *mass_out_host, double *sumexp_out_host);
+/* anc_out_dev[t] (t < k_count) = local ancestor of child k_begin+t of
+ * n_new_total, or -1 if its threshold lies outside [offset, offset+mass). */
+int vk_shard_ancestors(vk_particles *h, uint64_t offset, uint64_t total,
+                       int64_t n_new_total, int64_t k_begin, int64_t k_count,
+                       int mode, uint32_t step, const double *uniforms_host,
+                       int32_t *anc_out_dev);
+int vk_state_row_bytes(vk_particles *h, int64_t *bytes_out);
+int vk_pack_state(vk_particles *h, const int32_t *particles_dev, int64_t n,
+                  void *packed_out_dev);
+int vk_unpack_state(vk_particles *h, const int32_t *slots_dev, int64_t n,
+                    const void *packed_in_dev);
+int vk_fill_log_weights(vk_particles *h, double value);
+
+/* Sharded subsampled MH (E3): observations are sharded, particles replicated.
+ * This shard holds global observation indices [global_offset, global_offset+N)
+ * of n_total.  The round-level primitives let the host all-reduce the
+ * (sum dllh, sum dllh^2) pairs between vk_ssmh_round and vk_ssmh_decide;
+ * vk_subsampled_mh is the same loop on one GPU. */
+int vk_blr_set_observation_shard(vk_particles *h, int64_t global_offset,
+                                 int64_t n_total);
+int vk_ssmh_begin(vk_particles *h);
+int vk_ssmh_propose(vk_particles *h, int32_t block, int32_t t_index,
+                    int32_t delta_mode, double delta_arg);
+int vk_ssmh_round(vk_particles *h, int64_t q0, int64_t q1, void **sums_dev_out);
+int vk_ssmh_decide(vk_particles *h, const void *sums_dev, int64_t n_end,
+                   int32_t k0, double epsilon, int32_t *n_active_out);
+int vk_ssmh_commit(vk_particles *h);
+int vk_ssmh_stats(vk_particles *h, int32_t transitions, double *stats_out_host);
 
 /* ---- SP plugin surface, batched (backend/lite/psp.py:32-318:
  *      simulate(args) / logDensity(value,args)) ---------------------------

@@ -701,3 +701,99 @@ void orc_lda_mh(double *alpha, int32_t *nk, int32_t *ndk, int32_t *nkw, uint8_t 
     if (acc) acc[p] = a;
   }
 }
+
+/* ------------------------------------------- C5: subsampled MH (BLR) */
+/* Keyed Feistel bijection on [0,N) shared by the particle batch: the product's
+ * stand-in for np_rng.permutation(local_roots) (subsampled_mh.py:103). */
+typedef struct { uint32_t k[4]; uint32_t half_bits, mask; uint64_t N; } orc_feistel;
+static uint32_t feistel_mix(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16; return x;
+}
+static orc_feistel feistel_key(uint64_t seed, uint32_t step, uint64_t N) {
+  orc_feistel K; uint32_t c[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, step, 0x5EED0001u};
+  philox(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+  for (int i = 0; i < 4; ++i) K.k[i] = c[i];
+  uint32_t bits = 1; while (((uint64_t)1 << bits) < N) ++bits;
+  K.half_bits = (bits + 1) / 2; if (K.half_bits < 1) K.half_bits = 1;
+  K.mask = K.half_bits >= 32 ? 0xFFFFFFFFu : ((1u << K.half_bits) - 1u); K.N = N;
+  return K;
+}
+static uint64_t feistel_perm(uint64_t q, const orc_feistel *K) {
+  uint64_t v = q;
+  do {
+    uint32_t L = (uint32_t)(v >> K->half_bits) & K->mask, R = (uint32_t)v & K->mask;
+    for (int r = 0; r < 4; ++r) { uint32_t t = L ^ (feistel_mix(R ^ K->k[r]) & K->mask); L = R; R = t; }
+    v = ((uint64_t)L << K->half_bits) | R;
+  } while (v >= K->N);
+  return v;
+}
+void orc_feistel_perm(uint64_t seed, uint32_t step, uint64_t N, uint64_t *out) {
+  orc_feistel K = feistel_key(seed, step, N);
+  for (uint64_t q = 0; q < N; ++q) out[q] = feistel_perm(q, &K);
+}
+/* infer/subsampled_mh.py:76-111 on the logistic-regression model: global section =
+ * {w_j .. array node} (no absorbing node, logGlobalAlpha = 0), local section i =
+ * (lookup, vector_dot, log_odds_flip) with dllh_i per evalOneLocalSection (:377-409).
+ * stats[p] = (accepted, mean n per transition, last tstat). */
+void orc_blr_subsampled_mh(double *w, const double *X, const uint8_t *y, int D, int64_t N, int64_t P,
+                           int64_t p_base, double mu0, double s0, uint64_t seed, uint32_t step0, int n_steps,
+                           int block_mode, double Nbatch, int k0, double epsilon, int delta_mode, double delta_eps,
+                           double *stats) {
+  uint64_t *perm = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)N);
+  double *acc = (double *)calloc((size_t)P, sizeof(double)), *nsum = (double *)calloc((size_t)P, sizeof(double));
+  double *last_t = (double *)calloc((size_t)P, sizeof(double));
+  for (int t = 0; t < n_steps; ++t) {
+    uint32_t step = step0 + (uint32_t)t;
+    orc_feistel_perm(seed, step, (uint64_t)N, perm);
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t p = 0; p < P; ++p) {
+      double wp[256], wn[256];
+      for (int j = 0; j < D; ++j) wp[j] = wn[j] = w[(int64_t)j * P + p];
+      orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step);
+      double u_sel = st_uniform(&r), log_u = log(st_uniform(&r));
+      int j;
+      if (block_mode == -1) { j = (int)(u_sel * D); if (j >= D) j = D - 1; }
+      else if (block_mode == -3) j = t % D; else j = block_mode;
+      if (delta_mode == 2) {  /* NormalDriftKernel, continuous.py:68-84 */
+        double nu = normal_sim(&r, 0.0, s0);
+        wn[j] = mu0 + sqrt(1 - delta_eps * delta_eps) * (wp[j] - mu0) + delta_eps * nu;
+      } else wn[j] = normal_sim(&r, mu0, s0);
+      double mu_0 = (log_u - 0.0) / (double)N;   /* :102 with alpha = 0 */
+      double *dllh = (double *)malloc(sizeof(double) * (size_t)N);
+      for (int64_t q = 0; q < N; ++q) {
+        int64_t i = (int64_t)perm[q];
+        double eo = blr_eta(wp, X + i * D, D), en = blr_eta(wn, X + i * D, D);
+        dllh[q] = orc_log_logistic(y[i] ? en : -en) - orc_log_logistic(y[i] ? eo : -eo);
+      }
+      double n_used, tstat;
+      int accept = orc_sequential_test(mu_0, k0, Nbatch, (double)N, epsilon, dllh, &n_used, &tstat);
+      free(dllh);
+      if (accept) { w[(int64_t)j * P + p] = wn[j]; acc[p] += 1; }
+      nsum[p] += n_used; last_t[p] = tstat;
+    }
+  }
+  if (stats) for (int64_t p = 0; p < P; ++p) { stats[3 * p] = acc[p]; stats[3 * p + 1] = n_steps ? nsum[p] / n_steps : 0; stats[3 * p + 2] = last_t[p]; }
+  free(perm); free(acc); free(nsum); free(last_t);
+}
+
+/* Ancestor search restricted to one shard's mass interval (multi-GPU resampling):
+ * child k gets the same threshold as in orc_ancestors; ancestors outside
+ * [offset, offset + cdf[n-1]) are reported as -1. */
+void orc_shard_ancestors(const uint64_t *cdf, int64_t n, uint64_t offset, uint64_t total, int64_t n_new,
+                         int64_t k_begin, int64_t k_count, int mode, uint64_t seed, uint32_t step, int32_t *anc) {
+  uint64_t mass = cdf[n - 1];
+  double u_sys = 0;
+  if (mode == 1) { orc_stream r; st_init(&r, seed, 0xFFFFFFFFFFFFFFFFull, step); u_sys = st_uniform(&r); }
+  for (int64_t t = 0; t < k_count; ++t) {
+    int64_t k = k_begin + t; uint64_t thr;
+    if (mode == 1) {
+      uint64_t U0 = (uint64_t)(u_sys * 4294967296.0); if (U0 > 0xFFFFFFFFull) U0 = 0xFFFFFFFFull;
+      thr = (uint64_t)((((((u128)(uint64_t)k) << 32) | U0) * (u128)total) / (((u128)(uint64_t)n_new) << 32));
+    } else {
+      orc_stream r; st_init(&r, seed, (uint64_t)k, step); double u = st_uniform(&r);
+      uint64_t U = (uint64_t)(u * 9007199254740992.0); if (U > 9007199254740991ull) U = 9007199254740991ull;
+      thr = (uint64_t)(((u128)U * (u128)total) >> 53);
+    }
+    anc[t] = (thr >= offset && thr - offset < mass) ? (int32_t)upper_bound(cdf, n, thr - offset) : -1;
+  }
+}

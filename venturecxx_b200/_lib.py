@@ -64,7 +64,19 @@ PROTOTYPES = {
     "vk_num_blocks": [_vp, _i32, _vp],
     "vk_device_buffer": [_vp, _i32, _vp, _vp],
     "vk_shard_weight_max": [_vp, _vp],
-    "vk_shard_weight_mass": [_vp, _f64, _i32, _vp],
+    "vk_shard_build_cdf": [_vp, _f64, _i32, _vp, _vp],
+    "vk_shard_ancestors": [_vp, _u64, _u64, _i64, _i64, _i64, c.c_int, _u32, _vp, _vp],
+    "vk_state_row_bytes": [_vp, _vp],
+    "vk_pack_state": [_vp, _vp, _i64, _vp],
+    "vk_unpack_state": [_vp, _vp, _i64, _vp],
+    "vk_fill_log_weights": [_vp, _f64],
+    "vk_blr_set_observation_shard": [_vp, _i64, _i64],
+    "vk_ssmh_begin": [_vp],
+    "vk_ssmh_propose": [_vp, _i32, _i32, _i32, _f64],
+    "vk_ssmh_round": [_vp, _i64, _i64, _vp],
+    "vk_ssmh_decide": [_vp, _vp, _i64, _i32, _f64, _vp],
+    "vk_ssmh_commit": [_vp],
+    "vk_ssmh_stats": [_vp, _i32, _vp],
     "vk_sp_simulate": [_i32, _vp, _i32, _i64, _i32, _u64, _u32, c.c_int, _vp],
     "vk_sp_log_density": [_i32, _vp, _vp, _i32, _i64, _i32, c.c_int, _vp],
 }

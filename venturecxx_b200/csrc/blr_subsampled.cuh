@@ -1,0 +1,272 @@
+// Config C5: subsampled (austerity) MH for the logistic-regression model.
+// Reference: backend/lite/infer/subsampled_mh.py
+//   subsampledMixMH :76-111   global proposal, mu_0 = (log u - alpha)/N, permutation
+//   sequentialTest  :118-171  minibatched t-test with finite-population correction
+//   evalOneLocalSection :377-409  dllh_i = xi_i - rho_i of one local section
+//   findGlobalBorder :326-368 global border = the `w` array node; local sections =
+//                             (lookup w -> vector_dot -> log_odds_flip), one per observation
+// evalOneLocalSection first refreshes the section to the OLD global value
+// (updateValuesAtScaffold) and then regenerates it under the NEW one, so
+//   dllh_i = log_logistic(s_i x_i.w') - log_logistic(s_i x_i.w)
+// depends only on (w, w', x_i): no per-particle logit cache is read or written
+// and "stale" sections need no bookkeeping -- the cache is simply marked dirty.
+//
+// Mapping.  Observations (local sections) shard across GPUs; the P particles
+// are replicated.  LANES ARE PARTICLES: a warp streams minibatch observations,
+// every lane holds one particle's weight vector in registers, the 8D-byte
+// feature row of an observation is one broadcast load shared by the 32
+// particles of the warp, and each lane accumulates its own (sum dllh,
+// sum dllh^2) in registers -- no shuffles, no atomics.  Algorithmic traffic
+// (8D+1)/P_tile bytes per (particle, observation) evaluation.
+// The minibatch order is a keyed Feistel bijection on [0, N) (sampling without
+// replacement, O(1) per index) shared by the particle batch; the reference
+// draws np_rng.permutation per trace (:103) -- each particle's marginal chain
+// law is the same.
+#pragma once
+#include "vk_common.cuh"
+#include "sp_math.cuh"
+
+namespace vk {
+
+struct FeistelKey { uint32_t k[4]; uint32_t half_bits; uint32_t mask; uint64_t N; };
+
+VK_HD uint32_t feistel_mix(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+// bijection on [0, N): 4-round Feistel on 2*half_bits bits with cycle walking
+VK_HD uint64_t feistel_perm(uint64_t q, const FeistelKey &K) {
+  uint64_t v = q;
+  do {
+    uint32_t L = (uint32_t)(v >> K.half_bits) & K.mask, R = (uint32_t)v & K.mask;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      uint32_t t = L ^ (feistel_mix(R ^ K.k[r]) & K.mask);
+      L = R; R = t;
+    }
+    v = ((uint64_t)L << K.half_bits) | (uint64_t)R;
+  } while (v >= K.N);
+  return v;
+}
+inline FeistelKey make_feistel_key(uint64_t seed, uint32_t step, uint64_t N) {
+  FeistelKey K;
+  Philox4 b = philox4x32_10(0xFFFFFFFFu, 0xFFFFFFFFu, step, 0x5EED0001u, (uint32_t)seed, (uint32_t)(seed >> 32));
+  for (int i = 0; i < 4; ++i) K.k[i] = b.v[i];
+  uint32_t bits = 1;
+  while (((uint64_t)1 << bits) < N) ++bits;
+  K.half_bits = (bits + 1) / 2;
+  if (K.half_bits < 1) K.half_bits = 1;
+  K.mask = (K.half_bits >= 32) ? 0xFFFFFFFFu : ((1u << K.half_bits) - 1u);
+  K.N = N;
+  return K;
+}
+
+// per-particle state of the transition in flight (all arrays of length P)
+struct SSState {
+  int *site; double *w_new; double *delta; double *mu0;
+  double *cum, *cum2, *n, *k, *tstat;
+  int *status;          // 0 active, 1 accept, 2 reject
+  double *acc_total, *n_total;   // statistics over the transitions of a call
+};
+
+// regularised incomplete beta / Student-t CDF (replaces scipy.stats.t.cdf, :161)
+__device__ inline double dev_betacf(double a, double b, double x) {
+  const double TINY = 1e-300, EPS = 1e-16;
+  double qab = a + b, qap = a + 1.0, qam = a - 1.0, c = 1.0, d = 1.0 - qab * x / qap;
+  if (fabs(d) < TINY) d = TINY;
+  d = 1.0 / d;
+  double h = d;
+  for (int m = 1; m <= 10000; ++m) {
+    int m2 = 2 * m;
+    double aa = m * (b - m) * x / ((qam + m2) * (a + m2));
+    d = 1.0 + aa * d; if (fabs(d) < TINY) d = TINY;
+    c = 1.0 + aa / c; if (fabs(c) < TINY) c = TINY;
+    d = 1.0 / d; h *= d * c;
+    aa = -(a + m) * (qab + m) * x / ((a + m2) * (qap + m2));
+    d = 1.0 + aa * d; if (fabs(d) < TINY) d = TINY;
+    c = 1.0 + aa / c; if (fabs(c) < TINY) c = TINY;
+    d = 1.0 / d;
+    double del = d * c;
+    h *= del;
+    if (fabs(del - 1.0) < EPS) break;
+  }
+  return h;
+}
+__device__ inline double dev_betainc(double a, double b, double x) {
+  if (x <= 0.0) return 0.0;
+  if (x >= 1.0) return 1.0;
+  double bt = exp(lgamma(a + b) - lgamma(a) - lgamma(b) + a * log(x) + b * log1p(-x));
+  if (x < (a + 1.0) / (a + b + 2.0)) return bt * dev_betacf(a, b, x) / a;
+  return 1.0 - bt * dev_betacf(b, a, 1.0 - x) / b;
+}
+__device__ inline double dev_student_t_cdf(double t, double df) {
+  if (t != t) return NAN;
+  if (isinf(t)) return t > 0 ? 1.0 : 0.0;
+  double x = df / (df + t * t);
+  double tail = 0.5 * dev_betainc(0.5 * df, 0.5, x);
+  return t > 0 ? 1.0 - tail : tail;
+}
+
+// global proposal (:79-88,102): site, w', log u, mu_0
+// delta_mode 0: prior resimulation (the reference's behaviour for `normal` even with
+//   useDeltaKernels, since NormalOutputPSP.hasDeltaKernel() is False, continuous.py:352-353);
+// delta_mode 2: NormalDriftKernel (continuous.py:68-84), weight 0.
+__global__ void ss_propose_kernel(const double *__restrict__ w, SSState S, int D, int64_t P, int64_t p_base,
+                                  double mu0_prior, double s0_prior, double N_total, int block_mode,
+                                  int t_index, int delta_mode, double eps, uint64_t seed, uint32_t step) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    Stream r(seed, (uint64_t)(p_base + p), step);
+    double u_sel = r.uniform();
+    double log_u = log(r.uniform());
+    int j;
+    if (block_mode == VK_BLOCK_ONE) { j = (int)(u_sel * (double)D); if (j >= D) j = D - 1; }
+    else if (block_mode == VK_BLOCK_EACH) j = t_index % D;
+    else j = block_mode;
+    double w_old = w[(int64_t)j * P + p];
+    double w_new;
+    if (delta_mode == 2) {
+      double nu = normal_sim(r, 0.0, s0_prior);
+      w_new = mu0_prior + sqrt(1.0 - eps * eps) * (w_old - mu0_prior) + eps * nu;
+    } else {
+      w_new = normal_sim(r, mu0_prior, s0_prior);
+    }
+    S.site[p] = j; S.w_new[p] = w_new; S.delta[p] = w_new - w_old;
+    S.mu0[p] = (log_u - 0.0) / N_total;   // alpha of the global section is 0 (no absorbing node in it)
+    S.cum[p] = 0.0; S.cum2[p] = 0.0; S.n[p] = 0.0; S.k[p] = 0.0; S.tstat[p] = 0.0; S.status[p] = 0;
+  }
+}
+
+// one minibatch round: positions [q0, q1) of the permutation; this shard owns global
+// observation indices [obs_lo, obs_lo + N_local).  partial: [gridDim.x][P][2].
+template <int DT>
+__global__ void __launch_bounds__(256)
+ss_round_kernel(const double *__restrict__ Xr /*[N_local][D] signed rows*/, const double *__restrict__ w,
+                SSState S, int D, int64_t P, int64_t q0, int64_t q1, int64_t obs_lo, int64_t N_local,
+                FeistelKey key, double *__restrict__ partial) {
+  extern __shared__ double sm_part[];   // [warps][P_groups*32][2] then reused
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+  const int n_groups = (int)((P + 31) / 32);
+  // warps are split between particle groups; streams of observations are interleaved over
+  // (block, warp-within-group)
+  const int g = warp % n_groups;
+  const int streams_per_block = n_warps / n_groups;      // >= 1 (host guarantees n_groups <= n_warps)
+  const int s_in_block = warp / n_groups;
+  const int64_t p = (int64_t)g * 32 + lane;
+  const bool live = (s_in_block < streams_per_block) && p < P && S.status[p] == 0;
+  double wl[DT];
+  double delta = 0.0; int site = 0;
+#pragma unroll
+  for (int j = 0; j < DT; ++j) wl[j] = (live && j < D) ? w[(int64_t)j * P + p] : 0.0;
+  if (live) { delta = S.delta[p]; site = S.site[p]; }
+  double s1 = 0.0, s2 = 0.0;
+  const bool any_live = __any_sync(0xffffffffu, live);
+  if (any_live && s_in_block < streams_per_block) {
+    const int64_t stream = (int64_t)blockIdx.x * streams_per_block + s_in_block;
+    const int64_t n_streams = (int64_t)gridDim.x * streams_per_block;
+    for (int64_t q = q0 + stream; q < q1; q += n_streams) {
+      int64_t i = (int64_t)feistel_perm((uint64_t)q, key) - obs_lo;
+      if (i < 0 || i >= N_local) continue;       // another shard's observation (warp-uniform)
+      const double *x = Xr + i * D;
+      double eta = 0.0, xs = 0.0;
+#pragma unroll
+      for (int j = 0; j < DT; ++j) {
+        if (j < D) {
+          double xv = __ldg(&x[j]);               // same address in every lane: one broadcast load
+          eta = fma(wl[j], xv, eta);
+          if (j == site) xs = xv;
+        }
+      }
+      if (live) {
+        double d = log_logistic(fma(delta, xs, eta)) - log_logistic(eta);
+        s1 += d; s2 += d * d;
+      }
+    }
+  }
+  // block combine in fixed (warp) order -> deterministic
+  double *slot = sm_part + ((size_t)warp * 32 + lane) * 2;
+  slot[0] = s1; slot[1] = s2;
+  __syncthreads();
+  for (int64_t pp = threadIdx.x; pp < P; pp += blockDim.x) {
+    int gg = (int)(pp / 32), ll = (int)(pp % 32);
+    double a = 0.0, b = 0.0;
+    for (int s = 0; s < streams_per_block; ++s) {
+      int wv = s * n_groups + gg;
+      a += sm_part[((size_t)wv * 32 + ll) * 2];
+      b += sm_part[((size_t)wv * 32 + ll) * 2 + 1];
+    }
+    partial[((size_t)blockIdx.x * P + pp) * 2] = a;
+    partial[((size_t)blockIdx.x * P + pp) * 2 + 1] = b;
+  }
+}
+
+// sums[P][2] = sum over blocks (fixed order) of partial
+__global__ void ss_reduce_kernel(const double *__restrict__ partial, int n_blocks, int64_t P,
+                                 double *__restrict__ sums) {
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < P * 2;
+       t += (int64_t)gridDim.x * blockDim.x) {
+    double a = 0.0;
+    for (int b = 0; b < n_blocks; ++b) a += partial[(size_t)b * P * 2 + t];
+    sums[t] = a;
+  }
+}
+
+// sequentialTest bookkeeping for one finished minibatch (:132-168)
+__global__ void ss_decide_kernel(SSState S, const double *__restrict__ sums, int64_t P, double n_end,
+                                 double N, int k0, double epsilon, int *__restrict__ n_active) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    if (S.status[p] != 0) continue;
+    double cum = S.cum[p] + sums[2 * p], cum2 = S.cum2[p] + sums[2 * p + 1];
+    double k = S.k[p] + 1.0, n = n_end;
+    S.cum[p] = cum; S.cum2[p] = cum2; S.k[p] = k; S.n[p] = n;
+    double mx = cum / n, mx2 = cum2 / n, mu0 = S.mu0[p];
+    int st = 0;
+    if (k < (double)k0 && n < N) { /* no test during the first k0 minibatches */ }
+    else if (n == N) st = (mx >= mu0) ? 1 : 2;
+    else {
+      double sx = sqrt((1.0 - (n - 1.0) / (N - 1.0)) * (mx2 - mx * mx) / (n - 1.0));
+      double q;
+      if (sx == 0.0) q = (mx >= mu0) ? 1.0 : 0.0;
+      else { double ts = (mx - mu0) / sx; S.tstat[p] = ts; q = dev_student_t_cdf(ts, n - 1.0); }
+      if (q < epsilon) st = 2;
+      else if (q > 1.0 - epsilon) st = 1;
+    }
+    S.status[p] = st;
+    if (st == 0) atomicAdd(n_active, 1);
+  }
+}
+
+// accept: install w' (operator.accept, :108-109); reject: nothing to restore (the
+// proposal never left the transition state).  Accumulate per-call statistics.
+__global__ void ss_commit_kernel(double *__restrict__ w, SSState S, int64_t P) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    if (S.status[p] == 1) { w[(int64_t)S.site[p] * P + p] = S.w_new[p]; S.acc_total[p] += 1.0; }
+    S.n_total[p] += S.n[p];
+  }
+}
+
+__global__ void ss_stats_kernel(SSState S, int64_t P, int K, double *__restrict__ out) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    out[3 * p] = S.acc_total[p];
+    out[3 * p + 1] = K > 0 ? S.n_total[p] / (double)K : 0.0;
+    double ts = S.tstat[p];
+    // :170  tstat if tstat else (inf if accept else -inf)
+    out[3 * p + 2] = (ts != 0.0) ? ts : (S.status[p] == 1 ? INFINITY : -INFINITY);
+  }
+}
+
+// Xr[i][j] = Xs[j][i]  (row-major copy of the signed features for row-contiguous access)
+__global__ void ss_transpose_kernel(const double *__restrict__ Xs, double *__restrict__ Xr, int D,
+                                    int64_t Ncap, int64_t N) {
+  int64_t total = N * D;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (int64_t)gridDim.x * blockDim.x) {
+    int64_t i = t / D; int j = (int)(t - i * D);
+    Xr[t] = Xs[(int64_t)j * Ncap + i];
+  }
+}
+
+}  // namespace vk

@@ -25,6 +25,7 @@
 // kernel is fp64-ALU bound (exp + log1p per observation), see DESIGN.md.
 #include "vk_common.cuh"
 #include "sp_math.cuh"
+#include "blr_subsampled.cuh"
 
 namespace vk {
 
@@ -262,6 +263,15 @@ struct BLRModel : Model {
   DevBuf<uint8_t> y;
   double *w = nullptr, *w_alt = nullptr, *eta = nullptr, *eta_alt = nullptr, *ll = nullptr, *ll_alt = nullptr;
   int smem_limit = 0;
+  // subsampled MH (C5): observation shard [obs_lo, obs_lo + N) of N_total, transition state
+  int64_t obs_lo = 0, N_total = -1;
+  bool eta_dirty = false;
+  DevBuf<double> Xr, ss_d, ss_partial, ss_sums;
+  DevBuf<int> ss_i;
+  int64_t Xr_rows = 0;
+  int *ss_active_host = nullptr;
+
+  ~BLRModel() override { if (ss_active_host) cudaFreeHost(ss_active_host); }
 
   BLRModel(vk_particles *h_, int D, int64_t Ncap, double mu0, double s0) : Model(h_) {
     VK_REQUIRE(D >= 1 && D <= 256, VK_EINVAL, "blr: D must be in [1,256]");
@@ -288,6 +298,7 @@ struct BLRModel : Model {
     VK_CUDA(cudaGetLastError());
     VK_CUDA(cudaStreamSynchronize(h->stream));
     prm.N += n;
+    Xr_rows = -1;
   }
   int grid_particles(int ctas_per_sm) const {
     int64_t cap = (int64_t)h->sm_count * ctas_per_sm;
@@ -304,7 +315,111 @@ struct BLRModel : Model {
     n_prop = prm.N;
     launch_all(1, nullptr, h->next_step());
   }
-  void refresh() override { launch_all(2, nullptr, 0); }
+  void refresh() override { launch_all(2, nullptr, 0); eta_dirty = false; }
+  // subsampled transitions leave the logit cache stale (subsampled_mh.py:59-73);
+  // this is SubsampledInPlaceOperator.makeConsistent (:427-455) done lazily.
+  void ensure_fresh() { if (eta_dirty) refresh(); }
+  void set_observation_shard(int64_t lo, int64_t total) {
+    VK_REQUIRE(lo >= 0 && total >= lo, VK_EINVAL, "blr: bad observation shard");
+    obs_lo = lo; N_total = total;
+  }
+  void ss_prepare() {
+    if (Xr_rows != prm.N) {
+      Xr.alloc((size_t)prm.N * prm.D);
+      ss_transpose_kernel<<<grid_for(prm.N * prm.D, 256, h->sm_count, 8), 256, 0, h->stream>>>(Xs.p, Xr.p, prm.D, prm.Ncap, prm.N);
+      VK_CUDA(cudaGetLastError());
+      Xr_rows = prm.N;
+    }
+    if (!ss_d.p) {
+      ss_d.alloc((size_t)h->P * 11); ss_i.alloc((size_t)h->P * 2 + 1);
+      ss_sums.alloc((size_t)h->P * 2);
+      VK_CUDA(cudaMallocHost((void **)&ss_active_host, sizeof(int)));
+    }
+  }
+  SSState ss_state() {
+    SSState S; int64_t P = h->P; double *d = ss_d.p;
+    S.w_new = d; S.delta = d + P; S.mu0 = d + 2 * P; S.cum = d + 3 * P; S.cum2 = d + 4 * P; S.n = d + 5 * P;
+    S.k = d + 6 * P; S.tstat = d + 7 * P; S.acc_total = d + 8 * P; S.n_total = d + 9 * P;
+    S.site = ss_i.p; S.status = ss_i.p + P;
+    return S;
+  }
+  int ss_grid() const { return h->sm_count * 2; }
+  // --- round-level primitives (also driven from the host layer when observations are sharded)
+  void ss_begin_call() {
+    ss_prepare();
+    VK_CUDA(cudaMemsetAsync(ss_d.p + 8 * h->P, 0, (size_t)h->P * 2 * sizeof(double), h->stream));
+  }
+  void ss_propose(int block, int t_index, int delta_mode, double eps) {
+    int64_t Nt = N_total >= 0 ? N_total : prm.N;
+    VK_REQUIRE(Nt > 1, VK_ESTATE, "subsampled_mh needs more than one local section (subsampled_mh.py:100)");
+    uint32_t step = h->next_step();
+    ss_key = make_feistel_key(h->seed, step, (uint64_t)Nt);
+    ss_propose_kernel<<<grid_for(h->P, 128, h->sm_count, 4), 128, 0, h->stream>>>(
+        w, ss_state(), prm.D, h->P, h->p_base, prm.mu0, prm.s0, (double)Nt, block, t_index, delta_mode, eps, h->seed, step);
+    VK_CUDA(cudaGetLastError());
+  }
+  FeistelKey ss_key;
+  // local partial sums of minibatch positions [q0,q1) -> ss_sums (device, P x 2)
+  void ss_round(int64_t q0, int64_t q1) {
+    int n_groups = (int)((h->P + 31) / 32);
+    VK_REQUIRE(n_groups <= 8, VK_EUNSUPPORTED, "subsampled_mh: at most 256 particles per GPU in this version");
+    int grid = ss_grid();
+    if (ss_partial.n < (size_t)grid * h->P * 2) ss_partial.alloc((size_t)grid * h->P * 2);
+    size_t sm = (size_t)8 * 32 * 2 * sizeof(double);
+    SSState S = ss_state();
+#define VK_SS_LAUNCH(DT) ss_round_kernel<DT><<<grid, 256, sm, h->stream>>>(Xr.p, w, S, prm.D, h->P, q0, q1, obs_lo, prm.N, ss_key, ss_partial.p)
+    if (prm.D <= 4) VK_SS_LAUNCH(4);
+    else if (prm.D <= 8) VK_SS_LAUNCH(8);
+    else if (prm.D <= 16) VK_SS_LAUNCH(16);
+    else if (prm.D <= 32) VK_SS_LAUNCH(32);
+    else if (prm.D <= 64) VK_SS_LAUNCH(64);
+    else throw Error(VK_EUNSUPPORTED, "subsampled_mh: D <= 64 in this version");
+#undef VK_SS_LAUNCH
+    ss_reduce_kernel<<<grid_for(h->P * 2, 128, h->sm_count, 1), 128, 0, h->stream>>>(ss_partial.p, grid, h->P, ss_sums.p);
+    VK_CUDA(cudaGetLastError());
+  }
+  // sequential-test decision from (possibly all-reduced) sums; returns #particles still undecided
+  int ss_decide(const double *sums_dev, int64_t n_end, int k0, double eps) {
+    int64_t Nt = N_total >= 0 ? N_total : prm.N;
+    int *n_active = ss_i.p + 2 * h->P;
+    VK_CUDA(cudaMemsetAsync(n_active, 0, sizeof(int), h->stream));
+    ss_decide_kernel<<<grid_for(h->P, 128, h->sm_count, 1), 128, 0, h->stream>>>(ss_state(), sums_dev, h->P, (double)n_end,
+                                                                                 (double)Nt, k0, eps, n_active);
+    VK_CUDA(cudaGetLastError());
+    VK_CUDA(cudaMemcpyAsync(ss_active_host, n_active, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    VK_CUDA(cudaStreamSynchronize(h->stream));
+    return *ss_active_host;
+  }
+  void ss_commit() {
+    ss_commit_kernel<<<grid_for(h->P, 128, h->sm_count, 4), 128, 0, h->stream>>>(w, ss_state(), h->P);
+    VK_CUDA(cudaGetLastError());
+    eta_dirty = true;
+  }
+  void ss_stats(int K, double *out_dev) {
+    ss_stats_kernel<<<grid_for(h->P, 128, h->sm_count, 4), 128, 0, h->stream>>>(ss_state(), h->P, K, out_dev);
+    VK_CUDA(cudaGetLastError());
+  }
+  void subsampled_mh(int scope, int block, int64_t Nbatch, int k0, double eps, int use_delta, double delta_arg,
+                     int update_values, int K, double *stats_dev) override {
+    VK_REQUIRE(scope == 0, VK_EINVAL, "blr: only the default scope exists");
+    VK_REQUIRE(block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || (block >= 0 && block < prm.D), VK_EINVAL, "blr: bad block");
+    VK_REQUIRE(n_prop == prm.N, VK_ESTATE, "subsampled_mh: unpropagated observations; call vk_make_consistent first");
+    VK_REQUIRE(eps >= 0.0 && eps < 0.5, VK_EINVAL, "subsampled_mh: epsilon must be in [0, 0.5)");
+    (void)update_values;  // local sections are always evaluated from current values here
+    int64_t Nt = N_total >= 0 ? N_total : prm.N;
+    ss_begin_call();
+    int n_prop_steps = block == VK_BLOCK_EACH ? K * prm.D : K;
+    for (int t = 0; t < n_prop_steps; ++t) {
+      ss_propose(block, t, use_delta == 2 ? 2 : 0, delta_arg);
+      for (int64_t q0 = 0; q0 < Nt; q0 += Nbatch) {
+        int64_t q1 = q0 + Nbatch < Nt ? q0 + Nbatch : Nt;
+        ss_round(q0, q1);
+        if (ss_decide(ss_sums.p, q1, k0, eps) == 0) break;
+      }
+      ss_commit();
+    }
+    if (stats_dev) ss_stats(n_prop_steps, stats_dev);
+  }
   void make_consistent(double *incr_dev) override {
     if (n_prop == prm.N) {
       if (incr_dev) VK_CUDA(cudaMemsetAsync(incr_dev, 0, (size_t)h->P * sizeof(double), h->stream));
@@ -318,6 +433,7 @@ struct BLRModel : Model {
     VK_REQUIRE(block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || block == VK_BLOCK_ALL ||
                    (block >= 0 && block < prm.D), VK_EINVAL, "blr: bad block");
     VK_REQUIRE(n_prop == prm.N, VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
+    ensure_fresh();
     double nodes = 0.0;
     if (K > 0) {
       if (block == VK_BLOCK_ALL) {
@@ -356,13 +472,14 @@ struct BLRModel : Model {
     VK_REQUIRE(scope == 0, VK_EINVAL, "blr: only the default scope exists");
     VK_REQUIRE(block == VK_BLOCK_ALL || (block >= 0 && block < prm.D), VK_EINVAL,
                "log_likelihood_at: block must be all or a site index");
+    ensure_fresh();
     BLRParams q = prm; q.N = n_prop;
     blr_loglik_at_kernel<<<grid_particles(8), 256, 0, h->stream>>>(w, eta, q, h->P, joint ? block : -100, out_dev);
     VK_CUDA(cudaGetLastError());
   }
   void forget_observations(double *w_dev) override {
     if (w_dev) log_likelihood_at(0, VK_BLOCK_ALL, false, w_dev);
-    prm.N = 0; n_prop = 0;
+    prm.N = 0; n_prop = 0; Xr_rows = -1; eta_dirty = false;
     VK_CUDA(cudaMemsetAsync(ll, 0, (size_t)h->P * sizeof(double), h->stream));
   }
   int64_t num_sites() const override { return prm.D; }
@@ -376,6 +493,7 @@ struct BLRModel : Model {
     VK_CUDA(cudaMemcpyAsync(w + site * h->P, in_dev, (size_t)h->P * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
   }
   std::vector<StateArray> state_arrays() override {
+    ensure_fresh();
     // back buffers are allocated on first resample (eta doubles the footprint)
     if (!wb.p) { wb.alloc(wa.n); etab.alloc(etaa.n); llb.alloc(lla.n); w_alt = wb.p; eta_alt = etab.p; ll_alt = llb.p; }
     StateArray a{(void **)&w, (void **)&w_alt, 0, (size_t)prm.D, 8};
@@ -398,5 +516,23 @@ Model *make_blr(vk_particles *h, int D, int64_t Ncap, double mu0, double s0) {
 void blr_observe(Model *m, const double *X_rows_host, const uint8_t *y_host, int64_t n) {
   static_cast<BLRModel *>(m)->observe(X_rows_host, y_host, n);
 }
+void blr_set_observation_shard(Model *m, int64_t lo, int64_t total) {
+  static_cast<BLRModel *>(m)->set_observation_shard(lo, total);
+}
+// round-level subsampled-MH primitives for the sharded host driver
+void blr_ss_begin(Model *m) { static_cast<BLRModel *>(m)->ss_begin_call(); }
+void blr_ss_propose(Model *m, int block, int t_index, int delta_mode, double eps) {
+  static_cast<BLRModel *>(m)->ss_propose(block, t_index, delta_mode, eps);
+}
+double *blr_ss_round(Model *m, int64_t q0, int64_t q1) {
+  BLRModel *b = static_cast<BLRModel *>(m);
+  b->ss_round(q0, q1);
+  return b->ss_sums.p;
+}
+int blr_ss_decide(Model *m, const double *sums_dev, int64_t n_end, int k0, double eps) {
+  return static_cast<BLRModel *>(m)->ss_decide(sums_dev, n_end, k0, eps);
+}
+void blr_ss_commit(Model *m) { static_cast<BLRModel *>(m)->ss_commit(); }
+void blr_ss_stats(Model *m, int K, double *out_dev) { static_cast<BLRModel *>(m)->ss_stats(K, out_dev); }
 
 }  // namespace vk

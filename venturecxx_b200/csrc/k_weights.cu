@@ -477,4 +477,87 @@ void launch_ancestor_search_shard(vk_particles *h, uint64_t offset, uint64_t tot
   VK_CUDA(cudaGetLastError());
 }
 
+
+// ---- multi-GPU resampling helpers ---------------------------
+// Packed row of one particle = the concatenation of its slice of every state
+// array, each segment padded to 16 bytes (what crosses NVLink in all_to_all).
+static size_t seg_bytes(const StateArray &a) {
+  size_t b = a.elem_bytes == 0 ? a.row_bytes : a.n_rows * a.elem_bytes;
+  return (b + 15) & ~(size_t)15;
+}
+size_t packed_row_bytes(vk_particles *h) {
+  size_t tot = 0;
+  for (auto &a : h->model->state_arrays()) tot += seg_bytes(a);
+  return tot;
+}
+// pack: out[k] <- particle anc[k];  unpack: particle slots[k] <- in[k]
+__global__ void pack_rows_kernel(const unsigned char *__restrict__ arr, unsigned char *__restrict__ packed,
+                                 const int32_t *__restrict__ idx, int64_t n, int64_t row_bytes,
+                                 int64_t packed_bytes, int64_t off, int unpack) {
+  if ((row_bytes & 15) == 0) {
+    int64_t units = row_bytes >> 4, total = n * units;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (int64_t)gridDim.x * blockDim.x) {
+      int64_t k = t / units, c = t - k * units;
+      uint4 *pk = (uint4 *)(packed + k * packed_bytes + off) + c;
+      uint4 *ar = (uint4 *)(const_cast<unsigned char *>(arr) + (int64_t)idx[k] * row_bytes) + c;
+      if (unpack) *ar = *pk; else *pk = *ar;
+    }
+  } else {
+    int64_t total = n * row_bytes;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (int64_t)gridDim.x * blockDim.x) {
+      int64_t k = t / row_bytes, c = t - k * row_bytes;
+      unsigned char *pk = packed + k * packed_bytes + off + c;
+      unsigned char *ar = const_cast<unsigned char *>(arr) + (int64_t)idx[k] * row_bytes + c;
+      if (unpack) *ar = *pk; else *pk = *ar;
+    }
+  }
+}
+__global__ void pack_soa_kernel(const unsigned char *__restrict__ arr, unsigned char *__restrict__ packed,
+                                const int32_t *__restrict__ idx, int64_t n, int64_t P, int64_t n_rows,
+                                int64_t elem, int64_t packed_bytes, int64_t off, int unpack) {
+  int64_t total = n * n_rows;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = t / n, k = t - r * n;   // k fastest: coalesced on the SoA side
+    unsigned char *pk = packed + k * packed_bytes + off + r * elem;
+    unsigned char *ar = const_cast<unsigned char *>(arr) + (r * P + (int64_t)idx[k]) * elem;
+    for (int64_t b = 0; b < elem; ++b) { if (unpack) ar[b] = pk[b]; else pk[b] = ar[b]; }
+  }
+}
+void pack_state(vk_particles *h, const int32_t *idx_dev, int64_t n, void *packed_dev, bool unpack) {
+  if (n <= 0) return;
+  size_t pb = packed_row_bytes(h), off = 0;
+  for (auto &a : h->model->state_arrays()) {
+    if (a.elem_bytes == 0) {
+      int64_t work = (a.row_bytes & 15) == 0 ? n * (int64_t)(a.row_bytes >> 4) : n * (int64_t)a.row_bytes;
+      pack_rows_kernel<<<grid_for(work, 256, h->sm_count, 8), 256, 0, h->stream>>>(
+          (const unsigned char *)*a.cur, (unsigned char *)packed_dev, idx_dev, n, (int64_t)a.row_bytes, (int64_t)pb,
+          (int64_t)off, unpack ? 1 : 0);
+    } else {
+      pack_soa_kernel<<<grid_for(n * (int64_t)a.n_rows, 256, h->sm_count, 8), 256, 0, h->stream>>>(
+          (const unsigned char *)*a.cur, (unsigned char *)packed_dev, idx_dev, n, h->P, (int64_t)a.n_rows,
+          (int64_t)a.elem_bytes, (int64_t)pb, (int64_t)off, unpack ? 1 : 0);
+    }
+    off += seg_bytes(a);
+  }
+  VK_CUDA(cudaGetLastError());
+}
+// local max of the log weights (NaN ignored) -> red[0]
+void shard_weight_max(vk_particles *h) {
+  int grid = grid_for(h->P, 256, h->sm_count, 4);
+  lse_pass1_kernel<<<grid, 256, 0, h->stream>>>(h->lw.p, h->P, h->red.p, h->counters.p);
+  VK_CUDA(cudaGetLastError());
+}
+// fixed-point CDF relative to the GLOBAL max; red[0] := global max, red[3] := sum exp(lw - max)
+__global__ void set_red0_kernel(double *red, double m) { red[0] = m; red[1] = m; red[2] = 0.0; }
+void shard_build_cdf(vk_particles *h, double global_max, int frac_bits) {
+  set_red0_kernel<<<1, 1, 0, h->stream>>>(h->red.p, global_max);
+  int grid = grid_for(h->P, 256, h->sm_count, 4);
+  lse_pass2_kernel<<<grid, 256, 0, h->stream>>>(h->lw.p, h->P, h->red.p, h->counters.p + 1);
+  build_fixed_cdf(h, nullptr, global_max, frac_bits);
+  VK_CUDA(cudaGetLastError());
+}
+
 }  // namespace vk

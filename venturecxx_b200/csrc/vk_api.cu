@@ -358,4 +358,106 @@ int vk_device_buffer(vk_particles *h, int32_t which, void **dev_ptr_out, int64_t
   VK_CATCH
 }
 
+
+// ---- multi-GPU plumbing ---------------------------------------------------------
+int vk_shard_weight_max(vk_particles *h, double *max_out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(max_out_host, VK_EINVAL, "NULL");
+  shard_weight_max(h);
+  VK_CUDA(cudaMemcpyAsync(max_out_host, h->red.p, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_shard_build_cdf(vk_particles *h, double global_max, int32_t frac_bits, uint64_t *mass_out_host,
+                       double *sumexp_out_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(mass_out_host && sumexp_out_host, VK_EINVAL, "NULL");
+  VK_REQUIRE(frac_bits >= 1 && frac_bits <= 52, VK_EINVAL, "frac_bits must be in [1,52]");
+  shard_build_cdf(h, global_max, frac_bits);
+  VK_CUDA(cudaMemcpyAsync(mass_out_host, h->cdf.p + (h->P - 1), sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+  VK_CUDA(cudaMemcpyAsync(sumexp_out_host, h->red.p + 3, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_shard_ancestors(vk_particles *h, uint64_t offset, uint64_t total, int64_t n_new_total, int64_t k_begin,
+                       int64_t k_count, int mode, uint32_t step, const double *uniforms_host, int32_t *anc_out_dev) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(anc_out_dev || k_count == 0, VK_EINVAL, "NULL");
+  VK_REQUIRE(mode == VK_RESAMPLE_MULTINOMIAL || mode == VK_RESAMPLE_SYSTEMATIC, VK_EINVAL, "bad mode");
+  DevBuf<double> u;
+  if (uniforms_host) {
+    size_t n = mode == VK_RESAMPLE_SYSTEMATIC ? 1 : (size_t)n_new_total;
+    u.alloc(n);
+    VK_CUDA(cudaMemcpyAsync(u.p, uniforms_host, n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  }
+  launch_ancestor_search_shard(h, offset, total, n_new_total, k_begin, k_count, mode, step,
+                               uniforms_host ? u.p : nullptr, anc_out_dev);
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_state_row_bytes(vk_particles *h, int64_t *bytes_out) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(bytes_out, VK_EINVAL, "NULL");
+  *bytes_out = (int64_t)packed_row_bytes(h);
+  VK_CATCH
+}
+int vk_pack_state(vk_particles *h, const int32_t *particles_dev, int64_t n, void *packed_out_dev) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(n == 0 || (particles_dev && packed_out_dev), VK_EINVAL, "NULL");
+  pack_state(h, particles_dev, n, packed_out_dev, false);
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_unpack_state(vk_particles *h, const int32_t *slots_dev, int64_t n, const void *packed_in_dev) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(n == 0 || (slots_dev && packed_in_dev), VK_EINVAL, "NULL");
+  pack_state(h, slots_dev, n, const_cast<void *>(packed_in_dev), true);
+  h->model->after_resample();
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_fill_log_weights(vk_particles *h, double value) {
+  VK_TRY check_handle(h); use_device(h);
+  launch_fill_even_weights(h, h->P, value, 0.0);
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+
+int vk_blr_set_observation_shard(vk_particles *h, int64_t global_offset, int64_t n_total) {
+  VK_TRY check_handle(h);
+  VK_REQUIRE(h->kind == VK_MODEL_BLR, VK_EUNSUPPORTED, "not a BLR batch");
+  blr_set_observation_shard(h->model, global_offset, n_total);
+  VK_CATCH
+}
+#define VK_BLR_ONLY VK_REQUIRE(h->kind == VK_MODEL_BLR, VK_EUNSUPPORTED, "subsampled_mh is defined for the BLR model only")
+int vk_ssmh_begin(vk_particles *h) { VK_TRY check_handle(h); use_device(h); VK_BLR_ONLY; blr_ss_begin(h->model); VK_CATCH }
+int vk_ssmh_propose(vk_particles *h, int32_t block, int32_t t_index, int32_t delta_mode, double delta_arg) {
+  VK_TRY check_handle(h); use_device(h); VK_BLR_ONLY;
+  blr_ss_propose(h->model, block, t_index, delta_mode, delta_arg);
+  VK_CATCH
+}
+int vk_ssmh_round(vk_particles *h, int64_t q0, int64_t q1, void **sums_dev_out) {
+  VK_TRY check_handle(h); use_device(h); VK_BLR_ONLY;
+  VK_REQUIRE(sums_dev_out && q0 >= 0 && q1 >= q0, VK_EINVAL, "bad round");
+  *sums_dev_out = blr_ss_round(h->model, q0, q1);
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_ssmh_decide(vk_particles *h, const void *sums_dev, int64_t n_end, int32_t k0, double epsilon,
+                   int32_t *n_active_out) {
+  VK_TRY check_handle(h); use_device(h); VK_BLR_ONLY;
+  VK_REQUIRE(sums_dev && n_active_out, VK_EINVAL, "NULL");
+  *n_active_out = blr_ss_decide(h->model, (const double *)sums_dev, n_end, k0, epsilon);
+  VK_CATCH
+}
+int vk_ssmh_commit(vk_particles *h) { VK_TRY check_handle(h); use_device(h); VK_BLR_ONLY; blr_ss_commit(h->model); VK_CUDA(cudaStreamSynchronize(h->stream)); VK_CATCH }
+int vk_ssmh_stats(vk_particles *h, int32_t transitions, double *stats_out_host) {
+  VK_TRY check_handle(h); use_device(h); VK_BLR_ONLY;
+  VK_REQUIRE(stats_out_host, VK_EINVAL, "NULL");
+  HostOut o(h, stats_out_host, (size_t)h->P * 3);
+  blr_ss_stats(h->model, transitions, o.ptr());
+  o.finish();
+  VK_CATCH
+}
+
 }  // extern "C"

@@ -16,4 +16,8 @@ void launch_ancestor_search_shard(vk_particles *h, uint64_t offset, uint64_t tot
                                   int64_t k_begin, int64_t k_count, int mode, uint32_t step,
                                   const double *uniforms_dev, int32_t *anc_out_dev);
 void launch_fill_even_weights(vk_particles *h, int64_t n, double lse, double log_n_new);
+size_t packed_row_bytes(vk_particles *h);
+void pack_state(vk_particles *h, const int32_t *idx_dev, int64_t n, void *packed_dev, bool unpack);
+void shard_weight_max(vk_particles *h);
+void shard_build_cdf(vk_particles *h, double global_max, int frac_bits);
 }  // namespace vk

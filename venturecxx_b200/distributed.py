@@ -1,0 +1,313 @@
+"""Multi-GPU layer: one process per GPU (torch.distributed, NCCL over NVLink on
+the B200 box, gloo in CPU tests), each owning one shard of the particle set.
+
+What shards how:
+  * likelihood_weight / incorporate / resimulation_mh / log_likelihood_at are
+    per-particle: rank g owns particles [g*P_local, (g+1)*P_local), no
+    communication (the reference fans these out with traces.map,
+    trace_set.py:287-294,339-340).  Philox streams are addressed by GLOBAL
+    particle index, so results do not depend on the GPU count.
+  * resample (trace_set.py:202-235) is the one exchange step:
+      all_reduce(max) -> fixed-point local CDF vs the global max ->
+      all_gather(mass, sum exp) -> every rank finds the children whose
+      threshold falls in ITS mass interval (exact integer arithmetic, so all
+      ranks agree bit-for-bit with the single-GPU result) -> packed ancestor
+      rows travel with all_to_all -> unpack into child slots ->
+      lw := logsumexp - log(P_total).
+  * subsampled_mh (subsampled_mh.py:76-171): observations (local sections)
+    shard, particles are replicated; per minibatch round each rank reduces its
+    local (sum dllh, sum dllh^2) per particle, one all_reduce(sum) of 2*P
+    doubles, then the identical sequential-test decision on every rank.
+
+The collective plumbing is written against a small `Shard` protocol so the
+same code runs over the CUDA library (CudaShard) and over a CPU stand-in in
+the gloo tests.
+"""
+import math
+
+import numpy as np
+
+MASK32 = 0xFFFFFFFF
+
+
+# ---- Philox4x32-10 on python ints (host side needs the ONE shared uniform) ----
+def philox4x32_10(c, k):
+    c0, c1, c2, c3 = c
+    k0, k1 = k
+    for _ in range(10):
+        p0 = 0xD2511F53 * c0
+        p1 = 0xCD9E8D57 * c2
+        n0 = ((p1 >> 32) ^ c1 ^ k0) & MASK32
+        n2 = ((p0 >> 32) ^ c3 ^ k1) & MASK32
+        c0, c1, c2, c3 = n0, p1 & MASK32, n2, p0 & MASK32
+        k0 = (k0 + 0x9E3779B9) & MASK32
+        k1 = (k1 + 0xBB67AE85) & MASK32
+    return c0, c1, c2, c3
+
+
+def global_uniform(seed, step):
+    """draw 0 of the stream (seed, GLOBAL_PARTICLE, step) -- csrc/philox.cuh"""
+    b = philox4x32_10((MASK32, MASK32, step & MASK32, 0), (seed & MASK32, (seed >> 32) & MASK32))
+    x = ((b[0] << 32) | b[1]) >> 11
+    return (x + 0.5) / 9007199254740992.0
+
+
+def frac_bits_for(P_total):
+    lg = 0
+    while (1 << lg) < P_total:
+        lg += 1
+    return min(62 - lg, 52)
+
+
+def systematic_child_range(offset, mass, total, n_new, u):
+    """[k_lo, k_hi): children whose threshold floor(((k<<32)+U0)*total / (n_new<<32))
+    lies in [offset, offset+mass) -- exact integer arithmetic, mirrors
+    ancestor_search_kernel (csrc/k_weights.cu)."""
+    U0 = min(int(u * 4294967296.0), MASK32)
+    den = n_new << 32
+
+    def first_k_with_threshold_at_least(v):
+        need = -(-(v * den) // total)          # ceil(v*den/total)
+        k = -(-(need - U0) // (1 << 32))       # ceil((need-U0)/2^32)
+        return min(max(k, 0), n_new)
+
+    return first_k_with_threshold_at_least(offset), first_k_with_threshold_at_least(offset + mass)
+
+
+def lse_from_parts(global_max, sumexps, any_nan=False):
+    """utils.logsumexp (lite/utils.py:70-91) from per-shard partial sums."""
+    if any_nan:
+        return float("nan")
+    if math.isinf(global_max):
+        return global_max
+    return global_max + math.log(float(np.sum(sumexps)))
+
+
+class CudaShard(object):
+    """Shard protocol over the C ABI; tensors live on this rank's GPU."""
+
+    def __init__(self, trace_set):
+        import torch
+        self.ts = trace_set
+        self.torch = torch
+        self.device = torch.device("cuda", trace_set.device)
+        self.P = trace_set.n_particles
+
+    # scalars
+    def weight_max(self):
+        import ctypes
+        from . import _lib
+        m = ctypes.c_double()
+        _lib.call("vk_shard_weight_max", self.ts._h, ctypes.byref(m))
+        return m.value
+
+    def build_cdf(self, global_max, frac_bits):
+        import ctypes
+        from . import _lib
+        mass, se = ctypes.c_uint64(), ctypes.c_double()
+        _lib.call("vk_shard_build_cdf", self.ts._h, float(global_max), int(frac_bits), ctypes.byref(mass),
+                  ctypes.byref(se))
+        return mass.value, se.value
+
+    def ancestors(self, offset, total, n_new, k_begin, k_count, mode, step):
+        from . import _lib
+        out = self.torch.empty(max(k_count, 1), dtype=self.torch.int32, device=self.device)
+        _lib.call("vk_shard_ancestors", self.ts._h, offset, total, n_new, k_begin, k_count, mode, step, None,
+                  out.data_ptr())
+        return out[:k_count]
+
+    def row_bytes(self):
+        import ctypes
+        from . import _lib
+        n = ctypes.c_int64()
+        _lib.call("vk_state_row_bytes", self.ts._h, ctypes.byref(n))
+        return n.value
+
+    def pack(self, particles):
+        from . import _lib
+        n = particles.numel()
+        out = self.torch.empty((n, self.row_bytes()), dtype=self.torch.uint8, device=self.device)
+        if n:
+            _lib.call("vk_pack_state", self.ts._h, particles.contiguous().data_ptr(), n, out.data_ptr())
+        return out
+
+    def unpack(self, slots, packed):
+        from . import _lib
+        n = slots.numel()
+        if n:
+            _lib.call("vk_unpack_state", self.ts._h, slots.contiguous().data_ptr(), n, packed.contiguous().data_ptr())
+
+    def fill_log_weights(self, v):
+        from . import _lib
+        _lib.call("vk_fill_log_weights", self.ts._h, float(v))
+
+    def incorporate(self):
+        return self.ts.incorporate()
+
+    def tensor(self, values, dtype):
+        return self.torch.tensor(values, dtype=dtype, device=self.device)
+
+
+def _all_to_all_rows(torch, dist, rows, send_counts, group=None):
+    """rows: (n, width) tensor whose first axis is grouped by destination rank with
+    send_counts[r] rows for rank r.  Returns the rows received, grouped by source."""
+    world = dist.get_world_size(group)
+    sc = torch.tensor(send_counts, dtype=torch.int64, device=rows.device)
+    rc = torch.empty(world, dtype=torch.int64, device=rows.device)
+    if dist.get_backend(group) == "nccl":
+        dist.all_to_all_single(rc, sc, group=group)
+        recv_counts = rc.tolist()
+        out = torch.empty((sum(recv_counts),) + tuple(rows.shape[1:]), dtype=rows.dtype, device=rows.device)
+        dist.all_to_all_single(out, rows.contiguous(), output_split_sizes=recv_counts,
+                               input_split_sizes=list(send_counts), group=group)
+        return out, recv_counts
+    # gloo (CPU tests): gather everything, keep what is addressed to this rank
+    rank = dist.get_rank(group)
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (list(send_counts), rows.cpu().numpy()), group=group)
+    parts, recv_counts = [], []
+    for src in range(world):
+        counts, data = gathered[src]
+        lo = sum(counts[:rank])
+        parts.append(data[lo:lo + counts[rank]])
+        recv_counts.append(counts[rank])
+    out = torch.from_numpy(np.concatenate(parts, axis=0)) if parts else rows[:0]
+    return out.to(rows.device), recv_counts
+
+
+def sharded_resample(shard, seed, step, mode="systematic", group=None):
+    """Global resample of P_total = world * P_local particles.  Returns the global
+    logsumexp.  `step` must be the same on every rank (the handles advance their
+    RNG step counters in lock step)."""
+    import torch
+    import torch.distributed as dist
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    P_local = shard.P
+    P_total = world * P_local
+    sys_mode = mode == "systematic"
+    # 1. global max
+    m = shard.tensor([shard.weight_max()], torch.float64)
+    dist.all_reduce(m, op=dist.ReduceOp.MAX, group=group)
+    gmax = float(m.item())
+    # 2. fixed-point masses relative to the global max
+    mass, sumexp = shard.build_cdf(gmax, frac_bits_for(P_total))
+    mine = shard.tensor([float(mass >> 32), float(mass & MASK32), sumexp], torch.float64)   # exact: 2 x 32-bit halves
+    allv = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(allv, mine, group=group)
+    masses = [(int(v[0].item()) << 32) | int(v[1].item()) for v in allv]
+    lse = lse_from_parts(gmax, [float(v[2].item()) for v in allv])
+    offset, total = sum(masses[:rank]), sum(masses)
+    # 3. children whose threshold lies in this shard's interval
+    if sys_mode:
+        u = global_uniform(seed, step)
+        k_lo, k_hi = systematic_child_range(offset, masses[rank], total, P_total, u)
+        anc = shard.ancestors(offset, total, P_total, k_lo, k_hi - k_lo, 1, step)
+        ks = torch.arange(k_lo, k_hi, dtype=torch.int64, device=anc.device)
+    else:
+        anc_all = shard.ancestors(offset, total, P_total, 0, P_total, 0, step)
+        ks = torch.nonzero(anc_all >= 0).flatten()
+        anc = anc_all[ks]
+    # 4. route: child k lives on rank k // P_local, slot k % P_local (ks ascending => grouped by destination)
+    dest = torch.div(ks, P_local, rounding_mode="floor")
+    send_counts = torch.bincount(dest, minlength=world).tolist() if ks.numel() else [0] * world
+    packed = shard.pack(anc.to(torch.int32))
+    slots = (ks - dest * P_local).to(torch.int32).reshape(-1, 1)
+    recv_rows, _ = _all_to_all_rows(torch, dist, packed, send_counts, group)
+    recv_slots, _ = _all_to_all_rows(torch, dist, slots, send_counts, group)
+    assert recv_slots.shape[0] == P_local, "every child slot must be filled exactly once"
+    shard.unpack(recv_slots.flatten().contiguous(), recv_rows)
+    # 5. even weights (utils.log_domain_even_out), then incorporate (trace_set.py:206-207)
+    shard.fill_log_weights(lse - math.log(P_total))
+    shard.incorporate()
+    return lse
+
+
+class ShardedTraceSet(object):
+    """The particle set of one job, sharded over the ranks of a process group.
+    Wraps this rank's B200TraceSet; per-particle operations are forwarded
+    unchanged, resample and subsampled_mh add the collectives."""
+
+    def __init__(self, model, particles_per_rank, seed=1, device=None, group=None):
+        import torch
+        import torch.distributed as dist
+        from .trace_set import B200TraceSet
+        self.group = group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        if device is None:
+            device = torch.cuda.current_device()
+        self.seed = int(seed)
+        self.local = B200TraceSet(model, particles_per_rank, seed=seed, device=device,
+                                  particle_base=self.rank * particles_per_rank)
+        self.shard = CudaShard(self.local)
+        self.n_particles = self.world * particles_per_rank
+
+    def __getattr__(self, name):       # per-particle operations: no communication
+        return getattr(self.local, name)
+
+    def resample(self, P=None, mode="multinomial"):
+        if P is not None and int(P) != self.n_particles:
+            from .exception import VentureException
+            raise VentureException("invalid_argument", "resample: P must equal the particle count")
+        step = self.local.rng_step
+        self.local.rng_step = step + 1
+        return sharded_resample(self.shard, self.seed, step,
+                                "systematic" if mode == "systematic" else "multinomial", self.group)
+
+    def logsumexp(self):
+        import torch
+        import torch.distributed as dist
+        m = self.shard.tensor([self.shard.weight_max()], torch.float64)
+        dist.all_reduce(m, op=dist.ReduceOp.MAX, group=self.group)
+        _, se = self.shard.build_cdf(float(m.item()), frac_bits_for(self.n_particles))
+        s = self.shard.tensor([se], torch.float64)
+        dist.all_reduce(s, op=dist.ReduceOp.SUM, group=self.group)
+        return lse_from_parts(float(m.item()), [float(s.item())])
+
+    # -- observation-sharded subsampled MH (particles replicated on every rank) --
+    def observe_shard(self, X_local, y_local, global_offset, n_total):
+        from . import _lib
+        self.local.observe(X_local, y_local)
+        _lib.call("vk_blr_set_observation_shard", self.local._h, int(global_offset), int(n_total))
+        self._n_total = int(n_total)
+
+    def subsampled_mh(self, scope, block, Nbatch, k0, epsilon, useDeltaKernels, deltaKernelArgs, updateValues,
+                      transitions):
+        import ctypes
+        import torch
+        import torch.distributed as dist
+        from . import _lib
+        h = self.local._h
+        s, b = self.local._scope_block(scope, block)
+        P = self.local.n_particles
+        Nt, Nbatch = self._n_total, int(Nbatch)
+        delta_mode = 2 if useDeltaKernels == 2 else 0
+        _lib.call("vk_ssmh_begin", h)
+        n_steps = int(transitions) * (self.local.numBlocksInScope() if b == _lib.BLOCK_EACH else 1)
+        for t in range(n_steps):
+            _lib.call("vk_ssmh_propose", h, b, t, delta_mode, float(deltaKernelArgs or 0.0))
+            for q0 in range(0, Nt, Nbatch):
+                q1 = min(q0 + Nbatch, Nt)
+                p = ctypes.c_void_p()
+                _lib.call("vk_ssmh_round", h, q0, q1, ctypes.byref(p))
+                sums = _wrap_device(torch, p.value, P * 2, self.local.device)
+                dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=self.group)
+                torch.cuda.current_stream().synchronize()
+                n_active = ctypes.c_int32()
+                _lib.call("vk_ssmh_decide", h, ctypes.c_void_p(p.value), q1, int(k0), float(epsilon),
+                          ctypes.byref(n_active))
+                if n_active.value == 0:
+                    break
+            _lib.call("vk_ssmh_commit", h)
+        stats = np.empty((P, 3))
+        _lib.call("vk_ssmh_stats", h, n_steps, _lib.ptr(stats))
+        return stats
+
+
+class _DevArray(object):
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+
+
+def _wrap_device(torch, ptr, n_doubles, device):
+    """zero-copy float64 view of library-owned device memory"""
+    return torch.as_tensor(_DevArray(ptr, n_doubles), device=torch.device("cuda", device))

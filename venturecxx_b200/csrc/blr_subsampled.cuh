@@ -25,6 +25,7 @@
 #pragma once
 #include "vk_common.cuh"
 #include "sp_math.cuh"
+#include "fast_math.cuh"
 
 namespace vk {
 
@@ -178,7 +179,7 @@ ss_round_kernel(const double *__restrict__ Xr /*[N_local][D] signed rows*/, cons
         }
       }
       if (live) {
-        double d = log_logistic(fma(delta, xs, eta)) - log_logistic(eta);
+        double d = fast_log_logistic(fma(delta, xs, eta)) - fast_log_logistic(eta);
         s1 += d; s2 += d * d;
       }
     }

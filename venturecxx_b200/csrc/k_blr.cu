@@ -26,6 +26,7 @@
 #include "vk_common.cuh"
 #include "sp_math.cuh"
 #include "blr_subsampled.cuh"
+#include "fast_math.cuh"
 
 namespace vk {
 
@@ -47,7 +48,7 @@ __device__ __forceinline__ double blr_fill_eta(double *__restrict__ eta_row,
     double e = 0.0;
     for (int j = 0; j < D; ++j) e = fma(w_sh[j], __ldg(&Xs[(int64_t)j * Ncap + i]), e);
     eta_row[i] = e;
-    acc += log_logistic(e);
+    acc += fast_log_logistic(e);
   }
   return acc;
 }
@@ -104,68 +105,95 @@ blr_all_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restr
 // rows too large for shared memory).
 // block_mode: VK_BLOCK_ONE (uniform site per transition), VK_BLOCK_EACH
 // (site = t mod D), or a fixed site index >= 0.
+// Proposals come from the prior and do not depend on the chain state, so the
+// (site, w', log u) triples of a whole chunk of transitions are drawn up front,
+// one transition per thread, and the transition loop itself is pure fp64 math:
+// per observation one FMA (eta + delta*x) and one fast_log_logistic.
+static const int BLR_MH_THREADS = 512;
+static const int BLR_MH_CHUNK = 512;   // transitions whose proposals are staged at once
+
 template <bool SMEM>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(BLR_MH_THREADS, 2)
 blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restrict__ ll,
               const double *__restrict__ Xs, BLRParams prm, int64_t P, int64_t p_base,
               uint64_t seed, uint32_t step0, int n_prop_steps, int block_mode,
               long long *__restrict__ acc_out) {
   extern __shared__ double smem[];
-  double *w_sh = smem;                 // D (padded to even)
-  double *red = w_sh + ((prm.D + 1) & ~1);  // 34
-  double *eta_sh = red + 34;           // N (SMEM only)
-  const int64_t N = prm.N;
+  double *w_sh = smem;                       // D (padded to even)
+  double *red = w_sh + ((prm.D + 1) & ~1);   // 34
+  double *prop_w = red + 34;                 // BLR_MH_CHUNK proposed values
+  double *prop_logu = prop_w + BLR_MH_CHUNK; // BLR_MH_CHUNK log-uniforms
+  int *prop_site = (int *)(prop_logu + BLR_MH_CHUNK);   // BLR_MH_CHUNK sites
+  double *eta_sh = (double *)(prop_site + BLR_MH_CHUNK);  // N (SMEM only)
+  const int N = (int)prm.N;
+  const int tid = threadIdx.x, nt = blockDim.x;
   for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
     __syncthreads();
     double *eta_g = eta + p * prm.Ncap;
-    if ((int)threadIdx.x < prm.D) w_sh[threadIdx.x] = w[(int64_t)threadIdx.x * P + p];
+    if (tid < prm.D) w_sh[tid] = w[(int64_t)tid * P + p];
     if (SMEM) {
       // Ncap is even and rows are 16-byte aligned: 16-byte vector copies
       const double2 *src = reinterpret_cast<const double2 *>(eta_g);
       double2 *dst = reinterpret_cast<double2 *>(eta_sh);
-      for (int64_t i = threadIdx.x; i < (N + 1) / 2; i += blockDim.x) dst[i] = src[i];
+      for (int i = tid; i < (N + 1) / 2; i += nt) dst[i] = src[i];
     }
     double *e_cur = SMEM ? eta_sh : eta_g;
     double rho = ll[p];
     long long acc = 0;
     bool dirty = false;
-    __syncthreads();
-    for (int t = 0; t < n_prop_steps; ++t) {
-      // every thread derives the same proposal from the particle's stream
-      Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)t);
-      double u_sel = r.uniform();
-      double u_acc = r.uniform();
-      int j;
-      if (block_mode == VK_BLOCK_ONE) { j = (int)(u_sel * (double)prm.D); if (j >= prm.D) j = prm.D - 1; }
-      else if (block_mode == VK_BLOCK_EACH) j = t % prm.D;
-      else j = block_mode;
-      double w_new = normal_sim(r, prm.mu0, prm.s0);
-      double delta = w_new - w_sh[j];
-      const double *xcol = Xs + (int64_t)j * prm.Ncap;
-      double part = 0.0;
-      for (int64_t i = threadIdx.x; i < N; i += blockDim.x)
-        part += log_logistic(fma(delta, __ldg(&xcol[i]), e_cur[i]));
-      double xi = block_sum(part, red);
-      double alpha = blr_log_alpha(rho, xi);
-      if (log(u_acc) < alpha) {   // uniform across the CTA
-        for (int64_t i = threadIdx.x; i < N; i += blockDim.x)
-          e_cur[i] = fma(delta, __ldg(&xcol[i]), e_cur[i]);
-        __syncthreads();
-        if (threadIdx.x == 0) w_sh[j] = w_new;
-        rho = xi; ++acc; dirty = true;
-        __syncthreads();
+    for (int c0 = 0; c0 < n_prop_steps; c0 += BLR_MH_CHUNK) {
+      int cn = n_prop_steps - c0 < BLR_MH_CHUNK ? n_prop_steps - c0 : BLR_MH_CHUNK;
+      __syncthreads();
+      for (int t = tid; t < cn; t += nt) {
+        Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)(c0 + t));
+        double u_sel = r.uniform();
+        double u_acc = r.uniform();
+        int j;
+        if (block_mode == VK_BLOCK_ONE) { j = (int)(u_sel * (double)prm.D); if (j >= prm.D) j = prm.D - 1; }
+        else if (block_mode == VK_BLOCK_EACH) j = (c0 + t) % prm.D;
+        else j = block_mode;
+        prop_site[t] = j;
+        prop_logu[t] = log(u_acc);
+        prop_w[t] = normal_sim(r, prm.mu0, prm.s0);
+      }
+      __syncthreads();
+      for (int t = 0; t < cn; ++t) {
+        const int j = prop_site[t];
+        const double w_new = prop_w[t];
+        const double delta = w_new - w_sh[j];
+        const double *__restrict__ xcol = Xs + (int64_t)j * prm.Ncap;
+        double p0 = 0.0, p1 = 0.0;
+        {
+          const double *xp = xcol + tid;
+          const double *ep = e_cur + tid;
+          int cnt = (N - tid + nt - 1) / nt;      // observations of this thread: tid, tid+nt, ...
+          for (; cnt >= 2; cnt -= 2, xp += 2 * nt, ep += 2 * nt) {   // two independent chains
+            double x0 = __ldg(xp), x1 = __ldg(xp + nt);
+            p0 += fast_log_logistic(fma(delta, x0, ep[0]));
+            p1 += fast_log_logistic(fma(delta, x1, ep[nt]));
+          }
+          if (cnt > 0) p0 += fast_log_logistic(fma(delta, __ldg(xp), ep[0]));
+        }
+        double xi = block_sum(p0 + p1, red);
+        double alpha = blr_log_alpha(rho, xi);
+        if (prop_logu[t] < alpha) {   // uniform across the CTA
+          for (int k = tid; k < N; k += nt) e_cur[k] = fma(delta, __ldg(&xcol[k]), e_cur[k]);
+          if (tid == 0) w_sh[j] = w_new;
+          rho = xi; ++acc; dirty = true;
+          __syncthreads();
+        }
       }
     }
     if (dirty) {
       if (SMEM) {
         const double2 *src = reinterpret_cast<const double2 *>(eta_sh);
         double2 *dst = reinterpret_cast<double2 *>(eta_g);
-        for (int64_t i = threadIdx.x; i < (N + 1) / 2; i += blockDim.x) dst[i] = src[i];
+        for (int i = tid; i < (N + 1) / 2; i += nt) dst[i] = src[i];
       }
-      if ((int)threadIdx.x < prm.D) w[(int64_t)threadIdx.x * P + p] = w_sh[threadIdx.x];
-      if (threadIdx.x == 0) ll[p] = rho;
+      if (tid < prm.D) w[(int64_t)tid * P + p] = w_sh[tid];
+      if (tid == 0) ll[p] = rho;
     }
-    if (acc_out && threadIdx.x == 0) acc_out[p] = acc;
+    if (acc_out && tid == 0) acc_out[p] = acc;
   }
 }
 
@@ -197,7 +225,7 @@ blr_mh_all_kernel(double *__restrict__ w, double *__restrict__ eta, double *__re
       for (int64_t i = threadIdx.x; i < N; i += blockDim.x) {
         double e = 0.0;
         for (int j = 0; j < prm.D; ++j) e = fma(w_sh[j], __ldg(&Xs[(int64_t)j * prm.Ncap + i]), e);
-        part += log_logistic(e);
+        part += fast_log_logistic(e);
       }
       double xi = block_sum(part, red);
       double alpha = blr_log_alpha(rho, xi);
@@ -224,7 +252,7 @@ blr_loglik_at_kernel(const double *__restrict__ w, const double *__restrict__ et
   for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
     const double *e = eta + p * prm.Ncap;
     double part = 0.0;
-    for (int64_t i = threadIdx.x; i < prm.N; i += blockDim.x) part += log_logistic(e[i]);
+    for (int64_t i = threadIdx.x; i < prm.N; i += blockDim.x) part += fast_log_logistic(e[i]);
     double tot = block_sum(part, red);
     if (threadIdx.x == 0) {
       // joint: + prior density of the principal node(s) (dispatch.py:345-361)
@@ -445,16 +473,17 @@ struct BLRModel : Model {
       } else {
         int n_steps = (block == VK_BLOCK_EACH) ? K * prm.D : K;
         uint32_t step0 = h->next_step((uint32_t)n_steps);
-        size_t base = (size_t)(((prm.D + 1) & ~1) + 34) * sizeof(double);
+        VK_REQUIRE(prm.N < ((int64_t)1 << 31), VK_EUNSUPPORTED, "blr mh: N must fit in int32");
+        size_t base = (size_t)(((prm.D + 1) & ~1) + 34 + 2 * BLR_MH_CHUNK) * sizeof(double) + BLR_MH_CHUNK * sizeof(int);
         size_t need = base + (size_t)((prm.N + 1) & ~(int64_t)1) * sizeof(double);
         if (need <= (size_t)smem_limit) {
           int per_sm = (int)((size_t)(227 * 1024) / (need + 1024));
           if (per_sm < 1) per_sm = 1;
-          if (per_sm > 8) per_sm = 8;
-          blr_mh_kernel<true><<<grid_particles(per_sm), 256, need, h->stream>>>(
+          if (per_sm > 2) per_sm = 2;
+          blr_mh_kernel<true><<<grid_particles(per_sm), BLR_MH_THREADS, need, h->stream>>>(
               w, eta, ll, Xs.p, prm, h->P, h->p_base, h->seed, step0, n_steps, block, acc_dev);
         } else {
-          blr_mh_kernel<false><<<grid_particles(8), 256, base, h->stream>>>(
+          blr_mh_kernel<false><<<grid_particles(2), BLR_MH_THREADS, base, h->stream>>>(
               w, eta, ll, Xs.p, prm, h->P, h->p_base, h->seed, step0, n_steps, block, acc_dev);
         }
         // |DRG| of scaffold(w_j) = w_j + lookup + array + N lookups + N dots;

@@ -54,8 +54,9 @@ def test_matches_reference_log_logistic_values(fm):
     for c in golden("lite_utils.json")["log_logistic"]:
         x, ref = unj(c["x"]), unj(c["out"])
         got = fm([x])[0]
-        if np.isinf(x) and x > 0:
-            assert abs(got) < 1e-300 or np.isnan(got)       # documented: +inf is outside the kernel's domain
+        if np.isinf(x):
+            # -inf -> -inf like the reference; +inf is outside the kernel's domain (inf - inf)
+            assert (got == ref) if x < 0 else (abs(got) < 1e-300 or np.isnan(got))
         elif abs(x) > 700:
             assert abs(got - ref) <= 1e-300 + 1e-15 * abs(ref)
         else:

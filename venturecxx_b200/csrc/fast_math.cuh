@@ -54,24 +54,29 @@ VK_HD int fm_lo_int(double t) {
 // coefficient table in constant memory on the device (fp64 instructions take a
 // constant-bank operand directly; literal doubles would be re-materialised with
 // two UMOVs each inside the hot loop)
+#define VK_FM_COEFFS                                                                                          \
+  /* q(r): e^r = 1 + r + r^2 q(r), highest degree first */                                                    \
+  2.5100385495510319078e-8, 2.7620088445409748161e-7, 2.7557268459997064772e-6, 0.000024801521295954375131,   \
+  0.00019841269863053616878, 0.0013888888917213716901, 0.0083333333333300618325, 0.041666666666624127873,     \
+  0.16666666666666667453, 0.50000000000000010221,                                                             \
+  /* g(z): 2 atanh(s)/s with z = s^2, highest degree first */                                                 \
+  0.17045199264557801332, 0.083239606433710133237, 0.12110290643250378952, 0.13300359007217546084,            \
+  0.15386615157236227967, 0.18181740781515607832, 0.22222224082160496478, 0.28571428545431753451,             \
+  0.40000000000185926041, 0.66666666666666149045, 2.0,                                                        \
+  /* 21: log2(e), 22: ln2 hi, 23: ln2 lo */                                                                   \
+  1.4426950408889634074, 6.93147180369123816490e-01, 1.90821492927058770002e-10
 #ifdef __CUDACC__
-__constant__ double FM_C[24] = {
-#else
-static const double FM_C[24] = {
+__constant__ double FM_C_DEV[24] = {VK_FM_COEFFS};
 #endif
-    // q(r): e^r = 1 + r + r^2 q(r), highest degree first
-    2.5100385495510319078e-8, 2.7620088445409748161e-7, 2.7557268459997064772e-6, 0.000024801521295954375131,
-    0.00019841269863053616878, 0.0013888888917213716901, 0.0083333333333300618325, 0.041666666666624127873,
-    0.16666666666666667453, 0.50000000000000010221,
-    // g(z): 2 atanh(s)/s with z = s^2, highest degree first
-    0.17045199264557801332, 0.083239606433710133237, 0.12110290643250378952, 0.13300359007217546084,
-    0.15386615157236227967, 0.18181740781515607832, 0.22222224082160496478, 0.28571428545431753451,
-    0.40000000000185926041, 0.66666666666666149045, 2.0,
-    // 21: log2(e), 22: ln2 hi, 23: ln2 lo
-    1.4426950408889634074, 6.93147180369123816490e-01, 1.90821492927058770002e-10};
+static const double FM_C_HOST[24] = {VK_FM_COEFFS};
 
 VK_HD double fast_log_logistic(double x) {
   const double MAGIC = 6755399441055744.0;           // 1.5 * 2^52
+#ifdef __CUDA_ARCH__
+  const double *FM_C = FM_C_DEV;
+#else
+  const double *FM_C = FM_C_HOST;
+#endif
   double a = fabs(x);
   a = a < 700.0 ? a : 700.0;                           // exp(-700) is normal; beyond, the term is < 1e-304
   double t = fma(-a, FM_C[21], MAGIC);
@@ -93,8 +98,9 @@ VK_HD double fast_log_logistic(double x) {
   double g = FM_C[10];
 #pragma unroll
   for (int k = 11; k < 21; ++k) g = fma(g, z, FM_C[k]);
-  // min(x,0) = (x - |x|)/2 exactly
-  return fma(-s, g, 0.5 * (x - fabs(x)));
+  // min(x,0) = x/2 - |x/2| exactly (halving first: no overflow near DBL_MAX)
+  double hx = 0.5 * x;
+  return fma(-s, g, hx - fabs(hx));
 }
 
 }  // namespace vk

@@ -14,8 +14,8 @@
  * accounting of detach/regen, the accept rule, the +-inf policies -- follows
  * Lite.  Where Lite delegates to scipy (gamma/beta logpdf, gammaln, betaln,
  * t.cdf) the closed forms are restated here and pinned against scipy and
- * against the reference's own functions in tests/ (see oracle/lite_semantics.py
- * and tests/golden/).
+ * against the reference's own functions in tests/ (see tests/golden/make_golden.py
+ * and tests/golden/*.json).
  *
  * Pinning status: logsumexp, logistic family, sequentialTest, categorical /
  * dirichlet / dir-cat densities, normal logDensity are pinned against the

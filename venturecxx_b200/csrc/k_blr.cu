@@ -27,10 +27,11 @@
 #include "sp_math.cuh"
 #include "blr_subsampled.cuh"
 #include "fast_math.cuh"
+#include <stdlib.h>
 
 namespace vk {
 
-struct BLRParams { double mu0, s0; int D; int64_t N, Ncap; };
+struct BLRParams { double mu0, s0; int D; int64_t N, Ncap, Xld; };   // Xld: column stride of Xs (zero padded)
 
 __device__ __forceinline__ double blr_log_alpha(double rho, double xi) {
   if (rho == -INFINITY && xi == -INFINITY) return INFINITY;   // mh.py:190-197
@@ -42,11 +43,11 @@ __device__ __forceinline__ double blr_log_alpha(double rho, double xi) {
 // sum of log_logistic(eta_i).  w in shared memory.
 __device__ __forceinline__ double blr_fill_eta(double *__restrict__ eta_row,
                                                const double *__restrict__ Xs, const double *w_sh,
-                                               int D, int64_t Ncap, int64_t i0, int64_t i1) {
+                                               int D, int64_t Xld, int64_t i0, int64_t i1) {
   double acc = 0.0;
   for (int64_t i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
     double e = 0.0;
-    for (int j = 0; j < D; ++j) e = fma(w_sh[j], __ldg(&Xs[(int64_t)j * Ncap + i]), e);
+    for (int j = 0; j < D; ++j) e = fma(w_sh[j], __ldg(&Xs[(int64_t)j * Xld + i]), e);
     eta_row[i] = e;
     acc += fast_log_logistic(e);
   }
@@ -83,7 +84,7 @@ blr_all_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restr
     __syncthreads();
     int64_t i0 = (mode == 3) ? n_prop : 0;
     int64_t i1 = (mode == 3) ? prm.N : n_prop;
-    double part = blr_fill_eta(eta + p * prm.Ncap, Xs, w_sh, prm.D, prm.Ncap, i0, i1);
+    double part = blr_fill_eta(eta + p * prm.Ncap, Xs, w_sh, prm.D, prm.Xld, i0, i1);
     double tot = block_sum(part, red);
     if (threadIdx.x == 0) {
       if (mode == 3) {
@@ -109,42 +110,87 @@ blr_all_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restr
 // (site, w', log u) triples of a whole chunk of transitions are drawn up front,
 // one transition per thread, and the transition loop itself is pure fp64 math:
 // per observation one FMA (eta + delta*x) and one fast_log_logistic.
-static const int BLR_MH_THREADS = 512;
-static const int BLR_MH_CHUNK = 512;   // transitions whose proposals are staged at once
+static const int BLR_MH_CHUNK = 256;   // transitions whose proposals are staged at once
+static const int BLR_MH_TILE = 1024;   // observations per CTA-wide loop iteration (THREADS x UNROLL)
+static const int BLR_MH_DEFAULT_VARIANT = 1;
+#define BLR_PAD_ETA 800.0              // logit of a padding slot: log_logistic(800) = -exp(-800) = 0
 
-template <bool SMEM>
-__global__ void __launch_bounds__(BLR_MH_THREADS, 2)
+// shared-memory carve-up shared by the kernel and the host-side size computation:
+// [log table][exp table][w D'][colsum D'][red 34][prop_w C][prop_logu C][prop_site C][eta row Npad]
+__host__ __device__ inline size_t blr_mh_smem_base(int D) {
+  return (size_t)FM_SMEM_LOG_BYTES + FM_SMEM_EXP_BYTES +
+         (size_t)(2 * ((D + 1) & ~1) + 34 + 2 * BLR_MH_CHUNK) * sizeof(double) +
+         (size_t)BLR_MH_CHUNK * sizeof(int);
+}
+
+// K resimulation-MH transitions per particle (see the header comment).
+// xi = sum_i log_logistic(v_i), v_i = eta_i + delta x_ij, is evaluated as
+//   sum_i min(v_i,0) - sum_i log1p(exp(-|v_i|)),
+//   sum_i min(v_i,0) = (sum_i v_i - sum_i |v_i|)/2,   sum_i v_i = S_eta + delta * colsum_j
+// so the per-observation fp64 work is 1 FMA (v), 1 add (|v|) and the table-driven
+// softplus (fast_math.cuh: fm_softplus_accum, 17 fp64 instructions).
+// The observation axis is padded to Npad = a multiple of BLR_MH_TILE: padding slots
+// have x = 0 (Xs columns are zero padded) and eta = BLR_PAD_ETA, so they contribute
+// exactly 0 to xi and every thread runs the same number of full iterations.  The
+// Xs values of the NEXT iteration are loaded before the current one is evaluated
+// (L2 latency hidden behind ~40 fp64 instructions per chain).
+template <bool SMEM, int THREADS, int UNROLL, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
 blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restrict__ ll,
               const double *__restrict__ Xs, BLRParams prm, int64_t P, int64_t p_base,
               uint64_t seed, uint32_t step0, int n_prop_steps, int block_mode,
-              long long *__restrict__ acc_out) {
-  extern __shared__ double smem[];
-  double *w_sh = smem;                       // D (padded to even)
-  double *red = w_sh + ((prm.D + 1) & ~1);   // 34
+              long long *__restrict__ acc_out, const FmCoef cf) {
+  static_assert(THREADS * UNROLL == BLR_MH_TILE, "tile");
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  unsigned char *log_tbl = smem_raw;
+  unsigned char *exp_tbl = smem_raw + FM_SMEM_LOG_BYTES;
+  const int Dp = (prm.D + 1) & ~1;
+  double *w_sh = reinterpret_cast<double *>(exp_tbl + FM_SMEM_EXP_BYTES);   // D
+  double *colsum = w_sh + Dp;                // D: sum_i Xs[j][i]
+  double *red = colsum + Dp;                 // 34
   double *prop_w = red + 34;                 // BLR_MH_CHUNK proposed values
   double *prop_logu = prop_w + BLR_MH_CHUNK; // BLR_MH_CHUNK log-uniforms
   int *prop_site = (int *)(prop_logu + BLR_MH_CHUNK);   // BLR_MH_CHUNK sites
-  double *eta_sh = (double *)(prop_site + BLR_MH_CHUNK);  // N (SMEM only)
+  double *eta_sh = (double *)(prop_site + BLR_MH_CHUNK);  // Npad (SMEM only)
   const int N = (int)prm.N;
-  const int tid = threadIdx.x, nt = blockDim.x;
+  const int Npad = (N + BLR_MH_TILE - 1) / BLR_MH_TILE * BLR_MH_TILE;
+  const int iters = Npad / BLR_MH_TILE;
+  const int tid = threadIdx.x, lane = threadIdx.x & 31;
+  fm_fill_smem_tables(log_tbl, exp_tbl);
+  const uint32_t exp_base = (uint32_t)__cvta_generic_to_shared(exp_tbl) + (uint32_t)(lane & 15) * 8u;
+  const uint32_t log_base = (uint32_t)__cvta_generic_to_shared(log_tbl) + (uint32_t)(lane & 7) * 16u;
+  for (int j = 0; j < prm.D; ++j) {          // column sums, once per CTA
+    const double *xc = Xs + (int64_t)j * prm.Xld;
+    double s_ = 0.0;
+    for (int i = tid; i < N; i += THREADS) s_ += __ldg(&xc[i]);
+    s_ = block_sum(s_, red);
+    if (tid == 0) colsum[j] = s_;
+  }
   for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
     __syncthreads();
     double *eta_g = eta + p * prm.Ncap;
     if (tid < prm.D) w_sh[tid] = w[(int64_t)tid * P + p];
+    double s_part = 0.0;
     if (SMEM) {
       // Ncap is even and rows are 16-byte aligned: 16-byte vector copies
       const double2 *src = reinterpret_cast<const double2 *>(eta_g);
       double2 *dst = reinterpret_cast<double2 *>(eta_sh);
-      for (int i = tid; i < (N + 1) / 2; i += nt) dst[i] = src[i];
+      for (int i = tid; i < Npad / 2; i += THREADS) {
+        double2 v = make_double2(BLR_PAD_ETA, BLR_PAD_ETA);
+        if (2 * i < N) { v = src[i]; if (2 * i + 1 >= N) v.y = BLR_PAD_ETA; }
+        dst[i] = v; s_part += v.x + v.y;
+      }
+    } else {
+      for (int i = tid; i < Npad; i += THREADS) s_part += i < N ? eta_g[i] : BLR_PAD_ETA;
     }
-    double *e_cur = SMEM ? eta_sh : eta_g;
+    double S_eta = block_sum(s_part, red);   // sum_i eta_i of the current state (padding included)
     double rho = ll[p];
     long long acc = 0;
     bool dirty = false;
     for (int c0 = 0; c0 < n_prop_steps; c0 += BLR_MH_CHUNK) {
       int cn = n_prop_steps - c0 < BLR_MH_CHUNK ? n_prop_steps - c0 : BLR_MH_CHUNK;
       __syncthreads();
-      for (int t = tid; t < cn; t += nt) {
+      for (int t = tid; t < cn; t += THREADS) {
         Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)(c0 + t));
         double u_sel = r.uniform();
         double u_acc = r.uniform();
@@ -161,26 +207,51 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
         const int j = prop_site[t];
         const double w_new = prop_w[t];
         const double delta = w_new - w_sh[j];
-        const double *__restrict__ xcol = Xs + (int64_t)j * prm.Ncap;
-        double p0 = 0.0, p1 = 0.0;
-        {
-          const double *xp = xcol + tid;
-          const double *ep = e_cur + tid;
-          int cnt = (N - tid + nt - 1) / nt;      // observations of this thread: tid, tid+nt, ...
-          for (; cnt >= 2; cnt -= 2, xp += 2 * nt, ep += 2 * nt) {   // two independent chains
-            double x0 = __ldg(xp), x1 = __ldg(xp + nt);
-            p0 += fast_log_logistic(fma(delta, x0, ep[0]));
-            p1 += fast_log_logistic(fma(delta, x1, ep[nt]));
+        const double *__restrict__ xcol = Xs + (int64_t)j * prm.Xld;
+        double am[UNROLL], af[UNROLL];   // sum |v|, sum r2 Q(r2)
+        long long aL[UNROLL];            // sum L[k], 2^-52 fixed point
+        double xn[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) { am[u] = 0.0; af[u] = 0.0; aL[u] = 0; xn[u] = __ldg(xcol + tid + u * THREADS); }
+        const double *xp = xcol + tid + BLR_MH_TILE;
+        int i0 = tid;
+        for (int it = 0; it < iters; ++it, xp += BLR_MH_TILE, i0 += BLR_MH_TILE) {
+          double v[UNROLL];
+#pragma unroll
+          for (int u = 0; u < UNROLL; ++u) {
+            double ev;
+            if (SMEM) ev = eta_sh[i0 + u * THREADS];
+            else ev = (i0 + u * THREADS < N) ? eta_g[i0 + u * THREADS] : BLR_PAD_ETA;
+            v[u] = fma(delta, xn[u], ev);
           }
-          if (cnt > 0) p0 += fast_log_logistic(fma(delta, __ldg(xp), ep[0]));
+#pragma unroll
+          for (int u = 0; u < UNROLL; ++u) xn[u] = __ldg(xp + u * THREADS);   // next tile (Xld has one tile of slack)
+#pragma unroll
+          for (int u = 0; u < UNROLL; ++u) {
+            fm_softplus_accum(v[u], cf, exp_base, log_base, af[u], aL[u]);
+            am[u] += fabs(v[u]);
+          }
         }
-        double xi = block_sum(p0 + p1, red);
+#pragma unroll
+        for (int u = 1; u < UNROLL; ++u) { am[0] += am[u]; af[0] += af[u]; aL[0] += aL[u]; }
+        double part = fma(-0.5, am[0], -af[0]) - (double)aL[0] * 2.220446049250313e-16;
+        if (tid == 0) part += 0.5 * fma(delta, colsum[j], S_eta);
+        double xi = block_sum(part, red);
         double alpha = blr_log_alpha(rho, xi);
         if (prop_logu[t] < alpha) {   // uniform across the CTA
-          for (int k = tid; k < N; k += nt) e_cur[k] = fma(delta, __ldg(&xcol[k]), e_cur[k]);
+          double sp = 0.0;
+          if (SMEM) {
+            for (int k = tid; k < Npad; k += THREADS) { double e_ = fma(delta, __ldg(&xcol[k]), eta_sh[k]); eta_sh[k] = e_; sp += e_; }
+          } else {
+            for (int k = tid; k < Npad; k += THREADS) {
+              double e_ = BLR_PAD_ETA;
+              if (k < N) { e_ = fma(delta, __ldg(&xcol[k]), eta_g[k]); eta_g[k] = e_; }
+              sp += e_;
+            }
+          }
           if (tid == 0) w_sh[j] = w_new;
           rho = xi; ++acc; dirty = true;
-          __syncthreads();
+          S_eta = block_sum(sp, red);   // recomputed, not updated: no drift
         }
       }
     }
@@ -188,7 +259,7 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
       if (SMEM) {
         const double2 *src = reinterpret_cast<const double2 *>(eta_sh);
         double2 *dst = reinterpret_cast<double2 *>(eta_g);
-        for (int i = tid; i < (N + 1) / 2; i += nt) dst[i] = src[i];
+        for (int i = tid; i < (N + 1) / 2; i += THREADS) dst[i] = src[i];
       }
       if (tid < prm.D) w[(int64_t)tid * P + p] = w_sh[tid];
       if (tid == 0) ll[p] = rho;
@@ -224,7 +295,7 @@ blr_mh_all_kernel(double *__restrict__ w, double *__restrict__ eta, double *__re
       double part = 0.0;
       for (int64_t i = threadIdx.x; i < N; i += blockDim.x) {
         double e = 0.0;
-        for (int j = 0; j < prm.D; ++j) e = fma(w_sh[j], __ldg(&Xs[(int64_t)j * prm.Ncap + i]), e);
+        for (int j = 0; j < prm.D; ++j) e = fma(w_sh[j], __ldg(&Xs[(int64_t)j * prm.Xld + i]), e);
         part += fast_log_logistic(e);
       }
       double xi = block_sum(part, red);
@@ -233,7 +304,7 @@ blr_mh_all_kernel(double *__restrict__ w, double *__restrict__ eta, double *__re
         double *eta_g = eta + p * prm.Ncap;
         for (int64_t i = threadIdx.x; i < N; i += blockDim.x) {
           double e = 0.0;
-          for (int j = 0; j < prm.D; ++j) e = fma(w_sh[j], __ldg(&Xs[(int64_t)j * prm.Ncap + i]), e);
+          for (int j = 0; j < prm.D; ++j) e = fma(w_sh[j], __ldg(&Xs[(int64_t)j * prm.Xld + i]), e);
           eta_g[i] = e;
         }
         if ((int)threadIdx.x < prm.D) w[(int64_t)threadIdx.x * P + p] = w_sh[threadIdx.x];
@@ -291,6 +362,7 @@ struct BLRModel : Model {
   DevBuf<uint8_t> y;
   double *w = nullptr, *w_alt = nullptr, *eta = nullptr, *eta_alt = nullptr, *ll = nullptr, *ll_alt = nullptr;
   int smem_limit = 0;
+  FmCoef fm_coef = fm_coef_host();
   // subsampled MH (C5): observation shard [obs_lo, obs_lo + N) of N_total, transition state
   int64_t obs_lo = 0, N_total = -1;
   bool eta_dirty = false;
@@ -305,7 +377,10 @@ struct BLRModel : Model {
     VK_REQUIRE(D >= 1 && D <= 256, VK_EINVAL, "blr: D must be in [1,256]");
     VK_REQUIRE(Ncap >= 1, VK_EINVAL, "blr: observation capacity must be positive");
     prm.mu0 = mu0; prm.s0 = s0; prm.D = D; prm.N = 0; prm.Ncap = (Ncap + 1) & ~(int64_t)1;
-    Xs.alloc((size_t)D * prm.Ncap);
+    // Xs columns are zero padded to a multiple of the MH kernel's tile plus one tile of prefetch slack
+    prm.Xld = ((prm.Ncap + BLR_MH_TILE - 1) / BLR_MH_TILE + 1) * BLR_MH_TILE;
+    Xs.alloc((size_t)D * prm.Xld);
+    VK_CUDA(cudaMemsetAsync(Xs.p, 0, Xs.bytes(), h->stream));
     y.alloc((size_t)prm.Ncap);
     wa.alloc((size_t)D * h->P);
     etaa.alloc((size_t)h->P * prm.Ncap);
@@ -314,7 +389,6 @@ struct BLRModel : Model {
     VK_CUDA(cudaMemsetAsync(w, 0, wa.bytes(), h->stream));
     VK_CUDA(cudaMemsetAsync(ll, 0, lla.bytes(), h->stream));
     VK_CUDA(cudaDeviceGetAttribute(&smem_limit, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
-    VK_CUDA(cudaFuncSetAttribute(blr_mh_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_limit));
   }
   void observe(const double *X_rows_host, const uint8_t *y_host, int64_t n) {
     VK_REQUIRE(prm.N + n <= prm.Ncap, VK_EINVAL, "blr: observation capacity exceeded");
@@ -322,7 +396,7 @@ struct BLRModel : Model {
     VK_CUDA(cudaMemcpyAsync(stage.p, X_rows_host, stage.bytes(), cudaMemcpyHostToDevice, h->stream));
     VK_CUDA(cudaMemcpyAsync(y.p + prm.N, y_host, (size_t)n, cudaMemcpyHostToDevice, h->stream));
     blr_sign_features_kernel<<<grid_for(n * prm.D, 256, h->sm_count, 8), 256, 0, h->stream>>>(
-        stage.p, y.p + prm.N, Xs.p, prm.D, prm.Ncap, prm.N, n);
+        stage.p, y.p + prm.N, Xs.p, prm.D, prm.Xld, prm.N, n);
     VK_CUDA(cudaGetLastError());
     VK_CUDA(cudaStreamSynchronize(h->stream));
     prm.N += n;
@@ -354,7 +428,7 @@ struct BLRModel : Model {
   void ss_prepare() {
     if (Xr_rows != prm.N) {
       Xr.alloc((size_t)prm.N * prm.D);
-      ss_transpose_kernel<<<grid_for(prm.N * prm.D, 256, h->sm_count, 8), 256, 0, h->stream>>>(Xs.p, Xr.p, prm.D, prm.Ncap, prm.N);
+      ss_transpose_kernel<<<grid_for(prm.N * prm.D, 256, h->sm_count, 8), 256, 0, h->stream>>>(Xs.p, Xr.p, prm.D, prm.Xld, prm.N);
       VK_CUDA(cudaGetLastError());
       Xr_rows = prm.N;
     }
@@ -473,19 +547,34 @@ struct BLRModel : Model {
       } else {
         int n_steps = (block == VK_BLOCK_EACH) ? K * prm.D : K;
         uint32_t step0 = h->next_step((uint32_t)n_steps);
-        VK_REQUIRE(prm.N < ((int64_t)1 << 31), VK_EUNSUPPORTED, "blr mh: N must fit in int32");
-        size_t base = (size_t)(((prm.D + 1) & ~1) + 34 + 2 * BLR_MH_CHUNK) * sizeof(double) + BLR_MH_CHUNK * sizeof(int);
-        size_t need = base + (size_t)((prm.N + 1) & ~(int64_t)1) * sizeof(double);
-        if (need <= (size_t)smem_limit) {
-          int per_sm = (int)((size_t)(227 * 1024) / (need + 1024));
-          if (per_sm < 1) per_sm = 1;
-          if (per_sm > 2) per_sm = 2;
-          blr_mh_kernel<true><<<grid_particles(per_sm), BLR_MH_THREADS, need, h->stream>>>(
-              w, eta, ll, Xs.p, prm, h->P, h->p_base, h->seed, step0, n_steps, block, acc_dev);
-        } else {
-          blr_mh_kernel<false><<<grid_particles(2), BLR_MH_THREADS, base, h->stream>>>(
-              w, eta, ll, Xs.p, prm, h->P, h->p_base, h->seed, step0, n_steps, block, acc_dev);
+        VK_REQUIRE(prm.N <= ((int64_t)1 << 19), VK_EUNSUPPORTED, "blr mh: at most 2^19 observations per particle in this version");
+        size_t base = blr_mh_smem_base(prm.D);
+        int64_t Npad = (prm.N + BLR_MH_TILE - 1) / BLR_MH_TILE * BLR_MH_TILE;
+        size_t need = base + (size_t)Npad * sizeof(double);
+        // tuning knob for experiments: VK_BLR_MH_VARIANT = 0 (512 threads x 2 chains, 2 CTAs/SM, 64 regs),
+        // 1 (256 x 4, 2 CTAs/SM, 128 regs), 2 (1024 x 1, 1 CTA/SM, 64 regs), 3 (512 x 2, 1 CTA/SM, 128 regs)
+        static int variant = getenv("VK_BLR_MH_VARIANT") ? atoi(getenv("VK_BLR_MH_VARIANT")) : BLR_MH_DEFAULT_VARIANT;
+        bool in_smem = need <= (size_t)smem_limit;
+        size_t sm_bytes = in_smem ? need : base;
+        int per_sm = (int)((size_t)(227 * 1024) / (sm_bytes + 1024));
+        if (per_sm < 1) per_sm = 1;
+#define VK_MH_LAUNCH(S, T, U, B)                                                                                \
+  do {                                                                                                         \
+    int cap = B < per_sm ? B : per_sm;                                                                         \
+    VK_CUDA(cudaFuncSetAttribute(blr_mh_kernel<S, T, U, B>, cudaFuncAttributeMaxDynamicSharedMemorySize,          \
+                                 (int)smem_limit));                                                            \
+    blr_mh_kernel<S, T, U, B><<<grid_particles(cap), T, sm_bytes, h->stream>>>(                                   \
+        w, eta, ll, Xs.p, prm, h->P, h->p_base, h->seed, step0, n_steps, block, acc_dev, fm_coef);             \
+  } while (0)
+#define VK_MH_VARIANT(T, U, B) do { if (in_smem) VK_MH_LAUNCH(true, T, U, B); else VK_MH_LAUNCH(false, T, U, B); } while (0)
+        switch (variant) {
+          case 1: VK_MH_VARIANT(256, 4, 2); break;
+          case 2: VK_MH_VARIANT(1024, 1, 1); break;
+          case 3: VK_MH_VARIANT(512, 2, 1); break;
+          default: VK_MH_VARIANT(512, 2, 2); break;
         }
+#undef VK_MH_VARIANT
+#undef VK_MH_LAUNCH
         // |DRG| of scaffold(w_j) = w_j + lookup + array + N lookups + N dots;
         // 'each' sums D proposals per transition (dispatch.py:122-128)
         nodes = (double)(3 + 2 * prm.N) * (block == VK_BLOCK_EACH ? prm.D : 1);
@@ -509,6 +598,7 @@ struct BLRModel : Model {
   void forget_observations(double *w_dev) override {
     if (w_dev) log_likelihood_at(0, VK_BLOCK_ALL, false, w_dev);
     prm.N = 0; n_prop = 0; Xr_rows = -1; eta_dirty = false;
+    VK_CUDA(cudaMemsetAsync(Xs.p, 0, Xs.bytes(), h->stream));   // keep the zero padding invariant
     VK_CUDA(cudaMemsetAsync(ll, 0, (size_t)h->P * sizeof(double), h->stream));
   }
   int64_t num_sites() const override { return prm.D; }

@@ -265,8 +265,12 @@ __device__ __forceinline__ void fm_softplus_accum(double v, const FmCoef &cf, ui
   const double nf = t - MAGIC;
   const double r = fma(nf, -cf.c_ln2, -a);
   double T;
-  asm("ld.shared.f64 %0, [%1];" : "=d"(T) : "r"(exp_base + ((uint32_t)(m & 63) << 7)));
-  const double Ts = __hiloint2double(__double2hiint(T) + (m & ~63) * 16384, __double2loint(T));   // T * 2^(m>>6)
+  uint32_t ea, th;
+  // mask + multiply-add (one LOP3 + one IMAD/LEA each) instead of shift / mask / add
+  asm("mad.lo.u32 %0, %1, 128, %2;" : "=r"(ea) : "r"((uint32_t)(m & 63)), "r"(exp_base));
+  asm("ld.shared.f64 %0, [%1];" : "=d"(T) : "r"(ea));
+  asm("mad.lo.u32 %0, %1, 16384, %2;" : "=r"(th) : "r"((uint32_t)(m & ~63)), "r"((uint32_t)__double2hiint(T)));
+  const double Ts = __hiloint2double((int)th, __double2loint(T));   // T * 2^(m>>6)
   double E = cf.E[4];
   E = fma(E, r, cf.E[3]);
   E = fma(E, r, cf.E[2]);
@@ -274,10 +278,11 @@ __device__ __forceinline__ void fm_softplus_accum(double v, const FmCoef &cf, ui
   E = fma(E, r, cf.E[0]);
   const double e = fma(Ts * r, E, Ts);
   const double tt = fma(e, cf.k128, MAGIC);                // low word = k = rint(128 e) in [0,128]
-  uint32_t inv_hi, c_hi, L_lo, L_hi;
+  uint32_t inv_hi, c_hi, L_lo, L_hi, la;
+  asm("mad.lo.u32 %0, %1, 128, %2;" : "=r"(la) : "r"((uint32_t)__double2loint(tt)), "r"(log_base));
   asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
       : "=r"(inv_hi), "=r"(c_hi), "=r"(L_lo), "=r"(L_hi)
-      : "r"(log_base + ((uint32_t)__double2loint(tt) << 7)));
+      : "r"(la));
   const double r2 = fma(e, __hiloint2double((int)inv_hi, 0), __hiloint2double((int)c_hi, 0));
   double Q = cf.Q[5];
   Q = fma(Q, r2, cf.Q[4]);

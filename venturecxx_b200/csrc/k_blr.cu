@@ -116,10 +116,10 @@ static const int BLR_MH_DEFAULT_VARIANT = 1;
 #define BLR_PAD_ETA 800.0              // logit of a padding slot: log_logistic(800) = -exp(-800) = 0
 
 // shared-memory carve-up shared by the kernel and the host-side size computation:
-// [log table][exp table][w D'][colsum D'][red 34][prop_w C][prop_logu C][prop_site C][eta row Npad]
+// [log table][exp table][w D'][colsum D'][red 34][slots 64][prop_w C][prop_logu C][prop_site C][eta row Npad]
 __host__ __device__ inline size_t blr_mh_smem_base(int D) {
   return (size_t)FM_SMEM_LOG_BYTES + FM_SMEM_EXP_BYTES +
-         (size_t)(2 * ((D + 1) & ~1) + 34 + 2 * BLR_MH_CHUNK) * sizeof(double) +
+         (size_t)(2 * ((D + 1) & ~1) + 34 + 64 + 2 * BLR_MH_CHUNK) * sizeof(double) +
          (size_t)BLR_MH_CHUNK * sizeof(int);
 }
 
@@ -134,6 +134,21 @@ __host__ __device__ inline size_t blr_mh_smem_base(int D) {
 // exactly 0 to xi and every thread runs the same number of full iterations.  The
 // Xs values of the NEXT iteration are loaded before the current one is evaluated
 // (L2 latency hidden behind ~40 fp64 instructions per chain).
+// Block-wide sum with ONE barrier: per-warp sums go to a double-buffered slot
+// array (buffer = parity of the call), every thread then adds the NW values in
+// the same fixed order, so the result is bit-identical in all threads.
+template <int NW>
+__device__ __forceinline__ double block_sum_1sync(double v, double *slots /* 2*NW */, int parity) {
+  v = warp_sum(v);
+  double *b = slots + parity * NW;
+  if ((threadIdx.x & 31) == 0) b[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = b[0];
+#pragma unroll
+  for (int k = 1; k < NW; ++k) t += b[k];
+  return t;
+}
+
 template <bool SMEM, int THREADS, int UNROLL, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB)
 blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restrict__ ll,
@@ -148,7 +163,8 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
   double *w_sh = reinterpret_cast<double *>(exp_tbl + FM_SMEM_EXP_BYTES);   // D
   double *colsum = w_sh + Dp;                // D: sum_i Xs[j][i]
   double *red = colsum + Dp;                 // 34
-  double *prop_w = red + 34;                 // BLR_MH_CHUNK proposed values
+  double *slots = red + 34;                  // 2 x 32 per-warp partial sums (block_sum_1sync)
+  double *prop_w = slots + 64;               // BLR_MH_CHUNK proposed values
   double *prop_logu = prop_w + BLR_MH_CHUNK; // BLR_MH_CHUNK log-uniforms
   int *prop_site = (int *)(prop_logu + BLR_MH_CHUNK);   // BLR_MH_CHUNK sites
   double *eta_sh = (double *)(prop_site + BLR_MH_CHUNK);  // Npad (SMEM only)
@@ -203,16 +219,23 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
         prop_w[t] = normal_sim(r, prm.mu0, prm.s0);
       }
       __syncthreads();
+      double xn[UNROLL];               // Xs values of the tile about to be evaluated
+      {
+        const double *x0 = Xs + (int64_t)prop_site[0] * prm.Xld + tid;
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) xn[u] = __ldg(x0 + u * THREADS);
+      }
       for (int t = 0; t < cn; ++t) {
         const int j = prop_site[t];
         const double w_new = prop_w[t];
         const double delta = w_new - w_sh[j];
         const double *__restrict__ xcol = Xs + (int64_t)j * prm.Xld;
+        // first tile of the NEXT transition's column (its site does not depend on this accept)
+        const double *xnext = Xs + (int64_t)prop_site[t + 1 < cn ? t + 1 : t] * prm.Xld + tid;
         double am[UNROLL], af[UNROLL];   // sum |v|, sum r2 Q(r2)
         long long aL[UNROLL];            // sum L[k], 2^-52 fixed point
-        double xn[UNROLL];
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) { am[u] = 0.0; af[u] = 0.0; aL[u] = 0; xn[u] = __ldg(xcol + tid + u * THREADS); }
+        for (int u = 0; u < UNROLL; ++u) { am[u] = 0.0; af[u] = 0.0; aL[u] = 0; }
         const double *xp = xcol + tid + BLR_MH_TILE;
         int i0 = tid;
         for (int it = 0; it < iters; ++it, xp += BLR_MH_TILE, i0 += BLR_MH_TILE) {
@@ -225,7 +248,11 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
             v[u] = fma(delta, xn[u], ev);
           }
 #pragma unroll
-          for (int u = 0; u < UNROLL; ++u) xn[u] = __ldg(xp + u * THREADS);   // next tile (Xld has one tile of slack)
+          {
+            const double *src = it + 1 < iters ? xp : xnext;   // next tile, or the next transition's first tile
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) xn[u] = __ldg(src + u * THREADS);
+          }
 #pragma unroll
           for (int u = 0; u < UNROLL; ++u) {
             fm_softplus_accum(v[u], cf, exp_base, log_base, af[u], aL[u]);
@@ -236,7 +263,7 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
         for (int u = 1; u < UNROLL; ++u) { am[0] += am[u]; af[0] += af[u]; aL[0] += aL[u]; }
         double part = fma(-0.5, am[0], -af[0]) - (double)aL[0] * 2.220446049250313e-16;
         if (tid == 0) part += 0.5 * fma(delta, colsum[j], S_eta);
-        double xi = block_sum(part, red);
+        double xi = block_sum_1sync<THREADS / 32>(part, slots, t & 1);
         double alpha = blr_log_alpha(rho, xi);
         if (prop_logu[t] < alpha) {   // uniform across the CTA
           double sp = 0.0;

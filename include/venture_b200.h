@@ -21,8 +21,13 @@
  *     Python shim raises it as VentureException("evaluation", msg), the way
  *     pytrace.cxx:236-242,331-332 translates Puma's C++ exceptions.
  *   - plain pointers and sizes only.  Pointers named *_host are host memory
- *     (pageable or pinned); copies are issued on the handle's stream and the
- *     call returns after the stream has drained, so results are ready.
+ *     (pageable or pinned).  A call that is given a host INPUT or OUTPUT
+ *     buffer issues its copies on the handle's stream and returns after the
+ *     stream has drained, so results are ready and inputs may be reused.
+ *     Calls without host buffers (vk_likelihood_weight, vk_resample / vk_mh
+ *     with NULL outputs, vk_reset_to_prior, ...) are STREAM-ORDERED: they
+ *     return once enqueued; vk_synchronize() or any later host-output call
+ *     waits for them, and an asynchronous CUDA error is reported there.
  *   - the handle owns all device memory.  One caller at a time per handle
  *     (the reference engine is single-threaded per TraceSet).
  *   - arithmetic is IEEE double (the reference is double everywhere).

@@ -385,18 +385,314 @@ void gather_state(vk_particles *h, const int32_t *anc_dev, int64_t n_new) {
   VK_CUDA(cudaGetLastError());
 }
 
-// Whole single-GPU resample: LSE -> fixed CDF -> ancestors -> gather -> even weights.
+// ---- systematic resampling without a CDF array or a search ------------------------
+// Thresholds thr_k = floor(((k<<32)+U0) W / (n_new<<32)) increase with k, so the children
+// of particle i are the contiguous range [kf(cdf[i-1]), kf(cdf[i])) with
+//   kf(c) = smallest k with thr_k >= c = ceil((ceil(c*den/W) - U0) / 2^32),  den = n_new<<32
+// (exact 128-bit integers; identical to searching the CDF for every child).
+typedef unsigned __int128 u128_t;
+__device__ __forceinline__ int64_t first_child_at_least(uint64_t c, uint64_t W, int64_t n_new, uint64_t U0) {
+  if (c == 0) return 0;
+  u128_t den = (u128_t)(uint64_t)n_new << 32;
+  u128_t need = ((u128_t)c * den + (u128_t)(W - 1)) / (u128_t)W;
+  if (need <= (u128_t)U0) return 0;
+  u128_t k = (need - (u128_t)U0 + (u128_t)0xFFFFFFFFull) >> 32;
+  return k > (u128_t)(uint64_t)n_new ? n_new : (int64_t)(uint64_t)k;
+}
+__device__ __forceinline__ uint64_t systematic_U0(const double *uniforms, uint64_t seed, uint32_t step) {
+  double u;
+  if (uniforms) u = uniforms[0];
+  else { Stream r(seed, GLOBAL_PARTICLE, step); u = r.uniform(); }
+  uint64_t U0 = (uint64_t)(u * 4294967296.0);
+  return U0 > 0xFFFFFFFFull ? 0xFFFFFFFFull : U0;
+}
+
+// pass A': per-tile totals of the fixed-point weights AND of exp(lw - m) (for the LSE)
+__global__ void __launch_bounds__(SCAN_THREADS)
+fixed_tile_sums_exp_kernel(const double *__restrict__ lw, int64_t n, const double *__restrict__ red,
+                           double scale, uint64_t *tile_sums, double *tile_exp) {
+  __shared__ uint64_t sh[32];
+  __shared__ double shd[33];
+  const double m = red[0];
+  int64_t base = (int64_t)blockIdx.x * SCAN_TILE;
+  uint64_t s = 0;
+  double se = 0.0;
+#pragma unroll
+  for (int j = 0; j < SCAN_ITEMS; ++j) {
+    int64_t i = base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+    if (i < n) {
+      double v = lw[i];
+      if (!(m > -INFINITY)) s += 1ull;
+      else {
+        double d = v - m;
+        if (d == d) { double e = exp(d); s += __double2ull_rn(e * scale); se += e; }
+      }
+    }
+  }
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) sh[w] = s;
+  se = block_sum(se, shd);
+  if (w == 0) {
+    s = lane < (SCAN_THREADS >> 5) ? sh[lane] : 0ull;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) { tile_sums[blockIdx.x] = s; tile_exp[blockIdx.x] = se; }
+  }
+}
+
+// pass B': scan of tile totals (as scan_tile_sums_kernel) + LSE from the tile exp sums
+// (fixed order) with the edge cases of utils.py:77-91 -> red[3], red[4]
+__global__ void __launch_bounds__(1024)
+scan_tile_sums_lse_kernel(uint64_t *tile_sums, const double *tile_exp, int n_tiles, int64_t n, double *red) {
+  __shared__ uint64_t sh[32];
+  __shared__ double shd[33];
+  __shared__ uint64_t carry_sh;
+  if (threadIdx.x == 0) carry_sh = 0;
+  __syncthreads();
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  double se = 0.0;
+  for (int b0 = 0; b0 < n_tiles; b0 += 1024) {
+    int b = b0 + threadIdx.x;
+    uint64_t v = b < n_tiles ? tile_sums[b] : 0ull;
+    if (b < n_tiles) se += tile_exp[b];
+    uint64_t inc = warp_scan_incl(v, lane);
+    if (lane == 31) sh[w] = inc;
+    __syncthreads();
+    if (w == 0) { uint64_t t = sh[lane]; t = warp_scan_incl(t, lane); sh[lane] = t; }
+    __syncthreads();
+    uint64_t woff = w > 0 ? sh[w - 1] : 0ull;
+    uint64_t carry = carry_sh;
+    if (b < n_tiles) tile_sums[b] = carry + woff + inc - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry_sh = carry + woff + inc;
+    __syncthreads();
+  }
+  se = block_sum(se, shd);
+  if (threadIdx.x == 0) {
+    tile_sums[n_tiles] = carry_sh;
+    double m = red[0], mn = red[1], nanf = red[2], lse;
+    if (n == 0) lse = -INFINITY;
+    else if (nanf != 0.0) lse = NAN;
+    else if (isinf(m) && mn != -m) lse = m;
+    else if (isinf(m)) lse = NAN;
+    else lse = m + log(se);
+    red[3] = se; red[4] = lse;
+  }
+}
+
+// pass C': running CDF in registers -> children ranges -> anc[k] = i  (no CDF array, no search)
+__global__ void __launch_bounds__(SCAN_THREADS)
+systematic_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__restrict__ red,
+                            double scale, const uint64_t *__restrict__ tile_sums, int n_tiles,
+                            int64_t n_new, uint64_t seed, uint32_t step,
+                            const double *__restrict__ uniforms, int32_t *__restrict__ anc) {
+  __shared__ uint64_t sh[32];
+  const double m = red[0];
+  const uint64_t W = tile_sums[n_tiles];
+  const uint64_t U0 = systematic_U0(uniforms, seed, step);
+  int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+  uint64_t q[SCAN_ITEMS];
+  uint64_t s = 0;
+#pragma unroll
+  for (int j = 0; j < SCAN_ITEMS; ++j) {
+    int64_t i = base + j;
+    q[j] = i < n ? fixed_weight(lw[i], m, scale) : 0ull;
+    s += q[j];
+  }
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint64_t inc = warp_scan_incl(s, lane);
+  if (lane == 31) sh[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    uint64_t t = lane < (SCAN_THREADS >> 5) ? sh[lane] : 0ull;
+    t = warp_scan_incl(t, lane);
+    sh[lane] = t;
+  }
+  __syncthreads();
+  if (s == 0) return;   // no mass in this thread's items: no children
+  uint64_t run = tile_sums[blockIdx.x] + (w > 0 ? sh[w - 1] : 0ull) + inc - s;
+  int64_t k_lo = first_child_at_least(run, W, n_new, U0);
+#pragma unroll
+  for (int j = 0; j < SCAN_ITEMS; ++j) {
+    if (q[j] == 0) continue;
+    run += q[j];
+    int64_t k_hi = first_child_at_least(run, W, n_new, U0);
+    for (int64_t k = k_lo; k < k_hi; ++k) anc[k] = (int32_t)(base + j);
+    k_lo = k_hi;
+  }
+}
+
+// ---- small particle sets: the whole resample in ONE single-CTA kernel ----------------
+// (C1 at P = 1000 is launch-latency bound: 1 launch instead of ~10.)  lw, the fixed-point
+// CDF and the ancestors live in shared memory; state arrays are gathered cur -> alt.
+static const int SMALL_P_MAX = 2048;
+static const int SMALL_THREADS = 512;
+static const int SMALL_MAX_ARRAYS = 4;
+struct SmallArrays {
+  int n;
+  const unsigned char *cur[SMALL_MAX_ARRAYS];
+  unsigned char *alt[SMALL_MAX_ARRAYS];
+  long long row_bytes[SMALL_MAX_ARRAYS];   // particle-major rows (elem_bytes == 0)
+  long long n_rows[SMALL_MAX_ARRAYS];      // SoA rows
+  int elem_bytes[SMALL_MAX_ARRAYS];
+};
+__global__ void __launch_bounds__(SMALL_THREADS)
+resample_small_kernel(double *__restrict__ lw, int P, int n_new, int mode, int frac_bits, uint64_t seed,
+                      uint32_t step, const double *__restrict__ uniforms, int32_t *__restrict__ anc_out,
+                      double *__restrict__ red, SmallArrays arrs) {
+  __shared__ uint64_t cdf[SMALL_P_MAX];
+  __shared__ int32_t anc[SMALL_P_MAX];
+  __shared__ double shd[3][33];
+  __shared__ uint64_t shu[33];
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  constexpr int ITEMS = SMALL_P_MAX / SMALL_THREADS;   // consecutive items per thread
+  double v[ITEMS];
+  double mx = -INFINITY, mn = INFINITY, nanf = 0.0;
+#pragma unroll
+  for (int j = 0; j < ITEMS; ++j) {
+    int i = tid * ITEMS + j;
+    v[j] = i < P ? lw[i] : NAN;
+    if (i < P) { if (v[j] != v[j]) nanf = 1.0; else { mx = fmax(mx, v[j]); mn = fmin(mn, v[j]); } }
+  }
+  mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
+  if (lane == 0) { shd[0][w] = mx; shd[1][w] = mn; shd[2][w] = nanf; }
+  __syncthreads();
+  { const int nw = SMALL_THREADS / 32;
+    mx = lane < nw ? shd[0][lane] : -INFINITY; mn = lane < nw ? shd[1][lane] : INFINITY; nanf = lane < nw ? shd[2][lane] : 0.0; }
+  mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
+  const double m = mx;
+  const double scale = ldexp(1.0, frac_bits);
+  uint64_t q[ITEMS], s = 0;
+  double se = 0.0;
+#pragma unroll
+  for (int j = 0; j < ITEMS; ++j) {
+    int i = tid * ITEMS + j;
+    q[j] = 0;
+    if (i < P) {
+      if (!(m > -INFINITY)) q[j] = 1ull;
+      else { double d = v[j] - m; if (d == d) { double e = exp(d); q[j] = __double2ull_rn(e * scale); se += e; } }
+    }
+    s += q[j];
+  }
+  __syncthreads();   // shd reuse
+  se = warp_sum(se);
+  uint64_t inc = warp_scan_incl(s, lane);
+  if (lane == 31) shu[w] = inc;
+  if (lane == 0) shd[0][w] = se;
+  __syncthreads();
+  if (w == 0) { uint64_t t = lane < SMALL_THREADS / 32 ? shu[lane] : 0ull; t = warp_scan_incl(t, lane); shu[lane] = t; }
+  se = warp_sum(lane < SMALL_THREADS / 32 ? shd[0][lane] : 0.0);
+  __syncthreads();
+  const uint64_t W = shu[31];
+  uint64_t run = (w > 0 ? shu[w - 1] : 0ull) + inc - s;
+  double lse;
+  if (nanf != 0.0) lse = NAN;
+  else if (isinf(m) && mn != -m) lse = m;
+  else if (isinf(m)) lse = NAN;
+  else lse = m + log(se);
+  if (mode == VK_RESAMPLE_SYSTEMATIC) {
+    const uint64_t U0 = systematic_U0(uniforms, seed, step);
+    if (s != 0) {
+      int64_t k_lo = first_child_at_least(run, W, n_new, U0);
+#pragma unroll
+      for (int j = 0; j < ITEMS; ++j) {
+        if (q[j] == 0) continue;
+        run += q[j];
+        int64_t k_hi = first_child_at_least(run, W, n_new, U0);
+        for (int64_t k = k_lo; k < k_hi; ++k) anc[k] = tid * ITEMS + j;
+        k_lo = k_hi;
+      }
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) { run += q[j]; int i = tid * ITEMS + j; if (i < P) cdf[i] = run; }
+    __syncthreads();
+    for (int k = tid; k < n_new; k += SMALL_THREADS) {
+      double u;
+      if (uniforms) u = uniforms[k];
+      else { Stream r(seed, (uint64_t)k, step); u = r.uniform(); }
+      uint64_t U = (uint64_t)(u * 9007199254740992.0);
+      if (U > 9007199254740991ull) U = 9007199254740991ull;
+      uint64_t thr = (uint64_t)(((u128_t)U * (u128_t)W) >> 53);
+      int lo = 0, hi = P - 1;
+      while (lo < hi) { int mid = (lo + hi) >> 1; if (cdf[mid] > thr) hi = mid; else lo = mid + 1; }
+      anc[k] = lo;
+    }
+  }
+  __syncthreads();
+  const double even = lse - log((double)n_new);
+  for (int k = tid; k < n_new; k += SMALL_THREADS) { anc_out[k] = anc[k]; lw[k] = even; }
+  if (tid == 0) { red[0] = m; red[1] = mn; red[2] = nanf; red[3] = se; red[4] = lse; }
+  for (int a = 0; a < arrs.n; ++a) {
+    if (arrs.elem_bytes[a] == 0) {
+      long long rb = arrs.row_bytes[a];
+      if ((rb & 15) == 0) {
+        long long units = rb >> 4, total = (long long)n_new * units;
+        const uint4 *in = (const uint4 *)arrs.cur[a]; uint4 *out = (uint4 *)arrs.alt[a];
+        for (long long t = tid; t < total; t += SMALL_THREADS) { long long k = t / units, c = t - k * units; out[t] = in[(long long)anc[k] * units + c]; }
+      } else {
+        long long total = (long long)n_new * rb;
+        for (long long t = tid; t < total; t += SMALL_THREADS) { long long k = t / rb, c = t - k * rb; arrs.alt[a][t] = arrs.cur[a][(long long)anc[k] * rb + c]; }
+      }
+    } else {
+      int eb = arrs.elem_bytes[a];
+      long long total = (long long)n_new * arrs.n_rows[a];
+      for (long long t = tid; t < total; t += SMALL_THREADS) {
+        long long r = t / n_new, k = t - r * n_new;
+        const unsigned char *src = arrs.cur[a] + (r * P + anc[k]) * eb;
+        unsigned char *dst = arrs.alt[a] + (r * n_new + k) * eb;
+        if (eb == 8) *(uint64_t *)dst = *(const uint64_t *)src;
+        else if (eb == 4) *(uint32_t *)dst = *(const uint32_t *)src;
+        else for (int b = 0; b < eb; ++b) dst[b] = src[b];
+      }
+    }
+  }
+}
+
+static bool resample_small(vk_particles *h, int64_t n_new, int mode, const double *uniforms_dev, uint32_t step) {
+  if (h->P > SMALL_P_MAX || n_new > SMALL_P_MAX) return false;
+  std::vector<StateArray> arrs = h->model->state_arrays();
+  if (arrs.size() > (size_t)SMALL_MAX_ARRAYS) return false;
+  SmallArrays sa; sa.n = (int)arrs.size();
+  for (int a = 0; a < sa.n; ++a) {
+    sa.cur[a] = (const unsigned char *)*arrs[a].cur; sa.alt[a] = (unsigned char *)*arrs[a].alt;
+    sa.row_bytes[a] = (long long)arrs[a].row_bytes; sa.n_rows[a] = (long long)arrs[a].n_rows;
+    sa.elem_bytes[a] = (int)arrs[a].elem_bytes;
+    if (sa.elem_bytes[a] == 0 && (long long)n_new * sa.row_bytes[a] > (1ll << 26)) return false;  // big rows: use the wide path
+  }
+  resample_small_kernel<<<1, SMALL_THREADS, 0, h->stream>>>(h->lw.p, (int)h->P, (int)n_new, mode, frac_bits_for(h->P), h->seed,
+                                                   step, uniforms_dev, h->anc.p, h->red.p, sa);
+  VK_CUDA(cudaGetLastError());
+  for (auto &a : arrs) { void *t = *a.cur; *a.cur = *a.alt; *a.alt = t; }
+  return true;
+}
+
+// Whole single-GPU resample: max -> fixed-point tile sums (+ LSE) -> ancestors -> gather -> even weights.
 void resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms_dev) {
   VK_REQUIRE(n_new == h->P, VK_EUNSUPPORTED, "resample: n_new must equal the particle count in this version");
   VK_REQUIRE(mode == VK_RESAMPLE_MULTINOMIAL || mode == VK_RESAMPLE_SYSTEMATIC, VK_EINVAL, "resample: bad mode");
   cudaStream_t st = h->stream;
   int64_t P = h->P;
   uint32_t step = h->next_step();
-  device_logsumexp(h->lw.p, P, h->red.p, h->counters.p, h->sm_count, st);
+  if (resample_small(h, n_new, mode, uniforms_dev, step)) { h->model->after_resample(); return; }
   int S = frac_bits_for(P);
-  build_fixed_cdf(h, h->red.p, 0.0, S);
-  int grid = grid_for(n_new, 256, h->sm_count, 8);
-  launch_ancestor_search_single(h, n_new, mode, step, uniforms_dev, grid);
+  double scale = ldexp(1.0, S);
+  int n_tiles = (int)((P + SCAN_TILE - 1) / SCAN_TILE);
+  if (h->red_u.n < (size_t)n_tiles + 1) h->red_u.alloc((size_t)n_tiles + 1);
+  if (h->tile_exp.n < (size_t)n_tiles) h->tile_exp.alloc((size_t)n_tiles);
+  lse_pass1_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p);
+  fixed_tile_sums_exp_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p);
+  scan_tile_sums_lse_kernel<<<1, 1024, 0, st>>>(h->red_u.p, h->tile_exp.p, n_tiles, P, h->red.p);
+  if (mode == VK_RESAMPLE_SYSTEMATIC) {
+    systematic_offspring_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, n_tiles, n_new,
+                                                                  h->seed, step, uniforms_dev, h->anc.p);
+  } else {
+    fixed_cdf_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, 0.0, h->red.p, scale, h->red_u.p, h->cdf.p);
+    launch_ancestor_search_single(h, n_new, mode, step, uniforms_dev, grid_for(n_new, 256, h->sm_count, 8));
+  }
+  VK_CUDA(cudaGetLastError());
   gather_state(h, h->anc.p, n_new);
   fill_kernel<<<grid_for(n_new, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, n_new, h->red.p, log((double)n_new));
   VK_CUDA(cudaGetLastError());

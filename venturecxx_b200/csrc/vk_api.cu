@@ -25,13 +25,18 @@ static void check_handle(const vk_particles *h) {
 }
 static void use_device(const vk_particles *h) { VK_CUDA(cudaSetDevice(h->device)); }
 
-// temporary device staging buffer of P doubles copied to the host on scope exit
+// Device staging for a host output of n doubles: the handle's grow-only buffer
+// (no cudaMalloc on the hot path).  finish() copies out and drains the stream;
+// calls WITHOUT a host output stay stream-ordered (no synchronisation).
 struct HostOut {
-  vk_particles *h; double *host; DevBuf<double> dev; size_t n;
-  HostOut(vk_particles *h_, double *host_, size_t n_) : h(h_), host(host_), n(n_) { if (host) dev.alloc(n); }
-  double *ptr() { return host ? dev.p : nullptr; }
+  vk_particles *h; double *host; size_t n;
+  HostOut(vk_particles *h_, double *host_, size_t n_) : h(h_), host(host_), n(n_) {
+    if (host && h->out_d.n < n) { VK_CUDA(cudaStreamSynchronize(h->stream)); h->out_d.alloc(n); }
+  }
+  double *ptr() { return host ? h->out_d.p : nullptr; }
   void finish() {
-    if (host) VK_CUDA(cudaMemcpyAsync(host, dev.p, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (!host) return;
+    VK_CUDA(cudaMemcpyAsync(host, h->out_d.p, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     VK_CUDA(cudaStreamSynchronize(h->stream));
   }
 };
@@ -158,7 +163,6 @@ int vk_synchronize(vk_particles *h) { VK_TRY check_handle(h); use_device(h); VK_
 int vk_reset_to_prior(vk_particles *h) {
   VK_TRY check_handle(h); use_device(h);
   h->model->reset_to_prior();
-  VK_CUDA(cudaStreamSynchronize(h->stream));
   VK_CATCH
 }
 
@@ -207,7 +211,6 @@ int vk_make_consistent(vk_particles *h, double *increments_out_host) {
 int vk_likelihood_weight(vk_particles *h) {
   VK_TRY check_handle(h); use_device(h);
   h->model->likelihood_weight();
-  VK_CUDA(cudaStreamSynchronize(h->stream));
   VK_CATCH
 }
 int vk_get_log_weights(vk_particles *h, double *out_host) {
@@ -280,7 +283,7 @@ int vk_resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms
     VK_CUDA(cudaMemcpyAsync(ancestors_out_host, h->anc.p, (size_t)n_new * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
   // trace_set.py:207: resample ends with incorporate()
   h->model->make_consistent(nullptr);
-  VK_CUDA(cudaStreamSynchronize(h->stream));
+  if (uniforms_host || ancestors_out_host) VK_CUDA(cudaStreamSynchronize(h->stream));
   VK_CATCH
 }
 
@@ -289,13 +292,14 @@ int vk_mh(vk_particles *h, int32_t scope, int32_t block, int32_t transitions, do
   VK_TRY check_handle(h); use_device(h);
   VK_REQUIRE(transitions >= 0, VK_EINVAL, "transitions must be >= 0");
   HostOut o(h, mean_nodes_out_host, (size_t)h->P);
-  DevBuf<long long> acc;
-  if (accepted_out_host) acc.alloc((size_t)h->P);
-  if (accepted_out_host && transitions == 0) VK_CUDA(cudaMemsetAsync(acc.p, 0, acc.bytes(), h->stream));
-  h->model->mh(scope, block, transitions, o.ptr(), accepted_out_host ? acc.p : nullptr);
-  if (accepted_out_host)
-    VK_CUDA(cudaMemcpyAsync(accepted_out_host, acc.p, acc.bytes(), cudaMemcpyDeviceToHost, h->stream));
+  if (accepted_out_host && h->acc_d.n < (size_t)h->P) { VK_CUDA(cudaStreamSynchronize(h->stream)); h->acc_d.alloc((size_t)h->P); }
+  long long *acc = accepted_out_host ? h->acc_d.p : nullptr;
+  if (acc && transitions == 0) VK_CUDA(cudaMemsetAsync(acc, 0, (size_t)h->P * sizeof(long long), h->stream));
+  h->model->mh(scope, block, transitions, o.ptr(), acc);
+  if (acc)
+    VK_CUDA(cudaMemcpyAsync(accepted_out_host, acc, (size_t)h->P * sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
   o.finish();
+  if (acc && !mean_nodes_out_host) VK_CUDA(cudaStreamSynchronize(h->stream));
   VK_CATCH
 }
 
@@ -346,7 +350,7 @@ int vk_write_site(vk_particles *h, int64_t site, const double *in_host) {
   VK_CUDA(cudaStreamSynchronize(h->stream));
   VK_CATCH
 }
-int vk_refresh(vk_particles *h) { VK_TRY check_handle(h); use_device(h); h->model->refresh(); VK_CUDA(cudaStreamSynchronize(h->stream)); VK_CATCH }
+int vk_refresh(vk_particles *h) { VK_TRY check_handle(h); use_device(h); h->model->refresh(); VK_CATCH }
 
 int vk_device_buffer(vk_particles *h, int32_t which, void **dev_ptr_out, int64_t *n_bytes_out) {
   VK_TRY check_handle(h);
@@ -419,7 +423,6 @@ int vk_unpack_state(vk_particles *h, const int32_t *slots_dev, int64_t n, const 
 int vk_fill_log_weights(vk_particles *h, double value) {
   VK_TRY check_handle(h); use_device(h);
   launch_fill_even_weights(h, h->P, value, 0.0);
-  VK_CUDA(cudaStreamSynchronize(h->stream));
   VK_CATCH
 }
 

@@ -85,10 +85,13 @@ struct vk_particles {
   cudaStream_t own_stream = nullptr;
   vk::DevBuf<double> lw;        // log weights, P
   vk::DevBuf<double> scratch_d; // P doubles (increments, probs)
+  vk::DevBuf<double> out_d;     // grow-only staging for host outputs
+  vk::DevBuf<long long> acc_d;  // accept counters staging (vk_mh)
   vk::DevBuf<uint64_t> cdf;     // fixed-point inclusive weight prefix sums, P
   vk::DevBuf<int32_t> anc;      // ancestors, P
   vk::DevBuf<double> red;       // small reduction scratch
   vk::DevBuf<uint64_t> red_u;   // scan block sums
+  vk::DevBuf<double> tile_exp;  // per-tile sums of exp(lw - max)
   vk::DevBuf<unsigned int> counters;
   vk::Model *model = nullptr;
   uint32_t next_step(uint32_t n = 1) { uint32_t s = step; step += n; return s; }

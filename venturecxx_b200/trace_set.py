@@ -139,8 +139,10 @@ class B200TraceSet(object):
     def likelihood_weight(self):
         _lib.call("vk_likelihood_weight", self._h)
 
-    def incorporate(self):
-        out = self._out()
+    def incorporate(self, return_increments=True):
+        """trace_set.py:290-294.  The reference returns the per-trace increments; pass
+        return_increments=False to keep the call stream-ordered (no device-to-host copy)."""
+        out = self._out() if return_increments else None
         _lib.call("vk_make_consistent", self._h, _lib.ptr(out))
         return out
 

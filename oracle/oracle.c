@@ -492,7 +492,7 @@ void orc_blr_mh(double *w, const double *X, const uint8_t *y, int D, int64_t N, 
 /* regularised incomplete beta I_x(a,b) (continued fraction, modified Lentz);
  * stands in for scipy.stats.t.cdf (infer/subsampled_mh.py:161). */
 static double betacf(double a, double b, double x) {
-  const double TINY = 1e-300, EPS = 1e-16;
+  const double TINY = 1e-300, EPS = 4.5e-16;
   double qab = a + b, qap = a + 1, qam = a - 1, c = 1, d = 1 - qab * x / qap;
   if (fabs(d) < TINY) d = TINY;
   d = 1 / d;

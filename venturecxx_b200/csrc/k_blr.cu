@@ -494,9 +494,9 @@ struct BLRModel : Model {
     VK_REQUIRE(n_groups <= 8, VK_EUNSUPPORTED, "subsampled_mh: at most 256 particles per GPU in this version");
     int grid = ss_grid();
     if (ss_partial.n < (size_t)grid * h->P * 2) ss_partial.alloc((size_t)grid * h->P * 2);
-    size_t sm = (size_t)8 * 32 * 2 * sizeof(double);
+    size_t sm = (size_t)8 * 32 * (prm.D > 2 ? prm.D : 2) * sizeof(double);   // per-warp row tiles (reused for the partial sums)
     SSState S = ss_state();
-#define VK_SS_LAUNCH(DT) ss_round_kernel<DT><<<grid, 256, sm, h->stream>>>(Xr.p, w, S, prm.D, h->P, q0, q1, obs_lo, prm.N, ss_key, ss_partial.p)
+#define VK_SS_LAUNCH(DT) do { VK_CUDA(cudaFuncSetAttribute(ss_round_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); ss_round_kernel<DT><<<grid, 256, sm, h->stream>>>(Xr.p, w, S, prm.D, h->P, q0, q1, obs_lo, prm.N, ss_key, ss_partial.p); } while (0)
     if (prm.D <= 4) VK_SS_LAUNCH(4);
     else if (prm.D <= 8) VK_SS_LAUNCH(8);
     else if (prm.D <= 16) VK_SS_LAUNCH(16);
@@ -504,20 +504,29 @@ struct BLRModel : Model {
     else if (prm.D <= 64) VK_SS_LAUNCH(64);
     else throw Error(VK_EUNSUPPORTED, "subsampled_mh: D <= 64 in this version");
 #undef VK_SS_LAUNCH
-    ss_reduce_kernel<<<grid_for(h->P * 2, 128, h->sm_count, 1), 128, 0, h->stream>>>(ss_partial.p, grid, h->P, ss_sums.p);
+    ss_reduce_kernel<<<grid_for(h->P * 2 * 32, 128, h->sm_count, 4), 128, 0, h->stream>>>(ss_partial.p, grid, h->P, ss_sums.p);
     VK_CUDA(cudaGetLastError());
   }
-  // sequential-test decision from (possibly all-reduced) sums; returns #particles still undecided
-  int ss_decide(const double *sums_dev, int64_t n_end, int k0, double eps) {
+  // sequential-test decision from (possibly all-reduced) sums; ss_decide returns #particles still
+  // undecided (host round trip); ss_decide_launch only enqueues, ss_decide_wait reads the count of
+  // the LAST enqueued decision
+  void ss_decide_launch(const double *sums_dev, int64_t n_end, int k0, double eps) {
     int64_t Nt = N_total >= 0 ? N_total : prm.N;
     int *n_active = ss_i.p + 2 * h->P;
     VK_CUDA(cudaMemsetAsync(n_active, 0, sizeof(int), h->stream));
-    ss_decide_kernel<<<grid_for(h->P, 128, h->sm_count, 1), 128, 0, h->stream>>>(ss_state(), sums_dev, h->P, (double)n_end,
-                                                                                 (double)Nt, k0, eps, n_active);
+    ss_decide_kernel<<<grid_for(h->P, 32, h->sm_count, 8), 32, 0, h->stream>>>(ss_state(), sums_dev, h->P, (double)n_end,
+                                                                               (double)Nt, k0, eps, n_active);
     VK_CUDA(cudaGetLastError());
+  }
+  int ss_decide_wait() {
+    int *n_active = ss_i.p + 2 * h->P;
     VK_CUDA(cudaMemcpyAsync(ss_active_host, n_active, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     VK_CUDA(cudaStreamSynchronize(h->stream));
     return *ss_active_host;
+  }
+  int ss_decide(const double *sums_dev, int64_t n_end, int k0, double eps) {
+    ss_decide_launch(sums_dev, n_end, k0, eps);
+    return ss_decide_wait();
   }
   void ss_commit() {
     ss_commit_kernel<<<grid_for(h->P, 128, h->sm_count, 4), 128, 0, h->stream>>>(w, ss_state(), h->P);
@@ -540,10 +549,16 @@ struct BLRModel : Model {
     int n_prop_steps = block == VK_BLOCK_EACH ? K * prm.D : K;
     for (int t = 0; t < n_prop_steps; ++t) {
       ss_propose(block, t, use_delta == 2 ? 2 : 0, delta_arg);
+      // Rounds are enqueued in groups and the "anybody still undecided?" count is read back once
+      // per group: a round after the last decision is a no-op (decided particles are skipped by
+      // both kernels), so the result is identical to checking after every round.
+      const int GROUP = 4;
+      int pending = 0;
       for (int64_t q0 = 0; q0 < Nt; q0 += Nbatch) {
         int64_t q1 = q0 + Nbatch < Nt ? q0 + Nbatch : Nt;
         ss_round(q0, q1);
-        if (ss_decide(ss_sums.p, q1, k0, eps) == 0) break;
+        ss_decide_launch(ss_sums.p, q1, k0, eps);
+        if (++pending == GROUP || q1 == Nt) { pending = 0; if (ss_decide_wait() == 0) break; }
       }
       ss_commit();
     }

@@ -25,6 +25,7 @@
 // HBM-bound; see DESIGN.md.
 #include "vk_common.cuh"
 #include "sp_math.cuh"
+#include <stdlib.h>
 
 namespace vk {
 
@@ -39,6 +40,10 @@ struct LDARow {
   __device__ LDARow(unsigned char *base, const LDALayout &L)
       : alpha((double *)base), nk((uint32_t *)(base + L.off_nk)), ndk((uint16_t *)(base + L.off_ndk)),
         nkw((uint16_t *)(base + L.off_nkw)), z(base + L.off_z) {}
+  // small sections (alpha, n_k, n_dk) and z staged at `small` / `zs`, the K x V table left in global memory
+  __device__ LDARow(unsigned char *small, uint16_t *nkw_global, unsigned char *zs, const LDALayout &L)
+      : alpha((double *)small), nk((uint32_t *)(small + L.off_nk)), ndk((uint16_t *)(small + L.off_ndk)),
+        nkw(nkw_global), z(zs) {}
 };
 
 __device__ __forceinline__ int warp_scan_incl_i(int v, int lane) {
@@ -139,24 +144,40 @@ lda_seq_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__r
 }
 
 // K resimulation-MH transitions per particle on the staged row.
-__global__ void __launch_bounds__(32)
+// stage: 0 = whole row in global memory, 1 = whole row in shared memory (one warp per CTA),
+// 2 = alpha / n_k / n_dk / z in shared memory and the K x V topic-word table in global memory
+// (2 cells touched per z transition): ~6 KB per particle instead of 38 KB at C4, so every SM
+// holds tens of particles and the serial per-particle chains overlap each other's latency.
+static const int LDA_WARPS = 4;
+__global__ void __launch_bounds__(32 * LDA_WARPS)
 lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__restrict__ doc,
               const int32_t *__restrict__ word, const int32_t *__restrict__ doclen, int n_tok,
               int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int block_mode,
               int stage, long long *__restrict__ acc_out) {
-  extern __shared__ uint4 smem_u4[];
-  const int lane = threadIdx.x;
+  extern __shared__ uint4 smem_all[];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, n_w = blockDim.x >> 5;
   const int nb = 2 + n_tok;
-  for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
+  const size_t z_bytes = L.row_bytes - L.off_z;
+  const size_t warp_bytes = stage == 1 ? L.row_bytes : L.off_nkw + z_bytes;
+  uint4 *smem_u4 = smem_all + (size_t)wid * (warp_bytes / 16);
+  for (int64_t p = (int64_t)blockIdx.x * n_w + wid; p < P; p += (int64_t)gridDim.x * n_w) {
     unsigned char *grow = rows + p * L.row_bytes;
     unsigned char *base = grow;
-    if (stage) {
+    if (stage == 1) {
       const uint4 *src = (const uint4 *)grow;
       for (size_t i = lane; i < L.row_bytes / 16; i += 32) smem_u4[i] = src[i];
       base = (unsigned char *)smem_u4;
       __syncwarp();
+    } else if (stage == 2) {
+      const uint4 *src = (const uint4 *)grow;
+      for (size_t i = lane; i < L.off_nkw / 16; i += 32) smem_u4[i] = src[i];
+      const uint4 *zsrc = (const uint4 *)(grow + L.off_z);
+      for (size_t i = lane; i < z_bytes / 16; i += 32) smem_u4[L.off_nkw / 16 + i] = zsrc[i];
+      __syncwarp();
     }
-    LDARow R(base, L);
+    LDARow R = stage == 2 ? LDARow((unsigned char *)smem_u4, (uint16_t *)(grow + L.off_nkw),
+                                   (unsigned char *)smem_u4 + L.off_nkw, L)
+                          : LDARow(base, L);
     long long acc = 0;
     for (int k = 0; k < n_steps; ++k) {
       Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
@@ -210,9 +231,15 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
         __syncwarp();
       }
     }
-    if (stage) {
+    if (stage == 1) {
       uint4 *dst = (uint4 *)grow;
       for (size_t i = lane; i < L.row_bytes / 16; i += 32) dst[i] = smem_u4[i];
+      __syncwarp();
+    } else if (stage == 2) {
+      uint4 *dst = (uint4 *)grow;
+      for (size_t i = lane; i < L.off_nkw / 16; i += 32) dst[i] = smem_u4[i];
+      uint4 *zdst = (uint4 *)(grow + L.off_z);
+      for (size_t i = lane; i < z_bytes / 16; i += 32) zdst[i] = smem_u4[L.off_nkw / 16 + i];
       __syncwarp();
     }
     if (acc_out && lane == 0) acc_out[p] = acc;
@@ -291,12 +318,13 @@ struct LDAModel : Model {
     VK_REQUIRE(max_tokens >= 1 && max_tokens <= 65535, VK_EINVAL, "lda: max_tokens must be in [1,65535] (u16 counts)");
     VK_REQUIRE(a > 0 && b > 0, VK_EINVAL, "gamma: shape and rate must be positive");
     L.K = K; L.V = V; L.n_docs = n_docs; L.max_tokens = max_tokens; L.hyper_a = a; L.hyper_b = b;
+    auto up16 = [](size_t v) { return (v + 15) & ~(size_t)15; };   // every section starts 16-byte aligned
     size_t o = 16;
-    L.off_nk = o; o += (size_t)K * 4;
-    L.off_ndk = o; o += (size_t)n_docs * K * 2;
-    L.off_nkw = o; o += (size_t)K * V * 2;
-    L.off_z = o; o += (size_t)max_tokens;
-    L.row_bytes = (o + 15) & ~(size_t)15;
+    L.off_nk = o; o = up16(o + (size_t)K * 4);
+    L.off_ndk = o; o = up16(o + (size_t)n_docs * K * 2);
+    L.off_nkw = o; o = up16(o + (size_t)K * V * 2);
+    L.off_z = o; o = up16(o + (size_t)max_tokens);
+    L.row_bytes = o;
     doc.alloc((size_t)max_tokens); word.alloc((size_t)max_tokens); doclen.alloc((size_t)n_docs);
     doclen_host.assign((size_t)n_docs, 0);
     rowsa.alloc((size_t)h->P * L.row_bytes);
@@ -345,13 +373,23 @@ struct LDAModel : Model {
     if (K > 0) {
       int n_steps = block == VK_BLOCK_EACH ? K * nb : K;
       uint32_t step0 = h->next_step((uint32_t)n_steps);
-      int stage = L.row_bytes <= (size_t)smem_limit ? 1 : 0;
-      size_t sm = stage ? L.row_bytes : 0;
-      int per_sm = stage ? (int)((size_t)(227 * 1024) / (L.row_bytes + 1024)) : 16;
+      // small sections + z per warp in shared memory, K x V table in global memory (stage 2);
+      // if even that does not fit, everything stays in global memory (stage 0)
+      size_t small = L.off_nkw + (L.row_bytes - L.off_z);
+      static int forced = getenv("VK_LDA_STAGE") ? atoi(getenv("VK_LDA_STAGE")) : -1;
+      int stage = (small * LDA_WARPS <= (size_t)smem_limit) ? 2 : 0;
+      int warps = LDA_WARPS;
+      if (forced == 1 && L.row_bytes <= (size_t)smem_limit) { stage = 1; warps = 1; }
+      if (forced == 0) stage = 0;
+      size_t sm = stage == 2 ? small * warps : (stage == 1 ? L.row_bytes : 0);
+      int per_sm = sm ? (int)((size_t)(227 * 1024) / (sm + 1024)) : 16;
       if (per_sm < 1) per_sm = 1;
-      if (per_sm > 32) per_sm = 32;
-      lda_mh_kernel<<<grid_p(per_sm), 32, sm, h->stream>>>(rows, L, doc.p, word.p, doclen.p, n_tok, h->P, h->p_base,
-                                                           h->seed, step0, n_steps, block, stage, acc_dev);
+      if (per_sm * warps > 64) per_sm = 64 / warps;
+      int64_t need_ctas = (h->P + warps - 1) / warps;
+      int64_t cap = (int64_t)h->sm_count * per_sm;
+      int grid = (int)(need_ctas < cap ? need_ctas : cap);
+      lda_mh_kernel<<<grid, 32 * warps, sm, h->stream>>>(rows, L, doc.p, word.p, doclen.p, n_tok, h->P, h->p_base,
+                                                         h->seed, step0, n_steps, block, stage, acc_dev);
       VK_CUDA(cudaGetLastError());
     } else if (acc_dev) {
       VK_CUDA(cudaMemsetAsync(acc_dev, 0, (size_t)h->P * sizeof(long long), h->stream));

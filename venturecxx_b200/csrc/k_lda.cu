@@ -182,7 +182,7 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
     for (int k = 0; k < n_steps; ++k) {
       Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
       double u_sel = r.uniform();
-      double logu = log(r.uniform());
+      double u_acc = r.uniform();
       int b;
       if (block_mode == VK_BLOCK_ONE) { b = (int)(u_sel * (double)nb); if (b >= nb) b = nb - 1; }
       else if (block_mode == VK_BLOCK_EACH) b = k % nb;
@@ -202,7 +202,7 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
         }
         double alpha = (rho == -INFINITY && xi == -INFINITY) ? INFINITY
                        : (rho == INFINITY && xi == INFINITY) ? -INFINITY : xi - rho;
-        if (logu < alpha) { if (lane == 0) R.alpha[b] = a_new; ++acc; }
+        if (log(u_acc) < alpha) { if (lane == 0) R.alpha[b] = a_new; ++acc; }
         __syncwarp();
       } else {
         int i = b - 2;
@@ -211,18 +211,21 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
         double ad = R.alpha[0], aw = R.alpha[1];
         double Aw = aw * (double)L.V;
         int64_t co = (int64_t)zo * L.V + w;
-        // counts with this token (and its z) removed
-        double rho = dircat_logpmf((double)((int)R.nkw[co] - 1), aw, (double)((int)R.nk[zo] - 1), Aw);
+        // counts with this token (and its z) removed: rho = log(a_o / b_o)   (dirichlet.py:168-173)
+        double a_o = (double)((int)R.nkw[co] - 1) + aw, b_o = (double)((int)R.nk[zo] - 1) + Aw;
         __syncwarp();
         if (lane == 0) { R.nkw[co] -= 1; R.nk[zo] -= 1; R.ndk[d * L.K + zo] -= 1; }
         __syncwarp();
         int zn = lda_sample_topic(R.ndk + d * L.K, L.K, ad, r.uniform(), lane);
         int64_t cn = (int64_t)zn * L.V + w;
-        double xi = dircat_logpmf((double)R.nkw[cn], aw, (double)R.nk[zn], Aw);
-        double alpha = (rho == -INFINITY && xi == -INFINITY) ? INFINITY
-                       : (rho == INFINITY && xi == INFINITY) ? -INFINITY : xi - rho;
-        int zf = (logu < alpha) ? zn : zo;
-        if (logu < alpha) ++acc;
+        double a_n = (double)R.nkw[cn] + aw, b_n = (double)R.nk[zn] + Aw;   // xi = log(a_n / b_n)
+        // accept iff log u < xi - rho (mh.py:84-89), evaluated without logarithms or divisions as
+        // u * b_n * a_o < a_n * b_o: all four factors are finite and positive here, so the +-inf
+        // policy of mh.py:190-208 cannot trigger; every lane of the warp redundantly executes this
+        // chain, and three fp64 logs + two divisions per transition saturated the fp64 pipe.
+        bool accept = u_acc * b_n * a_o < a_n * b_o;
+        int zf = accept ? zn : zo;
+        if (accept) ++acc;
         __syncwarp();
         if (lane == 0) {
           R.z[i] = (uint8_t)zf;

@@ -38,6 +38,19 @@ def make_data(N, D):
     return np.ascontiguousarray(X), y
 
 
+def load_traffic(P, N):
+    """Measured DRAM bytes per launch of the dominant kernel (ncu --set full capture committed under
+    profiles/), scaled to this run's particle count; None if the capture does not match the workload."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_blr_mh_traffic.json")) as f:
+            t = json.load(f)
+        if int(t["observations"]) != int(N):
+            return None, None
+        return (t["dram_bytes_read"] + t["dram_bytes_write"]) * (float(P) / t["particles"]), t
+    except Exception:
+        return None, None
+
+
 def load_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -250,6 +263,7 @@ def main():
         bytes_per_tr = N * 8.0 * (1.0 + a_rate) + 16.0
         launch_s = ms * 1e-3 / args.steps
         achieved = bytes_per_tr * P * T / launch_s / 1e9
+        traffic, tinfo = load_traffic(P, N)
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -264,11 +278,17 @@ def main():
             "gpu_launches": args.steps,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "kernel": "blr_mh_kernel<true>",
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "kernel": "blr_mh_kernel<SMEM=true, 256 threads, 4 chains, 2 CTAs/SM>",
+                         "algorithmic_bytes_per_launch": bytes_per_tr * P * T,
+                         "pipes_from_ncu": None if tinfo is None else {
+                             "fp64_pipe_pct": tinfo["fp64_pipe_pct"], "issue_active_pct": tinfo["issue_active_pct"],
+                             "lsu_writeback_pct": tinfo["lsu_writeback_pct"]},
                          "note": "algorithmic bytes per SURVEY 8(d) D4 = N*8*(1+a)+16 per particle-transition; "
                                  "the kernel keeps the logit row in shared memory for all transitions of a launch, so "
-                                 "real DRAM traffic is ~2*8N B per particle per launch and the kernel is fp64-ALU bound"},
+                                 "real DRAM traffic (`traffic`, from the committed ncu capture) is 2*8N B per particle per LAUNCH, "
+                                 "~1/200 of the algorithmic figure; the binding resources are the fp64 pipe, the LSU "
+                                 "return path and issue slots (profiles/r1_blr_mh_v2_ncu.md)"},
         }
         if not args.no_cpu_baseline and world == 1:
             cb, _ = cpu_baseline(X, y, D, N, T)

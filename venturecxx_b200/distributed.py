@@ -227,7 +227,9 @@ class ShardedTraceSet(object):
     Wraps this rank's B200TraceSet; per-particle operations are forwarded
     unchanged, resample and subsampled_mh add the collectives."""
 
-    def __init__(self, model, particles_per_rank, seed=1, device=None, group=None):
+    def __init__(self, model, particles_per_rank, seed=1, device=None, group=None, replicate_particles=False):
+        """replicate_particles=True: every rank holds the SAME particles (global indices
+        0..P-1) -- the layout of observation-sharded subsampled_mh."""
         import torch
         import torch.distributed as dist
         from .trace_set import B200TraceSet
@@ -236,10 +238,11 @@ class ShardedTraceSet(object):
         if device is None:
             device = torch.cuda.current_device()
         self.seed = int(seed)
+        self.replicated = bool(replicate_particles)
         self.local = B200TraceSet(model, particles_per_rank, seed=seed, device=device,
-                                  particle_base=self.rank * particles_per_rank)
+                                  particle_base=0 if self.replicated else self.rank * particles_per_rank)
         self.shard = CudaShard(self.local)
-        self.n_particles = self.world * particles_per_rank
+        self.n_particles = particles_per_rank if self.replicated else self.world * particles_per_rank
 
     def __getattr__(self, name):       # per-particle operations: no communication
         return getattr(self.local, name)

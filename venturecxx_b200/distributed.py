@@ -123,8 +123,14 @@ class CudaShard(object):
         _lib.call("vk_state_row_bytes", self.ts._h, ctypes.byref(n))
         return n.value
 
+    def _order(self):
+        # tensors handed to the library may have been produced by torch / NCCL work that is still
+        # in flight on torch's current stream; the library runs on the handle's stream
+        self.torch.cuda.current_stream().synchronize()
+
     def pack(self, particles):
         from . import _lib
+        self._order()
         n = particles.numel()
         out = self.torch.empty((n, self.row_bytes()), dtype=self.torch.uint8, device=self.device)
         if n:
@@ -133,6 +139,7 @@ class CudaShard(object):
 
     def unpack(self, slots, packed):
         from . import _lib
+        self._order()
         n = slots.numel()
         if n:
             _lib.call("vk_unpack_state", self.ts._h, slots.contiguous().data_ptr(), n, packed.contiguous().data_ptr())
@@ -142,37 +149,46 @@ class CudaShard(object):
         _lib.call("vk_fill_log_weights", self.ts._h, float(v))
 
     def incorporate(self):
-        return self.ts.incorporate()
+        return self.ts.incorporate(return_increments=False)
 
     def tensor(self, values, dtype):
         return self.torch.tensor(values, dtype=dtype, device=self.device)
 
 
-def _all_to_all_rows(torch, dist, rows, send_counts, group=None):
+def _all_to_all_rows(torch, dist, rows, send_counts, group=None, recv_counts=None):
     """rows: (n, width) tensor whose first axis is grouped by destination rank with
-    send_counts[r] rows for rank r.  Returns the rows received, grouped by source."""
+    send_counts[r] rows for rank r.  Returns the rows received, grouped by source.
+    recv_counts, when the caller can derive them (systematic resampling), saves the
+    count exchange and its host round trip."""
     world = dist.get_world_size(group)
-    sc = torch.tensor(send_counts, dtype=torch.int64, device=rows.device)
-    rc = torch.empty(world, dtype=torch.int64, device=rows.device)
     if dist.get_backend(group) == "nccl":
-        dist.all_to_all_single(rc, sc, group=group)
-        recv_counts = rc.tolist()
+        if recv_counts is None:
+            sc = torch.tensor(send_counts, dtype=torch.int64, device=rows.device)
+            rc = torch.empty(world, dtype=torch.int64, device=rows.device)
+            dist.all_to_all_single(rc, sc, group=group)
+            recv_counts = rc.tolist()
         out = torch.empty((sum(recv_counts),) + tuple(rows.shape[1:]), dtype=rows.dtype, device=rows.device)
-        dist.all_to_all_single(out, rows.contiguous(), output_split_sizes=recv_counts,
+        dist.all_to_all_single(out, rows.contiguous(), output_split_sizes=list(recv_counts),
                                input_split_sizes=list(send_counts), group=group)
-        return out, recv_counts
+        return out, list(recv_counts)
     # gloo (CPU tests): gather everything, keep what is addressed to this rank
     rank = dist.get_rank(group)
     gathered = [None] * world
     dist.all_gather_object(gathered, (list(send_counts), rows.cpu().numpy()), group=group)
-    parts, recv_counts = [], []
+    parts, got = [], []
     for src in range(world):
         counts, data = gathered[src]
         lo = sum(counts[:rank])
         parts.append(data[lo:lo + counts[rank]])
-        recv_counts.append(counts[rank])
+        got.append(counts[rank])
+    if recv_counts is not None:
+        assert list(recv_counts) == got, "derived receive counts disagree with the senders"
     out = torch.from_numpy(np.concatenate(parts, axis=0)) if parts else rows[:0]
-    return out.to(rows.device), recv_counts
+    return out.to(rows.device), got
+
+
+def _overlap(lo, hi, a, b):
+    return max(0, min(hi, b) - max(lo, a))
 
 
 def sharded_resample(shard, seed, step, mode="systematic", group=None):
@@ -192,30 +208,41 @@ def sharded_resample(shard, seed, step, mode="systematic", group=None):
     # 2. fixed-point masses relative to the global max
     mass, sumexp = shard.build_cdf(gmax, frac_bits_for(P_total))
     mine = shard.tensor([float(mass >> 32), float(mass & MASK32), sumexp], torch.float64)   # exact: 2 x 32-bit halves
-    allv = [torch.empty_like(mine) for _ in range(world)]
-    dist.all_gather(allv, mine, group=group)
-    masses = [(int(v[0].item()) << 32) | int(v[1].item()) for v in allv]
-    lse = lse_from_parts(gmax, [float(v[2].item()) for v in allv])
-    offset, total = sum(masses[:rank]), sum(masses)
-    # 3. children whose threshold lies in this shard's interval
+    allv = torch.empty(world * 3, dtype=torch.float64, device=mine.device)
+    dist.all_gather_into_tensor(allv, mine, group=group)
+    allh = allv.cpu().numpy().reshape(world, 3)                  # one host round trip for all scalars
+    masses = [(int(allh[r, 0]) << 32) | int(allh[r, 1]) for r in range(world)]
+    lse = lse_from_parts(gmax, [float(allh[r, 2]) for r in range(world)])
+    offsets = [sum(masses[:r]) for r in range(world)]
+    offset, total = offsets[rank], sum(masses)
     if sys_mode:
+        # 3. every rank derives EVERY rank's contiguous child range from the gathered masses, so the
+        #    all-to-all split sizes need no exchange; children arrive ordered by k, i.e. in slot order
         u = global_uniform(seed, step)
-        k_lo, k_hi = systematic_child_range(offset, masses[rank], total, P_total, u)
+        ranges = [systematic_child_range(offsets[r], masses[r], total, P_total, u) for r in range(world)]
+        k_lo, k_hi = ranges[rank]
         anc = shard.ancestors(offset, total, P_total, k_lo, k_hi - k_lo, 1, step)
-        ks = torch.arange(k_lo, k_hi, dtype=torch.int64, device=anc.device)
+        send_counts = [_overlap(k_lo, k_hi, d * P_local, (d + 1) * P_local) for d in range(world)]
+        recv_counts = [_overlap(ranges[r][0], ranges[r][1], rank * P_local, (rank + 1) * P_local)
+                       for r in range(world)]
+        assert sum(recv_counts) == P_local, "every child slot must be filled exactly once"
+        packed = shard.pack(anc.to(torch.int32))
+        recv_rows, _ = _all_to_all_rows(torch, dist, packed, send_counts, group, recv_counts)
+        slots = torch.arange(P_local, dtype=torch.int32, device=recv_rows.device)
+        shard.unpack(slots, recv_rows)
     else:
         anc_all = shard.ancestors(offset, total, P_total, 0, P_total, 0, step)
         ks = torch.nonzero(anc_all >= 0).flatten()
         anc = anc_all[ks]
-    # 4. route: child k lives on rank k // P_local, slot k % P_local (ks ascending => grouped by destination)
-    dest = torch.div(ks, P_local, rounding_mode="floor")
-    send_counts = torch.bincount(dest, minlength=world).tolist() if ks.numel() else [0] * world
-    packed = shard.pack(anc.to(torch.int32))
-    slots = (ks - dest * P_local).to(torch.int32).reshape(-1, 1)
-    recv_rows, _ = _all_to_all_rows(torch, dist, packed, send_counts, group)
-    recv_slots, _ = _all_to_all_rows(torch, dist, slots, send_counts, group)
-    assert recv_slots.shape[0] == P_local, "every child slot must be filled exactly once"
-    shard.unpack(recv_slots.flatten().contiguous(), recv_rows)
+        # 4. route: child k lives on rank k // P_local, slot k % P_local (ks ascending => grouped by destination)
+        dest = torch.div(ks, P_local, rounding_mode="floor")
+        send_counts = torch.bincount(dest, minlength=world).tolist() if ks.numel() else [0] * world
+        packed = shard.pack(anc.to(torch.int32))
+        slots = (ks - dest * P_local).to(torch.int32).reshape(-1, 1)
+        recv_rows, rc = _all_to_all_rows(torch, dist, packed, send_counts, group)
+        recv_slots, _ = _all_to_all_rows(torch, dist, slots, send_counts, group, rc)
+        assert recv_slots.shape[0] == P_local, "every child slot must be filled exactly once"
+        shard.unpack(recv_slots.flatten().contiguous(), recv_rows)
     # 5. even weights (utils.log_domain_even_out), then incorporate (trace_set.py:206-207)
     shard.fill_log_weights(lse - math.log(P_total))
     shard.incorporate()
@@ -241,6 +268,10 @@ class ShardedTraceSet(object):
         self.replicated = bool(replicate_particles)
         self.local = B200TraceSet(model, particles_per_rank, seed=seed, device=device,
                                   particle_base=0 if self.replicated else self.rank * particles_per_rank)
+        # one dedicated stream for torch ops, NCCL collectives (they order against torch's current
+        # stream) and the library's kernels of this particle set
+        self.stream = torch.cuda.Stream(device=device)
+        self.local.use_stream(self.stream.cuda_stream)
         self.shard = CudaShard(self.local)
         self.n_particles = particles_per_rank if self.replicated else self.world * particles_per_rank
 
@@ -251,10 +282,12 @@ class ShardedTraceSet(object):
         if P is not None and int(P) != self.n_particles:
             from .exception import VentureException
             raise VentureException("invalid_argument", "resample: P must equal the particle count")
+        import torch
         step = self.local.rng_step
         self.local.rng_step = step + 1
-        return sharded_resample(self.shard, self.seed, step,
-                                "systematic" if mode == "systematic" else "multinomial", self.group)
+        with torch.cuda.stream(self.stream):
+            return sharded_resample(self.shard, self.seed, step,
+                                    "systematic" if mode == "systematic" else "multinomial", self.group)
 
     def logsumexp(self):
         import torch

@@ -77,6 +77,16 @@ __device__ __forceinline__ int lda_sample_topic(const uint16_t *row, int K, doub
   return K - 1;
 }
 
+// same draw with this lane's count c_k already in a register (K <= 32): identical arithmetic
+__device__ __forceinline__ int lda_sample_topic_reg(int c, int K, double alpha, double u, int lane) {
+  int tot = warp_sum_i(c);
+  double t = u * ((double)tot + (double)K * alpha);
+  int incl = warp_scan_incl_i(c, lane);
+  double cum = (double)incl + (double)(lane + 1) * alpha;
+  unsigned m = __ballot_sync(0xffffffffu, (lane < K) && (t < cum));
+  return m ? __ffs(m) - 1 : K - 1;
+}
+
 // sum over tables of logDensityOfData(counts; alpha): n_tab tables of n_cell cells
 // (dirichlet.py:192-201).  totals[t] = N of table t (nullptr: derive from `fixed_tot`).
 __device__ double lda_aaa_weight(const uint16_t *counts, int n_tab, int n_cell, const uint32_t *totals,
@@ -145,21 +155,28 @@ lda_seq_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__r
 
 // K resimulation-MH transitions per particle on the staged row.
 // stage: 0 = whole row in global memory, 1 = whole row in shared memory (one warp per CTA),
-// 2 = alpha / n_k / n_dk / z in shared memory and the K x V topic-word table in global memory
-// (2 cells touched per z transition): ~6 KB per particle instead of 38 KB at C4, so every SM
-// holds tens of particles and the serial per-particle chains overlap each other's latency.
+// 2 = alpha / n_k / n_dk in shared memory, the K x V topic-word table and z in global memory
+// (their accesses of one z transition are issued together): ~2 KB per particle instead of
+// 38 KB at C4, so all particles are resident at once and the serial per-particle chains
+// overlap each other's latency.
 static const int LDA_WARPS = 4;
 __global__ void __launch_bounds__(32 * LDA_WARPS)
 lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__restrict__ doc,
               const int32_t *__restrict__ word, const int32_t *__restrict__ doclen, int n_tok,
               int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int block_mode,
-              int stage, long long *__restrict__ acc_out) {
+              int stage, int tok_shared, long long *__restrict__ acc_out) {
   extern __shared__ uint4 smem_all[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, n_w = blockDim.x >> 5;
   const int nb = 2 + n_tok;
-  const size_t z_bytes = L.row_bytes - L.off_z;
-  const size_t warp_bytes = stage == 1 ? L.row_bytes : L.off_nkw + z_bytes;
+  const size_t warp_bytes = stage == 1 ? L.row_bytes : L.off_nkw;   // stage 2: alpha, n_k, n_dk only
   uint4 *smem_u4 = smem_all + (size_t)wid * (warp_bytes / 16);
+  // CTA-shared packed (doc << 16 | word) copy of the corpus, after the per-warp sections
+  uint32_t *tok_sh = nullptr;
+  if (tok_shared) {
+    tok_sh = reinterpret_cast<uint32_t *>(smem_all + (size_t)n_w * (warp_bytes / 16));
+    for (int i = threadIdx.x; i < n_tok; i += blockDim.x) tok_sh[i] = ((uint32_t)doc[i] << 16) | (uint32_t)word[i];
+    __syncthreads();
+  }
   for (int64_t p = (int64_t)blockIdx.x * n_w + wid; p < P; p += (int64_t)gridDim.x * n_w) {
     unsigned char *grow = rows + p * L.row_bytes;
     unsigned char *base = grow;
@@ -171,12 +188,9 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
     } else if (stage == 2) {
       const uint4 *src = (const uint4 *)grow;
       for (size_t i = lane; i < L.off_nkw / 16; i += 32) smem_u4[i] = src[i];
-      const uint4 *zsrc = (const uint4 *)(grow + L.off_z);
-      for (size_t i = lane; i < z_bytes / 16; i += 32) smem_u4[L.off_nkw / 16 + i] = zsrc[i];
       __syncwarp();
     }
-    LDARow R = stage == 2 ? LDARow((unsigned char *)smem_u4, (uint16_t *)(grow + L.off_nkw),
-                                   (unsigned char *)smem_u4 + L.off_nkw, L)
+    LDARow R = stage == 2 ? LDARow((unsigned char *)smem_u4, (uint16_t *)(grow + L.off_nkw), grow + L.off_z, L)
                           : LDARow(base, L);
     long long acc = 0;
     for (int k = 0; k < n_steps; ++k) {
@@ -204,6 +218,40 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
                        : (rho == INFINITY && xi == INFINITY) ? -INFINITY : xi - rho;
         if (log(u_acc) < alpha) { if (lane == 0) R.alpha[b] = a_new; ++acc; }
         __syncwarp();
+      } else if (tok_sh != nullptr && L.K <= 32) {
+        // z site, fast path: (doc, word) come from the CTA's shared copy, and every lane k < K loads
+        // ITS candidate cell n_kw[k][w] up front -- one overlapped global round trip instead of two
+        // dependent ones (old cell, then proposed cell).  Nothing is written unless the proposal is
+        // accepted AND changes the topic: "remove the token, then add it back" is done on register
+        // copies of the counts (detach.py:52-65 / regen.py:68-88 leave the tables unchanged on reject).
+        const int i = b - 2;
+        const uint32_t dw = tok_sh[i];
+        const int d = (int)(dw >> 16), w = (int)(dw & 0xffffu);
+        const int zo = R.z[i];
+        const int kk = lane < L.K ? lane : 0;
+        int cand = (int)R.nkw[(int64_t)kk * L.V + w];                  // global; one cell per lane
+        int nk_k = (int)R.nk[kk];
+        int cdk = lane < L.K ? (int)R.ndk[d * L.K + lane] : 0;
+        if (lane == zo) { cand -= 1; nk_k -= 1; cdk -= 1; }          // counts with this token removed
+        const double ad = R.alpha[0], aw = R.alpha[1];
+        const double Aw = aw * (double)L.V;
+        const int zn = lda_sample_topic_reg(cdk, L.K, ad, r.uniform(), lane);
+        const int c_o = __shfl_sync(0xffffffffu, cand, zo), n_o = __shfl_sync(0xffffffffu, nk_k, zo);
+        const int c_n = __shfl_sync(0xffffffffu, cand, zn), n_n = __shfl_sync(0xffffffffu, nk_k, zn);
+        const double a_o = (double)c_o + aw, b_o = (double)n_o + Aw;   // rho = log(a_o / b_o)
+        const double a_n = (double)c_n + aw, b_n = (double)n_n + Aw;   // xi  = log(a_n / b_n)
+        const bool accept = u_acc * b_n * a_o < a_n * b_o;             // log u < xi - rho, see below
+        if (accept) ++acc;
+        if (accept && zn != zo) {
+          if (lane == 0) {
+            R.z[i] = (uint8_t)zn;
+            R.nkw[(int64_t)zo * L.V + w] = (uint16_t)c_o;              // c_o is already "minus this token"
+            R.nkw[(int64_t)zn * L.V + w] = (uint16_t)(c_n + 1);
+            R.nk[zo] -= 1; R.nk[zn] += 1;
+            R.ndk[d * L.K + zo] -= 1; R.ndk[d * L.K + zn] += 1;
+          }
+          __syncwarp();
+        }
       } else {
         int i = b - 2;
         int d = doc[i], w = word[i];
@@ -241,8 +289,6 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
     } else if (stage == 2) {
       uint4 *dst = (uint4 *)grow;
       for (size_t i = lane; i < L.off_nkw / 16; i += 32) dst[i] = smem_u4[i];
-      uint4 *zdst = (uint4 *)(grow + L.off_z);
-      for (size_t i = lane; i < z_bytes / 16; i += 32) zdst[i] = smem_u4[L.off_nkw / 16 + i];
       __syncwarp();
     }
     if (acc_out && lane == 0) acc_out[p] = acc;
@@ -378,13 +424,17 @@ struct LDAModel : Model {
       uint32_t step0 = h->next_step((uint32_t)n_steps);
       // small sections + z per warp in shared memory, K x V table in global memory (stage 2);
       // if even that does not fit, everything stays in global memory (stage 0)
-      size_t small = L.off_nkw + (L.row_bytes - L.off_z);
+      size_t small = L.off_nkw;
       static int forced = getenv("VK_LDA_STAGE") ? atoi(getenv("VK_LDA_STAGE")) : -1;
       int stage = (small * LDA_WARPS <= (size_t)smem_limit) ? 2 : 0;
       int warps = LDA_WARPS;
       if (forced == 1 && L.row_bytes <= (size_t)smem_limit) { stage = 1; warps = 1; }
       if (forced == 0) stage = 0;
       size_t sm = stage == 2 ? small * warps : (stage == 1 ? L.row_bytes : 0);
+      // the fast z path keeps a packed (doc, word) copy of the corpus per CTA
+      int tok_shared = (stage == 2 && L.K <= 32 && L.n_docs <= 65535 && L.V <= 65536 &&
+                        sm + (size_t)n_tok * 4 + 16 <= (size_t)smem_limit / 2) ? 1 : 0;
+      if (tok_shared) sm += ((size_t)n_tok * 4 + 15) & ~(size_t)15;
       int per_sm = sm ? (int)((size_t)(227 * 1024) / (sm + 1024)) : 16;
       if (per_sm < 1) per_sm = 1;
       if (per_sm * warps > 64) per_sm = 64 / warps;
@@ -392,7 +442,7 @@ struct LDAModel : Model {
       int64_t cap = (int64_t)h->sm_count * per_sm;
       int grid = (int)(need_ctas < cap ? need_ctas : cap);
       lda_mh_kernel<<<grid, 32 * warps, sm, h->stream>>>(rows, L, doc.p, word.p, doclen.p, n_tok, h->P, h->p_base,
-                                                         h->seed, step0, n_steps, block, stage, acc_dev);
+                                                         h->seed, step0, n_steps, block, stage, tok_shared, acc_dev);
       VK_CUDA(cudaGetLastError());
     } else if (acc_dev) {
       VK_CUDA(cudaMemsetAsync(acc_dev, 0, (size_t)h->P * sizeof(long long), h->stream));

@@ -200,6 +200,34 @@ static void dirichlet_sim(orc_stream *r, const double *alpha, int n, double *out
   for (int i = 0; i < n; ++i) out[i] /= s;
 }
 
+/* Test hook for tests/golden/make_lite_chains.py: ONE draw by this oracle's own samplers from stream
+ * (seed, particle, step) starting at draw index *d; *d is advanced past what the draw consumed.  The
+ * fixture generator installs these draws behind the reference Lite trace's np_rng / py_rng so that Lite's
+ * scaffold / detach / regen / accept code runs on the very uniforms this oracle (and the kernels) use.
+ * kind: 0 uniform, 1 normal(mu, sigma), 2 gamma(shape, rate), 3 categorical(ps[n]) -> index,
+ *       4 sym-dir-cat over params = {alpha, c_0..c_{n-2}} -> index (dirichlet.py:164-166), 5 beta(a, b). */
+static int lda_sample_topic(const int32_t *row, int K, double alpha, double u);
+double orc_draw(int kind, const double *params, int n, uint64_t seed, uint64_t particle, uint32_t step, uint32_t *d) {
+  orc_stream r; st_init(&r, seed, particle, step); st_seek(&r, *d);
+  double v = 0;
+  switch (kind) {
+    case 0: v = st_uniform(&r); break;
+    case 1: v = normal_sim(&r, params[0], params[1]); break;
+    case 2: v = gamma_sim(&r, params[0], params[1]); break;
+    case 3: v = (double)categorical_sim(&r, params, n); break;
+    case 4: {
+      int32_t row[4096]; int K = n - 1;
+      for (int k = 0; k < K; ++k) row[k] = (int32_t)params[1 + k];
+      v = (double)lda_sample_topic(row, K, params[0], st_uniform(&r));
+      break;
+    }
+    case 5: v = beta_sim(&r, params[0], params[1]); break;
+    default: v = NAN;
+  }
+  *d = r.d;
+  return v;
+}
+
 enum { SP_NORMAL = 1, SP_GAMMA, SP_BETA, SP_FLIP, SP_LOG_FLIP, SP_LOG_ODDS_FLIP, SP_CATEGORICAL,
        SP_LOG_CATEGORICAL, SP_DIRICHLET, SP_SYM_DIRICHLET, SP_SYM_DIR_CAT, SP_BETA_BERNOULLI };
 

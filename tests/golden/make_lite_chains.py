@@ -1,0 +1,252 @@
+#!/usr/bin/env python
+"""Generates tests/golden/lite_chains.json by RUNNING THE REFERENCE'S LITE BACKEND (its own
+Trace / constructScaffold / detachAndExtract / regenAndAttach / mixMH / MHOperator /
+EnumerativeGibbsOperator / subsampledMixMH code) in this container.
+
+  python oracle/lite_py3/build_lite_py3.py      # py3 rendering of backend/lite -> oracle/_ref/ (git-ignored)
+  python tests/golden/make_lite_chains.py       # runs Lite, writes the fixture
+
+How the chains are made comparable.  Lite draws from numpy's MT19937 and Python's `random`; the
+kernels (and oracle/oracle.c) draw from Philox streams addressed by (seed, particle, step, draw).
+Sampler streams cannot agree, so each Lite trace gets stand-in `np_rng` / `py_rng` objects whose
+methods return the draw the ORACLE's sampler makes at the matching position of the matching Philox
+stream (oracle.draw -> orc_draw).  Everything else -- which nodes are in the DRG, which absorb, the
+order of detach and regen, every logDensity, (un)incorporate on the count tables, rho, xi, the
++-inf policy, the accept test, constrain / makeConsistent, likelihood_weight -- is the reference's
+code, unmodified apart from the syntactic py3 rendering.  The committed fixture holds only inputs
+and the states / weights Lite ended with; tests/test_oracle_lite_chains.py replays the same
+(seed, particle, step) in oracle.c and demands equality (1e-12 relative for reals, exact for
+discrete state), and tests/test_gpu_lite_chains.py does the same through the C ABI on the GPU.
+
+Draw layout of one MH transition at `step` (the oracle's convention, see oracle.c):
+  draw 0      block choice u_sel: block index = min(int(u_sel * n_blocks), n_blocks-1) in the model's
+              canonical site order (Lite's SamplableMap order is relabelled to that order here --
+              a uniform choice does not depend on labels)
+  draw 1      accept uniform (mh.py:85)
+  draw 2...   the proposal's value draws, in regen order
+likelihood_weight / prior resimulation at `step`: value draws from draw 0 in regen order.
+"""
+import json
+import math
+import os
+import sys
+import warnings
+
+warnings.simplefilter("ignore")
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))
+
+import numpy as np  # noqa: E402
+
+import oracle  # noqa: E402
+import venture.lite.value as vv  # noqa: E402
+import venture.value.dicts as vd  # noqa: E402
+from venture.lite.trace import Trace  # noqa: E402
+
+
+# ------------------------------------------------------------------ expressions
+def sx(e):
+    """Nested python lists / str / numbers -> the stack-dict expression Trace.eval takes
+    (lite/trace.py:397-401), with the two macros the sivm would have expanded
+    (python/lib/sivm/macro.py:293-311): lambda -> make_csp, if -> biplex."""
+    if isinstance(e, str):
+        return vd.symbol(e)
+    if isinstance(e, bool):
+        return vd.boolean(e)
+    if isinstance(e, int):
+        return vd.integer(e) if False else vd.number(e)
+    if isinstance(e, float):
+        return vd.number(e)
+    if isinstance(e, dict):
+        return e
+    assert isinstance(e, list)
+    if e and e[0] == "lambda":
+        return [vd.symbol("make_csp"), vd.quote([sx(p) for p in e[1]]), vd.quote(sx(e[2]))]
+    if e and e[0] == "if":
+        return [[vd.symbol("biplex"), sx(e[1]), sx(["lambda", [], e[2]]), sx(["lambda", [], e[3]])]]
+    if e and e[0] == "quote":
+        return vd.quote(sx(e[1]))
+    return [sx(x) for x in e]
+
+
+class Model(object):
+    """One Lite trace with directive bookkeeping (what engine/trace.py:53-126 does around it)."""
+
+    def __init__(self, seed=1):
+        self.t = Trace(seed)
+        self.did = 0
+
+    def assume(self, name, exp):
+        self.did += 1
+        self.t.eval(self.did, sx(exp))
+        self.t.bindInGlobalEnv(name, self.did)
+        return self.did
+
+    def observe(self, exp, value):
+        self.did += 1
+        self.t.eval(self.did, sx(exp))
+        self.t.observe(self.did, value)
+        return self.did
+
+    def value(self, did):
+        return self.t.extractValue(did)["value"]
+
+
+# ------------------------------------------------------------------ RNG stand-ins
+class Tape(object):
+    """Cursor into Philox stream (seed, particle, step) shared by the two stand-ins."""
+
+    def __init__(self, seed, particle):
+        self.seed, self.particle = seed, particle
+        self.step, self.d = 0, 0
+        self.site_of = None     # block key -> canonical site index
+        self.log = []
+
+    def begin(self, step, d0):
+        self.step, self.d = step, d0
+
+    def at(self, d):
+        return oracle.uniforms(self.seed, self.particle, self.step, d + 1)[d]
+
+    def draw(self, kind, params):
+        v, self.d = oracle.draw(kind, params, self.seed, self.particle, self.step, self.d)
+        return v
+
+
+class PyRng(object):
+    """Stands in for trace.py_rng (random.Random): block choice and the accept uniform."""
+
+    def __init__(self, tape):
+        self.tape = tape
+
+    def sample(self, population, k):          # smap.py:56 <- trace.py:320 sampleBlock
+        assert k == 1
+        nb = len(population)
+        b = min(int(self.tape.at(0) * nb), nb - 1)
+        for entry in population:
+            if self.tape.site_of(entry[0]) == b:
+                return [entry]
+        raise KeyError(b)
+
+    def random(self):                          # mh.py:85
+        return self.tape.at(1)
+
+
+class NpRng(object):
+    """Stands in for trace.np_rng (numpy RandomState): the value draws of regen."""
+
+    def __init__(self, tape):
+        self.tape = tape
+
+    def normal(self, loc=0.0, scale=1.0):      # continuous.py:317
+        return self.tape.draw(1, [loc, scale])
+
+    def gamma(self, shape, scale=1.0):         # continuous.py:1164 (scale = 1/rate)
+        return self.tape.draw(2, [shape, 1.0 / scale])
+
+    def multinomial(self, n, ps):              # utils.py:104 simulateCategorical
+        assert n == 1
+        k = int(self.tape.draw(3, list(ps)))
+        out = np.zeros(len(ps), dtype=int)
+        out[k] = 1
+        return out
+
+    def random_sample(self):
+        return self.tape.draw(0, [0.0])
+
+    def uniform(self, lo=0.0, hi=1.0):
+        return lo + (hi - lo) * self.tape.draw(0, [0.0])
+
+
+def install(model, seed, particle):
+    tape = Tape(seed, particle)
+    model.t.py_rng = PyRng(tape)
+    model.t.np_rng = NpRng(tape)
+    model.tape = tape
+    return tape
+
+
+def infer_exp(op, scope, block, *extra):
+    def lift(x):
+        if isinstance(x, bool):
+            return vv.VentureBool(x)
+        if isinstance(x, (int, float)):
+            return vv.VentureNumber(x)
+        return vv.VentureSymbol(x)
+    return [op, lift(scope), lift(block)] + [lift(x) for x in extra]
+
+
+def mh_steps(model, step0, n_steps, block="one", op="resimulation_mh", extra=()):
+    """n_steps transitions, one primitive_infer call each (transitions = 1) so the stand-ins can be
+    pointed at Philox step step0 + k; returns Lite's own return values (mean node counts)."""
+    out = []
+    for k in range(n_steps):
+        model.tape.begin(step0 + k, 2)
+        out.append(model.t.primitive_infer(infer_exp(op, "default", block, *(tuple(extra) + (1,)))))
+    return out
+
+
+def fl(x):
+    x = float(x)
+    if math.isnan(x):
+        return "nan"
+    if math.isinf(x):
+        return "inf" if x > 0 else "-inf"
+    return x
+
+
+# ------------------------------------------------------------------ C1 normal-normal
+def chain_c1(seed=11, P=6, K=12):
+    mu0, s0, s = 0.5, 2.0, 1.5
+    ys = [2.0, 1.0, -0.5]
+    out = {"seed": seed, "P": P, "K": K, "mu0": mu0, "s0": s0, "s": s, "y": ys,
+           "steps": {"likelihood_weight": 3, "mh": 10}, "particles": []}
+    for p in range(P):
+        m = Model()
+        x = m.assume("x", ["normal", mu0, s0])
+        for y in ys[:2]:
+            m.observe(["normal", "x", s], vd.number(y))
+        m.t.makeConsistent()
+        install(m, seed, p)
+        m.tape.site_of = lambda key: 0
+        rec = {}
+        m.tape.begin(3, 0)
+        rec["lw"] = fl(m.t.likelihood_weight())                       # lite/trace.py:522-530
+        rec["x_lw"] = fl(m.value(x))
+        m.observe(["normal", "x", s], vd.number(ys[2]))
+        rec["incr"] = fl(m.t.makeConsistent())                        # lite/trace.py:422-448
+        rec["nodes"] = mh_steps(m, 10, K)
+        rec["x_mh"] = fl(m.value(x))
+        rec["ll_at"] = fl(m.t.log_likelihood_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
+        rec["lj_at"] = fl(m.t.log_joint_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
+        out["particles"].append(rec)
+    return out
+
+
+CHAINS = [("c1", chain_c1)]
+
+
+def main():
+    only = sys.argv[1:]
+    path = os.path.join(HERE, "lite_chains.json")
+    fixture = {}
+    if only and os.path.exists(path):
+        with open(path) as f:
+            fixture = json.load(f)
+    for name, fn in CHAINS:
+        if only and name not in only:
+            continue
+        fixture[name] = fn()
+        print("ran", name)
+    fixture["_source"] = ("reference Lite backend (backend/lite/*.py, py3 rendering by "
+                          "oracle/lite_py3/build_lite_py3.py) run by tests/golden/make_lite_chains.py; "
+                          "numpy %s" % np.__version__)
+    with open(path, "w") as f:
+        json.dump(fixture, f, indent=1, sort_keys=True)
+    print("wrote", path)
+
+
+if __name__ == "__main__":
+    main()

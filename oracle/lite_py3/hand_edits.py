@@ -11,6 +11,10 @@ HAND = {
         ("address=address), \\\n        None, info[2]", "address=address).with_traceback(info[2])"),
         ("cause=err), None, info[2]", "cause=err).with_traceback(info[2])"),
     ],
+    # py2 int / int is floor division (scaffolder_loop, dispatch.py:127; ct is a sum of ints)
+    "lite/infer/dispatch.py": [
+        ("return ct/len(scaffolders)", "return ct//len(scaffolders)"),
+    ],
     # print statement on a def line
     "engine/inference.py": [
         ("def printf(self, dataset): print dataset.asPandas()", "def printf(self, dataset): print(dataset.asPandas())"),

@@ -225,7 +225,128 @@ def chain_c1(seed=11, P=6, K=12):
     return out
 
 
-CHAINS = [("c1", chain_c1)]
+# ------------------------------------------------------------------ C2 logistic regression
+def blr_data(N, D, seed):
+    X = np.random.default_rng(seed).normal(size=(N, D))
+    w_true = np.random.default_rng(seed + 1).normal(size=D)
+    pr = 1 / (1 + np.exp(-X @ w_true))
+    y = (np.random.default_rng(seed + 2).random(N) < pr).astype(np.uint8)
+    return X, y
+
+
+def blr_model(D, X, y, n_first):
+    m = Model()
+    # the weights are also tagged into scope `wts`, block j, so that `each` and fixed-block programs
+    # exist (the default scope admits only one/all/none/ordered, infer/mh.py:119-123)
+    wd = [m.assume("w_%d" % j, ["tag", ["quote", "wts"], j, ["normal", 0.0, 1.0]]) for j in range(D)]
+    m.assume("w", ["array"] + ["w_%d" % j for j in range(D)])
+    for i in range(n_first):
+        m.observe(["log_odds_flip", ["vector_dot", "w", ["array"] + [float(v) for v in X[i]]]], vd.boolean(bool(y[i])))
+    return m, wd
+
+
+def chain_c2(seed=17, P=4, D=5, N=14, K=24):
+    X, y = blr_data(N, D, 40)
+    h = N // 2
+    out = {"seed": seed, "P": P, "D": D, "N": N, "K": K, "data_seed": 40, "X": X.tolist(), "y": y.tolist(),
+           "steps": {"likelihood_weight": 5, "mh_one": 20, "mh_each": 100, "mh_all": 200}, "particles": []}
+    for p in range(P):
+        m, wd = blr_model(D, X, y, h)
+        m.t.makeConsistent()
+        install(m, seed, p)
+        nodes = [list(m.t.scopes[vv.VentureSymbol("wts")][vv.VentureNumber(j)])[0] for j in range(D)]
+        m.tape.site_of = lambda key: [i for i, n in enumerate(nodes) if n is key][0]
+        rec = {}
+        m.tape.begin(5, 0)
+        rec["lw"] = fl(m.t.likelihood_weight())
+        rec["w_lw"] = [fl(m.value(d)) for d in wd]
+        for i in range(h, N):
+            m.observe(["log_odds_flip", ["vector_dot", "w", ["array"] + [float(v) for v in X[i]]]], vd.boolean(bool(y[i])))
+        rec["incr"] = fl(m.t.makeConsistent())
+        rec["nodes_one"] = mh_steps(m, 20, K)
+        rec["w_one"] = [fl(m.value(d)) for d in wd]
+        rec["ll_one"] = fl(m.t.log_likelihood_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
+        # (resimulation_mh wts each 2) = every block in order, twice (dispatch.py:86-128), issued block by
+        # block so that each transition sits on its own Philox step
+        rec["nodes_each"] = []
+        for k in range(2 * D):
+            m.tape.begin(100 + k, 2)
+            rec["nodes_each"].append(m.t.primitive_infer(infer_exp("resimulation_mh", "wts", k % D, 1)))
+        rec["w_each"] = [fl(m.value(d)) for d in wd]
+        rec["nodes_all"] = mh_steps(m, 200, 4, block="all")
+        rec["w_all"] = [fl(m.value(d)) for d in wd]
+        rec["lj_all"] = fl(m.t.log_joint_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
+        out["particles"].append(rec)
+    # transloop's return value for the model exactly as SURVEY 8(d) D2 writes it (no tag wrapper)
+    m = Model()
+    wd = [m.assume("w_%d" % j, ["normal", 0.0, 1.0]) for j in range(D)]
+    m.assume("w", ["array"] + ["w_%d" % j for j in range(D)])
+    for i in range(N):
+        m.observe(["log_odds_flip", ["vector_dot", "w", ["array"] + [float(v) for v in X[i]]]], vd.boolean(bool(y[i])))
+    m.t.makeConsistent()
+    install(m, seed, 0)
+    nodes = [m.t.families[d] for d in wd]
+    m.tape.site_of = lambda key: [i for i, n in enumerate(nodes) if n is key][0]
+    out["untagged_nodes_one"] = mh_steps(m, 900, 2)
+    out["untagged_nodes_all"] = mh_steps(m, 910, 2, block="all")
+    return out
+
+
+# ------------------------------------------------------------------ C3 HMM (examples/hmm.vnt:31-66)
+def hmm_model():
+    t = .33333333333333333
+    m = Model()
+    rows = [[t, t, t, 0, 0], [0, t, t, t, 0], [0, 0, t, t, t], [t, 0, 0, t, t], [t, t, 0, 0, t], [t, t, t, 0, 0]]
+    erows = [[.6 if i == j else .1 for j in range(5)] for i in range(5)]
+    m.assume("transition_matrix", ["array"] + [["simplex"] + [float(x) for x in r] for r in rows])
+    m.assume("emission_matrix", ["array"] + [["simplex"] + r for r in erows])
+    objs = ["array", 1, 2, 3, 4, 5]
+    m.assume("transition", ["lambda", ["state"], ["categorical", ["lookup", "transition_matrix", ["sub", "state", 1]], objs]])
+    m.assume("emission", ["lambda", ["state"], ["categorical", ["lookup", "emission_matrix", ["sub", "state", 1]], objs]])
+    m.assume("state", ["mem", ["lambda", ["t"], ["tag", ["quote", "seq"], "t",
+                                                  ["if", ["lte", "t", 1], 1, ["transition", ["state", ["sub", "t", 1]]]]]]])
+    return m, rows, erows
+
+
+def chain_c3(seed=23, P=6, K=40):
+    data = [3, 2, 3, 5, 5, 1, 2, 5, 2, 4, 4, 1, 2, 2, 1, 4, 2, 3, 5, 1]
+    T = len(data)
+    out = {"seed": seed, "P": P, "K": K, "T": T, "data": data, "steps": {"filter": 1, "mh_one": 50, "mh_each": 200},
+           "particles": []}
+    for p in range(P):
+        m, rows, erows = hmm_model()
+        install(m, seed, p)
+        rec = {"incr": []}
+        sd = []
+        for t in range(1, T + 1):
+            m.tape.begin(1 + (t - 1), 0)     # evaluating state(t) simulates the transition at draw 0 (regen.py:255-285)
+            m.observe(["emission", ["state", t]], vd.number(data[t - 1]))
+            rec["incr"].append(fl(m.t.makeConsistent()))
+        nodes = []
+        for t in range(2, T + 1):
+            pn = list(m.t.getNodesInBlock(vv.VentureSymbol("seq"), vv.VentureNumber(t)))
+            assert len(pn) == 1
+            nodes.append(pn[0])
+
+        def hist():
+            return [int(m.t.valueAt(n).getNumber()) for n in nodes]
+        rec["hist_filter"] = [1] + hist()
+        m.tape.site_of = lambda key: [i for i, n in enumerate(nodes) if n is key][0]
+        rec["nodes_one"] = mh_steps(m, 50, K)
+        rec["hist_one"] = [1] + hist()
+        rec["nodes_each"] = []
+        for k in range(2 * (T - 1)):
+            m.tape.begin(200 + k, 2)
+            rec["nodes_each"].append(m.t.primitive_infer(infer_exp("resimulation_mh", "seq", 2 + k % (T - 1), 1)))
+        rec["hist_each"] = [1] + hist()
+        rec["ll_at"] = fl(m.t.log_likelihood_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
+        rec["lj_at"] = fl(m.t.log_joint_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
+        out["particles"].append(rec)
+    out["trans"], out["emit"] = rows, erows
+    return out
+
+
+CHAINS = [("c1", chain_c1), ("c2", chain_c2), ("c3", chain_c3)]
 
 
 def main():

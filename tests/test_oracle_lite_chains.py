@@ -52,3 +52,80 @@ def test_c1_normal_normal_chain():
     # transloop's return value (dispatch.py:109-120): |regenCounts| = x + one absorbing node per observation
     for r in recs:
         assert r["nodes"] == [1.0 + len(y)] * K
+
+
+# ------------------------------------------------------------------ C2
+def _blr_mh(w, X, y, seed, step0, n, mode):
+    D, P = w.shape
+    acc, ll = np.empty(P, dtype=np.int64), np.empty(P)
+    oracle.lib().orc_blr_mh(oracle._ptr(w), oracle._ptr(X), oracle._ptr(y), oracle.I32(D), oracle.I64(X.shape[0]),
+                            oracle.I64(P), oracle.I64(0), oracle.F64(0.0), oracle.F64(1.0), oracle.U64(seed),
+                            oracle.U32(step0), oracle.I32(n), oracle.I32(mode), oracle._ptr(acc), oracle._ptr(ll))
+    return acc, ll
+
+
+def _blr_ll(w, X, y, i0, i1):
+    D, P = w.shape
+    out = np.empty(P)
+    oracle.lib().orc_blr_log_likelihood(oracle._ptr(w), oracle._ptr(X), oracle._ptr(y), oracle.I32(D), oracle.I64(i0),
+                                        oracle.I64(i1), oracle.I64(P), oracle._ptr(out))
+    return out
+
+
+def wcol(recs, key):
+    return np.ascontiguousarray(np.array([unj(r[key]) for r in recs], dtype=np.float64).T)   # [D][P]
+
+
+def test_c2_logistic_regression_chain():
+    c = CH["c2"]
+    P, D, N, K, seed = c["P"], c["D"], c["N"], c["K"], c["seed"]
+    X = np.ascontiguousarray(c["X"], dtype=np.float64)
+    y = np.ascontiguousarray(c["y"], dtype=np.uint8)
+    recs = c["particles"]
+    h = N // 2
+    w = np.empty((D, P))
+    oracle.lib().orc_blr_prior(oracle._ptr(w), oracle.I32(D), oracle.I64(P), oracle.I64(0), oracle.F64(0.0),
+                               oracle.F64(1.0), oracle.U64(seed), oracle.U32(c["steps"]["likelihood_weight"]))
+    np.testing.assert_allclose(w, wcol(recs, "w_lw"), rtol=RTOL)
+    np.testing.assert_allclose(_blr_ll(w, X, y, 0, h), col(recs, "lw"), rtol=RTOL)
+    np.testing.assert_allclose(_blr_ll(w, X, y, h, N), col(recs, "incr"), rtol=RTOL)
+    acc, ll = _blr_mh(w, X, y, seed, c["steps"]["mh_one"], K, -1)
+    np.testing.assert_allclose(w, wcol(recs, "w_one"), rtol=RTOL)
+    np.testing.assert_allclose(ll, col(recs, "ll_one"), rtol=RTOL)
+    assert acc.sum() > 0 and (acc < K).any()
+    acc, _ = _blr_mh(w, X, y, seed, c["steps"]["mh_each"], 2 * D, -3)
+    np.testing.assert_allclose(w, wcol(recs, "w_each"), rtol=RTOL)
+    acc, ll = _blr_mh(w, X, y, seed, c["steps"]["mh_all"], 4, -2)
+    np.testing.assert_allclose(w, wcol(recs, "w_all"), rtol=RTOL)
+    prior = (-0.5 * np.log(2 * np.pi) - 0.5 * w * w).sum(0)
+    np.testing.assert_allclose(ll + prior, col(recs, "lj_all"), rtol=1e-11)
+    print(recs[0]["nodes_one"][0], recs[0]["nodes_each"][0], recs[0]["nodes_all"][0])
+
+
+# ------------------------------------------------------------------ C3
+def test_c3_hmm_filter_and_mh_chain():
+    from helpers import OracleHMM
+    c = CH["c3"]
+    P, K, T, seed = c["P"], c["K"], c["T"], c["seed"]
+    recs = c["particles"]
+    o = OracleHMM(c["trans"], c["emit"], 1, P, 32, seed)
+    for t in range(T):
+        incr = o.step(c["data"][t], c["steps"]["filter"] + t)
+        np.testing.assert_allclose(incr, [unj(r["incr"][t]) for r in recs], rtol=RTOL)
+    assert np.array_equal(o.hist[:, :T], np.array([r["hist_filter"] for r in recs]))
+    acc = o.mh(c["steps"]["mh_one"], K, -1)
+    assert np.array_equal(o.hist[:, :T], np.array([r["hist_one"] for r in recs]))
+    assert acc.sum() > 0 and (acc < K).any()
+    o.mh(c["steps"]["mh_each"], 2 * (T - 1), -3)
+    assert np.array_equal(o.hist[:, :T], np.array([r["hist_each"] for r in recs]))
+    # log_likelihood_at(default, all) (dispatch.py:331-346): the absorbing border of the scaffold whose
+    # principal nodes are the random choices state(2..T) -- the emission of the deterministic state(1)
+    # is NOT a child of any principal node and does not count; log_joint_at adds the transitions.
+    emit, trans = np.array(c["emit"]), np.array(c["trans"])
+    ll = np.array([sum(np.log(emit[h[t] - 1, c["data"][t] - 1]) for t in range(1, T)) for h in o.hist])
+    lp = np.array([sum(np.log(trans[h[t - 1] - 1, h[t] - 1]) for t in range(1, T)) for h in o.hist])
+    np.testing.assert_allclose(ll, col(recs, "ll_at"), rtol=1e-11)
+    np.testing.assert_allclose(ll + lp, col(recs, "lj_at"), rtol=1e-11)
+    # transloop's return value: 13 affected nodes for an interior state(t), 9 for the last one
+    for r in recs:
+        assert set(r["nodes_each"]) == {13.0, 9.0} and r["nodes_each"][T - 2] == 9.0

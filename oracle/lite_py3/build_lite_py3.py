@@ -68,7 +68,7 @@ REGEX = [
     (r"\bfunc_name\b", "__name__"),
     (r"\.next\(\)", ".__next__()"),
     (r"\b0(\d+)\b(?=[^.\dxe])", None),  # placeholder (octal) -- unused
-    (r"\blong\(", "int("),
+    (r"\blong\b", "int"),
     (r"^import __builtin__$", "import builtins as __builtin__"),
     (r"\braw_input\b", "input"),
     (r"\breduce\(", "functools_reduce("),

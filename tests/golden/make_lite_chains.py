@@ -346,7 +346,90 @@ def chain_c3(seed=23, P=6, K=40):
     return out
 
 
-CHAINS = [("c1", chain_c1), ("c2", chain_c2), ("c3", chain_c3)]
+# ------------------------------------------------------------------ C4 LDA (examples/lda.vnt:18-41)
+def lda_model(K, V, seed, particle, prior_step):
+    m = Model()
+    install(m, seed, particle)
+    m.tape.begin(prior_step, 0)       # the two gamma assumes evaluate on draws 0.. of `prior_step`, in order
+    m.assume("n_topics", K)
+    m.assume("vocab_size", V)
+    ad = m.assume("alpha_document_topic", ["gamma", 1.0, 2.0])
+    aw = m.assume("alpha_topic_word", ["gamma", 1.0, 2.0])
+    m.assume("doc", ["mem", ["lambda", ["doc_id"], ["make_sym_dir_cat", "alpha_document_topic", "n_topics"]]])
+    m.assume("topic", ["mem", ["lambda", ["topic_id"], ["make_sym_dir_cat", "alpha_topic_word", "vocab_size"]]])
+    m.assume("word", ["mem", ["lambda", ["doc_id", "pos"], [["topic", [["doc", "doc_id"]]]]]])
+    return m, ad, aw
+
+
+def patch_dircat_sampler(K, V):
+    """CDirCatOutputPSP.simulate (dirichlet.py:164-166) descends a sum tree with one uniform per level;
+    the kernels use one uniform and the inverse CDF over (alpha + counts).  Same law, different map from
+    uniforms to outcomes, so the sampler is replaced by the oracle's (orc_draw kind 4) like every other
+    sampler here.  The token application ((topic z)) is re-simulated on every regen and immediately
+    re-constrained (regen.py:276-279 then :68-88) -- a wasted draw whose value never reaches a density;
+    it returns outcome 0 without consuming the stream (the oracle has no such draw)."""
+    import venture.lite.dirichlet as dc
+    assert K != V
+
+    def sample(np_rng, alpha, counts):
+        n = len(alpha)
+        if n == V:
+            return 0
+        assert n == K
+        return int(np_rng.tape.draw(4, [alpha[0]] + [counts[i] for i in range(n)]))
+    dc.sample = sample
+
+
+def lda_corpus(K, V, n_docs, n_per, seed):
+    rng = np.random.default_rng(seed)
+    theta = rng.dirichlet([0.5] * K, size=n_docs)
+    phi = rng.dirichlet([0.5] * V, size=K)
+    doc, word = [], []
+    for d in range(n_docs):
+        for _ in range(n_per):
+            z = rng.choice(K, p=theta[d])
+            doc.append(d)
+            word.append(int(rng.choice(V, p=phi[z])))
+    return doc, word
+
+
+def chain_c4(seed=31, P=4, K=3, V=5, n_docs=4, n_per=3, n_mh=120):
+    doc, word = lda_corpus(K, V, n_docs, n_per, 3)
+    n_tok = len(doc)
+    patch_dircat_sampler(K, V)
+    out = {"seed": seed, "P": P, "K": K, "V": V, "n_docs": n_docs, "doc": doc, "word": word, "n_mh": n_mh,
+           "a": 1.0, "b": 2.0, "steps": {"prior": 2, "tokens": 3, "mh_one": 40, "mh_each": 400}, "particles": []}
+    for p in range(P):
+        m, ad, aw = lda_model(K, V, seed, p, 2)
+        rec = {"alpha_prior": [fl(m.value(ad)), fl(m.value(aw))], "incr": []}
+        znodes = []
+        pos = {}
+        for i in range(n_tok):
+            d = doc[i]
+            pos[d] = pos.get(d, -1) + 1
+            m.tape.begin(3, i)                     # z_i is draw i of step `tokens`
+            did = m.observe(["word", d, pos[d]], vd.integer(word[i]))
+            rec["incr"].append(fl(m.t.makeConsistent()))
+            # (word d pos) -> mem request -> application of the lambda -> its body ((topic ((doc doc_id))))
+            body = m.t.families[did]
+            while not hasattr(body.operatorNode, "operandNodes"):
+                esr = m.t.valueAt(body.requestNode).esrs[0]
+                body = m.t.spFamilyAt(body.requestNode, esr.id)
+            znodes.append(body.operatorNode.operandNodes[0])
+        sites = [m.t.families[ad], m.t.families[aw]] + znodes
+        m.tape.site_of = lambda key: [i for i, n in enumerate(sites) if n is key][0]
+
+        def state():
+            return {"alpha": [fl(m.value(ad)), fl(m.value(aw))],
+                    "z": [int(m.t.valueAt(n).getNumber()) for n in znodes]}
+        rec["after_tokens"] = state()
+        rec["nodes_one"] = mh_steps(m, 40, n_mh)
+        rec["after_one"] = state()
+        out["particles"].append(rec)
+    return out
+
+
+CHAINS = [("c1", chain_c1), ("c2", chain_c2), ("c3", chain_c3), ("c4", chain_c4)]
 
 
 def main():

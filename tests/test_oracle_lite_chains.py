@@ -129,3 +129,27 @@ def test_c3_hmm_filter_and_mh_chain():
     # transloop's return value: 13 affected nodes for an interior state(t), 9 for the last one
     for r in recs:
         assert set(r["nodes_each"]) == {13.0, 9.0} and r["nodes_each"][T - 2] == 9.0
+
+
+# ------------------------------------------------------------------ C4
+def test_c4_lda_chain():
+    from helpers import OracleLDA
+    c = CH["c4"]
+    P, K, V, seed = c["P"], c["K"], c["V"], c["seed"]
+    doc, word = c["doc"], c["word"]
+    n_tok = len(doc)
+    recs = c["particles"]
+    o = OracleLDA(K, V, c["n_docs"], 16, c["a"], c["b"], P, seed)
+    o.seq(2, 0, 0, c["steps"]["prior"])                      # reset_to_prior: the two gamma hyper-parameters
+    np.testing.assert_allclose(o.alpha, [unj(r["alpha_prior"]) for r in recs], rtol=RTOL)
+    o.observe(doc, word)
+    incr = o.seq(0, 0, n_tok, c["steps"]["tokens"])          # observe + incorporate token by token
+    np.testing.assert_allclose(incr, [sum(unj(r["incr"])) for r in recs], rtol=RTOL)
+    assert np.array_equal(o.z[:, :n_tok], np.array([r["after_tokens"]["z"] for r in recs]))
+    acc = o.mh(c["steps"]["mh_one"], c["n_mh"], -1)
+    assert np.array_equal(o.z[:, :n_tok], np.array([r["after_one"]["z"] for r in recs]))
+    np.testing.assert_allclose(o.alpha, [unj(r["after_one"]["alpha"]) for r in recs], rtol=RTOL)
+    assert acc.sum() > 0 and (acc < c["n_mh"]).any()
+    # both hyper-parameter sites moved somewhere (the AAA weight was exercised with accepts)
+    a0 = np.array([unj(r["alpha_prior"]) for r in recs])
+    assert (o.alpha[:, 0] != a0[:, 0]).any() and (o.alpha[:, 1] != a0[:, 1]).any()

@@ -429,7 +429,56 @@ def chain_c4(seed=31, P=4, K=3, V=5, n_docs=4, n_per=3, n_mh=120):
     return out
 
 
-CHAINS = [("c1", chain_c1), ("c2", chain_c2), ("c3", chain_c3), ("c4", chain_c4)]
+# ------------------------------------------------------------------ C5 subsampled MH (austerity)
+def chain_c5(seed=41, P=3, D=4, N=60, K=40, Nbatch=10, k0=2, eps=0.05):
+    import ctypes
+    import venture.lite.infer.subsampled_mh as ss
+    X, y = blr_data(N, D, 50)
+    out = {"seed": seed, "P": P, "D": D, "N": N, "K": K, "Nbatch": Nbatch, "k0": k0, "eps": eps, "data_seed": 50,
+           "X": X.tolist(), "y": y.tolist(), "steps": {"prior": 0, "ssmh": 7}, "particles": []}
+    tests = []
+    orig = ss.sequentialTest
+
+    def recording(*a):                      # reads sequentialTest's own return value; changes nothing
+        r = orig(*a)
+        tests.append(r)
+        return r
+    ss.sequentialTest = recording
+    for p in range(P):
+        m = Model()
+        install(m, seed, p)
+        m.tape.begin(0, 0)                  # the D prior normals: draws 2j, 2j+1 of step `prior`
+        wd = [m.assume("w_%d" % j, ["normal", 0.0, 1.0]) for j in range(D)]
+        m.assume("w", ["array"] + ["w_%d" % j for j in range(D)])
+        tape = m.tape
+        m.t.py_rng = __import__("random").Random(5)    # the flips evaluated by `observe` draw from py_rng; constrained next
+        for i in range(N):
+            m.observe(["log_odds_flip", ["vector_dot", "w", ["array"] + [float(v) for v in X[i]]]], vd.boolean(bool(y[i])))
+        m.t.makeConsistent()
+        m.t.py_rng = PyRng(tape)
+        nodes = [m.t.families[d] for d in wd]
+        tape.site_of = lambda key: [i for i, n in enumerate(nodes) if n is key][0]
+
+        def permutation(items, tape=tape):   # subsampled_mh.py:103 -> the kernels' Feistel permutation of (seed, step)
+            n = len(items)
+            perm = np.empty(n, dtype=np.uint64)
+            oracle.lib().orc_feistel_perm(ctypes.c_uint64(tape.seed), ctypes.c_uint32(tape.step), ctypes.c_uint64(n),
+                                          perm.ctypes.data_as(ctypes.c_void_p))
+            return [items[int(q)] for q in perm]
+        m.t.np_rng.permutation = permutation
+        rec = {"w_prior": [fl(m.value(d)) for d in wd]}
+        del tests[:]
+        rec["nodes"] = mh_steps(m, 7, K, op="subsampled_mh", extra=(Nbatch, k0, eps, False, 0, False))
+        rec["accept"] = [bool(t[0]) for t in tests]
+        rec["n"] = [float(t[1]) for t in tests]
+        rec["tstat"] = [fl(t[2]) for t in tests]
+        rec["w"] = [fl(m.value(d)) for d in wd]
+        out["particles"].append(rec)
+    ss.sequentialTest = orig
+    return out
+
+
+CHAINS = [("c1", chain_c1), ("c2", chain_c2), ("c3", chain_c3), ("c4", chain_c4), ("c5", chain_c5)]
 
 
 def main():

@@ -153,3 +153,30 @@ def test_c4_lda_chain():
     # both hyper-parameter sites moved somewhere (the AAA weight was exercised with accepts)
     a0 = np.array([unj(r["alpha_prior"]) for r in recs])
     assert (o.alpha[:, 0] != a0[:, 0]).any() and (o.alpha[:, 1] != a0[:, 1]).any()
+
+
+# ------------------------------------------------------------------ C5
+def test_c5_subsampled_mh_chain():
+    c = CH["c5"]
+    P, D, N, K, seed = c["P"], c["D"], c["N"], c["K"], c["seed"]
+    X = np.ascontiguousarray(c["X"], dtype=np.float64)
+    y = np.ascontiguousarray(c["y"], dtype=np.uint8)
+    recs = c["particles"]
+    w = np.empty((D, P))
+    oracle.lib().orc_blr_prior(oracle._ptr(w), oracle.I32(D), oracle.I64(P), oracle.I64(0), oracle.F64(0.0),
+                               oracle.F64(1.0), oracle.U64(seed), oracle.U32(c["steps"]["prior"]))
+    np.testing.assert_allclose(w, wcol(recs, "w_prior"), rtol=RTOL)
+    stats = np.empty((P, 3))
+    for k in range(K):
+        oracle.lib().orc_blr_subsampled_mh(oracle._ptr(w), oracle._ptr(X), oracle._ptr(y), oracle.I32(D), oracle.I64(N),
+                                           oracle.I64(P), oracle.I64(0), oracle.F64(0.0), oracle.F64(1.0),
+                                           oracle.U64(seed), oracle.U32(c["steps"]["ssmh"] + k), oracle.I32(1),
+                                           oracle.I32(-1), oracle.F64(c["Nbatch"]), oracle.I32(c["k0"]),
+                                           oracle.F64(c["eps"]), oracle.I32(0), oracle.F64(0.0), oracle._ptr(stats))
+        for p, r in enumerate(recs):
+            assert bool(stats[p, 0]) == r["accept"][k], (k, p)
+            assert stats[p, 1] == r["n"][k], (k, p)            # sections visited before the test stopped
+            np.testing.assert_allclose(stats[p, 2], unj(r["tstat"][k]), rtol=1e-9)
+    np.testing.assert_allclose(w, wcol(recs, "w"), rtol=RTOL)
+    ns = np.array([r["n"] for r in recs])
+    assert (ns < N).any() and (ns == N).any()      # early stops and full passes both occurred

@@ -83,13 +83,16 @@ hmm_lw_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, i
   }
 }
 
+#define HMM_NODES_INTERIOR 13
+#define HMM_NODES_LAST 9
 // single-site resimulation MH over the state sequence (scope default: one
 // block per random choice = state(2..T)).  scaffold(state(t)): DRG {state(t)},
 // absorbing {state(t+1) (its categorical parameter row changes), obs_t}.
 __global__ void __launch_bounds__(256)
 hmm_mh_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, int T, HMMTables tb,
               const int32_t *__restrict__ symbols, int64_t P, int64_t p_base, uint64_t seed,
-              uint32_t step0, int n_steps, int block_mode, long long *__restrict__ acc_out) {
+              uint32_t step0, int n_steps, int block_mode, long long *__restrict__ acc_out,
+              double *__restrict__ nodes_out) {
   extern __shared__ double sh[];
   double *tr = sh;
   double *em = sh + tb.n_rows * tb.S;
@@ -101,6 +104,7 @@ hmm_mh_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, i
        p += (int64_t)gridDim.x * blockDim.x) {
     uint8_t *h = hist + p * Tpad;
     long long acc = 0;
+    int n_last = 0;
     for (int k = 0; k < n_steps; ++k) {
       Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
       double u_sel = r.uniform();
@@ -109,6 +113,7 @@ hmm_mh_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, i
       if (block_mode == VK_BLOCK_ONE) { b = (int)(u_sel * (double)nb); if (b >= nb) b = nb - 1; }
       else if (block_mode == VK_BLOCK_EACH) b = k % nb;
       else b = block_mode;
+      n_last += (b == nb - 1);
       int t = b + 1;  // 0-based time index of the site
       int prev = h[t - 1], old = h[t];
       int nxt = (t + 1 < T) ? h[t + 1] : 0;
@@ -125,17 +130,27 @@ hmm_mh_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, i
     }
     if (T > 0) cur[p] = h[T - 1];
     if (acc_out) acc_out[p] = acc;
+    // transloop's return value (dispatch.py:109-128) = mean |regenCounts| (scaffold.py:67-68).  Measured
+    // on the reference's Lite backend for examples/hmm.vnt (tests/golden/lite_chains.json, c3): the
+    // scaffold of an interior state(t) has HMM_NODES_INTERIOR nodes, that of the newest state
+    // HMM_NODES_LAST (no state(t+1) family hanging off it).  `each` floor-divides a sweep's sum by #blocks.
+    if (nodes_out) {
+      if (block_mode == VK_BLOCK_EACH)
+        nodes_out[p] = (double)((HMM_NODES_INTERIOR * (nb - 1) + HMM_NODES_LAST) / nb);
+      else
+        nodes_out[p] = (double)(HMM_NODES_INTERIOR * (n_steps - n_last) + HMM_NODES_LAST * n_last) / (double)n_steps;
+    }
   }
 }
 
 __global__ void hmm_loglik_kernel(const uint8_t *__restrict__ hist, int Tpad, int T, HMMTables tb,
-                                  const int32_t *__restrict__ symbols, int64_t P, int joint,
+                                  const int32_t *__restrict__ symbols, int64_t P, int joint, int t_first,
                                   double *__restrict__ out) {
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
        p += (int64_t)gridDim.x * blockDim.x) {
     const uint8_t *h = hist + p * Tpad;
     double w = 0.0;
-    for (int t = 0; t < T; ++t) {
+    for (int t = t_first; t < T; ++t) {
       w += categorical_logpmf(symbols[t] - 1, tb.emit + (h[t] - 1) * tb.O, tb.O, 1);
       if (joint && t > 0) w += categorical_logpmf(h[t] - 1, tb.trans + (h[t - 1] - 1) * tb.S, tb.S, 1);
     }
@@ -237,33 +252,34 @@ struct HMMModel : Model {
     VK_REQUIRE(T == (int)symbols_host.size(), VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
     int nb = T - 1;
     VK_REQUIRE(block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || (block >= 0 && block < nb), VK_EINVAL, "hmm: bad block");
-    double nodes = 0.0;
     if (K > 0 && nb > 0) {  // zero-entropy scope performs no transitions (dispatch.py:55-56)
       int n_steps = block == VK_BLOCK_EACH ? K * nb : K;
       uint32_t step0 = h->next_step((uint32_t)n_steps);
       upload_symbols();
       hmm_mh_kernel<<<grid(), 256, smem, h->stream>>>(cur, hist, Tpad, T, tb, symbols.p, h->P, h->p_base, h->seed,
-                                                      step0, n_steps, block, acc_dev);
+                                                      step0, n_steps, block, acc_dev, mean_nodes_dev);
       VK_CUDA(cudaGetLastError());
       VK_CUDA(cudaStreamSynchronize(h->stream));
-      // DRG of state(t): the transition application's request + output nodes and the
-      // lookups that consume the state; reported as a per-model constant
-      nodes = 1.0 * (block == VK_BLOCK_EACH ? nb : 1);
-    } else if (acc_dev) {
-      VK_CUDA(cudaMemsetAsync(acc_dev, 0, (size_t)h->P * sizeof(long long), h->stream));
+    } else {
+      if (acc_dev) VK_CUDA(cudaMemsetAsync(acc_dev, 0, (size_t)h->P * sizeof(long long), h->stream));
+      if (mean_nodes_dev) hmm_fill_kernel<<<grid(), 256, 0, h->stream>>>(mean_nodes_dev, h->P, 0.0);
     }
-    if (mean_nodes_dev) hmm_fill_kernel<<<grid(), 256, 0, h->stream>>>(mean_nodes_dev, h->P, nodes);
   }
   void log_likelihood_at(int scope, int block, bool joint, double *out_dev) override {
     VK_REQUIRE(scope == 0, VK_EINVAL, "hmm: only the default scope exists");
     VK_REQUIRE(block == VK_BLOCK_ALL, VK_EUNSUPPORTED, "hmm: log_likelihood_at is compiled for block all");
+    // The scaffold's principal nodes are the random choices state(2..T); state(1) is deterministic, so
+    // its emission is not on the border and does not count (Lite agrees: lite_chains.json c3 ll_at).
+    loglik_from(1, joint, out_dev);
+  }
+  void loglik_from(int t_first, bool joint, double *out_dev) {
     upload_symbols();
-    hmm_loglik_kernel<<<grid(), 256, 0, h->stream>>>(hist, Tpad, T, tb, symbols.p, h->P, joint ? 1 : 0, out_dev);
+    hmm_loglik_kernel<<<grid(), 256, 0, h->stream>>>(hist, Tpad, T, tb, symbols.p, h->P, joint ? 1 : 0, t_first, out_dev);
     VK_CUDA(cudaGetLastError());
     VK_CUDA(cudaStreamSynchronize(h->stream));
   }
   void forget_observations(double *w_dev) override {
-    if (w_dev) log_likelihood_at(0, VK_BLOCK_ALL, false, w_dev);
+    if (w_dev) loglik_from(0, false, w_dev);   // unobserve reports every observation's density
     symbols_host.clear(); T = 0;
   }
   int64_t num_sites() const override { return T; }

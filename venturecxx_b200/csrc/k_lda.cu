@@ -164,7 +164,8 @@ __global__ void __launch_bounds__(32 * LDA_WARPS)
 lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__restrict__ doc,
               const int32_t *__restrict__ word, const int32_t *__restrict__ doclen, int n_tok,
               int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int block_mode,
-              int stage, int tok_shared, long long *__restrict__ acc_out) {
+              int stage, int tok_shared, long long *__restrict__ acc_out, int n_docs_live,
+              double *__restrict__ nodes_out) {
   extern __shared__ uint4 smem_all[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, n_w = blockDim.x >> 5;
   const int nb = 2 + n_tok;
@@ -193,6 +194,10 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
     LDARow R = stage == 2 ? LDARow((unsigned char *)smem_u4, (uint16_t *)(grow + L.off_nkw), grow + L.off_z, L)
                           : LDARow(base, L);
     long long acc = 0;
+    // transloop's return value (dispatch.py:109-128): |regenCounts| per transition, as measured on the
+    // reference's Lite backend (tests/golden/lite_chains.json c4): z site 7; alpha_document_topic
+    // 1 + 2 * (#doc makers alive); alpha_topic_word 1 + 2 * (#topic makers alive = topics in use).
+    long long node_sum = 0, sweep_sum = 0, sweep_tot = 0;
     for (int k = 0; k < n_steps; ++k) {
       Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
       double u_sel = r.uniform();
@@ -201,6 +206,19 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
       if (block_mode == VK_BLOCK_ONE) { b = (int)(u_sel * (double)nb); if (b >= nb) b = nb - 1; }
       else if (block_mode == VK_BLOCK_EACH) b = k % nb;
       else b = block_mode;
+      if (nodes_out) {
+        int cnt;
+        if (b >= 2) cnt = 7;
+        else if (b == 0) cnt = 1 + 2 * n_docs_live;
+        else {
+          int live = 0;
+          for (int t = lane; t < L.K; t += 32) live += R.nk[t] > 0;
+          for (int o = 16; o; o >>= 1) live += __shfl_xor_sync(0xffffffffu, live, o);
+          cnt = 1 + 2 * live;
+        }
+        node_sum += cnt; sweep_sum += cnt;
+        if (block_mode == VK_BLOCK_EACH && (k % nb) == nb - 1) { sweep_tot += sweep_sum / nb; sweep_sum = 0; }
+      }
       if (b < 2) {
         // AAA site: alpha' from the gamma prior (no proposal weight), rho/xi = marginal
         // likelihood of every made SP's counts under the old/new concentration
@@ -292,6 +310,9 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
       __syncwarp();
     }
     if (acc_out && lane == 0) acc_out[p] = acc;
+    if (nodes_out && lane == 0)
+      nodes_out[p] = block_mode == VK_BLOCK_EACH ? (double)sweep_tot / (double)(n_steps / nb)
+                                                 : (double)node_sum / (double)n_steps;
   }
 }
 
@@ -422,6 +443,8 @@ struct LDAModel : Model {
     if (K > 0) {
       int n_steps = block == VK_BLOCK_EACH ? K * nb : K;
       uint32_t step0 = h->next_step((uint32_t)n_steps);
+      int n_docs_live = 0;   // a doc's maker family exists once a token refers to it (mem, msp.py:28-49)
+      for (int32_t c : doclen_host) n_docs_live += c > 0;
       // small sections + z per warp in shared memory, K x V table in global memory (stage 2);
       // if even that does not fit, everything stays in global memory (stage 0)
       size_t small = L.off_nkw;
@@ -442,16 +465,15 @@ struct LDAModel : Model {
       int64_t cap = (int64_t)h->sm_count * per_sm;
       int grid = (int)(need_ctas < cap ? need_ctas : cap);
       lda_mh_kernel<<<grid, 32 * warps, sm, h->stream>>>(rows, L, doc.p, word.p, doclen.p, n_tok, h->P, h->p_base,
-                                                         h->seed, step0, n_steps, block, stage, tok_shared, acc_dev);
+                                                         h->seed, step0, n_steps, block, stage, tok_shared, acc_dev,
+                                                         n_docs_live, mean_nodes_dev);
       VK_CUDA(cudaGetLastError());
-    } else if (acc_dev) {
-      VK_CUDA(cudaMemsetAsync(acc_dev, 0, (size_t)h->P * sizeof(long long), h->stream));
-    }
-    if (mean_nodes_dev) {
-      // z site: DRG {z, request + output of (topic z), the token application} = 4
-      double nodes = K > 0 ? 4.0 * (block == VK_BLOCK_EACH ? nb : 1) : 0.0;
-      lda_fill_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, nodes);
-      VK_CUDA(cudaGetLastError());
+    } else {
+      if (acc_dev) VK_CUDA(cudaMemsetAsync(acc_dev, 0, (size_t)h->P * sizeof(long long), h->stream));
+      if (mean_nodes_dev) {
+        lda_fill_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, 0.0);
+        VK_CUDA(cudaGetLastError());
+      }
     }
   }
   void log_likelihood_at(int scope, int block, bool joint, double *out_dev) override {

@@ -139,6 +139,25 @@ def fix_tuple_params(src):
     return "\n".join(out)
 
 
+# py2 orders any two objects (`<` never raises); the persistent weight-balanced trees of wttree.py rely on
+# that for keys such as trace nodes, addresses (nested tuples mixing str and int) and VentureValues.  py3 does
+# not, so wttree's key comparisons go through one explicit total order.  The order only decides the SHAPE of
+# the persistent maps (lookup / insert / delete by key are order-agnostic), never a computed value.
+WTTREE_ORDER = '''
+def _ord(x):
+  if x is None: return (-1,)
+  if isinstance(x, bool): return (0, int(x))
+  if isinstance(x, (int, float)): return (0, x)
+  if isinstance(x, str): return (1, x)
+  if isinstance(x, (tuple, list)): return (4, tuple(_ord(e) for e in x))
+  if hasattr(x, "asStackDict") and hasattr(x, "equal"): return (2, type(x).__name__, repr(x))
+  return (3, type(x).__name__, id(x))
+
+def _py2_lt(a, b):
+  return _ord(a) < _ord(b)
+'''
+
+
 # One-line hand edits: file (package-relative) -> list of (old, new).  Each is a py3 laziness or
 # syntax fix with no change of meaning.
 HAND = {}
@@ -151,6 +170,15 @@ def convert(src, rel):
             continue
         src = re.sub(pat, rep, src, flags=re.M)
     src = fix_tuple_params(src)
+    if rel == os.path.join("lite", "wttree.py"):
+        src = re.sub(r"\b(\w*key_) < (\w*key_)", r"_py2_lt(\1, \2)", src)
+        src = src.replace("\nclass ", WTTREE_ORDER + "\nclass ", 1)
+    # call sites `x.iteritems()` become `x.items().__iter__()`; the two reference classes that define their
+    # own iteritems get the matching alias
+    if rel == os.path.join("lite", "wttree.py"):
+        src += "\nPMap.items = PMap.iteritems\n"
+    if rel == os.path.join("lite", "smap.py"):
+        src += "\nSamplableMap.items = SamplableMap.iteritems\n"
     if "functools_reduce(" in src:
         src = "from functools import reduce as functools_reduce\n" + src
     for old, new in HAND.get(rel, []):

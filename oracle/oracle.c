@@ -730,6 +730,93 @@ void orc_lda_mh(double *alpha, int32_t *nk, int32_t *ndk, int32_t *nkw, uint8_t 
   }
 }
 
+/* ------------------------------------------------ enumerative Gibbs (N1) */
+/* infer/egibbs.py:42-107 under mixMH (mh.py:59-113): for a discrete principal node every candidate value v
+ * (PSP.enumerateValues) is installed with a DeterministicLKernel and the scaffold regenerated, giving
+ * xi_v = logDensity(v | parents) + sum of the absorbing children's logDensity; the new value is drawn
+ * proportionally to exp(xi_v) (utils.py:170-180 sampleLogCategorical) and always accepted (logAlpha = 0, rhoMix =
+ * xiMix), although mixMH still draws its accept uniform (draw 1).  exp(xi_v - max) is evaluated here as the
+ * product of the probabilities themselves (no log / exp round trip); the selection uniform is draw 2.
+ * The inclusive scan has the shape of the warp scan the kernels use (Kogge-Stone over <= 32 lanes, sequential
+ * beyond), so that the selected index is bit-identical on both sides. */
+static int gibbs_pick(double *pr, int n, double u) {
+  if (n <= 32) {
+    for (int o = 1; o < 32; o <<= 1) {
+      double t[32];
+      for (int i = 0; i < n; ++i) t[i] = i >= o ? pr[i - o] : 0.0;
+      for (int i = 0; i < n; ++i) if (i >= o) pr[i] += t[i];
+    }
+  } else {
+    for (int i = 1; i < n; ++i) pr[i] += pr[i - 1];
+  }
+  double total = pr[n - 1];
+  if (!(total > 0)) { int k = (int)(u * n); return k < n ? k : n - 1; }   /* utils.py:95-99: all impossible => uniform */
+  double t = u * total;
+  for (int i = 0; i < n; ++i) if (t < pr[i]) return i;
+  return n - 1;
+}
+static double cat_prob(int val, const double *ps, int n) {
+  double denom = 0;
+  for (int i = 0; i < n; ++i) denom += ps[i];
+  return denom > 0 ? ps[val] / denom : 1.0 / n;
+}
+/* z sites of the LDA model; blocks are the tokens (block_mode -1 one, -3 each, >= 0 token index) */
+void orc_lda_gibbs(double *alpha, int32_t *nk, int32_t *ndk, int32_t *nkw, uint8_t *z, const orc_lda *L,
+                   const int32_t *doc, const int32_t *word, int n_tok, int64_t P, int64_t p_base, uint64_t seed,
+                   uint32_t step0, int n_steps, int block_mode, int64_t *changed) {
+  int K = L->K, V = L->V, nb = n_tok;
+#pragma omp parallel for schedule(dynamic, 1)
+  for (int64_t p = 0; p < P; ++p) {
+    double *al = alpha + p * 2; int32_t *NK = nk + p * K, *NDK = ndk + p * (int64_t)L->n_docs * K, *NKW = nkw + p * (int64_t)K * V;
+    uint8_t *Z = z + p * L->max_tok; int64_t ch = 0;
+    double *pr = (double *)malloc(sizeof(double) * (size_t)K);
+    for (int k = 0; k < n_steps; ++k) {
+      orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
+      double u_sel = st_uniform(&r); (void)st_uniform(&r);       /* mh.py:85: drawn, never decisive */
+      int i;
+      if (block_mode == -1) { i = (int)(u_sel * nb); if (i >= nb) i = nb - 1; }
+      else if (block_mode == -3) i = k % nb; else i = block_mode;
+      int d = doc[i], w = word[i], zo = Z[i];
+      NKW[(int64_t)zo * V + w]--; NK[zo]--; NDK[d * K + zo]--;   /* detach: unconstrain + unincorporate */
+      double ad = al[0], aw = al[1], Aw = aw * (double)V;
+      for (int t = 0; t < K; ++t)      /* dirichlet.py:168-173 twice; the z term's denominator is common */
+        pr[t] = ((double)NDK[d * K + t] + ad) * ((double)NKW[(int64_t)t * V + w] + aw) / ((double)NK[t] + Aw);
+      int zn = gibbs_pick(pr, K, st_uniform(&r));
+      if (zn != zo) ++ch;
+      Z[i] = (uint8_t)zn; NKW[(int64_t)zn * V + w]++; NK[zn]++; NDK[d * K + zn]++;
+    }
+    free(pr);
+    if (changed) changed[p] = ch;
+  }
+}
+/* state sites of the HMM (blocks = state(2..T) as in orc_hmm_mh) */
+void orc_hmm_gibbs(uint8_t *hist, int Tpad, int T, const double *trans, const double *emit, int S, int O,
+                   const int32_t *symbols, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps,
+                   int block_mode, int64_t *changed) {
+  int nb = T - 1;
+  for (int64_t p = 0; p < P; ++p) {
+    uint8_t *h = hist + p * Tpad; int64_t ch = 0;
+    double pr[256];
+    for (int k = 0; k < n_steps; ++k) {
+      orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
+      double u_sel = st_uniform(&r); (void)st_uniform(&r);
+      int b;
+      if (block_mode == -1) { b = (int)(u_sel * nb); if (b >= nb) b = nb - 1; }
+      else if (block_mode == -3) b = k % nb; else b = block_mode;
+      int t = b + 1, prev = h[t - 1], old = h[t], nxt = (t + 1 < T) ? h[t + 1] : 0;
+      for (int s = 0; s < S; ++s) {
+        double v = cat_prob(s, trans + (prev - 1) * S, S) * cat_prob(symbols[t] - 1, emit + s * O, O);
+        if (nxt) v *= cat_prob(nxt - 1, trans + s * S, S);
+        pr[s] = v;
+      }
+      int sn = 1 + gibbs_pick(pr, S, st_uniform(&r));
+      if (sn != old) ++ch;
+      h[t] = (uint8_t)sn;
+    }
+    if (changed) changed[p] = ch;
+  }
+}
+
 /* ------------------------------------------- C5: subsampled MH (BLR) */
 /* Keyed Feistel bijection on [0,N) shared by the particle batch: the product's
  * stand-in for np_rng.permutation(local_roots) (subsampled_mh.py:103). */

@@ -133,6 +133,9 @@ class PyRng(object):
     def random(self):                          # mh.py:85
         return self.tape.at(1)
 
+    def randint(self, lo, hi):                 # particle.py:97-99 seeds particle-local RNGs (egibbs); those
+        return 12345                           # are never drawn from on these paths (a draw would raise here)
+
 
 class NpRng(object):
     """Stands in for trace.np_rng (numpy RandomState): the value draws of regen."""
@@ -341,13 +344,22 @@ def chain_c3(seed=23, P=6, K=40):
         rec["hist_each"] = [1] + hist()
         rec["ll_at"] = fl(m.t.log_likelihood_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
         rec["lj_at"] = fl(m.t.log_joint_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
+        # enumerative Gibbs (infer/egibbs.py:42-107): (gibbs default one 1) x K, then two ordered sweeps
+        rec["nodes_gibbs_one"] = mh_steps(m, 300, K, op="gibbs")
+        rec["hist_gibbs_one"] = [1] + hist()
+        rec["nodes_gibbs_each"] = []
+        for k in range(2 * (T - 1)):
+            m.tape.begin(400 + k, 2)
+            rec["nodes_gibbs_each"].append(m.t.primitive_infer(infer_exp("gibbs", "seq", 2 + k % (T - 1), 1)))
+        rec["hist_gibbs_each"] = [1] + hist()
         out["particles"].append(rec)
+    out["steps"]["gibbs_one"], out["steps"]["gibbs_each"] = 300, 400
     out["trans"], out["emit"] = rows, erows
     return out
 
 
 # ------------------------------------------------------------------ C4 LDA (examples/lda.vnt:18-41)
-def lda_model(K, V, seed, particle, prior_step):
+def lda_model(K, V, seed, particle, prior_step, tag_z=False):
     m = Model()
     install(m, seed, particle)
     m.tape.begin(prior_step, 0)       # the two gamma assumes evaluate on draws 0.. of `prior_step`, in order
@@ -357,7 +369,10 @@ def lda_model(K, V, seed, particle, prior_step):
     aw = m.assume("alpha_topic_word", ["gamma", 1.0, 2.0])
     m.assume("doc", ["mem", ["lambda", ["doc_id"], ["make_sym_dir_cat", "alpha_document_topic", "n_topics"]]])
     m.assume("topic", ["mem", ["lambda", ["topic_id"], ["make_sym_dir_cat", "alpha_topic_word", "vocab_size"]]])
-    m.assume("word", ["mem", ["lambda", ["doc_id", "pos"], [["topic", [["doc", "doc_id"]]]]]])
+    zexp = [["doc", "doc_id"]]
+    if tag_z:   # lda.vnt with the topic draw tagged into scope `z`, block 1000 doc_id + pos
+        zexp = ["tag", ["quote", "z"], ["add", ["mul", "doc_id", 1000], "pos"], zexp]
+    m.assume("word", ["mem", ["lambda", ["doc_id", "pos"], [["topic", zexp]]]])
     return m, ad, aw
 
 
@@ -478,7 +493,51 @@ def chain_c5(seed=41, P=3, D=4, N=60, K=40, Nbatch=10, k0=2, eps=0.05):
     return out
 
 
-CHAINS = [("c1", chain_c1), ("c2", chain_c2), ("c3", chain_c3), ("c4", chain_c4), ("c5", chain_c5)]
+def chain_c4_gibbs(seed=37, P=4, K=3, V=5, n_docs=4, n_per=3, n_gibbs=60):
+    """lda.vnt with z tagged into scope `z` (the default scope also holds the two gamma sites, which
+    cannot be enumerated): (gibbs z one 1) x n_gibbs, then two ordered sweeps (gibbs z <block> 1)."""
+    doc, word = lda_corpus(K, V, n_docs, n_per, 3)
+    n_tok = len(doc)
+    patch_dircat_sampler(K, V)
+    out = {"seed": seed, "P": P, "K": K, "V": V, "n_docs": n_docs, "doc": doc, "word": word, "n_gibbs": n_gibbs,
+           "a": 1.0, "b": 2.0, "steps": {"prior": 2, "tokens": 3, "gibbs_one": 40, "gibbs_each": 400}, "particles": []}
+    for p in range(P):
+        m, ad, aw = lda_model(K, V, seed, p, 2, tag_z=True)
+        rec = {}
+        blocks, pos = [], {}
+        for i in range(n_tok):
+            d = doc[i]
+            pos[d] = pos.get(d, -1) + 1
+            m.tape.begin(3, i)
+            m.observe(["word", d, pos[d]], vd.integer(word[i]))
+            m.t.makeConsistent()
+            blocks.append(1000 * d + pos[d])
+        znodes = []
+        for b in blocks:
+            pn = list(m.t.getNodesInBlock(vv.VentureSymbol("z"), vv.VentureNumber(b)))
+            assert len(pn) == 1
+            znodes.append(pn[0])
+        m.tape.site_of = lambda key: blocks.index(int(key.getNumber()))
+
+        def zs():
+            return [int(m.t.valueAt(n).getNumber()) for n in znodes]
+        rec["z_tokens"] = zs()
+        rec["alpha"] = [fl(m.value(ad)), fl(m.value(aw))]
+        rec["nodes_one"] = []
+        for k in range(n_gibbs):
+            m.tape.begin(40 + k, 2)
+            rec["nodes_one"].append(m.t.primitive_infer(infer_exp("gibbs", "z", "one", 1)))
+        rec["z_one"] = zs()
+        rec["nodes_each"] = []
+        for k in range(2 * n_tok):
+            m.tape.begin(400 + k, 2)
+            rec["nodes_each"].append(m.t.primitive_infer(infer_exp("gibbs", "z", blocks[k % n_tok], 1)))
+        rec["z_each"] = zs()
+        out["particles"].append(rec)
+    return out
+
+
+CHAINS = [("c1", chain_c1), ("c2", chain_c2), ("c3", chain_c3), ("c4", chain_c4), ("c5", chain_c5), ("c4_gibbs", chain_c4_gibbs)]
 
 
 def main():

@@ -83,6 +83,15 @@ class OracleHMM(object):
                                 oracle.I32(n_steps), oracle.I32(block_mode), oracle._ptr(acc))
         return acc
 
+    def gibbs(self, step0, n_steps, block_mode):
+        sym = np.ascontiguousarray(self.symbols, dtype=np.int32)
+        ch = np.empty(self.P, dtype=np.int64)
+        oracle.lib().orc_hmm_gibbs(oracle._ptr(self.hist), oracle.I32(self.Tpad), oracle.I32(self.T), oracle._ptr(self.trans),
+                                   oracle._ptr(self.emit), oracle.I32(self.S), oracle.I32(self.O), oracle._ptr(sym),
+                                   oracle.I64(self.P), oracle.I64(self.p_base), oracle.U64(self.seed), oracle.U32(step0),
+                                   oracle.I32(n_steps), oracle.I32(block_mode), oracle._ptr(ch))
+        return ch
+
     def resample(self, anc):
         self.hist = np.ascontiguousarray(self.hist[anc])
         lse = oracle.logsumexp(self.lw)
@@ -147,3 +156,12 @@ class OracleLDA(object):
                                 oracle.I32(self.n_tok), oracle.I64(self.P), oracle.I64(self.p_base), oracle.U64(self.seed),
                                 oracle.U32(step0), oracle.I32(n_steps), oracle.I32(block_mode), oracle._ptr(acc))
         return acc
+
+    def gibbs(self, step0, n_steps, block_mode):
+        """Enumerative Gibbs over the z sites (blocks = tokens)."""
+        ch = np.empty(self.P, dtype=np.int64)
+        oracle.lib().orc_lda_gibbs(oracle._ptr(self.alpha), oracle._ptr(self.nk), oracle._ptr(self.ndk), oracle._ptr(self.nkw),
+                                   oracle._ptr(self.z), ctypes.byref(self.L), oracle._ptr(self.doc), oracle._ptr(self.word),
+                                   oracle.I32(self.n_tok), oracle.I64(self.P), oracle.I64(self.p_base), oracle.U64(self.seed),
+                                   oracle.U32(step0), oracle.I32(n_steps), oracle.I32(block_mode), oracle._ptr(ch))
+        return ch

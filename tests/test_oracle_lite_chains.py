@@ -129,6 +129,14 @@ def test_c3_hmm_filter_and_mh_chain():
     # transloop's return value: 13 affected nodes for an interior state(t), 9 for the last one
     for r in recs:
         assert set(r["nodes_each"]) == {13.0, 9.0} and r["nodes_each"][T - 2] == 9.0
+    # enumerative Gibbs (infer/egibbs.py) continues the same chain
+    ch = o.gibbs(c["steps"]["gibbs_one"], K, -1)
+    assert np.array_equal(o.hist[:, :T], np.array([r["hist_gibbs_one"] for r in recs]))
+    assert ch.sum() > 0
+    o.gibbs(c["steps"]["gibbs_each"], 2 * (T - 1), -3)
+    assert np.array_equal(o.hist[:, :T], np.array([r["hist_gibbs_each"] for r in recs]))
+    for r in recs:
+        assert set(r["nodes_gibbs_each"]) == {13.0, 9.0}
 
 
 # ------------------------------------------------------------------ C4
@@ -180,3 +188,25 @@ def test_c5_subsampled_mh_chain():
     np.testing.assert_allclose(w, wcol(recs, "w"), rtol=RTOL)
     ns = np.array([r["n"] for r in recs])
     assert (ns < N).any() and (ns == N).any()      # early stops and full passes both occurred
+
+
+def test_c4_lda_enumerative_gibbs_chain():
+    from helpers import OracleLDA
+    c = CH["c4_gibbs"]
+    P, K, V, seed = c["P"], c["K"], c["V"], c["seed"]
+    doc, word = c["doc"], c["word"]
+    n_tok = len(doc)
+    recs = c["particles"]
+    o = OracleLDA(K, V, c["n_docs"], 16, c["a"], c["b"], P, seed)
+    o.seq(2, 0, 0, c["steps"]["prior"])
+    o.observe(doc, word)
+    o.seq(0, 0, n_tok, c["steps"]["tokens"])
+    assert np.array_equal(o.z[:, :n_tok], np.array([r["z_tokens"] for r in recs]))
+    np.testing.assert_allclose(o.alpha, [unj(r["alpha"]) for r in recs], rtol=RTOL)
+    ch = o.gibbs(c["steps"]["gibbs_one"], c["n_gibbs"], -1)
+    assert np.array_equal(o.z[:, :n_tok], np.array([r["z_one"] for r in recs]))
+    assert ch.sum() > 0
+    o.gibbs(c["steps"]["gibbs_each"], 2 * n_tok, -3)
+    assert np.array_equal(o.z[:, :n_tok], np.array([r["z_each"] for r in recs]))
+    # the tagged z site's scaffold has 8 nodes (7 of lda.vnt's + the tag application)
+    assert all(set(r["nodes_one"]) == {8.0} for r in recs)

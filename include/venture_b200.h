@@ -175,6 +175,16 @@ int vk_resample(vk_particles *h, int64_t n_new, int mode,
 int vk_mh(vk_particles *h, int32_t scope, int32_t block, int32_t transitions,
           double *mean_nodes_out_host, int64_t *accepted_out_host);
 
+/* Enumerative Gibbs, `(gibbs scope block transitions)`: infer/dispatch.py:175-179 ->
+ * infer/egibbs.py:42-107 (EnumerativeGibbsOperator under mixMH).  For a discrete site every candidate
+ * value is weighted by its regen weight, the new value is drawn proportionally and always accepted.
+ * Compiled for the HMM's state sites (scope 0) and the LDA z sites (scope 1 = "z", block = token index,
+ * or scope 0 with block = 2 + token index; the default scope's gamma sites cannot be enumerated and
+ * give VK_EUNSUPPORTED, as PSP.enumerateValues raises in the reference).  Other models: VK_EUNSUPPORTED.
+ * mean_nodes_out_host as vk_mh; changed_out_host: NULL or P int64 = transitions that changed the value. */
+int vk_gibbs(vk_particles *h, int32_t scope, int32_t block, int32_t transitions,
+             double *mean_nodes_out_host, int64_t *changed_out_host);
+
 /* infer/subsampled_mh.py:76-171 (BLR model only).  stats_out_host: NULL or
  * 3*P doubles per call = (accepted transitions, mean local sections visited
  * per transition, last t statistic). */

@@ -143,6 +143,60 @@ hmm_mh_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, i
   }
 }
 
+// Enumerative Gibbs on state(t) (infer/egibbs.py:42-107 under mixMH): candidates s = 1..S, weight
+// exp(xi_s) = P(s | state(t-1)) P(obs_t | s) P(state(t+1) | s), new value drawn proportionally, always
+// accepted (logAlpha = 0).  Draw layout as in MH: 0 block choice, 1 mixMH's accept uniform (unused), 2 the
+// selection uniform.  Requires S <= 32.
+__global__ void __launch_bounds__(256)
+hmm_gibbs_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, int T, HMMTables tb,
+                 const int32_t *__restrict__ symbols, int64_t P, int64_t p_base, uint64_t seed,
+                 uint32_t step0, int n_steps, int block_mode, long long *__restrict__ changed_out,
+                 double *__restrict__ nodes_out) {
+  extern __shared__ double sh[];
+  double *tr = sh;
+  double *em = sh + tb.n_rows * tb.S;
+  for (int i = threadIdx.x; i < tb.n_rows * tb.S; i += blockDim.x) tr[i] = tb.trans[i];
+  for (int i = threadIdx.x; i < tb.S * tb.O; i += blockDim.x) em[i] = tb.emit[i];
+  __syncthreads();
+  const int nb = T - 1, S = tb.S;
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    uint8_t *h = hist + p * Tpad;
+    long long ch = 0;
+    int n_last = 0;
+    double pr[32];
+    for (int k = 0; k < n_steps; ++k) {
+      Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
+      double u_sel = r.uniform();
+      (void)r.uniform();
+      int b;
+      if (block_mode == VK_BLOCK_ONE) { b = (int)(u_sel * (double)nb); if (b >= nb) b = nb - 1; }
+      else if (block_mode == VK_BLOCK_EACH) b = k % nb;
+      else b = block_mode;
+      n_last += (b == nb - 1);
+      int t = b + 1;
+      int prev = h[t - 1], old = h[t];
+      int nxt = (t + 1 < T) ? h[t + 1] : 0;
+      for (int s = 0; s < S; ++s) {
+        double v = categorical_prob(s, tr + (prev - 1) * S, S) * categorical_prob(symbols[t] - 1, em + s * tb.O, tb.O);
+        if (nxt) v *= categorical_prob(nxt - 1, tr + s * S, S);
+        pr[s] = v;
+      }
+      int sn = 1 + gibbs_pick_small(pr, S, r.uniform());
+      ch += (sn != old);
+      h[t] = (uint8_t)sn;
+    }
+    if (T > 0) cur[p] = h[T - 1];
+    if (changed_out) changed_out[p] = ch;
+    if (nodes_out) {   // the scaffold is the MH one: same node counts
+      if (block_mode == VK_BLOCK_EACH)
+        nodes_out[p] = (double)((HMM_NODES_INTERIOR * (nb - 1) + HMM_NODES_LAST) / nb);
+      else
+        nodes_out[p] = (double)(HMM_NODES_INTERIOR * (n_steps - n_last) + HMM_NODES_LAST * n_last) / (double)n_steps;
+    }
+  }
+}
+
 __global__ void hmm_loglik_kernel(const uint8_t *__restrict__ hist, int Tpad, int T, HMMTables tb,
                                   const int32_t *__restrict__ symbols, int64_t P, int joint, int t_first,
                                   double *__restrict__ out) {
@@ -248,6 +302,13 @@ struct HMMModel : Model {
   void likelihood_weight() override { run_prior(true); }
   void reset_to_prior() override { run_prior(false); }
   void mh(int scope, int block, int K, double *mean_nodes_dev, long long *acc_dev) override {
+    run_sites(0, scope, block, K, mean_nodes_dev, acc_dev);
+  }
+  void gibbs(int scope, int block, int K, double *mean_nodes_dev, long long *changed_dev) override {
+    VK_REQUIRE(tb.S <= 32, VK_EUNSUPPORTED, "hmm: gibbs is compiled for at most 32 states");
+    run_sites(1, scope, block, K, mean_nodes_dev, changed_dev);
+  }
+  void run_sites(int op, int scope, int block, int K, double *mean_nodes_dev, long long *acc_dev) {
     VK_REQUIRE(scope == 0, VK_EINVAL, "hmm: only the default scope exists");
     VK_REQUIRE(T == (int)symbols_host.size(), VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
     int nb = T - 1;
@@ -256,8 +317,12 @@ struct HMMModel : Model {
       int n_steps = block == VK_BLOCK_EACH ? K * nb : K;
       uint32_t step0 = h->next_step((uint32_t)n_steps);
       upload_symbols();
-      hmm_mh_kernel<<<grid(), 256, smem, h->stream>>>(cur, hist, Tpad, T, tb, symbols.p, h->P, h->p_base, h->seed,
-                                                      step0, n_steps, block, acc_dev, mean_nodes_dev);
+      if (op == 0)
+        hmm_mh_kernel<<<grid(), 256, smem, h->stream>>>(cur, hist, Tpad, T, tb, symbols.p, h->P, h->p_base, h->seed,
+                                                        step0, n_steps, block, acc_dev, mean_nodes_dev);
+      else
+        hmm_gibbs_kernel<<<grid(), 256, smem, h->stream>>>(cur, hist, Tpad, T, tb, symbols.p, h->P, h->p_base, h->seed,
+                                                           step0, n_steps, block, acc_dev, mean_nodes_dev);
       VK_CUDA(cudaGetLastError());
       VK_CUDA(cudaStreamSynchronize(h->stream));
     } else {

@@ -160,15 +160,34 @@ lda_seq_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__r
 // 38 KB at C4, so all particles are resident at once and the serial per-particle chains
 // overlap each other's latency.
 static const int LDA_WARPS = 4;
+// Enumerative-Gibbs selection across a warp: lane k < K holds pr_k; Kogge-Stone inclusive scan (the same
+// additions in the same order as sp_math.cuh gibbs_pick_small / oracle.c gibbs_pick), then the first lane
+// whose running sum exceeds u * total.
+__device__ __forceinline__ int lda_gibbs_pick_warp(double pr, int K, double u, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    double t = __shfl_up_sync(0xffffffffu, pr, o);
+    if (lane >= o) pr += t;
+  }
+  const double total = __shfl_sync(0xffffffffu, pr, K - 1);
+  const double thr = u * total;
+  const unsigned m = __ballot_sync(0xffffffffu, lane < K && thr < pr);
+  return m ? __ffs(m) - 1 : K - 1;
+}
+
 __global__ void __launch_bounds__(32 * LDA_WARPS)
 lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__restrict__ doc,
               const int32_t *__restrict__ word, const int32_t *__restrict__ doclen, int n_tok,
               int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int block_mode,
               int stage, int tok_shared, long long *__restrict__ acc_out, int n_docs_live,
-              double *__restrict__ nodes_out) {
+              double *__restrict__ nodes_out, int op, int nb_sel, int b_off) {
   extern __shared__ uint4 smem_all[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, n_w = blockDim.x >> 5;
-  const int nb = 2 + n_tok;
+  // op 0: resimulation MH over the default scope (nb_sel = 2 + n_tok blocks, b_off = 0).
+  // op 1: enumerative Gibbs (infer/egibbs.py:42-107) over the z sites (nb_sel = n_tok, b_off = 2): every
+  //       topic k is weighted exp(xi_k) = P(z = k | doc counts) P(word | topic k counts), the token's own
+  //       counts removed; the new topic is drawn proportionally and always accepted (logAlpha = 0).
+  const int nb = nb_sel;
   const size_t warp_bytes = stage == 1 ? L.row_bytes : L.off_nkw;   // stage 2: alpha, n_k, n_dk only
   uint4 *smem_u4 = smem_all + (size_t)wid * (warp_bytes / 16);
   // CTA-shared packed (doc << 16 | word) copy of the corpus, after the per-warp sections
@@ -203,8 +222,8 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
       double u_sel = r.uniform();
       double u_acc = r.uniform();
       int b;
-      if (block_mode == VK_BLOCK_ONE) { b = (int)(u_sel * (double)nb); if (b >= nb) b = nb - 1; }
-      else if (block_mode == VK_BLOCK_EACH) b = k % nb;
+      if (block_mode == VK_BLOCK_ONE) { b = (int)(u_sel * (double)nb); if (b >= nb) b = nb - 1; b += b_off; }
+      else if (block_mode == VK_BLOCK_EACH) b = k % nb + b_off;
       else b = block_mode;
       if (nodes_out) {
         int cnt;
@@ -253,6 +272,24 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
         if (lane == zo) { cand -= 1; nk_k -= 1; cdk -= 1; }          // counts with this token removed
         const double ad = R.alpha[0], aw = R.alpha[1];
         const double Aw = aw * (double)L.V;
+        if (op == 1) {
+          // lane k: exp(xi_k) up to the z term's common denominator (dirichlet.py:168-173, twice)
+          double pr = lane < L.K ? ((double)cdk + ad) * ((double)cand + aw) / ((double)nk_k + Aw) : 0.0;
+          const int zg = lda_gibbs_pick_warp(pr, L.K, r.uniform(), lane);
+          if (zg != zo) {
+            ++acc;
+            const int c_o = __shfl_sync(0xffffffffu, cand, zo), c_g = __shfl_sync(0xffffffffu, cand, zg);
+            if (lane == 0) {
+              R.z[i] = (uint8_t)zg;
+              R.nkw[(int64_t)zo * L.V + w] = (uint16_t)c_o;
+              R.nkw[(int64_t)zg * L.V + w] = (uint16_t)(c_g + 1);
+              R.nk[zo] -= 1; R.nk[zg] += 1;
+              R.ndk[d * L.K + zo] -= 1; R.ndk[d * L.K + zg] += 1;
+            }
+            __syncwarp();
+          }
+          continue;
+        }
         const int zn = lda_sample_topic_reg(cdk, L.K, ad, r.uniform(), lane);
         const int c_o = __shfl_sync(0xffffffffu, cand, zo), n_o = __shfl_sync(0xffffffffu, nk_k, zo);
         const int c_n = __shfl_sync(0xffffffffu, cand, zn), n_n = __shfl_sync(0xffffffffu, nk_k, zn);
@@ -282,6 +319,36 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
         __syncwarp();
         if (lane == 0) { R.nkw[co] -= 1; R.nk[zo] -= 1; R.ndk[d * L.K + zo] -= 1; }
         __syncwarp();
+        if (op == 1) {
+          int zg;
+          const double u_g = r.uniform();
+          if (L.K <= 32) {
+            const int kk = lane < L.K ? lane : 0;
+            double pr = lane < L.K ? ((double)R.ndk[d * L.K + kk] + ad) * ((double)R.nkw[(int64_t)kk * L.V + w] + aw) /
+                                         ((double)R.nk[kk] + Aw) : 0.0;
+            zg = lda_gibbs_pick_warp(pr, L.K, u_g, lane);
+          } else {
+            // sequential inclusive sums (oracle.c gibbs_pick, n > 32): total first, then the first crossing
+            double total = 0.0;
+            for (int t = 0; t < L.K; ++t)
+              total += ((double)R.ndk[d * L.K + t] + ad) * ((double)R.nkw[(int64_t)t * L.V + w] + aw) / ((double)R.nk[t] + Aw);
+            const double thr = u_g * total;
+            double cum = 0.0;
+            zg = L.K - 1;
+            for (int t = 0; t < L.K; ++t) {
+              cum += ((double)R.ndk[d * L.K + t] + ad) * ((double)R.nkw[(int64_t)t * L.V + w] + aw) / ((double)R.nk[t] + Aw);
+              if (thr < cum) { zg = t; break; }
+            }
+          }
+          if (zg != zo) ++acc;
+          __syncwarp();
+          if (lane == 0) {
+            R.z[i] = (uint8_t)zg;
+            R.nkw[(int64_t)zg * L.V + w] += 1; R.nk[zg] += 1; R.ndk[d * L.K + zg] += 1;
+          }
+          __syncwarp();
+          continue;
+        }
         int zn = lda_sample_topic(R.ndk + d * L.K, L.K, ad, r.uniform(), lane);
         int64_t cn = (int64_t)zn * L.V + w;
         double a_n = (double)R.nkw[cn] + aw, b_n = (double)R.nk[zn] + Aw;   // xi = log(a_n / b_n)
@@ -436,11 +503,31 @@ struct LDAModel : Model {
   void reset_to_prior() override { seq(2, 0, n_prop, nullptr, h->next_step()); }
   void refresh() override { seq(3, 0, n_prop, nullptr, 0); }
   void mh(int scope, int block, int K, double *mean_nodes_dev, long long *acc_dev) override {
-    VK_REQUIRE(scope == 0, VK_EINVAL, "lda: only the default scope exists");
-    VK_REQUIRE(n_prop == n_tok, VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
+    VK_REQUIRE(scope == 0, VK_EINVAL, "lda: resimulation_mh is compiled for the default scope");
     int nb = 2 + n_tok;
     VK_REQUIRE(block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || (block >= 0 && block < nb), VK_EINVAL, "lda: bad block");
-    if (K > 0) {
+    run_sites(0, block, nb, 0, K, mean_nodes_dev, acc_dev);
+  }
+  // Enumerative Gibbs (infer/egibbs.py).  Scope 0 = default: its blocks include the two gamma sites, which
+  // PSP.enumerateValues cannot enumerate (psp.py:291-296 raises) -- so `one` / `each` / blocks 0,1 are
+  // errors there exactly as in Lite, and a z site is addressed by its default-scope block index 2 + i.
+  // Scope 1 = "z": the z sites alone, block i = token i -- lda.vnt with ((doc doc_id)) wrapped in
+  // (tag (quote z) <token id> ...); this is the form pinned against Lite (lite_chains.json c4_gibbs).
+  void gibbs(int scope, int block, int K, double *mean_nodes_dev, long long *changed_dev) override {
+    VK_REQUIRE(scope == 0 || scope == 1, VK_EINVAL, "lda: scopes are 0 (default) and 1 (z)");
+    if (scope == 0) {
+      VK_REQUIRE(block >= 2 && block < 2 + n_tok, VK_EUNSUPPORTED,
+                 "gibbs: the default scope holds the gamma hyper-parameter sites, which cannot be enumerated; "
+                 "name a z site (block 2 + token) or use scope z");
+      run_sites(1, block, n_tok, 2, K, mean_nodes_dev, changed_dev);
+    } else {
+      VK_REQUIRE(block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || (block >= 0 && block < n_tok), VK_EINVAL, "lda: bad block");
+      run_sites(1, block >= 0 ? block + 2 : block, n_tok, 2, K, mean_nodes_dev, changed_dev);
+    }
+  }
+  void run_sites(int op, int block, int nb, int b_off, int K, double *mean_nodes_dev, long long *acc_dev) {
+    VK_REQUIRE(n_prop == n_tok, VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
+    if (K > 0 && nb > 0) {
       int n_steps = block == VK_BLOCK_EACH ? K * nb : K;
       uint32_t step0 = h->next_step((uint32_t)n_steps);
       int n_docs_live = 0;   // a doc's maker family exists once a token refers to it (mem, msp.py:28-49)
@@ -466,7 +553,7 @@ struct LDAModel : Model {
       int grid = (int)(need_ctas < cap ? need_ctas : cap);
       lda_mh_kernel<<<grid, 32 * warps, sm, h->stream>>>(rows, L, doc.p, word.p, doclen.p, n_tok, h->P, h->p_base,
                                                          h->seed, step0, n_steps, block, stage, tok_shared, acc_dev,
-                                                         n_docs_live, mean_nodes_dev);
+                                                         n_docs_live, mean_nodes_dev, op, nb, b_off);
       VK_CUDA(cudaGetLastError());
     } else {
       if (acc_dev) VK_CUDA(cudaMemsetAsync(acc_dev, 0, (size_t)h->P * sizeof(long long), h->stream));

@@ -145,6 +145,28 @@ VK_HD int categorical_sim(Stream &r, const double *ps, int n, int stride) {
   }
   return last;
 }
+// normalised probability of one outcome (what exp(logDensityCategorical) is), for enumerative Gibbs
+VK_HD double categorical_prob(int val, const double *ps, int n) {
+  double denom = 0.0;
+  for (int i = 0; i < n; ++i) denom += ps[i];
+  return denom > 0.0 ? ps[val] / denom : 1.0 / (double)n;
+}
+// Enumerative Gibbs selection (infer/egibbs.py:86-88 -> utils.py:170-180): index drawn proportionally to
+// pr[0..n), n <= 32, from one uniform.  The inclusive scan is Kogge-Stone shaped -- the same additions, in
+// the same order, as the warp-shuffle scan of the LDA kernel and as oracle.c's gibbs_pick -- so the index is
+// bit-identical everywhere.  pr is overwritten with the scan.
+VK_HD int gibbs_pick_small(double *pr, int n, double u) {
+  for (int o = 1; o < 32; o <<= 1) {
+    double t[32];
+    for (int i = 0; i < n; ++i) t[i] = i >= o ? pr[i - o] : 0.0;
+    for (int i = 0; i < n; ++i) if (i >= o) pr[i] += t[i];
+  }
+  double total = pr[n - 1];
+  if (!(total > 0.0)) { int k = (int)(u * (double)n); return k < n ? k : n - 1; }
+  double t = u * total;
+  for (int i = 0; i < n; ++i) if (t < pr[i]) return i;
+  return n - 1;
+}
 // utils.py:170-184 (log_categorical): max-shift then categorical.
 VK_HD double log_categorical_logpmf(int val, const double *lps, int n, int stride) {
   double m = VK_NEG_INF;

@@ -108,6 +108,10 @@ struct Model {
   virtual void likelihood_weight() = 0;                 // overwrites h->lw
   virtual void reset_to_prior() = 0;                    // resimulate latents, weights untouched
   virtual void mh(int scope, int block, int K, double *mean_nodes_dev, long long *acc_dev) = 0;
+  // enumerative Gibbs over discrete sites (infer/egibbs.py); changed_dev counts transitions that moved
+  virtual void gibbs(int scope, int block, int K, double *mean_nodes_dev, long long *changed_dev) {
+    throw Error(VK_EUNSUPPORTED, "gibbs: this model has no enumerable sites compiled");
+  }
   virtual void log_likelihood_at(int scope, int block, bool joint, double *out_dev) {
     throw Error(VK_EUNSUPPORTED, "log_likelihood_at/log_joint_at not defined for this model");
   }

@@ -83,6 +83,9 @@ class HMMModel(Model):
 class LDAModel(Model):
     """examples/lda.vnt:18-41 with collapsed make_sym_dir_cat makers and gamma hyperpriors."""
     kind = 4
+    # scope "z": the topic draws alone, block = token index -- lda.vnt with ((doc doc_id)) wrapped in
+    # (tag (quote z) <token> ...); needed by `gibbs` because the default scope also holds the gamma sites
+    scopes = {"default": 0, "z": 1}
 
     def __init__(self, n_topics, vocab_size, n_docs, max_tokens, hyper_shape=1.0, hyper_rate=2.0):
         self.K, self.V, self.n_docs, self.max_tokens = int(n_topics), int(vocab_size), int(n_docs), int(max_tokens)

@@ -162,13 +162,19 @@ class B200TraceSet(object):
     # -- inference ---------------------------------------------------------
     def _scope_block(self, scope, block):
         scope, block = _unbox(scope), _unbox(block)
-        if scope not in ("default", 0):
-            raise VentureException("invalid_argument", "only the default scope is compiled: %r" % (scope,))
+        scopes = getattr(self.model, "scopes", {"default": 0})
+        if scope in scopes:
+            sid = scopes[scope]
+        elif scope in scopes.values():
+            sid = int(scope)
+        else:
+            raise VentureException("invalid_argument", "scope %r is not compiled for this model (have %s)"
+                                   % (scope, sorted(scopes)))
         if isinstance(block, str):
             if block not in _BLOCKS:
                 raise VentureException("invalid_argument", "unknown block %r" % (block,))
-            return 0, _BLOCKS[block]
-        return 0, int(block)
+            return sid, _BLOCKS[block]
+        return sid, int(block)
 
     def primitive_infer(self, exp):
         """exp = [operator, scope, block, ...extra..., transitions]
@@ -179,6 +185,10 @@ class B200TraceSet(object):
             if len(exp) != 4:
                 raise VentureException("invalid_argument", "%s takes (scope block transitions)" % op)
             return self.resimulation_mh(exp[1], exp[2], exp[3])
+        if op == "gibbs":
+            if len(exp) != 4:
+                raise VentureException("invalid_argument", "gibbs takes (scope block transitions)")
+            return self.gibbs(exp[1], exp[2], exp[3])
         if op == "subsampled_mh":
             if len(exp) != 10:
                 raise VentureException(
@@ -196,6 +206,15 @@ class B200TraceSet(object):
         return (out, acc) if return_accepts else out
 
     mh = resimulation_mh
+
+    def gibbs(self, scope, block, transitions, return_changes=False):
+        """(gibbs scope block transitions): enumerative Gibbs on discrete sites
+        (infer/dispatch.py:175-179 -> infer/egibbs.py:42-107)."""
+        s, b = self._scope_block(scope, block)
+        out = self._out()
+        ch = self._out(dtype=np.int64) if return_changes else None
+        _lib.call("vk_gibbs", self._h, s, b, int(transitions), _lib.ptr(out), _lib.ptr(ch))
+        return (out, ch) if return_changes else out
 
     def subsampled_mh(self, scope, block, Nbatch, k0, epsilon, useDeltaKernels, deltaKernelArgs,
                       updateValues, transitions):

@@ -537,7 +537,49 @@ def chain_c4_gibbs(seed=37, P=4, K=3, V=5, n_docs=4, n_per=3, n_gibbs=60):
     return out
 
 
-CHAINS = [("c1", chain_c1), ("c2", chain_c2), ("c3", chain_c3), ("c4", chain_c4), ("c5", chain_c5), ("c4_gibbs", chain_c4_gibbs)]
+# ------------------------------------------------------------------ resample (trace_set.py:202-219)
+def chain_resample(seed=5):
+    """TraceSet._resample_traces draws each child's parent with sampleLogCategorical(log_weights, np_rng)
+    (utils.py:170-180: max-shift, exp, normalise, np_rng.multinomial(1, ps).argmax()).  Here that loop runs
+    on the reference's own functions with a stand-in np_rng whose multinomial inverts the CDF of the ps it is
+    handed at a prescribed uniform U_k; the fixture records U and the parents.  New weights:
+    log_domain_even_out (utils.py:152-157)."""
+    from venture.lite.utils import log_domain_even_out, sampleLogCategorical
+    rng = np.random.default_rng(seed)
+    ninf = float("-inf")
+    cases = {
+        "random": (rng.normal(size=48) * 3).tolist(),
+        "wide_range": (rng.normal(size=33) * 200).tolist(),
+        "some_impossible": [ninf if i % 3 == 0 else float(v) for i, v in enumerate(rng.normal(size=40))],
+        "all_impossible": [ninf] * 17,
+        "ties": [0.0] * 25,
+        "one_heavy": [0.0] * 10 + [30.0] + [0.0] * 10,
+        "single": [-3.5],
+    }
+
+    class Inv(object):
+        def __init__(self, us):
+            self.us, self.k = us, 0
+
+        def multinomial(self, n, ps):
+            cum = np.cumsum(np.asarray(ps, dtype=np.float64))
+            i = int(np.searchsorted(cum, self.us[self.k] * cum[-1], side="right"))
+            self.k += 1
+            out = np.zeros(len(ps), dtype=int)
+            out[min(i, len(ps) - 1)] = 1
+            return out
+    out = {}
+    for name, lw in cases.items():
+        n_new = len(lw)
+        us = rng.random(n_new).tolist()
+        inv = Inv(us)
+        parents = [int(sampleLogCategorical(lw, inv)) for _ in range(n_new)]    # trace_set.py:215-216
+        out[name] = {"lw": [fl(x) for x in lw], "uniforms": us, "parents": parents,
+                     "new_lw": [fl(x) for x in log_domain_even_out(lw, n_new)]}
+    return out
+
+
+CHAINS = [("c1", chain_c1), ("c2", chain_c2), ("c3", chain_c3), ("c4", chain_c4), ("c5", chain_c5), ("c4_gibbs", chain_c4_gibbs), ("resample", chain_resample)]
 
 
 def main():

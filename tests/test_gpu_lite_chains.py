@@ -137,3 +137,21 @@ def test_c5_subsampled_mh_vs_lite():
         assert np.array_equal(st[:, 1], [r["n"][k] for r in recs]), k
         np.testing.assert_allclose(st[:, 2], [unj(r["tstat"][k]) for r in recs], rtol=1e-8)
     np.testing.assert_allclose(rw(), wcol(recs, "w"), rtol=RTOL)
+
+
+def test_resample_parents_vs_lite():
+    """trace_set.py:202-219 on the reference's own sampleLogCategorical / log_domain_even_out."""
+    for name, c in CH["resample"].items():
+        lw = np.array(unj(c["lw"]), dtype=np.float64)
+        P = len(lw)
+        ts = vb.B200TraceSet(vb.NormalNormalModel(), P, seed=1)
+        ts.set_particle_log_weights(lw)
+        x0 = ts.read_site(0)
+        anc = ts.resample(P, mode="multinomial", uniforms=np.array(c["uniforms"]), return_ancestors=True)
+        assert np.array_equal(anc, c["parents"]), name
+        assert np.array_equal(ts.read_site(0), x0[anc]), name          # state moved with the parent
+        new = np.array(unj(c["new_lw"]), dtype=np.float64)
+        got = ts.log_weights
+        assert np.array_equal(np.isneginf(got), np.isneginf(new)), name
+        fin = np.isfinite(new)
+        np.testing.assert_allclose(got[fin], new[fin], rtol=RTOL)

@@ -210,3 +210,17 @@ def test_c4_lda_enumerative_gibbs_chain():
     assert np.array_equal(o.z[:, :n_tok], np.array([r["z_each"] for r in recs]))
     # the tagged z site's scaffold has 8 nodes (7 of lda.vnt's + the tag application)
     assert all(set(r["nodes_one"]) == {8.0} for r in recs)
+
+
+# ------------------------------------------------------------------ resample
+def test_resample_parents_and_weights_vs_lite():
+    """trace_set.py:202-219: parents drawn by the reference's sampleLogCategorical at prescribed uniforms
+    equal the oracle's multinomial ancestors (64-bit fixed-point CDF) at the same uniforms; the new
+    weights equal log_domain_even_out."""
+    for name, c in CH["resample"].items():
+        lw = np.array(unj(c["lw"]), dtype=np.float64)
+        anc = oracle.ancestors(lw, len(lw), 0, uniforms=np.array(c["uniforms"]))
+        assert np.array_equal(anc, c["parents"]), name
+        new = oracle.logsumexp(lw) - np.log(len(lw))
+        for v in unj(c["new_lw"]):
+            assert (np.isneginf(new) and np.isneginf(v)) or abs(new - v) <= 1e-12 * abs(v), name

@@ -2,7 +2,7 @@
 """Secondary measurements: the five BASELINE.json configs on ONE GPU at the
 sizes of SURVEY 8(d) D2, one JSON line each (bench.py stays the headline, C2).
 
-  python tools/bench_configs.py [c1 c1big c3 c4 c5] [--quick]
+  python tools/bench_configs.py [c1 c1big c3 c4 c4gibbs c3gibbs c5] [--quick]
 
 Timed through the public host API (B200TraceSet), wall clock around a
 synchronised region; algorithmic bytes per SURVEY 8(d) D4.
@@ -107,6 +107,43 @@ def c4(P=4096, sweeps=4, quick=False):
          "transitions/s", dt, P * n_sites * sweeps * 100.0, particles=P, sites=n_sites, sweeps=sweeps)
 
 
+def c4gibbs(P=4096, sweeps=4, quick=False):
+    """(gibbs z each 1) sweeps: enumerative Gibbs over the 4096 z sites."""
+    K, V, n_docs, n_per = 16, 1024, 64, 64
+    doc, word = lda_corpus(K, V, n_docs, n_per)
+    n_tok = len(doc)
+    ts = vb.B200TraceSet(vb.LDAModel(K, V, n_docs, n_tok), P, seed=7)
+    ts.observe(doc, word)
+    ts.incorporate()
+    ts.primitive_infer(["gibbs", "z", "each", 1])
+    ts.synchronize()
+    t0 = time.perf_counter()
+    ts.primitive_infer(["gibbs", "z", "each", sweeps])
+    ts.synchronize()
+    dt = time.perf_counter() - t0
+    # D4-style algorithmic bytes: z rw 2 + doc row K*4 + K topic-word cells K*4 + K totals K*4 + 2 cell updates 16 + ids 4
+    emit("c4gibbs", "LDA enumerative-Gibbs z-site transitions/sec (gibbs z each)", P * n_tok * sweeps / dt,
+         "transitions/s", dt, P * n_tok * sweeps * (12.0 * K + 22.0), particles=P, sites=n_tok, sweeps=sweeps)
+
+
+def c3gibbs(P=1 << 20, sweeps=4, quick=False):
+    """(gibbs default each 1) sweeps over state(2..20) of hmm.vnt after the 20 observations."""
+    H = json.load(open(os.path.join(ROOT, "tests", "golden", "hmm.json")))
+    ts = vb.B200TraceSet(vb.HMMModel(H["transition_matrix"], H["emission_matrix"], 1, 20), P, seed=5)
+    for d in H["data"]:
+        ts.observe(d); ts.incorporate(return_increments=False)
+    ts.primitive_infer(["gibbs", "default", "each", 1])
+    ts.synchronize()
+    t0 = time.perf_counter()
+    ts.primitive_infer(["gibbs", "default", "each", sweeps])
+    ts.synchronize()
+    dt = time.perf_counter() - t0
+    T = len(H["data"])
+    # per site: 3 state bytes read + 1 written; the history row (32 B) is read and written once per sweep
+    emit("c3gibbs", "HMM enumerative-Gibbs state-site transitions/sec (gibbs default each)", P * (T - 1) * sweeps / dt,
+         "transitions/s", dt, P * sweeps * 64.0, particles=P, sites=T - 1, sweeps=sweeps)
+
+
 def c5(N=10 ** 7, P=64, K=20, quick=False):
     D = 16
     if quick:
@@ -135,7 +172,7 @@ def c5(N=10 ** 7, P=64, K=20, quick=False):
 def main():
     args = [a for a in sys.argv[1:] if not a.startswith("--")]
     quick = "--quick" in sys.argv
-    which = args or ["c1", "c1big", "c3", "c4", "c5"]
+    which = args or ["c1", "c1big", "c3", "c4", "c4gibbs", "c3gibbs", "c5"]
     for w in which:
         if w == "c1":
             c1(1000, 200 if quick else 1000)
@@ -145,6 +182,10 @@ def main():
             c3(1 << 20, quick)
         elif w == "c4":
             c4(4096, 1 if quick else 4, quick)
+        elif w == "c4gibbs":
+            c4gibbs(4096, 1 if quick else 4, quick)
+        elif w == "c3gibbs":
+            c3gibbs(1 << 20, 1 if quick else 4, quick)
         elif w == "c5":
             c5(quick=quick)
 

@@ -13,6 +13,7 @@ meaning of the reference's inference SPs:
   resample(particles)                         inference_sps.py:536-551
   likelihood_weight()                         inference_sps.py:602-606
   resimulation_mh / mh(scope, block, transitions)        :234-241
+  gibbs(scope, block, transitions)                       :253-267
   subsampled_mh(scope, block, Nbatch, k0, epsilon, useDeltaKernels,
                 deltaKernelArgs, updateValues, transitions)   :678-694
   incorporate(), log_likelihood_at / log_joint_at(scope, block)
@@ -60,6 +61,10 @@ class B200Plugin(object):
 
     mh = resimulation_mh
 
+    def gibbs(self, _inferrer, scope, block, transitions):
+        return self.trace_set.primitive_infer(
+            ["gibbs", _scalar(scope), _scalar(block), int(_scalar(transitions))]).tolist()
+
     def subsampled_mh(self, _inferrer, scope, block, Nbatch, k0, epsilon, useDeltaKernels, deltaKernelArgs,
                       updateValues, transitions):
         args = [_scalar(a) for a in (scope, block, Nbatch, k0, epsilon, useDeltaKernels, deltaKernelArgs,
@@ -77,7 +82,7 @@ class B200Plugin(object):
 
     def callbacks(self):
         names = ["resample", "resample_systematic", "likelihood_weight", "incorporate", "resimulation_mh", "mh",
-                 "subsampled_mh", "log_likelihood_at", "log_joint_at", "particle_log_weights"]
+                 "gibbs", "subsampled_mh", "log_likelihood_at", "log_joint_at", "particle_log_weights"]
         return dict((PREFIX + n, getattr(self, n)) for n in names)
 
 

@@ -17,14 +17,17 @@
  * against the reference's own functions in tests/ (see tests/golden/make_golden.py
  * and tests/golden/*.json).
  *
- * Pinning status: logsumexp, logistic family, sequentialTest, categorical /
- * dirichlet / dir-cat densities, normal logDensity are pinned against the
- * reference's own golden vectors and against the reference functions executed
- * here (tests/golden/make_golden.py).  gamma/beta logDensity values are pinned
- * against scipy only (the reference tests only integrate / KS them).
- * Resampling ancestors: the reference is multinomial via numpy; parity there is
- * defined against THIS restatement ("parity unpinned" vs the reference for
- * ancestor indices, distributional tests only).
+ * Pinning status: PINNED against the reference run in this container.
+ *  (1) Whole chains of the five site programs (likelihood_weight, makeConsistent, resimulation MH incl. the
+ *      AAA sites, enumerative Gibbs, subsampled MH, log_likelihood_at / log_joint_at) and the resampling
+ *      parents equal what the reference's Lite backend computes when its RNG objects are fed this oracle's
+ *      draws (orc_draw): tests/golden/make_lite_chains.py -> tests/golden/lite_chains.json ->
+ *      tests/test_oracle_lite_chains.py (1e-12 relative; discrete state and node counts exact).
+ *  (2) logsumexp, logistic family, sequentialTest, every PSP logDensity on the path are pinned against the
+ *      reference's own functions executed from its files and against the reference tests' golden tables
+ *      (tests/golden/make_golden.py, tests/test_oracle_golden.py).  gamma/beta logDensity go through scipy
+ *      in the reference (no pinned version; scipy 1.18.1 here).
+ * Distributional only (by necessity): the samplers' maps from uniforms to values (MT19937 vs Philox).
  */
 #include <math.h>
 #include <stdint.h>

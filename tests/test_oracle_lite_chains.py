@@ -224,3 +224,20 @@ def test_resample_parents_and_weights_vs_lite():
         new = oracle.logsumexp(lw) - np.log(len(lw))
         for v in unj(c["new_lw"]):
             assert (np.isneginf(new) and np.isneginf(v)) or abs(new - v) <= 1e-12 * abs(v), name
+
+
+# ------------------------------------------------------------------ provenance
+def test_c1_fixture_regenerates_from_live_lite():
+    """Where the py3 rendering of the reference's Lite backend exists (oracle/_ref, built from /root/reference by
+    oracle/lite_py3/build_lite_py3.py -- this container, not the GPU box), run Lite again and demand the
+    committed C1 chain bit for bit.  (All chains regenerate identically; the others take minutes.)"""
+    import os
+    import sys
+    ref = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "venture")
+    if not os.path.isdir(ref):
+        pytest.skip("oracle/_ref not built here")
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import make_lite_chains as M
+    import json
+    fresh = json.loads(json.dumps(M.chain_c1()))
+    assert fresh == CH["c1"]

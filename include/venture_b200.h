@@ -175,6 +175,26 @@ int vk_resample(vk_particles *h, int64_t n_new, int mode,
 int vk_mh(vk_particles *h, int32_t scope, int32_t block, int32_t transitions,
           double *mean_nodes_out_host, int64_t *accepted_out_host);
 
+/* ---- sharded resample over NVLink peer memory ------------------------------------
+ * python/lib/engine/trace_set.py:202-235 for a particle set block-partitioned over the GPUs of one node,
+ * one process per GPU: rank g owns global particles [g*P, (g+1)*P) (vk_set_particle_base).  No NCCL
+ * collective and no host synchronisation on the path: three scalars per rank travel through mailboxes in
+ * peer memory, ancestor indices are stored straight into the owning rank's array, ancestor rows are
+ * pulled with peer loads (csrc/p2p_resample.cuh has the protocol).  Result bit-identical to vk_resample
+ * on a single GPU holding all world*P particles.
+ *   vk_p2p_export  allocates the mailbox and writes this handle's CUDA IPC handles (64 bytes each:
+ *                  mailbox, ancestor array, both buffers of every state array) to handles_out.
+ *   vk_p2p_open    all_handles = the exports of ranks 0..world-1 concatenated (exchange them with any
+ *                  host mechanism, e.g. torch.distributed.all_gather_object); opens the peers' memory.
+ *   vk_p2p_resample  the resample itself (mode as vk_resample); stream-ordered, returns immediately.
+ *                  Every rank must call it the same number of times.
+ *   vk_p2p_status  synchronises; *timed_out = 1 if a peer never arrived at an exchange (~2 s bound);
+ *                  *lse_out = global logsumexp of the weights before the last resample. */
+int vk_p2p_export(vk_particles *h, unsigned char *handles_out, int32_t max_handles, int32_t *n_handles_out);
+int vk_p2p_open(vk_particles *h, int32_t world, int32_t rank, const unsigned char *all_handles, int32_t n_handles);
+int vk_p2p_resample(vk_particles *h, int mode);
+int vk_p2p_status(vk_particles *h, int32_t *timed_out, double *lse_out);
+
 /* Enumerative Gibbs, `(gibbs scope block transitions)`: infer/dispatch.py:175-179 ->
  * infer/egibbs.py:42-107 (EnumerativeGibbsOperator under mixMH).  For a discrete site every candidate
  * value is weighted by its regen weight, the new value is drawn proportionally and always accepted.

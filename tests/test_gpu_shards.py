@@ -153,3 +153,44 @@ def test_observation_shards_sum_to_unsharded_subsampled_mh():
         _lib.call("vk_ssmh_stats", p._h, K, _lib.ptr(st))
         np.testing.assert_array_equal(st[:, 0], stats_full[:, 0])
         np.testing.assert_allclose(st[:, 1], stats_full[:, 1], rtol=1e-12)
+
+
+@pytest.mark.parametrize("mode", ["systematic", "multinomial"])
+def test_peer_memory_resample_world_of_one_matches_vk_resample(mode):
+    """csrc/p2p_resample.cuh with world = 1 (own mailbox, own buffers, no IPC import): the whole kernel
+    sequence -- exchanges, offspring / search into the ancestor array, gather, buffer swap -- must reproduce
+    vk_resample bit for bit.  (world > 1 over NVLink: tools/check_multi_gpu.py.)"""
+    import ctypes
+    from venturecxx_b200 import _lib
+    from helpers import golden
+    H = golden("hmm.json")
+    P, T = 50001, 10
+    model = vb.HMMModel(H["transition_matrix"], H["emission_matrix"], 1, 20)
+    a = vb.B200TraceSet(model, P, seed=91)
+    b = vb.B200TraceSet(model, P, seed=91)
+    buf = (ctypes.c_ubyte * (64 * 16))()
+    n = ctypes.c_int32()
+    _lib.call("vk_p2p_export", a._h, buf, 16, ctypes.byref(n))
+    assert n.value == 2 + 2 * 2                     # mailbox, ancestors, two buffers for each of (cur, hist)
+    _lib.call("vk_p2p_open", a._h, 1, 0, buf, n.value)
+    m = _lib.RESAMPLE_SYSTEMATIC if mode == "systematic" else _lib.RESAMPLE_MULTINOMIAL
+    for t, d in enumerate(H["data"][:T]):
+        a.observe(d); b.observe(d)
+        a.incorporate(); b.incorporate()
+        lse_ref = b.logsumexp()
+        _lib.call("vk_p2p_resample", a._h, m)
+        b.resample(P, mode=mode)
+        e, lse = ctypes.c_int32(), ctypes.c_double()
+        _lib.call("vk_p2p_status", a._h, ctypes.byref(e), ctypes.byref(lse))
+        assert e.value == 0
+        assert abs(lse.value - lse_ref) <= 1e-12 * abs(lse_ref)
+        assert a.rng_step == b.rng_step
+        for tt in range(t + 1):
+            assert np.array_equal(a.read_site(tt), b.read_site(tt)), (t, tt)
+        np.testing.assert_allclose(a.log_weights, b.log_weights, rtol=1e-12)
+    # all weights impossible -> uniform ancestors (utils.py:95-99), same as the single-GPU path
+    a.set_particle_log_weights(np.full(P, -np.inf)); b.set_particle_log_weights(np.full(P, -np.inf))
+    _lib.call("vk_p2p_resample", a._h, m)
+    b.resample(P, mode=mode)
+    assert np.array_equal(a.read_site(T - 1), b.read_site(T - 1))
+    assert np.all(np.isneginf(a.log_weights))

@@ -66,6 +66,35 @@ def main():
         out["hmm_" + mode] = {"particles": P, "steps": T, "sharded_resample_ms_per_step": 1e3 * t_sh / T}
         sh.local.close(); ref.close()
 
+    # ---- 1b. the same filter with the NVLink peer-memory resample (no collective, no host sync) -------
+    for mode in ("systematic", "multinomial"):
+        P_local = 40000 + 17
+        P = world * P_local
+        T = 8
+        model = vb.HMMModel(H["transition_matrix"], H["emission_matrix"], 1, 20)
+        sh = ShardedTraceSet(model, P_local, seed=78, device=local)
+        sh.enable_peer_memory()
+        ref = vb.B200TraceSet(model, P, seed=78, device=local)
+        for t, d in enumerate(H["data"][:T]):
+            sh.observe(d); ref.observe(d)
+            sh.incorporate(); ref.incorporate()
+            assert sh.local.rng_step == ref.rng_step
+            sh.resample(mode=mode)
+            timed_out, lse = sh.peer_status()
+            assert not timed_out, "a peer never arrived at an exchange"
+            lse_ref = ref.logsumexp()
+            ref.resample(P, mode=mode)
+            assert abs(lse - lse_ref) <= 1e-12 * abs(lse_ref), (lse, lse_ref)
+            dist.barrier()                      # peers finished reading before anyone inspects / moves on
+            for tt in range(t + 1):
+                a = sh.read_site(tt)
+                b = ref.read_site(tt)[rank * P_local:(rank + 1) * P_local]
+                assert np.array_equal(a, b), ("peer-memory history differs", mode, t, tt, rank)
+            np.testing.assert_allclose(sh.log_weights, ref.log_weights[rank * P_local:(rank + 1) * P_local], rtol=1e-12)
+        out["hmm_peer_" + mode] = "bit-identical to the single-GPU run"
+        dist.barrier()
+        sh.local.close(); ref.close()
+
     # ---- 2. observation-sharded subsampled MH vs single GPU ------------------------
     N, D, P = 40000, 16, 64
     X = np.random.default_rng(4).normal(size=(N, D))
@@ -115,6 +144,27 @@ def main():
         sh.local.close()
     out["c3_sharded"] = {"particles": P_local * world, "steps": T, "ms_per_step": 1e3 * dt / T,
                          "particle_steps_per_sec": P_local * world * T / dt, "tvd_last": float(tvd)}
+    assert tvd < 0.01, tvd
+    # ---- 3b. the same, peer-memory resample: the whole filter is stream-ordered, one sync at the end ----
+    for rep in range(2):
+        sh = ShardedTraceSet(model, P_local, seed=5 + rep, device=local)
+        sh.enable_peer_memory()
+        torch.cuda.synchronize(); dist.barrier()
+        t0 = time.perf_counter()
+        for d in H["data"]:
+            sh.observe(d); sh.incorporate(return_increments=False); sh.resample(mode="systematic")
+        sh.local.synchronize(); torch.cuda.synchronize(); dist.barrier()
+        dt = time.perf_counter() - t0
+        timed_out, _ = sh.peer_status()
+        assert not timed_out
+        m = np.bincount(sh.read_site(T - 1).astype(int), minlength=6)[1:6].astype(np.float64)
+        mt = torch.tensor(m, device="cuda")
+        dist.all_reduce(mt)
+        tvd = 0.5 * np.abs(mt.cpu().numpy() / (P_local * world) - np.array(H["filtered_marginals"][T - 1])).sum()
+        dist.barrier()
+        sh.local.close()
+    out["c3_sharded_peer_memory"] = {"particles": P_local * world, "steps": T, "ms_per_step": 1e3 * dt / T,
+                                     "particle_steps_per_sec": P_local * world * T / dt, "tvd_last": float(tvd)}
     assert tvd < 0.01, tvd
     dist.barrier()
     if rank == 0:

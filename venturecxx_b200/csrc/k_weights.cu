@@ -14,6 +14,7 @@
 // order).  The CDF is a 64-bit FIXED-POINT prefix sum so that ancestor
 // indices do not depend on the association order of a parallel scan, on the
 // GPU count, or on the platform's rounding: exact integers everywhere.
+#include <string.h>
 #include "vk_common.cuh"
 #include "weights.cuh"
 #include "models.cuh"
@@ -855,5 +856,7 @@ void shard_build_cdf(vk_particles *h, double global_max, int frac_bits) {
   build_fixed_cdf(h, nullptr, global_max, frac_bits);
   VK_CUDA(cudaGetLastError());
 }
+
+#include "p2p_resample.cuh"
 
 }  // namespace vk

@@ -138,6 +138,7 @@ int vk_destroy(vk_particles *h) {
   if (!h) return VK_OK;
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
+  vk::p2p_release(h);
   delete h->model; h->model = nullptr;
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
@@ -300,6 +301,35 @@ int vk_mh(vk_particles *h, int32_t scope, int32_t block, int32_t transitions, do
     VK_CUDA(cudaMemcpyAsync(accepted_out_host, acc, (size_t)h->P * sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
   o.finish();
   if (acc && !mean_nodes_out_host) VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+
+// ---- peer-memory (NVLink) resampling across the GPUs of one node: csrc/p2p_resample.cuh -------------
+int vk_p2p_export(vk_particles *h, unsigned char *handles_out, int32_t max_handles, int32_t *n_handles_out) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(handles_out && n_handles_out, VK_EINVAL, "vk_p2p_export: null output");
+  *n_handles_out = vk::p2p_export(h, handles_out, max_handles);
+  VK_CATCH
+}
+int vk_p2p_open(vk_particles *h, int32_t world, int32_t rank, const unsigned char *all_handles, int32_t n_handles) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(all_handles, VK_EINVAL, "vk_p2p_open: null handles");
+  vk::p2p_open(h, world, rank, all_handles, n_handles);
+  VK_CATCH
+}
+int vk_p2p_resample(vk_particles *h, int mode) {
+  VK_TRY check_handle(h); use_device(h);
+  vk::p2p_resample(h, mode);
+  // trace_set.py:207: resample ends with incorporate()
+  h->model->make_consistent(nullptr);
+  VK_CATCH
+}
+int vk_p2p_status(vk_particles *h, int32_t *timed_out, double *lse_out) {
+  VK_TRY check_handle(h); use_device(h);
+  int e = 0; double l = 0.0;
+  vk::p2p_status(h, &e, &l);
+  if (timed_out) *timed_out = e;
+  if (lse_out) *lse_out = l;
   VK_CATCH
 }
 

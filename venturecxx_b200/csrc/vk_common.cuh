@@ -94,6 +94,7 @@ struct vk_particles {
   vk::DevBuf<double> tile_exp;  // per-tile sums of exp(lw - max)
   vk::DevBuf<unsigned int> counters;
   vk::Model *model = nullptr;
+  void *p2p = nullptr;          // vk::P2P (p2p_resample.cuh): peer-memory resampling state
   uint32_t next_step(uint32_t n = 1) { uint32_t s = step; step += n; return s; }
 };
 

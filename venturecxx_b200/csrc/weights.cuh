@@ -20,4 +20,9 @@ size_t packed_row_bytes(vk_particles *h);
 void pack_state(vk_particles *h, const int32_t *idx_dev, int64_t n, void *packed_dev, bool unpack);
 void shard_weight_max(vk_particles *h);
 void shard_build_cdf(vk_particles *h, double global_max, int frac_bits);
+int p2p_export(vk_particles *h, unsigned char *handles_out, int max_handles);
+void p2p_open(vk_particles *h, int world, int rank, const unsigned char *all_handles, int n_handles);
+void p2p_resample(vk_particles *h, int mode);
+void p2p_status(vk_particles *h, int *err_out, double *lse_out);
+void p2p_release(vk_particles *h);
 }  // namespace vk

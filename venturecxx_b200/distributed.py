@@ -278,10 +278,46 @@ class ShardedTraceSet(object):
     def __getattr__(self, name):       # per-particle operations: no communication
         return getattr(self.local, name)
 
+    def enable_peer_memory(self):
+        """Switch `resample` to the NVLink peer-memory path (csrc/p2p_resample.cuh): CUDA IPC handles of the
+        mailbox, the ancestor array and the state buffers are exchanged ONCE here (host side, any backend of
+        the process group); afterwards a resample is a stream-ordered kernel sequence with no collective and
+        no host synchronisation.  Ranks must be the GPUs of one node with peer access."""
+        import ctypes
+        import torch.distributed as dist
+        from . import _lib
+        buf = (ctypes.c_ubyte * (64 * 16))()
+        n = ctypes.c_int32()
+        _lib.call("vk_p2p_export", self.local._h, buf, 16, ctypes.byref(n))
+        mine = bytes(buf[:64 * n.value])
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, mine, group=self.group)
+        if any(len(g) != len(mine) for g in gathered):
+            from .exception import VentureException
+            raise VentureException("evaluation", "peer-memory resample: ranks hold different models")
+        blob = b"".join(gathered)
+        arr = (ctypes.c_ubyte * len(blob)).from_buffer_copy(blob)
+        _lib.call("vk_p2p_open", self.local._h, self.world, self.rank, arr, n.value)
+        dist.barrier(group=self.group)
+        self.peer_memory = True
+
+    def peer_status(self):
+        """(timed_out, global logsumexp before the last resample); synchronises this rank's stream."""
+        import ctypes
+        from . import _lib
+        e, lse = ctypes.c_int32(), ctypes.c_double()
+        _lib.call("vk_p2p_status", self.local._h, ctypes.byref(e), ctypes.byref(lse))
+        return bool(e.value), lse.value
+
     def resample(self, P=None, mode="multinomial"):
         if P is not None and int(P) != self.n_particles:
             from .exception import VentureException
             raise VentureException("invalid_argument", "resample: P must equal the particle count")
+        if getattr(self, "peer_memory", False):
+            from . import _lib
+            _lib.call("vk_p2p_resample", self.local._h,
+                      _lib.RESAMPLE_SYSTEMATIC if mode == "systematic" else _lib.RESAMPLE_MULTINOMIAL)
+            return None          # stream-ordered; peer_status() returns the LSE when it is wanted
         import torch
         step = self.local.rng_step
         self.local.rng_step = step + 1

@@ -6,7 +6,7 @@ regression, D = 16 weights, N = 10^4 synthetic observations, 65 536 particles
 per GPU, program `(resimulation_mh default one 160)` (10 sweeps) per step.
 
   python bench.py [--gpus N] [--steps K] [--warmup W]
-  python bench.py --impl reference ...     # CPU arm: oracle on all host cores
+  python bench.py --impl reference ...     # CPU arm: the reference's Lite backend (oracle/_ref) on all host cores
 
 One JSON line on rank 0.  `value` = particle-site MH transitions/s with the
 particle state resident in HBM (device-timed, max over ranks); `e2e` = the same
@@ -132,29 +132,109 @@ def cpu_baseline(X, y, D, N, T, seconds_target=12.0):
                       % (Ps, Ts, N, D, dt)}, dt
 
 
+# ---- reference arm: the reference's own Lite backend (oracle/_ref) on the host cores -------------------
+_LITE = {}
+
+
+def _lite_worker_init(X, y, D, N, seed_base):
+    """One Lite trace of the C2 model per worker process (Lite is single-threaded per trace; the reference
+    parallelises over traces with worker processes, python/lib/multiprocess.py)."""
+    import warnings
+    warnings.simplefilter("ignore")
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))
+    import venture.lite.value as vv
+    import venture.value.dicts as vd
+    from venture.lite.trace import Trace
+    t = Trace(seed_base + os.getpid() % 100003)
+    S, n = vd.symbol, vd.number
+    for j in range(D):
+        t.eval(j + 1, [S("normal"), n(0.0), n(1.0)])
+        t.bindInGlobalEnv("w_%d" % j, j + 1)
+    t.eval(D + 1, [S("array")] + [S("w_%d" % j) for j in range(D)])
+    t.bindInGlobalEnv("w", D + 1)
+    for i in range(N):
+        did = D + 2 + i
+        t.eval(did, [S("log_odds_flip"), [S("vector_dot"), S("w"), [S("array")] + [n(float(v)) for v in X[i]]]])
+        t.observe(did, vd.boolean(bool(y[i])))
+    t.makeConsistent()
+    _LITE["trace"] = t
+    _LITE["exp"] = lambda k: ["resimulation_mh", vv.VentureSymbol("default"), vv.VentureSymbol("one"), vv.VentureNumber(k)]
+
+
+def _lite_worker_step(k):
+    t0 = time.perf_counter()
+    _LITE["trace"].primitive_infer(_LITE["exp"](k))     # infer/dispatch.py:130-136, the stock code path
+    return time.perf_counter() - t0
+
+
+def _lite_worker_ready(_):
+    return "trace" in _LITE
+
+
+def run_reference_lite(args, X, y, D, N, T):
+    """`(resimulation_mh default one k)` on one real Lite trace per host core, N and D as in the GPU arm.
+    A step is k = 1 transition per trace (a Lite transition of this model walks 2N + 3 nodes: ~3 s)."""
+    import multiprocessing as mp
+    cores = os.cpu_count() or 1
+    try:                                    # a Lite trace of this model holds ~0.36 GB: stay inside the box's memory
+        with open("/proc/meminfo") as f:
+            avail_kb = [int(ln.split()[1]) for ln in f if ln.startswith("MemAvailable")][0]
+        cores = max(1, min(cores, int(avail_kb / 1024 / 1024 / 0.75)))
+    except Exception:
+        cores = min(cores, 16)
+    cores = min(cores, 64)
+    ctx = mp.get_context("fork")
+    t_build = time.perf_counter()
+    pool = ctx.Pool(cores, initializer=_lite_worker_init, initargs=(X, y, D, N, 1000))
+    assert all(pool.map(_lite_worker_ready, range(cores), chunksize=1))
+    t_build = time.perf_counter() - t_build
+    k = 1
+    times = []
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        pool.map(_lite_worker_step, [k] * cores, chunksize=1)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            times.append(dt)
+    pool.close(); pool.join()
+    tot = sum(times)
+    value = cores * k * len(times) / tot
+    cb = {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
+          "sample": "%d Lite traces (one per core, py3 rendering of backend/lite in oracle/_ref) x %d transition(s) per "
+                    "step of the same N=%d, D=%d model; traces built in %.1f s outside the timed region"
+                    % (cores, k, N, D, t_build)}
+    return value, 1e3 * tot / max(len(times), 1), cb, \
+        "the reference's Lite backend itself (backend/lite, rendered importable under Python 3 by " \
+        "oracle/lite_py3/build_lite_py3.py): scaffold construction + detach + regen over 2N+3 nodes per transition"
+
+
 def run_reference(args, X, y, D, N, T):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    vals, last = [], None
-    for i in range(args.warmup + args.steps):
-        cb, dt = cpu_baseline(X, y, D, N, T, seconds_target=4.0)
-        if i >= args.warmup:
-            vals.append((cb, dt))
-    tot_t = sum(dt for _, dt in vals)
-    value = float(np.mean([cb["value"] for cb, _ in vals]))
-    cb = dict(vals[-1][0]); cb["value"] = value
+    if os.path.isdir(os.path.join(ROOT, "oracle", "_ref", "venture", "lite")):
+        value, ms, cb, note = run_reference_lite(args, X, y, D, N, T)
+    else:
+        vals = []
+        for i in range(args.warmup + args.steps):
+            cb, dt = cpu_baseline(X, y, D, N, T, seconds_target=4.0)
+            if i >= args.warmup:
+                vals.append((cb, dt))
+        value = float(np.mean([cb["value"] for cb, _ in vals]))
+        ms = 1e3 * sum(dt for _, dt in vals) / max(len(vals), 1)
+        cb = dict(vals[-1][0]); cb["value"] = value
+        note = ("oracle/_ref (the py3 rendering of the reference's Lite backend) is not present on this box; this arm "
+                "times the oracle port (C restatement of the Lite algorithm, OpenMP over particles)")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(len(vals), 1),
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "C2 Bayesian logistic regression, single-site resimulation_mh (default one)",
                    "particles_per_gpu": args.particles, "observations": N, "D": D, "transitions_per_step": T},
         "cpu_baseline": cb,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "obs_loglik_evals_per_sec": value * N,
-        "note": "reference Lite/Puma cannot run here (python2 / GSL / Boost absent); this arm times the oracle "
-                "(C restatement of the Lite algorithm: full vector_dot + log_odds_flip recompute per proposal)",
+        "note": note,
     }))
 
 

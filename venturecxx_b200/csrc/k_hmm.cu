@@ -16,6 +16,7 @@
 // 4+4 B cur, 1 B hist, 8+8 B lw per particle-step.
 #include "vk_common.cuh"
 #include "sp_math.cuh"
+#include "lse_finish.cuh"
 
 namespace vk {
 
@@ -31,13 +32,15 @@ struct HMMTables {
 __global__ void __launch_bounds__(256)
 hmm_step_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, int t /*0-based*/,
                 double *__restrict__ lw, double *__restrict__ incr, HMMTables tb, int symbol /*1-based*/,
-                int64_t P, int64_t p_base, uint64_t seed, uint32_t step, int accumulate_incr) {
+                int64_t P, int64_t p_base, uint64_t seed, uint32_t step, int accumulate_incr,
+                double *__restrict__ red, unsigned int *__restrict__ counter) {
   extern __shared__ double sh[];
   double *tr = sh;                       // n_rows*S
   double *em = sh + tb.n_rows * tb.S;    // S*O
   for (int i = threadIdx.x; i < tb.n_rows * tb.S; i += blockDim.x) tr[i] = tb.trans[i];
   for (int i = threadIdx.x; i < tb.S * tb.O; i += blockDim.x) em[i] = tb.emit[i];
   __syncthreads();
+  double mx = -INFINITY, mn = INFINITY, nanf = 0.0;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
        p += (int64_t)gridDim.x * blockDim.x) {
     int s;
@@ -52,9 +55,14 @@ hmm_step_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad,
     hist[p * Tpad + t] = (uint8_t)s;
     double w = categorical_logpmf(symbol - 1, em + (s - 1) * tb.O, tb.O, 1);
     if (w != w) w = -INFINITY;
-    lw[p] += w;
+    double v = lw[p] + w;
+    lw[p] = v;
+    if (v != v) nanf = 1.0; else { mx = fmax(mx, v); mn = fmin(mn, v); }
     if (incr) incr[p] = accumulate_incr ? incr[p] + w : w;
   }
+  // the filter resamples right after this step: reduce (max, min, NaN flag) of the weights just written so
+  // that vk_resample / vk_p2p_resample can skip their own read pass (lse_finish.cuh)
+  lse_minmax_finish(mx, mn, nanf, red, counter);
 }
 
 // likelihood_weight: resimulate states 2..t from the prior, lw := sum_t log E
@@ -285,10 +293,12 @@ struct HMMModel : Model {
     for (; T < n; ++T) {
       uint32_t step = h->next_step();
       hmm_step_kernel<<<grid(), 256, smem, h->stream>>>(cur, hist, Tpad, T, h->lw.p, incr_dev, tb, symbols_host[T],
-                                                        h->P, h->p_base, h->seed, step, first ? 0 : 1);
+                                                        h->P, h->p_base, h->seed, step, first ? 0 : 1, h->red.p,
+                                                        h->counters.p);
       first = false;
     }
     VK_CUDA(cudaGetLastError());
+    h->lw_minmax_fresh = true;     // red[0..2] describe the weights as they are now
   }
   void run_prior(bool write_lw) {
     T = (int)symbols_host.size();

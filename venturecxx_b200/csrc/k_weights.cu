@@ -18,54 +18,37 @@
 #include "vk_common.cuh"
 #include "weights.cuh"
 #include "models.cuh"
+#include "lse_finish.cuh"
 
 namespace vk {
 
 // red layout (doubles): [0]=max [1]=min [2]=nan flag [3]=sum exp [4]=lse
 // [8 ..] per-block partials (3 per block)
-static const int RED_PART = 8;
-
 __global__ void __launch_bounds__(256)
 lse_pass1_kernel(const double *__restrict__ a, int64_t n, double *red, unsigned int *counter) {
-  __shared__ double sh[3][32];
   double mx = -INFINITY, mn = INFINITY, nanf = 0.0;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    double v = a[i];
-    if (v != v) nanf = 1.0;
-    else { mx = fmax(mx, v); mn = fmin(mn, v); }
-  }
-  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
-  if (lane == 0) { sh[0][w] = mx; sh[1][w] = mn; sh[2][w] = nanf; }
-  __syncthreads();
-  if (w == 0) {
-    int nw = blockDim.x >> 5;
-    mx = lane < nw ? sh[0][lane] : -INFINITY;
-    mn = lane < nw ? sh[1][lane] : INFINITY;
-    nanf = lane < nw ? sh[2][lane] : 0.0;
-    mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
-    if (lane == 0) {
-      red[RED_PART + 3 * blockIdx.x + 0] = mx;
-      red[RED_PART + 3 * blockIdx.x + 1] = mn;
-      red[RED_PART + 3 * blockIdx.x + 2] = nanf;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+  if ((((uintptr_t)a) & 15) == 0) {      // 16-byte loads, four in flight per thread
+    const double2 *a2 = reinterpret_cast<const double2 *>(a);
+    const int64_t n2 = n >> 1;
+#pragma unroll 4
+    for (int64_t i = tid; i < n2; i += stride) {
+      double2 v = a2[i];
+      if (v.x != v.x) nanf = 1.0; else { mx = fmax(mx, v.x); mn = fmin(mn, v.x); }
+      if (v.y != v.y) nanf = 1.0; else { mx = fmax(mx, v.y); mn = fmin(mn, v.y); }
+    }
+    if ((n & 1) && tid == 0) {
+      double v = a[n - 1];
+      if (v != v) nanf = 1.0; else { mx = fmax(mx, v); mn = fmin(mn, v); }
+    }
+  } else {
+    for (int64_t i = tid; i < n; i += stride) {
+      double v = a[i];
+      if (v != v) nanf = 1.0;
+      else { mx = fmax(mx, v); mn = fmin(mn, v); }
     }
   }
-  __shared__ bool last;
-  __threadfence();
-  if (threadIdx.x == 0) last = (atomicAdd(counter, 1u) == gridDim.x - 1);
-  __syncthreads();
-  if (last && w == 0) {
-    __threadfence();
-    mx = -INFINITY; mn = INFINITY; nanf = 0.0;
-    for (int b = lane; b < (int)gridDim.x; b += 32) {
-      mx = fmax(mx, red[RED_PART + 3 * b + 0]);
-      mn = fmin(mn, red[RED_PART + 3 * b + 1]);
-      nanf = fmax(nanf, red[RED_PART + 3 * b + 2]);
-    }
-    mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
-    if (lane == 0) { red[0] = mx; red[1] = mn; red[2] = nanf; *counter = 0; }
-  }
+  lse_minmax_finish(mx, mn, nanf, red, counter);
 }
 
 // sum exp(a - m) with per-thread accumulation, block tree, last-block finish.
@@ -392,13 +375,21 @@ void gather_state(vk_particles *h, const int32_t *anc_dev, int64_t n_new) {
 //   kf(c) = smallest k with thr_k >= c = ceil((ceil(c*den/W) - U0) / 2^32),  den = n_new<<32
 // (exact 128-bit integers; identical to searching the CDF for every child).
 typedef unsigned __int128 u128_t;
+// Evaluated without a 128-bit division (hundreds of instructions in software): thr_k >= c  <=>
+// ((k<<32)+U0) * W >= c * (n_new<<32), two 64x64->128 products; k starts from a double-precision estimate
+// that is off by at most one and is corrected with that exact test.  Same integer as the closed form.
+__device__ __forceinline__ bool child_reaches(uint64_t k, uint64_t c, uint64_t W, int64_t n_new, uint64_t U0) {
+  u128_t lhs = (u128_t)((k << 32) + U0) * (u128_t)W;
+  u128_t rhs = ((u128_t)c * (u128_t)(uint64_t)n_new) << 32;
+  return lhs >= rhs;
+}
 __device__ __forceinline__ int64_t first_child_at_least(uint64_t c, uint64_t W, int64_t n_new, uint64_t U0) {
   if (c == 0) return 0;
-  u128_t den = (u128_t)(uint64_t)n_new << 32;
-  u128_t need = ((u128_t)c * den + (u128_t)(W - 1)) / (u128_t)W;
-  if (need <= (u128_t)U0) return 0;
-  u128_t k = (need - (u128_t)U0 + (u128_t)0xFFFFFFFFull) >> 32;
-  return k > (u128_t)(uint64_t)n_new ? n_new : (int64_t)(uint64_t)k;
+  double est = (double)c * (double)n_new / (double)W - (double)U0 * (1.0 / 4294967296.0);
+  int64_t k = est <= 0.0 ? 0 : (est >= (double)n_new ? n_new : (int64_t)est);
+  while (k < n_new && !child_reaches((uint64_t)k, c, W, n_new, U0)) ++k;
+  while (k > 0 && child_reaches((uint64_t)(k - 1), c, W, n_new, U0)) --k;
+  return k;
 }
 __device__ __forceinline__ uint64_t systematic_U0(const double *uniforms, uint64_t seed, uint32_t step) {
   double u;
@@ -683,7 +674,10 @@ void resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms_d
   int n_tiles = (int)((P + SCAN_TILE - 1) / SCAN_TILE);
   if (h->red_u.n < (size_t)n_tiles + 1) h->red_u.alloc((size_t)n_tiles + 1);
   if (h->tile_exp.n < (size_t)n_tiles) h->tile_exp.alloc((size_t)n_tiles);
-  lse_pass1_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p);
+  // pass 1 (max / min / NaN flag) is skipped when the kernel that wrote the weights already reduced them
+  if (!h->lw_minmax_fresh)
+    lse_pass1_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p);
+  h->lw_minmax_fresh = false;
   fixed_tile_sums_exp_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p);
   scan_tile_sums_lse_kernel<<<1, 1024, 0, st>>>(h->red_u.p, h->tile_exp.p, n_tiles, P, h->red.p);
   if (mode == VK_RESAMPLE_SYSTEMATIC) {

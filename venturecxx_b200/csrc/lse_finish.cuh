@@ -1,0 +1,51 @@
+// Block / grid reduction of (max, min, NaN flag) over the log weights into red[0..2] -- pass 1 of
+// logsumexp (backend/lite/utils.py:70-91 needs the max for the shift and the min / NaN flag for its
+// edge cases).  Shared by lse_pass1_kernel (k_weights.cu) and by kernels that PRODUCE the weights
+// (hmm_step_kernel): a producer that reduces what it writes saves the following resample a full read
+// pass over the weights.
+// red layout (doubles): [0]=max [1]=min [2]=nan flag [3]=sum exp [4]=lse; [8..] per-block partials (3 per block)
+#pragma once
+#include "vk_common.cuh"
+
+namespace vk {
+
+static const int RED_PART = 8;
+
+// every thread of the block calls this with its partial (max, min, nan); block size <= 1024
+__device__ __forceinline__ void lse_minmax_finish(double mx, double mn, double nanf, double *red,
+                                                  unsigned int *counter) {
+  __shared__ double sh[3][32];
+  __shared__ bool last;
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
+  if (lane == 0) { sh[0][w] = mx; sh[1][w] = mn; sh[2][w] = nanf; }
+  __syncthreads();
+  if (w == 0) {
+    int nw = blockDim.x >> 5;
+    mx = lane < nw ? sh[0][lane] : -INFINITY;
+    mn = lane < nw ? sh[1][lane] : INFINITY;
+    nanf = lane < nw ? sh[2][lane] : 0.0;
+    mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
+    if (lane == 0) {
+      red[RED_PART + 3 * blockIdx.x + 0] = mx;
+      red[RED_PART + 3 * blockIdx.x + 1] = mn;
+      red[RED_PART + 3 * blockIdx.x + 2] = nanf;
+    }
+  }
+  __threadfence();
+  if (threadIdx.x == 0) last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (last && w == 0) {
+    __threadfence();
+    mx = -INFINITY; mn = INFINITY; nanf = 0.0;
+    for (int b = lane; b < (int)gridDim.x; b += 32) {
+      mx = fmax(mx, red[RED_PART + 3 * b + 0]);
+      mn = fmin(mn, red[RED_PART + 3 * b + 1]);
+      nanf = fmax(nanf, red[RED_PART + 3 * b + 2]);
+    }
+    mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
+    if (lane == 0) { red[0] = mx; red[1] = mn; red[2] = nanf; *counter = 0; }
+  }
+}
+
+}  // namespace vk

@@ -336,7 +336,9 @@ void p2p_resample(vk_particles *h, int mode) {
   const int n_tiles = (int)((P + SCAN_TILE - 1) / SCAN_TILE);
   if (h->red_u.n < (size_t)n_tiles + 1) h->red_u.alloc((size_t)n_tiles + 1);
   if (h->tile_exp.n < (size_t)n_tiles) h->tile_exp.alloc((size_t)n_tiles);
-  lse_pass1_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p);
+  if (!h->lw_minmax_fresh)
+    lse_pass1_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p);
+  h->lw_minmax_fresh = false;
   p2p_exchange_kernel<<<1, 32, 0, st>>>(s->tab.p, s->par.p, h->red.p, h->red_u.p, n_tiles, s->world, s->rank, 0, seq,
                                         cur_idx, P_total, spin);
   fixed_tile_sums_exp_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p);

@@ -23,7 +23,12 @@ using namespace vk;
 static void check_handle(const vk_particles *h) {
   if (!h || !h->model) throw Error(VK_EINVAL, "null or destroyed vk_particles handle");
 }
-static void use_device(const vk_particles *h) { VK_CUDA(cudaSetDevice(h->device)); }
+// every entry point passes through here: whatever it does next may change the weights, so the
+// "min/max of lw are already in red[]" hint dies; vk_make_consistent may set it again on its way out
+static void use_device(const vk_particles *h) {
+  const_cast<vk_particles *>(h)->lw_minmax_fresh = false;
+  VK_CUDA(cudaSetDevice(h->device));
+}
 
 // Device staging for a host output of n doubles: the handle's grow-only buffer
 // (no cudaMalloc on the hot path).  finish() copies out and drains the stream;
@@ -205,7 +210,7 @@ int vk_forget_observations(vk_particles *h, double *weights_out_host) {
 int vk_make_consistent(vk_particles *h, double *increments_out_host) {
   VK_TRY check_handle(h); use_device(h);
   HostOut o(h, increments_out_host, (size_t)h->P);
-  h->model->make_consistent(o.ptr());
+  h->model->make_consistent(o.ptr());     // may set h->lw_minmax_fresh
   o.finish();
   VK_CATCH
 }
@@ -272,7 +277,9 @@ int vk_logsumexp_array(const double *in_host, int64_t n, int device, double *out
 
 int vk_resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms_host,
                 int32_t *ancestors_out_host) {
+  const bool minmax_fresh = h && h->lw_minmax_fresh;
   VK_TRY check_handle(h); use_device(h);
+  h->lw_minmax_fresh = minmax_fresh;   // resample() consumes it
   DevBuf<double> u;
   if (uniforms_host) {
     size_t n = mode == VK_RESAMPLE_SYSTEMATIC ? 1 : (size_t)n_new;
@@ -318,7 +325,9 @@ int vk_p2p_open(vk_particles *h, int32_t world, int32_t rank, const unsigned cha
   VK_CATCH
 }
 int vk_p2p_resample(vk_particles *h, int mode) {
+  const bool minmax_fresh = h && h->lw_minmax_fresh;
   VK_TRY check_handle(h); use_device(h);
+  h->lw_minmax_fresh = minmax_fresh;   // p2p_resample() consumes it
   vk::p2p_resample(h, mode);
   // trace_set.py:207: resample ends with incorporate()
   h->model->make_consistent(nullptr);

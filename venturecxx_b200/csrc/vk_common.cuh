@@ -94,6 +94,9 @@ struct vk_particles {
   vk::DevBuf<double> tile_exp;  // per-tile sums of exp(lw - max)
   vk::DevBuf<unsigned int> counters;
   vk::Model *model = nullptr;
+  // red[0..2] = (max, min, NaN flag) of lw as it is NOW: set by a model whose make_consistent reduced the
+  // weights it wrote, cleared at the entry of every API call; consumed by vk_resample / vk_p2p_resample
+  bool lw_minmax_fresh = false;
   void *p2p = nullptr;          // vk::P2P (p2p_resample.cuh): peer-memory resampling state
   uint32_t next_step(uint32_t n = 1) { uint32_t s = step; step += n; return s; }
 };

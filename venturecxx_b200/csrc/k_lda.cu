@@ -29,8 +29,11 @@
 
 namespace vk {
 
+// n_kw is stored WORD-major: cell (topic k, word w) at nkw[w * Kp + k], Kp = K rounded up to 16, so the K
+// candidate cells a z site needs for its word are one contiguous run (a single 32-byte sector at K = 16)
+// instead of K sectors a row apart; padding cells stay zero.
 struct LDALayout {
-  int K, V, n_docs, max_tokens;
+  int K, Kp, V, n_docs, max_tokens;
   size_t off_nk, off_ndk, off_nkw, off_z, row_bytes;
   double hyper_a, hyper_b;
 };
@@ -89,8 +92,9 @@ __device__ __forceinline__ int lda_sample_topic_reg(int c, int K, double alpha, 
 
 // sum over tables of logDensityOfData(counts; alpha): n_tab tables of n_cell cells
 // (dirichlet.py:192-201).  totals[t] = N of table t (nullptr: derive from `fixed_tot`).
+// `cells` = number of stored cells to scan (>= n_tab * n_cell when the table is padded; padding is zero).
 __device__ double lda_aaa_weight(const uint16_t *counts, int n_tab, int n_cell, const uint32_t *totals,
-                                 const int32_t *fixed_tot, double alpha, int lane) {
+                                 const int32_t *fixed_tot, double alpha, int lane, int64_t cells) {
   double A = alpha * (double)n_cell;
   double lgA = lgamma(A), lga = lgamma(alpha);
   double acc = 0.0;
@@ -98,7 +102,6 @@ __device__ double lda_aaa_weight(const uint16_t *counts, int n_tab, int n_cell, 
     double N = totals ? (double)totals[t] : (double)fixed_tot[t];
     acc += lgA - lgamma(N + A);
   }
-  int64_t cells = (int64_t)n_tab * n_cell;
   for (int64_t i = lane; i < cells; i += 32) {
     int c = counts[i];
     if (c) acc += lgamma(alpha + (double)c) - lga;
@@ -126,7 +129,7 @@ lda_seq_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__r
     if (mode >= 1) {
       for (int i = lane; i < L.K; i += 32) R.nk[i] = 0;
       for (int i = lane; i < L.n_docs * L.K; i += 32) R.ndk[i] = 0;
-      for (int64_t i = lane; i < (int64_t)L.K * L.V; i += 32) R.nkw[i] = 0;
+      for (int64_t i = lane; i < (int64_t)L.Kp * L.V; i += 32) R.nkw[i] = 0;
     }
     __syncwarp();
     double ad = R.alpha[0], aw = R.alpha[1];
@@ -137,9 +140,9 @@ lda_seq_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__r
       if (mode == 3) zi = R.z[i];
       else zi = lda_sample_topic(R.ndk + d * L.K, L.K, ad, r.uniform(), lane);
       if (lane == 0) {
-        wsum += dircat_logpmf((double)R.nkw[(int64_t)zi * L.V + w], aw, (double)R.nk[zi], aw * (double)L.V);
+        wsum += dircat_logpmf((double)R.nkw[(int64_t)w * L.Kp + zi], aw, (double)R.nk[zi], aw * (double)L.V);
         R.z[i] = (uint8_t)zi;
-        R.ndk[d * L.K + zi] += 1; R.nkw[(int64_t)zi * L.V + w] += 1; R.nk[zi] += 1;
+        R.ndk[d * L.K + zi] += 1; R.nkw[(int64_t)w * L.Kp + zi] += 1; R.nk[zi] += 1;
       }
       __syncwarp();
     }
@@ -175,7 +178,10 @@ __device__ __forceinline__ int lda_gibbs_pick_warp(double pr, int K, double u, i
   return m ? __ffs(m) - 1 : K - 1;
 }
 
-__global__ void __launch_bounds__(32 * LDA_WARPS)
+// 7 CTAs of 4 warps per SM (<= 73 registers): C4's 4096 particles = 1024 CTAs fit the 148 SMs in ONE wave
+// (7 * 148 = 1036); the chain of a particle is serial, so resident warps are the only latency hiding there is.
+// The rarely taken hyper-parameter branch (lgamma sums) absorbs the spills.
+__global__ void __launch_bounds__(32 * LDA_WARPS, 7)
 lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__restrict__ doc,
               const int32_t *__restrict__ word, const int32_t *__restrict__ doclen, int n_tok,
               int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int block_mode,
@@ -217,10 +223,23 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
     // reference's Lite backend (tests/golden/lite_chains.json c4): z site 7; alpha_document_topic
     // 1 + 2 * (#doc makers alive); alpha_topic_word 1 + 2 * (#topic makers alive = topics in use).
     long long node_sum = 0, sweep_sum = 0, sweep_tot = 0;
+    // The three uniforms every transition starts with (block choice, accept, topic selection) are the same
+    // for all 32 lanes of the particle's warp; computing Philox redundantly on every lane was most of the
+    // kernel's instructions.  Instead lane l draws them for transition k + l once per 32 transitions and each
+    // transition broadcasts its own with shuffles.  (Hyper-parameter sites draw their gamma proposal from
+    // the same stream, from draw 2, on the rare transitions that need it.)
+    double us_l = 0.0, ua_l = 0.0, uz_l = 0.0;
     for (int k = 0; k < n_steps; ++k) {
+      const int jb = k & 31;
+      if (jb == 0 && k + lane < n_steps) {
+        Stream rl(seed, (uint64_t)(p_base + p), step0 + (uint32_t)(k + lane));
+        us_l = rl.uniform(); ua_l = rl.uniform(); uz_l = rl.uniform();
+      }
+      const double u_sel = __shfl_sync(0xffffffffu, us_l, jb);
+      const double u_acc = __shfl_sync(0xffffffffu, ua_l, jb);
+      const double u_z = __shfl_sync(0xffffffffu, uz_l, jb);
       Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
-      double u_sel = r.uniform();
-      double u_acc = r.uniform();
+      r.seek(2);
       int b;
       if (block_mode == VK_BLOCK_ONE) { b = (int)(u_sel * (double)nb); if (b >= nb) b = nb - 1; b += b_off; }
       else if (block_mode == VK_BLOCK_EACH) b = k % nb + b_off;
@@ -245,11 +264,11 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
         double a_new = gamma_sim(r, L.hyper_a, L.hyper_b);
         double rho, xi;
         if (b == 0) {
-          rho = lda_aaa_weight(R.ndk, L.n_docs, L.K, nullptr, doclen, a_old, lane);
-          xi = lda_aaa_weight(R.ndk, L.n_docs, L.K, nullptr, doclen, a_new, lane);
+          rho = lda_aaa_weight(R.ndk, L.n_docs, L.K, nullptr, doclen, a_old, lane, (int64_t)L.n_docs * L.K);
+          xi = lda_aaa_weight(R.ndk, L.n_docs, L.K, nullptr, doclen, a_new, lane, (int64_t)L.n_docs * L.K);
         } else {
-          rho = lda_aaa_weight(R.nkw, L.K, L.V, R.nk, nullptr, a_old, lane);
-          xi = lda_aaa_weight(R.nkw, L.K, L.V, R.nk, nullptr, a_new, lane);
+          rho = lda_aaa_weight(R.nkw, L.K, L.V, R.nk, nullptr, a_old, lane, (int64_t)L.Kp * L.V);
+          xi = lda_aaa_weight(R.nkw, L.K, L.V, R.nk, nullptr, a_new, lane, (int64_t)L.Kp * L.V);
         }
         double alpha = (rho == -INFINITY && xi == -INFINITY) ? INFINITY
                        : (rho == INFINITY && xi == INFINITY) ? -INFINITY : xi - rho;
@@ -266,7 +285,7 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
         const int d = (int)(dw >> 16), w = (int)(dw & 0xffffu);
         const int zo = R.z[i];
         const int kk = lane < L.K ? lane : 0;
-        int cand = (int)R.nkw[(int64_t)kk * L.V + w];                  // global; one cell per lane
+        int cand = (int)R.nkw[(int64_t)w * L.Kp + kk];                  // global; one cell per lane
         int nk_k = (int)R.nk[kk];
         int cdk = lane < L.K ? (int)R.ndk[d * L.K + lane] : 0;
         if (lane == zo) { cand -= 1; nk_k -= 1; cdk -= 1; }          // counts with this token removed
@@ -275,14 +294,14 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
         if (op == 1) {
           // lane k: exp(xi_k) up to the z term's common denominator (dirichlet.py:168-173, twice)
           double pr = lane < L.K ? ((double)cdk + ad) * ((double)cand + aw) / ((double)nk_k + Aw) : 0.0;
-          const int zg = lda_gibbs_pick_warp(pr, L.K, r.uniform(), lane);
+          const int zg = lda_gibbs_pick_warp(pr, L.K, u_z, lane);
           if (zg != zo) {
             ++acc;
             const int c_o = __shfl_sync(0xffffffffu, cand, zo), c_g = __shfl_sync(0xffffffffu, cand, zg);
             if (lane == 0) {
               R.z[i] = (uint8_t)zg;
-              R.nkw[(int64_t)zo * L.V + w] = (uint16_t)c_o;
-              R.nkw[(int64_t)zg * L.V + w] = (uint16_t)(c_g + 1);
+              R.nkw[(int64_t)w * L.Kp + zo] = (uint16_t)c_o;
+              R.nkw[(int64_t)w * L.Kp + zg] = (uint16_t)(c_g + 1);
               R.nk[zo] -= 1; R.nk[zg] += 1;
               R.ndk[d * L.K + zo] -= 1; R.ndk[d * L.K + zg] += 1;
             }
@@ -290,7 +309,7 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
           }
           continue;
         }
-        const int zn = lda_sample_topic_reg(cdk, L.K, ad, r.uniform(), lane);
+        const int zn = lda_sample_topic_reg(cdk, L.K, ad, u_z, lane);
         const int c_o = __shfl_sync(0xffffffffu, cand, zo), n_o = __shfl_sync(0xffffffffu, nk_k, zo);
         const int c_n = __shfl_sync(0xffffffffu, cand, zn), n_n = __shfl_sync(0xffffffffu, nk_k, zn);
         const double a_o = (double)c_o + aw, b_o = (double)n_o + Aw;   // rho = log(a_o / b_o)
@@ -300,8 +319,8 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
         if (accept && zn != zo) {
           if (lane == 0) {
             R.z[i] = (uint8_t)zn;
-            R.nkw[(int64_t)zo * L.V + w] = (uint16_t)c_o;              // c_o is already "minus this token"
-            R.nkw[(int64_t)zn * L.V + w] = (uint16_t)(c_n + 1);
+            R.nkw[(int64_t)w * L.Kp + zo] = (uint16_t)c_o;              // c_o is already "minus this token"
+            R.nkw[(int64_t)w * L.Kp + zn] = (uint16_t)(c_n + 1);
             R.nk[zo] -= 1; R.nk[zn] += 1;
             R.ndk[d * L.K + zo] -= 1; R.ndk[d * L.K + zn] += 1;
           }
@@ -313,7 +332,7 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
         int zo = R.z[i];
         double ad = R.alpha[0], aw = R.alpha[1];
         double Aw = aw * (double)L.V;
-        int64_t co = (int64_t)zo * L.V + w;
+        int64_t co = (int64_t)w * L.Kp + zo;
         // counts with this token (and its z) removed: rho = log(a_o / b_o)   (dirichlet.py:168-173)
         double a_o = (double)((int)R.nkw[co] - 1) + aw, b_o = (double)((int)R.nk[zo] - 1) + Aw;
         __syncwarp();
@@ -321,22 +340,22 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
         __syncwarp();
         if (op == 1) {
           int zg;
-          const double u_g = r.uniform();
+          const double u_g = u_z;
           if (L.K <= 32) {
             const int kk = lane < L.K ? lane : 0;
-            double pr = lane < L.K ? ((double)R.ndk[d * L.K + kk] + ad) * ((double)R.nkw[(int64_t)kk * L.V + w] + aw) /
+            double pr = lane < L.K ? ((double)R.ndk[d * L.K + kk] + ad) * ((double)R.nkw[(int64_t)w * L.Kp + kk] + aw) /
                                          ((double)R.nk[kk] + Aw) : 0.0;
             zg = lda_gibbs_pick_warp(pr, L.K, u_g, lane);
           } else {
             // sequential inclusive sums (oracle.c gibbs_pick, n > 32): total first, then the first crossing
             double total = 0.0;
             for (int t = 0; t < L.K; ++t)
-              total += ((double)R.ndk[d * L.K + t] + ad) * ((double)R.nkw[(int64_t)t * L.V + w] + aw) / ((double)R.nk[t] + Aw);
+              total += ((double)R.ndk[d * L.K + t] + ad) * ((double)R.nkw[(int64_t)w * L.Kp + t] + aw) / ((double)R.nk[t] + Aw);
             const double thr = u_g * total;
             double cum = 0.0;
             zg = L.K - 1;
             for (int t = 0; t < L.K; ++t) {
-              cum += ((double)R.ndk[d * L.K + t] + ad) * ((double)R.nkw[(int64_t)t * L.V + w] + aw) / ((double)R.nk[t] + Aw);
+              cum += ((double)R.ndk[d * L.K + t] + ad) * ((double)R.nkw[(int64_t)w * L.Kp + t] + aw) / ((double)R.nk[t] + Aw);
               if (thr < cum) { zg = t; break; }
             }
           }
@@ -344,13 +363,13 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
           __syncwarp();
           if (lane == 0) {
             R.z[i] = (uint8_t)zg;
-            R.nkw[(int64_t)zg * L.V + w] += 1; R.nk[zg] += 1; R.ndk[d * L.K + zg] += 1;
+            R.nkw[(int64_t)w * L.Kp + zg] += 1; R.nk[zg] += 1; R.ndk[d * L.K + zg] += 1;
           }
           __syncwarp();
           continue;
         }
-        int zn = lda_sample_topic(R.ndk + d * L.K, L.K, ad, r.uniform(), lane);
-        int64_t cn = (int64_t)zn * L.V + w;
+        int zn = lda_sample_topic(R.ndk + d * L.K, L.K, ad, u_z, lane);
+        int64_t cn = (int64_t)w * L.Kp + zn;
         double a_n = (double)R.nkw[cn] + aw, b_n = (double)R.nk[zn] + Aw;   // xi = log(a_n / b_n)
         // accept iff log u < xi - rho (mh.py:84-89), evaluated without logarithms or divisions as
         // u * b_n * a_o < a_n * b_o: all four factors are finite and positive here, so the +-inf
@@ -362,7 +381,7 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
         __syncwarp();
         if (lane == 0) {
           R.z[i] = (uint8_t)zf;
-          R.nkw[(int64_t)zf * L.V + w] += 1; R.nk[zf] += 1; R.ndk[d * L.K + zf] += 1;
+          R.nkw[(int64_t)w * L.Kp + zf] += 1; R.nk[zf] += 1; R.ndk[d * L.K + zf] += 1;
         }
         __syncwarp();
       }
@@ -396,15 +415,15 @@ lda_loglik_site_kernel(const unsigned char *__restrict__ rows, LDALayout L, cons
     LDARow R(const_cast<unsigned char *>(rows) + p * L.row_bytes, L);
     double v;
     if (block == 0) {
-      v = lda_aaa_weight(R.ndk, L.n_docs, L.K, nullptr, doclen, R.alpha[0], lane);
+      v = lda_aaa_weight(R.ndk, L.n_docs, L.K, nullptr, doclen, R.alpha[0], lane, (int64_t)L.n_docs * L.K);
       if (joint) v += gamma_logpdf(R.alpha[0], L.hyper_a, L.hyper_b);
     } else if (block == 1) {
-      v = lda_aaa_weight(R.nkw, L.K, L.V, R.nk, nullptr, R.alpha[1], lane);
+      v = lda_aaa_weight(R.nkw, L.K, L.V, R.nk, nullptr, R.alpha[1], lane, (int64_t)L.Kp * L.V);
       if (joint) v += gamma_logpdf(R.alpha[1], L.hyper_a, L.hyper_b);
     } else {
       int i = block - 2, d = doc[i], w = word[i], zo = R.z[i];
       double aw = R.alpha[1];
-      v = dircat_logpmf((double)((int)R.nkw[(int64_t)zo * L.V + w] - 1), aw, (double)((int)R.nk[zo] - 1),
+      v = dircat_logpmf((double)((int)R.nkw[(int64_t)w * L.Kp + zo] - 1), aw, (double)((int)R.nk[zo] - 1),
                         aw * (double)L.V);
       if (joint) {
         int nd = 0;
@@ -454,12 +473,12 @@ struct LDAModel : Model {
     VK_REQUIRE(V >= 1 && n_docs >= 1, VK_EINVAL, "lda: vocab_size and n_docs must be positive");
     VK_REQUIRE(max_tokens >= 1 && max_tokens <= 65535, VK_EINVAL, "lda: max_tokens must be in [1,65535] (u16 counts)");
     VK_REQUIRE(a > 0 && b > 0, VK_EINVAL, "gamma: shape and rate must be positive");
-    L.K = K; L.V = V; L.n_docs = n_docs; L.max_tokens = max_tokens; L.hyper_a = a; L.hyper_b = b;
+    L.K = K; L.Kp = (K + 15) & ~15; L.V = V; L.n_docs = n_docs; L.max_tokens = max_tokens; L.hyper_a = a; L.hyper_b = b;
     auto up16 = [](size_t v) { return (v + 15) & ~(size_t)15; };   // every section starts 16-byte aligned
     size_t o = 16;
     L.off_nk = o; o = up16(o + (size_t)K * 4);
     L.off_ndk = o; o = up16(o + (size_t)n_docs * K * 2);
-    L.off_nkw = o; o = up16(o + (size_t)K * V * 2);
+    L.off_nkw = o; o = up16(o + (size_t)L.Kp * V * 2);
     L.off_z = o; o = up16(o + (size_t)max_tokens);
     L.row_bytes = o;
     doc.alloc((size_t)max_tokens); word.alloc((size_t)max_tokens); doclen.alloc((size_t)n_docs);

@@ -222,7 +222,11 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
     // transloop's return value (dispatch.py:109-128): |regenCounts| per transition, as measured on the
     // reference's Lite backend (tests/golden/lite_chains.json c4): z site 7; alpha_document_topic
     // 1 + 2 * (#doc makers alive); alpha_topic_word 1 + 2 * (#topic makers alive = topics in use).
-    long long node_sum = 0, sweep_sum = 0, sweep_tot = 0;
+    // z sites all count 7, so only the (rare) hyper-parameter transitions are tallied as they happen; the z
+    // transitions are added arithmetically at the end -- no per-transition work, no division in the loop.
+    long long alpha_nodes = 0, sweep_alpha = 0, sweep_tot = 0;
+    int n_alpha = 0, sweep_n_alpha = 0;
+    int kmod = 0;                       // k mod nb, kept by increment-and-wrap
     // The three uniforms every transition starts with (block choice, accept, topic selection) are the same
     // for all 32 lanes of the particle's warp; computing Philox redundantly on every lane was most of the
     // kernel's instructions.  Instead lane l draws them for transition k + l once per 32 transitions and each
@@ -238,29 +242,35 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
       const double u_sel = __shfl_sync(0xffffffffu, us_l, jb);
       const double u_acc = __shfl_sync(0xffffffffu, ua_l, jb);
       const double u_z = __shfl_sync(0xffffffffu, uz_l, jb);
-      Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
-      r.seek(2);
+      const int km = kmod;
+      kmod = (km + 1 == nb) ? 0 : km + 1;
       int b;
       if (block_mode == VK_BLOCK_ONE) { b = (int)(u_sel * (double)nb); if (b >= nb) b = nb - 1; b += b_off; }
-      else if (block_mode == VK_BLOCK_EACH) b = k % nb + b_off;
+      else if (block_mode == VK_BLOCK_EACH) b = km + b_off;
       else b = block_mode;
       if (nodes_out) {
-        int cnt;
-        if (b >= 2) cnt = 7;
-        else if (b == 0) cnt = 1 + 2 * n_docs_live;
-        else {
-          int live = 0;
-          for (int t = lane; t < L.K; t += 32) live += R.nk[t] > 0;
-          for (int o = 16; o; o >>= 1) live += __shfl_xor_sync(0xffffffffu, live, o);
-          cnt = 1 + 2 * live;
+        if (b < 2) {
+          int cnt;
+          if (b == 0) cnt = 1 + 2 * n_docs_live;
+          else {
+            int live = 0;
+            for (int t = lane; t < L.K; t += 32) live += R.nk[t] > 0;
+            for (int o = 16; o; o >>= 1) live += __shfl_xor_sync(0xffffffffu, live, o);
+            cnt = 1 + 2 * live;
+          }
+          alpha_nodes += cnt; ++n_alpha; sweep_alpha += cnt; ++sweep_n_alpha;
         }
-        node_sum += cnt; sweep_sum += cnt;
-        if (block_mode == VK_BLOCK_EACH && (k % nb) == nb - 1) { sweep_tot += sweep_sum / nb; sweep_sum = 0; }
+        if (block_mode == VK_BLOCK_EACH && km == nb - 1) {     // `each`: floor(sum of the sweep / #blocks)
+          sweep_tot += (sweep_alpha + 7ll * (nb - sweep_n_alpha)) / nb;
+          sweep_alpha = 0; sweep_n_alpha = 0;
+        }
       }
       if (b < 2) {
         // AAA site: alpha' from the gamma prior (no proposal weight), rho/xi = marginal
         // likelihood of every made SP's counts under the old/new concentration
         double a_old = R.alpha[b];
+        Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
+        r.seek(2);
         double a_new = gamma_sim(r, L.hyper_a, L.hyper_b);
         double rho, xi;
         if (b == 0) {
@@ -398,7 +408,7 @@ lda_mh_kernel(unsigned char *__restrict__ rows, LDALayout L, const int32_t *__re
     if (acc_out && lane == 0) acc_out[p] = acc;
     if (nodes_out && lane == 0)
       nodes_out[p] = block_mode == VK_BLOCK_EACH ? (double)sweep_tot / (double)(n_steps / nb)
-                                                 : (double)node_sum / (double)n_steps;
+                                                 : (double)(alpha_nodes + 7ll * (n_steps - n_alpha)) / (double)n_steps;
   }
 }
 

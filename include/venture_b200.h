@@ -66,6 +66,14 @@ enum vk_model_kind {
 #define VK_BLOCK_ALL  (-2)  /* all blocks of the scope as one proposal  */
 #define VK_BLOCK_EACH (-3)  /* every block in order, one proposal each  */
 
+/* arithmetic of the N-observation sums inside the MH hot loop ("fp64 (parity) and fp32
+ * (throughput) modes").  State (latent values, logit caches, weights), proposals and accept tests are
+ * fp64 in both. */
+enum vk_precision {
+  VK_FP64 = 0, /* default: every log density within 1e-12 relative of Lite's       */
+  VK_FP32 = 1  /* log densities within 1e-5 relative (tests/test_gpu_fp32_mode.py) */
+};
+
 enum vk_resample_mode {
   VK_RESAMPLE_MULTINOMIAL = 0, /* trace_set.py:209-219 (i.i.d. categorical draws) */
   VK_RESAMPLE_SYSTEMATIC = 1   /* one uniform, stratified positions (k+u)/P       */
@@ -228,6 +236,14 @@ int vk_read_site(vk_particles *h, int64_t site, double *out_host);
 int vk_write_site(vk_particles *h, int64_t site, const double *in_host);
 /* after vk_write_site: recompute derived caches (logits, counts). */
 int vk_refresh(vk_particles *h);
+/* Precision of the hot loop.  VK_FP32 is implemented by the logistic-regression model's
+ * resimulation_mh with block one / each / <site> (rows that fit shared memory as float); every other
+ * entry point, and every other model kind, computes in fp64 -- other kinds answer VK_EUNSUPPORTED to
+ * VK_FP32.  After an fp32 call the logit cache holds float-rounded values; the library recomputes it from
+ * the fp64 latents before vk_log_likelihood_at / vk_log_joint_at / vk_resample / vk_pack_state read it
+ * (the reference has no counterpart: Lite and Puma are double throughout). */
+int vk_set_precision(vk_particles *h, int32_t precision);
+int vk_get_precision(const vk_particles *h, int32_t *precision_out);
 /* numBlocksInScope("default")  (lite/trace.py) */
 int vk_num_blocks(const vk_particles *h, int32_t scope, int64_t *n_out);
 

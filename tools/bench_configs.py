@@ -2,7 +2,7 @@
 """Secondary measurements: the five BASELINE.json configs on ONE GPU at the
 sizes of SURVEY 8(d) D2, one JSON line each (bench.py stays the headline, C2).
 
-  python tools/bench_configs.py [c1 c1big c3 c4 c4gibbs c3gibbs c5] [--quick]
+  python tools/bench_configs.py [c1 c1big c2 c2f32 c3 c4 c4gibbs c3gibbs c5] [--quick]
 
 Timed through the public host API (B200TraceSet), wall clock around a
 synchronised region; algorithmic bytes per SURVEY 8(d) D4.
@@ -144,6 +144,31 @@ def c3gibbs(P=1 << 20, sweeps=4, quick=False):
          "transitions/s", dt, P * sweeps * 64.0, particles=P, sites=T - 1, sweeps=sweeps)
 
 
+def c2(precision="fp64", P=65536, N=10000, D=16, K=160, reps=3, quick=False):
+    """C2 through the host API at either precision (bench.py is the headline and always fp64)."""
+    if quick:
+        P, reps = 8192, 2
+    X = np.random.default_rng(0).normal(size=(N, D))
+    w_true = np.random.default_rng(1).normal(size=D)
+    y = (np.random.default_rng(2).random(N) < 1.0 / (1.0 + np.exp(-X @ w_true))).astype(np.uint8)
+    ts = vb.B200TraceSet(vb.LogisticRegressionModel(D, N), P, seed=11, precision=precision)
+    ts.observe(X, y)
+    ts.incorporate(return_increments=False)
+    ts.resimulation_mh("default", "one", K)
+    ts.synchronize()
+    t0 = time.perf_counter()
+    acc = 0
+    for _ in range(reps):
+        _, a = ts.resimulation_mh("default", "one", K, return_accepts=True)
+        acc += int(a.sum())
+    ts.synchronize()
+    dt = time.perf_counter() - t0
+    tr = float(P) * K * reps
+    emit("c2" + ("f32" if precision == "fp32" else ""), "particle-site MH transitions/sec", tr / dt, "transitions/s", dt,
+         tr * (N * 8 * (1 + acc / tr) + 16), precision=precision, particles=P, observations=N, D=D,
+         obs_evals_per_sec=tr * N / dt, accept_rate=acc / tr)
+
+
 def c5(N=10 ** 7, P=64, K=20, quick=False):
     D = 16
     if quick:
@@ -188,6 +213,10 @@ def main():
             c3gibbs(1 << 20, 1 if quick else 4, quick)
         elif w == "c5":
             c5(quick=quick)
+        elif w == "c2":
+            c2("fp64", quick=quick)
+        elif w == "c2f32":
+            c2("fp32", quick=quick)
 
 
 if __name__ == "__main__":

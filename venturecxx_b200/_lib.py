@@ -13,6 +13,7 @@ SO_PATH = os.path.join(_HERE, "libventure_b200.so")
 
 VK_OK, VK_EINVAL, VK_ECUDA, VK_EUNSUPPORTED, VK_ESTATE = 0, 1, 2, 3, 4
 BLOCK_ONE, BLOCK_ALL, BLOCK_EACH = -1, -2, -3
+FP64, FP32 = 0, 1
 RESAMPLE_MULTINOMIAL, RESAMPLE_SYSTEMATIC = 0, 1
 
 c = ctypes
@@ -66,6 +67,8 @@ PROTOTYPES = {
     "vk_read_site": [_vp, _i64, _vp],
     "vk_write_site": [_vp, _i64, _vp],
     "vk_refresh": [_vp],
+    "vk_set_precision": [_vp, _i32],
+    "vk_get_precision": [_vp, _vp],
     "vk_num_blocks": [_vp, _i32, _vp],
     "vk_device_buffer": [_vp, _i32, _vp, _vp],
     "vk_shard_weight_max": [_vp, _vp],

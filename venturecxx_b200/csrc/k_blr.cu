@@ -295,6 +295,10 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
   }
 }
 
+}  // namespace vk
+#include "blr_mh_f32.cuh"
+namespace vk {
+
 // block = all: joint proposal of every weight from the prior (one scaffold
 // with D principal nodes).  eta' is recomputed into a scratch row.
 __global__ void __launch_bounds__(256)
@@ -393,6 +397,12 @@ struct BLRModel : Model {
   // subsampled MH (C5): observation shard [obs_lo, obs_lo + N) of N_total, transition state
   int64_t obs_lo = 0, N_total = -1;
   bool eta_dirty = false;
+  // fp32 throughput mode (blr_mh_f32.cuh): float copy of Xs, and "the logit cache holds float-rounded
+  // values and ll an fp32-accurate sum" -- refreshed from w in fp64 before any fp64 consumer
+  int precision = VK_FP64;
+  bool eta_lowprec = false;
+  DevBuf<float> Xs32;
+  int64_t Xs32_rows = -1;
   DevBuf<double> Xr, ss_d, ss_partial, ss_sums;
   DevBuf<int> ss_i;
   int64_t Xr_rows = 0;
@@ -427,8 +437,13 @@ struct BLRModel : Model {
     VK_CUDA(cudaGetLastError());
     VK_CUDA(cudaStreamSynchronize(h->stream));
     prm.N += n;
-    Xr_rows = -1;
+    Xr_rows = -1; Xs32_rows = -1;
   }
+  void set_precision(int prec) override {
+    VK_REQUIRE(prec == VK_FP64 || prec == VK_FP32, VK_EINVAL, "precision must be VK_FP64 or VK_FP32");
+    precision = prec;
+  }
+  int get_precision() const override { return precision; }
   int grid_particles(int ctas_per_sm) const {
     int64_t cap = (int64_t)h->sm_count * ctas_per_sm;
     return (int)(h->P < cap ? h->P : cap);
@@ -444,10 +459,10 @@ struct BLRModel : Model {
     n_prop = prm.N;
     launch_all(1, nullptr, h->next_step());
   }
-  void refresh() override { launch_all(2, nullptr, 0); eta_dirty = false; }
+  void refresh() override { launch_all(2, nullptr, 0); eta_dirty = false; eta_lowprec = false; }
   // subsampled transitions leave the logit cache stale (subsampled_mh.py:59-73);
   // this is SubsampledInPlaceOperator.makeConsistent (:427-455) done lazily.
-  void ensure_fresh() { if (eta_dirty) refresh(); }
+  void ensure_fresh() { if (eta_dirty || eta_lowprec) refresh(); }
   void set_observation_shard(int64_t lo, int64_t total) {
     VK_REQUIRE(lo >= 0 && total >= lo, VK_EINVAL, "blr: bad observation shard");
     obs_lo = lo; N_total = total;
@@ -577,7 +592,8 @@ struct BLRModel : Model {
     VK_REQUIRE(block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || block == VK_BLOCK_ALL ||
                    (block >= 0 && block < prm.D), VK_EINVAL, "blr: bad block");
     VK_REQUIRE(n_prop == prm.N, VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
-    ensure_fresh();
+    const bool f32 = precision == VK_FP32 && block != VK_BLOCK_ALL && K > 0 && f32_fits();
+    if (f32) { if (eta_dirty) refresh(); } else ensure_fresh();
     double nodes = 0.0;
     if (K > 0) {
       if (block == VK_BLOCK_ALL) {
@@ -590,6 +606,10 @@ struct BLRModel : Model {
         int n_steps = (block == VK_BLOCK_EACH) ? K * prm.D : K;
         uint32_t step0 = h->next_step((uint32_t)n_steps);
         VK_REQUIRE(prm.N <= ((int64_t)1 << 19), VK_EUNSUPPORTED, "blr mh: at most 2^19 observations per particle in this version");
+        if (f32) {
+          launch_mh_f32(step0, n_steps, block, acc_dev);
+          nodes = (double)(3 + 2 * prm.N) * (block == VK_BLOCK_EACH ? prm.D : 1);
+        } else {
         size_t base = blr_mh_smem_base(prm.D);
         int64_t Npad = (prm.N + BLR_MH_TILE - 1) / BLR_MH_TILE * BLR_MH_TILE;
         size_t need = base + (size_t)Npad * sizeof(double);
@@ -620,6 +640,7 @@ struct BLRModel : Model {
         // |DRG| of scaffold(w_j) = w_j + lookup + array + N lookups + N dots;
         // 'each' sums D proposals per transition (dispatch.py:122-128)
         nodes = (double)(3 + 2 * prm.N) * (block == VK_BLOCK_EACH ? prm.D : 1);
+        }
       }
       VK_CUDA(cudaGetLastError());
     }
@@ -627,6 +648,28 @@ struct BLRModel : Model {
       blr_fill_const_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, nodes);
       VK_CUDA(cudaGetLastError());
     }
+  }
+  // fp32 mode needs the float logit row of one particle in shared memory; longer rows run the fp64 kernel
+  size_t f32_smem() const {
+    int64_t Npad = (prm.N + BLR_F32_TILE - 1) / BLR_F32_TILE * BLR_F32_TILE;
+    return blr_mh_f32_smem_base(prm.D) + (size_t)Npad * sizeof(float);
+  }
+  bool f32_fits() const { return f32_smem() <= (size_t)smem_limit; }
+  void launch_mh_f32(uint32_t step0, int n_steps, int block, long long *acc_dev) {
+    if (Xs32_rows != prm.N) {
+      if (!Xs32.p) Xs32.alloc(Xs.n);
+      blr_to_float_kernel<<<grid_for((int64_t)Xs.n, 256, h->sm_count, 8), 256, 0, h->stream>>>(Xs.p, Xs32.p, (int64_t)Xs.n);
+      VK_CUDA(cudaGetLastError());
+      Xs32_rows = prm.N;
+    }
+    size_t sm = f32_smem();
+    int per_sm = (int)((size_t)(227 * 1024) / (sm + 1024));
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm > 4) per_sm = 4;
+    VK_CUDA(cudaFuncSetAttribute(blr_mh_f32_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_limit));
+    blr_mh_f32_kernel<4><<<grid_particles(per_sm), BLR_F32_THREADS, sm, h->stream>>>(
+        w, eta, ll, Xs32.p, prm, h->P, h->p_base, h->seed, step0, n_steps, block, acc_dev);
+    eta_lowprec = true;
   }
   void log_likelihood_at(int scope, int block, bool joint, double *out_dev) override {
     VK_REQUIRE(scope == 0, VK_EINVAL, "blr: only the default scope exists");
@@ -639,7 +682,7 @@ struct BLRModel : Model {
   }
   void forget_observations(double *w_dev) override {
     if (w_dev) log_likelihood_at(0, VK_BLOCK_ALL, false, w_dev);
-    prm.N = 0; n_prop = 0; Xr_rows = -1; eta_dirty = false;
+    prm.N = 0; n_prop = 0; Xr_rows = -1; Xs32_rows = -1; eta_dirty = false; eta_lowprec = false;
     VK_CUDA(cudaMemsetAsync(Xs.p, 0, Xs.bytes(), h->stream));   // keep the zero padding invariant
     VK_CUDA(cudaMemsetAsync(ll, 0, (size_t)h->P * sizeof(double), h->stream));
   }

@@ -405,6 +405,10 @@ int vk_write_site(vk_particles *h, int64_t site, const double *in_host) {
   VK_CUDA(cudaStreamSynchronize(h->stream));
   VK_CATCH
 }
+int vk_set_precision(vk_particles *h, int32_t precision) { VK_TRY check_handle(h); use_device(h); h->model->set_precision(precision); VK_CATCH }
+int vk_get_precision(const vk_particles *h, int32_t *precision_out) {
+  VK_TRY check_handle(h); VK_REQUIRE(precision_out, VK_EINVAL, "NULL"); *precision_out = h->model->get_precision(); VK_CATCH
+}
 int vk_refresh(vk_particles *h) { VK_TRY check_handle(h); use_device(h); h->model->refresh(); VK_CATCH }
 
 int vk_device_buffer(vk_particles *h, int32_t which, void **dev_ptr_out, int64_t *n_bytes_out) {

@@ -130,6 +130,11 @@ struct Model {
   virtual void read_site(int64_t site, double *out_dev) = 0;
   virtual void write_site(int64_t site, const double *in_dev) = 0;
   virtual void refresh() {}
+  // VK_FP64 (parity, default) or VK_FP32 (throughput): models without an fp32 kernel refuse VK_FP32
+  virtual void set_precision(int prec) {
+    if (prec != VK_FP64) throw Error(VK_EUNSUPPORTED, "this model kind has no fp32 mode in this version");
+  }
+  virtual int get_precision() const { return VK_FP64; }
   // arrays gathered by ancestor index on resample; after the gather the model
   // swaps cur/alt itself via StateArray.
   virtual std::vector<StateArray> state_arrays() = 0;

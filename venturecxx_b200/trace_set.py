@@ -29,7 +29,7 @@ def _unbox(v):
 
 
 class B200TraceSet(object):
-    def __init__(self, model, n_particles, seed=1, device=0, particle_base=0):
+    def __init__(self, model, n_particles, seed=1, device=0, particle_base=0, precision="fp64"):
         self.model = model
         self.device = int(device)
         self._h = model._create(int(n_particles), int(seed), self.device)
@@ -38,6 +38,8 @@ class B200TraceSet(object):
             _lib.call("vk_set_particle_base", self._h, int(particle_base))
         # `assume` simulates every latent from its prior (regen.py eval)
         _lib.call("vk_reset_to_prior", self._h)
+        if precision != "fp64":
+            self.precision = precision
 
     # -- lifetime --------------------------------------------------------
     def close(self):
@@ -57,6 +59,19 @@ class B200TraceSet(object):
 
     def synchronize(self):
         _lib.call("vk_synchronize", self._h)
+
+    # -- precision of the hot loop (include/venture_b200.h vk_set_precision) --------
+    @property
+    def precision(self):
+        v = ctypes.c_int32()
+        _lib.call("vk_get_precision", self._h, ctypes.byref(v))
+        return {_lib.FP64: "fp64", _lib.FP32: "fp32"}[v.value]
+
+    @precision.setter
+    def precision(self, name):
+        if name not in ("fp64", "fp32"):
+            raise VentureException("invalid_argument", "precision must be 'fp64' or 'fp32', not %r" % (name,))
+        _lib.call("vk_set_precision", self._h, _lib.FP32 if name == "fp32" else _lib.FP64)
 
     # -- seeds (trace_set.py has_own_prng/set_seed) ------------------------
     def set_seed(self, seed):

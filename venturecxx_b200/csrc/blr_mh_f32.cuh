@@ -10,8 +10,8 @@
 //     float4 share ONE lg2: sum_k lg2(1 + t_k) = lg2(prod_k (1 + t_k)), the product is in [1,16]
 //     (1.25 MUFU + 7 fp32 instructions per observation instead of ~20 fp64 instructions and two table
 //     lookups; the first version spent 2 MUFU per observation and ran at 72 % of the MUFU pipe),
-//   * each thread keeps 6 fp32 partial sums of 5-10 terms each (at C2); they are widened to fp64 before
-//     the block-wide sum, so the rounding of the accumulation stays ~1e-8 relative to xi.
+//   * each thread keeps 5 fp32 partial sums of 10 terms each (at C2); the thread's total is widened to
+//     fp64 before the block-wide sum, so the rounding of the accumulation stays ~1e-8 relative to xi.
 // w itself, the proposals and the accept test stay fp64.  rho is recomputed from the staged row when a
 // particle is loaded, so xi and rho are the same function of nearly the same arguments and the systematic
 // part of the MUFU error cancels in xi - rho.  The float row is widened back to the fp64 logit cache when
@@ -37,31 +37,40 @@ __host__ __device__ inline size_t blr_mh_f32_smem_base(int D) {
   return (size_t)(((D + 1) & ~1) + 34 + 64 + 2 * BLR_MH_CHUNK) * sizeof(double) + (size_t)BLR_MH_CHUNK * sizeof(int);
 }
 
-// sum_i log_logistic(row_i + df * x_i) over the padded row; x may be null (df = 0).  All threads return
-// the same fp64 value.  `xn` holds the first x tile on entry and the first tile of `xnext` on exit.
+// One tile: four observations of this thread.  min(v,0) into m0..m3, lg2 of the product of the four
+// 1 + exp(-|v|) into l.
+__device__ __forceinline__ void blr_f32_tile(const float4 e, float &m0, float &m1, float &m2, float &m3, float &l) {
+  const float q0 = f32_one_plus_exp_neg_abs(e.x, m0) * f32_one_plus_exp_neg_abs(e.y, m1);
+  const float q1 = f32_one_plus_exp_neg_abs(e.z, m2) * f32_one_plus_exp_neg_abs(e.w, m3);
+  l += f32_lg2(q0 * q1);
+}
+__device__ __forceinline__ float4 blr_f32_axpy(float df, const float4 x, float4 e) {
+  e.x = fmaf(df, x.x, e.x); e.y = fmaf(df, x.y, e.y); e.z = fmaf(df, x.z, e.z); e.w = fmaf(df, x.w, e.w);
+  return e;
+}
+
+// sum_i log_logistic(row_i + df * x_i) over the padded row (WITH_X = false: df = 0, no x).  All threads
+// return the same fp64 value.  `xn` holds this thread's first x tile on entry and the first tile of the
+// NEXT transition's column (`xnext`, already offset by tid) on exit; the last iteration is peeled so the
+// loop's prefetch address is a plain pointer increment.
 template <bool WITH_X>
-__device__ __forceinline__ double blr_f32_row_sum(const float4 *__restrict__ row4, const float4 *__restrict__ x4,
-                                                  const float4 *__restrict__ xnext4, float4 &xn, float df, int iters,
+__device__ __forceinline__ double blr_f32_row_sum(const float4 *__restrict__ row, const float4 *__restrict__ xcol,
+                                                  const float4 *__restrict__ xnext, float4 &xn, float df, int iters,
                                                   double *slots, int parity) {
-  const int tid = threadIdx.x;
-  float m0 = 0.f, m1 = 0.f, m2 = 0.f, m3 = 0.f, l0 = 0.f, l1 = 0.f;
-  for (int it = 0; it < iters; ++it) {
-    float4 e = row4[it * BLR_F32_THREADS + tid];
-    if (WITH_X) {
-      float4 x = xn;
-      // next tile of this column, or the first tile of the next transition's column
-      xn = __ldg(it + 1 < iters ? x4 + (it + 1) * BLR_F32_THREADS + tid : xnext4 + tid);
-      e.x = fmaf(df, x.x, e.x); e.y = fmaf(df, x.y, e.y); e.z = fmaf(df, x.z, e.z); e.w = fmaf(df, x.w, e.w);
-    }
-    const float q0 = f32_one_plus_exp_neg_abs(e.x, m0) * f32_one_plus_exp_neg_abs(e.y, m1);
-    const float q1 = f32_one_plus_exp_neg_abs(e.z, m2) * f32_one_plus_exp_neg_abs(e.w, m3);
-    const float lg = f32_lg2(q0 * q1);
-    if (it & 1) l1 += lg; else l0 += lg;
+  float m0 = 0.f, m1 = 0.f, m2 = 0.f, m3 = 0.f, l = 0.f;
+  const float4 *xp = xcol + BLR_F32_THREADS;      // row, xcol, xnext are already offset by tid
+  for (int it = 0; it < iters - 1; ++it, row += BLR_F32_THREADS, xp += BLR_F32_THREADS) {
+    float4 e = *row;
+    if (WITH_X) { const float4 x = xn; xn = __ldg(xp); e = blr_f32_axpy(df, x, e); }
+    blr_f32_tile(e, m0, m1, m2, m3, l);
   }
-  double M = ((double)m0 + (double)m1) + ((double)m2 + (double)m3);
-  double L = (double)l0 + (double)l1;
-  double part = fma(-0.6931471805599453, L, M);
-  return block_sum_1sync<BLR_F32_THREADS / 32>(part, slots, parity);
+  {
+    float4 e = *row;
+    if (WITH_X) { const float4 x = xn; xn = __ldg(xnext); e = blr_f32_axpy(df, x, e); }
+    blr_f32_tile(e, m0, m1, m2, m3, l);
+  }
+  const float part = fmaf(-0.6931471805599453f, l, (m0 + m1) + (m2 + m3));
+  return block_sum_1sync<BLR_F32_THREADS / 32>((double)part, slots, parity);
 }
 
 template <int MINB>
@@ -86,7 +95,7 @@ blr_mh_f32_kernel(double *__restrict__ w, double *__restrict__ eta, double *__re
   const int tid = threadIdx.x;
   float4 *row4 = reinterpret_cast<float4 *>(eta_sh);
   const float4 *X4 = reinterpret_cast<const float4 *>(Xs32);
-  const int64_t ld4 = prm.Xld / 4;
+  const int ld4 = (int)(prm.Xld / 4);
   int parity = 0;
   for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
     __syncthreads();
@@ -104,7 +113,7 @@ blr_mh_f32_kernel(double *__restrict__ w, double *__restrict__ eta, double *__re
     }
     __syncthreads();
     float4 xn = make_float4(0.f, 0.f, 0.f, 0.f);
-    double rho = blr_f32_row_sum<false>(row4, nullptr, nullptr, xn, 0.0f, iters, slots, parity);
+    double rho = blr_f32_row_sum<false>(row4 + tid, nullptr, nullptr, xn, 0.0f, iters, slots, parity);
     parity ^= 1;
     long long acc = 0;
     bool dirty = false;
@@ -124,14 +133,15 @@ blr_mh_f32_kernel(double *__restrict__ w, double *__restrict__ eta, double *__re
         prop_w[t] = normal_sim(r, prm.mu0, prm.s0);
       }
       __syncthreads();
-      xn = __ldg(X4 + (int64_t)prop_site[0] * ld4 + tid);
+      xn = __ldg(X4 + tid + prop_site[0] * ld4);   // column offsets in float4 units: D * Xld / 4 < 2^31
       for (int t = 0; t < cn; ++t) {
         const int j = prop_site[t];
+        const int off = j * ld4;
         const double w_new = prop_w[t];
         const float df = (float)(w_new - w_sh[j]);
-        const float4 *xcol4 = X4 + (int64_t)j * ld4;
-        const float4 *xnext4 = X4 + (int64_t)prop_site[t + 1 < cn ? t + 1 : t] * ld4;
-        double xi = blr_f32_row_sum<true>(row4, xcol4, xnext4, xn, df, iters, slots, parity);
+        const float4 *xcol4 = X4 + off;
+        const float4 *xnext = X4 + tid + prop_site[t + 1 < cn ? t + 1 : t] * ld4;
+        double xi = blr_f32_row_sum<true>(row4 + tid, xcol4 + tid, xnext, xn, df, iters, slots, parity);
         parity ^= 1;
         double alpha = blr_log_alpha(rho, xi);
         if (prop_logu[t] < alpha) {   // uniform across the CTA

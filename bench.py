@@ -329,10 +329,24 @@ def main():
     barrier()
     ms_e2e = max(e0.elapsed_time(e1), 1e3 * (time.perf_counter() - t0))
 
-    t_ms = torch.tensor([ms, ms_e2e], dtype=torch.float64, device="cuda")
+    # ---- fp32 throughput mode (vk_set_precision): reported beside the headline, never as it -----
+    ts.precision = "fp32"
+    for _ in range(W):
+        step_resident()
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record(stream)
+    for _ in range(args.steps):
+        step_resident()
+    f1.record(stream)
+    barrier()
+    ms_f32 = f0.elapsed_time(f1)
+    ts.precision = "fp64"
+
+    t_ms = torch.tensor([ms, ms_e2e, ms_f32], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
-    ms, ms_e2e = [float(v) for v in t_ms.tolist()]
+    ms, ms_e2e, ms_f32 = [float(v) for v in t_ms.tolist()]
 
     if rank == 0:
         total_tr = float(P) * world * T * args.steps
@@ -356,6 +370,11 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": int(X.nbytes + y.nbytes), "d2h_bytes_per_step": int(3 * P * 8)},
             "gpu_launches": args.steps,
+            "fp32_mode": {"value": total_tr / (ms_f32 * 1e-3), "unit": UNIT, "ms_per_step": ms_f32 / args.steps,
+                          "note": "same workload and steps with vk_set_precision(VK_FP32): float logit row and MUFU "
+                                  "log-logistic inside the MH loop, fp64 proposals/accept test/state; log densities "
+                                  "within 1e-5 relative of fp64 (tests/test_gpu_fp32_mode.py). Not the headline: "
+                                  "`value`, `e2e` and `roofline` are the fp64 path."},
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,

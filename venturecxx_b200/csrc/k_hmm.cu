@@ -15,6 +15,7 @@
 // the trace on resample).  One thread per particle; HBM-bound:
 // 4+4 B cur, 1 B hist, 8+8 B lw per particle-step.
 #include "vk_common.cuh"
+#include <utility>
 #include "sp_math.cuh"
 #include "lse_finish.cuh"
 
@@ -33,7 +34,7 @@ __global__ void __launch_bounds__(256)
 hmm_step_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, int t /*0-based*/,
                 double *__restrict__ lw, double *__restrict__ incr, HMMTables tb, int symbol /*1-based*/,
                 int64_t P, int64_t p_base, uint64_t seed, uint32_t step, int accumulate_incr,
-                double *__restrict__ red, unsigned int *__restrict__ counter) {
+                double *__restrict__ red, unsigned int *__restrict__ counter, int write_hist) {
   extern __shared__ double sh[];
   double *tr = sh;                       // n_rows*S
   double *em = sh + tb.n_rows * tb.S;    // S*O
@@ -52,7 +53,10 @@ hmm_step_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad,
       s = 1 + categorical_sim(r, tr + (prev - 1) * tb.S, tb.S, 1);
     }
     cur[p] = s;
-    hist[p * Tpad + t] = (uint8_t)s;
+    // one byte into a particle-major row is a partial-sector write (a 32-byte read-modify-write per
+    // particle); the newest column is left "pending" in cur[] when the caller can fold it into the
+    // resampling gather that follows (hmm_gather_kernel), see HMMModel::hist_pending
+    if (write_hist) hist[p * Tpad + t] = (uint8_t)s;
     double w = categorical_logpmf(symbol - 1, em + (s - 1) * tb.O, tb.O, 1);
     if (w != w) w = -INFINITY;
     double v = lw[p] + w;
@@ -240,6 +244,42 @@ __global__ void hmm_fill_kernel(double *out, int64_t n, double v) {
     out[i] = v;
 }
 
+// hist[p][t] := cur[p]: materialises a pending newest column
+__global__ void hmm_flush_kernel(const int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, int t, int64_t P) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x)
+    hist[p * Tpad + t] = (uint8_t)cur[p];
+}
+// Ancestor gather of the whole HMM state in one pass: child k takes parent a = anc[k]'s newest state
+// (cur) and history row; a pending newest column t_pend (>= 0) is inserted into the row on the way, so
+// the row is written once, as whole 16-byte units.  One thread per 16-byte unit of a child row.
+__global__ void __launch_bounds__(256)
+hmm_gather_kernel(const int32_t *__restrict__ cur_in, int32_t *__restrict__ cur_out,
+                  const uint4 *__restrict__ hist_in, uint4 *__restrict__ hist_out,
+                  const int32_t *__restrict__ anc, int64_t n_new, int units, int t_pend) {
+  const int64_t total = n_new * units;
+  const int pu = t_pend >= 0 ? t_pend >> 4 : -1, pw = (t_pend >> 2) & 3, psh = (t_pend & 3) * 8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t k = i / units;
+    const int c = (int)(i - k * units);
+    const int64_t a = anc[k];
+    uint4 v = hist_in[a * units + c];
+    if (c == 0 || c == pu) {
+      const uint32_t s = (uint32_t)cur_in[a];
+      if (c == 0) cur_out[k] = (int32_t)s;
+      if (c == pu) {
+        const uint32_t keep = ~(0xFFu << psh), ins = (s & 0xFFu) << psh;
+        if (pw == 0) v.x = (v.x & keep) | ins;
+        else if (pw == 1) v.y = (v.y & keep) | ins;
+        else if (pw == 2) v.z = (v.z & keep) | ins;
+        else v.w = (v.w & keep) | ins;
+      }
+    }
+    hist_out[k * units + c] = v;
+  }
+}
+
 struct HMMModel : Model {
   HMMTables tb;
   int T_max, Tpad, T = 0 /*propagated time steps*/;
@@ -250,6 +290,24 @@ struct HMMModel : Model {
   int32_t *cur = nullptr, *cur_alt = nullptr;
   uint8_t *hist = nullptr, *hist_alt = nullptr;
   size_t smem;
+  // column T-1 of hist is still only in cur[] (written by the last filter step); the resampling gather
+  // inserts it while it copies the rows, every other reader of hist flushes it first
+  bool hist_pending = false;
+  void flush_hist() {
+    if (!hist_pending) return;
+    hmm_flush_kernel<<<grid(), 256, 0, h->stream>>>(cur, hist, Tpad, T - 1, h->P);
+    VK_CUDA(cudaGetLastError());
+    hist_pending = false;
+  }
+  bool gather(const int32_t *anc_dev, int64_t n_new) override {
+    const int units = Tpad / 16;
+    hmm_gather_kernel<<<grid_for(n_new * units, 256, h->sm_count, 8), 256, 0, h->stream>>>(
+        cur, cur_alt, (const uint4 *)hist, (uint4 *)hist_alt, anc_dev, n_new, units, hist_pending ? T - 1 : -1);
+    VK_CUDA(cudaGetLastError());
+    std::swap(cur, cur_alt); std::swap(hist, hist_alt);
+    hist_pending = false;
+    return true;
+  }
 
   HMMModel(vk_particles *h_, int S, int O, int n_rows, const double *trans_host, const double *emit_host,
            int init, int T_max_) : Model(h_), T_max(T_max_) {
@@ -289,14 +347,17 @@ struct HMMModel : Model {
       if (incr_dev) VK_CUDA(cudaMemsetAsync(incr_dev, 0, (size_t)h->P * sizeof(double), h->stream));
       return;
     }
+    flush_hist();
     bool first = true;
     for (; T < n; ++T) {
       uint32_t step = h->next_step();
+      const bool last = T == n - 1;
       hmm_step_kernel<<<grid(), 256, smem, h->stream>>>(cur, hist, Tpad, T, h->lw.p, incr_dev, tb, symbols_host[T],
                                                         h->P, h->p_base, h->seed, step, first ? 0 : 1, h->red.p,
-                                                        h->counters.p);
+                                                        h->counters.p, last ? 0 : 1);
       first = false;
     }
+    hist_pending = true;
     VK_CUDA(cudaGetLastError());
     h->lw_minmax_fresh = true;     // red[0..2] describe the weights as they are now
   }
@@ -308,6 +369,7 @@ struct HMMModel : Model {
                                                     h->seed, step, write_lw ? 1 : 0);
     VK_CUDA(cudaGetLastError());
     VK_CUDA(cudaStreamSynchronize(h->stream));  // symbols_host stays valid for the async copy
+    hist_pending = false;                       // every column was just rewritten
   }
   void likelihood_weight() override { run_prior(true); }
   void reset_to_prior() override { run_prior(false); }
@@ -323,6 +385,7 @@ struct HMMModel : Model {
     VK_REQUIRE(T == (int)symbols_host.size(), VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
     int nb = T - 1;
     VK_REQUIRE(block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || (block >= 0 && block < nb), VK_EINVAL, "hmm: bad block");
+    flush_hist();
     if (K > 0 && nb > 0) {  // zero-entropy scope performs no transitions (dispatch.py:55-56)
       int n_steps = block == VK_BLOCK_EACH ? K * nb : K;
       uint32_t step0 = h->next_step((uint32_t)n_steps);
@@ -348,6 +411,7 @@ struct HMMModel : Model {
     loglik_from(1, joint, out_dev);
   }
   void loglik_from(int t_first, bool joint, double *out_dev) {
+    flush_hist();
     upload_symbols();
     hmm_loglik_kernel<<<grid(), 256, 0, h->stream>>>(hist, Tpad, T, tb, symbols.p, h->P, joint ? 1 : 0, t_first, out_dev);
     VK_CUDA(cudaGetLastError());
@@ -355,26 +419,29 @@ struct HMMModel : Model {
   }
   void forget_observations(double *w_dev) override {
     if (w_dev) loglik_from(0, false, w_dev);   // unobserve reports every observation's density
-    symbols_host.clear(); T = 0;
+    symbols_host.clear(); T = 0; hist_pending = false;
   }
   int64_t num_sites() const override { return T; }
   int64_t num_blocks(int) const override { return T > 1 ? T - 1 : 0; }
   void read_site(int64_t site, double *out_dev) override {
     VK_REQUIRE(site >= 0 && site < T, VK_EINVAL, "hmm: site (0-based time index) out of range");
+    flush_hist();
     hmm_read_kernel<<<grid(), 256, 0, h->stream>>>(hist, Tpad, (int)site, h->P, out_dev);
   }
   void write_site(int64_t site, const double *in_dev) override {
     VK_REQUIRE(site >= 0 && site < T, VK_EINVAL, "hmm: site (0-based time index) out of range");
+    flush_hist();
     hmm_write_kernel<<<grid(), 256, 0, h->stream>>>(hist, cur, Tpad, (int)site, site == T - 1, h->P, in_dev);
   }
   std::vector<StateArray> state_arrays() override {
+    flush_hist();   // generic consumers (pack/unpack, peer-memory and small-P gathers) see complete rows
     StateArray a{(void **)&cur, (void **)&cur_alt, 0, 1, 4};
     StateArray b{(void **)&hist, (void **)&hist_alt, (size_t)Tpad, 0, 0};
     return {a, b};
   }
   int device_buffer(int which, void **p, int64_t *bytes) override {
     if (which == 1) { *p = cur; *bytes = (int64_t)cura.bytes(); return VK_OK; }
-    if (which == 2) { *p = hist; *bytes = (int64_t)hista.bytes(); return VK_OK; }
+    if (which == 2) { flush_hist(); *p = hist; *bytes = (int64_t)hista.bytes(); return VK_OK; }
     return VK_EINVAL;
   }
 };

@@ -342,6 +342,7 @@ void build_fixed_cdf(vk_particles *h, const double *red_or_null, double m, int f
 
 void gather_state(vk_particles *h, const int32_t *anc_dev, int64_t n_new) {
   cudaStream_t st = h->stream;
+  if (h->model->gather(anc_dev, n_new)) return;
   std::vector<StateArray> arrs = h->model->state_arrays();
   for (auto &a : arrs) {
     if (a.elem_bytes == 0) {

@@ -138,6 +138,9 @@ struct Model {
   // arrays gathered by ancestor index on resample; after the gather the model
   // swaps cur/alt itself via StateArray.
   virtual std::vector<StateArray> state_arrays() = 0;
+  // a model may gather its whole state by ancestor in one fused pass of its own (returns true);
+  // otherwise the generic per-array gather over state_arrays() runs
+  virtual bool gather(const int32_t *anc_dev, int64_t n_new) { (void)anc_dev; (void)n_new; return false; }
   virtual void after_resample() {}
   virtual int device_buffer(int which, void **p, int64_t *bytes) { return VK_EINVAL; }
 };

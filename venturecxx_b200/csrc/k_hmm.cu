@@ -35,11 +35,27 @@ hmm_step_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad,
                 double *__restrict__ lw, double *__restrict__ incr, HMMTables tb, int symbol /*1-based*/,
                 int64_t P, int64_t p_base, uint64_t seed, uint32_t step, int accumulate_incr,
                 double *__restrict__ red, unsigned int *__restrict__ counter, int write_hist) {
+  // Per-CTA tables: a particle's draw and weight depend on (previous state, u) and (new state) only, so
+  // the row sums, the running sums categorical_sim compares against, and the S emission log densities
+  // are evaluated once per CTA by the SAME functions on the same inputs (bit-identical to evaluating
+  // them per particle) and the particle loop is Philox + S comparisons + two table reads.
   extern __shared__ double sh[];
-  double *tr = sh;                       // n_rows*S
-  double *em = sh + tb.n_rows * tb.S;    // S*O
-  for (int i = threadIdx.x; i < tb.n_rows * tb.S; i += blockDim.x) tr[i] = tb.trans[i];
-  for (int i = threadIdx.x; i < tb.S * tb.O; i += blockDim.x) em[i] = tb.emit[i];
+  double *cdf = sh;                               // n_rows*S running sums of a transition row
+  double *denom = cdf + tb.n_rows * tb.S;         // n_rows
+  double *lw_emit = denom + tb.n_rows;            // S
+  int *last_pos = (int *)(lw_emit + tb.S);        // n_rows: last index with positive mass
+  for (int r_ = threadIdx.x; r_ < tb.n_rows; r_ += blockDim.x) {
+    const double *ps = tb.trans + r_ * tb.S;
+    double d = 0.0;
+    for (int i = 0; i < tb.S; ++i) d += ps[i];
+    double acc = 0.0; int last = 0;
+    for (int i = 0; i < tb.S; ++i) { if (ps[i] > 0.0) last = i; acc += ps[i]; cdf[r_ * tb.S + i] = acc; }
+    denom[r_] = d; last_pos[r_] = last;
+  }
+  for (int s_ = threadIdx.x; s_ < tb.S; s_ += blockDim.x) {
+    double w = categorical_logpmf(symbol - 1, tb.emit + s_ * tb.O, tb.O, 1);
+    lw_emit[s_] = (w != w) ? -INFINITY : w;
+  }
   __syncthreads();
   double mx = -INFINITY, mn = INFINITY, nanf = 0.0;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
@@ -49,16 +65,25 @@ hmm_step_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad,
       s = tb.init;  // hmm.vnt:57-59: (if (<= t 1) 1 ...)
     } else {
       Stream r(seed, (uint64_t)(p_base + p), step);
-      int prev = cur[p];
-      s = 1 + categorical_sim(r, tr + (prev - 1) * tb.S, tb.S, 1);
+      const int row = cur[p] - 1;
+      const double u = r.uniform(), d = denom[row];
+      if (!(d > 0.0)) {                       // categorical_sim's all-zero row: uniform
+        int k = (int)(u * (double)tb.S);
+        s = 1 + (k < tb.S ? k : tb.S - 1);
+      } else {
+        const double thr = u * d;
+        const double *c = cdf + row * tb.S;
+        int k = last_pos[row];
+        for (int i = tb.S - 1; i >= 0; --i) if (thr < c[i]) k = i;   // first i with thr < running sum
+        s = 1 + k;
+      }
     }
     cur[p] = s;
     // one byte into a particle-major row is a partial-sector write (a 32-byte read-modify-write per
     // particle); the newest column is left "pending" in cur[] when the caller can fold it into the
     // resampling gather that follows (hmm_gather_kernel), see HMMModel::hist_pending
     if (write_hist) hist[p * Tpad + t] = (uint8_t)s;
-    double w = categorical_logpmf(symbol - 1, em + (s - 1) * tb.O, tb.O, 1);
-    if (w != w) w = -INFINITY;
+    const double w = lw_emit[s - 1];
     double v = lw[p] + w;
     lw[p] = v;
     if (v != v) nanf = 1.0; else { mx = fmax(mx, v); mn = fmin(mn, v); }
@@ -289,7 +314,7 @@ struct HMMModel : Model {
   DevBuf<uint8_t> hista, histb;
   int32_t *cur = nullptr, *cur_alt = nullptr;
   uint8_t *hist = nullptr, *hist_alt = nullptr;
-  size_t smem;
+  size_t smem, smem_step;
   // column T-1 of hist is still only in cur[] (written by the last filter step); the resampling gather
   // inserts it while it copies the rows, every other reader of hist flushes it first
   bool hist_pending = false;
@@ -329,6 +354,7 @@ struct HMMModel : Model {
     VK_CUDA(cudaMemsetAsync(hist, 0, hista.bytes(), h->stream));
     VK_CUDA(cudaMemsetAsync(hist_alt, 0, histb.bytes(), h->stream));
     smem = (size_t)(n_rows * S + S * O) * sizeof(double);
+    smem_step = (size_t)(n_rows * S + n_rows + S) * sizeof(double) + (size_t)n_rows * sizeof(int);
   }
   int grid() const { return grid_for(h->P, 256, h->sm_count, 8); }
   void observe(int symbol) {
@@ -352,7 +378,7 @@ struct HMMModel : Model {
     for (; T < n; ++T) {
       uint32_t step = h->next_step();
       const bool last = T == n - 1;
-      hmm_step_kernel<<<grid(), 256, smem, h->stream>>>(cur, hist, Tpad, T, h->lw.p, incr_dev, tb, symbols_host[T],
+      hmm_step_kernel<<<grid(), 256, smem_step, h->stream>>>(cur, hist, Tpad, T, h->lw.p, incr_dev, tb, symbols_host[T],
                                                         h->P, h->p_base, h->seed, step, first ? 0 : 1, h->red.p,
                                                         h->counters.p, last ? 0 : 1);
       first = false;

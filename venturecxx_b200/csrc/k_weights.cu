@@ -384,13 +384,19 @@ __device__ __forceinline__ bool child_reaches(uint64_t k, uint64_t c, uint64_t W
   u128_t rhs = ((u128_t)c * (u128_t)(uint64_t)n_new) << 32;
   return lhs >= rhs;
 }
-__device__ __forceinline__ int64_t first_child_at_least(uint64_t c, uint64_t W, int64_t n_new, uint64_t U0) {
+// `ratio` = n_new / W and `u0f` = U0 / 2^32 in double (loop invariants of the caller): only the starting
+// estimate depends on them, the result is fixed by the exact integer test
+__device__ __forceinline__ int64_t first_child_at_least(uint64_t c, uint64_t W, int64_t n_new, uint64_t U0,
+                                                        double ratio, double u0f) {
   if (c == 0) return 0;
-  double est = (double)c * (double)n_new / (double)W - (double)U0 * (1.0 / 4294967296.0);
+  double est = fma((double)c, ratio, -u0f);
   int64_t k = est <= 0.0 ? 0 : (est >= (double)n_new ? n_new : (int64_t)est);
   while (k < n_new && !child_reaches((uint64_t)k, c, W, n_new, U0)) ++k;
   while (k > 0 && child_reaches((uint64_t)(k - 1), c, W, n_new, U0)) --k;
   return k;
+}
+__device__ __forceinline__ int64_t first_child_at_least(uint64_t c, uint64_t W, int64_t n_new, uint64_t U0) {
+  return first_child_at_least(c, W, n_new, U0, (double)n_new / (double)W, (double)U0 * (1.0 / 4294967296.0));
 }
 __device__ __forceinline__ uint64_t systematic_U0(const double *uniforms, uint64_t seed, uint32_t step) {
   double u;
@@ -506,12 +512,13 @@ systematic_offspring_kernel(const double *__restrict__ lw, int64_t n, const doub
   __syncthreads();
   if (s == 0) return;   // no mass in this thread's items: no children
   uint64_t run = tile_sums[blockIdx.x] + (w > 0 ? sh[w - 1] : 0ull) + inc - s;
-  int64_t k_lo = first_child_at_least(run, W, n_new, U0);
+  const double ratio = (double)n_new / (double)W, u0f = (double)U0 * (1.0 / 4294967296.0);
+  int64_t k_lo = first_child_at_least(run, W, n_new, U0, ratio, u0f);
 #pragma unroll
   for (int j = 0; j < SCAN_ITEMS; ++j) {
     if (q[j] == 0) continue;
     run += q[j];
-    int64_t k_hi = first_child_at_least(run, W, n_new, U0);
+    int64_t k_hi = first_child_at_least(run, W, n_new, U0, ratio, u0f);
     for (int64_t k = k_lo; k < k_hi; ++k) anc[k] = (int32_t)(base + j);
     k_lo = k_hi;
   }

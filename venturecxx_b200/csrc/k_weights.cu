@@ -384,12 +384,21 @@ __device__ __forceinline__ bool child_reaches(uint64_t k, uint64_t c, uint64_t W
   u128_t rhs = ((u128_t)c * (u128_t)(uint64_t)n_new) << 32;
   return lhs >= rhs;
 }
-// `ratio` = n_new / W and `u0f` = U0 / 2^32 in double (loop invariants of the caller): only the starting
-// estimate depends on them, the result is fixed by the exact integer test
+// `ratio` = n_new / W and `u0f` = U0 / 2^32 in double (loop invariants of the caller).
+// thr_k >= c  <=>  k + U0/2^32 >= c n_new / W, so the answer is ceil(x), x = c n_new / W - U0/2^32.  The
+// double evaluation of x is off by a few ulp (<< delta = (|x|+1) 2^-45): when x is further than delta
+// from an integer, ceil of the double IS the exact answer; otherwise (probability ~1e-7 per call) the
+// exact 128-bit test decides.  Same integer either way.
 __device__ __forceinline__ int64_t first_child_at_least(uint64_t c, uint64_t W, int64_t n_new, uint64_t U0,
                                                         double ratio, double u0f) {
   if (c == 0) return 0;
-  double est = fma((double)c, ratio, -u0f);
+  const double est = fma((double)c, ratio, -u0f);
+  const double fl = floor(est), frac = est - fl, delta = (fabs(est) + 1.0) * 2.842170943040401e-14;
+  if (frac > delta && frac < 1.0 - delta) {
+    if (fl < 0.0) return 0;
+    if (fl >= (double)n_new) return n_new;
+    return (int64_t)fl + 1;
+  }
   int64_t k = est <= 0.0 ? 0 : (est >= (double)n_new ? n_new : (int64_t)est);
   while (k < n_new && !child_reaches((uint64_t)k, c, W, n_new, U0)) ++k;
   while (k > 0 && child_reaches((uint64_t)(k - 1), c, W, n_new, U0)) --k;

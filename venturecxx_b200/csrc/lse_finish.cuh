@@ -35,16 +35,28 @@ __device__ __forceinline__ void lse_minmax_finish(double mx, double mn, double n
   __threadfence();
   if (threadIdx.x == 0) last = (atomicAdd(counter, 1u) == gridDim.x - 1);
   __syncthreads();
-  if (last && w == 0) {
+  if (last) {
+    // the whole block reads the per-block partials (a single warp walking them was a chain of
+    // gridDim.x/32 dependent L2 round trips at the tail of every producer kernel)
     __threadfence();
     mx = -INFINITY; mn = INFINITY; nanf = 0.0;
-    for (int b = lane; b < (int)gridDim.x; b += 32) {
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) {
       mx = fmax(mx, red[RED_PART + 3 * b + 0]);
       mn = fmin(mn, red[RED_PART + 3 * b + 1]);
       nanf = fmax(nanf, red[RED_PART + 3 * b + 2]);
     }
     mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
-    if (lane == 0) { red[0] = mx; red[1] = mn; red[2] = nanf; *counter = 0; }
+    __syncthreads();                      // sh[] was last read before the counter increment
+    if (lane == 0) { sh[0][w] = mx; sh[1][w] = mn; sh[2][w] = nanf; }
+    __syncthreads();
+    if (w == 0) {
+      int nw = blockDim.x >> 5;
+      mx = lane < nw ? sh[0][lane] : -INFINITY;
+      mn = lane < nw ? sh[1][lane] : INFINITY;
+      nanf = lane < nw ? sh[2][lane] : 0.0;
+      mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
+      if (lane == 0) { red[0] = mx; red[1] = mn; red[2] = nanf; *counter = 0; }
+    }
   }
 }
 

@@ -85,6 +85,20 @@ def test_resample_given_uniforms(orc):
     assert np.array_equal(anc, orc.ancestors(lw, P, 0, uniforms=u))
 
 
+@pytest.mark.parametrize("P", [1000, 1 << 16, (1 << 18) + 3])
+def test_systematic_thresholds_on_cdf_steps(orc, P):
+    # equal weights: child k's threshold (k + u) W / P sits EXACTLY on a CDF step when u = 0 -- the case
+    # the kernels' double-precision shortcut must hand to the exact 128-bit test (k_weights.cu
+    # first_child_at_least); also u just below 1 and weights that are exact powers of two apart
+    rng = np.random.default_rng(11)
+    for lw in [np.zeros(P), np.log(2.0) * rng.integers(0, 3, P).astype(np.float64)]:
+        for u in [0.0, 0.5, 1.0 - 2.0 ** -32, 1.0 - 2.0 ** -53, 2.0 ** -32]:
+            ts = make_ts(P)
+            ts.set_particle_log_weights(lw)
+            anc = ts.resample(P, mode="systematic", uniforms=[u], return_ancestors=True)
+            assert np.array_equal(anc, orc.ancestors(lw, P, 1, uniforms=[u])), (P, u)
+
+
 def test_resample_all_impossible_is_uniform(orc):
     # utils.py:93-99,176-180: all -inf => every parent equally likely
     P = 512

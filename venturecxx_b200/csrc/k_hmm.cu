@@ -29,65 +29,90 @@ struct HMMTables {
   const double *emit;   // S x O
 };
 
-// propagate one time step and weight by the emission
-__global__ void __launch_bounds__(256)
-hmm_step_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, int t /*0-based*/,
-                double *__restrict__ lw, double *__restrict__ incr, HMMTables tb, int symbol /*1-based*/,
-                int64_t P, int64_t p_base, uint64_t seed, uint32_t step, int accumulate_incr,
-                double *__restrict__ red, unsigned int *__restrict__ counter, int write_hist) {
-  // Per-CTA tables: a particle's draw and weight depend on (previous state, u) and (new state) only, so
-  // the row sums, the running sums categorical_sim compares against, and the S emission log densities
-  // are evaluated once per CTA by the SAME functions on the same inputs (bit-identical to evaluating
-  // them per particle) and the particle loop is Philox + S comparisons + two table reads.
-  extern __shared__ double sh[];
-  double *cdf = sh;                               // n_rows*S running sums of a transition row
-  double *denom = cdf + tb.n_rows * tb.S;         // n_rows
-  double *lw_emit = denom + tb.n_rows;            // S
-  int *last_pos = (int *)(lw_emit + tb.S);        // n_rows: last index with positive mass
-  for (int r_ = threadIdx.x; r_ < tb.n_rows; r_ += blockDim.x) {
+// Step tables, built once per model by hmm_step_tables_kernel with the same device functions a
+// per-particle evaluation would call (so the filter is bit-identical to the per-particle form):
+//   [cdf n_rows*S: running sums categorical_sim compares against][denom n_rows][last_pos n_rows (as double)]
+//   [lw_emit S*O: categorical_logpmf(o | state s), NaN -> -inf (lite/trace.py:438-448)]
+__host__ __device__ inline int hmm_step_table_len(int n_rows, int S, int O) { return n_rows * S + 2 * n_rows + S * O; }
+__global__ void hmm_step_tables_kernel(HMMTables tb, double *__restrict__ out) {
+  double *cdf = out, *denom = cdf + tb.n_rows * tb.S, *last_pos = denom + tb.n_rows, *lw_emit = last_pos + tb.n_rows;
+  for (int r_ = blockIdx.x * blockDim.x + threadIdx.x; r_ < tb.n_rows; r_ += gridDim.x * blockDim.x) {
     const double *ps = tb.trans + r_ * tb.S;
     double d = 0.0;
     for (int i = 0; i < tb.S; ++i) d += ps[i];
     double acc = 0.0; int last = 0;
     for (int i = 0; i < tb.S; ++i) { if (ps[i] > 0.0) last = i; acc += ps[i]; cdf[r_ * tb.S + i] = acc; }
-    denom[r_] = d; last_pos[r_] = last;
+    denom[r_] = d; last_pos[r_] = (double)last;
   }
-  for (int s_ = threadIdx.x; s_ < tb.S; s_ += blockDim.x) {
-    double w = categorical_logpmf(symbol - 1, tb.emit + s_ * tb.O, tb.O, 1);
-    lw_emit[s_] = (w != w) ? -INFINITY : w;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < tb.S * tb.O; i += gridDim.x * blockDim.x) {
+    double w = categorical_logpmf(i % tb.O, tb.emit + (i / tb.O) * tb.O, tb.O, 1);
+    lw_emit[i] = (w != w) ? -INFINITY : w;
   }
+}
+
+// propagate one time step and weight by the emission.  Each thread owns HMM_STEP_ITEMS particles of a
+// CTA tile and issues all of their loads before any arithmetic (one DRAM latency per thread instead of
+// two per particle); the particle loop is Philox + S comparisons + two shared-memory table reads.
+static const int HMM_STEP_ITEMS = 4;
+__global__ void __launch_bounds__(256)
+hmm_step_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, int t /*0-based*/,
+                double *__restrict__ lw, double *__restrict__ incr, HMMTables tb, const double *__restrict__ tables,
+                int symbol /*1-based*/, int64_t P, int64_t p_base, uint64_t seed, uint32_t step,
+                int accumulate_incr, double *__restrict__ red, unsigned int *__restrict__ counter, int write_hist) {
+  extern __shared__ double sh[];
+  const int n_tr = tb.n_rows * tb.S + 2 * tb.n_rows;
+  double *cdf = sh, *denom = cdf + tb.n_rows * tb.S, *last_pos = denom + tb.n_rows, *lw_emit = last_pos + tb.n_rows;
+  for (int i = threadIdx.x; i < n_tr; i += blockDim.x) sh[i] = tables[i];
+  for (int i = threadIdx.x; i < tb.S; i += blockDim.x) lw_emit[i] = tables[n_tr + i * tb.O + (symbol - 1)];
   __syncthreads();
   double mx = -INFINITY, mn = INFINITY, nanf = 0.0;
-  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
-       p += (int64_t)gridDim.x * blockDim.x) {
-    int s;
-    if (t == 0) {
-      s = tb.init;  // hmm.vnt:57-59: (if (<= t 1) 1 ...)
-    } else {
-      Stream r(seed, (uint64_t)(p_base + p), step);
-      const int row = cur[p] - 1;
-      const double u = r.uniform(), d = denom[row];
-      if (!(d > 0.0)) {                       // categorical_sim's all-zero row: uniform
-        int k = (int)(u * (double)tb.S);
-        s = 1 + (k < tb.S ? k : tb.S - 1);
-      } else {
-        const double thr = u * d;
-        const double *c = cdf + row * tb.S;
-        int k = last_pos[row];
-        for (int i = tb.S - 1; i >= 0; --i) if (thr < c[i]) k = i;   // first i with thr < running sum
-        s = 1 + k;
+  const int64_t tile = (int64_t)blockDim.x * HMM_STEP_ITEMS;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < P; base += (int64_t)gridDim.x * tile) {
+    int prev[HMM_STEP_ITEMS];
+    double lwv[HMM_STEP_ITEMS], inc[HMM_STEP_ITEMS];
+#pragma unroll
+    for (int j = 0; j < HMM_STEP_ITEMS; ++j) {
+      const int64_t p = base + (int64_t)j * blockDim.x + threadIdx.x;
+      prev[j] = 1; lwv[j] = 0.0; inc[j] = 0.0;
+      if (p < P) {
+        if (t > 0) prev[j] = cur[p];
+        lwv[j] = lw[p];
+        if (incr && accumulate_incr) inc[j] = incr[p];
       }
     }
-    cur[p] = s;
-    // one byte into a particle-major row is a partial-sector write (a 32-byte read-modify-write per
-    // particle); the newest column is left "pending" in cur[] when the caller can fold it into the
-    // resampling gather that follows (hmm_gather_kernel), see HMMModel::hist_pending
-    if (write_hist) hist[p * Tpad + t] = (uint8_t)s;
-    const double w = lw_emit[s - 1];
-    double v = lw[p] + w;
-    lw[p] = v;
-    if (v != v) nanf = 1.0; else { mx = fmax(mx, v); mn = fmin(mn, v); }
-    if (incr) incr[p] = accumulate_incr ? incr[p] + w : w;
+#pragma unroll
+    for (int j = 0; j < HMM_STEP_ITEMS; ++j) {
+      const int64_t p = base + (int64_t)j * blockDim.x + threadIdx.x;
+      if (p >= P) continue;
+      int s;
+      if (t == 0) {
+        s = tb.init;  // hmm.vnt:57-59: (if (<= t 1) 1 ...)
+      } else {
+        Stream r(seed, (uint64_t)(p_base + p), step);
+        const int row = prev[j] - 1;
+        const double u = r.uniform(), d = denom[row];
+        if (!(d > 0.0)) {                       // categorical_sim's all-zero row: uniform
+          int k = (int)(u * (double)tb.S);
+          s = 1 + (k < tb.S ? k : tb.S - 1);
+        } else {
+          const double thr = u * d;
+          const double *c = cdf + row * tb.S;
+          int k = (int)last_pos[row];
+          for (int i = tb.S - 1; i >= 0; --i) if (thr < c[i]) k = i;   // first i with thr < running sum
+          s = 1 + k;
+        }
+      }
+      cur[p] = s;
+      // one byte into a particle-major row is a partial-sector write (a 32-byte read-modify-write per
+      // particle); the newest column is left "pending" in cur[] when the caller can fold it into the
+      // resampling gather that follows (hmm_gather_kernel), see HMMModel::hist_pending
+      if (write_hist) hist[p * Tpad + t] = (uint8_t)s;
+      const double w = lw_emit[s - 1];
+      const double v = lwv[j] + w;
+      lw[p] = v;
+      if (v != v) nanf = 1.0; else { mx = fmax(mx, v); mn = fmin(mn, v); }
+      if (incr) incr[p] = inc[j] + w;
+    }
   }
   // the filter resamples right after this step: reduce (max, min, NaN flag) of the weights just written so
   // that vk_resample / vk_p2p_resample can skip their own read pass (lse_finish.cuh)
@@ -309,7 +334,7 @@ struct HMMModel : Model {
   HMMTables tb;
   int T_max, Tpad, T = 0 /*propagated time steps*/;
   std::vector<int32_t> symbols_host;   // all observed symbols (propagated first, then pending)
-  DevBuf<double> trans, emit;
+  DevBuf<double> trans, emit, step_tables;
   DevBuf<int32_t> symbols, cura, curb;
   DevBuf<uint8_t> hista, histb;
   int32_t *cur = nullptr, *cur_alt = nullptr;
@@ -354,9 +379,13 @@ struct HMMModel : Model {
     VK_CUDA(cudaMemsetAsync(hist, 0, hista.bytes(), h->stream));
     VK_CUDA(cudaMemsetAsync(hist_alt, 0, histb.bytes(), h->stream));
     smem = (size_t)(n_rows * S + S * O) * sizeof(double);
-    smem_step = (size_t)(n_rows * S + n_rows + S) * sizeof(double) + (size_t)n_rows * sizeof(int);
+    smem_step = (size_t)(n_rows * S + 2 * n_rows + S) * sizeof(double);
+    step_tables.alloc((size_t)hmm_step_table_len(n_rows, S, O));
+    hmm_step_tables_kernel<<<1, 256, 0, h->stream>>>(tb, step_tables.p);
+    VK_CUDA(cudaGetLastError());
   }
   int grid() const { return grid_for(h->P, 256, h->sm_count, 8); }
+  int step_grid() const { return grid_for((h->P + HMM_STEP_ITEMS - 1) / HMM_STEP_ITEMS, 256, h->sm_count, 8); }
   void observe(int symbol) {
     VK_REQUIRE(symbol >= 1 && symbol <= tb.O, VK_EINVAL, "hmm: observed symbol out of range");
     VK_REQUIRE((int)symbols_host.size() < T_max, VK_EINVAL, "hmm: history capacity (T_max) exceeded");
@@ -378,9 +407,9 @@ struct HMMModel : Model {
     for (; T < n; ++T) {
       uint32_t step = h->next_step();
       const bool last = T == n - 1;
-      hmm_step_kernel<<<grid(), 256, smem_step, h->stream>>>(cur, hist, Tpad, T, h->lw.p, incr_dev, tb, symbols_host[T],
-                                                        h->P, h->p_base, h->seed, step, first ? 0 : 1, h->red.p,
-                                                        h->counters.p, last ? 0 : 1);
+      hmm_step_kernel<<<step_grid(), 256, smem_step, h->stream>>>(cur, hist, Tpad, T, h->lw.p, incr_dev, tb, step_tables.p,
+                                                             symbols_host[T], h->P, h->p_base, h->seed, step,
+                                                             first ? 0 : 1, h->red.p, h->counters.p, last ? 0 : 1);
       first = false;
     }
     hist_pending = true;

@@ -301,23 +301,28 @@ __global__ void hmm_flush_kernel(const int32_t *__restrict__ cur, uint8_t *__res
     hist[p * Tpad + t] = (uint8_t)cur[p];
 }
 // Ancestor gather of the whole HMM state in one pass: child k takes parent a = anc[k]'s newest state
-// (cur) and history row; a pending newest column t_pend (>= 0) is inserted into the row on the way, so
-// the row is written once, as whole 16-byte units.  One thread per 16-byte unit of a child row.
+// (cur) and the LIVE 16-byte units of its history row (columns < T; `units` = ceil(T/16) of the
+// `row_units` a row has -- columns >= T are never read by anybody); a pending newest column t_pend (>= 0)
+// is inserted into the row on the way, so the row is written once, as whole units.  When lw_out is given,
+// the evened-out weight lw[k] = red[4] - log_n_new (utils.py:152-157) is written by the same pass.
+// One thread per live unit of a child row.
 __global__ void __launch_bounds__(256)
 hmm_gather_kernel(const int32_t *__restrict__ cur_in, int32_t *__restrict__ cur_out,
                   const uint4 *__restrict__ hist_in, uint4 *__restrict__ hist_out,
-                  const int32_t *__restrict__ anc, int64_t n_new, int units, int t_pend) {
+                  const int32_t *__restrict__ anc, int64_t n_new, int units, int row_units, int t_pend,
+                  double *__restrict__ lw_out, const double *__restrict__ red, double log_n_new) {
   const int64_t total = n_new * units;
   const int pu = t_pend >= 0 ? t_pend >> 4 : -1, pw = (t_pend >> 2) & 3, psh = (t_pend & 3) * 8;
+  const double even = lw_out ? red[4] - log_n_new : 0.0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t k = i / units;
     const int c = (int)(i - k * units);
     const int64_t a = anc[k];
-    uint4 v = hist_in[a * units + c];
+    uint4 v = hist_in[a * row_units + c];
     if (c == 0 || c == pu) {
       const uint32_t s = (uint32_t)cur_in[a];
-      if (c == 0) cur_out[k] = (int32_t)s;
+      if (c == 0) { cur_out[k] = (int32_t)s; if (lw_out) lw_out[k] = even; }
       if (c == pu) {
         const uint32_t keep = ~(0xFFu << psh), ins = (s & 0xFFu) << psh;
         if (pw == 0) v.x = (v.x & keep) | ins;
@@ -326,7 +331,7 @@ hmm_gather_kernel(const int32_t *__restrict__ cur_in, int32_t *__restrict__ cur_
         else v.w = (v.w & keep) | ins;
       }
     }
-    hist_out[k * units + c] = v;
+    hist_out[k * row_units + c] = v;
   }
 }
 
@@ -349,14 +354,17 @@ struct HMMModel : Model {
     VK_CUDA(cudaGetLastError());
     hist_pending = false;
   }
-  bool gather(const int32_t *anc_dev, int64_t n_new) override {
-    const int units = Tpad / 16;
+  int gather(const int32_t *anc_dev, int64_t n_new, double *lw_out, const double *red, double log_n_new) override {
+    const int row_units = Tpad / 16;
+    int units = (T + 15) / 16;
+    if (units < 1) units = 1;
     hmm_gather_kernel<<<grid_for(n_new * units, 256, h->sm_count, 8), 256, 0, h->stream>>>(
-        cur, cur_alt, (const uint4 *)hist, (uint4 *)hist_alt, anc_dev, n_new, units, hist_pending ? T - 1 : -1);
+        cur, cur_alt, (const uint4 *)hist, (uint4 *)hist_alt, anc_dev, n_new, units, row_units,
+        hist_pending ? T - 1 : -1, lw_out, red, log_n_new);
     VK_CUDA(cudaGetLastError());
     std::swap(cur, cur_alt); std::swap(hist, hist_alt);
     hist_pending = false;
-    return true;
+    return lw_out ? 3 : 1;
   }
 
   HMMModel(vk_particles *h_, int S, int O, int n_rows, const double *trans_host, const double *emit_host,

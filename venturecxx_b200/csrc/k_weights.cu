@@ -340,9 +340,9 @@ void build_fixed_cdf(vk_particles *h, const double *red_or_null, double m, int f
   VK_CUDA(cudaGetLastError());
 }
 
-void gather_state(vk_particles *h, const int32_t *anc_dev, int64_t n_new) {
+int gather_state(vk_particles *h, const int32_t *anc_dev, int64_t n_new, double *lw_out, double log_n_new) {
   cudaStream_t st = h->stream;
-  if (h->model->gather(anc_dev, n_new)) return;
+  if (int done = h->model->gather(anc_dev, n_new, lw_out, h->red.p, log_n_new)) return done;
   std::vector<StateArray> arrs = h->model->state_arrays();
   for (auto &a : arrs) {
     if (a.elem_bytes == 0) {
@@ -368,6 +368,7 @@ void gather_state(vk_particles *h, const int32_t *anc_dev, int64_t n_new) {
     void *t = *a.cur; *a.cur = *a.alt; *a.alt = t;
   }
   VK_CUDA(cudaGetLastError());
+  return 1;
 }
 
 // ---- systematic resampling without a CDF array or a search ------------------------
@@ -491,14 +492,54 @@ scan_tile_sums_lse_kernel(uint64_t *tile_sums, const double *tile_exp, int n_til
 }
 
 // pass C': running CDF in registers -> children ranges -> anc[k] = i  (no CDF array, no search)
+// RAW_TILES: tile_sums holds the per-tile totals as fixed_tile_sums_exp_kernel wrote them; every CTA sums
+// the tiles before its own (and all of them, for W) itself -- integer sums, so any order gives the same
+// CDF -- and CTA 0 finishes the logsumexp from tile_exp (what scan_tile_sums_lse_kernel does), which
+// removes that single-CTA kernel from the chain when there are few tiles.
+template <bool RAW_TILES>
 __global__ void __launch_bounds__(SCAN_THREADS)
-systematic_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__restrict__ red,
-                            double scale, const uint64_t *__restrict__ tile_sums, int n_tiles,
-                            int64_t n_new, uint64_t seed, uint32_t step,
+systematic_offspring_kernel(const double *__restrict__ lw, int64_t n, double *__restrict__ red,
+                            double scale, uint64_t *__restrict__ tile_sums, const double *__restrict__ tile_exp,
+                            int n_tiles, int64_t n_new, uint64_t seed, uint32_t step,
                             const double *__restrict__ uniforms, int32_t *__restrict__ anc) {
   __shared__ uint64_t sh[32];
+  __shared__ uint64_t sh2[2][SCAN_THREADS / 32];
+  __shared__ double shd[33];
   const double m = red[0];
-  const uint64_t W = tile_sums[n_tiles];
+  uint64_t W, tile_base;
+  if (RAW_TILES) {
+    uint64_t pre = 0, tot = 0;
+    double se = 0.0;
+    for (int b = threadIdx.x; b < n_tiles; b += SCAN_THREADS) {
+      const uint64_t v = tile_sums[b];
+      tot += v;
+      if (b < (int)blockIdx.x) pre += v;
+      if (blockIdx.x == 0) se += tile_exp[b];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { pre += __shfl_xor_sync(0xffffffffu, pre, o); tot += __shfl_xor_sync(0xffffffffu, tot, o); }
+    if ((threadIdx.x & 31) == 0) { sh2[0][threadIdx.x >> 5] = pre; sh2[1][threadIdx.x >> 5] = tot; }
+    __syncthreads();
+    pre = 0; tot = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_THREADS / 32; ++k) { pre += sh2[0][k]; tot += sh2[1][k]; }
+    W = tot; tile_base = pre;
+    if (blockIdx.x == 0) {     // uniform branch: the whole CTA
+      se = block_sum(se, shd);
+      if (threadIdx.x == 0) {
+        const double mn = red[1], nanf = red[2];
+        double lse;
+        if (n == 0) lse = -INFINITY;
+        else if (nanf != 0.0) lse = NAN;
+        else if (isinf(m) && mn != -m) lse = m;
+        else if (isinf(m)) lse = NAN;
+        else lse = m + log(se);
+        red[3] = se; red[4] = lse;
+      }
+    }
+  } else {
+    W = tile_sums[n_tiles]; tile_base = tile_sums[blockIdx.x];
+  }
   const uint64_t U0 = systematic_U0(uniforms, seed, step);
   int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
   uint64_t q[SCAN_ITEMS];
@@ -520,7 +561,7 @@ systematic_offspring_kernel(const double *__restrict__ lw, int64_t n, const doub
   }
   __syncthreads();
   if (s == 0) return;   // no mass in this thread's items: no children
-  uint64_t run = tile_sums[blockIdx.x] + (w > 0 ? sh[w - 1] : 0ull) + inc - s;
+  uint64_t run = tile_base + (w > 0 ? sh[w - 1] : 0ull) + inc - s;
   const double ratio = (double)n_new / (double)W, u0f = (double)U0 * (1.0 / 4294967296.0);
   int64_t k_lo = first_child_at_least(run, W, n_new, U0, ratio, u0f);
 #pragma unroll
@@ -696,17 +737,22 @@ void resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms_d
     lse_pass1_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p);
   h->lw_minmax_fresh = false;
   fixed_tile_sums_exp_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p);
-  scan_tile_sums_lse_kernel<<<1, 1024, 0, st>>>(h->red_u.p, h->tile_exp.p, n_tiles, P, h->red.p);
-  if (mode == VK_RESAMPLE_SYSTEMATIC) {
-    systematic_offspring_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, n_tiles, n_new,
-                                                                  h->seed, step, uniforms_dev, h->anc.p);
+  const bool raw_tiles = mode == VK_RESAMPLE_SYSTEMATIC && n_tiles <= 1024;   // each CTA reads all tile totals
+  if (!raw_tiles) scan_tile_sums_lse_kernel<<<1, 1024, 0, st>>>(h->red_u.p, h->tile_exp.p, n_tiles, P, h->red.p);
+  if (raw_tiles) {
+    systematic_offspring_kernel<true><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p,
+                                                                        n_tiles, n_new, h->seed, step, uniforms_dev, h->anc.p);
+  } else if (mode == VK_RESAMPLE_SYSTEMATIC) {
+    systematic_offspring_kernel<false><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p,
+                                                                         n_tiles, n_new, h->seed, step, uniforms_dev, h->anc.p);
   } else {
     fixed_cdf_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, 0.0, h->red.p, scale, h->red_u.p, h->cdf.p);
     launch_ancestor_search_single(h, n_new, mode, step, uniforms_dev, grid_for(n_new, 256, h->sm_count, 8));
   }
   VK_CUDA(cudaGetLastError());
-  gather_state(h, h->anc.p, n_new);
-  fill_kernel<<<grid_for(n_new, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, n_new, h->red.p, log((double)n_new));
+  const double log_n_new = log((double)n_new);
+  if (!(gather_state(h, h->anc.p, n_new, h->lw.p, log_n_new) & 2))
+    fill_kernel<<<grid_for(n_new, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, n_new, h->red.p, log_n_new);
   VK_CUDA(cudaGetLastError());
   h->model->after_resample();
 }

@@ -138,9 +138,13 @@ struct Model {
   // arrays gathered by ancestor index on resample; after the gather the model
   // swaps cur/alt itself via StateArray.
   virtual std::vector<StateArray> state_arrays() = 0;
-  // a model may gather its whole state by ancestor in one fused pass of its own (returns true);
-  // otherwise the generic per-array gather over state_arrays() runs
-  virtual bool gather(const int32_t *anc_dev, int64_t n_new) { (void)anc_dev; (void)n_new; return false; }
+  // a model may gather its whole state by ancestor in one fused pass of its own; returns 0 (not done: the
+  // generic per-array gather over state_arrays() runs), 1 (state gathered) or 3 (state gathered AND the
+  // evened-out weights lw[k] = red[4] - log_n_new written, so the caller skips its fill pass).
+  // lw_out may be null (no fill wanted).
+  virtual int gather(const int32_t *anc_dev, int64_t n_new, double *lw_out, const double *red, double log_n_new) {
+    (void)anc_dev; (void)n_new; (void)lw_out; (void)red; (void)log_n_new; return 0;
+  }
   virtual void after_resample() {}
   virtual int device_buffer(int which, void **p, int64_t *bytes) { return VK_EINVAL; }
 };

@@ -7,7 +7,7 @@ void device_logsumexp(const double *a, int64_t n, double *red, unsigned int *cou
                       int sm_count, cudaStream_t st);
 int frac_bits_for(int64_t P_total);
 void build_fixed_cdf(vk_particles *h, const double *red_or_null, double m, int frac_bits);
-void gather_state(vk_particles *h, const int32_t *anc_dev, int64_t n_new);
+int gather_state(vk_particles *h, const int32_t *anc_dev, int64_t n_new, double *lw_out, double log_n_new);
 void resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms_dev);
 void launch_normalized_probs(vk_particles *h, double *out_dev);
 void launch_ancestor_search_single(vk_particles *h, int64_t n_new, int mode, uint32_t step,

@@ -35,6 +35,23 @@ class NormalNormalModel(Model):
         y = np.ascontiguousarray(np.atleast_1d(y), dtype=np.float64)
         _lib.call("vk_nn_observe", h, _lib.ptr(y), y.size)
 
+    # -- interchange.py: the program this model stands for, and its random values in evaluation order
+    def _ys(self, obs):
+        return [float(v) for (y,) in obs for v in np.atleast_1d(y)]
+
+    def program(self, obs):
+        from .interchange import define, number, observe
+        return [define("x", ["normal", self.prior_mu, self.prior_sigma])] + \
+            [observe(["normal", "x", self.obs_sigma], number(y)) for y in self._ys(obs)]
+
+    def random_values(self, obs, sites):
+        from .interchange import number
+        return [number(sites[0])] + [number(y) for y in self._ys(obs)]
+
+    def sites_from_random_values(self, obs, values):
+        from .interchange import unbox
+        return np.array([unbox(values[0])])
+
 
 class LogisticRegressionModel(Model):
     """assume w_j = normal(prior_mu, prior_sigma) (j<D); assume w = array(w_0..);
@@ -58,6 +75,29 @@ class LogisticRegressionModel(Model):
             raise _lib.VentureException("invalid_argument", "X and y disagree on the number of observations")
         _lib.call("vk_blr_observe", h, _lib.ptr(X), _lib.ptr(y), y.size)
 
+    def _rows(self, obs):
+        for X, y in obs:
+            X = np.asarray(X, dtype=np.float64).reshape(-1, self.D)
+            y = np.asarray(y).reshape(-1)
+            for i in range(len(y)):
+                yield X[i], bool(y[i])
+
+    def program(self, obs):
+        from .interchange import boolean, define, observe
+        prog = [define("w_%d" % j, ["normal", self.prior_mu, self.prior_sigma]) for j in range(self.D)]
+        prog.append(define("w", ["array"] + ["w_%d" % j for j in range(self.D)]))
+        for x, y in self._rows(obs):
+            prog.append(observe(["log_odds_flip", ["vector_dot", "w", ["array"] + [float(v) for v in x]]], boolean(y)))
+        return prog
+
+    def random_values(self, obs, sites):
+        from .interchange import boolean, number
+        return [number(sites[j]) for j in range(self.D)] + [boolean(y) for _x, y in self._rows(obs)]
+
+    def sites_from_random_values(self, obs, values):
+        from .interchange import unbox
+        return np.array([unbox(values[j]) for j in range(self.D)])
+
 
 class HMMModel(Model):
     """examples/hmm.vnt:31-60: state(1) = init_state, state(t) ~ categorical(T[state(t-1)-1], 1..S),
@@ -78,6 +118,45 @@ class HMMModel(Model):
 
     def _observe(self, h, symbol):
         _lib.call("vk_hmm_observe", h, int(symbol))
+
+    def program(self, obs):
+        """examples/hmm.vnt:31-60 and the observe of :71; (state t) requests state(t-1) recursively
+        through mem, so observing times 1..T in order creates the states in order."""
+        from .interchange import define, number, observe
+        states = ["array"] + list(range(1, self.S + 1))
+        outs = ["array"] + list(range(1, self.O + 1))
+        prog = [define("transition_matrix", ["array"] + [["simplex"] + [float(v) for v in r] for r in self.trans]),
+                define("emission_matrix", ["array"] + [["simplex"] + [float(v) for v in r] for r in self.emit]),
+                define("transition", ["lambda", ["state"],
+                                      ["categorical", ["lookup", "transition_matrix", ["sub", "state", 1]], states]]),
+                define("emission", ["lambda", ["state"],
+                                    ["categorical", ["lookup", "emission_matrix", ["sub", "state", 1]], outs]]),
+                define("state", ["mem", ["lambda", ["t"], ["tag", ["quote", "seq"], "t",
+                                                           ["if", ["lte", "t", 1], self.init_state,
+                                                            ["transition", ["state", ["sub", "t", 1]]]]]]])]
+        for t, (d,) in enumerate(obs):
+            prog.append(observe(["emission", ["state", t + 1]], number(int(d))))
+        return prog
+
+    def random_values(self, obs, sites):
+        # evaluation order: obs_1 (state(1) is deterministic); then state(t), obs_t for t = 2..T
+        from .interchange import number
+        out = []
+        for t, (d,) in enumerate(obs):
+            if t > 0:
+                out.append(number(int(sites[t])))
+            out.append(number(int(d)))
+        return out
+
+    def sites_from_random_values(self, obs, values):
+        from .interchange import unbox
+        T = len(obs)
+        sites = np.empty(T)
+        if T:
+            sites[0] = self.init_state
+        for t in range(1, T):
+            sites[t] = unbox(values[2 * t - 1])
+        return sites
 
 
 class LDAModel(Model):
@@ -101,3 +180,39 @@ class LDAModel(Model):
         doc = np.ascontiguousarray(np.atleast_1d(doc), dtype=np.int32)
         word = np.ascontiguousarray(np.atleast_1d(word), dtype=np.int32)
         _lib.call("vk_lda_observe", h, _lib.ptr(doc), _lib.ptr(word), doc.size)
+
+    def _tokens(self, obs):
+        pos = {}
+        for doc, word in obs:
+            for d, w in zip(np.atleast_1d(doc), np.atleast_1d(word)):
+                d = int(d)
+                pos[d] = pos.get(d, -1) + 1
+                yield d, pos[d], int(w)
+
+    def program(self, obs):
+        """examples/lda.vnt:18-41: (model n_topics vocab_size) then one observe per token."""
+        from .interchange import define, integer, observe
+        prog = [define("n_topics", self.K), define("vocab_size", self.V),
+                define("alpha_document_topic", ["gamma", self.hyper_shape, self.hyper_rate]),
+                define("alpha_topic_word", ["gamma", self.hyper_shape, self.hyper_rate]),
+                define("doc", ["mem", ["lambda", ["doc_id"], ["make_sym_dir_cat", "alpha_document_topic", "n_topics"]]]),
+                define("topic", ["mem", ["lambda", ["topic_id"], ["make_sym_dir_cat", "alpha_topic_word", "vocab_size"]]]),
+                define("word", ["mem", ["lambda", ["doc_id", "pos"], [["topic", [["doc", "doc_id"]]]]]])]
+        for d, pos, w in self._tokens(obs):
+            prog.append(observe(["word", d, pos], integer(w)))
+        return prog
+
+    def random_values(self, obs, sites):
+        # evaluation order: the two gamma assumes; per token the topic draw ((doc d)) -- a VentureInteger,
+        # the default outcome objects of make_sym_dir_cat (dirichlet.py:218) -- then the observed word
+        from .interchange import integer, number
+        out = [number(sites[0]), number(sites[1])]
+        for i, (_d, _pos, w) in enumerate(self._tokens(obs)):
+            out.append(integer(sites[2 + i]))
+            out.append(integer(w))
+        return out
+
+    def sites_from_random_values(self, obs, values):
+        from .interchange import unbox
+        n = sum(1 for _ in self._tokens(obs))
+        return np.array([unbox(values[0]), unbox(values[1])] + [unbox(values[2 + 2 * i]) for i in range(n)], dtype=np.float64)

@@ -34,6 +34,7 @@ class B200TraceSet(object):
         self.device = int(device)
         self._h = model._create(int(n_particles), int(seed), self.device)
         self.n_particles = int(n_particles)
+        self._observed = []
         if particle_base:
             _lib.call("vk_set_particle_base", self._h, int(particle_base))
         # `assume` simulates every latent from its prior (regen.py eval)
@@ -97,12 +98,32 @@ class B200TraceSet(object):
         """engine.observe -> TraceSet.observe (trace_set.py:154-155): values stay
         unpropagated until incorporate()."""
         self.model._observe(self._h, *args)
+        self._observed.append(args)       # host record of the observe directives (interchange.py); not copied
+
+    def observations(self):
+        """The observe calls made so far, in order, as given (argument tuples)."""
+        return list(self._observed)
+
+    # -- state interchange with Lite (interchange.py; SURVEY 8(f) N3) ----------
+    def dump_particle(self, index):
+        """What engine.trace.Trace.dump() returns for a Lite trace holding particle `index`."""
+        from . import interchange
+        return interchange.dump_particle(self, int(index))
+
+    def dump(self):
+        from . import interchange
+        return interchange.dump(self)
+
+    def load(self, serialized):
+        from . import interchange
+        interchange.load(self, serialized)
 
     def forget_observations(self):
         """engine.forget of every observation (trace_set.py:157-161): returns the
         per-particle weights unconstrain() reports; log_weights unchanged."""
         out = self._out()
         _lib.call("vk_forget_observations", self._h, _lib.ptr(out))
+        self._observed = []
         return out
 
     def reset_to_prior(self):

@@ -293,6 +293,65 @@ __device__ __forceinline__ void fm_softplus_accum(double v, const FmCoef &cf, ui
   af = fma(r2, Q, af);
   aL += (long long)(((unsigned long long)L_hi << 32) | L_lo);
 }
+// ---- grouped variant: ONE log for four observations ---------------------------------------
+//   sum_k log1p(e_k) = log prod_k (1 + e_k),   prod in [1,16]
+// The exponential half is fm_softplus_accum's; the logarithm half runs once per group:
+//   q = 2^n m, m in [1,2): n and the table index k = round(128 (m - 1)) come from the high word with
+//   integer instructions; r2 = m inv[k] - 1 (one FMA, inv[k] is an exact 20-bit value);
+//   log q = n ln2 + L[k] + r2 Q(r2).
+// fp64 instructions per observation: 9 (exp) + 14/4 (log) = 12.5 instead of 17, log-table reads 1/4.
+// What is given up is RELATIVE accuracy of a single tiny term (1 + 1e-20 rounds to 1); the ABSOLUTE error
+// per group stays ~4 ulp of a number in [0, 2.8] (four additions, three products, one FMA), which is what
+// a sum of N ~ 1e4 terms of magnitude ~1 sees: measured against the term-by-term version in
+// tests/test_gpu_blr.py (chains and log likelihoods equal to the oracle's at 1e-12).
+__device__ __forceinline__ double fm_exp_neg_abs(double v, const FmCoef &cf, uint32_t exp_base) {
+  const double MAGIC = 6755399441055744.0;       // 1.5 * 2^52: ulp 1
+  int hi = __double2hiint(v) & 0x7fffffff;
+  hi = min(hi, 0x4085E000);
+  const double a = __hiloint2double(hi, __double2loint(v));
+  const double t = fma(a, cf.neg_scale, MAGIC);            // low word = m = rint(-a 64/ln2)
+  const int m = __double2loint(t);
+  const double nf = t - MAGIC;
+  const double r = fma(nf, -cf.c_ln2, -a);
+  double T;
+  uint32_t ea, th;
+  asm("mad.lo.u32 %0, %1, 128, %2;" : "=r"(ea) : "r"((uint32_t)(m & 63)), "r"(exp_base));
+  asm("ld.shared.f64 %0, [%1];" : "=d"(T) : "r"(ea));
+  asm("mad.lo.u32 %0, %1, 16384, %2;" : "=r"(th) : "r"((uint32_t)(m & ~63)), "r"((uint32_t)__double2hiint(T)));
+  const double Ts = __hiloint2double((int)th, __double2loint(T));   // T * 2^(m>>6)
+  double E = cf.E[4];
+  E = fma(E, r, cf.E[3]);
+  E = fma(E, r, cf.E[2]);
+  E = fma(E, r, cf.E[1]);
+  E = fma(E, r, cf.E[0]);
+  return fma(Ts * r, E, Ts);
+}
+// af += r2 Q(r2), aL += L[k] (2^-52 fixed point), an += biased exponent of the product (1023 per group
+// is subtracted by the caller)
+__device__ __forceinline__ void fm_log_group4(double e0, double e1, double e2, double e3, const FmCoef &cf,
+                                              uint32_t log_base, double &af, long long &aL, int &an) {
+  const double q = ((1.0 + e0) * (1.0 + e1)) * ((1.0 + e2) * (1.0 + e3));
+  const uint32_t hi = (uint32_t)__double2hiint(q);
+  an += (int)(hi >> 20);
+  const uint32_t mant = hi & 0xFFFFFu;
+  const double m = __hiloint2double((int)(mant | 0x3FF00000u), __double2loint(q));
+  const uint32_t k = (mant + 0x1000u) >> 13;               // round(128 (m - 1)) in [0,128]
+  uint32_t inv_hi, c_hi, L_lo, L_hi, la;
+  asm("mad.lo.u32 %0, %1, 128, %2;" : "=r"(la) : "r"(k), "r"(log_base));
+  asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+      : "=r"(inv_hi), "=r"(c_hi), "=r"(L_lo), "=r"(L_hi)
+      : "r"(la));
+  (void)c_hi;
+  const double r2 = fma(m, __hiloint2double((int)inv_hi, 0), -1.0);
+  double Q = cf.Q[5];
+  Q = fma(Q, r2, cf.Q[4]);
+  Q = fma(Q, r2, cf.Q[3]);
+  Q = fma(Q, r2, cf.Q[2]);
+  Q = fma(Q, r2, cf.Q[1]);
+  Q = fma(Q, r2, cf.Q[0]);
+  af = fma(r2, Q, af);
+  aL += (long long)(((unsigned long long)L_hi << 32) | L_lo);
+}
 #endif  // __CUDACC__
 
 // host-side convenience (tests): unreplicated tables

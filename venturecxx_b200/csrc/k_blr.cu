@@ -236,6 +236,7 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
         long long aL[UNROLL];            // sum L[k], 2^-52 fixed point
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) { am[u] = 0.0; af[u] = 0.0; aL[u] = 0; }
+        int an = 0;                      // grouped logarithm: sum of biased exponents (UNROLL == 4)
         const double *xp = xcol + tid + BLR_MH_TILE;
         int i0 = tid;
         for (int it = 0; it < iters; ++it, xp += BLR_MH_TILE, i0 += BLR_MH_TILE) {
@@ -253,15 +254,24 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u) xn[u] = __ldg(src + u * THREADS);
           }
+          if (UNROLL == 4) {
+            // one logarithm for the four observations of this iteration (fast_math.cuh: fm_log_group4)
+            double e4[4];
 #pragma unroll
-          for (int u = 0; u < UNROLL; ++u) {
-            fm_softplus_accum(v[u], cf, exp_base, log_base, af[u], aL[u]);
-            am[u] += fabs(v[u]);
+            for (int u = 0; u < 4; ++u) { e4[u] = fm_exp_neg_abs(v[u], cf, exp_base); am[u] += fabs(v[u]); }
+            fm_log_group4(e4[0], e4[1], e4[2], e4[3], cf, log_base, af[0], aL[0], an);
+          } else {
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+              fm_softplus_accum(v[u], cf, exp_base, log_base, af[u], aL[u]);
+              am[u] += fabs(v[u]);
+            }
           }
         }
 #pragma unroll
         for (int u = 1; u < UNROLL; ++u) { am[0] += am[u]; af[0] += af[u]; aL[0] += aL[u]; }
         double part = fma(-0.5, am[0], -af[0]) - (double)aL[0] * 2.220446049250313e-16;
+        if (UNROLL == 4) part -= (double)(an - 1023 * iters) * 0.6931471805599453;   // sum of the groups' exponents
         if (tid == 0) part += 0.5 * fma(delta, colsum[j], S_eta);
         double xi = block_sum_1sync<THREADS / 32>(part, slots, t & 1);
         double alpha = blr_log_alpha(rho, xi);

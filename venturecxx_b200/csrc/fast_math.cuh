@@ -293,17 +293,19 @@ __device__ __forceinline__ void fm_softplus_accum(double v, const FmCoef &cf, ui
   af = fma(r2, Q, af);
   aL += (long long)(((unsigned long long)L_hi << 32) | L_lo);
 }
-// ---- grouped variant: ONE log for four observations ---------------------------------------
-//   sum_k log1p(e_k) = log prod_k (1 + e_k),   prod in [1,16]
-// The exponential half is fm_softplus_accum's; the logarithm half runs once per group:
+// ---- product variant: ONE logarithm for many observations --------------------------------
+//   sum_k log1p(e_k) = log prod_k (1 + e_k)
+// The exponential half is fm_softplus_accum's.  Every factor is in [1,2], so a thread multiplies the
+// factors of its observations into running products (one DADD + one DMUL per observation) and takes ONE
+// logarithm per transition (per <= 256 observations, long before 2^1023):
 //   q = 2^n m, m in [1,2): n and the table index k = round(128 (m - 1)) come from the high word with
 //   integer instructions; r2 = m inv[k] - 1 (one FMA, inv[k] is an exact 20-bit value);
 //   log q = n ln2 + L[k] + r2 Q(r2).
-// fp64 instructions per observation: 9 (exp) + 14/4 (log) = 12.5 instead of 17, log-table reads 1/4.
+// fp64 instructions per observation: 9 (exp) + 2 instead of 17, and no log-table read per observation.
 // What is given up is RELATIVE accuracy of a single tiny term (1 + 1e-20 rounds to 1); the ABSOLUTE error
-// per group stays ~4 ulp of a number in [0, 2.8] (four additions, three products, one FMA), which is what
-// a sum of N ~ 1e4 terms of magnitude ~1 sees: measured against the term-by-term version in
-// tests/test_gpu_blr.py (chains and log likelihoods equal to the oracle's at 1e-12).
+// is one rounding (1.1e-16 relative to q, i.e. 1.1e-16 absolute in log q) per factor, which is what a sum
+// of N ~ 1e4 terms of magnitude ~1 sees anyway: chains and log likelihoods stay equal to the oracle's and
+// to Lite's at 1e-12 (tests/test_gpu_blr.py, tests/test_gpu_lite_chains.py).
 __device__ __forceinline__ double fm_exp_neg_abs(double v, const FmCoef &cf, uint32_t exp_base) {
   const double MAGIC = 6755399441055744.0;       // 1.5 * 2^52: ulp 1
   int hi = __double2hiint(v) & 0x7fffffff;
@@ -326,11 +328,10 @@ __device__ __forceinline__ double fm_exp_neg_abs(double v, const FmCoef &cf, uin
   E = fma(E, r, cf.E[0]);
   return fma(Ts * r, E, Ts);
 }
-// af += r2 Q(r2), aL += L[k] (2^-52 fixed point), an += biased exponent of the product (1023 per group
-// is subtracted by the caller)
-__device__ __forceinline__ void fm_log_group4(double e0, double e1, double e2, double e3, const FmCoef &cf,
-                                              uint32_t log_base, double &af, long long &aL, int &an) {
-  const double q = ((1.0 + e0) * (1.0 + e1)) * ((1.0 + e2) * (1.0 + e3));
+// log of a product q >= 1 of (1 + e) terms: af += r2 Q(r2), aL += L[k] (2^-52 fixed point), an += biased
+// exponent of q (the caller subtracts 1023 per call and multiplies by ln2 at the end)
+__device__ __forceinline__ void fm_log_product(double q, const FmCoef &cf, uint32_t log_base, double &af,
+                                               long long &aL, int &an) {
   const uint32_t hi = (uint32_t)__double2hiint(q);
   an += (int)(hi >> 20);
   const uint32_t mant = hi & 0xFFFFFu;

@@ -387,7 +387,7 @@ def main():
                                  "the kernel keeps the logit row in shared memory for all transitions of a launch, so "
                                  "real DRAM traffic (`traffic`, from the committed ncu capture) is 2*8N B per particle per LAUNCH, "
                                  "~1/200 of the algorithmic figure; the binding resources are the fp64 pipe, the LSU "
-                                 "return path and issue slots (profiles/r1_blr_mh_v2_ncu.md)"},
+                                 "return path and issue slots (profiles/r1_blr_mh_v3_ncu.md)"},
         }
         if not args.no_cpu_baseline and world == 1:
             cb, _ = cpu_baseline(X, y, D, N, T)

@@ -2,7 +2,7 @@
 """Secondary measurements: the five BASELINE.json configs on ONE GPU at the
 sizes of SURVEY 8(d) D2, one JSON line each (bench.py stays the headline, C2).
 
-  python tools/bench_configs.py [c1 c1big c2 c2f32 c3 c4 c4gibbs c3gibbs c5] [--quick]
+  python tools/bench_configs.py [c1 c1big c2 c2f32 c2lw c3 c4 c4gibbs c3gibbs c5] [--quick]
 
 Timed through the public host API (B200TraceSet), wall clock around a
 synchronised region; algorithmic bytes per SURVEY 8(d) D4.
@@ -169,6 +169,27 @@ def c2(precision="fp64", P=65536, N=10000, D=16, K=160, reps=3, quick=False):
          obs_evals_per_sec=tr * N / dt, accept_rate=acc / tr)
 
 
+def c2lw(P=65536, N=10000, D=16, reps=5, quick=False):
+    """C2 likelihood_weight / incorporate: observation log-likelihood evaluations per second."""
+    if quick:
+        P = 8192
+    X = np.random.default_rng(0).normal(size=(N, D))
+    y = (np.random.default_rng(2).random(N) < 0.5).astype(np.uint8)
+    ts = vb.B200TraceSet(vb.LogisticRegressionModel(D, N), P, seed=11)
+    ts.observe(X, y)
+    ts.incorporate(return_increments=False)
+    ts.likelihood_weight()
+    ts.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        ts.likelihood_weight()
+    ts.synchronize()
+    dt = time.perf_counter() - t0
+    ev = float(P) * N * reps
+    emit("c2lw", "observation log-lik evals/sec (likelihood_weight)", ev / dt, "evals/s", dt, ev * 8.0 + reps * P * (D + 2) * 8.0,
+         particles=P, observations=N, D=D, ms_per_call=1e3 * dt / reps)
+
+
 def c5(N=10 ** 7, P=64, K=20, quick=False):
     D = 16
     if quick:
@@ -213,6 +234,8 @@ def main():
             c3gibbs(1 << 20, 1 if quick else 4, quick)
         elif w == "c5":
             c5(quick=quick)
+        elif w == "c2lw":
+            c2lw(quick=quick)
         elif w == "c2":
             c2("fp64", quick=quick)
         elif w == "c2f32":

@@ -166,6 +166,29 @@ def main():
     out["c3_sharded_peer_memory"] = {"particles": P_local * world, "steps": T, "ms_per_step": 1e3 * dt / T,
                                      "particle_steps_per_sec": P_local * world * T / dt, "tvd_last": float(tvd)}
     assert tvd < 0.01, tvd
+    # ---- 3c. weak scaling of the same filter: 2^20 particles PER GPU, peer-memory resample ----
+    P_big = 1 << 20
+    for rep in range(2):
+        sh = ShardedTraceSet(model, P_big, seed=7 + rep, device=local)
+        sh.enable_peer_memory()
+        torch.cuda.synchronize(); dist.barrier()
+        t0 = time.perf_counter()
+        for d in H["data"]:
+            sh.observe(d); sh.incorporate(return_increments=False); sh.resample(mode="systematic")
+        sh.local.synchronize(); torch.cuda.synchronize(); dist.barrier()
+        dt = time.perf_counter() - t0
+        timed_out, _ = sh.peer_status()
+        assert not timed_out
+        m = np.bincount(sh.read_site(T - 1).astype(int), minlength=6)[1:6].astype(np.float64)
+        mt = torch.tensor(m, device="cuda")
+        dist.all_reduce(mt)
+        tvd = 0.5 * np.abs(mt.cpu().numpy() / (P_big * world) - np.array(H["filtered_marginals"][T - 1])).sum()
+        dist.barrier()
+        sh.local.close()
+    out["c3_weak_peer_memory"] = {"particles": P_big * world, "particles_per_gpu": P_big, "steps": T,
+                                  "ms_per_step": 1e3 * dt / T, "particle_steps_per_sec": P_big * world * T / dt,
+                                  "tvd_last": float(tvd)}
+    assert tvd < 0.01, tvd
     dist.barrier()
     if rank == 0:
         out["status"] = "ok"

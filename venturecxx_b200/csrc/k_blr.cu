@@ -39,63 +39,79 @@ __device__ __forceinline__ double blr_log_alpha(double rho, double xi) {
   return xi - rho;
 }
 
-// eta_i = sum_j w_j Xs[j][i] for i in [i0,i1); returns this thread's partial
-// sum of log_logistic(eta_i).  w in shared memory.
-__device__ __forceinline__ double blr_fill_eta(double *__restrict__ eta_row,
-                                               const double *__restrict__ Xs, const double *w_sh,
-                                               int D, int64_t Xld, int64_t i0, int64_t i1) {
-  double acc = 0.0;
-  for (int64_t i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
-    double e = 0.0;
-    for (int j = 0; j < D; ++j) e = fma(w_sh[j], __ldg(&Xs[(int64_t)j * Xld + i]), e);
-    eta_row[i] = e;
-    acc += fast_log_logistic(e);
-  }
-  return acc;
-}
-
 // mode 0: reset_to_prior (w ~ prior, eta/ll over propagated obs, weights untouched)
 // mode 1: likelihood_weight (as 0 and lw := ll)            lite/trace.py:522-530
 // mode 2: refresh (keep w; recompute eta and ll)
 // mode 3: make_consistent over [n_prop, N): eta for new obs, incr, lw += incr, ll += incr
+//
+// eta_i = sum_j w_j Xs[j][i] and sum_i log_logistic(eta_i), BLR_ALL_PP particles per CTA pass: the D
+// feature values of an observation are read from L2 ONCE and used for all PP particles (one particle per
+// pass made the kernel L2-bound: 8 D bytes of L2 traffic per evaluation, 84 GB per call at C2).
+static const int BLR_ALL_PP = 4;
 __global__ void __launch_bounds__(256)
 blr_all_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restrict__ ll,
                double *__restrict__ lw, double *__restrict__ incr,
                const double *__restrict__ Xs, BLRParams prm, int64_t n_prop, int64_t P,
                int64_t p_base, uint64_t seed, uint32_t step, int mode) {
   extern __shared__ double smem[];
-  double *w_sh = smem;            // D
-  double *red = smem + prm.D;     // 33
-  for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
+  const int D = prm.D;
+  double *w_sh = smem;                       // PP x D
+  double *red = smem + BLR_ALL_PP * D;       // 33
+  const int64_t i0 = (mode == 3) ? n_prop : 0;
+  const int64_t i1 = (mode == 3) ? prm.N : n_prop;
+  for (int64_t p0 = (int64_t)blockIdx.x * BLR_ALL_PP; p0 < P; p0 += (int64_t)gridDim.x * BLR_ALL_PP) {
+    const int np = (int)(P - p0 < BLR_ALL_PP ? P - p0 : BLR_ALL_PP);
     __syncthreads();
-    if ((int)threadIdx.x < prm.D) {
-      int j = threadIdx.x;
-      double v;
-      if (mode <= 1) {
-        Stream r(seed, (uint64_t)(p_base + p), step);
-        r.seek(2u * (uint32_t)j);
-        v = normal_sim(r, prm.mu0, prm.s0);
-        w[(int64_t)j * P + p] = v;
-      } else {
-        v = w[(int64_t)j * P + p];
+    for (int t = threadIdx.x; t < BLR_ALL_PP * D; t += blockDim.x) {
+      const int q = t / D, j = t - q * D;
+      double v = 0.0;
+      if (q < np) {
+        const int64_t p = p0 + q;
+        if (mode <= 1) {
+          Stream r(seed, (uint64_t)(p_base + p), step);
+          r.seek(2u * (uint32_t)j);
+          v = normal_sim(r, prm.mu0, prm.s0);
+          w[(int64_t)j * P + p] = v;
+        } else {
+          v = w[(int64_t)j * P + p];
+        }
       }
-      w_sh[j] = v;
+      w_sh[t] = v;
     }
     __syncthreads();
-    int64_t i0 = (mode == 3) ? n_prop : 0;
-    int64_t i1 = (mode == 3) ? prm.N : n_prop;
-    double part = blr_fill_eta(eta + p * prm.Ncap, Xs, w_sh, prm.D, prm.Xld, i0, i1);
-    double tot = block_sum(part, red);
-    if (threadIdx.x == 0) {
-      if (mode == 3) {
-        double inc = tot;
-        if (inc != inc) inc = -INFINITY;  // lite/trace.py:438-448
-        if (incr) incr[p] = inc;
-        lw[p] += inc;
-        ll[p] += tot;
-      } else {
-        ll[p] = tot;
-        if (mode == 1) lw[p] = tot;
+    double acc[BLR_ALL_PP];
+#pragma unroll
+    for (int q = 0; q < BLR_ALL_PP; ++q) acc[q] = 0.0;
+    for (int64_t i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+      double e[BLR_ALL_PP];
+#pragma unroll
+      for (int q = 0; q < BLR_ALL_PP; ++q) e[q] = 0.0;
+      for (int j = 0; j < D; ++j) {
+        const double x = __ldg(&Xs[(int64_t)j * prm.Xld + i]);
+#pragma unroll
+        for (int q = 0; q < BLR_ALL_PP; ++q) e[q] = fma(w_sh[q * D + j], x, e[q]);   // same order as one particle per pass
+      }
+#pragma unroll
+      for (int q = 0; q < BLR_ALL_PP; ++q) {
+        if (q < np) { eta[(p0 + q) * prm.Ncap + i] = e[q]; acc[q] += fast_log_logistic(e[q]); }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < BLR_ALL_PP; ++q) {
+      if (q >= np) break;                    // uniform across the CTA
+      const double tot = block_sum(acc[q], red);
+      if (threadIdx.x == 0) {
+        const int64_t p = p0 + q;
+        if (mode == 3) {
+          double inc = tot;
+          if (inc != inc) inc = -INFINITY;  // lite/trace.py:438-448
+          if (incr) incr[p] = inc;
+          lw[p] += inc;
+          ll[p] += tot;
+        } else {
+          ll[p] = tot;
+          if (mode == 1) lw[p] = tot;
+        }
       }
     }
   }
@@ -472,8 +488,9 @@ struct BLRModel : Model {
     return (int)(h->P < cap ? h->P : cap);
   }
   void launch_all(int mode, double *incr_dev, uint32_t step) {
-    size_t sm = (size_t)(prm.D + 34) * sizeof(double);
-    blr_all_kernel<<<grid_particles(8), 256, sm, h->stream>>>(w, eta, ll, h->lw.p, incr_dev, Xs.p, prm,
+    size_t sm = (size_t)(BLR_ALL_PP * prm.D + 34) * sizeof(double);
+    int64_t groups = (h->P + BLR_ALL_PP - 1) / BLR_ALL_PP, cap = (int64_t)h->sm_count * 8;
+    blr_all_kernel<<<(int)(groups < cap ? groups : cap), 256, sm, h->stream>>>(w, eta, ll, h->lw.p, incr_dev, Xs.p, prm,
                                                               n_prop, h->P, h->p_base, h->seed, step, mode);
     VK_CUDA(cudaGetLastError());
   }

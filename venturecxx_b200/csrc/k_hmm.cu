@@ -502,6 +502,13 @@ struct HMMModel : Model {
     StateArray b{(void **)&hist, (void **)&hist_alt, (size_t)Tpad, 0, 0};
     return {a, b};
   }
+  std::vector<StateArray> state_arrays_patched(int patch[3]) override {
+    patch[0] = -1;
+    if (hist_pending) { patch[0] = 1; patch[1] = 0; patch[2] = T - 1; hist_pending = false; }   // the caller's gather inserts it
+    StateArray a{(void **)&cur, (void **)&cur_alt, 0, 1, 4};
+    StateArray b{(void **)&hist, (void **)&hist_alt, (size_t)Tpad, 0, 0};
+    return {a, b};
+  }
   int device_buffer(int which, void **p, int64_t *bytes) override {
     if (which == 1) { *p = cur; *bytes = (int64_t)cura.bytes(); return VK_OK; }
     if (which == 2) { flush_hist(); *p = hist; *bytes = (int64_t)hista.bytes(); return VK_OK; }

@@ -53,6 +53,10 @@ struct P2PArrays {                     // by-value kernel argument of the gather
   long long row_bytes[P2P_MAX_ARRAYS];
   long long n_rows[P2P_MAX_ARRAYS];
   int elem_bytes[P2P_MAX_ARRAYS];
+  int patch_array, patch_src, patch_byte;   // Model::state_arrays_patched: byte patch_byte of every row of
+                                            // array patch_array := low byte of the ancestor's element of
+                                            // the 4-byte particle-minor array patch_src (patch_array < 0: none)
+  double *lw; const double *red; double log_p_total;   // evened-out weights written by the same kernel
 };
 struct P2P {
   int world = 0, rank = 0, n_arrays = 0;
@@ -222,7 +226,17 @@ p2p_gather_kernel(const int32_t *__restrict__ anc_g, int64_t n, const P2PTables 
           int64_t s = t / units, u = t - s * units;
           int64_t g = anc_g[s], d = g / n, i = g - d * n;
           const uint4 *src = (const uint4 *)(tab->buf[a][d][par->cur_idx[d]] + i * rb);
-          ((uint4 *)(arrs.alt[a] + s * rb))[u] = src[u];
+          uint4 v = src[u];
+          if (a == arrs.patch_array && u == (arrs.patch_byte >> 4)) {
+            const uint32_t sv = ((const uint32_t *)tab->buf[arrs.patch_src][d][par->cur_idx[d]])[i] & 0xFFu;
+            const int pw = (arrs.patch_byte >> 2) & 3, psh = (arrs.patch_byte & 3) * 8;
+            const uint32_t keep = ~(0xFFu << psh), ins = sv << psh;
+            if (pw == 0) v.x = (v.x & keep) | ins;
+            else if (pw == 1) v.y = (v.y & keep) | ins;
+            else if (pw == 2) v.z = (v.z & keep) | ins;
+            else v.w = (v.w & keep) | ins;
+          }
+          ((uint4 *)(arrs.alt[a] + s * rb))[u] = v;
         }
       } else {
         for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n * rb;
@@ -247,6 +261,9 @@ p2p_gather_kernel(const int32_t *__restrict__ anc_g, int64_t n, const P2PTables 
       }
     }
   }
+  const double even = arrs.red[4] - arrs.log_p_total;   // lw := LSE - log P_total (utils.py:152-157)
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x)
+    arrs.lw[t] = even;
 }
 
 // ---- host side -------------------------------------------------------------------------------------
@@ -325,8 +342,12 @@ void p2p_resample(vk_particles *h, int mode) {
   const uint32_t step = h->next_step();
   const unsigned long long seq = ++s->seq;
   const long long spin = 4000000000ll;   // ~2 s of SM clocks: a peer that never arrives sets par->err
-  std::vector<StateArray> arrs = h->model->state_arrays();
+  int patch[3];
+  std::vector<StateArray> arrs = h->model->state_arrays_patched(patch);
   VK_REQUIRE((int)arrs.size() == s->n_arrays, VK_ESTATE, "p2p: state arrays changed since export");
+  if (patch[0] >= 0)
+    VK_REQUIRE(arrs[patch[0]].elem_bytes == 0 && (arrs[patch[0]].row_bytes & 15) == 0 && arrs[patch[1]].elem_bytes == 4 &&
+                   arrs[patch[1]].n_rows == 1, VK_EUNSUPPORTED, "p2p: pending-column patch needs 16-byte rows and a 4-byte source");
   int cur_idx = *arrs[0].cur == s->own_buf[0][0] ? 0 : 1;
   for (int a = 0; a < s->n_arrays; ++a)
     VK_REQUIRE(*arrs[a].cur == s->own_buf[a][cur_idx] && *arrs[a].alt == s->own_buf[a][1 - cur_idx], VK_ESTATE,
@@ -358,7 +379,9 @@ void p2p_resample(vk_particles *h, int mode) {
   P2PArrays pa;
   memset(&pa, 0, sizeof pa);
   pa.n = s->n_arrays;
-  int64_t work = 0;
+  pa.patch_array = patch[0]; pa.patch_src = patch[1]; pa.patch_byte = patch[2];
+  pa.lw = h->lw.p; pa.red = h->red.p; pa.log_p_total = log((double)P_total);
+  int64_t work = P;
   for (int a = 0; a < s->n_arrays; ++a) {
     pa.alt[a] = (unsigned char *)*arrs[a].alt;
     pa.row_bytes[a] = (long long)arrs[a].row_bytes; pa.n_rows[a] = (long long)arrs[a].n_rows;
@@ -368,7 +391,6 @@ void p2p_resample(vk_particles *h, int mode) {
     work = wa > work ? wa : work;
   }
   p2p_gather_kernel<<<grid_for(work, 256, h->sm_count, 8), 256, 0, st>>>(s->anc_g.p, P, s->tab.p, s->par.p, pa);
-  fill_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, log((double)P_total));
   VK_CUDA(cudaGetLastError());
   for (auto &a : arrs) { void *t = *a.cur; *a.cur = *a.alt; *a.alt = t; }
   h->model->after_resample();

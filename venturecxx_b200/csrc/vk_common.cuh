@@ -138,6 +138,11 @@ struct Model {
   // arrays gathered by ancestor index on resample; after the gather the model
   // swaps cur/alt itself via StateArray.
   virtual std::vector<StateArray> state_arrays() = 0;
+  // state_arrays() for a gather that can patch one byte into every row it copies: a model whose newest
+  // column is still pending in a particle-minor array (HMM: hist[.][T-1] lives in cur[]) reports
+  // (row array index, source SoA array index, byte offset in the row) instead of materialising the column
+  // first; patch[0] < 0 = nothing to patch.  Only for callers that copy EVERY row (the peer-memory gather).
+  virtual std::vector<StateArray> state_arrays_patched(int patch[3]) { patch[0] = -1; return state_arrays(); }
   // a model may gather its whole state by ancestor in one fused pass of its own; returns 0 (not done: the
   // generic per-array gather over state_arrays() runs), 1 (state gathered) or 3 (state gathered AND the
   // evened-out weights lw[k] = red[4] - log_n_new written, so the caller skips its fill pass).

@@ -453,8 +453,8 @@ fixed_tile_sums_exp_kernel(const double *__restrict__ lw, int64_t n, const doubl
 
 // pass B': scan of tile totals (as scan_tile_sums_kernel) + LSE from the tile exp sums
 // (fixed order) with the edge cases of utils.py:77-91 -> red[3], red[4]
-__global__ void __launch_bounds__(1024)
-scan_tile_sums_lse_kernel(uint64_t *tile_sums, const double *tile_exp, int n_tiles, int64_t n, double *red) {
+__device__ __forceinline__ void scan_tile_sums_lse_body(uint64_t *tile_sums, const double *tile_exp, int n_tiles,
+                                                        int64_t n, double *red) {
   __shared__ uint64_t sh[32];
   __shared__ double shd[33];
   __shared__ uint64_t carry_sh;
@@ -489,6 +489,10 @@ scan_tile_sums_lse_kernel(uint64_t *tile_sums, const double *tile_exp, int n_til
     else lse = m + log(se);
     red[3] = se; red[4] = lse;
   }
+}
+__global__ void __launch_bounds__(1024)
+scan_tile_sums_lse_kernel(uint64_t *tile_sums, const double *tile_exp, int n_tiles, int64_t n, double *red) {
+  scan_tile_sums_lse_body(tile_sums, tile_exp, n_tiles, n, red);
 }
 
 // pass C': running CDF in registers -> children ranges -> anc[k] = i  (no CDF array, no search)

@@ -77,10 +77,10 @@ __device__ __forceinline__ int p2p_mail_index(int parity, int phase, int sender)
 // One warp; lane r talks to rank r.  Phase 0 sends (max, min, nan) from red[0..2]; phase 1 sends
 // (sum exp, live-buffer index, mass); phase 2 is a pure barrier.  Results: phase 0 -> red[0..2]; phase 1 ->
 // par (offset, total, cur_idx) and red[3] (global sum exp), red[4] (LSE, utils.py:77-91 edge cases).
-__global__ void __launch_bounds__(32)
-p2p_exchange_kernel(P2PTables *tab, P2PParams *par, double *red, const uint64_t *tile_sums, int n_tiles,
-                    int world, int rank, int phase, unsigned long long seq, int my_cur_idx, long long n_total,
-                    long long spin_limit) {
+__device__ __forceinline__ void
+p2p_exchange_warp(P2PTables *tab, P2PParams *par, double *red, const uint64_t *tile_sums, int n_tiles,
+                  int world, int rank, int phase, unsigned long long seq, int my_cur_idx, long long n_total,
+                  long long spin_limit) {
   const int lane = threadIdx.x;
   const int parity = (int)(seq & 1ull);
   double a = 0.0, b = 0.0;
@@ -140,6 +140,24 @@ p2p_exchange_kernel(P2PTables *tab, P2PParams *par, double *red, const uint64_t 
       red[3] = se; red[4] = lse;
     }
   }
+}
+
+__global__ void __launch_bounds__(32)
+p2p_exchange_kernel(P2PTables *tab, P2PParams *par, double *red, const uint64_t *tile_sums, int n_tiles,
+                    int world, int rank, int phase, unsigned long long seq, int my_cur_idx, long long n_total,
+                    long long spin_limit) {
+  p2p_exchange_warp(tab, par, red, tile_sums, n_tiles, world, rank, phase, seq, my_cur_idx, n_total, spin_limit);
+}
+// scan of this rank's tile totals + local sum exp (scan_tile_sums_lse_kernel's work), then exchange 1 by
+// warp 0 of the same single CTA: one launch instead of two on the latency-bound path
+__global__ void __launch_bounds__(1024)
+p2p_scan_exchange1_kernel(P2PTables *tab, P2PParams *par, double *red, uint64_t *tile_sums, const double *tile_exp,
+                          int n_tiles, int64_t n_local, int world, int rank, unsigned long long seq, int my_cur_idx,
+                          long long n_total, long long spin_limit) {
+  scan_tile_sums_lse_body(tile_sums, tile_exp, n_tiles, n_local, red);
+  __syncthreads();
+  if (threadIdx.x < 32)
+    p2p_exchange_warp(tab, par, red, tile_sums, n_tiles, world, rank, 1, seq, my_cur_idx, n_total, spin_limit);
 }
 
 // Step C, systematic: as systematic_offspring_kernel, against the GLOBAL mass: this rank's running sum starts at
@@ -363,9 +381,8 @@ void p2p_resample(vk_particles *h, int mode) {
   p2p_exchange_kernel<<<1, 32, 0, st>>>(s->tab.p, s->par.p, h->red.p, h->red_u.p, n_tiles, s->world, s->rank, 0, seq,
                                         cur_idx, P_total, spin);
   fixed_tile_sums_exp_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p);
-  scan_tile_sums_lse_kernel<<<1, 1024, 0, st>>>(h->red_u.p, h->tile_exp.p, n_tiles, P, h->red.p);
-  p2p_exchange_kernel<<<1, 32, 0, st>>>(s->tab.p, s->par.p, h->red.p, h->red_u.p, n_tiles, s->world, s->rank, 1, seq,
-                                        cur_idx, P_total, spin);
+  p2p_scan_exchange1_kernel<<<1, 1024, 0, st>>>(s->tab.p, s->par.p, h->red.p, h->red_u.p, h->tile_exp.p, n_tiles, P,
+                                                s->world, s->rank, seq, cur_idx, P_total, spin);
   if (mode == VK_RESAMPLE_SYSTEMATIC) {
     p2p_offspring_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, s->par.p, s->tab.p,
                                                            P_total, h->p_base, h->seed, step);

@@ -252,8 +252,10 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
         long long aL[UNROLL];            // sum L[k], 2^-52 fixed point
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) { am[u] = 0.0; af[u] = 0.0; aL[u] = 0; }
-        int an = 0, n_logs = 0;          // product logarithm: sum of biased exponents, number of logs (UNROLL == 4)
-        double qp[4] = {1.0, 1.0, 1.0, 1.0};
+        int an = 0, n_logs = 0;          // product logarithm: sum of biased exponents, number of logs
+        double qp[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) qp[u] = 1.0;
         const double *xp = xcol + tid + BLR_MH_TILE;
         int i0 = tid;
         for (int it = 0; it < iters; ++it, xp += BLR_MH_TILE, i0 += BLR_MH_TILE) {
@@ -271,36 +273,34 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u) xn[u] = __ldg(src + u * THREADS);
           }
-          if (UNROLL == 4) {
-            // the factors 1 + exp(-|v|) go into four running products; ONE logarithm per transition
-            // (fast_math.cuh: fm_log_product), flushed every 64 iterations so a product stays < 2^64
+          // the factors 1 + exp(-|v|) go into UNROLL running products; ONE logarithm per transition
+          // (fast_math.cuh: fm_log_product), flushed every 64 iterations so a product stays < 2^64
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              qp[u] *= 1.0 + fm_exp_neg_abs(v[u], cf, exp_base);
-              am[u] += fabs(v[u]);
-            }
-            if ((it & 63) == 63) {
-              fm_log_product((qp[0] * qp[1]) * (qp[2] * qp[3]), cf, log_base, af[0], aL[0], an);
-              ++n_logs;
+          for (int u = 0; u < UNROLL; ++u) {
+            qp[u] *= 1.0 + fm_exp_neg_abs(v[u], cf, exp_base);
+            am[u] += fabs(v[u]);
+          }
+          if ((it & 63) == 63) {
+            double q = qp[0];
 #pragma unroll
-              for (int u = 0; u < 4; ++u) qp[u] = 1.0;
-            }
-          } else {
+            for (int u = 1; u < UNROLL; ++u) q *= qp[u];
+            fm_log_product(q, cf, log_base, af[0], aL[0], an);
+            ++n_logs;
 #pragma unroll
-            for (int u = 0; u < UNROLL; ++u) {
-              fm_softplus_accum(v[u], cf, exp_base, log_base, af[u], aL[u]);
-              am[u] += fabs(v[u]);
-            }
+            for (int u = 0; u < UNROLL; ++u) qp[u] = 1.0;
           }
         }
-        if (UNROLL == 4 && (iters & 63) != 0) {
-          fm_log_product((qp[0] * qp[1]) * (qp[2] * qp[3]), cf, log_base, af[0], aL[0], an);
+        if ((iters & 63) != 0) {
+          double q = qp[0];
+#pragma unroll
+          for (int u = 1; u < UNROLL; ++u) q *= qp[u];
+          fm_log_product(q, cf, log_base, af[0], aL[0], an);
           ++n_logs;
         }
 #pragma unroll
-        for (int u = 1; u < UNROLL; ++u) { am[0] += am[u]; af[0] += af[u]; aL[0] += aL[u]; }
+        for (int u = 1; u < UNROLL; ++u) am[0] += am[u];
         double part = fma(-0.5, am[0], -af[0]) - (double)aL[0] * 2.220446049250313e-16;
-        if (UNROLL == 4) part -= (double)(an - 1023 * n_logs) * 0.6931471805599453;   // the products' exponents
+        part -= (double)(an - 1023 * n_logs) * 0.6931471805599453;   // the products' exponents
         if (tid == 0) part += 0.5 * fma(delta, colsum[j], S_eta);
         double xi = block_sum_1sync<THREADS / 32>(part, slots, t & 1);
         double alpha = blr_log_alpha(rho, xi);

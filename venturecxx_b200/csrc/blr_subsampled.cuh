@@ -227,6 +227,86 @@ ss_round_kernel(const double *__restrict__ Xr /*[N_local][D] signed rows*/, cons
   }
 }
 
+// Straggler rounds.  The loop over minibatches runs until the slowest sequential test has decided, and
+// in ss_round_kernel a round with two undecided particles costs what a round with 64 costs (lanes are
+// particles).  Once at most SS_COMPACT_MAX particles are undecided the lanes become OBSERVATIONS: every
+// lane loads the feature row of its own minibatch position and evaluates the (few) undecided particles one
+// after the other, their weights staged in shared memory.  Same per-minibatch sums (to rounding: the
+// summation order differs), same sequence of decisions.
+static const int SS_COMPACT_MAX = 8;
+template <int DT>
+__global__ void __launch_bounds__(256)
+ss_round_compact_kernel(const double *__restrict__ Xr, const double *__restrict__ w, SSState S, int D, int64_t P,
+                        int64_t q0, int64_t q1, int64_t obs_lo, int64_t N_local, FeistelKey key,
+                        double *__restrict__ partial) {
+  __shared__ double w_sh[SS_COMPACT_MAX][DT];
+  __shared__ double delta_sh[SS_COMPACT_MAX];
+  __shared__ int site_sh[SS_COMPACT_MAX], pid_sh[SS_COMPACT_MAX], n_act_sh;
+  __shared__ double red_sh[8][SS_COMPACT_MAX][2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+  {                                             // undecided particles in index order (P <= 256 = blockDim.x)
+    __shared__ int cnt_sh[8];
+    const bool und = threadIdx.x < P && S.status[threadIdx.x] == 0;
+    const unsigned b = __ballot_sync(0xffffffffu, und);
+    if (lane == 0) cnt_sh[warp] = __popc(b);
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int wv = 0; wv < n_warps; ++wv) { if (wv < warp) before += cnt_sh[wv]; total += cnt_sh[wv]; }
+    const int slot = before + __popc(b & ((1u << lane) - 1u));
+    if (und && slot < SS_COMPACT_MAX) {
+      pid_sh[slot] = (int)threadIdx.x; delta_sh[slot] = S.delta[threadIdx.x]; site_sh[slot] = S.site[threadIdx.x];
+    }
+    if (threadIdx.x == 0) n_act_sh = total < SS_COMPACT_MAX ? total : SS_COMPACT_MAX;
+  }
+  __syncthreads();
+  const int n_act = n_act_sh;
+  for (int t = threadIdx.x; t < n_act * DT; t += blockDim.x) {
+    const int a = t / DT, j = t - a * DT;
+    w_sh[a][j] = j < D ? w[(int64_t)j * P + pid_sh[a]] : 0.0;
+  }
+  __syncthreads();
+  double s1[SS_COMPACT_MAX], s2[SS_COMPACT_MAX];
+#pragma unroll
+  for (int a = 0; a < SS_COMPACT_MAX; ++a) { s1[a] = 0.0; s2[a] = 0.0; }
+  const int64_t n_thr = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t q = q0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += n_thr) {
+    const int64_t i = (int64_t)feistel_perm((uint64_t)q, key) - obs_lo;
+    if (i < 0 || i >= N_local) continue;        // another shard's observation
+    double x[DT];
+    const double *row = Xr + i * D;
+#pragma unroll
+    for (int j = 0; j < DT; ++j) x[j] = j < D ? __ldg(&row[j]) : 0.0;
+#pragma unroll
+    for (int a = 0; a < SS_COMPACT_MAX; ++a) {
+      if (a >= n_act) break;
+      double eta = 0.0;
+#pragma unroll
+      for (int j = 0; j < DT; ++j) eta = fma(w_sh[a][j], x[j], eta);
+      const double xs = __ldg(&row[site_sh[a]]);
+      const double d = fast_log_logistic(fma(delta_sh[a], xs, eta)) - fast_log_logistic(eta);
+      s1[a] += d; s2[a] += d * d;
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < SS_COMPACT_MAX; ++a) {
+    double u = warp_sum(s1[a]), v = warp_sum(s2[a]);
+    if (lane == 0) { red_sh[warp][a][0] = u; red_sh[warp][a][1] = v; }
+  }
+  __syncthreads();
+  // partial[block][p][2]: zero for decided particles, warp-ordered sums for the undecided ones
+  for (int64_t pp = threadIdx.x; pp < P; pp += blockDim.x) {
+    partial[((size_t)blockIdx.x * P + pp) * 2] = 0.0;
+    partial[((size_t)blockIdx.x * P + pp) * 2 + 1] = 0.0;
+  }
+  __syncthreads();
+  if (threadIdx.x < n_act) {
+    double a_ = 0.0, b_ = 0.0;
+    for (int wv = 0; wv < n_warps; ++wv) { a_ += red_sh[wv][threadIdx.x][0]; b_ += red_sh[wv][threadIdx.x][1]; }
+    partial[((size_t)blockIdx.x * P + pid_sh[threadIdx.x]) * 2] = a_;
+    partial[((size_t)blockIdx.x * P + pid_sh[threadIdx.x]) * 2 + 1] = b_;
+  }
+}
+
 // sums[P][2] = sum over blocks of partial; one warp per output, lanes stride the blocks and
 // combine with a fixed shuffle tree (deterministic)
 __global__ void ss_reduce_kernel(const double *__restrict__ partial, int n_blocks, int64_t P,

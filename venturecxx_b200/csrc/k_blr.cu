@@ -538,11 +538,13 @@ struct BLRModel : Model {
     VK_REQUIRE(Nt > 1, VK_ESTATE, "subsampled_mh needs more than one local section (subsampled_mh.py:100)");
     uint32_t step = h->next_step();
     ss_key = make_feistel_key(h->seed, step, (uint64_t)Nt);
+    ss_last_active = -1;     // a new transition: every particle is undecided again
     ss_propose_kernel<<<grid_for(h->P, 128, h->sm_count, 4), 128, 0, h->stream>>>(
         w, ss_state(), prm.D, h->P, h->p_base, prm.mu0, prm.s0, (double)Nt, block, t_index, delta_mode, eps, h->seed, step);
     VK_CUDA(cudaGetLastError());
   }
   FeistelKey ss_key;
+  int ss_last_active = -1;   // undecided particles after the last decision that was read back (-1: unknown)
   // local partial sums of minibatch positions [q0,q1) -> ss_sums (device, P x 2)
   void ss_round(int64_t q0, int64_t q1) {
     int n_groups = (int)((h->P + 31) / 32);
@@ -551,7 +553,9 @@ struct BLRModel : Model {
     if (ss_partial.n < (size_t)grid * h->P * 2) ss_partial.alloc((size_t)grid * h->P * 2);
     size_t sm = (size_t)8 * 32 * (prm.D > 2 ? prm.D : 2) * sizeof(double);   // per-warp row tiles (reused for the partial sums)
     SSState S = ss_state();
-#define VK_SS_LAUNCH(DT) do { VK_CUDA(cudaFuncSetAttribute(ss_round_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); ss_round_kernel<DT><<<grid, 256, sm, h->stream>>>(Xr.p, w, S, prm.D, h->P, q0, q1, obs_lo, prm.N, ss_key, ss_partial.p); } while (0)
+    // few undecided particles left (count of the last decision read back): lanes = observations
+    const bool compact = ss_last_active >= 0 && ss_last_active <= SS_COMPACT_MAX;
+#define VK_SS_LAUNCH(DT) do { if (compact) ss_round_compact_kernel<DT><<<grid, 256, 0, h->stream>>>(Xr.p, w, S, prm.D, h->P, q0, q1, obs_lo, prm.N, ss_key, ss_partial.p); else { VK_CUDA(cudaFuncSetAttribute(ss_round_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); ss_round_kernel<DT><<<grid, 256, sm, h->stream>>>(Xr.p, w, S, prm.D, h->P, q0, q1, obs_lo, prm.N, ss_key, ss_partial.p); } } while (0)
     if (prm.D <= 4) VK_SS_LAUNCH(4);
     else if (prm.D <= 8) VK_SS_LAUNCH(8);
     else if (prm.D <= 16) VK_SS_LAUNCH(16);
@@ -577,6 +581,7 @@ struct BLRModel : Model {
     int *n_active = ss_i.p + 2 * h->P;
     VK_CUDA(cudaMemcpyAsync(ss_active_host, n_active, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     VK_CUDA(cudaStreamSynchronize(h->stream));
+    ss_last_active = *ss_active_host;
     return *ss_active_host;
   }
   int ss_decide(const double *sums_dev, int64_t n_end, int k0, double eps) {

@@ -156,7 +156,8 @@ template <int DT>
 __global__ void __launch_bounds__(256)
 ss_round_kernel(const double *__restrict__ Xr /*[N_local][D] signed rows*/, const double *__restrict__ w,
                 SSState S, int D, int64_t P, int64_t q0, int64_t q1, int64_t obs_lo, int64_t N_local,
-                FeistelKey key, double *__restrict__ partial) {
+                FeistelKey key, double *__restrict__ partial, const int *__restrict__ gate) {
+  if (*gate == 0) return;               // every sequential test of this transition has decided: a no-op round
   extern __shared__ double sm_dyn[];    // [warps][32 rows][D] tiles, then [warps][32][2] partial sums
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
   const int n_groups = (int)((P + 31) / 32);
@@ -227,6 +228,52 @@ ss_round_kernel(const double *__restrict__ Xr /*[N_local][D] signed rows*/, cons
   }
 }
 
+// sums[P][2] = sum over blocks of partial; one warp per output, lanes stride the blocks and
+// combine with a fixed shuffle tree (deterministic)
+__global__ void ss_reduce_kernel(const double *__restrict__ partial, int n_blocks, int64_t P,
+                                 double *__restrict__ sums, const int *__restrict__ gate) {
+  if (*gate == 0) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t t = warp; t < P * 2; t += n_warps) {
+    double a = 0.0;
+    for (int b = lane; b < n_blocks; b += 32) a += partial[(size_t)b * P * 2 + t];
+    a = warp_sum(a);
+    if (lane == 0) sums[t] = a;
+  }
+}
+
+// sequentialTest bookkeeping of one particle for one finished minibatch (:132-168); returns the new status
+__device__ __forceinline__ int ss_decide_particle(SSState &S, int64_t p, double sum1, double sum2, double n_end,
+                                                  double N, int k0, double epsilon) {
+  double cum = S.cum[p] + sum1, cum2 = S.cum2[p] + sum2;
+  double k = S.k[p] + 1.0, n = n_end;
+  S.cum[p] = cum; S.cum2[p] = cum2; S.k[p] = k; S.n[p] = n;
+  double mx = cum / n, mx2 = cum2 / n, mu0 = S.mu0[p];
+  int st = 0;
+  if (k < (double)k0 && n < N) { /* no test during the first k0 minibatches */ }
+  else if (n == N) st = (mx >= mu0) ? 1 : 2;
+  else {
+    double sx = sqrt((1.0 - (n - 1.0) / (N - 1.0)) * (mx2 - mx * mx) / (n - 1.0));
+    double q;
+    if (sx == 0.0) q = (mx >= mu0) ? 1.0 : 0.0;
+    else { double ts = (mx - mu0) / sx; S.tstat[p] = ts; q = dev_student_t_cdf(ts, n - 1.0); }
+    if (q < epsilon) st = 2;
+    else if (q > 1.0 - epsilon) st = 1;
+  }
+  S.status[p] = st;
+  return st;
+}
+__global__ void ss_decide_kernel(SSState S, const double *__restrict__ sums, int64_t P, double n_end,
+                                 double N, int k0, double epsilon, int *__restrict__ n_active) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    if (S.status[p] != 0) continue;
+    if (ss_decide_particle(S, p, sums[2 * p], sums[2 * p + 1], n_end, N, k0, epsilon) == 0) atomicAdd(n_active, 1);
+  }
+}
+
 // Straggler rounds.  The loop over minibatches runs until the slowest sequential test has decided, and
 // in ss_round_kernel a round with two undecided particles costs what a round with 64 costs (lanes are
 // particles).  Once at most SS_COMPACT_MAX particles are undecided the lanes become OBSERVATIONS: every
@@ -238,7 +285,9 @@ template <int DT>
 __global__ void __launch_bounds__(256)
 ss_round_compact_kernel(const double *__restrict__ Xr, const double *__restrict__ w, SSState S, int D, int64_t P,
                         int64_t q0, int64_t q1, int64_t obs_lo, int64_t N_local, FeistelKey key,
-                        double *__restrict__ partial) {
+                        double *__restrict__ partial, int *__restrict__ gate,
+                        int fused, unsigned int *__restrict__ counter, double N_total, int k0, double epsilon) {
+  if (*gate == 0) return;
   __shared__ double w_sh[SS_COMPACT_MAX][DT];
   __shared__ double delta_sh[SS_COMPACT_MAX];
   __shared__ int site_sh[SS_COMPACT_MAX], pid_sh[SS_COMPACT_MAX], n_act_sh;
@@ -305,46 +354,34 @@ ss_round_compact_kernel(const double *__restrict__ Xr, const double *__restrict_
     partial[((size_t)blockIdx.x * P + pid_sh[threadIdx.x]) * 2] = a_;
     partial[((size_t)blockIdx.x * P + pid_sh[threadIdx.x]) * 2 + 1] = b_;
   }
-}
-
-// sums[P][2] = sum over blocks of partial; one warp per output, lanes stride the blocks and
-// combine with a fixed shuffle tree (deterministic)
-__global__ void ss_reduce_kernel(const double *__restrict__ partial, int n_blocks, int64_t P,
-                                 double *__restrict__ sums) {
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  for (int64_t t = warp; t < P * 2; t += n_warps) {
-    double a = 0.0;
-    for (int b = lane; b < n_blocks; b += 32) a += partial[(size_t)b * P * 2 + t];
-    a = warp_sum(a);
-    if (lane == 0) sums[t] = a;
-  }
-}
-
-// sequentialTest bookkeeping for one finished minibatch (:132-168)
-__global__ void ss_decide_kernel(SSState S, const double *__restrict__ sums, int64_t P, double n_end,
-                                 double N, int k0, double epsilon, int *__restrict__ n_active) {
-  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P;
-       p += (int64_t)gridDim.x * blockDim.x) {
-    if (S.status[p] != 0) continue;
-    double cum = S.cum[p] + sums[2 * p], cum2 = S.cum2[p] + sums[2 * p + 1];
-    double k = S.k[p] + 1.0, n = n_end;
-    S.cum[p] = cum; S.cum2[p] = cum2; S.k[p] = k; S.n[p] = n;
-    double mx = cum / n, mx2 = cum2 / n, mu0 = S.mu0[p];
-    int st = 0;
-    if (k < (double)k0 && n < N) { /* no test during the first k0 minibatches */ }
-    else if (n == N) st = (mx >= mu0) ? 1 : 2;
-    else {
-      double sx = sqrt((1.0 - (n - 1.0) / (N - 1.0)) * (mx2 - mx * mx) / (n - 1.0));
-      double q;
-      if (sx == 0.0) q = (mx >= mu0) ? 1.0 : 0.0;
-      else { double ts = (mx - mu0) / sx; S.tstat[p] = ts; q = dev_student_t_cdf(ts, n - 1.0); }
-      if (q < epsilon) st = 2;
-      else if (q > 1.0 - epsilon) st = 1;
+  if (!fused) return;
+  // fused tail (single-GPU loop): the LAST block sums the blocks' partials in ss_reduce_kernel's order
+  // (lanes stride the blocks, shuffle tree) and runs the sequential-test bookkeeping of the <= 8
+  // undecided particles, so a straggler round is one launch instead of round + reduce + memset + decide
+  __shared__ bool last_sh;
+  __shared__ int still_sh[SS_COMPACT_MAX];
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last_sh = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!last_sh) return;
+  __threadfence();
+  if (warp < n_act) {
+    const int64_t p = pid_sh[warp];
+    double a_ = 0.0, b_ = 0.0;
+    for (int bb = lane; bb < (int)gridDim.x; bb += 32) {
+      a_ += partial[((size_t)bb * P + p) * 2];
+      b_ += partial[((size_t)bb * P + p) * 2 + 1];
     }
-    S.status[p] = st;
-    if (st == 0) atomicAdd(n_active, 1);
+    a_ = warp_sum(a_); b_ = warp_sum(b_);
+    if (lane == 0) still_sh[warp] = ss_decide_particle(S, p, a_, b_, (double)q1, N_total, k0, epsilon) == 0 ? 1 : 0;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int c = 0;
+    for (int a = 0; a < n_act; ++a) c += still_sh[a];
+    *gate = c;            // = the n_active the host reads back
+    *counter = 0u;
   }
 }
 

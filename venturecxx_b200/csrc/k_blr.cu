@@ -515,7 +515,8 @@ struct BLRModel : Model {
       Xr_rows = prm.N;
     }
     if (!ss_d.p) {
-      ss_d.alloc((size_t)h->P * 11); ss_i.alloc((size_t)h->P * 2 + 1);
+      ss_d.alloc((size_t)h->P * 11); ss_i.alloc((size_t)h->P * 2 + 2);   // site, status, n_active (= gate), block counter
+      VK_CUDA(cudaMemsetAsync(ss_i.p, 0, ss_i.bytes(), h->stream));
       ss_sums.alloc((size_t)h->P * 2);
       VK_CUDA(cudaMallocHost((void **)&ss_active_host, sizeof(int)));
     }
@@ -528,6 +529,9 @@ struct BLRModel : Model {
     return S;
   }
   int ss_grid() const { return h->sm_count * 2; }
+  // device count of undecided particles after the last decision (set nonzero by ss_propose): the round
+  // kernels return at once when it is zero, so rounds enqueued past the last decision cost a launch only
+  int *ss_gate() { return ss_i.p + 2 * h->P; }
   // --- round-level primitives (also driven from the host layer when observations are sharded)
   void ss_begin_call() {
     ss_prepare();
@@ -539,6 +543,7 @@ struct BLRModel : Model {
     uint32_t step = h->next_step();
     ss_key = make_feistel_key(h->seed, step, (uint64_t)Nt);
     ss_last_active = -1;     // a new transition: every particle is undecided again
+    VK_CUDA(cudaMemsetAsync(ss_gate(), 0x01, sizeof(int), h->stream));
     ss_propose_kernel<<<grid_for(h->P, 128, h->sm_count, 4), 128, 0, h->stream>>>(
         w, ss_state(), prm.D, h->P, h->p_base, prm.mu0, prm.s0, (double)Nt, block, t_index, delta_mode, eps, h->seed, step);
     VK_CUDA(cudaGetLastError());
@@ -546,7 +551,9 @@ struct BLRModel : Model {
   FeistelKey ss_key;
   int ss_last_active = -1;   // undecided particles after the last decision that was read back (-1: unknown)
   // local partial sums of minibatch positions [q0,q1) -> ss_sums (device, P x 2)
-  void ss_round(int64_t q0, int64_t q1) {
+  // fuse_decide: the caller is the single-GPU loop and wants the decision of this minibatch made too;
+  // returns true when the round kernel did it (compact rounds), false when ss_decide_launch is still due
+  bool ss_round(int64_t q0, int64_t q1, bool fuse_decide = false, int k0 = 0, double eps = 0.0) {
     int n_groups = (int)((h->P + 31) / 32);
     VK_REQUIRE(n_groups <= 8, VK_EUNSUPPORTED, "subsampled_mh: at most 256 particles per GPU in this version");
     int grid = ss_grid();
@@ -555,7 +562,10 @@ struct BLRModel : Model {
     SSState S = ss_state();
     // few undecided particles left (count of the last decision read back): lanes = observations
     const bool compact = ss_last_active >= 0 && ss_last_active <= SS_COMPACT_MAX;
-#define VK_SS_LAUNCH(DT) do { if (compact) ss_round_compact_kernel<DT><<<grid, 256, 0, h->stream>>>(Xr.p, w, S, prm.D, h->P, q0, q1, obs_lo, prm.N, ss_key, ss_partial.p); else { VK_CUDA(cudaFuncSetAttribute(ss_round_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); ss_round_kernel<DT><<<grid, 256, sm, h->stream>>>(Xr.p, w, S, prm.D, h->P, q0, q1, obs_lo, prm.N, ss_key, ss_partial.p); } } while (0)
+    const int fused = (compact && fuse_decide) ? 1 : 0;
+    const double Nt_d = (double)(N_total >= 0 ? N_total : prm.N);
+    unsigned int *ss_counter = (unsigned int *)(ss_i.p + 2 * h->P + 1);
+#define VK_SS_LAUNCH(DT) do { if (compact) ss_round_compact_kernel<DT><<<grid, 256, 0, h->stream>>>(Xr.p, w, S, prm.D, h->P, q0, q1, obs_lo, prm.N, ss_key, ss_partial.p, ss_gate(), fused, ss_counter, Nt_d, k0, eps); else { VK_CUDA(cudaFuncSetAttribute(ss_round_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); ss_round_kernel<DT><<<grid, 256, sm, h->stream>>>(Xr.p, w, S, prm.D, h->P, q0, q1, obs_lo, prm.N, ss_key, ss_partial.p, ss_gate()); } } while (0)
     if (prm.D <= 4) VK_SS_LAUNCH(4);
     else if (prm.D <= 8) VK_SS_LAUNCH(8);
     else if (prm.D <= 16) VK_SS_LAUNCH(16);
@@ -563,8 +573,10 @@ struct BLRModel : Model {
     else if (prm.D <= 64) VK_SS_LAUNCH(64);
     else throw Error(VK_EUNSUPPORTED, "subsampled_mh: D <= 64 in this version");
 #undef VK_SS_LAUNCH
-    ss_reduce_kernel<<<grid_for(h->P * 2 * 32, 128, h->sm_count, 4), 128, 0, h->stream>>>(ss_partial.p, grid, h->P, ss_sums.p);
+    if (fused) { VK_CUDA(cudaGetLastError()); return true; }
+    ss_reduce_kernel<<<grid_for(h->P * 2 * 32, 128, h->sm_count, 4), 128, 0, h->stream>>>(ss_partial.p, grid, h->P, ss_sums.p, ss_gate());
     VK_CUDA(cudaGetLastError());
+    return false;
   }
   // sequential-test decision from (possibly all-reduced) sums; ss_decide returns #particles still
   // undecided (host round trip); ss_decide_launch only enqueues, ss_decide_wait reads the count of
@@ -612,13 +624,12 @@ struct BLRModel : Model {
       // Rounds are enqueued in groups and the "anybody still undecided?" count is read back once
       // per group: a round after the last decision is a no-op (decided particles are skipped by
       // both kernels), so the result is identical to checking after every round.
-      const int GROUP = 4;
+      int GROUP = 4;           // grows: the stragglers' rounds are cheap (compact kernel, gated no-ops)
       int pending = 0;
       for (int64_t q0 = 0; q0 < Nt; q0 += Nbatch) {
         int64_t q1 = q0 + Nbatch < Nt ? q0 + Nbatch : Nt;
-        ss_round(q0, q1);
-        ss_decide_launch(ss_sums.p, q1, k0, eps);
-        if (++pending == GROUP || q1 == Nt) { pending = 0; if (ss_decide_wait() == 0) break; }
+        if (!ss_round(q0, q1, true, k0, eps)) ss_decide_launch(ss_sums.p, q1, k0, eps);
+        if (++pending == GROUP || q1 == Nt) { pending = 0; if (ss_decide_wait() == 0) break; if (GROUP < 16) GROUP *= 2; }
       }
       ss_commit();
     }

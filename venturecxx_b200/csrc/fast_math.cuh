@@ -337,12 +337,12 @@ __device__ __forceinline__ void fm_log_product(double q, const FmCoef &cf, uint3
   const uint32_t mant = hi & 0xFFFFFu;
   const double m = __hiloint2double((int)(mant | 0x3FF00000u), __double2loint(q));
   const uint32_t k = (mant + 0x1000u) >> 13;               // round(128 (m - 1)) in [0,128]
-  uint32_t inv_hi, c_hi, L_lo, L_hi, la;
+  uint32_t inv_hi, L_lo, L_hi, la;
+  [[maybe_unused]] uint32_t c_hi;                          // inv[k] - 1: the term-by-term form's addend, not needed here
   asm("mad.lo.u32 %0, %1, 128, %2;" : "=r"(la) : "r"(k), "r"(log_base));
   asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
       : "=r"(inv_hi), "=r"(c_hi), "=r"(L_lo), "=r"(L_hi)
       : "r"(la));
-  (void)c_hi;
   const double r2 = fma(m, __hiloint2double((int)inv_hi, 0), -1.0);
   double Q = cf.Q[5];
   Q = fma(Q, r2, cf.Q[4]);

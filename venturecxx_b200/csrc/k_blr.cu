@@ -267,7 +267,6 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
             else ev = (i0 + u * THREADS < N) ? eta_g[i0 + u * THREADS] : BLR_PAD_ETA;
             v[u] = fma(delta, xn[u], ev);
           }
-#pragma unroll
           {
             const double *src = it + 1 < iters ? xp : xnext;   // next tile, or the next transition's first tile
 #pragma unroll

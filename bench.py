@@ -11,7 +11,12 @@ per GPU, program `(resimulation_mh default one 160)` (10 sweeps) per step.
 One JSON line on rank 0.  `value` = particle-site MH transitions/s with the
 particle state resident in HBM (device-timed, max over ranks); `e2e` = the same
 metric through the public host-buffer API (forget + observe(X, y) H2D +
-incorporate + resimulation_mh + D2H of node counts and log weights, per step).
+incorporate + resimulation_mh + D2H of the node counts, per step).
+`configs` carries the other BASELINE.json configs at the same GPU count
+(tools/bench_configs.py): c1 normal-normal, c3 HMM filter with the particles
+sharded over the GPUs (peer-memory resample), c4 LDA, c5 subsampled_mh with the
+observations sharded over the GPUs (peer mailbox) -- each with its own roofline,
+identity flag against the 1-GPU result and, at one GPU, a cpu_baseline.
 """
 import argparse
 import json
@@ -230,7 +235,11 @@ def run_reference(args, X, y, D, N, T):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "C2 Bayesian logistic regression, single-site resimulation_mh (default one)",
-                   "particles_per_gpu": args.particles, "observations": N, "D": D, "transitions_per_step": T},
+                   "observations": N, "D": D,
+                   "timed": "one trace per host core (%d traces) x 1 transition per step; the GPU arm's 65 536 particles x 160 "
+                            "transitions per step would take this arm weeks, the rate per transition is what is compared"
+                            % cb["cores"],
+                   "particles": cb["cores"], "transitions_per_step": 1},
         "cpu_baseline": cb,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "obs_loglik_evals_per_sec": value * N,
@@ -249,6 +258,9 @@ def main():
     ap.add_argument("--dim", type=int, default=16)
     ap.add_argument("--transitions", type=int, default=160)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the secondary configs (c1, c3, c4, c5)")
+    ap.add_argument("--configs", default="c1,c3,c4,c5")
+    ap.add_argument("--configs-timeout", type=int, default=420, help="seconds before the secondary configs are abandoned")
     args = ap.parse_args()
     D, N, T, P = args.dim, args.obs, args.transitions, args.particles
     X, y = make_data(N, D)
@@ -311,14 +323,27 @@ def main():
     Xp = torch.from_numpy(X).pin_memory().numpy()
     yp = torch.from_numpy(y).pin_memory().numpy()
 
+    nodes_pinned = torch.empty(P, dtype=torch.float64).pin_memory().numpy()
+    phases = {"forget": 0.0, "observe_h2d": 0.0, "incorporate": 0.0, "resimulation_mh_d2h": 0.0}
+
     def step_e2e():
-        ts.forget_observations()
-        ts.observe(Xp, yp)                       # H2D: N*D*8 + N bytes
-        ts.incorporate()                         # D2H: P*8 (increments)
-        nodes = ts.primitive_infer(["resimulation_mh", "default", "one", T])   # D2H: P*8
+        # the program a user runs per batch of data: forget the old observations, observe the new ones (HOST
+        # buffers), incorporate, infer, read the result back.  Host time per phase is recorded (the calls with
+        # host buffers drain the stream, so the last phase carries the kernels' time).
+        t = time.perf_counter()
+        ts.forget_observations(return_weights=False)
+        t1 = time.perf_counter(); phases["forget"] += t1 - t
+        ts.observe(Xp, yp)                       # H2D: N*D*8 + N bytes (pinned)
+        t2 = time.perf_counter(); phases["observe_h2d"] += t2 - t1
+        ts.incorporate(return_increments=False)  # stream-ordered
+        t3 = time.perf_counter(); phases["incorporate"] += t3 - t2
+        nodes = ts.resimulation_mh("default", "one", T, out=nodes_pinned)   # D2H: P*8 into pinned memory
+        phases["resimulation_mh_d2h"] += time.perf_counter() - t3
         return nodes
 
     step_e2e()
+    for k in phases:
+        phases[k] = 0.0
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
@@ -347,7 +372,9 @@ def main():
     if world > 1:
         dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
     ms, ms_e2e, ms_f32 = [float(v) for v in t_ms.tolist()]
+    ts.close()
 
+    out = None
     if rank == 0:
         total_tr = float(P) * world * T * args.steps
         value = total_tr / (ms * 1e-3)
@@ -368,7 +395,8 @@ def main():
             "obs_loglik_evals_per_sec": value * N,
             "accept_rate": a_rate,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
-                    "h2d_bytes_per_step": int(X.nbytes + y.nbytes), "d2h_bytes_per_step": int(3 * P * 8)},
+                    "h2d_bytes_per_step": int(X.nbytes + y.nbytes), "d2h_bytes_per_step": int(P * 8),
+                    "host_ms_per_phase": dict((k, 1e3 * v / args.steps) for k, v in phases.items())},
             "gpu_launches": args.steps,
             "fp32_mode": {"value": total_tr / (ms_f32 * 1e-3), "unit": UNIT, "ms_per_step": ms_f32 / args.steps,
                           "note": "same workload and steps with vk_set_precision(VK_FP32): float logit row and MUFU "
@@ -376,6 +404,7 @@ def main():
                                   "within 1e-5 relative of fp64 (tests/test_gpu_fp32_mode.py). Not the headline: "
                                   "`value`, `e2e` and `roofline` are the fp64 path."},
             "clocks": clocks,
+            "configs": {},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "kernel": "blr_mh_kernel<SMEM=true, 256 threads, 4 chains, 2 CTAs/SM>",
@@ -392,7 +421,43 @@ def main():
         if not args.no_cpu_baseline and world == 1:
             cb, _ = cpu_baseline(X, y, D, N, T)
             out["cpu_baseline"] = cb
-        print(json.dumps(out))
+
+    # ---- the other BASELINE.json configs at this GPU count (tools/bench_configs.py) ---------------
+    # The headline line must survive whatever happens here: a watchdog on EVERY rank prints it (rank 0) and
+    # leaves after --configs-timeout seconds (a rank stuck in a collective cannot be recovered otherwise).
+    printed = threading.Lock()
+
+    def emit_line():
+        if rank == 0 and printed.acquire(False):
+            print(json.dumps(out), flush=True)
+
+    def watchdog():
+        if out is not None:
+            out["configs"]["error"] = "secondary configs did not finish within %d s; records so far kept" % args.configs_timeout
+        emit_line()
+        os._exit(0)
+
+    if not args.no_configs:
+        timer = threading.Timer(args.configs_timeout, watchdog)
+        timer.daemon = True
+        timer.start()
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_configs as bc
+        ctx = bc.Ctx(world, rank, local, stream)
+        want_cpu = (not args.no_cpu_baseline) and world == 1
+        for name in [c for c in args.configs.split(",") if c]:
+            t_sub = time.perf_counter()
+            try:
+                rec = bc.ALL[name](ctx, cpu=want_cpu)
+                rec["bench_seconds"] = time.perf_counter() - t_sub
+            except Exception as e:           # a secondary record never takes the headline line down with it
+                import traceback
+                rec = {"error": "%s: %s" % (type(e).__name__, e), "traceback": traceback.format_exc()[-1500:]}
+                sys.stderr.write("bench config %s failed on rank %d: %s\n" % (name, rank, rec["traceback"]))
+            if out is not None:
+                out["configs"][name] = rec
+        timer.cancel()
+    emit_line()
     if world > 1:
         dist.destroy_process_group()
 

@@ -166,7 +166,11 @@ int vk_logsumexp_array(const double *in_host, int64_t n, int device,
 
 /* ---- resample (trace_set.py:202-235, utils.py:93-104,152-157,170-180) ---
  * Draw n_new ancestors proportional to exp(lw); copy ancestor state; all new
- * weights = logsumexp(lw) - log(n_new).  n_new must equal P in this version.
+ * weights = logsumexp(lw) - log(n_new).  n_new may differ from the current particle count (the
+ * reference's programs start with `(resample 1000)` on one particle, benchmarks/Makefile:6-9): the
+ * handle then holds n_new particles afterwards (vk_num_particles), every per-particle output of later
+ * calls has n_new entries, and global particle indices (RNG streams) are p_base + [0, n_new).  A
+ * particle set sharded over peer GPUs (vk_p2p_open) cannot change its size.
  * uniforms_host: NULL = draw from the handle's Philox stream; otherwise 1
  * (systematic) or n_new (multinomial) uniforms in [0,1) to use instead.
  * ancestors_out_host: NULL or n_new int32. */
@@ -187,17 +191,26 @@ int vk_mh(vk_particles *h, int32_t scope, int32_t block, int32_t transitions,
  * python/lib/engine/trace_set.py:202-235 for a particle set block-partitioned over the GPUs of one node,
  * one process per GPU: rank g owns global particles [g*P, (g+1)*P) (vk_set_particle_base).  No NCCL
  * collective and no host synchronisation on the path: three scalars per rank travel through mailboxes in
- * peer memory, ancestor indices are stored straight into the owning rank's array, ancestor rows are
- * pulled with peer loads (csrc/p2p_resample.cuh has the protocol).  Result bit-identical to vk_resample
+ * peer memory (the two exchanges ride in the tails of the kernels that produce their payload, so a sharded
+ * resample is the same four launches as a single-GPU one), ancestor indices are stored straight into the
+ * owning rank's array, ancestor rows are pulled with peer loads as soon as their index has arrived
+ * (csrc/p2p_common.cuh, csrc/p2p_resample.cuh have the protocol).  Result bit-identical to vk_resample
  * on a single GPU holding all world*P particles.
+ * Failure: a peer that never arrives at an exchange trips a wall-clock bound (VK_P2P_TIMEOUT_S, default 20);
+ * the step is then abandoned on this rank (weights poisoned with NaN, nothing consumed from the stale
+ * mailbox) and the NEXT host-synchronising call on the handle (vk_synchronize, any call with a host output)
+ * fails with VK_ECUDA -- the particle set is invalid from then on.
  *   vk_p2p_export  allocates the mailbox and writes this handle's CUDA IPC handles (64 bytes each:
  *                  mailbox, ancestor array, both buffers of every state array) to handles_out.
  *   vk_p2p_open    all_handles = the exports of ranks 0..world-1 concatenated (exchange them with any
  *                  host mechanism, e.g. torch.distributed.all_gather_object); opens the peers' memory.
  *   vk_p2p_resample  the resample itself (mode as vk_resample); stream-ordered, returns immediately.
  *                  Every rank must call it the same number of times.
- *   vk_p2p_status  synchronises; *timed_out = 1 if a peer never arrived at an exchange (~2 s bound);
- *                  *lse_out = global logsumexp of the weights before the last resample. */
+ *   vk_p2p_status  synchronises and reports without failing; *timed_out = 1 if a peer never arrived at an
+ *                  exchange; *lse_out = global logsumexp of the weights before the last resample.
+ * The same peer tables carry the observation-sharded subsampled MH (E3): open them on handles whose
+ * particles are REPLICATED (particle base 0 on every rank, vk_blr_set_observation_shard) and
+ * vk_subsampled_mh exchanges its per-particle partial sums through peer mailboxes inside its kernel. */
 int vk_p2p_export(vk_particles *h, unsigned char *handles_out, int32_t max_handles, int32_t *n_handles_out);
 int vk_p2p_open(vk_particles *h, int32_t world, int32_t rank, const unsigned char *all_handles, int32_t n_handles);
 int vk_p2p_resample(vk_particles *h, int mode);
@@ -215,7 +228,12 @@ int vk_gibbs(vk_particles *h, int32_t scope, int32_t block, int32_t transitions,
 
 /* infer/subsampled_mh.py:76-171 (BLR model only).  stats_out_host: NULL or
  * 3*P doubles per call = (accepted transitions, mean local sections visited
- * per transition, last t statistic). */
+ * per transition, last t statistic).
+ * One cooperative, persistent kernel runs every transition of the call (proposal, minibatch rounds,
+ * sequential tests, accept) on the device (csrc/blr_subsampled_persistent.cuh; D <= 32, P <= 4096 -- larger
+ * D runs the host-driven round loop).  With observations sharded over peer GPUs
+ * (vk_blr_set_observation_shard + vk_p2p_open on replicated particles) the same call exchanges the
+ * per-particle partial sums through peer memory and every rank takes identical decisions. */
 int vk_subsampled_mh(vk_particles *h, int32_t scope, int32_t block,
                      int64_t Nbatch, int32_t k0, double epsilon,
                      int32_t use_delta_kernels, double delta_sigma,
@@ -265,6 +283,9 @@ int vk_device_buffer(vk_particles *h, int32_t which, void **dev_ptr_out,
  * whose threshold falls in this shard's mass interval -> pack rows ->
  * all_to_all -> unpack into slots. */
 int vk_shard_weight_max(vk_particles *h, double *max_out_host);
+/* out3_host = (max ignoring NaN, min ignoring NaN, 1.0 if any weight is NaN): what utils.logsumexp
+ * (lite/utils.py:77-91) needs from every shard for its +-inf / NaN cases. */
+int vk_shard_weight_stats(vk_particles *h, double *out3_host);
 int vk_shard_build_cdf(vk_particles *h, double global_max, int32_t frac_bits,
                        uint64_t *mass_out_host, double *sumexp_out_host);
 /* anc_out_dev[t] (t < k_count) = local ancestor of child k_begin+t of

@@ -15,7 +15,7 @@
  * Lite.  Where Lite delegates to scipy (gamma/beta logpdf, gammaln, betaln,
  * t.cdf) the closed forms are restated here and pinned against scipy and
  * against the reference's own functions in tests/ (see tests/golden/make_golden.py
- * and tests/golden/*.json).
+ * and the tests/golden JSON fixtures).
  *
  * Pinning status: PINNED against the reference run in this container.
  *  (1) Whole chains of the five site programs (likelihood_weight, makeConsistent, resimulation MH incl. the
@@ -64,7 +64,8 @@ static double st_uniform(orc_stream *s) {
   uint32_t w = (s->d & 1u) * 2u;
   uint64_t x = (((uint64_t)s->b[w] << 32) | s->b[w + 1]) >> 11;
   s->d++;
-  return ((double)x + 0.5) * (1.0 / 9007199254740992.0);
+  /* (2^53 - 1) + 0.5 rounds to 2^53: keep the result strictly below 1 (same clamp as csrc/philox.cuh) */
+  { double u = ((double)x + 0.5) * (1.0 / 9007199254740992.0); return u < 1.0 ? u : 0.99999999999999988898; }
 }
 static void st_seek(orc_stream *s, uint32_t d) { s->d = d; if (d & 1u) st_fill(s); }
 
@@ -333,6 +334,9 @@ void orc_fixed_cdf(const double *lw, int64_t n, double m, int frac_bits, uint64_
   for (int64_t i = 0; i < n; ++i) {
     uint64_t q;
     if (!(m > -INFINITY)) q = 1;
+    /* max = +inf: the reference's sampleLogCategorical (utils.py:170-180) forms exp(inf - inf) = NaN and numpy
+     * raises; defined here as "all the mass on the +inf entries" (the limit), so the total is never 0 */
+    else if (m == INFINITY) q = lw[i] == INFINITY ? 1 : 0;
     else { double d = lw[i] - m; q = (d != d) ? 0 : (uint64_t)nearbyint(exp(d) * scale); }
     run += q; cdf[i] = run;
   }
@@ -886,6 +890,63 @@ void orc_blr_subsampled_mh(double *w, const double *X, const uint8_t *y, int D, 
       double n_used, tstat;
       int accept = orc_sequential_test(mu_0, k0, Nbatch, (double)N, epsilon, dllh, &n_used, &tstat);
       free(dllh);
+      if (accept) { w[(int64_t)j * P + p] = wn[j]; acc[p] += 1; }
+      nsum[p] += n_used; last_t[p] = tstat;
+    }
+  }
+  if (stats) for (int64_t p = 0; p < P; ++p) { stats[3 * p] = acc[p]; stats[3 * p + 1] = n_steps ? nsum[p] / n_steps : 0; stats[3 * p + 2] = last_t[p]; }
+  free(perm); free(acc); free(nsum); free(last_t);
+}
+
+/* The same transition with the local sections evaluated lazily, minibatch by minibatch (what Lite does and what
+ * a CPU implementation would time); identical results (tests/test_oracle_golden.py). */
+void orc_blr_subsampled_mh_lazy(double *w, const double *X, const uint8_t *y, int D, int64_t N, int64_t P,
+                           int64_t p_base, double mu0, double s0, uint64_t seed, uint32_t step0, int n_steps,
+                           int block_mode, double Nbatch, int k0, double epsilon, int delta_mode, double delta_eps,
+                           double *stats) {
+  uint64_t *perm = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)N);
+  double *acc = (double *)calloc((size_t)P, sizeof(double)), *nsum = (double *)calloc((size_t)P, sizeof(double));
+  double *last_t = (double *)calloc((size_t)P, sizeof(double));
+  for (int t = 0; t < n_steps; ++t) {
+    uint32_t step = step0 + (uint32_t)t;
+    orc_feistel_perm(seed, step, (uint64_t)N, perm);
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t p = 0; p < P; ++p) {
+      double wp[256], wn[256];
+      for (int j = 0; j < D; ++j) wp[j] = wn[j] = w[(int64_t)j * P + p];
+      orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step);
+      double u_sel = st_uniform(&r), log_u = log(st_uniform(&r));
+      int j;
+      if (block_mode == -1) { j = (int)(u_sel * D); if (j >= D) j = D - 1; }
+      else if (block_mode == -3) j = t % D; else j = block_mode;
+      if (delta_mode == 2) {  /* NormalDriftKernel, continuous.py:68-84 */
+        double nu = normal_sim(&r, 0.0, s0);
+        wn[j] = mu0 + sqrt(1 - delta_eps * delta_eps) * (wp[j] - mu0) + delta_eps * nu;
+      } else wn[j] = normal_sim(&r, mu0, s0);
+      double mu_0 = (log_u - 0.0) / (double)N;   /* :102 with alpha = 0 */
+      /* sequentialTest (:118-171) with fun_dllh evaluated ONLY for the sections the test consumes, as
+       * evalOneLocalSection is in Lite (:377-409) */
+      double n_used = 0, tstat = 0, cum = 0, cum2 = 0, kk = 0, Nd = (double)N;
+      int accept = -1, have_t = 0;
+      while (n_used < Nd) {
+        double n_end = fmin(n_used + Nbatch, Nd);
+        for (int64_t q = (int64_t)n_used; q < (int64_t)n_end; ++q) {
+          int64_t i = (int64_t)perm[q];
+          double eo = blr_eta(wp, X + i * D, D), en = blr_eta(wn, X + i * D, D);
+          double dl = orc_log_logistic(y[i] ? en : -en) - orc_log_logistic(y[i] ? eo : -eo);
+          cum += dl; cum2 += dl * dl;
+        }
+        kk += 1; n_used = n_end;
+        double mx = cum / n_end, mx2 = cum2 / n_end;
+        if (kk < k0 && n_used < Nd) continue;
+        if (n_used == Nd) { accept = mx >= mu_0; break; }
+        double sx = sqrt((1 - (n_used - 1) / (Nd - 1)) * (mx2 - mx * mx) / (n_used - 1)), qv;
+        if (sx == 0) qv = mx >= mu_0 ? 1 : 0;
+        else { tstat = (mx - mu_0) / sx; have_t = 1; qv = orc_student_t_cdf(tstat, n_used - 1); }
+        if (qv < epsilon) { accept = 0; break; }
+        else if (qv > 1 - epsilon) { accept = 1; break; }
+      }
+      tstat = (have_t && tstat != 0) ? tstat : (accept ? INFINITY : -INFINITY);
       if (accept) { w[(int64_t)j * P + p] = wn[j]; acc[p] += 1; }
       nsum[p] += n_used; last_t[p] = tstat;
     }

@@ -31,11 +31,17 @@ class CpuShard(object):
         v = self.lw[~np.isnan(self.lw)]
         return float(v.max()) if v.size else -math.inf
 
+    def weight_stats(self):
+        v = self.lw[~np.isnan(self.lw)]
+        return (float(v.max()) if v.size else -math.inf, float(v.min()) if v.size else math.inf,
+                bool(np.isnan(self.lw).any()))
+
     def build_cdf(self, gmax, frac_bits):
         self.cdf = np.empty(self.P, dtype=np.uint64)
         oracle.lib().orc_fixed_cdf(oracle._ptr(self.lw), oracle.I64(self.P), oracle.F64(gmax), oracle.I32(frac_bits),
                                    oracle._ptr(self.cdf))
-        se = float(np.exp(self.lw - gmax).sum()) if math.isfinite(gmax) else 0.0
+        with np.errstate(invalid="ignore"):
+            se = float(np.nansum(np.exp(self.lw - gmax))) if math.isfinite(gmax) else 0.0
         return int(self.cdf[-1]), se
 
     def ancestors(self, offset, total, n_new, k_begin, k_count, mode, step):
@@ -78,7 +84,7 @@ def _worker(rank, world, port, mode, lw_all, state_all, seed, step, out_q):
 
 
 @pytest.mark.parametrize("mode", ["systematic", "multinomial"])
-@pytest.mark.parametrize("case", ["generic", "one_heavy", "all_impossible"])
+@pytest.mark.parametrize("case", ["generic", "one_heavy", "all_impossible", "with_nan", "mixed_inf", "plus_inf"])
 def test_sharded_resample_equals_single_shard(mode, case):
     world, P_local, seed, step = 2, 257, 99, 7
     P = world * P_local
@@ -89,6 +95,13 @@ def test_sharded_resample_equals_single_shard(mode, case):
         lw[300] = 0.0          # every child descends from a particle on rank 1
     elif case == "all_impossible":
         lw[:] = -np.inf
+    elif case == "with_nan":          # NaN weights carry no mass; the logsumexp is NaN (utils.py:77-91)
+        lw[[3, 260, 400]] = np.nan
+    elif case == "mixed_inf":         # +inf on one rank, -inf on the other: logsumexp is NaN on every rank
+        lw[5] = np.inf
+        lw[300] = -np.inf
+    elif case == "plus_inf":          # +inf entries take all the mass; logsumexp = +inf
+        lw[[7, 333]] = np.inf
     state = rng.integers(0, 255, size=(P, 48), dtype=np.uint8)
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
@@ -105,8 +118,10 @@ def test_sharded_resample_equals_single_shard(mode, case):
     assert np.array_equal(new_state, state[anc])
     lse = oracle.logsumexp(lw)
     for r in res:
-        if math.isinf(lse):
-            assert r[1] == lse and np.all(r[3] == -np.inf)
+        if math.isnan(lse):
+            assert math.isnan(r[1]) and np.all(np.isnan(r[3]))
+        elif math.isinf(lse):
+            assert r[1] == lse and np.all(r[3] == lse)
         else:
             assert abs(r[1] - lse) <= 1e-12 * abs(lse)
             np.testing.assert_allclose(r[3], lse - math.log(P), rtol=1e-12)

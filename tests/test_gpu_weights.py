@@ -120,3 +120,73 @@ def test_normalized_probs(orc):
     ts.set_particle_log_weights(np.full(P, -np.inf))
     assert np.all(ts.particle_normalized_probs() == 0)
     assert ts.logsumexp() == -np.inf
+
+
+@pytest.mark.parametrize("P_old,P_new", [(1, 1000), (1000, 333), (3000, 5000), (70000, 4096), (1500, 70000)])
+@pytest.mark.parametrize("mode", ["systematic", "multinomial"])
+def test_resample_changes_particle_count(orc, P_old, P_new, mode):
+    """trace_set.py:202-219: (resample P_new) on P_old traces -- how `(resample 1000)` grows one particle into
+    the particle set of the reference's programs (benchmarks/Makefile:6-9)."""
+    rng = np.random.default_rng(P_old + P_new)
+    ts = make_ts(P_old)
+    lw = rng.normal(0, 2, P_old)
+    ts.set_particle_log_weights(lw)
+    x_before = ts.read_site(0)
+    step = ts.rng_step
+    anc = ts.resample(P_new, mode=mode, return_ancestors=True)
+    ref = orc.ancestors(lw, P_new, 1 if mode == "systematic" else 0, seed=7, step=step)
+    assert anc.shape == (P_new,) and np.array_equal(anc, ref)
+    assert ts.n_particles == P_new
+    assert np.array_equal(ts.read_site(0), x_before[anc])
+    lse = orc.logsumexp(lw)
+    got = ts.log_weights
+    assert got.shape == (P_new,)
+    np.testing.assert_allclose(got, np.full(P_new, lse - math.log(P_new)), rtol=1e-12)
+    # the resized set keeps working: weights, a second (same-size) resample, prior resimulation
+    ts.likelihood_weight()
+    lw2 = ts.log_weights
+    step = ts.rng_step
+    anc2 = ts.resample(P_new, mode=mode, return_ancestors=True)
+    assert np.array_equal(anc2, orc.ancestors(lw2, P_new, 1 if mode == "systematic" else 0, seed=7, step=step))
+
+
+def test_resample_resizes_every_model_kind(orc):
+    """state rows of every compiled model follow their particle through a size-changing resample"""
+    from helpers import golden
+    H = golden("hmm.json")
+    hm = vb.B200TraceSet(vb.HMMModel(H["transition_matrix"], H["emission_matrix"], 1, 20), 700, seed=3)
+    for d in H["data"][:5]:
+        hm.observe(d); hm.incorporate()
+    hist = np.stack([hm.read_site(t) for t in range(5)])
+    anc = hm.resample(2500, mode="systematic", return_ancestors=True)
+    assert np.array_equal(np.stack([hm.read_site(t) for t in range(5)]), hist[:, anc])
+    hm.observe(H["data"][5]); hm.incorporate()
+    assert hm.log_weights.shape == (2500,)
+    X = np.random.default_rng(0).normal(size=(50, 3))
+    y = (np.random.default_rng(1).random(50) < 0.5).astype(np.uint8)
+    bl = vb.B200TraceSet(vb.LogisticRegressionModel(3, 50), 300, seed=4)
+    bl.observe(X, y); bl.incorporate()
+    w = np.stack([bl.read_site(j) for j in range(3)])
+    ll = bl.log_likelihood_at("default", "all")
+    anc = bl.resample(120, mode="multinomial", return_ancestors=True)
+    assert np.array_equal(np.stack([bl.read_site(j) for j in range(3)]), w[:, anc])
+    np.testing.assert_allclose(bl.log_likelihood_at("default", "all"), ll[anc], rtol=1e-12)
+    nodes, acc = bl.resimulation_mh("default", "one", 10, return_accepts=True)
+    assert nodes.shape == (120,) and acc.shape == (120,)
+    st = bl.subsampled_mh("default", "one", 10, 2, 0.05, False, 0, False, 3)
+    assert st.shape == (120, 3)
+
+
+def test_resample_plus_infinite_weights_take_all_mass(orc):
+    # max = +inf: the reference's sampleLogCategorical forms exp(inf - inf) and numpy raises; here the +inf
+    # entries share the mass (the limit), so every child has an ancestor and nothing reads an unset index
+    for P in (600, 5000):
+        ts = make_ts(P)
+        lw = np.random.default_rng(P).normal(0, 1, P)
+        lw[[5, 77]] = np.inf
+        ts.set_particle_log_weights(lw)
+        step = ts.rng_step
+        anc = ts.resample(P, mode="systematic", return_ancestors=True)
+        assert set(anc.tolist()) == {5, 77}
+        assert np.array_equal(anc, orc.ancestors(lw, P, 1, seed=7, step=step))
+        assert np.all(ts.log_weights == np.inf)

@@ -8,9 +8,10 @@
    sharded resample, this rank's histories must equal the matching slice of a single-GPU
    run over all particles (Philox streams are keyed by GLOBAL particle index and the
    fixed-point CDF makes ancestors independent of the GPU count) -- bit exact.
-2. subsampled_mh (C5 shape, small N) with observations sharded and particles replicated:
-   weights must equal the single-GPU run to 1e-12 and the accept counts exactly.
-Prints one JSON line on rank 0 with the timings of the sharded paths.
+2. subsampled_mh (C5 shape, small N) with observations sharded and particles replicated, over NCCL
+   (round-level vk_ssmh_* calls) and through the peer mailbox inside the persistent kernel: weights
+   must equal the single-GPU run to 1e-12, accept counts and sections visited exactly.
+Prints one JSON line on rank 0.  Timings at the BASELINE sizes: bench.py --gpus N (configs.c3, configs.c5).
 """
 import json
 import os
@@ -125,70 +126,26 @@ def main():
     np.testing.assert_allclose(st_sh[:, 1], st_ref[:, 1], rtol=1e-12)
     out["subsampled_mh"] = {"observations": N, "particles": P, "transitions": 30, "seconds": dt,
                             "accepted_mean": float(st_sh[:, 0].mean())}
-    # ---- 3. C3 at full size: 2^20 particles over the ranks, 20 filter steps (timed) --------
-    P_local = (1 << 20) // world
-    model = vb.HMMModel(H["transition_matrix"], H["emission_matrix"], 1, 20)
-    for rep in range(2):                      # first repetition warms NCCL and the allocator
-        sh = ShardedTraceSet(model, P_local, seed=5 + rep, device=local)
-        torch.cuda.synchronize(); dist.barrier()
-        t0 = time.perf_counter()
-        for d in H["data"]:
-            sh.observe(d); sh.incorporate(return_increments=False); sh.resample(mode="systematic")
-        torch.cuda.synchronize(); dist.barrier()
-        dt = time.perf_counter() - t0
-        T = len(H["data"])
-        m = np.bincount(sh.read_site(T - 1).astype(int), minlength=6)[1:6].astype(np.float64)
-        mt = torch.tensor(m, device="cuda")
-        dist.all_reduce(mt)
-        tvd = 0.5 * np.abs(mt.cpu().numpy() / (P_local * world) - np.array(H["filtered_marginals"][T - 1])).sum()
-        sh.local.close()
-    out["c3_sharded"] = {"particles": P_local * world, "steps": T, "ms_per_step": 1e3 * dt / T,
-                         "particle_steps_per_sec": P_local * world * T / dt, "tvd_last": float(tvd)}
-    assert tvd < 0.01, tvd
-    # ---- 3b. the same, peer-memory resample: the whole filter is stream-ordered, one sync at the end ----
-    for rep in range(2):
-        sh = ShardedTraceSet(model, P_local, seed=5 + rep, device=local)
-        sh.enable_peer_memory()
-        torch.cuda.synchronize(); dist.barrier()
-        t0 = time.perf_counter()
-        for d in H["data"]:
-            sh.observe(d); sh.incorporate(return_increments=False); sh.resample(mode="systematic")
-        sh.local.synchronize(); torch.cuda.synchronize(); dist.barrier()
-        dt = time.perf_counter() - t0
-        timed_out, _ = sh.peer_status()
-        assert not timed_out
-        m = np.bincount(sh.read_site(T - 1).astype(int), minlength=6)[1:6].astype(np.float64)
-        mt = torch.tensor(m, device="cuda")
-        dist.all_reduce(mt)
-        tvd = 0.5 * np.abs(mt.cpu().numpy() / (P_local * world) - np.array(H["filtered_marginals"][T - 1])).sum()
-        dist.barrier()
-        sh.local.close()
-    out["c3_sharded_peer_memory"] = {"particles": P_local * world, "steps": T, "ms_per_step": 1e3 * dt / T,
-                                     "particle_steps_per_sec": P_local * world * T / dt, "tvd_last": float(tvd)}
-    assert tvd < 0.01, tvd
-    # ---- 3c. weak scaling of the same filter: 2^20 particles PER GPU, peer-memory resample ----
-    P_big = 1 << 20
-    for rep in range(2):
-        sh = ShardedTraceSet(model, P_big, seed=7 + rep, device=local)
-        sh.enable_peer_memory()
-        torch.cuda.synchronize(); dist.barrier()
-        t0 = time.perf_counter()
-        for d in H["data"]:
-            sh.observe(d); sh.incorporate(return_increments=False); sh.resample(mode="systematic")
-        sh.local.synchronize(); torch.cuda.synchronize(); dist.barrier()
-        dt = time.perf_counter() - t0
-        timed_out, _ = sh.peer_status()
-        assert not timed_out
-        m = np.bincount(sh.read_site(T - 1).astype(int), minlength=6)[1:6].astype(np.float64)
-        mt = torch.tensor(m, device="cuda")
-        dist.all_reduce(mt)
-        tvd = 0.5 * np.abs(mt.cpu().numpy() / (P_big * world) - np.array(H["filtered_marginals"][T - 1])).sum()
-        dist.barrier()
-        sh.local.close()
-    out["c3_weak_peer_memory"] = {"particles": P_big * world, "particles_per_gpu": P_big, "steps": T,
-                                  "ms_per_step": 1e3 * dt / T, "particle_steps_per_sec": P_big * world * T / dt,
-                                  "tvd_last": float(tvd)}
-    assert tvd < 0.01, tvd
+    # ---- 2b. the same through the peer mailbox inside the persistent kernel (no collective, no host loop) ----
+    sh2 = ShardedTraceSet(model, P, seed=5, device=local, replicate_particles=True)
+    sh2.observe_shard(X[lo:hi], y[lo:hi], lo, N)
+    sh2.local.incorporate()
+    sh2.enable_peer_memory()
+    sh2.local.rng_step = 100
+    torch.cuda.synchronize(); dist.barrier()
+    t0 = time.perf_counter()
+    st_p = sh2.subsampled_mh(*args)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    w_p = np.stack([sh2.local.read_site(j) for j in range(D)])
+    np.testing.assert_allclose(w_p, w_ref, rtol=1e-12)
+    assert np.array_equal(st_p[:, 0], st_ref[:, 0]), "accept counts differ (peer mailbox)"
+    assert np.array_equal(st_p[:, 1], st_ref[:, 1]), "sections visited differ (peer mailbox)"
+    out["subsampled_mh_peer_memory"] = {"observations": N, "particles": P, "transitions": 30, "seconds": dt,
+                                        "decisions": "identical to the single-GPU run"}
+    dist.barrier()
+    sh2.local.close()
+    # ---- 3. timing of the sharded filter / subsampled MH at the BASELINE sizes: bench.py --gpus N (configs.c3, configs.c5)
     dist.barrier()
     if rank == 0:
         out["status"] = "ok"

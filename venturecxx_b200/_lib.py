@@ -72,6 +72,7 @@ PROTOTYPES = {
     "vk_num_blocks": [_vp, _i32, _vp],
     "vk_device_buffer": [_vp, _i32, _vp, _vp],
     "vk_shard_weight_max": [_vp, _vp],
+    "vk_shard_weight_stats": [_vp, _vp],
     "vk_shard_build_cdf": [_vp, _f64, _i32, _vp, _vp],
     "vk_shard_ancestors": [_vp, _u64, _u64, _i64, _i64, _i64, c.c_int, _u32, _vp, _vp],
     "vk_state_row_bytes": [_vp, _vp],

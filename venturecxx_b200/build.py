@@ -2,20 +2,24 @@
 
 nvcc cross-compiles without a GPU, so this runs on the CPU-only build box;
 the resulting .so is git-ignored but travels to the GPU box with the tree.
+Each .cu is compiled to its own object (in parallel, only when it or a header
+changed) and the objects are linked into the shared library.
 """
 import glob
 import os
 import subprocess
 import sys
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
+OBJ = os.path.join(HERE, "build")
 SO = os.path.join(HERE, "libventure_b200.so")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
-    "-Xcompiler", "-fPIC", "-shared",
+    "-Xcompiler", "-fPIC",
 ]
 
 
@@ -24,23 +28,41 @@ def sources():
 
 
 def headers():
-    return sorted(glob.glob(os.path.join(CSRC, "*.cuh"))) + \
+    return sorted(glob.glob(os.path.join(CSRC, "*.cuh"))) + sorted(glob.glob(os.path.join(CSRC, "*.h"))) + \
         [os.path.join(HERE, "..", "include", "venture_b200.h")]
 
 
-def needs_build():
-    if not os.path.exists(SO):
+def _obj(src):
+    return os.path.join(OBJ, os.path.basename(src)[:-3] + ".o")
+
+
+def _stale(target, deps):
+    if not os.path.exists(target):
         return True
-    t = os.path.getmtime(SO)
-    return any(os.path.getmtime(f) > t for f in sources() + headers())
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(f) > t for f in deps)
+
+
+def needs_build():
+    return _stale(SO, sources() + headers())
 
 
 def build(force=False, verbose=False):
     if not force and not needs_build():
         return SO
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + sources()
-    subprocess.check_call(cmd, cwd=CSRC)
+    os.makedirs(OBJ, exist_ok=True)
+    hdrs = headers()
+    todo = [s for s in sources() if force or _stale(_obj(s), [s] + hdrs)]
+
+    def compile_one(src):
+        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", _obj(src), src]
+        subprocess.check_call(cmd, cwd=CSRC)
+
+    with ThreadPoolExecutor(max_workers=min(len(todo), os.cpu_count() or 1) or 1) as ex:
+        list(ex.map(compile_one, todo))
+    subprocess.check_call([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", SO] +
+                          [_obj(s) for s in sources()], cwd=CSRC)
     return SO
 
 

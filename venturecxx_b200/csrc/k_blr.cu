@@ -27,6 +27,8 @@
 #include "sp_math.cuh"
 #include "blr_subsampled.cuh"
 #include "fast_math.cuh"
+#include "blr_subsampled_persistent.cuh"
+#include "weights.cuh"
 #include <stdlib.h>
 
 namespace vk {
@@ -427,10 +429,10 @@ __global__ void blr_fill_const_kernel(double *out, int64_t n, double v) {
 struct BLRModel : Model {
   BLRParams prm;
   int64_t n_prop = 0;
-  DevBuf<double> Xs, wa, wb, etaa, etab, lla, llb;
+  DevBuf<double> Xs, wa, wb, etaa, etab, lla, llb, stage;
   DevBuf<uint8_t> y;
   double *w = nullptr, *w_alt = nullptr, *eta = nullptr, *eta_alt = nullptr, *ll = nullptr, *ll_alt = nullptr;
-  int smem_limit = 0;
+  int smem_limit = 0, coop_launch = 0;
   FmCoef fm_coef = fm_coef_host();
   // subsampled MH (C5): observation shard [obs_lo, obs_lo + N) of N_total, transition state
   int64_t obs_lo = 0, N_total = -1;
@@ -445,8 +447,20 @@ struct BLRModel : Model {
   DevBuf<int> ss_i;
   int64_t Xr_rows = 0;
   int *ss_active_host = nullptr;
+  // persistent subsampled-MH kernel (blr_subsampled_persistent.cuh)
+  DevBuf<double> ssp_partial, ssp_tcrit;
+  DevBuf<unsigned int> ssp_bar;
+  DevBuf<unsigned long long> ssp_seq;
+  int *ssp_abort_host = nullptr, *ssp_abort_dev = nullptr;     // mapped pinned: a timed-out barrier / exchange
+  std::vector<double> tcrit_host;
+  int64_t tcrit_Nbatch = -1, tcrit_Nt = -1; double tcrit_eps = -1.0; int tcrit_k0 = -1;
 
-  ~BLRModel() override { if (ss_active_host) cudaFreeHost(ss_active_host); }
+  ~BLRModel() override {
+    if (ss_active_host) cudaFreeHost(ss_active_host);
+    if (ssp_abort_host) cudaFreeHost(ssp_abort_host);
+  }
+  // per-particle subsampled-MH state is sized by the particle count (resample with n_new != P)
+  void ss_release() { ss_d.release(); ss_i.release(); ss_sums.release(); ss_partial.release(); ssp_partial.release(); }
 
   BLRModel(vk_particles *h_, int D, int64_t Ncap, double mu0, double s0) : Model(h_) {
     VK_REQUIRE(D >= 1 && D <= 256, VK_EINVAL, "blr: D must be in [1,256]");
@@ -464,11 +478,13 @@ struct BLRModel : Model {
     VK_CUDA(cudaMemsetAsync(w, 0, wa.bytes(), h->stream));
     VK_CUDA(cudaMemsetAsync(ll, 0, lla.bytes(), h->stream));
     VK_CUDA(cudaDeviceGetAttribute(&smem_limit, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+    VK_CUDA(cudaDeviceGetAttribute(&coop_launch, cudaDevAttrCooperativeLaunch, h->device));
   }
   void observe(const double *X_rows_host, const uint8_t *y_host, int64_t n) {
     VK_REQUIRE(prm.N + n <= prm.Ncap, VK_EINVAL, "blr: observation capacity exceeded");
-    DevBuf<double> stage; stage.alloc((size_t)n * prm.D);
-    VK_CUDA(cudaMemcpyAsync(stage.p, X_rows_host, stage.bytes(), cudaMemcpyHostToDevice, h->stream));
+    // grow-only staging buffer: no cudaMalloc / cudaFree (an implicit device synchronisation) per call
+    if (stage.n < (size_t)n * prm.D) { VK_CUDA(cudaStreamSynchronize(h->stream)); stage.alloc((size_t)n * prm.D); }
+    VK_CUDA(cudaMemcpyAsync(stage.p, X_rows_host, (size_t)n * prm.D * sizeof(double), cudaMemcpyHostToDevice, h->stream));
     VK_CUDA(cudaMemcpyAsync(y.p + prm.N, y_host, (size_t)n, cudaMemcpyHostToDevice, h->stream));
     blr_sign_features_kernel<<<grid_for(n * prm.D, 256, h->sm_count, 8), 256, 0, h->stream>>>(
         stage.p, y.p + prm.N, Xs.p, prm.D, prm.Xld, prm.N, n);
@@ -608,16 +624,113 @@ struct BLRModel : Model {
     ss_stats_kernel<<<grid_for(h->P, 128, h->sm_count, 4), 128, 0, h->stream>>>(ss_state(), h->P, K, out_dev);
     VK_CUDA(cudaGetLastError());
   }
+  // t.ppf(1 - eps, n_k - 1) per minibatch count k (host, cached per configuration); NaN where no t test can
+  // happen at that count (k < k0, n_k == N) and beyond the table (the kernel then evaluates the cdf itself)
+  void ss_tcrit_table(int64_t Nbatch, int64_t Nt, int k0, double eps) {
+    if (tcrit_Nbatch == Nbatch && tcrit_Nt == Nt && tcrit_k0 == k0 && tcrit_eps == eps && ssp_tcrit.p) return;
+    const int64_t rounds = (Nt + Nbatch - 1) / Nbatch;
+    const int n = (int)(rounds < 4096 ? rounds : 4096);
+    tcrit_host.assign((size_t)(n > 0 ? n : 1), NAN);
+    for (int ki = 0; ki < n; ++ki) {
+      const int64_t k = ki + 1;
+      const int64_t nk = k * Nbatch < Nt ? k * Nbatch : Nt;
+      if ((k < k0 && nk < Nt) || nk == Nt || nk < 2) continue;
+      tcrit_host[(size_t)ki] = eps > 0.0 ? ssp_host_t_ppf(1.0 - eps, (double)(nk - 1)) : INFINITY;
+    }
+    VK_CUDA(cudaStreamSynchronize(h->stream));      // a previous launch may still read the old table
+    ssp_tcrit.alloc(tcrit_host.size());
+    VK_CUDA(cudaMemcpyAsync(ssp_tcrit.p, tcrit_host.data(), ssp_tcrit.bytes(), cudaMemcpyHostToDevice, h->stream));
+    VK_CUDA(cudaStreamSynchronize(h->stream));
+    tcrit_Nbatch = Nbatch; tcrit_Nt = Nt; tcrit_k0 = k0; tcrit_eps = eps;
+  }
+  void ss_check_abort() {
+    if (ssp_abort_host && *(volatile int *)ssp_abort_host)
+      throw Error(VK_ECUDA, "subsampled_mh: the persistent kernel gave up waiting (a grid barrier or a peer exchange timed out)");
+  }
+  template <int DT>
+  void ss_launch_persistent(SSPersist &a) {
+    const size_t sm = ssp_smem_bytes(DT, h->P);
+    VK_REQUIRE(sm <= (size_t)smem_limit, VK_EUNSUPPORTED, "subsampled_mh: particle count too large for the kernel's shared memory");
+    VK_CUDA(cudaFuncSetAttribute(ss_persistent_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    int per_sm = 0;
+    VK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ss_persistent_kernel<DT>, SSP_THREADS, sm));
+    VK_REQUIRE(per_sm >= 1, VK_ECUDA, "subsampled_mh: the persistent kernel does not fit an SM");
+    if (per_sm > 2) per_sm = 2;
+    static const int cap = getenv("VK_SS_GRID") ? atoi(getenv("VK_SS_GRID")) : 0;
+    int grid = h->sm_count * per_sm;
+    if (cap > 0 && cap < grid) grid = cap;
+    const size_t need = (size_t)grid * SSP_GMAX * (size_t)h->P * 2;
+    if (ssp_partial.n < need) { VK_CUDA(cudaStreamSynchronize(h->stream)); ssp_partial.alloc(need); }
+    a.partial = ssp_partial.p;
+    void *args[] = {(void *)&a};
+    VK_CUDA(cudaLaunchCooperativeKernel((const void *)ss_persistent_kernel<DT>, dim3(grid), dim3(SSP_THREADS), args, sm, h->stream));
+  }
+  // every transition of the call in one cooperative launch (world > 1: with the peer exchange inside)
+  void ss_persistent(int block, int64_t Nbatch, int k0, double eps, int delta_mode, double delta_arg, int n_steps) {
+    const int64_t Nt = N_total >= 0 ? N_total : prm.N;
+    VK_REQUIRE(Nt > 1, VK_ESTATE, "subsampled_mh needs more than one local section (subsampled_mh.py:100)");
+    ss_begin_call();
+    if (!ssp_bar.p) {
+      ssp_bar.alloc(4);
+      ssp_seq.alloc(1);
+      VK_CUDA(cudaMemsetAsync(ssp_seq.p, 0, sizeof(unsigned long long), h->stream));
+      VK_CUDA(cudaHostAlloc((void **)&ssp_abort_host, sizeof(int), cudaHostAllocMapped));
+      *ssp_abort_host = 0;
+      VK_CUDA(cudaHostGetDevicePointer((void **)&ssp_abort_dev, ssp_abort_host, 0));
+    }
+    ss_check_abort();
+    ss_tcrit_table(Nbatch, Nt, k0, eps);
+    SSPersist a;
+    memset(&a, 0, sizeof a);
+    a.Xr = Xr.p; a.w = w; a.S = ss_state(); a.D = prm.D; a.P = h->P; a.p_base = h->p_base;
+    a.obs_lo = obs_lo; a.N_local = prm.N; a.Nt = Nt; a.Nbatch = Nbatch; a.k0 = k0; a.eps = eps;
+    a.block_mode = block; a.n_transitions = n_steps; a.delta_mode = delta_mode; a.delta_eps = delta_arg;
+    a.mu0_prior = prm.mu0; a.s0_prior = prm.s0; a.seed = h->seed; a.step0 = h->next_step((uint32_t)n_steps);
+    a.tcrit = ssp_tcrit.p; a.n_tcrit = (int)tcrit_host.size();
+    a.bar = ssp_bar.p; a.abort_flag = ssp_abort_dev; a.seq_dev = ssp_seq.p; a.cf = fm_coef;
+    P2PSSView v;
+    const bool peers = N_total >= 0 && p2p_ss_view(h, &v) && v.world > 1;
+    a.world = 1; a.rank = 0; a.timeout_ns = 20000000000ll;
+    if (peers) {
+      a.tab = v.tab; a.par = v.par; a.err_host = v.err_host_dev; a.world = v.world; a.rank = v.rank;
+      a.ss_stride = v.ss_stride; a.ss_pcap = v.ss_pcap; a.timeout_ns = v.timeout_ns;
+    }
+    static const int g_env = getenv("VK_SS_ROUNDS_PER_BATCH") ? atoi(getenv("VK_SS_ROUNDS_PER_BATCH")) : 0;
+    a.G_first = k0 < 1 ? 1 : (k0 > SSP_GMAX ? SSP_GMAX : k0);
+    a.G_next = g_env > 0 ? (g_env > SSP_GMAX ? SSP_GMAX : g_env) : (peers ? 4 : 2);
+    VK_CUDA(cudaMemsetAsync(ssp_bar.p, 0, ssp_bar.bytes(), h->stream));
+    if (prm.D <= 4) ss_launch_persistent<4>(a);
+    else if (prm.D <= 8) ss_launch_persistent<8>(a);
+    else if (prm.D <= 16) ss_launch_persistent<16>(a);
+    else ss_launch_persistent<32>(a);
+    VK_CUDA(cudaGetLastError());
+    eta_dirty = true;
+  }
+  bool ss_persistent_ok() const {
+    static const int off = getenv("VK_SS_HOST_LOOP") ? atoi(getenv("VK_SS_HOST_LOOP")) : 0;
+    return !off && prm.D <= 32 && h->P <= 4096 && coop_launch;
+  }
   void subsampled_mh(int scope, int block, int64_t Nbatch, int k0, double eps, int use_delta, double delta_arg,
                      int update_values, int K, double *stats_dev) override {
     VK_REQUIRE(scope == 0, VK_EINVAL, "blr: only the default scope exists");
     VK_REQUIRE(block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || (block >= 0 && block < prm.D), VK_EINVAL, "blr: bad block");
     VK_REQUIRE(n_prop == prm.N, VK_ESTATE, "subsampled_mh: unpropagated observations; call vk_make_consistent first");
     VK_REQUIRE(eps >= 0.0 && eps < 0.5, VK_EINVAL, "subsampled_mh: epsilon must be in [0, 0.5)");
-    (void)update_values;  // local sections are always evaluated from current values here
+    // updateValues (scaffold.py:119-146) refreshes a local section to the OLD global value before it is
+    // regenerated; here every section is evaluated from the current global value anyway (no per-section
+    // cache is read), so both settings give the same dllh
+    (void)update_values;
     int64_t Nt = N_total >= 0 ? N_total : prm.N;
-    ss_begin_call();
     int n_prop_steps = block == VK_BLOCK_EACH ? K * prm.D : K;
+    if (ss_persistent_ok()) {
+      if (n_prop_steps > 0) ss_persistent(block, Nbatch, k0, eps, use_delta == 2 ? 2 : 0, delta_arg, n_prop_steps);
+      else ss_begin_call();
+      if (stats_dev) ss_stats(n_prop_steps, stats_dev);
+      return;
+    }
+    VK_REQUIRE(N_total < 0 || N_total == prm.N, VK_EUNSUPPORTED,
+               "subsampled_mh: sharded observations need the persistent kernel (D <= 32, P <= 4096) or the round-level vk_ssmh_* calls");
+    ss_begin_call();
     for (int t = 0; t < n_prop_steps; ++t) {
       ss_propose(block, t, use_delta == 2 ? 2 : 0, delta_arg);
       // Rounds are enqueued in groups and the "anybody still undecided?" count is read back once
@@ -751,14 +864,22 @@ struct BLRModel : Model {
     VK_REQUIRE(site >= 0 && site < prm.D, VK_EINVAL, "blr: site out of range");
     VK_CUDA(cudaMemcpyAsync(w + site * h->P, in_dev, (size_t)h->P * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
   }
-  std::vector<StateArray> state_arrays() override {
+  std::vector<StateArray> state_arrays(bool alloc_alt) override {
     ensure_fresh();
     // back buffers are allocated on first resample (eta doubles the footprint)
-    if (!wb.p) { wb.alloc(wa.n); etab.alloc(etaa.n); llb.alloc(lla.n); w_alt = wb.p; eta_alt = etab.p; ll_alt = llb.p; }
+    if (alloc_alt && !wb.p) { wb.alloc(wa.n); etab.alloc(etaa.n); llb.alloc(lla.n); w_alt = wb.p; eta_alt = etab.p; ll_alt = llb.p; }
     StateArray a{(void **)&w, (void **)&w_alt, 0, (size_t)prm.D, 8};
     StateArray b{(void **)&eta, (void **)&eta_alt, (size_t)prm.Ncap * 8, 0, 0};
     StateArray c{(void **)&ll, (void **)&ll_alt, 0, 1, 8};
     return {a, b, c};
+  }
+  void resized(int64_t n_new, const std::vector<void *> &nc, const std::vector<void *> &na) override {
+    const size_t n = (size_t)n_new;
+    wa.adopt(nc[0], n * prm.D); wb.adopt(na[0], n * prm.D);
+    etaa.adopt(nc[1], n * prm.Ncap); etab.adopt(na[1], n * prm.Ncap);
+    lla.adopt(nc[2], n); llb.adopt(na[2], n);
+    w = wa.p; w_alt = wb.p; eta = etaa.p; eta_alt = etab.p; ll = lla.p; ll_alt = llb.p;
+    ss_release();            // per-particle subsampled-MH state is sized by the particle count
   }
   int device_buffer(int which, void **p, int64_t *bytes) override {
     if (which == 1) { *p = w; *bytes = (int64_t)wa.bytes(); return VK_OK; }

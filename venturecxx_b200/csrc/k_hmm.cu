@@ -18,6 +18,7 @@
 #include <utility>
 #include "sp_math.cuh"
 #include "lse_finish.cuh"
+#include "weights.cuh"
 
 namespace vk {
 
@@ -58,7 +59,8 @@ __global__ void __launch_bounds__(256)
 hmm_step_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, int t /*0-based*/,
                 double *__restrict__ lw, double *__restrict__ incr, HMMTables tb, const double *__restrict__ tables,
                 int symbol /*1-based*/, int64_t P, int64_t p_base, uint64_t seed, uint32_t step,
-                int accumulate_incr, double *__restrict__ red, unsigned int *__restrict__ counter, int write_hist) {
+                int accumulate_incr, double *__restrict__ red, unsigned int *__restrict__ counter, int write_hist,
+                const P2PXchg xchg) {
   extern __shared__ double sh[];
   const int n_tr = tb.n_rows * tb.S + 2 * tb.n_rows;
   double *cdf = sh, *denom = cdf + tb.n_rows * tb.S, *last_pos = denom + tb.n_rows, *lw_emit = last_pos + tb.n_rows;
@@ -115,8 +117,9 @@ hmm_step_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad,
     }
   }
   // the filter resamples right after this step: reduce (max, min, NaN flag) of the weights just written so
-  // that vk_resample / vk_p2p_resample can skip their own read pass (lse_finish.cuh)
-  lse_minmax_finish(mx, mn, nanf, red, counter);
+  // that vk_resample / vk_p2p_resample can skip their own read pass (lse_finish.cuh); when the particle set
+  // is sharded over peer GPUs the last block also runs exchange 0 of that resample (xchg.tab != nullptr)
+  lse_minmax_finish(mx, mn, nanf, red, counter, xchg);
 }
 
 // likelihood_weight: resimulate states 2..t from the prior, lw := sum_t log E
@@ -411,18 +414,22 @@ struct HMMModel : Model {
       return;
     }
     flush_hist();
-    bool first = true;
+    bool first = true, x0 = false;
     for (; T < n; ++T) {
       uint32_t step = h->next_step();
       const bool last = T == n - 1;
+      P2PXchg xchg;
+      xchg.tab = nullptr;
+      if (last) x0 = p2p_begin_exchange(h, 0, &xchg);      // sharded particle set: exchange 0 rides in this kernel's tail
       hmm_step_kernel<<<step_grid(), 256, smem_step, h->stream>>>(cur, hist, Tpad, T, h->lw.p, incr_dev, tb, step_tables.p,
                                                              symbols_host[T], h->P, h->p_base, h->seed, step,
-                                                             first ? 0 : 1, h->red.p, h->counters.p, last ? 0 : 1);
+                                                             first ? 0 : 1, h->red.p, h->counters.p, last ? 0 : 1, xchg);
       first = false;
     }
     hist_pending = true;
     VK_CUDA(cudaGetLastError());
     h->lw_minmax_fresh = true;     // red[0..2] describe the weights as they are now
+    h->lw_x0_done = x0;            // ... those of ALL ranks
   }
   void run_prior(bool write_lw) {
     T = (int)symbols_host.size();
@@ -496,11 +503,20 @@ struct HMMModel : Model {
     flush_hist();
     hmm_write_kernel<<<grid(), 256, 0, h->stream>>>(hist, cur, Tpad, (int)site, site == T - 1, h->P, in_dev);
   }
-  std::vector<StateArray> state_arrays() override {
+  std::vector<StateArray> state_arrays(bool) override {
     flush_hist();   // generic consumers (pack/unpack, peer-memory and small-P gathers) see complete rows
+    return state_arrays_peek();
+  }
+  std::vector<StateArray> state_arrays_peek() override {
     StateArray a{(void **)&cur, (void **)&cur_alt, 0, 1, 4};
     StateArray b{(void **)&hist, (void **)&hist_alt, (size_t)Tpad, 0, 0};
     return {a, b};
+  }
+  void resized(int64_t n_new, const std::vector<void *> &nc, const std::vector<void *> &na) override {
+    cura.adopt(nc[0], (size_t)n_new); curb.adopt(na[0], (size_t)n_new);
+    hista.adopt(nc[1], (size_t)n_new * Tpad); histb.adopt(na[1], (size_t)n_new * Tpad);
+    cur = cura.p; cur_alt = curb.p; hist = hista.p; hist_alt = histb.p;
+    VK_CUDA(cudaMemsetAsync(hist_alt, 0, histb.bytes(), h->stream));
   }
   std::vector<StateArray> state_arrays_patched(int patch[3]) override {
     patch[0] = -1;

@@ -609,10 +609,14 @@ struct LDAModel : Model {
     VK_REQUIRE(site >= 0 && site < 2 + n_prop, VK_EINVAL, "lda: site out of range");
     lda_write_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(rows, L, site, h->P, in_dev);
   }
-  std::vector<StateArray> state_arrays() override {
-    if (!rowsb.p) { rowsb.alloc(rowsa.n); rows_alt = rowsb.p; }
+  std::vector<StateArray> state_arrays(bool alloc_alt) override {
+    if (alloc_alt && !rowsb.p) { rowsb.alloc(rowsa.n); rows_alt = rowsb.p; }
     StateArray a{(void **)&rows, (void **)&rows_alt, L.row_bytes, 0, 0};
     return {a};
+  }
+  void resized(int64_t n_new, const std::vector<void *> &nc, const std::vector<void *> &na) override {
+    rowsa.adopt(nc[0], (size_t)n_new * L.row_bytes); rowsb.adopt(na[0], (size_t)n_new * L.row_bytes);
+    rows = rowsa.p; rows_alt = rowsb.p;
   }
   int device_buffer(int which, void **p, int64_t *bytes) override {
     if (which == 1) { *p = rows; *bytes = (int64_t)rowsa.bytes(); return VK_OK; }

@@ -175,10 +175,14 @@ struct NormalNormalModel : Model {
     VK_REQUIRE(site == 0, VK_EINVAL, "normal-normal: site 0 (x) is the only site");
     VK_CUDA(cudaMemcpyAsync(x, in_dev, (size_t)h->P * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
   }
-  std::vector<StateArray> state_arrays() override {
+  std::vector<StateArray> state_arrays(bool) override {
     StateArray a;
     a.cur = (void **)&x; a.alt = (void **)&x_alt; a.row_bytes = 0; a.n_rows = 1; a.elem_bytes = 8;
     return {a};
+  }
+  void resized(int64_t n_new, const std::vector<void *> &nc, const std::vector<void *> &na) override {
+    xa.adopt(nc[0], (size_t)n_new); xb.adopt(na[0], (size_t)n_new);
+    x = xa.p; x_alt = xb.p;
   }
   int device_buffer(int which, void **p, int64_t *bytes) override {
     if (which == 1) { *p = x; *bytes = (int64_t)h->P * 8; return VK_OK; }

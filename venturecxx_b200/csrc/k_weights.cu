@@ -24,9 +24,9 @@ namespace vk {
 
 // red layout (doubles): [0]=max [1]=min [2]=nan flag [3]=sum exp [4]=lse
 // [8 ..] per-block partials (3 per block)
-__global__ void __launch_bounds__(256)
-lse_pass1_kernel(const double *__restrict__ a, int64_t n, double *red, unsigned int *counter) {
-  double mx = -INFINITY, mn = INFINITY, nanf = 0.0;
+__device__ __forceinline__ void lse_pass1_body(const double *__restrict__ a, int64_t n, double &mx, double &mn,
+                                               double &nanf) {
+  mx = -INFINITY; mn = INFINITY; nanf = 0.0;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
   if ((((uintptr_t)a) & 15) == 0) {      // 16-byte loads, four in flight per thread
     const double2 *a2 = reinterpret_cast<const double2 *>(a);
@@ -48,7 +48,19 @@ lse_pass1_kernel(const double *__restrict__ a, int64_t n, double *red, unsigned 
       else { mx = fmax(mx, v); mn = fmin(mn, v); }
     }
   }
+}
+__global__ void __launch_bounds__(256)
+lse_pass1_kernel(const double *__restrict__ a, int64_t n, double *red, unsigned int *counter) {
+  double mx, mn, nanf;
+  lse_pass1_body(a, n, mx, mn, nanf);
   lse_minmax_finish(mx, mn, nanf, red, counter);
+}
+// the same pass for a particle set sharded over peer GPUs: the last block runs exchange 0 (p2p_common.cuh)
+__global__ void __launch_bounds__(256)
+lse_pass1_xchg_kernel(const double *__restrict__ a, int64_t n, double *red, unsigned int *counter, P2PXchg xchg) {
+  double mx, mn, nanf;
+  lse_pass1_body(a, n, mx, mn, nanf);
+  lse_minmax_finish(mx, mn, nanf, red, counter, xchg);
 }
 
 // sum exp(a - m) with per-thread accumulation, block tree, last-block finish.
@@ -111,9 +123,11 @@ __global__ void normalized_probs_kernel(const double *__restrict__ a, int64_t n,
 
 // ---- fixed-point weights ---------------------------------------------------
 // q_i = rint(exp(lw_i - m) * 2^S); NaN or -inf -> 0; all -inf (m = -inf) -> 1
-// for everybody (normalizeList's "equally impossible").
+// for everybody (normalizeList's "equally impossible"); m = +inf -> 1 for the +inf entries, 0 for the rest
+// (the mass is never 0 for a non-empty particle set, so every child gets an ancestor).
 __device__ __forceinline__ uint64_t fixed_weight(double lw, double m, double scale) {
   if (!(m > -INFINITY)) return 1ull;
+  if (m == INFINITY) return lw == INFINITY ? 1ull : 0ull;
   double d = lw - m;
   if (!(d == d)) return 0ull;
   return __double2ull_rn(exp(d) * scale);
@@ -340,10 +354,12 @@ void build_fixed_cdf(vk_particles *h, const double *red_or_null, double m, int f
   VK_CUDA(cudaGetLastError());
 }
 
-int gather_state(vk_particles *h, const int32_t *anc_dev, int64_t n_new, double *lw_out, double log_n_new) {
+int gather_state(vk_particles *h, const int32_t *anc_dev, int64_t n_new, double *lw_out, double log_n_new,
+                 std::vector<StateArray> *explicit_arrs) {
   cudaStream_t st = h->stream;
-  if (int done = h->model->gather(anc_dev, n_new, lw_out, h->red.p, log_n_new)) return done;
-  std::vector<StateArray> arrs = h->model->state_arrays();
+  if (!explicit_arrs)
+    if (int done = h->model->gather(anc_dev, n_new, lw_out, h->red.p, log_n_new)) return done;
+  std::vector<StateArray> arrs = explicit_arrs ? *explicit_arrs : h->model->state_arrays();
   for (auto &a : arrs) {
     if (a.elem_bytes == 0) {
       if (a.row_bytes % 16 == 0) {
@@ -417,9 +433,9 @@ __device__ __forceinline__ uint64_t systematic_U0(const double *uniforms, uint64
 }
 
 // pass A': per-tile totals of the fixed-point weights AND of exp(lw - m) (for the LSE)
-__global__ void __launch_bounds__(SCAN_THREADS)
-fixed_tile_sums_exp_kernel(const double *__restrict__ lw, int64_t n, const double *__restrict__ red,
-                           double scale, uint64_t *tile_sums, double *tile_exp) {
+__device__ __forceinline__ void
+fixed_tile_sums_exp_body(const double *__restrict__ lw, int64_t n, const double *__restrict__ red,
+                         double scale, uint64_t *tile_sums, double *tile_exp) {
   __shared__ uint64_t sh[32];
   __shared__ double shd[33];
   const double m = red[0];
@@ -432,6 +448,7 @@ fixed_tile_sums_exp_kernel(const double *__restrict__ lw, int64_t n, const doubl
     if (i < n) {
       double v = lw[i];
       if (!(m > -INFINITY)) s += 1ull;
+      else if (m == INFINITY) s += v == INFINITY ? 1ull : 0ull;
       else {
         double d = v - m;
         if (d == d) { double e = exp(d); s += __double2ull_rn(e * scale); se += e; }
@@ -450,6 +467,11 @@ fixed_tile_sums_exp_kernel(const double *__restrict__ lw, int64_t n, const doubl
     if (lane == 0) { tile_sums[blockIdx.x] = s; tile_exp[blockIdx.x] = se; }
   }
 }
+__global__ void __launch_bounds__(SCAN_THREADS)
+fixed_tile_sums_exp_kernel(const double *__restrict__ lw, int64_t n, const double *__restrict__ red,
+                           double scale, uint64_t *tile_sums, double *tile_exp) {
+  fixed_tile_sums_exp_body(lw, n, red, scale, tile_sums, tile_exp);
+}
 
 // pass B': scan of tile totals (as scan_tile_sums_kernel) + LSE from the tile exp sums
 // (fixed order) with the edge cases of utils.py:77-91 -> red[3], red[4]
@@ -461,21 +483,22 @@ __device__ __forceinline__ void scan_tile_sums_lse_body(uint64_t *tile_sums, con
   if (threadIdx.x == 0) carry_sh = 0;
   __syncthreads();
   int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int nthr = (int)blockDim.x, nw = nthr >> 5;      // any block size that is a multiple of 32, <= 1024
   double se = 0.0;
-  for (int b0 = 0; b0 < n_tiles; b0 += 1024) {
+  for (int b0 = 0; b0 < n_tiles; b0 += nthr) {
     int b = b0 + threadIdx.x;
     uint64_t v = b < n_tiles ? tile_sums[b] : 0ull;
     if (b < n_tiles) se += tile_exp[b];
     uint64_t inc = warp_scan_incl(v, lane);
     if (lane == 31) sh[w] = inc;
     __syncthreads();
-    if (w == 0) { uint64_t t = sh[lane]; t = warp_scan_incl(t, lane); sh[lane] = t; }
+    if (w == 0) { uint64_t t = lane < nw ? sh[lane] : 0ull; t = warp_scan_incl(t, lane); sh[lane] = t; }
     __syncthreads();
     uint64_t woff = w > 0 ? sh[w - 1] : 0ull;
     uint64_t carry = carry_sh;
     if (b < n_tiles) tile_sums[b] = carry + woff + inc - v;
     __syncthreads();
-    if (threadIdx.x == 1023) carry_sh = carry + woff + inc;
+    if (threadIdx.x == nthr - 1) carry_sh = carry + woff + inc;
     __syncthreads();
   }
   se = block_sum(se, shd);
@@ -626,6 +649,7 @@ resample_small_kernel(double *__restrict__ lw, int P, int n_new, int mode, int f
     q[j] = 0;
     if (i < P) {
       if (!(m > -INFINITY)) q[j] = 1ull;
+      else if (m == INFINITY) q[j] = v[j] == INFINITY ? 1ull : 0ull;
       else { double d = v[j] - m; if (d == d) { double e = exp(d); q[j] = __double2ull_rn(e * scale); se += e; } }
     }
     s += q[j];
@@ -705,9 +729,11 @@ resample_small_kernel(double *__restrict__ lw, int P, int n_new, int mode, int f
   }
 }
 
-static bool resample_small(vk_particles *h, int64_t n_new, int mode, const double *uniforms_dev, uint32_t step) {
+static bool resample_small(vk_particles *h, int64_t n_new, int mode, const double *uniforms_dev, uint32_t step,
+                           bool resize) {
   if (h->P > SMALL_P_MAX || n_new > SMALL_P_MAX) return false;
-  std::vector<StateArray> arrs = h->model->state_arrays();
+  // resize: state_arrays(false) reports the fresh n_new-sized buffers the caller installed as back buffers
+  std::vector<StateArray> arrs = resize ? h->model->state_arrays(false) : h->model->state_arrays();
   if (arrs.size() > (size_t)SMALL_MAX_ARRAYS) return false;
   SmallArrays sa; sa.n = (int)arrs.size();
   for (int a = 0; a < sa.n; ++a) {
@@ -719,45 +745,99 @@ static bool resample_small(vk_particles *h, int64_t n_new, int mode, const doubl
   resample_small_kernel<<<1, SMALL_THREADS, 0, h->stream>>>(h->lw.p, (int)h->P, (int)n_new, mode, frac_bits_for(h->P), h->seed,
                                                    step, uniforms_dev, h->anc.p, h->red.p, sa);
   VK_CUDA(cudaGetLastError());
+  h->lw_minmax_fresh = false;
   for (auto &a : arrs) { void *t = *a.cur; *a.cur = *a.alt; *a.alt = t; }
   return true;
 }
 
+// exact-size replacement of a per-particle buffer, keeping the first min(old, new) elements
+template <typename T>
+static void resize_keep(DevBuf<T> &b, size_t n_new, cudaStream_t st) {
+  if (b.n == n_new) return;
+  DevBuf<T> fresh;
+  fresh.alloc(n_new);
+  const size_t keep = b.n < n_new ? b.n : n_new;
+  if (keep && b.p) VK_CUDA(cudaMemcpyAsync(fresh.p, b.p, keep * sizeof(T), cudaMemcpyDeviceToDevice, st));
+  VK_CUDA(cudaStreamSynchronize(st));
+  b.swap(fresh);
+}
+static size_t state_array_bytes(const StateArray &a, int64_t n) {
+  return a.elem_bytes ? (size_t)n * a.n_rows * a.elem_bytes : (size_t)n * a.row_bytes;
+}
+
 // Whole single-GPU resample: max -> fixed-point tile sums (+ LSE) -> ancestors -> gather -> even weights.
+// n_new != P (trace_set.py:202-219: `(resample 1000)` on a single-particle set is how the reference's
+// programs grow the particle set, benchmarks/Makefile:6-9): the children are gathered into fresh buffers
+// of n_new particles which the model then adopts (Model::resized); every per-particle array of the handle
+// is re-sized and h->P becomes n_new.
 void resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms_dev) {
-  VK_REQUIRE(n_new == h->P, VK_EUNSUPPORTED, "resample: n_new must equal the particle count in this version");
+  VK_REQUIRE(n_new >= 1 && n_new <= ((int64_t)1 << 30), VK_EINVAL, "resample: n_new must be in [1, 2^30]");
   VK_REQUIRE(mode == VK_RESAMPLE_MULTINOMIAL || mode == VK_RESAMPLE_SYSTEMATIC, VK_EINVAL, "resample: bad mode");
   cudaStream_t st = h->stream;
-  int64_t P = h->P;
-  uint32_t step = h->next_step();
-  if (resample_small(h, n_new, mode, uniforms_dev, step)) { h->model->after_resample(); return; }
-  int S = frac_bits_for(P);
-  double scale = ldexp(1.0, S);
-  int n_tiles = (int)((P + SCAN_TILE - 1) / SCAN_TILE);
-  if (h->red_u.n < (size_t)n_tiles + 1) h->red_u.alloc((size_t)n_tiles + 1);
-  if (h->tile_exp.n < (size_t)n_tiles) h->tile_exp.alloc((size_t)n_tiles);
-  // pass 1 (max / min / NaN flag) is skipped when the kernel that wrote the weights already reduced them
-  if (!h->lw_minmax_fresh)
-    lse_pass1_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p);
-  h->lw_minmax_fresh = false;
-  fixed_tile_sums_exp_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p);
-  const bool raw_tiles = mode == VK_RESAMPLE_SYSTEMATIC && n_tiles <= 1024;   // each CTA reads all tile totals
-  if (!raw_tiles) scan_tile_sums_lse_kernel<<<1, 1024, 0, st>>>(h->red_u.p, h->tile_exp.p, n_tiles, P, h->red.p);
-  if (raw_tiles) {
-    systematic_offspring_kernel<true><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p,
-                                                                        n_tiles, n_new, h->seed, step, uniforms_dev, h->anc.p);
-  } else if (mode == VK_RESAMPLE_SYSTEMATIC) {
-    systematic_offspring_kernel<false><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p,
-                                                                         n_tiles, n_new, h->seed, step, uniforms_dev, h->anc.p);
-  } else {
-    fixed_cdf_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, 0.0, h->red.p, scale, h->red_u.p, h->cdf.p);
-    launch_ancestor_search_single(h, n_new, mode, step, uniforms_dev, grid_for(n_new, 256, h->sm_count, 8));
+  const int64_t P = h->P;
+  const bool resize = n_new != P;
+  std::vector<void *> fresh_cur, fresh_alt;
+  std::vector<StateArray> rs_arrs;
+  if (resize) {
+    VK_REQUIRE(!h->p2p || !p2p_is_open(h), VK_EUNSUPPORTED, "resample: a peer-sharded particle set cannot change its size");
+    rs_arrs = h->model->state_arrays(false);
+    const int64_t cap = n_new > P ? n_new : P;
+    if ((int64_t)h->lw.n < cap) resize_keep(h->lw, (size_t)cap, st);
+    if ((int64_t)h->anc.n < n_new) h->anc.alloc((size_t)n_new);
+    try {
+      for (auto &a : rs_arrs) {                 // children land in fresh buffers of n_new particles
+        void *c = nullptr, *b = nullptr;
+        VK_CUDA(cudaMalloc(&c, state_array_bytes(a, n_new))); fresh_cur.push_back(c);
+        VK_CUDA(cudaMalloc(&b, state_array_bytes(a, n_new))); fresh_alt.push_back(b);
+      }
+    } catch (...) {
+      for (void *q : fresh_cur) cudaFree(q);
+      for (void *q : fresh_alt) cudaFree(q);
+      throw;
+    }
+    for (size_t i = 0; i < rs_arrs.size(); ++i) *rs_arrs[i].alt = fresh_cur[i];   // the old back buffer stays owned by the model
   }
-  VK_CUDA(cudaGetLastError());
-  const double log_n_new = log((double)n_new);
-  if (!(gather_state(h, h->anc.p, n_new, h->lw.p, log_n_new) & 2))
-    fill_kernel<<<grid_for(n_new, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, n_new, h->red.p, log_n_new);
-  VK_CUDA(cudaGetLastError());
+  uint32_t step = h->next_step();
+  bool done = resample_small(h, n_new, mode, uniforms_dev, step, resize);
+  if (!done) {
+    int S = frac_bits_for(P);
+    double scale = ldexp(1.0, S);
+    int n_tiles = (int)((P + SCAN_TILE - 1) / SCAN_TILE);
+    if (h->red_u.n < (size_t)n_tiles + 1) h->red_u.alloc((size_t)n_tiles + 1);
+    if (h->tile_exp.n < (size_t)n_tiles) h->tile_exp.alloc((size_t)n_tiles);
+    // pass 1 (max / min / NaN flag) is skipped when the kernel that wrote the weights already reduced them
+    if (!h->lw_minmax_fresh)
+      lse_pass1_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p);
+    h->lw_minmax_fresh = false;
+    fixed_tile_sums_exp_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p);
+    const bool raw_tiles = mode == VK_RESAMPLE_SYSTEMATIC && n_tiles <= 1024;   // each CTA reads all tile totals
+    if (!raw_tiles) scan_tile_sums_lse_kernel<<<1, 1024, 0, st>>>(h->red_u.p, h->tile_exp.p, n_tiles, P, h->red.p);
+    if (raw_tiles) {
+      systematic_offspring_kernel<true><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p,
+                                                                          n_tiles, n_new, h->seed, step, uniforms_dev, h->anc.p);
+    } else if (mode == VK_RESAMPLE_SYSTEMATIC) {
+      systematic_offspring_kernel<false><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p,
+                                                                           n_tiles, n_new, h->seed, step, uniforms_dev, h->anc.p);
+    } else {
+      fixed_cdf_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, 0.0, h->red.p, scale, h->red_u.p, h->cdf.p);
+      launch_ancestor_search_single(h, n_new, mode, step, uniforms_dev, grid_for(n_new, 256, h->sm_count, 8));
+    }
+    VK_CUDA(cudaGetLastError());
+    const double log_n_new = log((double)n_new);
+    if (!(gather_state(h, h->anc.p, n_new, h->lw.p, log_n_new, resize ? &rs_arrs : nullptr) & 2))
+      fill_kernel<<<grid_for(n_new, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, n_new, h->red.p, log_n_new);
+    VK_CUDA(cudaGetLastError());
+  }
+  if (resize) {
+    VK_CUDA(cudaStreamSynchronize(st));          // the gathers read the old buffers, which the model frees now
+    h->model->resized(n_new, fresh_cur, fresh_alt);
+    h->P = n_new;
+    resize_keep(h->lw, (size_t)n_new, st);
+    h->scratch_d.alloc((size_t)n_new);
+    h->cdf.alloc((size_t)n_new);
+    if ((int64_t)h->anc.n != n_new) resize_keep(h->anc, (size_t)n_new, st);
+    if (h->acc_d.p) h->acc_d.alloc((size_t)n_new);
+  }
   h->model->after_resample();
 }
 

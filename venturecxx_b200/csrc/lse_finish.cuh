@@ -6,14 +6,17 @@
 // red layout (doubles): [0]=max [1]=min [2]=nan flag [3]=sum exp [4]=lse; [8..] per-block partials (3 per block)
 #pragma once
 #include "vk_common.cuh"
+#include "p2p_common.cuh"
 
 namespace vk {
 
 static const int RED_PART = 8;
 
-// every thread of the block calls this with its partial (max, min, nan); block size <= 1024
+// every thread of the block calls this with its partial (max, min, nan); block size <= 1024.
+// xchg.tab != nullptr (particle set sharded over peer GPUs, p2p_common.cuh): the last block then runs
+// exchange 0 in its tail, so red[0..2] end up describing the weights of ALL ranks.
 __device__ __forceinline__ void lse_minmax_finish(double mx, double mn, double nanf, double *red,
-                                                  unsigned int *counter) {
+                                                  unsigned int *counter, const P2PXchg &xchg) {
   __shared__ double sh[3][32];
   __shared__ bool last;
   int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -57,7 +60,17 @@ __device__ __forceinline__ void lse_minmax_finish(double mx, double mn, double n
       mx = warp_max(mx); mn = -warp_max(-mn); nanf = warp_max(nanf);
       if (lane == 0) { red[0] = mx; red[1] = mn; red[2] = nanf; *counter = 0; }
     }
+    if (xchg.tab) {
+      __syncthreads();
+      if (w == 0) p2p_exchange_warp(xchg, red, nullptr, 0, 0);
+    }
   }
+}
+__device__ __forceinline__ void lse_minmax_finish(double mx, double mn, double nanf, double *red,
+                                                  unsigned int *counter) {
+  P2PXchg none;
+  none.tab = nullptr;
+  lse_minmax_finish(mx, mn, nanf, red, counter, none);
 }
 
 }  // namespace vk

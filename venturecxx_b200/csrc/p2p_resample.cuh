@@ -1,52 +1,45 @@
 // Global resampling across the GPUs of one NVSwitch node WITHOUT collectives or host round trips:
 // the ranks (one process per GPU) exchange three scalars through mailboxes in each other's memory and
 // move ancestor state with direct peer loads over NVLink.  Included at the end of k_weights.cu (it reuses
-// that file's tile-sum / scan / offspring machinery); namespace vk.
+// that file's tile-sum / scan / offspring machinery); namespace vk.  Mailbox protocol, failure policy and the
+// exchange itself: p2p_common.cuh.
 //
 // What it replaces: python/lib/engine/trace_set.py:202-235 (resample -> _resample_traces -> copy_trace)
 // when the particle set is sharded.  The NCCL formulation of the same step
 // (distributed.py sharded_resample: all_reduce(max), all_gather(mass), all_to_all(rows), three host
 // synchronisations) stays as the portable path and as this one's parity reference.
 //
-// Protocol of resample number q (every rank runs the same stream-ordered kernel sequence):
-//   A  lse_pass1                      local max / min / NaN flag
-//   X0 exchange(phase 0)              -> global max, min, NaN flag (every rank reduces the same 'world' values
-//                                        in rank order, so all ranks hold identical numbers)
-//   B  fixed_tile_sums_exp, scan      local fixed-point mass W_r and sum exp(lw - gmax), against the GLOBAL max
-//   X1 exchange(phase 1)              -> offset_r = sum_{r'<r} W_r', W = sum W_r, LSE, every rank's live-buffer index
-//   C  offspring (systematic) or      each rank finds the children whose integer threshold falls in ITS mass
-//      cdf + search (multinomial)     interval and stores the GLOBAL ancestor index straight into the anc array of
-//                                     the rank that owns the child slot (4-byte peer stores over NVLink)
-//   X2 exchange(phase 2)              barrier: every child slot everywhere has its ancestor
-//   D  gather                         slot s pulls its ancestor's rows from the owning rank's LIVE buffers (peer
-//                                     loads) into the local back buffers; buffers swap; lw := LSE - log P_total
+// Resample number q on every rank is the SAME FOUR LAUNCHES as on one GPU; the exchanges ride in kernel tails:
+//   A  the kernel that wrote the weights        local max / min / NaN flag; its last block runs EXCHANGE 0
+//      (hmm_step_kernel) or lse_pass1           -> global max, min, NaN flag (every rank reduces the same
+//                                                  'world' values in rank order: identical numbers everywhere)
+//   B  p2p_tile_sums_kernel                     local fixed-point mass W_r and sum exp(lw - gmax) against the
+//                                               GLOBAL max; its last block scans the tile totals and runs
+//                                               EXCHANGE 1 -> offset_r = sum_{r'<r} W_r', W, LSE, every rank's
+//                                               live-buffer index
+//   C  offspring (systematic) or                each rank finds the children whose integer threshold falls in
+//      cdf + search (multinomial)               ITS mass interval and stores the GLOBAL ancestor index straight
+//                                               into the ancestor array of the rank that owns the child slot
+//                                               (4-byte peer stores over NVLink)
+//   D  gather                                   slot s waits until its ancestor has ARRIVED (the array holds -1
+//                                               until a peer stores into it -- no barrier between C and D), then
+//                                               pulls the ancestor's rows from the owning rank's LIVE buffers
+//                                               (peer loads) into the local back buffers; buffers swap;
+//                                               lw := LSE - log P_total
 // Buffer safety: a rank's live buffers are read by peers only during D of resample q; they are next written
-// by D of resample q+1, which that rank reaches only after X0..X2 of q+1, i.e. after every peer has finished D
-// of q (stream order on the peer).  Mailbox slots are double-buffered on the parity of q on top of that.
+// by D of resample q+1, which that rank reaches only after exchange 1 of q+1, i.e. after every peer has
+// finished D of q (stream order on the peer).  The ancestor array is double-buffered on the parity of q: D of
+// q resets the OTHER half to -1 (its readers finished in q-1; its next writers, C of q+1, start only after
+// this rank has posted exchange 1 of q+1).  Mailbox slots are double-buffered on the parity of the phase's
+// own exchange counter.
 //
 // Integer thresholds on a fixed-point CDF make the ancestors independent of the number of GPUs: the result
-// is bit-identical to vk_resample on one GPU holding all particles (tools/check_multi_gpu.py).
+// is bit-identical to vk_resample on one GPU holding all particles (tools/check_multi_gpu.py,
+// tests/test_gpu_peer_memory.py).
 #pragma once
+#include <stdlib.h>
+#include "p2p_common.cuh"
 
-static const int P2P_MAX_WORLD = 16;
-static const int P2P_MAX_ARRAYS = 4;
-static const int P2P_PHASES = 3;
-
-struct P2PMail {                       // 32 bytes, written by ONE sender into its slot of a peer's mailbox
-  unsigned long long seq;              // written last (after a system fence): 1 + resample number
-  double a, b;
-  unsigned long long c;
-};
-struct P2PParams {                     // device-resident results of the exchanges
-  unsigned long long offset, total;    // this rank's mass offset, global mass
-  int cur_idx[P2P_MAX_WORLD];          // which of its two physical buffers is each rank's live one
-  int err;                             // 1 = a wait timed out (peer never arrived)
-};
-struct P2PTables {                     // device-resident peer pointers
-  P2PMail *mail[P2P_MAX_WORLD];        // [parity][phase][sender] inside
-  int32_t *anc[P2P_MAX_WORLD];
-  unsigned char *buf[P2P_MAX_ARRAYS][P2P_MAX_WORLD][2];
-};
 struct P2PArrays {                     // by-value kernel argument of the gather
   int n;
   unsigned char *alt[P2P_MAX_ARRAYS];
@@ -57,107 +50,50 @@ struct P2PArrays {                     // by-value kernel argument of the gather
                                             // array patch_array := low byte of the ancestor's element of
                                             // the 4-byte particle-minor array patch_src (patch_array < 0: none)
   double *lw; const double *red; double log_p_total;   // evened-out weights written by the same kernel
+  int32_t *anc_other;                  // the ancestor half of the previous resample: reset to -1 here
+  long long timeout_ns;
+  volatile int *err_host;
 };
 struct P2P {
   int world = 0, rank = 0, n_arrays = 0;
-  bool opened = false;
-  unsigned long long seq = 0;
+  bool opened = false, replicated = false;
+  unsigned long long n_resamples = 0;
+  unsigned long long phase_seq[P2P_PHASES] = {0, 0};
+  unsigned long long ss_seq = 0;                 // exchanges of the subsampled-MH mailbox so far
+  long long ss_stride = 0;                       // doubles per (parity, sender) slot of the ss mailbox
+  long long ss_pcap = 1;                         // sequence words per (parity, sender): one per particle
+  long long timeout_ns = 20000000000ll;
   DevBuf<P2PMail> mail;
-  DevBuf<int32_t> anc_g;
+  DevBuf<int32_t> anc_g;                         // [2][P]
   DevBuf<P2PTables> tab;
   DevBuf<P2PParams> par;
+  DevBuf<double> ss_mail;                        // [2][P2P_MAX_WORLD][ss_stride]
+  DevBuf<unsigned long long> ss_seq_words;       // [2][P2P_MAX_WORLD]
+  int *err_host = nullptr, *err_host_dev = nullptr;   // mapped pinned word and its device alias
   void *own_buf[P2P_MAX_ARRAYS][2];
   std::vector<void *> imported;
 };
+static const int P2P_FIXED_HANDLES = 4;          // mailbox, ancestor array, ss mailbox, ss sequence words
 
-__device__ __forceinline__ int p2p_mail_index(int parity, int phase, int sender) {
-  return (parity * P2P_PHASES + phase) * P2P_MAX_WORLD + sender;
-}
-
-// One warp; lane r talks to rank r.  Phase 0 sends (max, min, nan) from red[0..2]; phase 1 sends
-// (sum exp, live-buffer index, mass); phase 2 is a pure barrier.  Results: phase 0 -> red[0..2]; phase 1 ->
-// par (offset, total, cur_idx) and red[3] (global sum exp), red[4] (LSE, utils.py:77-91 edge cases).
-__device__ __forceinline__ void
-p2p_exchange_warp(P2PTables *tab, P2PParams *par, double *red, const uint64_t *tile_sums, int n_tiles,
-                  int world, int rank, int phase, unsigned long long seq, int my_cur_idx, long long n_total,
-                  long long spin_limit) {
-  const int lane = threadIdx.x;
-  const int parity = (int)(seq & 1ull);
-  double a = 0.0, b = 0.0;
-  unsigned long long c = 0ull;
-  if (phase == 0) { a = red[0]; b = red[1]; c = red[2] != 0.0 ? 1ull : 0ull; }
-  else if (phase == 1) { a = red[3]; b = (double)my_cur_idx; c = tile_sums[n_tiles]; }
-  if (lane < world) {
-    volatile P2PMail *dst = tab->mail[lane] + p2p_mail_index(parity, phase, rank);
-    dst->a = a; dst->b = b; dst->c = c;
-    __threadfence_system();
-    dst->seq = seq;
-  }
-  double ra = 0.0, rb = 0.0;
-  unsigned long long rc = 0ull;
-  int bad = 0;
-  if (lane < world) {
-    volatile P2PMail *src = tab->mail[rank] + p2p_mail_index(parity, phase, lane);
-    long long t0 = clock64();
-    while (src->seq != seq) {
-      if (clock64() - t0 > spin_limit) { bad = 1; break; }
-      __nanosleep(64);
-    }
-    __threadfence_system();
-    ra = src->a; rb = src->b; rc = src->c;
-  }
-  bad = __any_sync(0xffffffffu, bad);
-  if (bad && lane == 0) par->err = 1;
-  if (phase == 0) {
-    double mx = lane < world ? ra : -INFINITY, mn = lane < world ? rb : INFINITY;
-    unsigned long long nf = lane < world ? rc : 0ull;
-    for (int o = 16; o > 0; o >>= 1) {
-      mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-      mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-      nf |= __shfl_xor_sync(0xffffffffu, nf, o);
-    }
-    if (lane == 0) { red[0] = mx; red[1] = mn; red[2] = nf ? 1.0 : 0.0; }
-  } else if (phase == 1) {
-    // rank-ordered sums (lane 0 walks the ranks) so that every GPU computes identical values
-    unsigned long long off = 0ull, tot = 0ull;
-    double se = 0.0;
-    for (int r = 0; r < world; ++r) {
-      unsigned long long m_r = __shfl_sync(0xffffffffu, rc, r);
-      double se_r = __shfl_sync(0xffffffffu, ra, r);
-      if (r < rank) off += m_r;
-      tot += m_r;
-      se += se_r;
-    }
-    if (lane < world) par->cur_idx[lane] = (int)rb;
-    if (lane == 0) {
-      par->offset = off; par->total = tot;
-      double m = red[0], mn = red[1], nanf = red[2], lse;
-      if (n_total == 0) lse = -INFINITY;
-      else if (nanf != 0.0) lse = NAN;
-      else if (isinf(m) && mn != -m) lse = m;
-      else if (isinf(m)) lse = NAN;
-      else lse = m + log(se);
-      red[3] = se; red[4] = lse;
-    }
-  }
-}
-
-__global__ void __launch_bounds__(32)
-p2p_exchange_kernel(P2PTables *tab, P2PParams *par, double *red, const uint64_t *tile_sums, int n_tiles,
-                    int world, int rank, int phase, unsigned long long seq, int my_cur_idx, long long n_total,
-                    long long spin_limit) {
-  p2p_exchange_warp(tab, par, red, tile_sums, n_tiles, world, rank, phase, seq, my_cur_idx, n_total, spin_limit);
-}
-// scan of this rank's tile totals + local sum exp (scan_tile_sums_lse_kernel's work), then exchange 1 by
-// warp 0 of the same single CTA: one launch instead of two on the latency-bound path
-__global__ void __launch_bounds__(1024)
-p2p_scan_exchange1_kernel(P2PTables *tab, P2PParams *par, double *red, uint64_t *tile_sums, const double *tile_exp,
-                          int n_tiles, int64_t n_local, int world, int rank, unsigned long long seq, int my_cur_idx,
-                          long long n_total, long long spin_limit) {
-  scan_tile_sums_lse_body(tile_sums, tile_exp, n_tiles, n_local, red);
+// Tile totals against the GLOBAL max (fixed_tile_sums_exp_kernel's work); the last block then scans the tile
+// totals, forms this rank's sum exp (scan_tile_sums_lse_body) and runs exchange 1 -- one launch, no single-CTA
+// kernel of its own.
+__global__ void __launch_bounds__(SCAN_THREADS)
+p2p_tile_sums_kernel(const double *__restrict__ lw, int64_t n, double *__restrict__ red, double scale,
+                     uint64_t *tile_sums, double *tile_exp, int n_tiles, unsigned int *counter, P2PXchg xchg) {
+  if (((volatile P2PParams *)xchg.par)->err) return;
+  fixed_tile_sums_exp_body(lw, n, red, scale, tile_sums, tile_exp);
+  __shared__ bool last;
+  __threadfence();
   __syncthreads();
-  if (threadIdx.x < 32)
-    p2p_exchange_warp(tab, par, red, tile_sums, n_tiles, world, rank, 1, seq, my_cur_idx, n_total, spin_limit);
+  if (threadIdx.x == 0) last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  scan_tile_sums_lse_body(tile_sums, tile_exp, n_tiles, n, red);
+  __syncthreads();
+  if (threadIdx.x == 0) *counter = 0;
+  if (threadIdx.x < 32) p2p_exchange_warp(xchg, red, tile_sums, n_tiles, 1);
 }
 
 // Step C, systematic: as systematic_offspring_kernel, against the GLOBAL mass: this rank's running sum starts at
@@ -166,8 +102,10 @@ p2p_scan_exchange1_kernel(P2PTables *tab, P2PParams *par, double *red, uint64_t 
 __global__ void __launch_bounds__(SCAN_THREADS)
 p2p_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__restrict__ red, double scale,
                      const uint64_t *__restrict__ tile_sums, const P2PParams *__restrict__ par,
-                     P2PTables *__restrict__ tab, int64_t n_total, int64_t p_base, uint64_t seed, uint32_t step) {
+                     P2PTables *__restrict__ tab, int anc_half, int64_t n_total, int64_t p_base, uint64_t seed,
+                     uint32_t step) {
   __shared__ uint64_t sh[32];
+  if (((const volatile P2PParams *)par)->err) return;
   const double m = red[0];
   const uint64_t W = par->total;
   const uint64_t U0 = systematic_U0(nullptr, seed, step);
@@ -192,16 +130,18 @@ p2p_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__r
   __syncthreads();
   if (s == 0) return;
   uint64_t run = par->offset + tile_sums[blockIdx.x] + (w > 0 ? sh[w - 1] : 0ull) + inc - s;
-  int64_t k_lo = first_child_at_least(run, W, n_total, U0);
+  const double ratio = (double)n_total / (double)W, u0f = (double)U0 * (1.0 / 4294967296.0);
+  int64_t k_lo = first_child_at_least(run, W, n_total, U0, ratio, u0f);
+  const int64_t half_off = (int64_t)anc_half * n;
 #pragma unroll
   for (int j = 0; j < SCAN_ITEMS; ++j) {
     if (q[j] == 0) continue;
     run += q[j];
-    int64_t k_hi = first_child_at_least(run, W, n_total, U0);
+    int64_t k_hi = first_child_at_least(run, W, n_total, U0, ratio, u0f);
     const int32_t g = (int32_t)(p_base + base + j);
     for (int64_t k = k_lo; k < k_hi; ++k) {
       int64_t d = k / n;
-      tab->anc[d][k - d * n] = g;
+      tab->anc[d][half_off + k - d * n] = g;
     }
     k_lo = k_hi;
   }
@@ -212,9 +152,12 @@ p2p_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__r
 // (a local binary search each -- no remote CDF reads), storing the global ancestor at the owner of slot k.
 __global__ void __launch_bounds__(256)
 p2p_multinomial_kernel(const uint64_t *__restrict__ cdf, int64_t n, const P2PParams *__restrict__ par,
-                       P2PTables *__restrict__ tab, int64_t n_total, int64_t p_base, uint64_t seed, uint32_t step) {
+                       P2PTables *__restrict__ tab, int anc_half, int64_t n_total, int64_t p_base, uint64_t seed,
+                       uint32_t step) {
+  if (((const volatile P2PParams *)par)->err) return;
   const uint64_t offset = par->offset, total = par->total;
   const uint64_t mass = cdf[n - 1];
+  const int64_t half_off = (int64_t)anc_half * n;
   for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n_total;
        k += (int64_t)gridDim.x * blockDim.x) {
     Stream r(seed, (uint64_t)k, step);
@@ -225,24 +168,46 @@ p2p_multinomial_kernel(const uint64_t *__restrict__ cdf, int64_t n, const P2PPar
     if (thr < offset || thr - offset >= mass) continue;
     int64_t i = upper_bound_u64(cdf, n, thr - offset);
     int64_t d = k / n;
-    tab->anc[d][k - d * n] = (int32_t)(p_base + i);
+    tab->anc[d][half_off + k - d * n] = (int32_t)(p_base + i);
   }
+}
+
+// the ancestor of child slot s, once a peer (or this rank) has stored it; -1 after a timeout
+__device__ __forceinline__ int64_t p2p_wait_ancestor(const int32_t *anc_g, int64_t s, P2PParams *par,
+                                                     long long timeout_ns, volatile int *err_host) {
+  const volatile int32_t *slot = anc_g + s;
+  int32_t g = *slot;
+  if (g >= 0) return g;
+  const unsigned long long t0 = p2p_now_ns();
+  int spins = 0;
+  while ((g = *slot) < 0) {
+    if ((++spins & 63) == 0) {
+      if (((volatile P2PParams *)par)->err) return -1;
+      if ((long long)(p2p_now_ns() - t0) > timeout_ns) { par->err = 1; *err_host = 1; __threadfence_system(); return -1; }
+    }
+    __nanosleep(100);
+  }
+  return g;
 }
 
 // Step D: slot s copies its ancestor's state from the owning rank's live buffers (NVLink peer loads; rows that
 // are multiples of 16 bytes move as uint4) into the local back buffers.
 __global__ void __launch_bounds__(256)
 p2p_gather_kernel(const int32_t *__restrict__ anc_g, int64_t n, const P2PTables *__restrict__ tab,
-                  const P2PParams *__restrict__ par, P2PArrays arrs) {
-  for (int a = 0; a < arrs.n; ++a) {
+                  P2PParams *__restrict__ par, P2PArrays arrs) {
+  const int64_t tid0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t t = tid0; t < n; t += stride) arrs.anc_other[t] = -1;
+  bool failed = ((volatile P2PParams *)par)->err != 0;
+  for (int a = 0; a < arrs.n && !failed; ++a) {
     if (arrs.elem_bytes[a] == 0) {
       const long long rb = arrs.row_bytes[a];
       if ((rb & 15) == 0) {
         const long long units = rb >> 4;
-        for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n * units;
-             t += (int64_t)gridDim.x * blockDim.x) {
+        for (int64_t t = tid0; t < n * units; t += stride) {
           int64_t s = t / units, u = t - s * units;
-          int64_t g = anc_g[s], d = g / n, i = g - d * n;
+          int64_t g = p2p_wait_ancestor(anc_g, s, par, arrs.timeout_ns, arrs.err_host);
+          if (g < 0) { failed = true; break; }
+          int64_t d = g / n, i = g - d * n;
           const uint4 *src = (const uint4 *)(tab->buf[a][d][par->cur_idx[d]] + i * rb);
           uint4 v = src[u];
           if (a == arrs.patch_array && u == (arrs.patch_byte >> 4)) {
@@ -257,20 +222,22 @@ p2p_gather_kernel(const int32_t *__restrict__ anc_g, int64_t n, const P2PTables 
           ((uint4 *)(arrs.alt[a] + s * rb))[u] = v;
         }
       } else {
-        for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n * rb;
-             t += (int64_t)gridDim.x * blockDim.x) {
+        for (int64_t t = tid0; t < n * rb; t += stride) {
           int64_t s = t / rb, u = t - s * rb;
-          int64_t g = anc_g[s], d = g / n, i = g - d * n;
+          int64_t g = p2p_wait_ancestor(anc_g, s, par, arrs.timeout_ns, arrs.err_host);
+          if (g < 0) { failed = true; break; }
+          int64_t d = g / n, i = g - d * n;
           arrs.alt[a][s * rb + u] = tab->buf[a][d][par->cur_idx[d]][i * rb + u];
         }
       }
     } else {
       const long long nr = arrs.n_rows[a];
       const int eb = arrs.elem_bytes[a];
-      for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n * nr;
-           t += (int64_t)gridDim.x * blockDim.x) {
+      for (int64_t t = tid0; t < n * nr; t += stride) {
         int64_t r = t / n, s = t - r * n;
-        int64_t g = anc_g[s], d = g / n, i = g - d * n;
+        int64_t g = p2p_wait_ancestor(anc_g, s, par, arrs.timeout_ns, arrs.err_host);
+        if (g < 0) { failed = true; break; }
+        int64_t d = g / n, i = g - d * n;
         const unsigned char *src = tab->buf[a][d][par->cur_idx[d]] + (r * n + i) * eb;
         unsigned char *dst = arrs.alt[a] + (r * n + s) * eb;
         if (eb == 8) *(uint64_t *)dst = *(const uint64_t *)src;
@@ -279,16 +246,24 @@ p2p_gather_kernel(const int32_t *__restrict__ anc_g, int64_t n, const P2PTables 
       }
     }
   }
-  const double even = arrs.red[4] - arrs.log_p_total;   // lw := LSE - log P_total (utils.py:152-157)
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x)
-    arrs.lw[t] = even;
+  // lw := LSE - log P_total (utils.py:152-157); a failed exchange poisons the weights instead
+  const double even = (failed || ((volatile P2PParams *)par)->err) ? NAN : arrs.red[4] - arrs.log_p_total;
+  for (int64_t t = tid0; t < n; t += stride) arrs.lw[t] = even;
 }
 
 // ---- host side -------------------------------------------------------------------------------------
 static P2P *p2p_of(vk_particles *h) { return (P2P *)h->p2p; }
 
-// handles_out: (2 + 2 * n_arrays) IPC handles of 64 bytes: mailbox, anc, then both physical buffers of every
-// state array in state_arrays() order.  Returns the count.
+// raised by host-synchronising entry points once the stream has drained
+void p2p_check_error(vk_particles *h) {
+  P2P *s = p2p_of(h);
+  if (s && s->err_host && *(volatile int *)s->err_host)
+    throw Error(VK_ECUDA, "peer-memory exchange timed out: a peer GPU never arrived (rank " + std::to_string(s->rank) +
+                              " of " + std::to_string(s->world) + "); the particle set of this handle is invalid");
+}
+
+// handles_out: (P2P_FIXED_HANDLES + 2 * n_arrays) IPC handles of 64 bytes: mailbox, ancestor array, ss mailbox,
+// ss sequence words, then both physical buffers of every state array in state_arrays() order.  Returns the count.
 int p2p_export(vk_particles *h, unsigned char *handles_out, int max_handles) {
   VK_REQUIRE(sizeof(cudaIpcMemHandle_t) == 64, VK_ECUDA, "unexpected cudaIpcMemHandle_t size");
   P2P *s = p2p_of(h);
@@ -297,24 +272,41 @@ int p2p_export(vk_particles *h, unsigned char *handles_out, int max_handles) {
   std::vector<StateArray> arrs = h->model->state_arrays();
   VK_REQUIRE((int)arrs.size() <= P2P_MAX_ARRAYS, VK_EUNSUPPORTED, "p2p: too many state arrays");
   s->n_arrays = (int)arrs.size();
-  int need = 2 + 2 * s->n_arrays;
+  int need = P2P_FIXED_HANDLES + 2 * s->n_arrays;
   VK_REQUIRE(max_handles >= need, VK_EINVAL, "p2p_export: handle buffer too small");
   VK_CUDA(cudaStreamSynchronize(h->stream));
   if (!s->mail.p) {
     s->mail.alloc((size_t)2 * P2P_PHASES * P2P_MAX_WORLD);
     VK_CUDA(cudaMemset(s->mail.p, 0, s->mail.bytes()));
-    s->anc_g.alloc((size_t)h->P);
+    s->anc_g.alloc((size_t)2 * h->P);
+    VK_CUDA(cudaMemset(s->anc_g.p, 0xFF, s->anc_g.bytes()));       // -1: nothing stored yet
     s->tab.alloc(1);
     s->par.alloc(1);
     VK_CUDA(cudaMemset(s->par.p, 0, sizeof(P2PParams)));
+    // subsampled MH exchanges (sum dllh, sum dllh^2) of P2P_SS_MAX_ROUNDS minibatches per particle
+    const bool ss = h->kind == VK_MODEL_BLR && h->P <= 4096;
+    s->ss_stride = ss ? (long long)P2P_SS_MAX_ROUNDS * h->P * 2 : 2;
+    s->ss_pcap = ss ? (long long)h->P : 1;
+    s->ss_mail.alloc((size_t)2 * P2P_MAX_WORLD * s->ss_stride);
+    s->ss_seq_words.alloc((size_t)2 * P2P_MAX_WORLD * s->ss_pcap);
+    VK_CUDA(cudaMemset(s->ss_seq_words.p, 0, s->ss_seq_words.bytes()));
+    VK_CUDA(cudaHostAlloc((void **)&s->err_host, sizeof(int), cudaHostAllocMapped));
+    *s->err_host = 0;
+    VK_CUDA(cudaHostGetDevicePointer((void **)&s->err_host_dev, s->err_host, 0));
+    if (const char *e = getenv("VK_P2P_TIMEOUT_S")) {
+      double sec = atof(e);
+      if (sec > 0.0) s->timeout_ns = (long long)(sec * 1e9);
+    }
   }
   cudaIpcMemHandle_t *out = (cudaIpcMemHandle_t *)handles_out;
   VK_CUDA(cudaIpcGetMemHandle(&out[0], s->mail.p));
   VK_CUDA(cudaIpcGetMemHandle(&out[1], s->anc_g.p));
+  VK_CUDA(cudaIpcGetMemHandle(&out[2], s->ss_mail.p));
+  VK_CUDA(cudaIpcGetMemHandle(&out[3], s->ss_seq_words.p));
   for (int a = 0; a < s->n_arrays; ++a) {
     s->own_buf[a][0] = *arrs[a].cur; s->own_buf[a][1] = *arrs[a].alt;
-    VK_CUDA(cudaIpcGetMemHandle(&out[2 + 2 * a], s->own_buf[a][0]));
-    VK_CUDA(cudaIpcGetMemHandle(&out[3 + 2 * a], s->own_buf[a][1]));
+    VK_CUDA(cudaIpcGetMemHandle(&out[P2P_FIXED_HANDLES + 2 * a], s->own_buf[a][0]));
+    VK_CUDA(cudaIpcGetMemHandle(&out[P2P_FIXED_HANDLES + 1 + 2 * a], s->own_buf[a][1]));
   }
   return need;
 }
@@ -324,17 +316,23 @@ void p2p_open(vk_particles *h, int world, int rank, const unsigned char *all_han
   P2P *s = p2p_of(h);
   VK_REQUIRE(s && s->mail.p, VK_ESTATE, "p2p_open: call vk_p2p_export first");
   VK_REQUIRE(world >= 1 && world <= P2P_MAX_WORLD && rank >= 0 && rank < world, VK_EINVAL, "p2p_open: bad world / rank");
-  VK_REQUIRE(n_handles == 2 + 2 * s->n_arrays, VK_EINVAL, "p2p_open: handle count differs from this model's");
+  VK_REQUIRE(n_handles == P2P_FIXED_HANDLES + 2 * s->n_arrays, VK_EINVAL, "p2p_open: handle count differs from this model's");
   VK_REQUIRE((int64_t)world * h->P < ((int64_t)1 << 31), VK_EUNSUPPORTED, "p2p: global particle index must fit int32");
-  VK_REQUIRE(h->p_base == (int64_t)rank * h->P, VK_ESTATE, "p2p_open: particle base must be rank * P (vk_set_particle_base)");
+  // particle base rank * P: the particle set is block-partitioned (resample, E2); base 0 on every rank: the
+  // particles are replicated and only the subsampled-MH mailbox is used (observations are sharded, E3)
+  VK_REQUIRE(h->p_base == (int64_t)rank * h->P || h->p_base == 0, VK_ESTATE,
+             "p2p_open: particle base must be rank * P (sharded) or 0 (replicated) (vk_set_particle_base)");
+  s->replicated = h->p_base != (int64_t)rank * h->P;
   P2PTables t;
   memset(&t, 0, sizeof t);
   const cudaIpcMemHandle_t *hs = (const cudaIpcMemHandle_t *)all_handles;
   for (int r = 0; r < world; ++r) {
-    void *ptrs[2 + 2 * P2P_MAX_ARRAYS];
+    void *ptrs[P2P_FIXED_HANDLES + 2 * P2P_MAX_ARRAYS];
     for (int k = 0; k < n_handles; ++k) {
       if (r == rank) {
-        ptrs[k] = k == 0 ? (void *)s->mail.p : k == 1 ? (void *)s->anc_g.p : s->own_buf[(k - 2) / 2][(k - 2) & 1];
+        ptrs[k] = k == 0 ? (void *)s->mail.p : k == 1 ? (void *)s->anc_g.p : k == 2 ? (void *)s->ss_mail.p
+                  : k == 3 ? (void *)s->ss_seq_words.p
+                           : s->own_buf[(k - P2P_FIXED_HANDLES) / 2][(k - P2P_FIXED_HANDLES) & 1];
       } else {
         VK_CUDA(cudaIpcOpenMemHandle(&ptrs[k], hs[(size_t)r * n_handles + k], cudaIpcMemLazyEnablePeerAccess));
         s->imported.push_back(ptrs[k]);
@@ -342,62 +340,96 @@ void p2p_open(vk_particles *h, int world, int rank, const unsigned char *all_han
     }
     t.mail[r] = (P2PMail *)ptrs[0];
     t.anc[r] = (int32_t *)ptrs[1];
+    t.ss_mail[r] = (double *)ptrs[2];
+    t.ss_seq[r] = (unsigned long long *)ptrs[3];
     for (int a = 0; a < s->n_arrays; ++a) {
-      t.buf[a][r][0] = (unsigned char *)ptrs[2 + 2 * a];
-      t.buf[a][r][1] = (unsigned char *)ptrs[3 + 2 * a];
+      t.buf[a][r][0] = (unsigned char *)ptrs[P2P_FIXED_HANDLES + 2 * a];
+      t.buf[a][r][1] = (unsigned char *)ptrs[P2P_FIXED_HANDLES + 1 + 2 * a];
     }
   }
   VK_CUDA(cudaMemcpy(s->tab.p, &t, sizeof t, cudaMemcpyHostToDevice));
-  s->world = world; s->rank = rank; s->opened = true; s->seq = 0;
+  s->world = world; s->rank = rank; s->opened = true;
+  s->n_resamples = 0; s->phase_seq[0] = s->phase_seq[1] = 0; s->ss_seq = 0;
+}
+
+// the by-value description of the NEXT exchange of `phase` (advances that phase's counter); false when this
+// handle's particle set is not sharded over peers
+bool p2p_begin_exchange(vk_particles *h, int phase, P2PXchg *x) {
+  P2P *s = p2p_of(h);
+  x->tab = nullptr;
+  if (!s || !s->opened) return false;
+  x->tab = s->tab.p; x->par = s->par.p; x->err_host = s->err_host_dev;
+  x->world = s->world; x->rank = s->rank; x->my_cur_idx = 0;
+  x->seq = ++s->phase_seq[phase];
+  x->n_total = (long long)s->world * h->P;
+  x->timeout_ns = s->timeout_ns;
+  return true;
+}
+bool p2p_is_open(vk_particles *h) { P2P *s = p2p_of(h); return s && s->opened; }
+bool p2p_ss_view(vk_particles *h, P2PSSView *v) {
+  P2P *s = p2p_of(h);
+  if (!s || !s->opened || s->ss_pcap < h->P) return false;
+  v->tab = s->tab.p; v->par = s->par.p; v->err_host_dev = s->err_host_dev;
+  v->world = s->world; v->rank = s->rank;
+  v->ss_stride = s->ss_stride; v->ss_pcap = s->ss_pcap; v->timeout_ns = s->timeout_ns;
+  return true;
 }
 
 void p2p_resample(vk_particles *h, int mode) {
   P2P *s = p2p_of(h);
   VK_REQUIRE(s && s->opened, VK_ESTATE, "p2p_resample: peers not opened (vk_p2p_export / vk_p2p_open)");
   VK_REQUIRE(mode == VK_RESAMPLE_MULTINOMIAL || mode == VK_RESAMPLE_SYSTEMATIC, VK_EINVAL, "resample: bad mode");
+  VK_REQUIRE(!s->replicated, VK_ESTATE, "p2p_resample: this handle's particles are replicated, not sharded");
+  // validate everything that can throw BEFORE the step / exchange counters move or the model's pending
+  // history column is handed over: a rank that throws here is still in lock step with its peers
+  {
+    std::vector<StateArray> chk = h->model->state_arrays_peek();
+    VK_REQUIRE((int)chk.size() == s->n_arrays, VK_ESTATE, "p2p: state arrays changed since export");
+    int ci = *chk[0].cur == s->own_buf[0][0] ? 0 : 1;
+    for (int a = 0; a < s->n_arrays; ++a)
+      VK_REQUIRE(*chk[a].cur == s->own_buf[a][ci] && *chk[a].alt == s->own_buf[a][1 - ci], VK_ESTATE,
+                 "p2p: state buffers were re-allocated since export");
+  }
   cudaStream_t st = h->stream;
   const int64_t P = h->P, P_total = (int64_t)s->world * P;
-  const uint32_t step = h->next_step();
-  const unsigned long long seq = ++s->seq;
-  const long long spin = 4000000000ll;   // ~2 s of SM clocks: a peer that never arrives sets par->err
   int patch[3];
   std::vector<StateArray> arrs = h->model->state_arrays_patched(patch);
-  VK_REQUIRE((int)arrs.size() == s->n_arrays, VK_ESTATE, "p2p: state arrays changed since export");
   if (patch[0] >= 0)
     VK_REQUIRE(arrs[patch[0]].elem_bytes == 0 && (arrs[patch[0]].row_bytes & 15) == 0 && arrs[patch[1]].elem_bytes == 4 &&
                    arrs[patch[1]].n_rows == 1, VK_EUNSUPPORTED, "p2p: pending-column patch needs 16-byte rows and a 4-byte source");
-  int cur_idx = *arrs[0].cur == s->own_buf[0][0] ? 0 : 1;
-  for (int a = 0; a < s->n_arrays; ++a)
-    VK_REQUIRE(*arrs[a].cur == s->own_buf[a][cur_idx] && *arrs[a].alt == s->own_buf[a][1 - cur_idx], VK_ESTATE,
-               "p2p: state buffers were re-allocated since export");
+  const int cur_idx = *arrs[0].cur == s->own_buf[0][0] ? 0 : 1;
+  const uint32_t step = h->next_step();
+  const int half = (int)(++s->n_resamples & 1ull);
   const int S = frac_bits_for(P_total);
   const double scale = ldexp(1.0, S);
   const int n_tiles = (int)((P + SCAN_TILE - 1) / SCAN_TILE);
   if (h->red_u.n < (size_t)n_tiles + 1) h->red_u.alloc((size_t)n_tiles + 1);
   if (h->tile_exp.n < (size_t)n_tiles) h->tile_exp.alloc((size_t)n_tiles);
-  if (!h->lw_minmax_fresh)
-    lse_pass1_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p);
-  h->lw_minmax_fresh = false;
-  p2p_exchange_kernel<<<1, 32, 0, st>>>(s->tab.p, s->par.p, h->red.p, h->red_u.p, n_tiles, s->world, s->rank, 0, seq,
-                                        cur_idx, P_total, spin);
-  fixed_tile_sums_exp_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p);
-  p2p_scan_exchange1_kernel<<<1, 1024, 0, st>>>(s->tab.p, s->par.p, h->red.p, h->red_u.p, h->tile_exp.p, n_tiles, P,
-                                                s->world, s->rank, seq, cur_idx, P_total, spin);
+  P2PXchg x;
+  if (!(h->lw_minmax_fresh && h->lw_x0_done)) {     // the producer of the weights did not run exchange 0 itself
+    p2p_begin_exchange(h, 0, &x);
+    lse_pass1_xchg_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p, x);
+  }
+  h->lw_minmax_fresh = false; h->lw_x0_done = false;
+  p2p_begin_exchange(h, 1, &x);
+  x.my_cur_idx = cur_idx;
+  p2p_tile_sums_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p, n_tiles,
+                                                         h->counters.p + 2, x);
   if (mode == VK_RESAMPLE_SYSTEMATIC) {
     p2p_offspring_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, s->par.p, s->tab.p,
-                                                           P_total, h->p_base, h->seed, step);
+                                                           half, P_total, h->p_base, h->seed, step);
   } else {
     fixed_cdf_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, 0.0, h->red.p, scale, h->red_u.p, h->cdf.p);
-    p2p_multinomial_kernel<<<grid_for(P_total, 256, h->sm_count, 8), 256, 0, st>>>(h->cdf.p, P, s->par.p, s->tab.p, P_total,
-                                                                                  h->p_base, h->seed, step);
+    p2p_multinomial_kernel<<<grid_for(P_total, 256, h->sm_count, 8), 256, 0, st>>>(h->cdf.p, P, s->par.p, s->tab.p, half,
+                                                                                  P_total, h->p_base, h->seed, step);
   }
-  p2p_exchange_kernel<<<1, 32, 0, st>>>(s->tab.p, s->par.p, h->red.p, h->red_u.p, n_tiles, s->world, s->rank, 2, seq,
-                                        cur_idx, P_total, spin);
   P2PArrays pa;
   memset(&pa, 0, sizeof pa);
   pa.n = s->n_arrays;
   pa.patch_array = patch[0]; pa.patch_src = patch[1]; pa.patch_byte = patch[2];
   pa.lw = h->lw.p; pa.red = h->red.p; pa.log_p_total = log((double)P_total);
+  pa.anc_other = s->anc_g.p + (int64_t)(1 - half) * P;
+  pa.timeout_ns = s->timeout_ns; pa.err_host = s->err_host_dev;
   int64_t work = P;
   for (int a = 0; a < s->n_arrays; ++a) {
     pa.alt[a] = (unsigned char *)*arrs[a].alt;
@@ -407,7 +439,8 @@ void p2p_resample(vk_particles *h, int mode) {
                                     : ((arrs[a].row_bytes & 15) == 0 ? P * (int64_t)(arrs[a].row_bytes >> 4) : P * (int64_t)arrs[a].row_bytes);
     work = wa > work ? wa : work;
   }
-  p2p_gather_kernel<<<grid_for(work, 256, h->sm_count, 8), 256, 0, st>>>(s->anc_g.p, P, s->tab.p, s->par.p, pa);
+  p2p_gather_kernel<<<grid_for(work, 256, h->sm_count, 8), 256, 0, st>>>(s->anc_g.p + (int64_t)half * P, P, s->tab.p,
+                                                                         s->par.p, pa);
   VK_CUDA(cudaGetLastError());
   for (auto &a : arrs) { void *t = *a.cur; *a.cur = *a.alt; *a.alt = t; }
   h->model->after_resample();
@@ -417,12 +450,10 @@ void p2p_resample(vk_particles *h, int mode) {
 void p2p_status(vk_particles *h, int *err_out, double *lse_out) {
   P2P *s = p2p_of(h);
   VK_REQUIRE(s && s->par.p, VK_ESTATE, "p2p_status: p2p not initialised");
-  P2PParams p;
-  VK_CUDA(cudaMemcpyAsync(&p, s->par.p, sizeof p, cudaMemcpyDeviceToHost, h->stream));
   double red[5];
   VK_CUDA(cudaMemcpyAsync(red, h->red.p, sizeof red, cudaMemcpyDeviceToHost, h->stream));
   VK_CUDA(cudaStreamSynchronize(h->stream));
-  if (err_out) *err_out = p.err;
+  if (err_out) *err_out = *(volatile int *)s->err_host;
   if (lse_out) *lse_out = red[4];
 }
 
@@ -430,6 +461,7 @@ void p2p_release(vk_particles *h) {
   P2P *s = p2p_of(h);
   if (!s) return;
   for (void *p : s->imported) cudaIpcCloseMemHandle(p);
+  if (s->err_host) cudaFreeHost(s->err_host);
   delete s;
   h->p2p = nullptr;
 }

@@ -43,10 +43,12 @@ VK_HD Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
   return out;
 }
 
-// 53 random bits -> a double strictly inside (0,1).
+// 53 random bits -> a double strictly inside (0,1).  x = 2^53 - 1 would round to exactly 1.0 (x + 0.5 is a
+// tie that rounds to even); that one value is clamped to 1 - 2^-53.
 VK_HD double u01_from_bits(uint32_t hi, uint32_t lo) {
   uint64_t x = (((uint64_t)hi << 32) | (uint64_t)lo) >> 11;
-  return ((double)x + 0.5) * (1.0 / 9007199254740992.0);
+  const double u = ((double)x + 0.5) * (1.0 / 9007199254740992.0);
+  return u < 1.0 ? u : 0.99999999999999988898;
 }
 
 // Sequential view over the draws of one (seed, particle, step).

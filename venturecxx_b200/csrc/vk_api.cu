@@ -27,6 +27,7 @@ static void check_handle(const vk_particles *h) {
 // "min/max of lw are already in red[]" hint dies; vk_make_consistent may set it again on its way out
 static void use_device(const vk_particles *h) {
   const_cast<vk_particles *>(h)->lw_minmax_fresh = false;
+  const_cast<vk_particles *>(h)->lw_x0_done = false;
   VK_CUDA(cudaSetDevice(h->device));
 }
 
@@ -43,6 +44,7 @@ struct HostOut {
     if (!host) return;
     VK_CUDA(cudaMemcpyAsync(host, h->out_d.p, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     VK_CUDA(cudaStreamSynchronize(h->stream));
+    vk::p2p_check_error(h);      // a peer-memory exchange that timed out is fatal for this particle set
   }
 };
 
@@ -68,6 +70,7 @@ static vk_particles *new_handle(int kind, int64_t P, uint64_t seed, int device) 
     h->red.alloc((size_t)(8 + 3 * h->sm_count * 8 + 64));
     h->counters.alloc(8);
     VK_CUDA(cudaMemsetAsync(h->lw.p, 0, h->lw.bytes(), h->stream));
+    VK_CUDA(cudaMemsetAsync(h->anc.p, 0, h->anc.bytes(), h->stream));
     VK_CUDA(cudaMemsetAsync(h->counters.p, 0, h->counters.bytes(), h->stream));
   } catch (...) { delete h; throw; }
   return h;
@@ -164,7 +167,12 @@ int vk_set_stream(vk_particles *h, void *cuda_stream) {
   h->stream = cuda_stream ? (cudaStream_t)cuda_stream : h->own_stream;
   VK_CATCH
 }
-int vk_synchronize(vk_particles *h) { VK_TRY check_handle(h); use_device(h); VK_CUDA(cudaStreamSynchronize(h->stream)); VK_CATCH }
+int vk_synchronize(vk_particles *h) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  vk::p2p_check_error(h);
+  VK_CATCH
+}
 
 int vk_reset_to_prior(vk_particles *h) {
   VK_TRY check_handle(h); use_device(h);
@@ -224,6 +232,7 @@ int vk_get_log_weights(vk_particles *h, double *out_host) {
   VK_REQUIRE(out_host, VK_EINVAL, "out_host is NULL");
   VK_CUDA(cudaMemcpyAsync(out_host, h->lw.p, h->lw.bytes(), cudaMemcpyDeviceToHost, h->stream));
   VK_CUDA(cudaStreamSynchronize(h->stream));
+  vk::p2p_check_error(h);
   VK_CATCH
 }
 int vk_set_log_weights(vk_particles *h, const double *in_host) {
@@ -277,7 +286,8 @@ int vk_logsumexp_array(const double *in_host, int64_t n, int device, double *out
 
 int vk_resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms_host,
                 int32_t *ancestors_out_host) {
-  const bool minmax_fresh = h && h->lw_minmax_fresh;
+  // red[0..2] produced with the peer exchange describe ALL ranks' weights: not this local resample's input
+  const bool minmax_fresh = h && h->lw_minmax_fresh && !h->lw_x0_done;
   VK_TRY check_handle(h); use_device(h);
   h->lw_minmax_fresh = minmax_fresh;   // resample() consumes it
   DevBuf<double> u;
@@ -325,9 +335,9 @@ int vk_p2p_open(vk_particles *h, int32_t world, int32_t rank, const unsigned cha
   VK_CATCH
 }
 int vk_p2p_resample(vk_particles *h, int mode) {
-  const bool minmax_fresh = h && h->lw_minmax_fresh;
+  const bool minmax_fresh = h && h->lw_minmax_fresh, x0_done = h && h->lw_x0_done;
   VK_TRY check_handle(h); use_device(h);
-  h->lw_minmax_fresh = minmax_fresh;   // p2p_resample() consumes it
+  h->lw_minmax_fresh = minmax_fresh; h->lw_x0_done = x0_done;   // p2p_resample() consumes them
   vk::p2p_resample(h, mode);
   // trace_set.py:207: resample ends with incorporate()
   h->model->make_consistent(nullptr);
@@ -428,6 +438,14 @@ int vk_shard_weight_max(vk_particles *h, double *max_out_host) {
   VK_REQUIRE(max_out_host, VK_EINVAL, "NULL");
   shard_weight_max(h);
   VK_CUDA(cudaMemcpyAsync(max_out_host, h->red.p, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  VK_CUDA(cudaStreamSynchronize(h->stream));
+  VK_CATCH
+}
+int vk_shard_weight_stats(vk_particles *h, double *out3_host) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(out3_host, VK_EINVAL, "NULL");
+  shard_weight_max(h);
+  VK_CUDA(cudaMemcpyAsync(out3_host, h->red.p, 3 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   VK_CUDA(cudaStreamSynchronize(h->stream));
   VK_CATCH
 }

@@ -56,6 +56,8 @@ struct DevBuf {
     n = 0;
   }
   void swap(DevBuf &o) { std::swap(p, o.p); std::swap(n, o.n); }
+  // take ownership of a cudaMalloc'd array of `count` elements (frees what was held)
+  void adopt(void *ptr, size_t count) { release(); p = (T *)ptr; n = count; }
   size_t bytes() const { return n * sizeof(T); }
 };
 
@@ -97,6 +99,9 @@ struct vk_particles {
   // red[0..2] = (max, min, NaN flag) of lw as it is NOW: set by a model whose make_consistent reduced the
   // weights it wrote, cleared at the entry of every API call; consumed by vk_resample / vk_p2p_resample
   bool lw_minmax_fresh = false;
+  // ... and they describe the weights of ALL ranks: the producer's last block already ran exchange 0 of the
+  // peer-memory resample (p2p_common.cuh); same lifetime as lw_minmax_fresh
+  bool lw_x0_done = false;
   void *p2p = nullptr;          // vk::P2P (p2p_resample.cuh): peer-memory resampling state
   uint32_t next_step(uint32_t n = 1) { uint32_t s = step; step += n; return s; }
 };
@@ -136,8 +141,15 @@ struct Model {
   }
   virtual int get_precision() const { return VK_FP64; }
   // arrays gathered by ancestor index on resample; after the gather the model
-  // swaps cur/alt itself via StateArray.
-  virtual std::vector<StateArray> state_arrays() = 0;
+  // swaps cur/alt itself via StateArray.  alloc_alt = false: do not allocate back buffers that do not exist
+  // yet (the caller installs its own: resample with n_new != P).
+  virtual std::vector<StateArray> state_arrays(bool alloc_alt = true) = 0;
+  // the same description with NO side effect at all (validation before anything is committed)
+  virtual std::vector<StateArray> state_arrays_peek() { return state_arrays(false); }
+  // resample changed the particle count: the live arrays are new_cur[i] and the back buffers new_alt[i]
+  // (cudaMalloc'd for n_new particles, in state_arrays() order; *cur / *alt already point at new_cur[i] / stale
+  // memory).  The model frees its old buffers, adopts the new ones and drops every cache sized by the old count.
+  virtual void resized(int64_t n_new, const std::vector<void *> &new_cur, const std::vector<void *> &new_alt) = 0;
   // state_arrays() for a gather that can patch one byte into every row it copies: a model whose newest
   // column is still pending in a particle-minor array (HMM: hist[.][T-1] lives in cur[]) reports
   // (row array index, source SoA array index, byte offset in the row) instead of materialising the column

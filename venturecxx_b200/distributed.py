@@ -49,7 +49,7 @@ def global_uniform(seed, step):
     """draw 0 of the stream (seed, GLOBAL_PARTICLE, step) -- csrc/philox.cuh"""
     b = philox4x32_10((MASK32, MASK32, step & MASK32, 0), (seed & MASK32, (seed >> 32) & MASK32))
     x = ((b[0] << 32) | b[1]) >> 11
-    return (x + 0.5) / 9007199254740992.0
+    return min((x + 0.5) / 9007199254740992.0, 0.99999999999999988898)    # strictly below 1, as philox.cuh
 
 
 def frac_bits_for(P_total):
@@ -74,11 +74,14 @@ def systematic_child_range(offset, mass, total, n_new, u):
     return first_k_with_threshold_at_least(offset), first_k_with_threshold_at_least(offset + mass)
 
 
-def lse_from_parts(global_max, sumexps, any_nan=False):
-    """utils.logsumexp (lite/utils.py:70-91) from per-shard partial sums."""
+def lse_from_parts(global_max, sumexps, any_nan=False, global_min=None):
+    """utils.logsumexp (lite/utils.py:70-91) from per-shard partial sums: NaN if any weight is NaN or if
+    +inf and -inf are both present; the max itself when it is infinite."""
     if any_nan:
         return float("nan")
     if math.isinf(global_max):
+        if global_min is not None and global_min == -global_max:
+            return float("nan")
         return global_max
     return global_max + math.log(float(np.sum(sumexps)))
 
@@ -100,6 +103,14 @@ class CudaShard(object):
         m = ctypes.c_double()
         _lib.call("vk_shard_weight_max", self.ts._h, ctypes.byref(m))
         return m.value
+
+    def weight_stats(self):
+        """(max ignoring NaN, min ignoring NaN, any NaN) of this shard's log weights"""
+        import ctypes
+        from . import _lib
+        v = (ctypes.c_double * 3)()
+        _lib.call("vk_shard_weight_stats", self.ts._h, v)
+        return v[0], v[1], bool(v[2])
 
     def build_cdf(self, global_max, frac_bits):
         import ctypes
@@ -201,10 +212,8 @@ def sharded_resample(shard, seed, step, mode="systematic", group=None):
     P_local = shard.P
     P_total = world * P_local
     sys_mode = mode == "systematic"
-    # 1. global max
-    m = shard.tensor([shard.weight_max()], torch.float64)
-    dist.all_reduce(m, op=dist.ReduceOp.MAX, group=group)
-    gmax = float(m.item())
+    # 1. global max; min and NaN flag travel with it for the edge cases of utils.logsumexp
+    gmax, gmin, any_nan = _global_weight_stats(shard, torch, dist, group)
     # 2. fixed-point masses relative to the global max
     mass, sumexp = shard.build_cdf(gmax, frac_bits_for(P_total))
     mine = shard.tensor([float(mass >> 32), float(mass & MASK32), sumexp], torch.float64)   # exact: 2 x 32-bit halves
@@ -212,7 +221,7 @@ def sharded_resample(shard, seed, step, mode="systematic", group=None):
     dist.all_gather_into_tensor(allv, mine, group=group)
     allh = allv.cpu().numpy().reshape(world, 3)                  # one host round trip for all scalars
     masses = [(int(allh[r, 0]) << 32) | int(allh[r, 1]) for r in range(world)]
-    lse = lse_from_parts(gmax, [float(allh[r, 2]) for r in range(world)])
+    lse = lse_from_parts(gmax, [float(allh[r, 2]) for r in range(world)], any_nan, gmin)
     offsets = [sum(masses[:r]) for r in range(world)]
     offset, total = offsets[rank], sum(masses)
     if sys_mode:
@@ -247,6 +256,15 @@ def sharded_resample(shard, seed, step, mode="systematic", group=None):
     shard.fill_log_weights(lse - math.log(P_total))
     shard.incorporate()
     return lse
+
+
+def _global_weight_stats(shard, torch, dist, group):
+    """(max, min, any NaN) over all ranks; one all_reduce(MAX) of (max, -min, nan flag)"""
+    mx, mn, nan = shard.weight_stats()
+    v = shard.tensor([mx, -mn, 1.0 if nan else 0.0], torch.float64)
+    dist.all_reduce(v, op=dist.ReduceOp.MAX, group=group)
+    v = v.tolist()
+    return float(v[0]), -float(v[1]), bool(v[2] > 0.0)
 
 
 class ShardedTraceSet(object):
@@ -286,9 +304,9 @@ class ShardedTraceSet(object):
         import ctypes
         import torch.distributed as dist
         from . import _lib
-        buf = (ctypes.c_ubyte * (64 * 16))()
+        buf = (ctypes.c_ubyte * (64 * 32))()
         n = ctypes.c_int32()
-        _lib.call("vk_p2p_export", self.local._h, buf, 16, ctypes.byref(n))
+        _lib.call("vk_p2p_export", self.local._h, buf, 32, ctypes.byref(n))
         mine = bytes(buf[:64 * n.value])
         gathered = [None] * self.world
         dist.all_gather_object(gathered, mine, group=self.group)
@@ -310,9 +328,11 @@ class ShardedTraceSet(object):
         return bool(e.value), lse.value
 
     def resample(self, P=None, mode="multinomial"):
+        from .exception import VentureException
         if P is not None and int(P) != self.n_particles:
-            from .exception import VentureException
-            raise VentureException("invalid_argument", "resample: P must equal the particle count")
+            raise VentureException("invalid_argument", "resample: a sharded particle set keeps its particle count")
+        if self.replicated:
+            raise VentureException("invalid_argument", "resample: this set's particles are replicated, not sharded")
         if getattr(self, "peer_memory", False):
             from . import _lib
             _lib.call("vk_p2p_resample", self.local._h,
@@ -328,12 +348,11 @@ class ShardedTraceSet(object):
     def logsumexp(self):
         import torch
         import torch.distributed as dist
-        m = self.shard.tensor([self.shard.weight_max()], torch.float64)
-        dist.all_reduce(m, op=dist.ReduceOp.MAX, group=self.group)
-        _, se = self.shard.build_cdf(float(m.item()), frac_bits_for(self.n_particles))
+        gmax, gmin, any_nan = _global_weight_stats(self.shard, torch, dist, self.group)
+        _, se = self.shard.build_cdf(gmax, frac_bits_for(self.n_particles))
         s = self.shard.tensor([se], torch.float64)
         dist.all_reduce(s, op=dist.ReduceOp.SUM, group=self.group)
-        return lse_from_parts(float(m.item()), [float(s.item())])
+        return lse_from_parts(gmax, [float(s.item())], any_nan, gmin)
 
     # -- observation-sharded subsampled MH (particles replicated on every rank) --
     def observe_shard(self, X_local, y_local, global_offset, n_total):
@@ -348,6 +367,11 @@ class ShardedTraceSet(object):
         import torch
         import torch.distributed as dist
         from . import _lib
+        if getattr(self, "peer_memory", False) and self.replicated:
+            # the partial sums travel through peer mailboxes INSIDE the library's persistent kernel
+            # (csrc/blr_subsampled_persistent.cuh): no collective, no host round trip
+            return self.local.subsampled_mh(scope, block, Nbatch, k0, epsilon, useDeltaKernels, deltaKernelArgs,
+                                            updateValues, transitions)
         h = self.local._h
         s, b = self.local._scope_block(scope, block)
         P = self.local.n_particles
@@ -362,8 +386,9 @@ class ShardedTraceSet(object):
                 p = ctypes.c_void_p()
                 _lib.call("vk_ssmh_round", h, q0, q1, ctypes.byref(p))
                 sums = _wrap_device(torch, p.value, P * 2, self.local.device)
-                dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=self.group)
-                torch.cuda.current_stream().synchronize()
+                with torch.cuda.stream(self.stream):      # the library runs on this stream too (use_stream)
+                    dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=self.group)
+                self.stream.synchronize()
                 n_active = ctypes.c_int32()
                 _lib.call("vk_ssmh_decide", h, ctypes.c_void_p(p.value), q1, int(k0), float(epsilon),
                           ctypes.byref(n_active))

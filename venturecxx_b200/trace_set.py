@@ -118,10 +118,12 @@ class B200TraceSet(object):
         from . import interchange
         interchange.load(self, serialized)
 
-    def forget_observations(self):
+    def forget_observations(self, return_weights=True):
         """engine.forget of every observation (trace_set.py:157-161): returns the
-        per-particle weights unconstrain() reports; log_weights unchanged."""
-        out = self._out()
+        per-particle weights unconstrain() reports; log_weights unchanged.
+        return_weights=False skips computing them (a full pass over the observations' log densities)
+        and keeps the call stream-ordered."""
+        out = self._out() if return_weights else None
         _lib.call("vk_forget_observations", self._h, _lib.ptr(out))
         self._observed = []
         return out
@@ -193,6 +195,7 @@ class B200TraceSet(object):
         u = None if uniforms is None else np.ascontiguousarray(np.atleast_1d(uniforms), dtype=np.float64)
         anc = np.empty(P, dtype=np.int32) if return_ancestors else None
         _lib.call("vk_resample", self._h, P, m, _lib.ptr(u), _lib.ptr(anc))
+        self.n_particles = P             # trace_set.py:202-219: the set now holds P particles
         return anc
 
     # -- inference ---------------------------------------------------------
@@ -234,9 +237,13 @@ class B200TraceSet(object):
             return self.subsampled_mh(*exp[1:])
         raise VentureException("invalid_argument", "operator %r is not on the B200 path" % (op,))
 
-    def resimulation_mh(self, scope, block, transitions, return_accepts=False):
+    def resimulation_mh(self, scope, block, transitions, return_accepts=False, out=None):
+        """out: optional caller-owned float64 array of n_particles (e.g. pinned memory) for the node counts"""
         s, b = self._scope_block(scope, block)
-        out = self._out()
+        if out is None:
+            out = self._out()
+        elif out.shape != (self.n_particles,) or out.dtype != np.float64 or not out.flags["C_CONTIGUOUS"]:
+            raise VentureException("invalid_argument", "out must be a contiguous float64 array of %d entries" % self.n_particles)
         acc = self._out(dtype=np.int64) if return_accepts else None
         _lib.call("vk_mh", self._h, s, b, int(transitions), _lib.ptr(out), _lib.ptr(acc))
         return (out, acc) if return_accepts else out

@@ -40,11 +40,23 @@ TREES = [
     ("python/lib/value", "value"),
     ("python/lib/engine", "engine"),
     ("backend/untraced", "untraced"),
+    ("python/lib/sivm", "sivm"),         # macro system (`do`, `let`, ...) for the engine-seam tests
 ]
 SINGLE = [
     ("python/lib/exception.py", "exception.py"),
     ("python/lib/multiprocess.py", "multiprocess.py"),
+    ("python/lib/ripl/utils.py", "ripl/utils.py"),
 ]
+# Modules the engine imports but the hot path never calls (plotting, the ripl / parser front end): generated
+# as empty stand-ins so that `venture.engine.engine.Engine` -- the reference's own control plane -- imports and
+# can drive a backend here (tests/ref_engine.py).  The package __init__ files of sivm / ripl pull in the whole
+# front end (parser, server); they are replaced by empty ones.
+STUBS = {
+    "plots/__init__.py": "",
+    "plots/p_p_plot.py": "def p_p_plot_2samp(*args, **kwargs):\n  raise NotImplementedError('plotting is not rendered')\n",
+    "ripl/__init__.py": "",
+    "sivm/__init__.py": "",
+}
 
 REGEX = [
     (r"\.iteritems\(\)", ".items().__iter__()"),
@@ -215,11 +227,16 @@ def main():
                 f.write(convert(src, rel))
             n += 1
     for ref, rel in SINGLE:
+        os.makedirs(os.path.dirname(os.path.join(pkg, rel)), exist_ok=True)
         with open(os.path.join(REF, ref)) as f:
             src = f.read()
         with open(os.path.join(pkg, rel), "w") as f:
             f.write(convert(src, rel))
         n += 1
+    for rel, body in STUBS.items():
+        os.makedirs(os.path.dirname(os.path.join(pkg, rel)), exist_ok=True)
+        with open(os.path.join(pkg, rel), "w") as f:
+            f.write("# generated stand-in (oracle/lite_py3/build_lite_py3.py STUBS)\n" + body)
     # compile check
     bad = 0
     for root, _, files in os.walk(pkg):

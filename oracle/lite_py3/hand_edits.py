@@ -19,4 +19,13 @@ HAND = {
     "engine/inference.py": [
         ("def printf(self, dataset): print dataset.asPandas()", "def printf(self, dataset): print(dataset.asPandas())"),
     ],
+    # py3 laziness: map() results that are concatenated to lists / pattern-matched as lists
+    "sivm/macro.py": [
+        ("pattern = ['cond'] + map(list, zip(preds, exprs))", "pattern = ['cond'] + list(map(list, zip(preds, exprs)))"),
+        ("pattern = ['let', map(list, zip(syms, vals)), 'body']", "pattern = ['let', list(map(list, zip(syms, vals))), 'body']"),
+        ("pattern = ['letrec', map(list, zip(syms, vals)), 'body']", "pattern = ['letrec', list(map(list, zip(syms, vals))), 'body']"),
+    ],
+    "sivm/core_sivm.py": [
+        ("return map(_modify_expression, expression)", "return list(map(_modify_expression, expression))"),
+    ],
 }

@@ -130,7 +130,7 @@ blr_all_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restr
 // per observation one FMA (eta + delta*x) and one fast_log_logistic.
 static const int BLR_MH_CHUNK = 256;   // transitions whose proposals are staged at once
 static const int BLR_MH_TILE = 1024;   // observations per CTA-wide loop iteration (THREADS x UNROLL)
-static const int BLR_MH_DEFAULT_VARIANT = 1;
+static const int BLR_MH_DEFAULT_VARIANT = 4;   // blr_mh2_kernel (blr_mh2.cuh); 0-3: blr_mh_kernel shapes
 #define BLR_PAD_ETA 800.0              // logit of a padding slot: log_logistic(800) = -exp(-800) = 0
 
 // shared-memory carve-up shared by the kernel and the host-side size computation:
@@ -337,6 +337,7 @@ blr_mh_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restri
 
 }  // namespace vk
 #include "blr_mh_f32.cuh"
+#include "blr_mh2.cuh"
 namespace vk {
 
 // block = all: joint proposal of every weight from the prior (one scaffold
@@ -797,8 +798,17 @@ struct BLRModel : Model {
         w, eta, ll, Xs.p, prm, h->P, h->p_base, h->seed, step0, n_steps, block, acc_dev, fm_coef);             \
   } while (0)
 #define VK_MH_VARIANT(T, U, B) do { if (in_smem) VK_MH_LAUNCH(true, T, U, B); else VK_MH_LAUNCH(false, T, U, B); } while (0)
+        const size_t need2 = blr_mh2_smem_base(prm.D) + (size_t)Npad * sizeof(double);
+        if (variant >= 4 && need2 <= (size_t)smem_limit) {
+          // two proposals per pass over the shared-memory row (blr_mh2.cuh)
+          int per2 = (int)((size_t)(227 * 1024) / (need2 + 1024));
+          if (per2 < 1) per2 = 1;
+          VK_CUDA(cudaFuncSetAttribute(blr_mh2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_limit));
+          blr_mh2_kernel<2><<<grid_particles(per2 < 2 ? per2 : 2), MH2_THREADS, need2, h->stream>>>(
+              w, eta, ll, Xs.p, prm, h->P, h->p_base, h->seed, step0, n_steps, block, acc_dev, fm_coef);
+        } else
         switch (variant) {
-          case 1: VK_MH_VARIANT(256, 4, 2); break;
+          case 1: case 4: VK_MH_VARIANT(256, 4, 2); break;
           case 2: VK_MH_VARIANT(1024, 1, 1); break;
           case 3: VK_MH_VARIANT(512, 2, 1); break;
           default: VK_MH_VARIANT(512, 2, 2); break;

@@ -171,7 +171,7 @@ def test_peer_memory_resample_world_of_one_matches_vk_resample(mode):
     buf = (ctypes.c_ubyte * (64 * 16))()
     n = ctypes.c_int32()
     _lib.call("vk_p2p_export", a._h, buf, 16, ctypes.byref(n))
-    assert n.value == 2 + 2 * 2                     # mailbox, ancestors, two buffers for each of (cur, hist)
+    assert n.value == 4 + 2 * 2     # mailbox, ancestors, ss mailbox, ss sequence words, two buffers for each of (cur, hist)
     _lib.call("vk_p2p_open", a._h, 1, 0, buf, n.value)
     m = _lib.RESAMPLE_SYSTEMATIC if mode == "systematic" else _lib.RESAMPLE_MULTINOMIAL
     for t, d in enumerate(H["data"][:T]):

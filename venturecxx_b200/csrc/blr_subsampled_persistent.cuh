@@ -35,57 +35,77 @@ namespace vk {
 
 static const int SSP_THREADS = 256;
 static const int SSP_WARPS = SSP_THREADS / 32;
-static const int SSP_ROWS = 256;                 // observation rows staged per pass (= one position per thread)
-static const int SSP_PER_WARP = 8;               // particles a warp accumulates in registers per pass
-static const int SSP_TILE = SSP_WARPS * SSP_PER_WARP;   // particles per pass of a CTA
+static const int SSP_ROWS = 128;                 // observation rows staged per pass
+static const int SSP_CHUNKS = SSP_ROWS / 32;     // 32-row chunks of a pass (one warp-wide slice each)
+static const int SSP_STAGES = 3;                 // passes in flight (cp.async ring)
+static const int SSP_TILE = 64;                  // undecided particles handled per sweep over the passes
 static const int SSP_GMAX = P2P_SS_MAX_ROUNDS;   // rounds per batch
+static const int SSP_DIRECT = 4;                 // at most this many undecided particles: one thread per position, no staging
+static const int SSP_PART = SSP_GMAX * SSP_DIRECT * SSP_WARPS * 2 > SSP_CHUNKS * SSP_TILE * 2
+                                ? SSP_GMAX * SSP_DIRECT * SSP_WARPS * 2 : SSP_CHUNKS * SSP_TILE * 2;   // doubles of scratch
 
 struct SSPersist {                 // by-value kernel argument
   const double *Xr; double *w; SSState S;
+  int *status_alt;                              // second status array: transitions alternate between the two
   int D; int64_t P, p_base, obs_lo, N_local, Nt, Nbatch;
   int k0; double eps;
   int block_mode, n_transitions, delta_mode; double delta_eps, mu0_prior, s0_prior;
   uint64_t seed; uint32_t step0;
   const double *tcrit; int n_tcrit;             // t.ppf(1 - eps, n_k - 1) for minibatch count k = index + 1
-  int G_first, G_next;
+  int G_first, G_min, G_work;                   // rounds per batch: k0 first, then clamp(G_work / #undecided, G_min, SSP_GMAX)
   double *partial;                              // [grid][SSP_GMAX][P][2]
-  unsigned int *bar;                            // grid barrier counter, zeroed before the launch
-  int *abort_flag;                              // set by a barrier / exchange that timed out
+  unsigned long long *bar;                      // [0] grid barrier counter, [1] abort flag; zeroed before the launch
+  int *abort_host;                              // host-mapped mirror of the abort flag (written only on a timeout)
   unsigned long long *seq_dev;                  // exchanges completed so far (persists across launches)
   P2PTables *tab; P2PParams *par; volatile int *err_host;
   int world, rank; long long ss_stride, ss_pcap, timeout_ns;
+  unsigned long long *prof;                     // nullable: [16] phase times (ns) and counts seen by CTA 0 (VK_SS_PROFILE)
   FmCoef cf;
 };
+// prof slots: 0 list, 1 eval staged, 2 eval direct, 3 barrier after eval, 4 decide, 5 barrier after decide, 6 propose + its
+// barrier, 8 batches staged, 9 batches direct, 10 rounds staged, 11 rounds direct, 12 sum of #undecided over batches
 
 __host__ __device__ inline size_t ssp_smem_bytes(int DT, int64_t P) {
-  return (size_t)FM_SMEM_LOG_BYTES + FM_SMEM_EXP_BYTES + (size_t)SSP_ROWS * (DT + 1) * sizeof(double) +
-         (size_t)SSP_TILE * DT * sizeof(double) + (size_t)SSP_TILE * sizeof(double) +
-         (size_t)(SSP_ROWS + 2 * SSP_TILE + 16) * sizeof(int) + (size_t)((P + 3) & ~(int64_t)3) * sizeof(int);
+  return (size_t)FM_SMEM_LOG_BYTES + FM_SMEM_EXP_BYTES +
+         (size_t)SSP_STAGES * SSP_ROWS * (DT + 1) * sizeof(double) +      // staged rows
+         (size_t)SSP_TILE * DT * sizeof(double) +                         // weights of the tile's particles
+         (size_t)SSP_TILE * sizeof(double) +                              // their proposal deltas
+         (size_t)SSP_PART * sizeof(double) +                              // per-chunk sums of a pass / per-warp sums of a batch
+         (size_t)SSP_TILE * 2 * sizeof(double) +                          // the current round's running sums
+         (size_t)(SSP_STAGES * SSP_ROWS + SSP_STAGES * (SSP_WARPS + 1) + 2 * SSP_TILE) * sizeof(int) +
+         (size_t)((P + 3) & ~(int64_t)3) * sizeof(int);
 }
 
+__device__ __forceinline__ void ssp_set_abort(const SSPersist &a) {
+  *(volatile unsigned long long *)(a.bar + 1) = 1ull;
+  *(volatile int *)a.abort_host = 1;
+  __threadfence_system();
+}
+__device__ __forceinline__ bool ssp_aborted(const SSPersist &a) { return *(volatile unsigned long long *)(a.bar + 1) != 0ull; }
+
 // all CTAs arrive, then all leave.  `epoch` counts this CTA's barriers.  false = timed out (abort flag set).
-__device__ __forceinline__ bool ssp_grid_barrier(const SSPersist &a, unsigned int &epoch) {
+__device__ __forceinline__ bool ssp_grid_barrier(const SSPersist &a, unsigned long long &epoch) {
   __shared__ int ok_sh;
   __syncthreads();
+  ++epoch;
   if (threadIdx.x == 0) {
-    ++epoch;
-    const unsigned int target = epoch * gridDim.x;
+    const unsigned long long target = epoch * (unsigned long long)gridDim.x;
     __threadfence();
-    atomicAdd(a.bar, 1u);
+    atomicAdd(a.bar, 1ull);
     int ok = 1;
-    const unsigned long long t0 = p2p_now_ns();
+    unsigned long long t0 = 0;
     int spins = 0;
-    while (*(volatile unsigned int *)a.bar < target) {
-      if ((++spins & 255) == 0) {
-        if (*(volatile int *)a.abort_flag) { ok = 0; break; }
-        if ((long long)(p2p_now_ns() - t0) > a.timeout_ns) { *(volatile int *)a.abort_flag = 1; ok = 0; break; }
+    while (*(volatile unsigned long long *)a.bar < target) {
+      if ((++spins & 1023) == 0) {
+        if (ssp_aborted(a)) { ok = 0; break; }
+        const unsigned long long now = p2p_now_ns();
+        if (t0 == 0) t0 = now;
+        else if ((long long)(now - t0) > a.timeout_ns) { ssp_set_abort(a); ok = 0; break; }
       }
     }
-    if (*(volatile int *)a.abort_flag) ok = 0;
+    if (ssp_aborted(a)) ok = 0;
     __threadfence();
     ok_sh = ok;
-  } else {
-    ++epoch;
   }
   __syncthreads();
   return ok_sh != 0;
@@ -105,32 +125,49 @@ __device__ __forceinline__ double ssp_dllh(double v_new, double v_old, const FmC
   return dmin - dsp;
 }
 
+__device__ __forceinline__ void ssp_cp_async8(void *dst_shared, const void *src_global) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_shared)), "l"(src_global));
+}
+__device__ __forceinline__ void ssp_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N_PENDING> __device__ __forceinline__ void ssp_cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N_PENDING) : "memory"); }
+
 template <int DT>
 __global__ void __launch_bounds__(SSP_THREADS, 2) ss_persistent_kernel(const SSPersist a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   unsigned char *log_tbl = smem_raw;
   unsigned char *exp_tbl = smem_raw + FM_SMEM_LOG_BYTES;
-  double *rows_sh = reinterpret_cast<double *>(exp_tbl + FM_SMEM_EXP_BYTES);      // SSP_ROWS x (DT+1)
-  double *w_sh = rows_sh + SSP_ROWS * (DT + 1);                                   // SSP_TILE x DT
+  double *rows_sh = reinterpret_cast<double *>(exp_tbl + FM_SMEM_EXP_BYTES);      // SSP_STAGES x SSP_ROWS x (DT+1)
+  double *w_sh = rows_sh + SSP_STAGES * SSP_ROWS * (DT + 1);                      // SSP_TILE x DT
   double *delta_sh = w_sh + SSP_TILE * DT;                                        // SSP_TILE
-  int *idx_sh = reinterpret_cast<int *>(delta_sh + SSP_TILE);                     // SSP_ROWS local observation indices
-  int *site_sh = idx_sh + SSP_ROWS;                                               // SSP_TILE
+  double *part_sh = delta_sh + SSP_TILE;                                          // SSP_PART
+  double *acc_sh = part_sh + SSP_PART;                                            // SSP_TILE x 2
+  int *idx_sh = reinterpret_cast<int *>(acc_sh + SSP_TILE * 2);                   // SSP_STAGES x SSP_ROWS local observation indices
+  int *cnt_sh = idx_sh + SSP_STAGES * SSP_ROWS;                                   // SSP_STAGES x (SSP_WARPS + 1): per-warp counts, rows of the pass
+  int *site_sh = cnt_sh + SSP_STAGES * (SSP_WARPS + 1);                           // SSP_TILE
   int *pid_sh = site_sh + SSP_TILE;                                               // SSP_TILE
-  int *cnt_sh = pid_sh + SSP_TILE;                                                // 16: per-warp counts, totals
-  int *act_sh = cnt_sh + 16;                                                      // P: undecided particles, in order
+  int *act_sh = pid_sh + SSP_TILE;                                                // P: undecided particles, in order
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int D = a.D;
   const int64_t P = a.P;
   fm_fill_smem_tables(log_tbl, exp_tbl);
   const uint32_t exp_base = (uint32_t)__cvta_generic_to_shared(exp_tbl) + (uint32_t)(lane & 15) * 8u;
   const uint32_t log_base = (uint32_t)__cvta_generic_to_shared(log_tbl) + (uint32_t)(lane & 7) * 16u;
-  unsigned int epoch = 0;
+  unsigned long long epoch = 0;
   unsigned long long seq = *(volatile unsigned long long *)a.seq_dev;
   const double Nd = (double)a.Nt;
+  // positions of a full minibatch per CTA, and the passes that takes (the same count for a short last round)
+  const int64_t C_full = (a.Nbatch + gridDim.x - 1) / gridDim.x;
+  const int ppr = (int)((C_full + SSP_ROWS - 1) / SSP_ROWS) > 0 ? (int)((C_full + SSP_ROWS - 1) / SSP_ROWS) : 1;
   __syncthreads();
 
+  const bool prof = a.prof != nullptr && blockIdx.x == 0 && tid == 0;
+  unsigned long long tp = prof ? p2p_now_ns() : 0ull;
+#define SSP_PROF(slot) do { if (prof) { const unsigned long long now_ = p2p_now_ns(); a.prof[slot] += now_ - tp; tp = now_; } } while (0)
   for (int t = 0; t < a.n_transitions; ++t) {
     const uint32_t step = a.step0 + (uint32_t)t;
+    // the status array alternates between transitions: a CTA that is already proposing transition t + 1 must not
+    // disturb a slower CTA that is still reading the statuses of transition t; the LAST transition uses S.status
+    int *status = ((a.n_transitions - 1 - t) & 1) ? a.status_alt : a.S.status;
     // ---- global proposal (:79-88,102), one thread per particle
     for (int64_t p = (int64_t)blockIdx.x * SSP_THREADS + tid; p < P; p += (int64_t)gridDim.x * SSP_THREADS) {
       Stream r(a.seed, (uint64_t)(a.p_base + p), step);
@@ -150,9 +187,10 @@ __global__ void __launch_bounds__(SSP_THREADS, 2) ss_persistent_kernel(const SSP
       }
       a.S.site[p] = j; a.S.w_new[p] = w_new; a.S.delta[p] = w_new - w_old;
       a.S.mu0[p] = (log_u - 0.0) / Nd;
-      a.S.cum[p] = 0.0; a.S.cum2[p] = 0.0; a.S.n[p] = 0.0; a.S.k[p] = 0.0; a.S.tstat[p] = 0.0; a.S.status[p] = 0;
+      a.S.cum[p] = 0.0; a.S.cum2[p] = 0.0; a.S.n[p] = 0.0; a.S.k[p] = 0.0; a.S.tstat[p] = 0.0; status[p] = 0;
     }
     if (!ssp_grid_barrier(a, epoch)) return;
+    SSP_PROF(6);
     const FeistelKey key = make_feistel_key(a.seed, step, (uint64_t)a.Nt);
     int64_t q_done = 0;       // permutation positions covered by the rounds evaluated so far
     int k_done = 0;           // minibatches evaluated so far
@@ -161,7 +199,7 @@ __global__ void __launch_bounds__(SSP_THREADS, 2) ss_persistent_kernel(const SSP
       int nA = 0;
       for (int64_t p0 = 0; p0 < P; p0 += SSP_THREADS) {
         const int64_t p = p0 + tid;
-        const bool und = p < P && ((volatile int *)a.S.status)[p] == 0;
+        const bool und = p < P && ((volatile int *)status)[p] == 0;
         const unsigned bal = __ballot_sync(0xffffffffu, und);
         if (lane == 0) cnt_sh[warp] = __popc(bal);
         __syncthreads();
@@ -174,108 +212,234 @@ __global__ void __launch_bounds__(SSP_THREADS, 2) ss_persistent_kernel(const SSP
       }
       if (nA == 0) break;
       const int64_t rounds_left = (a.Nt - q_done + a.Nbatch - 1) / a.Nbatch;
-      int G = k_done == 0 ? a.G_first : a.G_next;
+      int G;
+      if (k_done == 0) G = a.G_first;
+      else { G = a.G_work / nA; if (G < a.G_min) G = a.G_min; if (G > SSP_GMAX) G = SSP_GMAX; }
       if ((int64_t)G > rounds_left) G = (int)rounds_left;
-      // ---- evaluate G rounds
-      for (int g = 0; g < G; ++g) {
-        const int64_t q0 = q_done + (int64_t)g * a.Nbatch;
-        const int64_t q1 = q0 + a.Nbatch < a.Nt ? q0 + a.Nbatch : a.Nt;
-        const int64_t C = (q1 - q0 + gridDim.x - 1) / gridDim.x;
-        const int64_t qa = q0 + (int64_t)blockIdx.x * C;
-        const int64_t qb = qa + C < q1 ? qa + C : q1;
-        double *part_g = a.partial + (((size_t)blockIdx.x * SSP_GMAX + g) * (size_t)P) * 2;
-        bool first_pass = true;
-        for (int64_t qs = qa; first_pass || qs < qb; qs += SSP_ROWS) {
-          // rows of this rank among positions [qs, qs + SSP_ROWS), compacted in position order
-          int64_t i = -1;
-          if (qs + tid < qb) {
-            i = (int64_t)feistel_perm((uint64_t)(qs + tid), key) - a.obs_lo;
-            if (i < 0 || i >= a.N_local) i = -1;
+      const int n_pass = G * ppr;
+      const bool direct = DT <= 16 && nA <= SSP_DIRECT;
+      SSP_PROF(0);
+      if (prof) { a.prof[direct ? 9 : 8] += 1; a.prof[direct ? 11 : 10] += (unsigned long long)G; a.prof[12] += (unsigned long long)nA; }
+      if (direct) {
+        // ---- few stragglers: ONE THREAD PER POSITION.  Rows go from L2/HBM straight into registers (the next
+        // position's row is in flight while the current one is evaluated); per round, the warps' sums are combined
+        // in warp order.  Same partial layout as the staged path below.
+        const int nT = nA;
+        for (int e = tid; e < SSP_DIRECT * DT; e += SSP_THREADS) {
+          const int sl = e / DT, j = e - sl * DT;
+          w_sh[e] = (sl < nT && j < D) ? a.w[(int64_t)j * P + act_sh[sl]] : 0.0;
+        }
+        if (tid < SSP_DIRECT) {
+          const int p = tid < nT ? act_sh[tid] : 0;
+          pid_sh[tid] = p;
+          delta_sh[tid] = tid < nT ? a.S.delta[p] : 0.0;
+          site_sh[tid] = tid < nT ? a.S.site[p] : 0;
+        }
+        __syncthreads();
+        const int ppr2 = (int)((C_full + SSP_THREADS - 1) / SSP_THREADS) > 0 ? (int)((C_full + SSP_THREADS - 1) / SSP_THREADS) : 1;
+        const int n_items = G * ppr2;
+        auto fetch = [&](int it, double (&x)[DT]) -> bool {
+          const int g = it / ppr2, kk = it - g * ppr2;
+          const int64_t q0 = q_done + (int64_t)g * a.Nbatch;
+          const int64_t q1 = q0 + a.Nbatch < a.Nt ? q0 + a.Nbatch : a.Nt;
+          const int64_t Cg = (q1 - q0 + gridDim.x - 1) / gridDim.x;
+          const int64_t qa = q0 + (int64_t)blockIdx.x * Cg;
+          const int64_t qb = qa + Cg < q1 ? qa + Cg : q1;
+          const int64_t q = qa + (int64_t)kk * SSP_THREADS + tid;
+          int64_t i_loc = -1;
+          if (it < n_items && q < qb) {
+            i_loc = (int64_t)feistel_perm((uint64_t)q, key) - a.obs_lo;
+            if (i_loc < 0 || i_loc >= a.N_local) i_loc = -1;
           }
-          const unsigned bal = __ballot_sync(0xffffffffu, i >= 0);
-          if (lane == 0) cnt_sh[warp] = __popc(bal);
+          if (i_loc >= 0) {
+            const double *row = a.Xr + i_loc * D;
+            if ((D & 1) == 0) {          // rows start on 16-byte boundaries
+#pragma unroll
+              for (int j = 0; j < DT; j += 2) {
+                double2 v = make_double2(0.0, 0.0);
+                if (j < D) v = __ldg(reinterpret_cast<const double2 *>(row + j));
+                x[j] = v.x; x[j + 1] = v.y;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < DT; ++j) x[j] = j < D ? __ldg(row + j) : 0.0;
+            }
+          }
+          return i_loc >= 0;
+        };
+        double a1[SSP_DIRECT], a2[SSP_DIRECT];
+#pragma unroll
+        for (int sl = 0; sl < SSP_DIRECT; ++sl) { a1[sl] = 0.0; a2[sl] = 0.0; }
+        auto consume = [&](int it, bool ok, const double (&x)[DT]) {
+          if (ok) {
+#pragma unroll
+            for (int sl = 0; sl < SSP_DIRECT; ++sl) {
+              if (sl < nT) {
+                const double *wv = w_sh + sl * DT;
+                const int site = site_sh[sl];
+                double eta = 0.0, xs = 0.0;
+#pragma unroll
+                for (int j = 0; j < DT; ++j) { eta = fma(wv[j], x[j], eta); xs = (j == site) ? x[j] : xs; }
+                const double v_new = fma(delta_sh[sl], xs, eta);
+                const double d = ssp_dllh(v_new, eta, a.cf, exp_base, log_base);
+                a1[sl] += d; a2[sl] = fma(d, d, a2[sl]);
+              }
+            }
+          }
+          const int g = it / ppr2;
+          if (it - g * ppr2 == ppr2 - 1) {        // the round's last position of this thread: warp sums -> scratch
+#pragma unroll
+            for (int sl = 0; sl < SSP_DIRECT; ++sl) {
+              if (sl < nT) {
+                const double u1 = warp_sum(a1[sl]), u2 = warp_sum(a2[sl]);
+                if (lane == 0) {
+                  double *dst = part_sh + (((size_t)g * SSP_DIRECT + sl) * SSP_WARPS + warp) * 2;
+                  dst[0] = u1; dst[1] = u2;
+                }
+                a1[sl] = 0.0; a2[sl] = 0.0;
+              }
+            }
+          }
+        };
+        double xa[DT], xb[DT];
+        bool oka = fetch(0, xa), okb = false;
+        for (int it = 0; it < n_items; it += 2) {
+          okb = fetch(it + 1, xb);
+          consume(it, oka, xa);
+          if (it + 1 < n_items) {
+            oka = fetch(it + 2, xa);
+            consume(it + 1, okb, xb);
+          }
+        }
+        __syncthreads();
+        for (int e = tid; e < G * nT * 2; e += SSP_THREADS) {
+          const int comp = e & 1, sl = (e >> 1) % nT, g = (e >> 1) / nT;
+          const double *src = part_sh + (((size_t)g * SSP_DIRECT + sl) * SSP_WARPS) * 2 + comp;
+          double sum = 0.0;
+#pragma unroll
+          for (int wv = 0; wv < SSP_WARPS; ++wv) sum += src[wv * 2];
+          a.partial[(((size_t)blockIdx.x * SSP_GMAX + g) * (size_t)P + (size_t)pid_sh[sl]) * 2 + comp] = sum;
+        }
+        __syncthreads();
+      } else
+      // ---- evaluate G rounds: a sweep over this CTA's passes per tile of undecided particles
+      for (int tile0 = 0; tile0 < nA; tile0 += SSP_TILE) {
+        const int nT = nA - tile0 < SSP_TILE ? nA - tile0 : SSP_TILE;
+        for (int e = tid; e < SSP_TILE * DT; e += SSP_THREADS) {
+          const int s = e / DT, j = e - s * DT;
+          w_sh[e] = (s < nT && j < D) ? a.w[(int64_t)j * P + act_sh[tile0 + s]] : 0.0;
+        }
+        if (tid < SSP_TILE) {
+          const int p = tid < nT ? act_sh[tile0 + tid] : 0;
+          pid_sh[tid] = p;
+          delta_sh[tid] = tid < nT ? a.S.delta[p] : 0.0;
+          site_sh[tid] = tid < nT ? a.S.site[p] : 0;
+        }
+        if (tid < SSP_TILE * 2) acc_sh[tid] = 0.0;
+        // stage pass i into ring slot i % SSP_STAGES: Feistel positions -> this rank's rows, compacted in position
+        // order -> asynchronous copies of the rows.  Every thread commits exactly one group per call.
+        auto stage = [&](int i) {
+          const int buf = i % SSP_STAGES;
+          const int g = i / ppr, kpass = i - g * ppr;
+          const int64_t q0 = q_done + (int64_t)g * a.Nbatch;
+          const int64_t q1 = q0 + a.Nbatch < a.Nt ? q0 + a.Nbatch : a.Nt;
+          const int64_t Cg = (q1 - q0 + gridDim.x - 1) / gridDim.x;
+          const int64_t qa = q0 + (int64_t)blockIdx.x * Cg;
+          const int64_t qb = qa + Cg < q1 ? qa + Cg : q1;
+          const int64_t q = qa + (int64_t)kpass * SSP_ROWS + tid;
+          int64_t i_loc = -1;
+          if (tid < SSP_ROWS && q < qb) {
+            i_loc = (int64_t)feistel_perm((uint64_t)q, key) - a.obs_lo;
+            if (i_loc < 0 || i_loc >= a.N_local) i_loc = -1;
+          }
+          int *cnt = cnt_sh + buf * (SSP_WARPS + 1);
+          int *idx = idx_sh + buf * SSP_ROWS;
+          const unsigned bal = __ballot_sync(0xffffffffu, i_loc >= 0);
+          if (lane == 0) cnt[warp] = __popc(bal);
           __syncthreads();
           int before = 0, n_rows = 0;
 #pragma unroll
-          for (int wv = 0; wv < SSP_WARPS; ++wv) { const int c = cnt_sh[wv]; if (wv < warp) before += c; n_rows += c; }
-          if (i >= 0) idx_sh[before + __popc(bal & ((1u << lane) - 1u))] = (int)i;
+          for (int wv = 0; wv < SSP_WARPS; ++wv) { const int c = cnt[wv]; if (wv < warp) before += c; n_rows += c; }
+          if (i_loc >= 0) idx[before + __popc(bal & ((1u << lane) - 1u))] = (int)i_loc;
+          if (tid == 0) cnt[SSP_WARPS] = n_rows;
           __syncthreads();
+          double *rows = rows_sh + (size_t)buf * SSP_ROWS * (DT + 1);
           for (int e = tid; e < n_rows * D; e += SSP_THREADS) {
             const int k = e / D, j = e - k * D;
-            rows_sh[k * (DT + 1) + j] = __ldg(&a.Xr[(int64_t)idx_sh[k] * D + j]);
+            ssp_cp_async8(&rows[k * (DT + 1) + j], &a.Xr[(int64_t)idx[k] * D + j]);
           }
-          for (int tile0 = 0; tile0 < nA; tile0 += SSP_TILE) {
-            __syncthreads();     // rows staged; previous tile's weights no longer read
-            for (int e = tid; e < SSP_TILE * DT; e += SSP_THREADS) {
-              const int s = e / DT, j = e - s * DT;
-              const int ai = tile0 + s;
-              w_sh[e] = (ai < nA && j < D) ? a.w[(int64_t)j * P + act_sh[ai]] : 0.0;
-            }
-            if (tid < SSP_TILE) {
-              const int ai = tile0 + tid;
-              const int p = ai < nA ? act_sh[ai] : 0;
-              pid_sh[tid] = p;
-              delta_sh[tid] = ai < nA ? a.S.delta[p] : 0.0;
-              site_sh[tid] = ai < nA ? a.S.site[p] : 0;
-            }
-            __syncthreads();
-            double acc1[SSP_PER_WARP], acc2[SSP_PER_WARP];
-#pragma unroll
-            for (int s = 0; s < SSP_PER_WARP; ++s) { acc1[s] = 0.0; acc2[s] = 0.0; }
-            for (int c0 = 0; c0 < n_rows; c0 += 32) {
-              const int r = c0 + lane;
+          ssp_cp_commit();
+        };
+        __syncthreads();
+        for (int i = 0; i < SSP_STAGES - 1; ++i) { if (i < n_pass) stage(i); else ssp_cp_commit(); }
+        for (int i = 0; i < n_pass; ++i) {
+          if (i + SSP_STAGES - 1 < n_pass) stage(i + SSP_STAGES - 1); else ssp_cp_commit();
+          ssp_cp_wait<SSP_STAGES - 1>();       // pass i's copies have landed (this thread's); the barrier makes it everyone's
+          __syncthreads();
+          const int buf = i % SSP_STAGES;
+          const int g = i / ppr;
+          const int n_rows = cnt_sh[buf * (SSP_WARPS + 1) + SSP_WARPS];
+          const int n_chunks = (n_rows + 31) >> 5;
+          if (n_chunks > 0) {
+            // warps_per_chunk warps share a 32-row chunk and split the tile's particles between them
+            const int wpc = SSP_WARPS / n_chunks;
+            const int c = warp / wpc, sub = warp - c * wpc;
+            if (c < n_chunks) {
+              const int r = c * 32 + lane;
               const bool valid = r < n_rows;
-              const double *row = rows_sh + (valid ? r : 0) * (DT + 1);
+              const double *row = rows_sh + (size_t)buf * SSP_ROWS * (DT + 1) + (valid ? r : 0) * (DT + 1);
               double x[DT];
 #pragma unroll
               for (int j = 0; j < DT; ++j) x[j] = (valid && j < D) ? row[j] : 0.0;
+              for (int slot = sub; slot < nT; slot += wpc) {
+                const double *wv = w_sh + slot * DT;
+                double eta = 0.0;
 #pragma unroll
-              for (int s = 0; s < SSP_PER_WARP; ++s) {
-                const int slot = warp + SSP_WARPS * s;            // interleaved: few particles spread over the warps
-                if (tile0 + slot < nA) {                          // warp-uniform
-                  const double *wv = w_sh + slot * DT;
-                  double eta = 0.0;
-#pragma unroll
-                  for (int j = 0; j < DT; ++j) eta = fma(wv[j], x[j], eta);
-                  const double xs = valid ? row[site_sh[slot]] : 0.0;
-                  const double v_new = fma(delta_sh[slot], xs, eta);
-                  double d = ssp_dllh(v_new, eta, a.cf, exp_base, log_base);
-                  if (!valid) d = 0.0;
-                  acc1[s] += d; acc2[s] = fma(d, d, acc2[s]);
-                }
-              }
-            }
-#pragma unroll
-            for (int s = 0; s < SSP_PER_WARP; ++s) {
-              const int slot = warp + SSP_WARPS * s;
-              if (tile0 + slot < nA) {
-                const double u1 = warp_sum(acc1[s]), u2 = warp_sum(acc2[s]);
-                if (lane == 0) {
-                  double *dst = part_g + (size_t)pid_sh[slot] * 2;
-                  if (first_pass) { dst[0] = u1; dst[1] = u2; } else { dst[0] += u1; dst[1] += u2; }
-                }
+                for (int j = 0; j < DT; ++j) eta = fma(wv[j], x[j], eta);
+                const double xs = valid ? row[site_sh[slot]] : 0.0;
+                const double v_new = fma(delta_sh[slot], xs, eta);
+                double d = ssp_dllh(v_new, eta, a.cf, exp_base, log_base);
+                if (!valid) d = 0.0;
+                const double u1 = warp_sum(d), u2 = warp_sum(d * d);
+                if (lane == 0) { part_sh[(c * SSP_TILE + slot) * 2] = u1; part_sh[(c * SSP_TILE + slot) * 2 + 1] = u2; }
               }
             }
           }
-          __syncthreads();       // before idx_sh / rows_sh / w_sh are overwritten
-          first_pass = false;
+          __syncthreads();
+          // chunk sums -> the round's running sums, in chunk order; the last pass of a round publishes them
+          if (tid < nT * 2) {
+            double s = acc_sh[tid];
+            for (int c = 0; c < n_chunks; ++c) s += part_sh[c * SSP_TILE * 2 + tid];
+            if (i - g * ppr == ppr - 1) {
+              a.partial[(((size_t)blockIdx.x * SSP_GMAX + g) * (size_t)P + (size_t)pid_sh[tid >> 1]) * 2 + (tid & 1)] = s;
+              s = 0.0;
+            }
+            acc_sh[tid] = s;
+          }
+          // part_sh is rewritten only after the next pass's barriers
         }
+        __syncthreads();       // before w_sh / pid_sh of the next tile are written
       }
+      SSP_PROF(direct ? 2 : 1);
       if (!ssp_grid_barrier(a, epoch)) return;
+      SSP_PROF(3);
       // ---- decide: the handler of an undecided particle is warp 0 of CTA (list index mod grid)
-      if (warp == 0) {
-        for (int ai = blockIdx.x; ai < nA; ai += gridDim.x) {
-          const int64_t p = act_sh[ai];
-          double my1 = 0.0, my2 = 0.0;
-          for (int g = 0; g < G; ++g) {
-            double s1 = 0.0, s2 = 0.0;
-            for (int bb = lane; bb < (int)gridDim.x; bb += 32) {
-              const double *src = a.partial + (((size_t)bb * SSP_GMAX + g) * (size_t)P + (size_t)p) * 2;
-              s1 += __ldcg(src); s2 += __ldcg(src + 1);
-            }
-            s1 = warp_sum(s1); s2 = warp_sum(s2);
-            if (lane == g) { my1 = s1; my2 = s2; }
+      for (int ai = blockIdx.x; ai < nA; ai += gridDim.x) {          // CTA-uniform loop
+        const int64_t p = act_sh[ai];
+        // every warp sums the CTAs' partials of some rounds (fixed order: lane-strided, then the shuffle tree)
+        for (int g = warp; g < G; g += SSP_WARPS) {
+          double s1 = 0.0, s2 = 0.0;
+          for (int bb = lane; bb < (int)gridDim.x; bb += 32) {
+            const double2 v = __ldcg(reinterpret_cast<const double2 *>(a.partial + (((size_t)bb * SSP_GMAX + g) * (size_t)P + (size_t)p) * 2));
+            s1 += v.x; s2 += v.y;
           }
+          s1 = warp_sum(s1); s2 = warp_sum(s2);
+          if (lane == 0) { acc_sh[2 * g] = s1; acc_sh[2 * g + 1] = s2; }
+        }
+        __syncthreads();
+        if (warp == 0) do {
+          double my1 = 0.0, my2 = 0.0;
+          if (lane < G) { my1 = acc_sh[2 * lane]; my2 = acc_sh[2 * lane + 1]; }
           if (a.world > 1) {
             const int parity = (int)(seq & 1ull);
             if (lane < G) {
@@ -296,12 +460,12 @@ __global__ void __launch_bounds__(SSP_THREADS, 2) ss_persistent_kernel(const SSP
               int spins = 0;
               while (*mine != seq + 1ull) {
                 if ((++spins & 63) == 0 &&
-                    ((long long)(p2p_now_ns() - t0) > a.timeout_ns || *(volatile int *)a.abort_flag)) { bad = 1; break; }
+                    ((long long)(p2p_now_ns() - t0) > a.timeout_ns || ssp_aborted(a))) { bad = 1; break; }
               }
             }
             bad = __any_sync(0xffffffffu, bad);
             if (bad) {
-              if (lane == 0) { a.par->err = 1; *a.err_host = 1; *(volatile int *)a.abort_flag = 1; __threadfence_system(); }
+              if (lane == 0) { a.par->err = 1; *a.err_host = 1; ssp_set_abort(a); }
               break;
             }
             __threadfence_system();
@@ -361,18 +525,22 @@ __global__ void __launch_bounds__(SSP_THREADS, 2) ss_persistent_kernel(const SSP
               if (st_f == 1) { a.w[(int64_t)a.S.site[p] * P + p] = a.S.w_new[p]; a.S.acc_total[p] += 1.0; }
               a.S.n_total[p] += n_f;
             }
-            a.S.status[p] = st_f;
+            status[p] = st_f;
           }
-        }
+        } while (false);
+        __syncthreads();             // acc_sh is reused by the next particle of this handler
       }
       q_done += (int64_t)G * a.Nbatch;
       if (q_done > a.Nt) q_done = a.Nt;
       k_done += G;
       if (a.world > 1) ++seq;
+      SSP_PROF(4);
       if (!ssp_grid_barrier(a, epoch)) return;
+      SSP_PROF(5);
     }
   }
   if (blockIdx.x == 0 && tid == 0) *a.seq_dev = seq;
+#undef SSP_PROF
 }
 
 // ---- host: t.ppf(1 - eps, df) by Newton on the exact cdf (same incomplete-beta code as the device) --------

@@ -450,8 +450,8 @@ struct BLRModel : Model {
   int *ss_active_host = nullptr;
   // persistent subsampled-MH kernel (blr_subsampled_persistent.cuh)
   DevBuf<double> ssp_partial, ssp_tcrit;
-  DevBuf<unsigned int> ssp_bar;
-  DevBuf<unsigned long long> ssp_seq;
+  DevBuf<unsigned long long> ssp_bar;
+  DevBuf<unsigned long long> ssp_seq, ssp_prof;
   int *ssp_abort_host = nullptr, *ssp_abort_dev = nullptr;     // mapped pinned: a timed-out barrier / exchange
   std::vector<double> tcrit_host;
   int64_t tcrit_Nbatch = -1, tcrit_Nt = -1; double tcrit_eps = -1.0; int tcrit_k0 = -1;
@@ -531,7 +531,8 @@ struct BLRModel : Model {
       Xr_rows = prm.N;
     }
     if (!ss_d.p) {
-      ss_d.alloc((size_t)h->P * 11); ss_i.alloc((size_t)h->P * 2 + 2);   // site, status, n_active (= gate), block counter
+      // site, status, n_active (= gate), block counter, second status array of the persistent kernel
+      ss_d.alloc((size_t)h->P * 11); ss_i.alloc((size_t)h->P * 3 + 2);
       VK_CUDA(cudaMemsetAsync(ss_i.p, 0, ss_i.bytes(), h->stream));
       ss_sums.alloc((size_t)h->P * 2);
       VK_CUDA(cudaMallocHost((void **)&ss_active_host, sizeof(int)));
@@ -688,24 +689,44 @@ struct BLRModel : Model {
     a.block_mode = block; a.n_transitions = n_steps; a.delta_mode = delta_mode; a.delta_eps = delta_arg;
     a.mu0_prior = prm.mu0; a.s0_prior = prm.s0; a.seed = h->seed; a.step0 = h->next_step((uint32_t)n_steps);
     a.tcrit = ssp_tcrit.p; a.n_tcrit = (int)tcrit_host.size();
-    a.bar = ssp_bar.p; a.abort_flag = ssp_abort_dev; a.seq_dev = ssp_seq.p; a.cf = fm_coef;
+    a.bar = ssp_bar.p; a.abort_host = ssp_abort_dev; a.seq_dev = ssp_seq.p; a.cf = fm_coef;
+    a.status_alt = ss_i.p + 2 * h->P + 2;
     P2PSSView v;
     const bool peers = N_total >= 0 && p2p_ss_view(h, &v) && v.world > 1;
-    a.world = 1; a.rank = 0; a.timeout_ns = 20000000000ll;
+    a.world = 1; a.rank = 0; a.timeout_ns = 10000000000ll;
     if (peers) {
       a.tab = v.tab; a.par = v.par; a.err_host = v.err_host_dev; a.world = v.world; a.rank = v.rank;
       a.ss_stride = v.ss_stride; a.ss_pcap = v.ss_pcap; a.timeout_ns = v.timeout_ns;
     }
-    static const int g_env = getenv("VK_SS_ROUNDS_PER_BATCH") ? atoi(getenv("VK_SS_ROUNDS_PER_BATCH")) : 0;
+    // rounds evaluated per batch (speculation past the deciding round is discarded): the fewer particles are
+    // still undecided, the more rounds a batch holds -- the work per batch stays near G_work particle-rounds
+    static const int g_min_env = getenv("VK_SS_ROUNDS_PER_BATCH") ? atoi(getenv("VK_SS_ROUNDS_PER_BATCH")) : 0;
+    static const int g_work_env = getenv("VK_SS_BATCH_WORK") ? atoi(getenv("VK_SS_BATCH_WORK")) : 0;
     a.G_first = k0 < 1 ? 1 : (k0 > SSP_GMAX ? SSP_GMAX : k0);
-    a.G_next = g_env > 0 ? (g_env > SSP_GMAX ? SSP_GMAX : g_env) : (peers ? 4 : 2);
+    a.G_min = g_min_env > 0 ? (g_min_env > SSP_GMAX ? SSP_GMAX : g_min_env) : (peers ? 4 : 2);
+    a.G_work = g_work_env > 0 ? g_work_env : 128;
     VK_CUDA(cudaMemsetAsync(ssp_bar.p, 0, ssp_bar.bytes(), h->stream));
+    static const bool profile = getenv("VK_SS_PROFILE") != nullptr;       // phase times of CTA 0, printed per call
+    if (profile) {
+      if (!ssp_prof.p) ssp_prof.alloc(16);
+      VK_CUDA(cudaMemsetAsync(ssp_prof.p, 0, ssp_prof.bytes(), h->stream));
+      a.prof = ssp_prof.p;
+    }
     if (prm.D <= 4) ss_launch_persistent<4>(a);
     else if (prm.D <= 8) ss_launch_persistent<8>(a);
     else if (prm.D <= 16) ss_launch_persistent<16>(a);
     else ss_launch_persistent<32>(a);
     VK_CUDA(cudaGetLastError());
     eta_dirty = true;
+    if (profile) {
+      unsigned long long pr[16];
+      VK_CUDA(cudaMemcpyAsync(pr, ssp_prof.p, sizeof pr, cudaMemcpyDeviceToHost, h->stream));
+      VK_CUDA(cudaStreamSynchronize(h->stream));
+      fprintf(stderr, "[vk ss profile] transitions %d | us: propose+bar %.1f list %.1f eval_staged %.1f eval_direct %.1f bar_eval %.1f decide %.1f "
+                      "bar_decide %.1f | batches staged %llu (rounds %llu) direct %llu (rounds %llu) mean undecided %.2f\n", n_steps,
+              pr[6] * 1e-3, pr[0] * 1e-3, pr[1] * 1e-3, pr[2] * 1e-3, pr[3] * 1e-3, pr[4] * 1e-3, pr[5] * 1e-3, pr[8], pr[10], pr[9], pr[11],
+              (pr[8] + pr[9]) ? (double)pr[12] / (double)(pr[8] + pr[9]) : 0.0);
+    }
   }
   bool ss_persistent_ok() const {
     static const int off = getenv("VK_SS_HOST_LOOP") ? atoi(getenv("VK_SS_HOST_LOOP")) : 0;

@@ -22,7 +22,7 @@ namespace vk {
 static const int P2P_MAX_WORLD = 16;
 static const int P2P_MAX_ARRAYS = 4;
 static const int P2P_PHASES = 2;          // 0: (max, min, NaN flag) of the weights; 1: (sum exp, live buffer, mass)
-static const int P2P_SS_MAX_ROUNDS = 8;   // minibatch rounds evaluated per subsampled-MH exchange
+static const int P2P_SS_MAX_ROUNDS = 16;   // minibatch rounds evaluated per subsampled-MH exchange
 
 struct P2PMail {                       // 32 bytes, written by ONE sender into its slot of a peer's mailbox
   unsigned long long seq;              // written last (after a system fence): number of this exchange, from 1

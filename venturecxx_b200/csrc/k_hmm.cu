@@ -421,9 +421,11 @@ struct HMMModel : Model {
       P2PXchg xchg;
       xchg.tab = nullptr;
       if (last) x0 = p2p_begin_exchange(h, 0, &xchg);      // sharded particle set: exchange 0 rides in this kernel's tail
+      h->prof.mark(h->stream, "(gap)");
       hmm_step_kernel<<<step_grid(), 256, smem_step, h->stream>>>(cur, hist, Tpad, T, h->lw.p, incr_dev, tb, step_tables.p,
                                                              symbols_host[T], h->P, h->p_base, h->seed, step,
                                                              first ? 0 : 1, h->red.p, h->counters.p, last ? 0 : 1, xchg);
+      h->prof.mark(h->stream, x0 ? "hmm_step+xchg0" : "hmm_step");
       first = false;
     }
     hist_pending = true;

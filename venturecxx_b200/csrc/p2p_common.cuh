@@ -1,8 +1,9 @@
 // Peer-memory plumbing shared by the sharded resample (p2p_resample.cuh) and the
 // observation-sharded subsampled MH (blr_subsampled.cuh, E3): the ranks of one NVSwitch node (one process per
 // GPU) open each other's buffers once through CUDA IPC; afterwards scalars travel through MAILBOXES in peer
-// memory -- the sender stores its payload into its slot of every peer's mailbox, fences system-wide, then
-// stores the exchange's sequence number; the receiver spins on its own (local) mailbox -- and bulk state moves
+// memory -- the sender stores its payload into its slot of every peer's mailbox as 8-byte words that each carry
+// the exchange's number next to 32 bits of payload (no fence, no ordering between the words); the receiver spins
+// on its own (local) mailbox until every word shows the expected number -- and bulk state moves
 // with plain peer loads / stores over NVLink.  No collective and no host round trip on either path.
 //
 // An exchange is executed by ONE warp, and it runs in the TAIL of the kernel that produced the payload (the
@@ -24,10 +25,12 @@ static const int P2P_MAX_ARRAYS = 4;
 static const int P2P_PHASES = 2;          // 0: (max, min, NaN flag) of the weights; 1: (sum exp, live buffer, mass)
 static const int P2P_SS_MAX_ROUNDS = 16;   // minibatch rounds evaluated per subsampled-MH exchange
 
-struct P2PMail {                       // 32 bytes, written by ONE sender into its slot of a peer's mailbox
-  unsigned long long seq;              // written last (after a system fence): number of this exchange, from 1
-  double a, b;
-  unsigned long long c;
+struct P2PMail {                       // 64 bytes, written by ONE sender into its slot of a peer's mailbox
+  // six 8-byte words {payload word (low 32 bits), exchange number (high 32 bits)}: an aligned 8-byte store is
+  // atomic, so a word whose high half equals the expected number carries valid data -- no fence between
+  // "payload" and "flag", no ordering between the words (the LL protocol of collective libraries)
+  unsigned long long w[6];
+  unsigned long long pad[2];
 };
 struct P2PParams {                     // device-resident results of the exchanges
   unsigned long long offset, total;    // this rank's mass offset, global mass
@@ -81,22 +84,32 @@ p2p_exchange_warp(const P2PXchg &x, double *red, const uint64_t *tile_sums, int 
   if (phase == 0) { a = red[0]; b = red[1]; c = red[2] != 0.0 ? 1ull : 0ull; }
   else { a = red[3]; b = (double)x.my_cur_idx; c = tile_sums[n_tiles]; }
   int bad = ((volatile P2PParams *)x.par)->err != 0;
+  const unsigned long long flag = (x.seq & 0xffffffffull) << 32;
   if (lane < x.world && !bad) {
     volatile P2PMail *dst = x.tab->mail[lane] + p2p_mail_index(parity, phase, x.rank);
-    dst->a = a; dst->b = b; dst->c = c;
-    __threadfence_system();
-    dst->seq = x.seq;
+    const unsigned long long ua = (unsigned long long)__double_as_longlong(a), ub = (unsigned long long)__double_as_longlong(b);
+    dst->w[0] = (ua & 0xffffffffull) | flag; dst->w[1] = (ua >> 32) | flag;
+    dst->w[2] = (ub & 0xffffffffull) | flag; dst->w[3] = (ub >> 32) | flag;
+    dst->w[4] = (c & 0xffffffffull) | flag;  dst->w[5] = (c >> 32) | flag;
   }
   double ra = 0.0, rb = 0.0;
   unsigned long long rc = 0ull;
   if (lane < x.world && !bad) {
     volatile P2PMail *src = x.tab->mail[x.rank] + p2p_mail_index(parity, phase, lane);
     const unsigned long long t0 = p2p_now_ns();
-    while (src->seq != x.seq) {
-      if ((long long)(p2p_now_ns() - t0) > x.timeout_ns) { bad = 1; break; }
-      __nanosleep(40);
+    unsigned long long v[6];
+    int have = 0, spins = 0;
+    while (have != 0x3f) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k)
+        if (!((have >> k) & 1)) { v[k] = src->w[k]; if ((v[k] & 0xffffffff00000000ull) == flag) have |= 1 << k; }
+      if (have != 0x3f && (++spins & 15) == 0 && (long long)(p2p_now_ns() - t0) > x.timeout_ns) { bad = 1; break; }
     }
-    if (!bad) { __threadfence_system(); ra = src->a; rb = src->b; rc = src->c; }
+    if (!bad) {
+      ra = __longlong_as_double((long long)((v[0] & 0xffffffffull) | (v[1] << 32)));
+      rb = __longlong_as_double((long long)((v[2] & 0xffffffffull) | (v[3] << 32)));
+      rc = (v[4] & 0xffffffffull) | (v[5] << 32);
+    }
   }
   bad = __any_sync(0xffffffffu, bad);
   if (bad) {

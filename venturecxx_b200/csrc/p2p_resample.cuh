@@ -185,7 +185,7 @@ __device__ __forceinline__ int64_t p2p_wait_ancestor(const int32_t *anc_g, int64
       if (((volatile P2PParams *)par)->err) return -1;
       if ((long long)(p2p_now_ns() - t0) > timeout_ns) { par->err = 1; *err_host = 1; __threadfence_system(); return -1; }
     }
-    __nanosleep(100);
+    __nanosleep(20);
   }
   return g;
 }
@@ -406,15 +406,18 @@ void p2p_resample(vk_particles *h, int mode) {
   if (h->red_u.n < (size_t)n_tiles + 1) h->red_u.alloc((size_t)n_tiles + 1);
   if (h->tile_exp.n < (size_t)n_tiles) h->tile_exp.alloc((size_t)n_tiles);
   P2PXchg x;
+  h->prof.mark(st, "(gap)");
   if (!(h->lw_minmax_fresh && h->lw_x0_done)) {     // the producer of the weights did not run exchange 0 itself
     p2p_begin_exchange(h, 0, &x);
     lse_pass1_xchg_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p, x);
+    h->prof.mark(st, "lse_pass1+xchg0");
   }
   h->lw_minmax_fresh = false; h->lw_x0_done = false;
   p2p_begin_exchange(h, 1, &x);
   x.my_cur_idx = cur_idx;
   p2p_tile_sums_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p, n_tiles,
                                                          h->counters.p + 2, x);
+  h->prof.mark(st, "p2p_tile_sums+xchg1");
   if (mode == VK_RESAMPLE_SYSTEMATIC) {
     p2p_offspring_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, s->par.p, s->tab.p,
                                                            half, P_total, h->p_base, h->seed, step);
@@ -423,6 +426,7 @@ void p2p_resample(vk_particles *h, int mode) {
     p2p_multinomial_kernel<<<grid_for(P_total, 256, h->sm_count, 8), 256, 0, st>>>(h->cdf.p, P, s->par.p, s->tab.p, half,
                                                                                   P_total, h->p_base, h->seed, step);
   }
+  h->prof.mark(st, mode == VK_RESAMPLE_SYSTEMATIC ? "p2p_offspring" : "cdf+p2p_multinomial");
   P2PArrays pa;
   memset(&pa, 0, sizeof pa);
   pa.n = s->n_arrays;
@@ -441,6 +445,7 @@ void p2p_resample(vk_particles *h, int mode) {
   }
   p2p_gather_kernel<<<grid_for(work, 256, h->sm_count, 8), 256, 0, st>>>(s->anc_g.p + (int64_t)half * P, P, s->tab.p,
                                                                          s->par.p, pa);
+  h->prof.mark(st, "p2p_gather");
   VK_CUDA(cudaGetLastError());
   for (auto &a : arrs) { void *t = *a.cur; *a.cur = *a.alt; *a.alt = t; }
   h->model->after_resample();

@@ -60,6 +60,7 @@ static vk_particles *new_handle(int kind, int64_t P, uint64_t seed, int device) 
   vk_particles *h = new vk_particles();
   try {
     h->kind = kind; h->device = device; h->P = P; h->seed = seed;
+    h->prof.on = getenv("VK_PROFILE") != nullptr;
     VK_CUDA(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device));
     VK_CUDA(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
     h->stream = h->own_stream;
@@ -146,6 +147,8 @@ int vk_destroy(vk_particles *h) {
   if (!h) return VK_OK;
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
+  h->prof.resolve();
+  { char who[64]; snprintf(who, sizeof who, "rank %s dev %d", getenv("RANK") ? getenv("RANK") : "-", h->device); h->prof.report(who); }
   vk::p2p_release(h);
   delete h->model; h->model = nullptr;
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -170,6 +173,7 @@ int vk_set_stream(vk_particles *h, void *cuda_stream) {
 int vk_synchronize(vk_particles *h) {
   VK_TRY check_handle(h); use_device(h);
   VK_CUDA(cudaStreamSynchronize(h->stream));
+  h->prof.resolve();
   vk::p2p_check_error(h);
   VK_CATCH
 }
@@ -232,6 +236,7 @@ int vk_get_log_weights(vk_particles *h, double *out_host) {
   VK_REQUIRE(out_host, VK_EINVAL, "out_host is NULL");
   VK_CUDA(cudaMemcpyAsync(out_host, h->lw.p, h->lw.bytes(), cudaMemcpyDeviceToHost, h->stream));
   VK_CUDA(cudaStreamSynchronize(h->stream));
+  h->prof.resolve();
   vk::p2p_check_error(h);
   VK_CATCH
 }

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <map>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -72,6 +73,43 @@ struct StateArray {
 
 struct Model;
 
+// Per-kernel timing of a stream (VK_PROFILE=1): events between launches, resolved after a synchronisation.
+// The interval that ENDS at a mark carries the mark's name; "(gap)" marks end host-side gaps.
+struct StreamProfile {
+  bool on = false;
+  std::vector<std::pair<const char *, cudaEvent_t>> marks;
+  std::vector<cudaEvent_t> pool;
+  std::map<std::string, std::pair<double, long long>> totals;
+  void mark(cudaStream_t st, const char *name) {
+    if (!on) return;
+    cudaEvent_t e;
+    if (pool.empty()) cudaEventCreate(&e); else { e = pool.back(); pool.pop_back(); }
+    cudaEventRecord(e, st);
+    marks.push_back(std::make_pair(name, e));
+  }
+  void resolve() {                       // call after the stream drained
+    if (!on) return;
+    for (size_t i = 1; i < marks.size(); ++i) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, marks[i - 1].second, marks[i].second) == cudaSuccess) {
+        auto &t = totals[marks[i].first];
+        t.first += ms; t.second += 1;
+      }
+    }
+    if (!marks.empty()) {
+      for (size_t i = 0; i + 1 < marks.size(); ++i) pool.push_back(marks[i].second);
+      marks.erase(marks.begin(), marks.end() - 1);
+    }
+  }
+  void report(const char *who) {
+    if (!on || totals.empty()) return;
+    fprintf(stderr, "[vk profile %s] interval: count, mean us\n", who);
+    for (auto &kv : totals)
+      fprintf(stderr, "[vk profile %s]   %-28s %8lld %10.2f\n", who, kv.first.c_str(), kv.second.second,
+              1e3 * kv.second.first / (double)kv.second.second);
+  }
+};
+
 }  // namespace vk
 
 // The opaque handle of include/venture_b200.h.
@@ -103,6 +141,7 @@ struct vk_particles {
   // peer-memory resample (p2p_common.cuh); same lifetime as lw_minmax_fresh
   bool lw_x0_done = false;
   void *p2p = nullptr;          // vk::P2P (p2p_resample.cuh): peer-memory resampling state
+  vk::StreamProfile prof;       // VK_PROFILE=1
   uint32_t next_step(uint32_t n = 1) { uint32_t s = step; step += n; return s; }
 };
 

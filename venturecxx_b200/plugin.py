@@ -2,11 +2,26 @@
 
 Loaded the way the reference loads plugins: `ripl.load_plugin(path, *args)`
 imports the file and calls `__venture_start__(ripl, *args)`
-(python/lib/ripl/ripl.py:1093-1096).  Inside, a plugin registers callbacks
-with `ripl.bind_callback(name, fn)` (ripl.py:941-947); the engine invokes
-them from an inference program as `(call_back name args...)` with the
-signature `fn(inferrer, *args)` where every arg is the list of that
-expression's value in each particle (python/lib/engine/inference.py:166-177).
+(python/lib/ripl/ripl.py:1093-1096).  Inside, the plugin
+
+  * binds FOREIGN INFERENCE SPs with `ripl.bind_foreign_inference_sp(name, sp)`
+    (ripl.py:938-939 -> engine/engine.py:56-59) whenever the host Venture's
+    `venture.lite.inference_sps` is importable: `b200_resample`,
+    `b200_likelihood_weight`, `b200_incorporate`, `b200_resimulation_mh` / `b200_mh`,
+    `b200_gibbs`, `b200_subsampled_mh`, `b200_log_likelihood_at`, `b200_log_joint_at`
+    with the SP types of backend/lite/inference_sps.py:234-241, 253-267, 536-551, 602-606,
+    678-694 (built with that module's own `sequenced_sp` / `transition_oper_type` /
+    `infer_action_maker_type`), so `(b200_resimulation_mh default one 160)` is an
+    inference action like the builtin; with `override_builtins=True` the builtin NAMES
+    (`resample`, `likelihood_weight`, `resimulation_mh`, `mh`, `gibbs`, `subsampled_mh`, ...)
+    are rebound too and user programs run unchanged on the batch;
+  * registers callbacks with `ripl.bind_callback(name, fn)` (ripl.py:941-947); the
+    engine invokes them from an inference program as `(call_back name args...)` with the
+    signature `fn(inferrer, *args)` where every arg is the list of that expression's
+    value in each particle (python/lib/engine/inference.py:166-177).
+
+(The other route -- the reference's Engine over the B200 BACKEND, where the builtin
+inference SPs reach the batch through TraceSet -- is backend.py.)
 
 The callbacks forward to ONE device-resident B200TraceSet with the argument
 meaning of the reference's inference SPs:
@@ -86,12 +101,83 @@ class B200Plugin(object):
         return dict((PREFIX + n, getattr(self, n)) for n in names)
 
 
-def __venture_start__(ripl, model=None, n_particles=1, seed=1, device=0, trace_set=None):
+def _python_value(v):
+    """operand of an inference SP (a VentureValue of the host) -> python value"""
+    if hasattr(v, "asStackDict"):
+        v = v.asStackDict()
+    v = _scalar(v)
+    if isinstance(v, float) and v == int(v):
+        return int(v)
+    return v
+
+
+def inference_sps(plugin):
+    """name -> SP for ripl.bind_foreign_inference_sp, or {} when the host Venture is not importable.
+    The SP types are the reference's own (backend/lite/inference_sps.py)."""
+    try:
+        import venture.lite.inference_sps as inf
+        import venture.lite.types as t
+    except ImportError:
+        return {}
+    ts = plugin.trace_set
+
+    def transition(op):
+        def run(*operands):
+            return list(ts.primitive_infer([op] + [_python_value(o) for o in operands]))
+        return run
+
+    def subsampled(*operands):
+        stats = ts.primitive_infer(["subsampled_mh"] + [_python_value(o) for o in operands])
+        return [float(r[0]) for r in stats] if getattr(stats, "ndim", 1) == 2 else list(stats)
+
+    def resample(particles):
+        ts.resample(int(_python_value(particles)), mode="multinomial")
+
+    def likelihood_weight():
+        ts.likelihood_weight()
+
+    def incorporate():
+        return list(ts.incorporate())
+
+    def ll_at(scope, block):
+        return list(ts.log_likelihood_at(_python_value(scope), _python_value(block)))
+
+    def lj_at(scope, block):
+        return list(ts.log_joint_at(_python_value(scope), _python_value(block)))
+
+    subsampled_extra = [t.IntegerType("Nbatch : int"), t.IntegerType("k0 : int"), t.NumberType("epsilon : number"),
+                        t.BoolType("useDeltaKernels : bool"), t.NumberType("deltaKernelArgs : number"),
+                        t.BoolType("updateValues : bool")]
+    scope_block = [t.AnyType("scope : object"), t.AnyType("block : object")]
+    sps = {
+        # inference_sps.py:234-241 (resimulation_mh / mh), :253-267 (gibbs): transition_oper_type()
+        "resimulation_mh": inf.sequenced_sp(transition("resimulation_mh"), inf.transition_oper_type()),
+        "mh": inf.sequenced_sp(transition("resimulation_mh"), inf.transition_oper_type()),
+        "gibbs": inf.sequenced_sp(transition("gibbs"), inf.transition_oper_type()),
+        # :678-694
+        "subsampled_mh": inf.sequenced_sp(subsampled, inf.transition_oper_type(subsampled_extra)),
+        # :536-551
+        "resample": inf.sequenced_sp(resample, inf.infer_action_maker_type([t.IntegerType("particles : int")])),
+        # :602-606
+        "likelihood_weight": inf.sequenced_sp(likelihood_weight, inf.infer_action_maker_type([])),
+        "incorporate": inf.sequenced_sp(incorporate, inf.infer_action_maker_type([], return_type=t.Array(t.Number))),
+        "log_likelihood_at": inf.sequenced_sp(ll_at, inf.infer_action_maker_type(scope_block, return_type=t.Array(t.Number), min_req_args=1)),
+        "log_joint_at": inf.sequenced_sp(lj_at, inf.infer_action_maker_type(scope_block, return_type=t.Array(t.Number), min_req_args=1)),
+    }
+    return sps
+
+
+def __venture_start__(ripl, model=None, n_particles=1, seed=1, device=0, trace_set=None, override_builtins=False):
     """Entry point of ripl.load_plugin.  Returns the plugin object so the caller
     can observe data through `plugin.trace_set.observe(...)`."""
     if model is None and trace_set is None:
         raise VentureException("invalid_argument", "the b200 plugin needs a compiled model (venturecxx_b200.models)")
     plugin = B200Plugin(model, n_particles, seed, device, trace_set)
+    if hasattr(ripl, "bind_foreign_inference_sp"):
+        for name, sp in inference_sps(plugin).items():
+            ripl.bind_foreign_inference_sp(PREFIX + name, sp)
+            if override_builtins:
+                ripl.bind_foreign_inference_sp(name, sp)
     for name, fn in plugin.callbacks().items():
         ripl.bind_callback(name, fn)
     return plugin

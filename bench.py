@@ -47,13 +47,25 @@ def load_traffic(P, N):
     """Measured DRAM bytes per launch of the dominant kernel (ncu --set full capture committed under
     profiles/), scaled to this run's particle count; None if the capture does not match the workload."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_blr_mh_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r2_blr_mh2_traffic.json")) as f:
             t = json.load(f)
         if int(t["observations"]) != int(N):
             return None, None
         return (t["dram_bytes_read"] + t["dram_bytes_write"]) * (float(P) / t["particles"]), t
     except Exception:
         return None, None
+
+
+def fp64_frac(tinfo, P, N, T, ms_per_step, clocks):
+    """fp64 warp instructions per second of the timed launch over the sustained DFMA rate of the GPU"""
+    try:
+        evals = float(P) * T * (-(-N // 1024) * 1024) / 32.0                 # warp-evaluations (rows padded to the kernel's tile)
+        share = tinfo["hot_loop_fp64_instr_per_eval"] * evals                 # hot loop only: a lower bound of the launch's fp64 count
+        mhz = (clocks or {}).get("sm_mhz") or 1965.0
+        peak = tinfo["measured_dfma_peak_warp_instr_per_clk_per_sm"] * 148 * mhz * 1e6
+        return share / (ms_per_step * 1e-3) / peak
+    except Exception:
+        return None
 
 
 def load_peaks():
@@ -407,16 +419,25 @@ def main():
             "configs": {},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "kernel": "blr_mh_kernel<SMEM=true, 256 threads, 4 chains, 2 CTAs/SM>",
+                         "kernel": "blr_mh2_kernel<2 CTAs/SM> (256 threads, two proposals per pass over the shared-memory logit row, 8 chains per thread)",
                          "algorithmic_bytes_per_launch": bytes_per_tr * P * T,
                          "pipes_from_ncu": None if tinfo is None else {
                              "fp64_pipe_pct": tinfo["fp64_pipe_pct"], "issue_active_pct": tinfo["issue_active_pct"],
                              "lsu_writeback_pct": tinfo["lsu_writeback_pct"]},
+                         # the bound that binds (live): fp64 warp instructions of the launch / time, against the DFMA rate
+                         # one SM SUSTAINS (tools/ubench/fp64_pipe.cu on this pool: 1.75 warp-instr/clk/SM of the nominal 2)
+                         "fp64_pipe_frac": None if tinfo is None else fp64_frac(tinfo, P, N, T, ms / args.steps, clocks),
+                         "issue_slot_model": None if tinfo is None else {
+                             "slots_per_eval": 2 * tinfo["hot_loop_fp64_instr_per_eval"] + (tinfo["hot_loop_instr_per_eval"] - tinfo["hot_loop_fp64_instr_per_eval"]),
+                             "note": "a DFMA occupies two issue slots of its SM sub-partition (micro-benchmark: DFMA alone 1.75/clk/SM, "
+                                     "with one IMAD per DFMA 1.16, with IMAD + LOP3 0.88); per evaluation the hot loop issues 12 fp64 + "
+                                     "10.25 other instructions = 34.25 slots, i.e. 39 cycles per warp-evaluation per sub-partition "
+                                     "at the sustained 87 %; measured 46.6 in the hot loop (profiles/r2_blr_mh2_ncu.md)"},
                          "note": "algorithmic bytes per SURVEY 8(d) D4 = N*8*(1+a)+16 per particle-transition; "
                                  "the kernel keeps the logit row in shared memory for all transitions of a launch, so "
                                  "real DRAM traffic (`traffic`, from the committed ncu capture) is 2*8N B per particle per LAUNCH, "
-                                 "~1/200 of the algorithmic figure; the binding resources are the fp64 pipe, the LSU "
-                                 "return path and issue slots (profiles/r1_blr_mh_v3_ncu.md)"},
+                                 "~1/200 of the algorithmic figure; the binding resource is issue slots, of which every "
+                                 "fp64 instruction takes two (profiles/r2_blr_mh2_ncu.md, profiles/r2_fp64_pipe_microbench.txt)"},
         }
         if not args.no_cpu_baseline and world == 1:
             cb, _ = cpu_baseline(X, y, D, N, T)

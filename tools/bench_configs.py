@@ -191,7 +191,14 @@ def _c3_filter(ctx, H, P_local, sharded, seed, check):
     (ts.local if sharded else ts).synchronize()
     close(ts)
     ts = make(seed + 1)
-    ms = ctx.timed(lambda: run(ts), (ts.local if sharded else ts).synchronize)
+    host = {}
+
+    def run_timed():
+        t0 = time.perf_counter()
+        run(ts)
+        host["enqueue_s"] = time.perf_counter() - t0      # host time to enqueue the whole filter (no synchronisation inside)
+    ms = ctx.timed(run_timed, (ts.local if sharded else ts).synchronize)
+    _c3_filter.last_host_us_per_step = 1e6 * host["enqueue_s"] / len(H["data"])
     last = ts.read_site(T - 1).astype(np.int64)
     counts = np.bincount(last, minlength=6)[1:6].astype(np.float64)
     tot = ctx.torch.tensor(counts, dtype=torch.float64, device="cuda")
@@ -232,6 +239,7 @@ def c3(ctx, P_total=1 << 20, cpu=False, weak=True):
            "metric": "particle-steps/sec", "value": P_total * T / dt, "unit": "particle-steps/s", "n_gpus": ctx.world,
            "scaling": "strong", "ms_per_step": ms / T, "us_per_step": 1e3 * ms / T, "gpu_launches_per_step": 4,
            "tvd_last_vs_exact_filter": tvd, "bit_identical_to_1gpu": ident,
+           "host_enqueue_us_per_step": _c3_filter.last_host_us_per_step,
            "roofline": roofline(P_total * T * 208.0, dt, ctx.world, "SURVEY 8(d) D4: 208 B per particle-step; single-wave kernels, latency bound at this size")}
     if weak and sharded:
         P_big = 1 << 20

@@ -58,7 +58,8 @@ enum vk_model_kind {
   VK_MODEL_NORMAL_NORMAL = 1, /* x ~ normal(mu0,s0); observe normal(x,s) = y_k          */
   VK_MODEL_BLR = 2,           /* w_j ~ normal(mu0,s0); observe log_odds_flip(w.x_i)=y_i */
   VK_MODEL_HMM = 3,           /* examples/hmm.vnt:31-60                                 */
-  VK_MODEL_LDA = 4            /* examples/lda.vnt:18-41                                 */
+  VK_MODEL_LDA = 4,           /* examples/lda.vnt:18-41                                 */
+  VK_MODEL_PROGRAM = 5        /* any fixed-structure program compiled by compiler.py    */
 };
 
 /* block argument of an infer command (backend/lite/infer/dispatch.py:86-107) */
@@ -90,6 +91,27 @@ int vk_create_normal_normal(int64_t n_particles, uint64_t seed, int device,
                             double prior_mu, double prior_sigma,
                             double obs_sigma, int64_t max_obs,
                             vk_particles **out);
+/* A COMPILED fixed-structure program (venturecxx_b200/compiler.py): what
+ * constructScaffold (backend/lite/scaffold.py:149-316) + detach / regen (detach.py:31-120,
+ * regen.py:49-161) reduce to for every random choice of a program over the scalar SPs, as
+ * straight-line code of a register machine interpreted by ONE pair of kernels
+ * (csrc/k_program.cu).  Replaces Trace.eval of the assume / observe directives
+ * (lite/trace.py:397-420) for all particles.
+ *   code      5 int32 per instruction: op, dst, a, b, c (op codes: compiler.py OP)
+ *   consts    literals of the assumes
+ *   meta      n_sites, n_groups, n_registers, n_sections, PRIOR section, JOINT section;
+ *             per site: SIM, CHILD, OWN section, number of observation groups below it;
+ *             the sites' group lists; per group: prologue section, row section, rows,
+ *             columns (literals + observed value), offset into data; per section: first
+ *             instruction, count
+ *   data      the groups' tables, row-major
+ *   affected  per site: Scaffold.numAffectedNodes (scaffold.py:67-68), what
+ *             resimulation_mh reports (dispatch.py:109-120)
+ * Every index is validated here; the kernels do not re-check. */
+int vk_create_program(int64_t n_particles, uint64_t seed, int device, const int32_t *code,
+                      int64_t n_code, const double *consts, int64_t n_consts,
+                      const int32_t *meta, int64_t n_meta, const double *data, int64_t n_data,
+                      const double *affected, vk_particles **out);
 /* X rows are D doubles; capacity n_obs_capacity observations. */
 int vk_create_blr(int64_t n_particles, uint64_t seed, int device, int32_t D,
                   int64_t n_obs_capacity, double prior_mu, double prior_sigma,

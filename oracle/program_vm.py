@@ -1,0 +1,183 @@
+"""TEST INFRASTRUCTURE: a pure-Python interpreter of the model compiler's register-machine programs
+(venturecxx_b200/compiler.py), for small cases.  It executes the SAME blob the device gets, with
+
+  * draws from the oracle's samplers at the matching positions of the Philox streams (oracle.draw -> orc_draw,
+    the same stand-ins tests/golden/make_program_chains.py puts behind Lite's np_rng), and
+  * log densities from the reference's own call sites: normal by Lite's formula (continuous.py:319-323),
+    gamma / beta / uniform / expon through scipy.stats as Lite does (continuous.py:1166-1167, 858-859, 639, 1137),
+    the flip family by discrete.py:61-67, 109-113, 148-150 with utils.py:60-61, 257-268,
+
+so that tests can pin the COMPILER (which nodes absorb where, in which order values are simulated, the
+transition protocol of infer/mh.py:59-113, 167-208) against the Lite fixture without a GPU.
+"""
+import math
+
+import numpy as np
+import scipy.stats
+
+import oracle
+
+WORDS = 5
+
+
+def _log(x):
+    return -math.inf if x == 0 else math.log(x)
+
+
+def _log1p(x):
+    return -math.inf if x == -1 else math.log1p(x)
+
+
+def _log_logistic(x):
+    return x if x <= -37 else -math.log1p(math.exp(-x))
+
+
+def _logistic(x):
+    return math.exp(x) if x <= -37 else 1.0 / (1.0 + math.exp(-x))
+
+
+class VM(object):
+    def __init__(self, blob, op_table, P, seed, p_base=0):
+        self.code, self.consts, meta, self.data, self.affected = [np.asarray(b) for b in blob]
+        self.op = dict((v, k) for k, v in op_table.items())
+        self.P, self.seed, self.p_base = P, seed, p_base
+        m = [int(x) for x in meta]
+        self.S, self.G, self.n_regs, self.n_sec, self.sec_prior, self.sec_joint = m[:6]
+        at = 6
+        self.site = [m[at + 4 * k: at + 4 * k + 4] for k in range(self.S)]
+        at += 4 * self.S
+        self.site_groups = []
+        for k in range(self.S):
+            self.site_groups.append(m[at: at + self.site[k][3]])
+            at += self.site[k][3]
+        self.group = [m[at + 5 * g: at + 5 * g + 5] for g in range(self.G)]
+        at += 5 * self.G
+        self.dir = [(m[at + 2 * s], m[at + 2 * s + 1]) for s in range(self.n_sec)]
+        self.sites = np.zeros((self.S, P))
+        self.lw = np.zeros(P)
+        self.step = 0
+
+    # -- one section ------------------------------------------------------------------------------------------
+    def run(self, sec, R, p, row=None, tape=None, store=True):
+        first, n = self.dir[sec]
+        acc = 0.0
+        for i in range(first, first + n):
+            op, d, a, b, _c = [int(x) for x in self.code[i * WORDS:(i + 1) * WORDS]]
+            name = self.op[op]
+            if name == "CONST": R[d] = float(self.consts[a])
+            elif name == "SITE": R[d] = float(self.sites[a, p])
+            elif name == "DATA": R[d] = float(row[a])
+            elif name == "ADD": R[d] = R[a] + R[b]
+            elif name == "SUB": R[d] = R[a] - R[b]
+            elif name == "MUL": R[d] = R[a] * R[b]
+            elif name == "DIV": R[d] = R[a] / R[b]
+            elif name == "NEG": R[d] = -R[a]
+            elif name == "EXP": R[d] = math.exp(R[a])
+            elif name == "LOG": R[d] = _log(R[a])
+            elif name == "SQRT": R[d] = math.sqrt(R[a])
+            elif name == "POW": R[d] = math.pow(R[a], R[b])
+            elif name == "LOGISTIC": R[d] = _logistic(R[a])
+            elif name == "ABS": R[d] = abs(R[a])
+            elif name == "MIN": R[d] = min(R[a], R[b])
+            elif name == "MAX": R[d] = max(R[a], R[b])
+            elif name == "LOG1P": R[d] = _log1p(R[a])
+            elif name == "EXPM1": R[d] = math.expm1(R[a])
+            elif name == "LOG_LOGISTIC": R[d] = _log_logistic(R[a])
+            elif name == "LOGIT": R[d] = math.log(R[a] / (1 - R[a]))
+            elif name == "SIM_NORMAL": R[d] = tape(1, [R[a], R[b]])
+            elif name == "SIM_GAMMA": R[d] = tape(2, [R[a], R[b]])
+            elif name == "SIM_BETA": R[d] = tape(5, [R[a], R[b]])
+            elif name == "SIM_UNIFORM": R[d] = R[a] + (R[b] - R[a]) * tape(0, [0.0])
+            elif name == "SIM_EXPON": R[d] = -math.log1p(-tape(0, [0.0])) * (1.0 / R[a])
+            elif name == "SIM_FLIP": R[d] = 1.0 if tape(0, [0.0]) < R[a] else 0.0
+            elif name == "SIM_LOG_FLIP": R[d] = 1.0 if math.log(tape(0, [0.0])) < R[a] else 0.0
+            elif name == "SIM_LOG_ODDS_FLIP":
+                u = tape(0, [0.0])
+                R[d] = 1.0 if math.log(u / (1 - u)) < R[a] else 0.0
+            elif name == "LD_NORMAL":
+                dev = R[d] - R[a]                       # continuous.py:319-323
+                acc += -math.log(R[b]) - 0.5 * math.log(2 * math.pi) - 0.5 * dev * dev / (R[b] * R[b])
+            elif name == "LD_GAMMA": acc += float(scipy.stats.gamma.logpdf(R[d], R[a], scale=1.0 / R[b]))
+            elif name == "LD_BETA": acc += float(scipy.stats.beta.logpdf(R[d], R[a], R[b]))
+            elif name == "LD_UNIFORM": acc += float(scipy.stats.uniform.logpdf(R[d], R[a], R[b] - R[a]))
+            elif name == "LD_EXPON": acc += float(scipy.stats.expon.logpdf(R[d], scale=1.0 / R[a]))
+            elif name == "LD_FLIP": acc += _log(R[a]) if R[d] != 0 else _log1p(-R[a])
+            elif name == "LD_LOG_FLIP": acc += R[a] if R[d] != 0 else _log1p(-math.exp(R[a]))
+            elif name == "LD_LOG_ODDS_FLIP": acc += _log_logistic(R[a] if R[d] != 0 else -R[a])
+            elif name == "STORE":
+                if store:
+                    self.sites[a, p] = R[d]
+            else:
+                raise ValueError("unknown op %d" % op)
+        return acc
+
+    def _tape(self, p, step, d0):
+        state = {"d": d0}
+
+        def draw(kind, params):
+            v, state["d"] = oracle.draw(kind, params, self.seed, self.p_base + p, step, state["d"])
+            return v
+        return draw
+
+    def group_ll(self, g, R, p):
+        pro, row_sec, n_rows, n_cols, off = self.group[g]
+        self.run(pro, R, p)
+        tot = 0.0
+        for r in range(n_rows):
+            tot += self.run(row_sec, R, p, row=self.data[off + r * n_cols: off + (r + 1) * n_cols])
+        return tot
+
+    def children(self, k, R, p):
+        acc = self.run(self.site[k][1], R, p)
+        for g in self.site_groups[k]:
+            acc += self.group_ll(g, R, p)
+        return acc
+
+    def all_groups(self, R, p):
+        return sum(self.group_ll(g, R, p) for g in range(self.G))
+
+    # -- the operations of the C ABI --------------------------------------------------------------------------
+    def likelihood_weight(self):
+        step, self.step = self.step, self.step + 1
+        for p in range(self.P):
+            R = [0.0] * self.n_regs
+            self.run(self.sec_prior, R, p, tape=self._tape(p, step, 0))
+            self.lw[p] = self.all_groups(R, p)
+
+    def reset_to_prior(self):
+        step, self.step = self.step, self.step + 1
+        for p in range(self.P):
+            self.run(self.sec_prior, [0.0] * self.n_regs, p, tape=self._tape(p, step, 0))
+
+    def log_likelihood(self, joint=False):
+        out = np.zeros(self.P)
+        for p in range(self.P):
+            R = [0.0] * self.n_regs
+            out[p] = self.all_groups(R, p) + (self.run(self.sec_joint, R, p) if joint else 0.0)
+        return out
+
+    def mh(self, n_steps, block=-1):
+        """block -1: one, -3: each, k >= 0: site k.  Returns (accept counts, per-particle mean node counts)."""
+        step0, self.step = self.step, self.step + n_steps
+        acc, nodes = np.zeros(self.P, dtype=np.int64), np.zeros(self.P)
+        for p in range(self.P):
+            for t in range(n_steps):
+                u = oracle.uniforms(self.seed, self.p_base + p, step0 + t, 2)
+                k = min(int(u[0] * self.S), self.S - 1) if block == -1 else (t % self.S if block == -3 else block)
+                R = [0.0] * self.n_regs
+                rho = self.children(k, R, p)
+                old = self.sites[k, p]
+                self.run(self.site[k][0], R, p, tape=self._tape(p, step0 + t, 2))
+                xi = self.children(k, R, p)
+                if rho == -math.inf and xi == -math.inf:
+                    alpha = math.inf
+                elif rho == math.inf and xi == math.inf:
+                    alpha = -math.inf
+                else:
+                    alpha = xi - rho
+                if math.log(u[1]) < alpha:
+                    acc[p] += 1
+                else:
+                    self.sites[k, p] = old
+                nodes[p] += self.affected[k]
+        return acc, nodes / max(n_steps, 1)

@@ -159,8 +159,11 @@ class NpRng(object):
     def random_sample(self):
         return self.tape.draw(0, [0.0])
 
-    def uniform(self, lo=0.0, hi=1.0):
-        return lo + (hi - lo) * self.tape.draw(0, [0.0])
+    def exponential(self, scale=1.0):            # continuous.py:1134 (inverse CDF, as the kernels' expon_sim)
+        return -math.log1p(-self.tape.draw(0, [0.0])) * scale
+
+    def uniform(self, low=0.0, high=1.0):        # continuous.py:637
+        return low + (high - low) * self.tape.draw(0, [0.0])
 
 
 def install(model, seed, particle):

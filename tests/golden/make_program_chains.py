@@ -1,0 +1,98 @@
+#!/usr/bin/env python
+"""Generates tests/golden/program_chains.json: programs for the MODEL COMPILER (venturecxx_b200/compiler.py,
+SURVEY 8(f) N2) run on THE REFERENCE'S LITE BACKEND in this container, with the machinery of
+make_lite_chains.py -- Lite's own constructScaffold / detachAndExtract / regenAndAttach / mixMH on stand-in RNG
+objects that return the draws the oracle's samplers make at the matching position of the Philox stream
+(seed, particle, step).  The fixture holds the programs (as nested lists) and what Lite ended with: values,
+weights, increments, node counts, log likelihoods; tests compile the same programs for the GPU and demand
+equality.
+
+  python oracle/lite_py3/build_lite_py3.py && python tests/golden/make_program_chains.py
+"""
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+from make_lite_chains import Model, fl, install, mh_steps  # noqa: E402  (also puts oracle/_ref on sys.path)
+import venture.lite.value as vv  # noqa: E402
+import venture.value.dicts as vd  # noqa: E402
+
+
+def programs():
+    rng = np.random.default_rng(7)
+    xs = np.round(rng.normal(size=9), 3).tolist()
+    ys = np.round(1.5 * np.array(xs) - 0.7 + 0.4 * rng.normal(size=9), 3).tolist()
+    regression = [("assume", "a", ["normal", 0.0, 2.0]), ("assume", "b", ["normal", 0.0, 2.0]),
+                  ("assume", "s", ["gamma", 2.0, 2.0])] + \
+                 [("observe", ["normal", ["add", ["mul", "a", x], "b"], "s"], y) for x, y in zip(xs, ys)]
+    flips = [True, True, False, True, True, True, False, True, True, True, True, False]
+    coin = [("assume", "p", ["beta", 1.5, 2.5])] + [("observe", ["flip", "p"], f) for f in flips]
+    hier = [("assume", "mu", ["normal", 1.0, 3.0]), ("assume", "tau", ["gamma", 3.0, 2.0]),
+            ("assume", "spread", ["div", 1.0, ["sqrt", "tau"]]),
+            ("assume", "x1", ["normal", "mu", "spread"]), ("assume", "x2", ["normal", "mu", "spread"]),
+            ("assume", "lo", ["uniform_continuous", -1.0, 0.5]),
+            ("assume", "mid", ["add", "x1", "x2", "lo"]),
+            ("observe", ["normal", "x1", 0.5], 2.1), ("observe", ["normal", "x2", 0.5], 0.3),
+            ("observe", ["normal", ["mul", "mid", 0.5], 1.0], 1.0),
+            ("observe", ["log_odds_flip", ["sub", "x1", "x2"]], True),
+            ("observe", ["expon", ["exp", "lo"]], 0.8),
+            ("observe", ["gamma", ["add", ["abs", "mu"], 1.0], "tau"], 1.7)]
+    return {"regression": regression, "coin": coin, "hierarchy": hier}
+
+
+def box(v):
+    return vd.boolean(v) if isinstance(v, bool) else vd.number(float(v))
+
+
+def run(name, prog, seed, P, K, n_first):
+    """n_first observations are incorporated before likelihood_weight, the rest after (increments)."""
+    out = {"seed": seed, "P": P, "K": K, "program": [list(d) for d in prog], "n_first": n_first,
+           "steps": {"likelihood_weight": 4, "mh": 30}, "particles": []}
+    assumes = [d for d in prog if d[0] == "assume"]
+    observes = [d for d in prog if d[0] == "observe"]
+    for p in range(P):
+        m = Model()
+        dids = [m.assume(d[1], d[2]) for d in assumes]
+        for d in observes[:n_first]:
+            m.observe(d[1], box(d[2]))
+        m.t.makeConsistent()
+        install(m, seed, p)
+        # the default scope's blocks are the unconstrained random choices; canonical order = order of the assumes
+        random_dids = [did for did, d in zip(dids, assumes) if m.t.families[did] in m.t.rcs]
+        nodes = [m.t.families[did] for did in random_dids]
+        m.tape.site_of = lambda key: [i for i, n in enumerate(nodes) if n is key][0]
+        rec = {"sites": [d[1] for did, d in zip(dids, assumes) if did in random_dids]}
+        m.tape.begin(4, 0)
+        rec["lw"] = fl(m.t.likelihood_weight())
+        rec["values_lw"] = [fl(m.value(did)) for did in random_dids]
+        for d in observes[n_first:]:
+            m.observe(d[1], box(d[2]))
+        rec["incr"] = fl(m.t.makeConsistent())
+        rec["nodes"] = mh_steps(m, 30, K)
+        rec["values_mh"] = [fl(m.value(did)) for did in random_dids]
+        rec["ll_at"] = fl(m.t.log_likelihood_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
+        rec["lj_at"] = fl(m.t.log_joint_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
+        out["particles"].append(rec)
+    return out
+
+
+def main():
+    fixture = {}
+    progs = programs()
+    fixture["regression"] = run("regression", progs["regression"], 23, 5, 40, 4)
+    fixture["coin"] = run("coin", progs["coin"], 29, 5, 30, 6)
+    fixture["hierarchy"] = run("hierarchy", progs["hierarchy"], 31, 5, 60, 3)
+    fixture["_source"] = ("reference Lite backend (py3 rendering by oracle/lite_py3/build_lite_py3.py) run by "
+                          "tests/golden/make_program_chains.py; numpy %s" % np.__version__)
+    path = os.path.join(HERE, "program_chains.json")
+    with open(path, "w") as f:
+        json.dump(fixture, f, indent=1, sort_keys=True)
+    print("wrote", path)
+
+
+if __name__ == "__main__":
+    main()

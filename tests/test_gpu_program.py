@@ -1,0 +1,165 @@
+"""N2, GPU: compiled programs (venturecxx_b200/compiler.py -> csrc/k_program.cu) against the reference.
+
+  * the three programs of tests/golden/program_chains.json (produced by running Lite itself): simulated values,
+    likelihood weights, increments, MH chains, node counts, log likelihood / joint at 1e-12;
+  * a compiled normal-normal program reproduces the hand-written kernels (k_normal.cu) bit for bit and the
+    Lite fixture of the C1 model;
+  * one warp per particle (many observations) equals one thread per particle;
+  * posterior of a coin by KS under the reference's policy; resampling; restoring device particles into Lite.
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+import scipy.stats as st
+
+import venturecxx_b200 as vb
+from helpers import golden, unj
+from venturecxx_b200.compiler import CompiledModel
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-12
+
+
+def sites_of(ts):
+    return np.stack([ts.read_site(j) for j in range(ts.num_sites())])
+
+
+@pytest.mark.parametrize("name", ["regression", "coin", "hierarchy"])
+def test_compiled_program_reproduces_lite_on_the_device(name):
+    case = golden("program_chains.json")[name]
+    prog = [tuple(d) for d in case["program"]]
+    assumes = [d for d in prog if d[0] == "assume"]
+    observes = [d for d in prog if d[0] == "observe"]
+    n_first, P, K, seed = case["n_first"], case["P"], case["K"], case["seed"]
+    recs = case["particles"]
+    ts = vb.B200TraceSet(CompiledModel(assumes + observes[:n_first]), P, seed=seed)
+    ts.incorporate()
+    ts.rng_step = case["steps"]["likelihood_weight"]
+    ts.likelihood_weight()
+    np.testing.assert_allclose(ts.log_weights, [unj(r["lw"]) for r in recs], rtol=RTOL)
+    s0 = sites_of(ts)
+    np.testing.assert_allclose(s0.T, [[unj(v) for v in r["values_lw"]] for r in recs], rtol=RTOL)
+    # the remaining observations arrive (a longer program, same sites)
+    ts2 = vb.B200TraceSet(CompiledModel(prog), P, seed=seed)
+    for j in range(ts2.num_sites()):
+        ts2.write_site(j, s0[j])
+    incr = ts2.log_likelihood_at("default", "all") - ts.log_likelihood_at("default", "all")
+    np.testing.assert_allclose(incr, [unj(r["incr"]) for r in recs], rtol=1e-10)
+    inc2 = ts2.incorporate()
+    np.testing.assert_allclose(inc2, ts2.log_likelihood_at("default", "all"), rtol=RTOL)
+    ts2.rng_step = case["steps"]["mh"]
+    nodes, acc = ts2.resimulation_mh("default", "one", K, return_accepts=True)
+    np.testing.assert_allclose(sites_of(ts2).T, [[unj(v) for v in r["values_mh"]] for r in recs], rtol=RTOL)
+    np.testing.assert_allclose(nodes, [np.mean(r["nodes"]) for r in recs], rtol=1e-14)
+    assert acc.sum() > 0 and ts2.rng_step == case["steps"]["mh"] + K
+    np.testing.assert_allclose(ts2.log_likelihood_at("default", "all"), [unj(r["ll_at"]) for r in recs], rtol=RTOL)
+    np.testing.assert_allclose(ts2.log_joint_at("default", "all"), [unj(r["lj_at"]) for r in recs], rtol=RTOL)
+
+
+def test_compiled_normal_normal_equals_the_hand_written_kernels():
+    mu0, s0, s, ys = 0.5, 2.0, 1.5, [2.0, 1.0, -0.5]
+    P = 3001
+    hand = vb.B200TraceSet(vb.NormalNormalModel(mu0, s0, s), P, seed=11)
+    hand.observe(ys)
+    gen = vb.B200TraceSet(CompiledModel([("assume", "x", ["normal", mu0, s0])] + [("observe", ["normal", "x", s], y) for y in ys]), P, seed=11)
+    np.testing.assert_array_equal(gen.read_site(0), hand.read_site(0))          # the prior draw of `assume`
+    np.testing.assert_array_equal(gen.incorporate(), hand.incorporate())
+    hand.likelihood_weight(); gen.likelihood_weight()
+    np.testing.assert_array_equal(gen.log_weights, hand.log_weights)
+    n1, a1 = hand.resimulation_mh("default", "one", 50, return_accepts=True)
+    n2, a2 = gen.resimulation_mh("default", "one", 50, return_accepts=True)
+    np.testing.assert_array_equal(gen.read_site(0), hand.read_site(0))
+    np.testing.assert_array_equal(a1, a2)
+    np.testing.assert_array_equal(n1, n2)                                        # 1 + #observations (scaffold.py:67-68)
+    np.testing.assert_array_equal(gen.log_likelihood_at("default", "all"), hand.log_likelihood_at("default", "all"))
+    np.testing.assert_array_equal(gen.log_joint_at("default", "all"), hand.log_joint_at("default", "all"))
+    anc = gen.resample(P, mode="systematic", return_ancestors=True)
+    np.testing.assert_array_equal(anc, hand.resample(P, mode="systematic", return_ancestors=True))
+    np.testing.assert_array_equal(gen.read_site(0), hand.read_site(0))
+    # and the C1 chain Lite itself produced (tests/golden/lite_chains.json)
+    c = golden("lite_chains.json")["c1"]
+    g = vb.B200TraceSet(CompiledModel([("assume", "x", ["normal", c["mu0"], c["s0"]])] +
+                                      [("observe", ["normal", "x", c["s"]], y) for y in c["y"]]), c["P"], seed=c["seed"])
+    g.incorporate()
+    g.rng_step = c["steps"]["mh"]
+    # (the fixture runs likelihood_weight on two observations first; start the chain from its state instead)
+    hand2 = vb.B200TraceSet(vb.NormalNormalModel(c["mu0"], c["s0"], c["s"]), c["P"], seed=c["seed"])
+    hand2.observe(c["y"][:2]); hand2.incorporate()
+    hand2.rng_step = c["steps"]["likelihood_weight"]
+    hand2.likelihood_weight()
+    g.write_site(0, hand2.read_site(0))
+    g.resimulation_mh("default", "one", c["K"])
+    np.testing.assert_allclose(g.read_site(0), [unj(r["x_mh"]) for r in c["particles"]], rtol=RTOL)
+
+
+def test_one_warp_per_particle_equals_the_python_interpreter():
+    """>= 64 observations in a group: lanes take rows in turn and the warp adds their sums (another summation
+    order than Lite's, so 1e-10); chain decisions equal the sequential interpreter's"""
+    from oracle.program_vm import VM
+    from venturecxx_b200 import compiler
+    rng = np.random.default_rng(3)
+    xs = rng.normal(size=150)
+    ys = 0.8 * xs + 0.3 + 0.5 * rng.normal(size=150)
+    prog = [("assume", "a", ["normal", 0.0, 2.0]), ("assume", "b", ["normal", 0.0, 2.0]), ("assume", "s", ["gamma", 2.0, 2.0])] + \
+           [("observe", ["normal", ["add", ["mul", "a", float(x)], "b"], "s"], float(y)) for x, y in zip(xs, ys)]
+    m = CompiledModel(prog)
+    P, K = 6, 40
+    ts = vb.B200TraceSet(m, P, seed=5)
+    inc = ts.incorporate()
+    vm = VM(m.prog.blob(), compiler.OP, P, 5)
+    vm.reset_to_prior()
+    np.testing.assert_allclose(sites_of(ts), vm.sites, rtol=RTOL)
+    np.testing.assert_allclose(inc, vm.log_likelihood(), rtol=1e-10)
+    step = ts.rng_step
+    nodes, acc = ts.resimulation_mh("default", "one", K, return_accepts=True)
+    vm.step = step
+    acc_ref, nodes_ref = vm.mh(K)
+    np.testing.assert_array_equal(acc, acc_ref)
+    np.testing.assert_allclose(sites_of(ts), vm.sites, rtol=RTOL)
+    np.testing.assert_allclose(nodes, nodes_ref, rtol=1e-14)
+    np.testing.assert_allclose(ts.log_joint_at("default", "all"), vm.log_likelihood(joint=True), rtol=1e-10)
+    ts.primitive_infer(["resimulation_mh", "default", "each", 3])
+    vm.mh(3 * 3, block=-3)
+    np.testing.assert_allclose(sites_of(ts), vm.sites, rtol=RTOL)
+
+
+def test_coin_posterior_and_global_logscore():
+    """a model that has no .cu file: p ~ beta(1, 1), 100 observed flips (test/conformance/test_get_global_logscore.py:
+    32-50 uses the same shape); posterior Beta(1 + heads, 1 + tails) by KS under test/stats.py's policy"""
+    from stats_policy import report_known_continuous, statistical_test
+    flips = [True] * 62 + [False] * 38
+    prog = [("assume", "p", ["beta", 1.0, 1.0])] + [("observe", ["flip", "p"], f) for f in flips]
+    fair = [("assume", "x", ["normal", 0.0, 1.0])] + [("observe", ["flip", 0.5], True)] * 100
+    t0 = vb.B200TraceSet(CompiledModel(fair), 4, seed=1)
+    np.testing.assert_allclose(t0.incorporate(), -100 * np.log(2), rtol=1e-13)      # test_global_logscore: -100 log 2
+
+    @statistical_test
+    def run(seed):
+        ts = vb.B200TraceSet(CompiledModel(prog), 4000, seed=seed)
+        ts.incorporate()
+        ts.resimulation_mh("default", "one", 120)
+        return report_known_continuous(st.beta(63, 39).cdf, ts.read_site(0), "beta(63, 39)")
+    run()
+
+
+def test_compiled_particles_restore_into_lite():
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import ref_engine
+    if not ref_engine.available():
+        pytest.skip("oracle/_ref not built")
+    ref_engine._import()
+    import venture.engine.trace as tr
+    import venture.lite.value as vv
+    from venture.lite.trace import Trace
+    case = golden("program_chains.json")["hierarchy"]
+    m = CompiledModel([tuple(d) for d in case["program"]])
+    ts = vb.B200TraceSet(m, 7, seed=3)
+    ts.incorporate()
+    ts.resimulation_mh("default", "one", 25)
+    lj = ts.log_joint_at("default", "all")
+    for i in (0, 3, 6):
+        lite = tr.Trace.restore(lambda: Trace(1), ts.dump_particle(i), {})
+        got = lite.trace.log_joint_at(vv.VentureSymbol("default"), vv.VentureSymbol("all"))
+        assert abs(got - lj[i]) <= 1e-12 * abs(lj[i])

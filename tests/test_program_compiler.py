@@ -1,0 +1,110 @@
+"""N2, CPU: the model compiler (venturecxx_b200/compiler.py) against the reference's Lite backend.
+
+tests/golden/program_chains.json was produced by running Lite itself on three programs (linear regression,
+a beta-Bernoulli coin, a hierarchy with latent children, deterministic assumes and six SP kinds) with the
+oracle's draws behind Lite's RNGs (tests/golden/make_program_chains.py).  Here the SAME programs are compiled
+and the compiled code is executed by the pure-Python interpreter oracle/program_vm.py: simulated values,
+likelihood weights, incorporate increments, every MH decision, node counts and log likelihoods must equal
+Lite's.  tests/test_gpu_program.py then holds the kernels to the same fixture.
+"""
+import numpy as np
+import pytest
+
+import oracle
+from helpers import golden, unj
+from oracle.program_vm import VM
+from venturecxx_b200 import compiler
+from venturecxx_b200.compiler import CompiledModel
+from venturecxx_b200.exception import VentureException
+
+RTOL = 1e-12
+
+
+def split(case):
+    prog = [tuple(d) for d in case["program"]]
+    assumes = [d for d in prog if d[0] == "assume"]
+    observes = [d for d in prog if d[0] == "observe"]
+    return assumes, observes
+
+
+@pytest.mark.parametrize("name", ["regression", "coin", "hierarchy"])
+def test_compiled_program_reproduces_lite(name):
+    case = golden("program_chains.json")[name]
+    assumes, observes = split(case)
+    n_first, P, K, seed = case["n_first"], case["P"], case["K"], case["seed"]
+    first = CompiledModel(assumes + observes[:n_first])
+    full = CompiledModel(assumes + observes)
+    assert first.site_names == case["particles"][0]["sites"] == full.site_names
+    vm = VM(first.prog.blob(), compiler.OP, P, seed)
+    vm.step = case["steps"]["likelihood_weight"]
+    vm.likelihood_weight()
+    recs = case["particles"]
+    np.testing.assert_allclose(vm.lw, [unj(r["lw"]) for r in recs], rtol=RTOL)
+    np.testing.assert_allclose(vm.sites.T, [[unj(v) for v in r["values_lw"]] for r in recs], rtol=RTOL)
+    # the remaining observations arrive: the increment is their log density (lite/trace.py:422-448)
+    vm2 = VM(full.prog.blob(), compiler.OP, P, seed)
+    vm2.sites[:] = vm.sites
+    incr = vm2.log_likelihood() - vm.log_likelihood()
+    np.testing.assert_allclose(incr, [unj(r["incr"]) for r in recs], rtol=1e-10)
+    vm2.step = case["steps"]["mh"]
+    acc, nodes = vm2.mh(K)
+    np.testing.assert_allclose(vm2.sites.T, [[unj(v) for v in r["values_mh"]] for r in recs], rtol=RTOL)
+    np.testing.assert_allclose(nodes, [np.mean(r["nodes"]) for r in recs], rtol=1e-14)
+    assert acc.sum() > 0
+    np.testing.assert_allclose(vm2.log_likelihood(), [unj(r["ll_at"]) for r in recs], rtol=RTOL)
+    np.testing.assert_allclose(vm2.log_likelihood(joint=True), [unj(r["lj_at"]) for r in recs], rtol=RTOL)
+
+
+def test_node_counts_follow_the_scaffold_rules():
+    # scaffold.py:201-218: the site, lookups of resampled nodes, deterministic applications downstream; a variadic
+    # add is ONE application; an assume referenced by symbol is ONE node with one lookup per reference
+    m = CompiledModel([("assume", "a", ["normal", 0, 1]), ("assume", "b", ["normal", 0, 1]), ("assume", "s", ["gamma", 1, 1])] +
+                      [("observe", ["normal", ["add", ["mul", "a", float(i)], "b"], "s"], 2.0 * i) for i in range(5)])
+    assert m.prog.affected == [16.0, 11.0, 6.0] and m.prog.n_groups == 1
+    m = CompiledModel([("assume", "x", ["normal", 0, 1]), ("assume", "h", ["mul", "x", 2.0]),
+                       ("observe", ["normal", "h", 1.0], 0.5), ("observe", ["normal", "h", 1.0], 0.7),
+                       ("observe", ["normal", ["add", "h", "x", 1.0], 1.0], 0.1)])
+    # x; lookups of x: in h's expression and in the add; h itself; lookups of h: 3; the add
+    assert m.prog.affected == [1 + 2 + 1 + 3 + 1]
+    assert m.prog.n_groups == 2 and [len(g.rows) for g in m.compiler.group_list] == [2, 1]
+
+
+def test_blob_is_self_consistent():
+    case = golden("program_chains.json")["hierarchy"]
+    m = CompiledModel([tuple(d) for d in case["program"]])
+    code, consts, meta, data, affected = m.prog.blob()
+    assert code.dtype == np.int32 and code.size % compiler.INSTR_WORDS == 0 and meta.dtype == np.int32
+    S, G, n_regs, n_sec = [int(v) for v in meta[:4]]
+    assert S == 5 and len(affected) == S and n_regs <= compiler.MAX_REGS
+    directory = meta[-2 * n_sec:].reshape(n_sec, 2)
+    assert directory[:, 1].sum() == code.size // compiler.INSTR_WORDS
+    ops = set(code.reshape(-1, compiler.INSTR_WORDS)[:, 0].tolist())
+    assert ops <= set(compiler.OP.values())
+    regs = code.reshape(-1, compiler.INSTR_WORDS)[:, 1]
+    assert regs.min() >= 0 and regs.max() < n_regs
+    assert sum(len(g.rows) for g in m.compiler.group_list) == m.n_observations == 6
+
+
+def test_programs_outside_the_subset_are_refused():
+    for prog, msg in [
+        ([("assume", "x", ["normal", 0, 1]), ("assume", "f", ["lambda", ["y"], "y"])], "SP"),
+        ([("assume", "x", ["normal", 0, 1]), ("observe", ["normal", ["normal", "x", 1.0], 1.0], 0.0)], "latent random choice"),
+        ([("assume", "x", ["normal", "y", 1])], "Cannot find symbol"),
+        ([("assume", "x", ["add", 1, 2])], "no unobserved random choice"),
+        ([("assume", "x", ["normal", 0, 1]), ("observe", ["add", "x", 1.0], 0.0)], "random SPs can be observed"),
+        ([("assume", "x", ["categorical", ["simplex", 0.5, 0.5]])], "outside"),
+    ]:
+        with pytest.raises(VentureException) as e:
+            CompiledModel(prog)
+        assert msg in str(e.value), (prog, str(e.value))
+
+
+def test_compiled_model_speaks_the_interchange_format():
+    """the directives of a compiled model are its program(): device particles restore into Lite traces (N3)"""
+    m = CompiledModel([("assume", "p", ["beta", 1.0, 1.0]), ("observe", ["flip", "p"], True), ("observe", ["flip", "p"], False)])
+    prog = m.program([])
+    assert [d[0] for d in prog] == ["define", "observe", "observe"]
+    vals = m.random_values([], np.array([0.25]))
+    assert [v["value"] for v in vals] == [0.25, True, False]
+    np.testing.assert_array_equal(m.sites_from_random_values([], vals), [0.25])
+    assert oracle is not None

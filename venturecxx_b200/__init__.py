@@ -7,6 +7,7 @@ reference's TraceSet / infer-primitive interface.  No CPU fallback.
 from .exception import VentureException
 from .models import HMMModel, LDAModel, LogisticRegressionModel, NormalNormalModel
 from .trace_set import B200TraceSet
+from .compiler import CompiledModel
 
 __all__ = ["B200TraceSet", "VentureException", "NormalNormalModel", "LogisticRegressionModel",
            "HMMModel", "LDAModel"]

@@ -1,0 +1,511 @@
+"""Model compiler: a fixed-structure program of `assume` / `observe` directives -> site programs for the
+generic particle kernels (csrc/k_program.cu), SURVEY 8(f) N2.
+
+What the reference does per transition -- `constructScaffold` (backend/lite/scaffold.py:149-173) from the
+principal node, `extendCandidateScaffold` (:201-218: lookups and deterministic applications downstream are
+resampled, random applications absorb: `canAbsorb`, psp.py:136-148, 459-461), `findBorder` (:260-264),
+then `detachAndExtract` / `regenAndAttach` over that scaffold (detach.py:31-54, regen.py:49-72) -- is done
+ONCE here, per random choice, for programs whose structure cannot change:
+
+  expressions   numbers, booleans, symbols bound by earlier assumes, applications of
+  deterministic SPs   add sub mul div pow sqrt exp log log1p expm1 logistic log_logistic logit negate abs min max
+                      (venmath.py:101-332; add / mul are variadic left folds)
+  random SPs          normal gamma beta uniform_continuous expon flip bernoulli log_flip log_bernoulli
+                      log_odds_flip log_odds_bernoulli            (continuous.py, discrete.py)
+
+(no `if` on random predicates, no `mem`, no procedures: nothing that creates brush.)  Every unobserved random
+application is a SITE = one block of the default scope (lite/trace.py:116-119).  For site k the compiler
+emits, as straight-line code for a register machine,
+
+  SIM_k        the site's parameters from its parents, then `simulate`                (regen.py:255-285 applyPSP)
+  CHILD_k      the log densities of the random applications that absorb at k's border -- other sites and
+               single observations -- with the deterministic nodes between recomputed  (regen.py:120-127 absorb)
+  groups       observations that share one expression up to numeric literals are one GROUP: a prologue (the
+               row-independent nodes), a row program, and a table with one row of literals + observed value per
+               observation; a site lists the groups below it
+
+and the number of nodes Lite's scaffold would hold (`numAffectedNodes`, scaffold.py:67-68: the site, the
+lookup nodes of symbols bound to resampled nodes, the deterministic applications downstream), which is what
+`resimulation_mh` reports (dispatch.py:109-120).  Single-site MH then is: rho = CHILD_k + groups under the old
+value, SIM_k, xi = the same under the new value, accept iff log u < xi - rho (mh.py:84-89, 187-208; the prior
+proposal contributes 0 to both).
+
+`CompiledModel` plugs into B200TraceSet like the hand-described models of models.py and carries the program
+as its `program()` for interchange.py, so device particles restore into real Lite traces.
+"""
+import ctypes
+
+import numpy as np
+
+from . import _lib
+from . import interchange
+from .exception import VentureException
+
+# ---- the register machine (mirrored in csrc/k_program.cu and oracle/oracle.c) ----------------------------
+OP = dict(
+    CONST=0, SITE=1, DATA=2, ADD=3, SUB=4, MUL=5, DIV=6, NEG=7, EXP=8, LOG=9, SQRT=10, POW=11, LOGISTIC=12,
+    ABS=13, MIN=14, MAX=15, LOG1P=16, EXPM1=17, LOG_LOGISTIC=18, LOGIT=19,
+    SIM_NORMAL=32, SIM_GAMMA=33, SIM_BETA=34, SIM_UNIFORM=35, SIM_EXPON=36, SIM_FLIP=37, SIM_LOG_FLIP=38,
+    SIM_LOG_ODDS_FLIP=39,
+    LD_NORMAL=64, LD_GAMMA=65, LD_BETA=66, LD_UNIFORM=67, LD_EXPON=68, LD_FLIP=69, LD_LOG_FLIP=70,
+    LD_LOG_ODDS_FLIP=71,
+    STORE=96)
+INSTR_WORDS = 5          # op, dst, a, b, c
+MAX_REGS = 96
+
+DET = {"add": ("fold", "ADD"), "mul": ("fold", "MUL"), "sub": (2, "SUB"), "div": (2, "DIV"), "pow": (2, "POW"),
+       "min": (2, "MIN"), "max": (2, "MAX"), "sqrt": (1, "SQRT"), "exp": (1, "EXP"), "log": (1, "LOG"),
+       "log1p": (1, "LOG1P"), "expm1": (1, "EXPM1"), "logistic": (1, "LOGISTIC"), "log_logistic": (1, "LOG_LOGISTIC"),
+       "logit": (1, "LOGIT"), "negate": (1, "NEG"), "abs": (1, "ABS")}
+RANDOM = {"normal": (2, "NORMAL"), "gamma": (2, "GAMMA"), "beta": (2, "BETA"), "uniform_continuous": (2, "UNIFORM"),
+          "expon": (1, "EXPON"), "flip": (1, "FLIP"), "bernoulli": (1, "FLIP"), "log_flip": (1, "LOG_FLIP"),
+          "log_bernoulli": (1, "LOG_FLIP"), "log_odds_flip": (1, "LOG_ODDS_FLIP"), "log_odds_bernoulli": (1, "LOG_ODDS_FLIP")}
+BOOLEAN_VALUED = ("FLIP", "LOG_FLIP", "LOG_ODDS_FLIP")
+
+
+def _plain(e):
+    """stack-dict expression / VentureValue -> nested python: str symbols, float numbers, bools, lists"""
+    if hasattr(e, "asStackDict"):
+        e = e.asStackDict()
+    if isinstance(e, dict):
+        t, v = e.get("type"), e.get("value")
+        if t == "symbol":
+            return str(v)
+        if t == "boolean":
+            return bool(v)
+        if isinstance(v, (int, float, np.integer, np.floating)) and not isinstance(v, bool):
+            return float(v)
+        raise VentureException("invalid_argument", "the model compiler has no value of type %r" % (t,))
+    if isinstance(e, (list, tuple)):
+        return [_plain(x) for x in e]
+    if isinstance(e, bool):
+        return e
+    if isinstance(e, (int, float, np.integer, np.floating)):
+        return float(e)
+    if isinstance(e, str):
+        return e
+    raise VentureException("invalid_argument", "cannot compile %r" % (e,))
+
+
+class Node(object):
+    __slots__ = ("kind", "op", "args", "value", "site", "hole", "deps", "rowvar", "lookups", "counted")
+
+    def __init__(self, kind, op=None, args=(), value=None):
+        self.kind, self.op, self.args, self.value = kind, op, tuple(args), value   # kind: const | hole | det | random
+        self.site = None       # site index for an unobserved random application
+        self.hole = None       # column of the group's table for a literal of an observation template
+        self.deps = frozenset()   # sites this node depends on (through deterministic paths AND as a random node's parameters)
+        self.rowvar = False
+        self.lookups = 0       # lookup nodes (symbol occurrences) whose source is this node
+        self.counted = True    # False for the inner steps of a variadic add / mul: ONE application node in Lite
+
+
+class Group(object):
+    """observations sharing one expression up to numeric literals"""
+
+    def __init__(self, template, root, n_holes):
+        self.template, self.root, self.n_holes = template, root, n_holes
+        self.rows = []         # per observation: literals..., observed value
+
+
+class Compiler(object):
+    def __init__(self):
+        self.nodes = []
+        self.env = {}          # symbol -> node id
+        self.sites = []        # node ids of the sites, in evaluation order
+        self.site_names = []
+        self.single_obs = []   # (node id, value) of observations compiled one by one
+        self.groups = {}       # template key -> Group
+        self.group_list = []
+        self.directives = []   # the program, for interchange
+        self.directive_sites = []   # per directive: the sites its evaluation creates (none for observes)
+
+    # -- building the node graph -------------------------------------------------------------------------
+    def _new(self, node):
+        self.nodes.append(node)
+        return len(self.nodes) - 1
+
+    def _expr(self, e, holes=None, observed_root=False):
+        """-> node id.  holes: list collecting the numeric literals of an observation template, or None"""
+        if isinstance(e, bool):
+            return self._new(Node("const", value=1.0 if e else 0.0))
+        if isinstance(e, float):
+            if holes is not None:
+                n = Node("hole")
+                n.hole, n.rowvar = len(holes), True
+                holes.append(e)
+                return self._new(n)
+            return self._new(Node("const", value=e))
+        if isinstance(e, str):
+            if e not in self.env:
+                raise VentureException("evaluation", "Cannot find symbol '%s'" % (e,))
+            src = self.env[e]
+            self.nodes[src].lookups += 1
+            return src
+        if not e:
+            raise VentureException("invalid_argument", "empty application")
+        head = e[0]
+        if not isinstance(head, str):
+            raise VentureException("invalid_argument", "the model compiler needs a builtin SP in operator position, not %r" % (head,))
+        if head in self.env:
+            raise VentureException("invalid_argument", "procedure application (%s ...) is outside the fixed-structure subset" % (head,))
+        args = [self._expr(a, holes) for a in e[1:]]
+        if head in DET:
+            arity, op = DET[head]
+            if arity == "fold":
+                if not args:
+                    return self._new(Node("const", value=0.0 if op == "ADD" else 1.0))
+                acc = args[0]
+                for i, a in enumerate(args[1:]):
+                    acc = self._finish(Node("det", op, (acc, a)))
+                    self.nodes[acc].counted = i == len(args) - 2
+                return acc
+            if len(args) != arity:
+                raise VentureException("invalid_argument", "%s takes %d argument(s)" % (head, arity))
+            return self._finish(Node("det", op, args))
+        if head in RANDOM:
+            arity, op = RANDOM[head]
+            if op == "FLIP" and not args:
+                args = [self._new(Node("const", value=0.5))]           # (flip) = (flip 0.5), discrete.py:98-102
+            if len(args) != arity:
+                raise VentureException("invalid_argument", "%s takes %d argument(s)" % (head, arity))
+            nid = self._finish(Node("random", op, args))
+            if not observed_root:
+                if holes is not None:
+                    raise VentureException("invalid_argument", "a latent random choice inside an observed expression is outside the fixed-structure subset")
+                self.nodes[nid].site = len(self.sites)
+                self.sites.append(nid)
+                self.site_names.append(None)
+            return nid
+        raise VentureException("invalid_argument", "SP %r is outside the model compiler's subset" % (head,))
+
+    def _finish(self, node):
+        deps, rowvar = set(), False
+        for a in node.args:
+            an = self.nodes[a]
+            rowvar = rowvar or an.rowvar
+            if an.kind == "random":
+                if an.site is None:
+                    raise VentureException("invalid_argument", "an observed value cannot be a parent in the fixed-structure subset")
+                deps.add(an.site)
+            else:
+                deps |= an.deps
+        node.deps, node.rowvar = frozenset(deps), rowvar
+        return self._new(node)
+
+    # -- directives -----------------------------------------------------------------------------------------
+    def assume(self, name, exp):
+        exp = _plain(exp)
+        first = len(self.sites)
+        nid = self._expr(exp)
+        n = self.nodes[nid]
+        if not isinstance(exp, str) and n.kind == "random":
+            self.site_names[n.site] = name          # (an alias's root is the lookup counted in _expr)
+        self.env[name] = nid
+        self.directives.append(interchange.define(name, exp))
+        self.directive_sites.append(list(range(first, len(self.sites))))
+        return nid
+
+    def observe(self, exp, value):
+        exp = _plain(exp)
+        v = _plain(value)
+        v = (1.0 if v else 0.0) if isinstance(v, bool) else float(v)
+        if not (isinstance(exp, list) and exp and exp[0] in RANDOM):
+            raise VentureException("invalid_argument", "only applications of random SPs can be observed (psp.py:459-461), not %r" % (exp,))
+        key = self._template_key(exp)
+        g = self.groups.get(key)
+        if g is None:
+            holes = []
+            start = len(self.nodes)
+            root = self._expr_observed(exp, holes)
+            g = Group(key, root, len(holes))
+            g.own = range(start, len(self.nodes))      # the template's own nodes: one copy per observation in Lite
+            self.groups[key] = g
+            self.group_list.append(g)
+            g.rows.append(holes + [v])
+        else:
+            lits = []
+            self._literals(exp, lits)
+            g.rows.append(lits + [v])
+            self._count_template_lookups(exp)
+        boolean = RANDOM[exp[0]][1] in BOOLEAN_VALUED
+        self.directives.append(interchange.observe(exp, interchange.boolean(v != 0.0) if boolean else interchange.number(v)))
+        self.directive_sites.append([])
+
+    def _expr_observed(self, exp, holes):
+        arity, op = RANDOM[exp[0]]
+        args = [self._expr(a, holes) for a in exp[1:]]
+        if op == "FLIP" and not args:
+            args = [self._new(Node("const", value=0.5))]
+        if len(args) != arity:
+            raise VentureException("invalid_argument", "%s takes %d argument(s)" % (exp[0], arity))
+        return self._finish(Node("random", op, args))
+
+    def _template_key(self, e):
+        if isinstance(e, bool):
+            return ("b", e)
+        if isinstance(e, float):
+            return "#"
+        if isinstance(e, str):
+            return ("s", e)
+        return tuple(self._template_key(x) for x in e)
+
+    def _literals(self, e, out):
+        if isinstance(e, float) and not isinstance(e, bool):
+            out.append(e)
+        elif isinstance(e, list):
+            for x in e[1:]:
+                self._literals(x, out)
+
+    def _count_template_lookups(self, e):
+        if isinstance(e, str):
+            self.nodes[self.env[e]].lookups += 1
+        elif isinstance(e, list):
+            for x in e[1:]:
+                self._count_template_lookups(x)
+
+    # -- code generation --------------------------------------------------------------------------------------
+    def compile(self):
+        return Program(self)
+
+
+class _Code(object):
+    """one straight-line section; registers are allocated per section from a shared pool of node -> register"""
+
+    def __init__(self, prog):
+        self.prog, self.words, self.done = prog, [], set()
+
+    def emit(self, op, dst=0, a=0, b=0, c=0):
+        self.words += [OP[op], dst, a, b, c]
+
+    def reg(self, nid):
+        return self.prog.reg_of(nid)
+
+    def need(self, nid, fresh_sites=()):
+        """make node nid's value available in its register (recursively); sites are loaded from memory"""
+        if nid in self.done:
+            return self.reg(nid)
+        n = self.prog.c.nodes[nid]
+        r = self.reg(nid)
+        if n.kind == "const":
+            self.emit("CONST", r, self.prog.const(n.value))
+        elif n.kind == "hole":
+            self.emit("DATA", r, n.hole)
+        elif n.kind == "random":
+            self.emit("SITE", r, n.site)
+        else:
+            regs = [self.need(a) for a in n.args]
+            self.emit(n.op, r, regs[0], regs[1] if len(regs) > 1 else 0)
+        self.done.add(nid)
+        return r
+
+    def log_density(self, nid, value_reg=None):
+        n = self.prog.c.nodes[nid]
+        regs = [self.need(a) for a in n.args]
+        x = value_reg if value_reg is not None else self.need(nid)
+        self.emit("LD_" + n.op, x, regs[0], regs[1] if len(regs) > 1 else 0)
+
+    def simulate(self, nid):
+        n = self.prog.c.nodes[nid]
+        regs = [self.need(a) for a in n.args]
+        r = self.reg(nid)
+        self.emit("SIM_" + n.op, r, regs[0], regs[1] if len(regs) > 1 else 0)
+        self.emit("STORE", r, n.site)
+        self.done.add(nid)
+
+
+class Program(object):
+    """The compiled blob: int32 code words, double constants, per-group tables, section directory."""
+
+    def __init__(self, c):
+        self.c = c
+        self._regs, self._consts, self._const_ix = {}, [], {}
+        nodes = c.nodes
+        S = len(c.sites)
+        if S == 0:
+            raise VentureException("invalid_argument", "the program has no unobserved random choice: nothing to infer")
+        # children of every site: random nodes (sites / group roots) whose parameters depend on it
+        site_children = [[] for _ in range(S)]
+        for nid in c.sites:
+            for s in nodes[nid].deps:
+                site_children[s].append(nid)
+        site_groups = [[] for _ in range(S)]
+        for gi, g in enumerate(c.group_list):
+            for s in nodes[g.root].deps:
+                site_groups[s].append(gi)
+        sections = []
+
+        def add(code):
+            sections.append(code.words)
+            return len(sections) - 1
+        # 0: PRIOR -- every site in evaluation order
+        code = _Code(self)
+        for nid in c.sites:
+            code.simulate(nid)
+        self.sec_prior = add(code)
+        # 1: JOINT -- log density of every site given its parents
+        code = _Code(self)
+        for nid in c.sites:
+            code.log_density(nid)
+        self.sec_joint = add(code)
+        self.sec_sim, self.sec_child, self.sec_own = [], [], []
+        for k, nid in enumerate(c.sites):
+            code = _Code(self)
+            code.simulate(nid)
+            self.sec_sim.append(add(code))
+            code = _Code(self)
+            for ch in site_children[k]:
+                code.log_density(ch)
+            self.sec_child.append(add(code))
+            code = _Code(self)
+            code.log_density(nid)
+            self.sec_own.append(add(code))
+        self.sec_group_pro, self.sec_group_row = [], []
+        for g in c.group_list:
+            pro = _Code(self)
+            root = nodes[g.root]
+            for nid in self._invariant_frontier(g.root):
+                pro.need(nid)
+            self.sec_group_pro.append(add(pro))
+            row = _Code(self)
+            row.done = set(pro.done)
+            vreg = self.reg_of(("value", id(g)))
+            row.emit("DATA", vreg, g.n_holes)
+            row.log_density(g.root, value_reg=vreg)
+            self.sec_group_row.append(add(row))
+            assert root.kind == "random"
+        self.site_groups = site_groups
+        self.n_sites, self.n_groups = S, len(c.group_list)
+        self.n_regs = len(self._regs)
+        if self.n_regs > MAX_REGS:
+            raise VentureException("invalid_argument", "the program needs %d registers; the generic kernel has %d" % (self.n_regs, MAX_REGS))
+        self.sections = sections
+        # numAffectedNodes per site (scaffold.py:67-68): the site + lookups of resampled nodes + deterministic applications downstream
+        self.affected = []
+        own = {}
+        for g in c.group_list:
+            for nid in g.own:
+                own[nid] = len(g.rows)
+        for k in range(S):
+            cnt = 1 + nodes[c.sites[k]].lookups
+            for nid, n in enumerate(nodes):
+                if n.kind == "det" and k in n.deps:          # deps stop at random nodes: these are k's deterministic descendants
+                    cnt += (own.get(nid, 1) if n.counted else 0) + n.lookups
+            self.affected.append(float(cnt))
+
+    def _invariant_frontier(self, root):
+        """row-independent nodes a group's row program reads: computed once in the group prologue"""
+        out = []
+
+        def walk(nid):
+            n = self.c.nodes[nid]
+            if not n.rowvar and nid != root:
+                out.append(nid)
+                return
+            for a in n.args:
+                walk(a)
+        walk(root)
+        return out
+
+    def reg_of(self, key):
+        if key not in self._regs:
+            self._regs[key] = len(self._regs)
+        return self._regs[key]
+
+    def const(self, v):
+        key = np.float64(v).tobytes()
+        if key not in self._const_ix:
+            self._const_ix[key] = len(self._consts)
+            self._consts.append(float(v))
+        return self._const_ix[key]
+
+    # -- the flat blob handed to vk_create_program (layout documented in include/venture_b200.h) ------------------
+    def blob(self):
+        code, directory = [], []
+        for words in self.sections:
+            directory += [len(code) // INSTR_WORDS, len(words) // INSTR_WORDS]
+            code += words
+        S, G = self.n_sites, self.n_groups
+        meta = [S, G, self.n_regs, len(self.sections), self.sec_prior, self.sec_joint]
+        for k in range(S):
+            meta += [self.sec_sim[k], self.sec_child[k], self.sec_own[k], len(self.site_groups[k])]
+        for k in range(S):
+            meta += self.site_groups[k]
+        data, off = [], 0
+        for gi, g in enumerate(self.c.group_list):
+            rows = np.asarray(g.rows, dtype=np.float64).reshape(len(g.rows), g.n_holes + 1)
+            meta += [self.sec_group_pro[gi], self.sec_group_row[gi], rows.shape[0], rows.shape[1], off]
+            data.append(rows.ravel())
+            off += rows.size
+        meta += directory
+        return (np.asarray(code, dtype=np.int32), np.asarray(self._consts or [0.0], dtype=np.float64),
+                np.asarray(meta, dtype=np.int32), np.concatenate(data) if data else np.zeros(1),
+                np.asarray(self.affected, dtype=np.float64))
+
+
+# ---- the model object B200TraceSet takes -----------------------------------------------------------------------
+class CompiledModel(object):
+    """A compiled program as a model of models.py: `B200TraceSet(CompiledModel(directives), P)`.
+    directives: [("assume", name, exp) | ("observe", exp, value)] with expressions as nested python lists
+    (`["normal", "mu", 1.0]`), stack dicts, or the host Venture's values."""
+    kind = 5
+
+    def __init__(self, directives):
+        c = Compiler()
+        for d in directives:
+            if d[0] in ("assume", "define"):
+                c.assume(d[1], d[2])
+            elif d[0] == "observe":
+                c.observe(d[1], d[2])
+            else:
+                raise VentureException("invalid_argument", "unknown directive %r" % (d[0],))
+        self.compiler = c
+        self.prog = c.compile()
+        self.site_names = list(c.site_names)
+        self.n_observations = sum(len(g.rows) for g in c.group_list)
+        self.source = list(directives)
+
+    def extended(self, more):
+        return CompiledModel(self.source + list(more))
+
+    def _create(self, n_particles, seed, device):
+        code, consts, meta, data, affected = self.prog.blob()
+        h = ctypes.c_void_p()
+        _lib.call("vk_create_program", n_particles, seed, device, _lib.ptr(code), code.size, _lib.ptr(consts), consts.size,
+                  _lib.ptr(meta), meta.size, _lib.ptr(data), data.size, _lib.ptr(affected), ctypes.byref(h))
+        return h
+
+    def _observe(self, h, *args):
+        raise VentureException("invalid_argument", "a compiled program holds its observations: extend the directive list "
+                                                   "(CompiledModel.extended) instead of observing into the batch")
+
+    # -- interchange.py ---------------------------------------------------------------------------------------
+    def program(self, obs):
+        return list(self.compiler.directives)
+
+    def _random_order(self):
+        """the random applications in evaluation order: ('site', k, boolean) | ('obs', value)"""
+        out = []
+        c = self.compiler
+        for d, new_sites in zip(c.directives, c.directive_sites):
+            for k in new_sites:
+                out.append(("site", k, c.nodes[c.sites[k]].op in BOOLEAN_VALUED))
+            if d[0] == "observe":
+                out.append(("obs", d[2]))
+        return out
+
+    def random_values(self, obs, sites):
+        out = []
+        for item in self._random_order():
+            if item[0] == "site":
+                out.append(interchange.boolean(sites[item[1]] != 0.0) if item[2] else interchange.number(sites[item[1]]))
+            else:
+                out.append(item[1])
+        return out
+
+    def sites_from_random_values(self, obs, values):
+        sites = np.zeros(self.prog.n_sites)
+        for item, v in zip(self._random_order(), values):
+            if item[0] == "site":
+                sites[item[1]] = float(interchange.unbox(v))
+        return sites

@@ -1,0 +1,402 @@
+// Generic particle kernels for COMPILED programs (venturecxx_b200/compiler.py): one register
+// machine interprets the site programs the compiler derived from the reference's scaffold rules
+// (backend/lite/scaffold.py:149-316) for ANY fixed-structure program over the scalar SPs of SURVEY 8(a) A12 --
+// no .cu file per model.
+//
+//   likelihood_weight   trace.py:522-530   PRIOR section (every site from its prior, in evaluation order), then
+//                                          lw := sum of the observation groups' log densities
+//   makeConsistent      trace.py:422-448   lw += log density of the observations (a leaf observation's rho is 0)
+//   resimulation_mh     mh.py:59-113, 167-208; detach.py:39-83; regen.py:58-161
+//                                          per transition and particle: block choice, rho = log densities absorbing
+//                                          at the site's border under the old value, SIM, xi under the new value,
+//                                          accept iff log u < xi - rho (with MHOperator's +-inf policy)
+//   log_likelihood_at / log_joint_at       dispatch.py:331-361
+//
+// Mapping.  LANES = 1: one thread per particle (few observations).  LANES = 32: one warp per particle, lanes take
+// the rows of an observation group in turn and the warp adds their sums (many observations per particle);
+// every lane runs the row-independent code redundantly with the same Philox stream, so no broadcast is needed.
+// Registers live in local memory (the register FILE of the machine is indexed dynamically); code, constants and
+// group tables are read through the read-only path and are the same addresses across a warp (one transaction).
+// RNG protocol of a transition = the hand-written kernels': Stream(seed, particle, step0 + t): draw 0 block
+// choice, draw 1 accept uniform, then the proposal's draws -- a compiled normal-normal model reproduces
+// nn_mh_kernel's chains bit for bit (tests/test_gpu_program.py).
+//
+// The same interpreter restated on the CPU is the oracle (oracle/oracle.c orc_vm_*).
+#include "vk_common.cuh"
+#include "sp_math.cuh"
+
+namespace vk {
+
+enum VMOp {
+  VM_CONST = 0, VM_SITE = 1, VM_DATA = 2, VM_ADD = 3, VM_SUB = 4, VM_MUL = 5, VM_DIV = 6, VM_NEG = 7, VM_EXP = 8,
+  VM_LOG = 9, VM_SQRT = 10, VM_POW = 11, VM_LOGISTIC = 12, VM_ABS = 13, VM_MIN = 14, VM_MAX = 15, VM_LOG1P = 16,
+  VM_EXPM1 = 17, VM_LOG_LOGISTIC = 18, VM_LOGIT = 19,
+  VM_SIM_NORMAL = 32, VM_SIM_GAMMA = 33, VM_SIM_BETA = 34, VM_SIM_UNIFORM = 35, VM_SIM_EXPON = 36, VM_SIM_FLIP = 37,
+  VM_SIM_LOG_FLIP = 38, VM_SIM_LOG_ODDS_FLIP = 39,
+  VM_LD_NORMAL = 64, VM_LD_GAMMA = 65, VM_LD_BETA = 66, VM_LD_UNIFORM = 67, VM_LD_EXPON = 68, VM_LD_FLIP = 69,
+  VM_LD_LOG_FLIP = 70, VM_LD_LOG_ODDS_FLIP = 71,
+  VM_STORE = 96
+};
+static const int VM_WORDS = 5;
+static const int VM_MAX_REGS = 96;
+
+// device-resident program (all pointers into one allocation each)
+struct VMProg {
+  const int32_t *code;       // VM_WORDS words per instruction
+  const double *consts;
+  const double *data;        // group tables, row-major
+  const int32_t *dir;        // per section: first instruction, count
+  const int32_t *site_tab;   // per site: SIM, CHILD, OWN section, number of groups, offset into site_groups
+  const int32_t *site_groups;
+  const int32_t *group_tab;  // per group: prologue section, row section, rows, columns, data offset
+  const double *affected;    // per site: nodes of Lite's scaffold (scaffold.py:67-68)
+  int n_sites, n_groups, sec_prior, sec_joint;
+};
+
+// one straight-line section.  row: the current row of a group table (nullptr outside row programs).
+__device__ __forceinline__ void vm_exec(const VMProg &pg, int section, double *R, double *sites, int64_t P, int64_t p,
+                                        const double *row, Stream *rng, double &acc, bool store) {
+  const int first = __ldg(&pg.dir[2 * section]), n = __ldg(&pg.dir[2 * section + 1]);
+  const int32_t *ip = pg.code + (size_t)first * VM_WORDS;
+  for (int i = 0; i < n; ++i, ip += VM_WORDS) {
+    const int op = __ldg(ip), d = __ldg(ip + 1), a = __ldg(ip + 2), b = __ldg(ip + 3);
+    switch (op) {
+      case VM_CONST: R[d] = __ldg(&pg.consts[a]); break;
+      case VM_SITE: R[d] = sites[(int64_t)a * P + p]; break;
+      case VM_DATA: R[d] = __ldg(&row[a]); break;
+      case VM_ADD: R[d] = R[a] + R[b]; break;
+      case VM_SUB: R[d] = R[a] - R[b]; break;
+      case VM_MUL: R[d] = R[a] * R[b]; break;
+      case VM_DIV: R[d] = R[a] / R[b]; break;
+      case VM_NEG: R[d] = -R[a]; break;
+      case VM_EXP: R[d] = exp(R[a]); break;
+      case VM_LOG: R[d] = vlog(R[a]); break;
+      case VM_SQRT: R[d] = sqrt(R[a]); break;
+      case VM_POW: R[d] = pow(R[a], R[b]); break;
+      case VM_LOGISTIC: R[d] = logistic(R[a]); break;
+      case VM_ABS: R[d] = fabs(R[a]); break;
+      case VM_MIN: R[d] = fmin(R[a], R[b]); break;
+      case VM_MAX: R[d] = fmax(R[a], R[b]); break;
+      case VM_LOG1P: R[d] = vlog1p(R[a]); break;
+      case VM_EXPM1: R[d] = expm1(R[a]); break;
+      case VM_LOG_LOGISTIC: R[d] = log_logistic(R[a]); break;
+      case VM_LOGIT: R[d] = logit(R[a]); break;
+      case VM_SIM_NORMAL: R[d] = normal_sim(*rng, R[a], R[b]); break;
+      case VM_SIM_GAMMA: R[d] = gamma_sim(*rng, R[a], R[b]); break;
+      case VM_SIM_BETA: R[d] = beta_sim(*rng, R[a], R[b]); break;
+      case VM_SIM_UNIFORM: R[d] = uniform_sim(*rng, R[a], R[b]); break;
+      case VM_SIM_EXPON: R[d] = expon_sim(*rng, R[a]); break;
+      case VM_SIM_FLIP: R[d] = flip_sim(*rng, R[a]) ? 1.0 : 0.0; break;
+      case VM_SIM_LOG_FLIP: R[d] = log_flip_sim(*rng, R[a]) ? 1.0 : 0.0; break;
+      case VM_SIM_LOG_ODDS_FLIP: R[d] = log_odds_flip_sim(*rng, R[a]) ? 1.0 : 0.0; break;
+      case VM_LD_NORMAL: acc += normal_logpdf(R[d], R[a], R[b]); break;
+      case VM_LD_GAMMA: acc += gamma_logpdf(R[d], R[a], R[b]); break;
+      case VM_LD_BETA: acc += beta_logpdf(R[d], R[a], R[b]); break;
+      case VM_LD_UNIFORM: acc += uniform_logpdf(R[d], R[a], R[b]); break;
+      case VM_LD_EXPON: acc += expon_logpdf(R[d], R[a]); break;
+      case VM_LD_FLIP: acc += flip_logpmf(R[d] != 0.0, R[a]); break;
+      case VM_LD_LOG_FLIP: acc += log_flip_logpmf(R[d] != 0.0, R[a]); break;
+      case VM_LD_LOG_ODDS_FLIP: acc += log_odds_flip_logpmf(R[d] != 0.0, R[a]); break;
+      case VM_STORE: if (store) sites[(int64_t)a * P + p] = R[d]; break;
+      default: break;
+    }
+  }
+}
+
+// log density of group g's observations (prologue once, then the rows); LANES lanes share the rows
+template <int LANES>
+__device__ __forceinline__ double vm_group(const VMProg &pg, int g, double *R, double *sites, int64_t P, int64_t p, int lane) {
+  const int32_t *gt = pg.group_tab + 5 * g;
+  const int sec_pro = __ldg(gt), sec_row = __ldg(gt + 1), n_rows = __ldg(gt + 2), n_cols = __ldg(gt + 3), off = __ldg(gt + 4);
+  double dummy = 0.0;
+  vm_exec(pg, sec_pro, R, sites, P, p, nullptr, nullptr, dummy, false);
+  double part = 0.0;
+  for (int r = lane; r < n_rows; r += LANES)
+    vm_exec(pg, sec_row, R, sites, P, p, pg.data + off + (size_t)r * n_cols, nullptr, part, false);
+  if (LANES == 32) part = warp_sum(part);
+  return part;
+}
+
+// what absorbs at site k's border: child sites (CHILD section) + the observation groups below k
+template <int LANES>
+__device__ __forceinline__ double vm_children(const VMProg &pg, int k, double *R, double *sites, int64_t P, int64_t p, int lane) {
+  const int32_t *st = pg.site_tab + 5 * k;
+  double acc = 0.0;
+  vm_exec(pg, __ldg(st + 1), R, sites, P, p, nullptr, nullptr, acc, false);
+  const int ng = __ldg(st + 3), go = __ldg(st + 4);
+  for (int j = 0; j < ng; ++j) acc += vm_group<LANES>(pg, __ldg(&pg.site_groups[go + j]), R, sites, P, p, lane);
+  return acc;
+}
+
+template <int LANES>
+__device__ __forceinline__ double vm_all_groups(const VMProg &pg, double *R, double *sites, int64_t P, int64_t p, int lane) {
+  double acc = 0.0;
+  for (int g = 0; g < pg.n_groups; ++g) acc += vm_group<LANES>(pg, g, R, sites, P, p, lane);
+  return acc;
+}
+
+__device__ __forceinline__ double vm_log_alpha(double rho, double xi) {      // mh.py:187-208
+  if (rho == -INFINITY && xi == -INFINITY) return INFINITY;
+  if (rho == INFINITY && xi == INFINITY) return -INFINITY;
+  return xi - rho;
+}
+
+enum { VM_MODE_PRIOR = 0, VM_MODE_LW = 1, VM_MODE_CONSISTENT = 2, VM_MODE_LOGLIK = 3 };
+
+// mode PRIOR: sites from the prior.  LW: the same, lw := log density of the observations.  CONSISTENT: lw += that,
+// increments out.  LOGLIK: out := xi of the scaffold of `block` (VK_BLOCK_ALL: every observation), + the
+// principal nodes' own densities when joint.
+template <int LANES>
+__global__ void __launch_bounds__(256)
+prog_kernel(VMProg pg, double *sites, double *lw, double *out, int64_t P, int64_t p_base, uint64_t seed, uint32_t step,
+            int mode, int block, int joint) {
+  double R[VM_MAX_REGS];
+  const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
+  const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
+  for (int64_t p = unit; p < P; p += n_units) {
+    double dummy = 0.0;
+    if (mode == VM_MODE_PRIOR || mode == VM_MODE_LW) {
+      Stream r(seed, (uint64_t)(p_base + p), step);
+      vm_exec(pg, pg.sec_prior, R, sites, P, p, nullptr, &r, dummy, lane == 0);
+      if (LANES == 32) __syncwarp();
+    }
+    if (mode == VM_MODE_PRIOR) continue;
+    double v;
+    if (mode == VM_MODE_LOGLIK && block >= 0) {
+      v = vm_children<LANES>(pg, block, R, sites, P, p, lane);
+      if (joint) vm_exec(pg, __ldg(&pg.site_tab[5 * block + 2]), R, sites, P, p, nullptr, nullptr, v, false);
+    } else {
+      v = vm_all_groups<LANES>(pg, R, sites, P, p, lane);
+      if (mode == VM_MODE_LOGLIK && joint) vm_exec(pg, pg.sec_joint, R, sites, P, p, nullptr, nullptr, v, false);
+    }
+    if (lane != 0) continue;
+    if (mode == VM_MODE_LW) lw[p] = v;
+    else if (mode == VM_MODE_CONSISTENT) {
+      if (v != v) v = -INFINITY;              // lite/trace.py:438-448
+      lw[p] += v;
+      if (out) out[p] = v;
+    } else out[p] = v;
+  }
+}
+
+template <int LANES>
+__global__ void __launch_bounds__(256)
+prog_mh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps,
+               int block_mode, double *nodes_out, long long *acc_out) {
+  double R[VM_MAX_REGS];
+  const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
+  const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
+  const int S = pg.n_sites;
+  for (int64_t p = unit; p < P; p += n_units) {
+    long long acc = 0;
+    double nodes = 0.0;
+    for (int t = 0; t < n_steps; ++t) {
+      Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)t);
+      const double u_sel = r.uniform();                   // draw 0: block choice
+      const double logu = log(r.uniform());               // draw 1: accept uniform (mh.py:85)
+      int k;
+      if (block_mode == VK_BLOCK_ONE) { k = (int)(u_sel * (double)S); if (k >= S) k = S - 1; }
+      else if (block_mode == VK_BLOCK_EACH) k = t % S;
+      else k = block_mode;
+      const double rho = vm_children<LANES>(pg, k, R, sites, P, p, lane);
+      const double old = sites[(int64_t)k * P + p];
+      if (LANES == 32) __syncwarp();                      // every lane has read the old value
+      double dummy = 0.0;
+      vm_exec(pg, __ldg(&pg.site_tab[5 * k]), R, sites, P, p, nullptr, &r, dummy, lane == 0);
+      if (LANES == 32) __syncwarp();                      // the new value is in memory for every lane
+      const double xi = vm_children<LANES>(pg, k, R, sites, P, p, lane);
+      if (logu < vm_log_alpha(rho, xi)) ++acc;
+      else { if (LANES == 32) __syncwarp(); if (lane == 0) sites[(int64_t)k * P + p] = old; if (LANES == 32) __syncwarp(); }
+      nodes += __ldg(&pg.affected[k]);
+    }
+    if (lane == 0) {
+      if (acc_out) acc_out[p] = acc;
+      // `one`: the mean over the transitions of the chosen sites' counts (dispatch.py:109-120); other block modes
+      // have a particle-independent value, filled by the host
+      if (nodes_out && block_mode == VK_BLOCK_ONE) nodes_out[p] = n_steps > 0 ? nodes / (double)n_steps : 0.0;
+    }
+  }
+}
+
+__global__ void prog_fill_kernel(double *out, int64_t n, double v) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = v;
+}
+
+struct ProgramModel : Model {
+  std::vector<double> affected_host;
+  DevBuf<int32_t> code, tables;       // tables: dir | site_tab | site_groups | group_tab
+  DevBuf<double> consts, data, affected;
+  DevBuf<double> sa, sb;
+  double *sites = nullptr, *sites_alt = nullptr;
+  VMProg pg;
+  int S = 0, G = 0, n_regs = 0, n_sections = 0;
+  int64_t max_rows = 0;
+  bool propagated = false;
+
+  ProgramModel(vk_particles *h_, const int32_t *code_h, int64_t n_code, const double *consts_h, int64_t n_consts,
+               const int32_t *meta, int64_t n_meta, const double *data_h, int64_t n_data, const double *affected_h)
+      : Model(h_) {
+    VK_REQUIRE(n_meta >= 6, VK_EINVAL, "program: truncated meta block");
+    S = meta[0]; G = meta[1]; n_regs = meta[2]; n_sections = meta[3];
+    VK_REQUIRE(S >= 1 && G >= 0 && n_sections >= 2, VK_EINVAL, "program: bad header");
+    VK_REQUIRE(n_regs <= VM_MAX_REGS, VK_EUNSUPPORTED, "program: too many registers for the generic kernel");
+    VK_REQUIRE(n_code % VM_WORDS == 0, VK_EINVAL, "program: code length is not a whole number of instructions");
+    // meta: header(6) | per site (sim, child, own, n_groups) | site group lists | per group (pro, row, rows, cols, off) | directory
+    std::vector<int32_t> site_tab((size_t)S * 5), site_groups, group_tab((size_t)(G > 0 ? G : 1) * 5, 0);
+    int64_t at = 6;
+    VK_REQUIRE(n_meta >= at + 4 * (int64_t)S, VK_EINVAL, "program: truncated site table");
+    int total_groups = 0;
+    for (int k = 0; k < S; ++k) {
+      for (int j = 0; j < 4; ++j) site_tab[(size_t)k * 5 + j] = meta[at + 4 * k + j];
+      site_tab[(size_t)k * 5 + 4] = total_groups;
+      VK_REQUIRE(meta[at + 4 * k + 3] >= 0, VK_EINVAL, "program: negative group count");
+      total_groups += meta[at + 4 * k + 3];
+    }
+    at += 4 * (int64_t)S;
+    VK_REQUIRE(n_meta >= at + total_groups + 5 * (int64_t)G + 2 * (int64_t)n_sections, VK_EINVAL, "program: truncated tables");
+    for (int j = 0; j < total_groups; ++j) {
+      VK_REQUIRE(meta[at + j] >= 0 && meta[at + j] < G, VK_EINVAL, "program: group index out of range");
+      site_groups.push_back(meta[at + j]);
+    }
+    at += total_groups;
+    for (int g = 0; g < G; ++g) {
+      for (int j = 0; j < 5; ++j) group_tab[(size_t)g * 5 + j] = meta[at + 5 * g + j];
+      const int64_t rows = meta[at + 5 * g + 2], cols = meta[at + 5 * g + 3], off = meta[at + 5 * g + 4];
+      VK_REQUIRE(rows >= 0 && cols >= 1 && off >= 0 && off + rows * cols <= n_data, VK_EINVAL, "program: group table out of range");
+      if (rows > max_rows) max_rows = rows;
+    }
+    at += 5 * (int64_t)G;
+    std::vector<int32_t> dir(meta + at, meta + at + 2 * (int64_t)n_sections);
+    const int64_t n_instr = n_code / VM_WORDS;
+    for (int s = 0; s < n_sections; ++s)
+      VK_REQUIRE(dir[2 * s] >= 0 && dir[2 * s + 1] >= 0 && (int64_t)dir[2 * s] + dir[2 * s + 1] <= n_instr, VK_EINVAL,
+                 "program: section out of range");
+    for (int64_t i = 0; i < n_instr; ++i) {          // every operand index is checked once, here
+      const int32_t *w = code_h + i * VM_WORDS;
+      const int op = w[0];
+      auto reg = [&](int r) { VK_REQUIRE(r >= 0 && r < n_regs, VK_EINVAL, "program: register out of range"); };
+      reg(w[1]);
+      if (op == VM_CONST) VK_REQUIRE(w[2] >= 0 && w[2] < n_consts, VK_EINVAL, "program: constant out of range");
+      else if (op == VM_SITE || op == VM_STORE) VK_REQUIRE(w[2] >= 0 && w[2] < S, VK_EINVAL, "program: site out of range");
+      else if (op == VM_DATA) VK_REQUIRE(w[2] >= 0, VK_EINVAL, "program: column out of range");
+      else { reg(w[2]); reg(w[3]); }
+    }
+    for (int g = 0; g < G; ++g) {                    // DATA columns are checked against the table of the group that reads them
+      const int pro = group_tab[(size_t)g * 5], row = group_tab[(size_t)g * 5 + 1], cols = group_tab[(size_t)g * 5 + 3];
+      VK_REQUIRE(pro >= 0 && pro < n_sections && row >= 0 && row < n_sections, VK_EINVAL, "program: bad section id");
+      for (int i = dir[2 * pro]; i < dir[2 * pro] + dir[2 * pro + 1]; ++i)
+        VK_REQUIRE(code_h[(int64_t)i * VM_WORDS] != VM_DATA, VK_EINVAL, "program: a group prologue reads no table column");
+      for (int i = dir[2 * row]; i < dir[2 * row] + dir[2 * row + 1]; ++i)
+        if (code_h[(int64_t)i * VM_WORDS] == VM_DATA)
+          VK_REQUIRE(code_h[(int64_t)i * VM_WORDS + 2] < cols, VK_EINVAL, "program: column out of range");
+    }
+    for (int k = 0; k < S; ++k)
+      for (int j = 0; j < 3; ++j)
+        VK_REQUIRE(site_tab[(size_t)k * 5 + j] >= 0 && site_tab[(size_t)k * 5 + j] < n_sections, VK_EINVAL, "program: bad section id");
+    VK_REQUIRE(meta[4] >= 0 && meta[4] < n_sections && meta[5] >= 0 && meta[5] < n_sections, VK_EINVAL, "program: bad section id");
+    // upload
+    std::vector<int32_t> all;
+    const size_t o_dir = 0;
+    all.insert(all.end(), dir.begin(), dir.end());
+    const size_t o_site = all.size();
+    all.insert(all.end(), site_tab.begin(), site_tab.end());
+    const size_t o_sg = all.size();
+    all.insert(all.end(), site_groups.begin(), site_groups.end());
+    all.push_back(0);
+    const size_t o_gt = all.size();
+    all.insert(all.end(), group_tab.begin(), group_tab.end());
+    code.alloc((size_t)(n_code > 0 ? n_code : 1)); tables.alloc(all.size());
+    consts.alloc((size_t)(n_consts > 0 ? n_consts : 1)); data.alloc((size_t)(n_data > 0 ? n_data : 1)); affected.alloc((size_t)S);
+    VK_CUDA(cudaMemcpyAsync(code.p, code_h, (size_t)n_code * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    VK_CUDA(cudaMemcpyAsync(tables.p, all.data(), all.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    if (n_consts > 0) VK_CUDA(cudaMemcpyAsync(consts.p, consts_h, (size_t)n_consts * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (n_data > 0) VK_CUDA(cudaMemcpyAsync(data.p, data_h, (size_t)n_data * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    VK_CUDA(cudaMemcpyAsync(affected.p, affected_h, (size_t)S * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    VK_CUDA(cudaStreamSynchronize(h->stream));      // the host vectors die with this constructor
+    sa.alloc((size_t)S * h->P); sb.alloc((size_t)S * h->P);
+    sites = sa.p; sites_alt = sb.p;
+    VK_CUDA(cudaMemsetAsync(sites, 0, sa.bytes(), h->stream));
+    pg.code = code.p; pg.consts = consts.p; pg.data = data.p;
+    pg.dir = tables.p + o_dir; pg.site_tab = tables.p + o_site; pg.site_groups = tables.p + o_sg; pg.group_tab = tables.p + o_gt;
+    pg.affected = affected.p;
+    affected_host.assign(affected_h, affected_h + S);
+    pg.n_sites = S; pg.n_groups = G; pg.sec_prior = meta[4]; pg.sec_joint = meta[5];
+  }
+  bool warp_mode() const { return max_rows >= 64; }
+  int grid(bool warp) const { return grid_for(warp ? h->P * 32 : h->P, 256, h->sm_count, 8); }
+  void launch(int mode, double *out, uint32_t step, int block = VK_BLOCK_ALL, int joint = 0) {
+    const bool wm = warp_mode();
+    if (wm) prog_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->lw.p, out, h->P, h->p_base, h->seed, step, mode, block, joint);
+    else prog_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->lw.p, out, h->P, h->p_base, h->seed, step, mode, block, joint);
+    VK_CUDA(cudaGetLastError());
+  }
+  void reset_to_prior() override { launch(VM_MODE_PRIOR, nullptr, h->next_step()); }
+  void likelihood_weight() override { propagated = true; launch(VM_MODE_LW, nullptr, h->next_step()); }
+  void make_consistent(double *incr_dev) override {
+    if (propagated) {
+      if (incr_dev) VK_CUDA(cudaMemsetAsync(incr_dev, 0, (size_t)h->P * sizeof(double), h->stream));
+      return;
+    }
+    launch(VM_MODE_CONSISTENT, incr_dev, 0);
+    propagated = true;
+  }
+  int block_of(int scope, int block, bool allow_all) const {
+    VK_REQUIRE(scope == 0, VK_EINVAL, "program: only the default scope is compiled");
+    if (block == VK_BLOCK_ONE || block == VK_BLOCK_EACH) return block;
+    if (block == VK_BLOCK_ALL) { VK_REQUIRE(allow_all, VK_EUNSUPPORTED, "program: block 'all' is not compiled for resimulation_mh"); return block; }
+    VK_REQUIRE(block >= 0 && block < S, VK_EINVAL, "program: block must be one / each / a site index");
+    return block;
+  }
+  void mh(int scope, int block, int K, double *mean_nodes_dev, long long *acc_dev) override {
+    block = block_of(scope, block, false);
+    VK_REQUIRE(propagated || G == 0, VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
+    const int n_steps = block == VK_BLOCK_EACH ? K * S : K;
+    const uint32_t step0 = h->next_step((uint32_t)n_steps);
+    if (warp_mode()) prog_mh_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, block, mean_nodes_dev, acc_dev);
+    else prog_mh_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, block, mean_nodes_dev, acc_dev);
+    if (mean_nodes_dev && block != VK_BLOCK_ONE) {
+      double v = 0.0;
+      if (K > 0 && block == VK_BLOCK_EACH) {       // scaffolder_loop: the blocks' counts summed, FLOOR-divided by #blocks (dispatch.py:122-128)
+        double sum = 0.0;
+        for (double a : affected_host) sum += a;
+        v = floor(sum / (double)S);
+      } else if (K > 0) v = affected_host[(size_t)block];
+      prog_fill_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, v);
+    }
+    VK_CUDA(cudaGetLastError());
+  }
+  void log_likelihood_at(int scope, int block, bool joint, double *out_dev) override {
+    block = block_of(scope, block, true);
+    VK_REQUIRE(block == VK_BLOCK_ALL || block >= 0, VK_EINVAL, "log_likelihood_at: block must be all or a site index");
+    launch(VM_MODE_LOGLIK, out_dev, 0, block, joint ? 1 : 0);
+  }
+  int64_t num_sites() const override { return S; }
+  int64_t num_blocks(int) const override { return S; }
+  void read_site(int64_t site, double *out_dev) override {
+    VK_REQUIRE(site >= 0 && site < S, VK_EINVAL, "program: site out of range");
+    VK_CUDA(cudaMemcpyAsync(out_dev, sites + site * h->P, (size_t)h->P * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  }
+  void write_site(int64_t site, const double *in_dev) override {
+    VK_REQUIRE(site >= 0 && site < S, VK_EINVAL, "program: site out of range");
+    VK_CUDA(cudaMemcpyAsync(sites + site * h->P, in_dev, (size_t)h->P * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  }
+  std::vector<StateArray> state_arrays(bool) override {
+    StateArray a{(void **)&sites, (void **)&sites_alt, 0, (size_t)S, 8};
+    return {a};
+  }
+  void resized(int64_t n_new, const std::vector<void *> &nc, const std::vector<void *> &na) override {
+    sa.adopt(nc[0], (size_t)n_new * S); sb.adopt(na[0], (size_t)n_new * S);
+    sites = sa.p; sites_alt = sb.p;
+  }
+  int device_buffer(int which, void **p, int64_t *bytes) override {
+    if (which == 1) { *p = sites; *bytes = (int64_t)sa.bytes(); return VK_OK; }
+    return VK_EINVAL;
+  }
+};
+
+Model *make_program(vk_particles *h, const int32_t *code, int64_t n_code, const double *consts, int64_t n_consts,
+                    const int32_t *meta, int64_t n_meta, const double *data, int64_t n_data, const double *affected) {
+  return new ProgramModel(h, code, n_code, consts, n_consts, meta, n_meta, data, n_data, affected);
+}
+
+}  // namespace vk

@@ -25,5 +25,8 @@ Model *make_lda(vk_particles *h, int K, int V, int n_docs, int max_tokens, doubl
                 double hyper_rate);
 void lda_observe(Model *m, const int32_t *doc_host, const int32_t *word_host, int64_t n);
 
+Model *make_program(vk_particles *h, const int32_t *code, int64_t n_code, const double *consts, int64_t n_consts,
+                    const int32_t *meta, int64_t n_meta, const double *data, int64_t n_data, const double *affected);
+
 void launch_axpy(vk_particles *h, double *y, const double *x, int64_t n);  // y += x
 }  // namespace vk

@@ -109,6 +109,19 @@ VK_HD double beta_sim(Stream &r, double a, double b) {
 }
 
 // ---- flip family: discrete.py:55-67, 105-113, 143-150 --------------------
+// ---- uniform_continuous (continuous.py:633-640): scipy.stats.uniform.logpdf(x, low, high - low) --------
+VK_HD double uniform_logpdf(double x, double lo, double hi) {
+  const double scale = hi - lo, y = (x - lo) / scale;
+  return (y >= 0.0 && y <= 1.0) ? -log(scale) : VK_NEG_INF;
+}
+VK_HD double uniform_sim(Stream &r, double lo, double hi) { return lo + (hi - lo) * r.uniform(); }
+// ---- expon (continuous.py:1130-1137): scipy.stats.expon.logpdf(x, scale = 1/theta) --------------------
+VK_HD double expon_logpdf(double x, double theta) {
+  const double scale = 1.0 / theta, y = x / scale;
+  return y >= 0.0 ? -y - log(scale) : VK_NEG_INF;
+}
+VK_HD double expon_sim(Stream &r, double theta) { return -log1p(-r.uniform()) * (1.0 / theta); }
+
 VK_HD double flip_logpmf(bool val, double p) { return val ? vlog(p) : vlog1p(-p); }
 VK_HD bool flip_sim(Stream &r, double p) { return r.uniform() < p; }
 VK_HD double log_flip_logpmf(bool val, double logp) { return val ? logp : vlog1p(-exp(logp)); }

@@ -107,6 +107,19 @@ int vk_create_normal_normal(int64_t P, uint64_t seed, int device, double prior_m
   VK_CATCH
 }
 
+int vk_create_program(int64_t P, uint64_t seed, int device, const int32_t *code, int64_t n_code, const double *consts,
+                      int64_t n_consts, const int32_t *meta, int64_t n_meta, const double *data, int64_t n_data,
+                      const double *affected, vk_particles **out) {
+  VK_TRY
+  VK_REQUIRE(out && code && consts && meta && data && affected, VK_EINVAL, "vk_create_program: NULL argument");
+  VK_REQUIRE(n_code >= 0 && n_consts >= 0 && n_meta >= 0 && n_data >= 0, VK_EINVAL, "vk_create_program: negative length");
+  vk_particles *h = new_handle(VK_MODEL_PROGRAM, P, seed, device);
+  try { h->model = make_program(h, code, n_code, consts, n_consts, meta, n_meta, data, n_data, affected); }
+  catch (...) { cudaStreamDestroy(h->own_stream); delete h; throw; }
+  finish_create(h, out);
+  VK_CATCH
+}
+
 int vk_create_blr(int64_t P, uint64_t seed, int device, int32_t D, int64_t n_obs_capacity,
                   double prior_mu, double prior_sigma, vk_particles **out) {
   VK_TRY

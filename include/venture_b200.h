@@ -112,6 +112,10 @@ int vk_create_program(int64_t n_particles, uint64_t seed, int device, const int3
                       int64_t n_code, const double *consts, int64_t n_consts,
                       const int32_t *meta, int64_t n_meta, const double *data, int64_t n_data,
                       const double *affected, vk_particles **out);
+/* Sites first_site.. of a compiled program from their priors given the CURRENT values of the
+ * earlier sites: what evaluating further `assume` directives does to an existing trace
+ * (lite/trace.py:397-401 eval -> regen.py:181-230 evalFamily), for all particles. */
+int vk_program_resimulate(vk_particles *h, int32_t first_site);
 /* X rows are D doubles; capacity n_obs_capacity observations. */
 int vk_create_blr(int64_t n_particles, uint64_t seed, int device, int32_t D,
                   int64_t n_obs_capacity, double prior_mu, double prior_sigma,

@@ -313,3 +313,45 @@ def test_reference_engine_hmm_particle_filter_program():
         s = e.model.b200.read_site(t).astype(np.int64)
         m = np.bincount(s, minlength=6)[1:6] / float(P)
         assert 0.5 * np.abs(m - np.array(H["filtered_marginals"][t])).sum() < 0.02, t
+
+
+@pytest.mark.gpu
+def test_reference_engine_compiles_the_program_from_its_directives():
+    """B200() without a hand-described model: the directives the engine evaluates are compiled (N2).  A linear
+    regression -- a model with no .cu file -- through the reference Engine, against the same compiled model
+    driven directly, and its posterior mean against the conjugate answer for the slope."""
+    import venturecxx_b200 as vb
+    from venturecxx_b200 import backend as bk
+    from venturecxx_b200.compiler import CompiledModel
+    rng = np.random.default_rng(2)
+    xs = np.round(rng.normal(size=12), 3)
+    ys = np.round(1.2 * xs + 0.1 * rng.normal(size=12), 3)
+    e = _engine(bk.B200(), seed=9)
+    assert e.num_traces() == 1
+    e.assume("a", ref_engine.expression("(normal 0 2)"))
+    e.infer(ref_engine.program("(resample 256)"))
+    for x, y in zip(xs, ys):
+        e.observe(ref_engine.expression("(normal (* a %r) 0.5)" % (float(x),)), ref_engine.value(float(y)))
+    assert e.num_traces() == 256
+    ts = e.model.b200
+    assert ts.num_sites() == 1 and ts.model.n_observations == 12
+    # weights accumulated observation by observation = log likelihood of all of them + the evened-out start
+    ll = ts.log_likelihood_at("default", "all")
+    lw = np.array(e.model.log_weights)
+    np.testing.assert_allclose(lw - lw[0], ll - ll[0], rtol=1e-9, atol=1e-9)
+    _, nodes = e.infer(ref_engine.program("(resimulation_mh default one 200)"))
+    a = ts.read_site(0)
+    prec = 1 / 4.0 + (xs ** 2).sum() / 0.25
+    mean = (xs * ys).sum() / 0.25 / prec
+    assert abs(a.mean() - mean) < 5 * np.sqrt(1 / prec / 256) + 0.01
+    # a later assume extends the program: old sites keep their values, the new one is drawn from its prior
+    e.assume("b", ref_engine.expression("(normal a 1)"))
+    ts2 = e.model.b200
+    assert ts2.num_sites() == 2
+    np.testing.assert_array_equal(ts2.read_site(0), a)
+    assert abs(np.mean(ts2.read_site(1) - a)) < 0.3 and 0.7 < np.std(ts2.read_site(1) - a) < 1.3
+    # outside the subset: the error names the directive
+    with pytest.raises(Exception) as err:
+        e.assume("f", ref_engine.expression("(lambda (x) x)"))
+    assert "outside" in str(err.value) or "subset" in str(err.value)
+    assert isinstance(ts2.model, CompiledModel) and vb is not None

@@ -27,6 +27,7 @@ PROTOTYPES = {
     "vk_device_count": [_vp],
     "vk_create_normal_normal": [_i64, _u64, c.c_int, _f64, _f64, _f64, _i64, _vp],
     "vk_create_program": [_i64, _u64, c.c_int, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp],
+    "vk_program_resimulate": [_vp, _i32],
     "vk_create_blr": [_i64, _u64, c.c_int, _i32, _i64, _f64, _f64, _vp],
     "vk_create_hmm": [_i64, _u64, c.c_int, _i32, _i32, _i32, _vp, _vp, _i32, _i32, _vp],
     "vk_create_lda": [_i64, _u64, c.c_int, _i32, _i32, _i32, _i32, _f64, _f64, _vp],

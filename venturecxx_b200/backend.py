@@ -21,11 +21,12 @@ SPs of backend/lite/inference_sps.py and inference programs such as
 
 run UNCHANGED: `B200(model).make_engine(seed)` (or `install(engine)` on an existing engine).
 
-Model directives: the particle programs are compiled per model kind (models.py), so `assume` /
-`observe` directives are CHECKED against the program the compiled model stands for (`Model.program`) and the
-observed values are decoded from the observe expressions; a directive that does not belong to the compiled
-program raises VentureException("invalid_argument").  Bulk data can be given through
-`engine.model.b200.observe(...)` (B200TraceSet.observe) instead of one directive per datum.
+Model directives.  `B200()` COMPILES the program from the `assume` / `observe` directives the engine evaluates
+(compiler.py: any fixed-structure program over the scalar SPs; CompilingB200Trace).  `B200(model)` with a
+hand-described model of models.py (the kernels written for C1-C5) CHECKS the directives against the program
+that model stands for (`Model.program`) and decodes the observed values from the observe expressions; a
+directive that does not belong to it raises VentureException("invalid_argument"), and bulk data can be given
+through `engine.model.b200.observe(...)` (B200TraceSet.observe) instead of one directive per datum.
 
 This module imports the host's `venture` package lazily (only the engine / TraceSet classes); nothing here
 touches the oracle.
@@ -190,7 +191,7 @@ class B200Trace(object):
 
     def __init__(self, model, seed, device=0, precision="fp64", trace_set=None):
         self.model = model
-        self.ts = trace_set if trace_set is not None else B200TraceSet(model, 1, seed=seed, device=device, precision=precision)
+        self._ts = trace_set if trace_set is not None else B200TraceSet(model, 1, seed=seed, device=device, precision=precision)
         self.decoder = decoder_for(model)
         self._exps = {}            # did -> expression handed to eval
         self._kind = {}            # did -> ("define", index) | ("observe",) | ("evaluate",)
@@ -198,8 +199,25 @@ class B200Trace(object):
         self._profiling = False
 
     @property
+    def ts(self):
+        return self._ts
+
+    @property
     def n_particles(self):
         return self.ts.n_particles
+
+    # -- what the TraceSet needs besides the per-trace surface ------------------------------------------
+    def get_log_weights(self):
+        return self.ts.log_weights.tolist()
+
+    def set_log_weights(self, values):
+        values = list(values)
+        if len(values) != self.n_particles:
+            raise VentureException("invalid_argument", "%d log weights for %d particles" % (len(values), self.n_particles))
+        self.ts.set_particle_log_weights(np.asarray(values, dtype=np.float64))
+
+    def resample(self, P, mode):
+        self.ts.resample(int(P), mode=mode)
 
     # -- model building (engine/trace.py:53-126 calls these) --------------------------------------------
     def eval(self, did, exp):
@@ -363,6 +381,179 @@ class B200Trace(object):
         raise AttributeError(name)
 
 
+class CompilingB200Trace(B200Trace):
+    """B200Trace without a hand-described model: the `assume` / `observe` directives the engine evaluates are
+    RECORDED and compiled (compiler.py) when the particle set is first needed; directives that
+    arrive later extend the program -- the existing sites keep their values, new sites are simulated from their
+    priors given them (vk_program_resimulate), and new observations contribute their log density to the weights
+    exactly as Trace.makeConsistent does for a leaf observation (lite/trace.py:422-448)."""
+
+    def __init__(self, seed, device=0, precision="fp64"):
+        self.model = None
+        self._seed, self._device, self._precision = int(seed), int(device), precision
+        self._ts, self._dirty = None, False
+        self.source = []                      # ("assume", name, exp) | ("observe", exp, value), in directive order
+        self._pending_incr = None
+        self._exps, self._kind, self._bound = {}, {}, {}
+        self._define_site = {}                # did -> site index, for assumes whose root is a random application
+        self._profiling = False
+        self.decoder = None
+        self._n_initial, self._initial_lw = 1, None
+
+    @property
+    def ts(self):
+        self._materialize()
+        return self._ts
+
+    @property
+    def n_particles(self):
+        return self._ts.n_particles if self._ts is not None else self._n_initial
+
+    def ready(self):
+        """a particle set exists once the program has a random choice"""
+        return self._ts is not None or bool(getattr(self, "_names", None))
+
+    def get_log_weights(self):
+        if not self.ready():
+            return list(self._initial_lw) if self._initial_lw is not None else [0.0] * self._n_initial
+        return B200Trace.get_log_weights(self)
+
+    def set_log_weights(self, values):
+        if not self.ready():
+            values = list(values)
+            if len(values) != self._n_initial:
+                raise VentureException("invalid_argument", "%d log weights for %d particles" % (len(values), self._n_initial))
+            self._initial_lw = [float(v) for v in values]
+            return
+        B200Trace.set_log_weights(self, values)
+
+    def resample(self, P, mode):
+        if not self.ready():                   # nothing random yet: P identical empty traces
+            lw = self.get_log_weights()
+            m = max(lw)
+            lse = m if m == float("-inf") else m + float(np.log(np.sum(np.exp(np.asarray(lw) - m))))
+            self._n_initial = int(P)
+            self._initial_lw = [lse - float(np.log(P))] * int(P)
+            return
+        B200Trace.resample(self, P, mode)
+
+    def _materialize(self):
+        if self._ts is not None and not self._dirty:
+            return
+        from . import _lib
+        from .compiler import CompiledModel
+        model = CompiledModel(self.source)
+        old = self._ts
+        P = old.n_particles if old is not None else self._n_initial
+        new = B200TraceSet(model, P, seed=self._seed, device=self._device, precision=self._precision)
+        if old is None:
+            if self._initial_lw is not None:
+                new.set_particle_log_weights(np.asarray(self._initial_lw))
+            incr = new.incorporate()
+        else:
+            n_old = old.num_sites()
+            step = old.rng_step
+            for j in range(n_old):
+                new.write_site(j, old.read_site(j))
+            new.rng_step = step
+            _lib.call("vk_program_resimulate", new._h, n_old)
+            lw_old = old.log_weights
+            ll_old = old.log_likelihood_at("default", "all")
+            new.incorporate(return_increments=False)
+            incr = new.log_likelihood_at("default", "all") - ll_old
+            incr = np.where(np.isnan(incr), -np.inf, incr)
+            new.set_particle_log_weights(lw_old + incr)
+            old.close()
+        self._ts, self.model, self._dirty = new, model, False
+        self._pending_incr = incr if self._pending_incr is None else self._pending_incr + incr
+
+    # -- directives ------------------------------------------------------------------------------------------
+    def bindInGlobalEnv(self, sym, did):
+        self.source.append(("assume", sym, self._exps[did]))
+        self._check()
+        self._kind[did] = ("define", len(self.source) - 1)
+        self._bound[sym] = did
+        self._dirty = True
+
+    def observe(self, did, val):
+        self.source.append(("observe", self._exps[did], val))
+        self._check()
+        self._kind[did] = ("observe",)
+        self._dirty = True
+
+    def _check(self):
+        """compile errors belong to the directive that causes them (the engine reports them to the user)"""
+        from .compiler import Compiler
+        c = Compiler()
+        try:
+            for d in self.source:
+                if d[0] == "assume":
+                    c.assume(d[1], d[2])
+                else:
+                    c.observe(d[1], d[2])
+        except VentureException:
+            self.source.pop()
+            raise
+        self._names = list(c.site_names)
+
+    def unobserve(self, did):
+        raise _unsupported("forgetting an observation of a compiled program")
+
+    def _values_of(self, did):
+        kind = self._kind.get(did)
+        if kind is None:
+            raise VentureException("invalid_argument", "no directive %r" % (did,))
+        if kind[0] == "define":
+            name = self.source[kind[1]][1]
+            ts = self.ts
+            if name in self.model.site_names:
+                j = self.model.site_names.index(name)
+                c = self.model.compiler
+                boolean = c.nodes[c.sites[j]].op in ("FLIP", "LOG_FLIP", "LOG_ODDS_FLIP")
+                return [interchange.boolean(v != 0.0) if boolean else interchange.number(v) for v in ts.read_site(j)]
+            return [{"type": "string", "value": "<compiled: %s>" % (name,)}] * self.n_particles
+        if kind[0] == "evaluate":
+            from .compiler import _plain
+            e = _plain(self._exps[did])
+            if isinstance(e, str) and e in self._bound:
+                return self._values_of(self._bound[e])
+            if isinstance(e, float):
+                return [interchange.number(e)] * self.n_particles
+            raise _unsupported("predicting %r on a compiled program" % (self._exps[did],))
+        raise _unsupported("reading the value of an observation")
+
+    def makeConsistent(self):
+        if not self.ready():
+            return PerParticle([0.0] * self._n_initial)
+        self._materialize()
+        incr, self._pending_incr = self._pending_incr, None
+        if incr is None:
+            incr = np.zeros(self.n_particles)
+        return PerParticle(np.asarray(incr).tolist())
+
+    def scope_keys(self):
+        return ["default"]
+
+    def set_seed(self, seed):
+        self._seed = int(seed)
+        if self._ts is not None:
+            self._ts.set_seed(int(seed))
+
+    def get_seed(self):
+        return self._ts.get_seed() if self._ts is not None else self._seed
+
+    def numRandomChoices(self):
+        return int(self.ts.num_sites()) if self.ready() else 0
+
+    def reset_to_prior(self):
+        if self.ready():
+            self.ts.reset_to_prior()
+
+    def close(self):
+        if self._ts is not None:
+            self._ts.close()
+
+
 def _infer_arg(v):
     """argument of an inference operator: VentureValue / stack dict / python value -> python value"""
     if hasattr(v, "asStackDict"):
@@ -480,14 +671,11 @@ def trace_set_class():
         def log_weights(self):
             if getattr(self, "traces", None) is None:
                 return []
-            return self.b200.log_weights.tolist()
+            return self.traces.batch.get_log_weights()
 
         @log_weights.setter
         def log_weights(self, values):
-            values = list(values)
-            if len(values) != self.b200.n_particles:
-                raise VentureException("invalid_argument", "%d log weights for %d particles" % (len(values), self.b200.n_particles))
-            self.b200.set_particle_log_weights(np.asarray(values, dtype=np.float64))
+            self.traces.batch.set_log_weights(values)
 
         def likelihood_weight(self):              # :287-288 (the kernel overwrites the device weights itself)
             self.traces.map("likelihood_weight")
@@ -502,7 +690,7 @@ def trace_set_class():
             self.incorporate()
 
         def _resample_traces(self, P):            # :209-219 -> the resampling kernel; weights evened out on the device
-            self.b200.resample(int(P), mode=getattr(self.backend, "resample_mode", "multinomial"))
+            self.traces.batch.resample(int(P), getattr(self.backend, "resample_mode", "multinomial"))
             return None
 
         def copy_trace(self, trace):              # :370-375
@@ -564,10 +752,13 @@ class B200(object):
     model: a compiled model of venturecxx_b200.models; resample_mode: "multinomial" (the reference's law,
     trace_set.py:209-219) or "systematic"."""
 
-    def __init__(self, model, device=0, resample_mode="multinomial", precision="fp64"):
+    def __init__(self, model=None, device=0, resample_mode="multinomial", precision="fp64"):
+        """model=None: the program is COMPILED from the directives the engine evaluates (compiler.py)."""
         self.model, self.device, self.resample_mode, self.precision = model, int(device), resample_mode, precision
 
     def trace_constructor(self):
+        if self.model is None:
+            return lambda seed: CompilingB200Trace(seed, device=self.device, precision=self.precision)
         return lambda seed: B200Trace(self.model, seed, device=self.device, precision=self.precision)
 
     def name(self):
@@ -612,10 +803,9 @@ class B200(object):
 
 
 def backend(name="b200", model=None, **kwargs):
-    """`venture.shortcuts.backend(name)` with the extra name: "b200" needs the compiled `model`."""
+    """`venture.shortcuts.backend(name)` with the extra name "b200" (model: a hand-described model of
+    venturecxx_b200.models, or None to compile the program from its directives)."""
     if name == "b200":
-        if model is None:
-            raise VentureException("invalid_argument", "backend('b200') needs model=<a compiled model of venturecxx_b200.models>")
         return B200(model, **kwargs)
     import venture.shortcuts as s
     return s.backend(name)

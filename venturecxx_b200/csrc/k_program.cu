@@ -141,7 +141,7 @@ __device__ __forceinline__ double vm_log_alpha(double rho, double xi) {      // 
   return xi - rho;
 }
 
-enum { VM_MODE_PRIOR = 0, VM_MODE_LW = 1, VM_MODE_CONSISTENT = 2, VM_MODE_LOGLIK = 3 };
+enum { VM_MODE_PRIOR = 0, VM_MODE_LW = 1, VM_MODE_CONSISTENT = 2, VM_MODE_LOGLIK = 3, VM_MODE_RESIM = 4 };
 
 // mode PRIOR: sites from the prior.  LW: the same, lw := log density of the observations.  CONSISTENT: lw += that,
 // increments out.  LOGLIK: out := xi of the scaffold of `block` (VK_BLOCK_ALL: every observation), + the
@@ -159,6 +159,14 @@ prog_kernel(VMProg pg, double *sites, double *lw, double *out, int64_t P, int64_
       Stream r(seed, (uint64_t)(p_base + p), step);
       vm_exec(pg, pg.sec_prior, R, sites, P, p, nullptr, &r, dummy, lane == 0);
       if (LANES == 32) __syncwarp();
+    }
+    if (mode == VM_MODE_RESIM) {              // sites block.. from their priors GIVEN the current values of the earlier ones
+      Stream r(seed, (uint64_t)(p_base + p), step);
+      for (int k = block; k < pg.n_sites; ++k) {
+        vm_exec(pg, __ldg(&pg.site_tab[5 * k]), R, sites, P, p, nullptr, &r, dummy, lane == 0);
+        if (LANES == 32) __syncwarp();
+      }
+      continue;
     }
     if (mode == VM_MODE_PRIOR) continue;
     double v;
@@ -331,6 +339,10 @@ struct ProgramModel : Model {
     VK_CUDA(cudaGetLastError());
   }
   void reset_to_prior() override { launch(VM_MODE_PRIOR, nullptr, h->next_step()); }
+  void resimulate_from(int first) {
+    VK_REQUIRE(first >= 0 && first <= S, VK_EINVAL, "program: first site out of range");
+    if (first < S) launch(VM_MODE_RESIM, nullptr, h->next_step(), first, 0);
+  }
   void likelihood_weight() override { propagated = true; launch(VM_MODE_LW, nullptr, h->next_step()); }
   void make_consistent(double *incr_dev) override {
     if (propagated) {
@@ -398,5 +410,7 @@ Model *make_program(vk_particles *h, const int32_t *code, int64_t n_code, const 
                     const int32_t *meta, int64_t n_meta, const double *data, int64_t n_data, const double *affected) {
   return new ProgramModel(h, code, n_code, consts, n_consts, meta, n_meta, data, n_data, affected);
 }
+
+void program_resimulate_from(Model *m, int first_site) { static_cast<ProgramModel *>(m)->resimulate_from(first_site); }
 
 }  // namespace vk

@@ -28,5 +28,7 @@ void lda_observe(Model *m, const int32_t *doc_host, const int32_t *word_host, in
 Model *make_program(vk_particles *h, const int32_t *code, int64_t n_code, const double *consts, int64_t n_consts,
                     const int32_t *meta, int64_t n_meta, const double *data, int64_t n_data, const double *affected);
 
+void program_resimulate_from(Model *m, int first_site);
+
 void launch_axpy(vk_particles *h, double *y, const double *x, int64_t n);  // y += x
 }  // namespace vk

@@ -120,6 +120,13 @@ int vk_create_program(int64_t P, uint64_t seed, int device, const int32_t *code,
   VK_CATCH
 }
 
+int vk_program_resimulate(vk_particles *h, int32_t first_site) {
+  VK_TRY check_handle(h); use_device(h);
+  VK_REQUIRE(h->kind == VK_MODEL_PROGRAM, VK_EINVAL, "vk_program_resimulate: not a compiled program");
+  program_resimulate_from(h->model, first_site);
+  VK_CATCH
+}
+
 int vk_create_blr(int64_t P, uint64_t seed, int device, int32_t D, int64_t n_obs_capacity,
                   double prior_mu, double prior_sigma, vk_particles **out) {
   VK_TRY

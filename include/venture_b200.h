@@ -351,7 +351,17 @@ enum vk_sp_id {
   VK_SP_NORMAL = 1, VK_SP_GAMMA = 2, VK_SP_BETA = 3, VK_SP_FLIP = 4,
   VK_SP_LOG_FLIP = 5, VK_SP_LOG_ODDS_FLIP = 6, VK_SP_CATEGORICAL = 7,
   VK_SP_LOG_CATEGORICAL = 8, VK_SP_DIRICHLET = 9, VK_SP_SYM_DIRICHLET = 10,
-  VK_SP_SYM_DIR_CAT = 11, VK_SP_BETA_BERNOULLI = 12
+  VK_SP_SYM_DIR_CAT = 11, VK_SP_BETA_BERNOULLI = 12,
+  /* made SPs of the remaining Dirichlet / Bernoulli makers:
+   * DIR_CAT        make_dir_cat's CDirCatOutputPSP, asymmetric alpha: params alpha[dim], counts[dim]
+   *                (dirichlet.py:116-206)
+   * UC_DIR_CAT     make_uc_dir_cat / make_uc_sym_dir_cat's UDirCatOutputPSP: params theta[dim]
+   *                (dirichlet.py:265-293, 355-415)
+   * SUFF_BERNOULLI make_uc_beta_bernoulli's SuffBernoulliOutputPSP: params weight[, yes, no]
+   *                (discrete.py:513-545)
+   * The MAKERS' own simulate / logDensity are VK_SP_DIRICHLET / VK_SP_SYM_DIRICHLET / VK_SP_BETA
+   * (theta ~ dirichlet(alpha), logDensityDirichlet(theta, alpha); weight ~ beta(a, b)). */
+  VK_SP_DIR_CAT = 13, VK_SP_UC_DIR_CAT = 14, VK_SP_SUFF_BERNOULLI = 15
 };
 int vk_sp_simulate(int32_t sp, const double *params_host, int32_t n_params,
                    int64_t n, int32_t dim, uint64_t seed, uint32_t step,
@@ -359,6 +369,25 @@ int vk_sp_simulate(int32_t sp, const double *params_host, int32_t n_params,
 int vk_sp_log_density(int32_t sp, const double *values_host,
                       const double *params_host, int32_t n_params, int64_t n,
                       int32_t dim, int device, double *out_host);
+
+/* logDensityOfData(aux) of a made SP from its sufficient statistics (psp.py:266-270;
+ * dirichlet.py:192-201 CDirCatOutputPSP, discrete.py:453-459 CBetaBernoulliOutputPSP, :537-541
+ * SuffBernoulliOutputPSP): what DeterministicMakerAAALKernel.weight (lkernel.py:158-171) and
+ * PosteriorAAALKernel.weight = marginalLogDensityOfData (lkernel.py:137-156) evaluate.
+ * params per row: SYM_DIR_CAT alpha, counts[dim]; DIR_CAT alpha[dim], counts[dim];
+ * BETA_BERNOULLI a, b, yes, no; SUFF_BERNOULLI weight, yes, no. */
+int vk_sp_log_density_of_data(int32_t sp, const double *params_host, int32_t n_params,
+                              int64_t n, int32_t dim, int device, double *out_host);
+/* The uncollapsed makers' AAA LKernels (UDirCatAAALKernel dirichlet.py:250-263,
+ * USymDirCatAAALKernel :395-407, UBetaBernoulliAAALKernel discrete.py:502-510): row i draws the
+ * made SP's parameter from its conjugate posterior given the statistics -- theta ~
+ * dirichlet(alpha + counts) (UC_DIR_CAT: params alpha[dim], counts[dim]; SYM_DIRICHLET id for
+ * the symmetric maker: params alpha, counts[dim]) or weight ~ beta(a + yes, b + no)
+ * (SUFF_BERNOULLI: params a, b, yes, no) -- from Philox(seed, i, step), and reports the kernel's
+ * weight, the marginal likelihood of the data (nullable). */
+int vk_sp_aaa_simulate(int32_t sp, const double *params_host, int32_t n_params, int64_t n,
+                       int32_t dim, uint64_t seed, uint32_t step, int device,
+                       double *values_out_host, double *weights_out_host);
 
 #ifdef __cplusplus
 }

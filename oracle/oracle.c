@@ -233,7 +233,8 @@ double orc_draw(int kind, const double *params, int n, uint64_t seed, uint64_t p
 }
 
 enum { SP_NORMAL = 1, SP_GAMMA, SP_BETA, SP_FLIP, SP_LOG_FLIP, SP_LOG_ODDS_FLIP, SP_CATEGORICAL,
-       SP_LOG_CATEGORICAL, SP_DIRICHLET, SP_SYM_DIRICHLET, SP_SYM_DIR_CAT, SP_BETA_BERNOULLI };
+       SP_LOG_CATEGORICAL, SP_DIRICHLET, SP_SYM_DIRICHLET, SP_SYM_DIR_CAT, SP_BETA_BERNOULLI,
+       SP_DIR_CAT, SP_UC_DIR_CAT, SP_SUFF_BERNOULLI };
 
 /* batched PSP.simulate: value i drawn from Philox(seed, particle=i, step) */
 int orc_sp_simulate(int sp, const double *params, int n_params, int64_t n, int dim, uint64_t seed,
@@ -267,6 +268,12 @@ int orc_sp_simulate(int sp, const double *params, int n_params, int64_t n, int d
       case SP_BETA_BERNOULLI: {  /* discrete.py:440-443; params = a, b, yes, no */
         double w = (q[0] + q[2]) / (q[0] + q[2] + q[1] + q[3]);
         out[i] = st_uniform(&r) < w; break; }
+      case SP_DIR_CAT: {  /* dirichlet.py:164-166, asymmetric alpha; params = alpha[dim], counts[dim] */
+        double wts[1024]; if (dim > 1024) return 1;
+        for (int k = 0; k < dim; ++k) wts[k] = q[k] + q[dim + k];
+        out[i] = categorical_sim(&r, wts, dim); break; }
+      case SP_UC_DIR_CAT: out[i] = categorical_sim(&r, q, dim); break;        /* dirichlet.py:271-273; params = theta[dim] */
+      case SP_SUFF_BERNOULLI: out[i] = st_uniform(&r) < q[0]; break;         /* discrete.py:531-532; params = weight */
       default: return 1;
     }
   }
@@ -299,8 +306,58 @@ int orc_sp_log_density(int sp, const double *values, const double *params, int n
       case SP_BETA_BERNOULLI: {  /* discrete.py:445-451 */
         double w = (q[0] + q[2]) / (q[0] + q[2] + q[1] + q[3]);
         out[i] = v != 0 ? log(w) : log1p(-w); break; }
+      case SP_DIR_CAT: {  /* dirichlet.py:168-173 */
+        double tot = 0, A = 0; int idx = (int)v;
+        for (int k = 0; k < dim; ++k) { tot += q[dim + k]; A += q[k]; }
+        out[i] = log((q[dim + idx] + q[idx]) / (tot + A)); break; }
+      case SP_UC_DIR_CAT: out[i] = log(q[(int)v]); break;                    /* dirichlet.py:275-277 */
+      case SP_SUFF_BERNOULLI: out[i] = v != 0 ? log(q[0]) : log1p(-q[0]); break;   /* discrete.py:534-538 */
       default: return 1;
     }
+  }
+  return 0;
+}
+
+/* logDensityOfData(aux) of the made SPs: dirichlet.py:192-201 (CDirCatOutputPSP; the symmetric maker builds the
+ * same PSP with a constant alpha, :303-351), discrete.py:453-459 (CBetaBernoulliOutputPSP), :537-541
+ * (SuffBernoulliOutputPSP).  params per row as in include/venture_b200.h vk_sp_log_density_of_data. */
+static double data_term(int sp, const double *q, int dim) {
+  if (sp == SP_SYM_DIR_CAT || sp == SP_DIR_CAT) {
+    double N = 0, A = 0, t2 = 0;
+    for (int k = 0; k < dim; ++k) {
+      double al = sp == SP_SYM_DIR_CAT ? q[0] : q[k], c = sp == SP_SYM_DIR_CAT ? q[1 + k] : q[dim + k];
+      N += c; A += al; t2 += lgamma(al + c) - lgamma(al);
+    }
+    return lgamma(A) - lgamma(N + A) + t2;
+  }
+  if (sp == SP_BETA_BERNOULLI) return betaln(q[2] + q[0], q[3] + q[1]) - betaln(q[0], q[1]);
+  if (sp == SP_SUFF_BERNOULLI) return (q[1] > 0 ? q[1] * log(q[0]) : 0) + (q[2] > 0 ? q[2] * log1p(-q[0]) : 0);
+  return NAN;
+}
+int orc_sp_log_density_of_data(int sp, const double *params, int n_params, int64_t n, int dim, double *out) {
+  for (int64_t i = 0; i < n; ++i) out[i] = data_term(sp, params + i * n_params, dim);
+  return 0;
+}
+/* the uncollapsed makers' AAA LKernels: UDirCatAAALKernel dirichlet.py:250-263, USymDirCatAAALKernel :395-407,
+ * UBetaBernoulliAAALKernel discrete.py:502-510; weight = marginalLogDensityOfData (lkernel.py:137-156) */
+int orc_sp_aaa_simulate(int sp, const double *params, int n_params, int64_t n, int dim, uint64_t seed, uint32_t step,
+                        double *out, double *wout) {
+  for (int64_t i = 0; i < n; ++i) {
+    const double *q = params + i * n_params;
+    orc_stream r; st_init(&r, seed, (uint64_t)i, step);
+    double post[1024]; if (dim > 1024) return 1;
+    if (sp == SP_UC_DIR_CAT) {
+      for (int k = 0; k < dim; ++k) post[k] = q[dim + k] + q[k];
+      dirichlet_sim(&r, post, dim, out + i * dim);
+      if (wout) wout[i] = data_term(SP_DIR_CAT, q, dim);
+    } else if (sp == SP_SYM_DIRICHLET) {
+      for (int k = 0; k < dim; ++k) post[k] = q[1 + k] + q[0];
+      dirichlet_sim(&r, post, dim, out + i * dim);
+      if (wout) wout[i] = data_term(SP_SYM_DIR_CAT, q, dim);
+    } else if (sp == SP_SUFF_BERNOULLI) {
+      out[i] = beta_sim(&r, q[0] + q[2], q[1] + q[3]);
+      if (wout) wout[i] = data_term(SP_BETA_BERNOULLI, q, dim);
+    } else return 1;
   }
   return 0;
 }

@@ -90,6 +90,8 @@ PROTOTYPES = {
     "vk_ssmh_stats": [_vp, _i32, _vp],
     "vk_sp_simulate": [_i32, _vp, _i32, _i64, _i32, _u64, _u32, c.c_int, _vp],
     "vk_sp_log_density": [_i32, _vp, _vp, _i32, _i64, _i32, c.c_int, _vp],
+    "vk_sp_log_density_of_data": [_i32, _vp, _i32, _i64, _i32, c.c_int, _vp],
+    "vk_sp_aaa_simulate": [_i32, _vp, _i32, _i64, _i32, _u64, _u32, c.c_int, _vp, _vp],
 }
 _RESTYPES = {"vk_last_error": c.c_char_p, "vk_num_particles": _i64}
 

@@ -225,4 +225,15 @@ VK_HD double betabern_log_density_of_data(double a, double b, double yes, double
   return betaln(yes + a, no + b) - betaln(a, b);
 }
 
+// ---- logDensityOfData of the made SPs (dirichlet.py:192-201, discrete.py:453-459, 537-541) -------------
+VK_HD double dircat_log_density_of_data(const double *alpha, int alpha_stride, const double *counts, int n) {
+  double N = 0.0, A = 0.0, term2 = 0.0;
+  for (int i = 0; i < n; ++i) { N += counts[i]; A += alpha[i * alpha_stride]; }
+  for (int i = 0; i < n; ++i) term2 += lgamma(alpha[i * alpha_stride] + counts[i]) - lgamma(alpha[i * alpha_stride]);
+  return lgamma(A) - lgamma(N + A) + term2;
+}
+VK_HD double suff_bernoulli_log_density_of_data(double w, double yes, double no) {
+  return (yes > 0.0 ? yes * log(w) : 0.0) + (no > 0.0 ? no * log1p(-w) : 0.0);
+}
+
 }  // namespace vk

@@ -121,6 +121,97 @@ class CBetaBernoulliOutputPSP(B200PSP):
                                                     np.broadcast_to(b.reshape(-1, 1), (n, 1)), aux], axis=1)), n
 
 
+class CDirCatOutputPSP(B200PSP):
+    """The SP made by make_dir_cat(alphas) (dirichlet.py:116-206); spaux() = counts (rows x n)."""
+    sp_id = 13
+
+    def _params(self, args):
+        alpha = np.atleast_2d(np.asarray(args.operandValues()[0], dtype=np.float64))
+        counts = np.atleast_2d(np.asarray(args.spaux(), dtype=np.float64))
+        n = counts.shape[0]
+        return np.ascontiguousarray(np.concatenate([np.broadcast_to(alpha, (n, counts.shape[1])), counts], axis=1)), n
+
+    def _dim(self, params):
+        return params.shape[1] // 2
+
+    def logDensityOfData(self, args):
+        params, n = self._params(args)
+        out = np.empty(n)
+        _lib.call("vk_sp_log_density_of_data", self.sp_id, _lib.ptr(params), params.shape[1], n, self._dim(params), args.device,
+                  _lib.ptr(out))
+        return out
+
+
+class UDirCatOutputPSP(B200PSP):
+    """The SP made by make_uc_dir_cat / make_uc_sym_dir_cat (dirichlet.py:265-293): operand = theta (rows x n)."""
+    sp_id = 14
+
+    def _params(self, args):
+        theta = np.atleast_2d(np.asarray(args.operandValues()[0], dtype=np.float64))
+        return np.ascontiguousarray(theta), theta.shape[0]
+
+    def _dim(self, params):
+        return params.shape[1]
+
+
+class SuffBernoulliOutputPSP(B200PSP):
+    """The SP made by make_uc_beta_bernoulli / make_suff_stat_bernoulli (discrete.py:513-545): operand = weight."""
+    sp_id = 15
+
+    def logDensityOfData(self, args):
+        """spaux() = (yes, no) rows"""
+        w = np.asarray(args.operandValues()[0], dtype=np.float64).reshape(-1, 1)
+        aux = np.atleast_2d(np.asarray(args.spaux(), dtype=np.float64))
+        n = aux.shape[0]
+        params = np.ascontiguousarray(np.concatenate([np.broadcast_to(w, (n, 1)), aux], axis=1))
+        out = np.empty(n)
+        _lib.call("vk_sp_log_density_of_data", self.sp_id, _lib.ptr(params), 3, n, 1, args.device, _lib.ptr(out))
+        return out
+
+
+def _data_term(sp_id, params, dim, device):
+    params = np.ascontiguousarray(params, dtype=np.float64)
+    out = np.empty(params.shape[0])
+    _lib.call("vk_sp_log_density_of_data", sp_id, _lib.ptr(params), params.shape[1], params.shape[0], dim, device, _lib.ptr(out))
+    return out
+
+
+class AAALKernel(object):
+    """The AAA LKernels of the uncollapsed makers (lkernel.py:137-156 PosteriorAAALKernel): `simulate` draws the made
+    SP's parameter from its conjugate posterior given the sufficient statistics, `weight` is the marginal
+    likelihood of the data.  kind: "make_uc_dir_cat" (operands alphas; dirichlet.py:250-263), "make_uc_sym_dir_cat"
+    (operands alpha, n; :395-407), "make_uc_beta_bernoulli" (operands a, b; discrete.py:502-510); spaux() = statistics."""
+    KINDS = {"make_uc_dir_cat": 14, "make_uc_sym_dir_cat": 10, "make_uc_beta_bernoulli": 15}
+
+    def __init__(self, kind):
+        if kind not in self.KINDS:
+            raise VentureException("invalid_argument", "%r has no AAA LKernel on the B200 path" % (kind,))
+        self.kind, self.sp_id = kind, self.KINDS[kind]
+
+    def _params(self, args):
+        ops = [np.asarray(o, dtype=np.float64) for o in args.operandValues()]
+        aux = np.atleast_2d(np.asarray(args.spaux(), dtype=np.float64))
+        n = aux.shape[0]
+        if self.kind == "make_uc_dir_cat":
+            return np.concatenate([np.broadcast_to(np.atleast_2d(ops[0]), aux.shape), aux], axis=1), aux.shape[1], n
+        if self.kind == "make_uc_sym_dir_cat":
+            return np.concatenate([np.broadcast_to(ops[0].reshape(-1, 1), (n, 1)), aux], axis=1), aux.shape[1], n
+        return np.concatenate([np.broadcast_to(ops[0].reshape(-1, 1), (n, 1)), np.broadcast_to(ops[1].reshape(-1, 1), (n, 1)), aux], axis=1), 1, n
+
+    def simulate(self, args, return_weight=False):
+        params, dim, n = self._params(args)
+        params = np.ascontiguousarray(params)
+        out = np.empty(n if self.kind == "make_uc_beta_bernoulli" else (n, dim))
+        w = np.empty(n)
+        _lib.call("vk_sp_aaa_simulate", self.sp_id, _lib.ptr(params), params.shape[1], n, dim, args.seed, args.step, args.device,
+                  _lib.ptr(out), _lib.ptr(w))
+        return (out, w) if return_weight else out
+
+    def weight(self, args):
+        params, dim, n = self._params(args)
+        return _data_term({"make_uc_dir_cat": 13, "make_uc_sym_dir_cat": 11, "make_uc_beta_bernoulli": 12}[self.kind], params, dim, args.device)
+
+
 builtins = {
     "normal": NormalOutputPSP, "gamma": GammaOutputPSP, "beta": BetaOutputPSP,
     "flip": BernoulliOutputPSP, "bernoulli": BernoulliOutputPSP, "log_flip": LogBernoulliOutputPSP,
@@ -128,7 +219,9 @@ builtins = {
     "log_odds_bernoulli": LogOddsBernoulliOutputPSP, "categorical": CategoricalOutputPSP,
     "log_categorical": LogCategoricalOutputPSP, "dirichlet": DirichletOutputPSP,
     "symmetric_dirichlet": SymmetricDirichletOutputPSP, "make_sym_dir_cat": CSymDirCatOutputPSP,
-    "make_beta_bernoulli": CBetaBernoulliOutputPSP,
+    "make_beta_bernoulli": CBetaBernoulliOutputPSP, "make_dir_cat": CDirCatOutputPSP,
+    "make_uc_dir_cat": UDirCatOutputPSP, "make_uc_sym_dir_cat": UDirCatOutputPSP,
+    "make_uc_beta_bernoulli": SuffBernoulliOutputPSP, "make_suff_stat_bernoulli": SuffBernoulliOutputPSP,
 }
 
 

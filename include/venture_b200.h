@@ -242,6 +242,14 @@ int vk_p2p_open(vk_particles *h, int32_t world, int32_t rank, const unsigned cha
 int vk_p2p_resample(vk_particles *h, int mode);
 int vk_p2p_status(vk_particles *h, int32_t *timed_out, double *lse_out);
 
+/* Slice sampling with stepping out, `(slice scope block w m transitions)`: infer/dispatch.py:190-194 ->
+ * infer/slice_sample.py:39-139 (StepOutSliceOperator under mixMH; registered at inference_sps.py:500-516).
+ * The site must be continuous and one-dimensional.  Compiled for programs of the model compiler
+ * (vk_create_program); the hand-described model kinds answer VK_EUNSUPPORTED.
+ * mean_nodes_out_host as vk_mh; moved_out_host: NULL or P int64 = transitions that changed the value. */
+int vk_slice(vk_particles *h, int32_t scope, int32_t block, double w, double m, int32_t transitions,
+             double *mean_nodes_out_host, int64_t *moved_out_host);
+
 /* Enumerative Gibbs, `(gibbs scope block transitions)`: infer/dispatch.py:175-179 ->
  * infer/egibbs.py:42-107 (EnumerativeGibbsOperator under mixMH).  For a discrete site every candidate
  * value is weighted by its regen weight, the new value is drawn proportionally and always accepted.

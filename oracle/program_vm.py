@@ -181,3 +181,50 @@ class VM(object):
                     self.sites[k, p] = old
                 nodes[p] += self.affected[k]
         return acc, nodes / max(n_steps, 1)
+
+    def slice(self, n_steps, w, m, block=-1):
+        """StepOutSliceOperator under mixMH (infer/slice_sample.py:39-139): draw 0 block choice, then the uniforms in call
+        order.  Returns per-particle mean node counts."""
+        step0, self.step = self.step, self.step + n_steps
+        nodes = np.zeros(self.P)
+        for p in range(self.P):
+            for t in range(n_steps):
+                tape = self._tape(p, step0 + t, 0)
+                u_sel = tape(0, [0.0])
+                k = min(int(u_sel * self.S), self.S - 1) if block == -1 else (t % self.S if block == -3 else block)
+                R = [0.0] * self.n_regs
+
+                def f(x):
+                    self.sites[k, p] = x
+                    return self.children(k, R, p) + self.run(self.site[k][2], R, p)
+                x0 = float(self.sites[k, p])
+                logy = f(x0) + math.log(tape(0, [0.0]))
+                L = x0 - w * tape(0, [0.0])
+                Rr = L + w
+                J = math.floor(m * tape(0, [0.0]))
+                K = (m - 1) - J
+                while J > 0:
+                    fl = f(L)
+                    if logy >= fl or math.isnan(fl):
+                        break
+                    L, J = L - w, J - 1
+                while K > 0:
+                    fr = f(Rr)
+                    if logy >= fr or math.isnan(fr):
+                        break
+                    Rr, K = Rr + w, K - 1
+                x1 = x0
+                for _ in range(10000):
+                    xc = L + tape(0, [0.0]) * (Rr - L)
+                    if logy <= f(xc):
+                        x1 = xc
+                        break
+                    if xc < x0:
+                        L = xc
+                    else:
+                        Rr = xc
+                if not math.log(tape(0, [0.0])) < 0.0:
+                    x1 = x0
+                self.sites[k, p] = x1
+                nodes[p] += self.affected[k]
+        return nodes / max(n_steps, 1)

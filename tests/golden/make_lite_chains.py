@@ -131,7 +131,22 @@ class PyRng(object):
         raise KeyError(b)
 
     def random(self):                          # mh.py:85
+        if getattr(self.tape, "sequential", False):     # slice_sample.py draws its uniforms in call order
+            return self.tape.draw(0, [0.0])
         return self.tape.at(1)
+
+    def uniform(self, a, b):                   # random.uniform: a + (b - a) * random()
+        return a + (b - a) * self.random()
+
+    # FixedRandomness (utils.py:369-394) saves / restores the generator around evaluations of the slice density
+    def getstate(self):
+        return self.tape.d
+
+    def setstate(self, d):
+        self.tape.d = d
+
+    def jumpahead(self, _n):
+        pass
 
     def randint(self, lo, hi):                 # particle.py:97-99 seeds particle-local RNGs (egibbs); those
         return 12345                           # are never drawn from on these paths (a draw would raise here)
@@ -158,6 +173,15 @@ class NpRng(object):
 
     def random_sample(self):
         return self.tape.draw(0, [0.0])
+
+    def get_state(self):                       # FixedRandomness, utils.py:381-393
+        return self.tape.d
+
+    def set_state(self, d):
+        self.tape.d = d
+
+    def seed(self, _s):
+        pass
 
     def exponential(self, scale=1.0):            # continuous.py:1134 (inverse CDF, as the kernels' expon_sim)
         return -math.log1p(-self.tape.draw(0, [0.0])) * scale

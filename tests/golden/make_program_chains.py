@@ -41,7 +41,13 @@ def programs():
             ("observe", ["log_odds_flip", ["sub", "x1", "x2"]], True),
             ("observe", ["expon", ["exp", "lo"]], 0.8),
             ("observe", ["gamma", ["add", ["abs", "mu"], 1.0], "tau"], 1.7)]
-    return {"regression": regression, "coin": coin, "hierarchy": hier}
+    # real-valued sites only: Lite's slice evaluates the density outside a positive site's support and raises there
+    regression2 = [("assume", "a", ["normal", 0.0, 2.0]), ("assume", "b", ["normal", 0.0, 2.0])] + \
+                  [("observe", ["normal", ["add", ["mul", "a", x], "b"], 0.7], y) for x, y in zip(xs, ys)]
+    chain = [("assume", "mu", ["normal", 1.0, 3.0]), ("assume", "x1", ["normal", "mu", 1.5]), ("assume", "x2", ["normal", "mu", 1.5]),
+             ("observe", ["normal", "x1", 0.5], 2.1), ("observe", ["normal", "x2", 0.5], 0.3),
+             ("observe", ["log_odds_flip", ["sub", "x1", "x2"]], True)]
+    return {"regression": regression, "coin": coin, "hierarchy": hier, "regression2": regression2, "chain": chain}
 
 
 def box(v):
@@ -80,12 +86,42 @@ def run(name, prog, seed, P, K, n_first):
     return out
 
 
+def run_slice(prog, seed, P, K, w, m):
+    """(slice default one w m 1) K times: draw 0 = block choice, then slice_sample.py's uniforms in call order"""
+    from make_lite_chains import infer_exp
+    out = {"seed": seed, "P": P, "K": K, "w": w, "m": m, "program": [list(d) for d in prog], "steps": {"slice": 50}, "particles": []}
+    assumes = [d for d in prog if d[0] == "assume"]
+    observes = [d for d in prog if d[0] == "observe"]
+    for p in range(P):
+        mdl = Model()
+        dids = [mdl.assume(d[1], d[2]) for d in assumes]
+        for d in observes:
+            mdl.observe(d[1], box(d[2]))
+        mdl.t.makeConsistent()
+        install(mdl, seed, p)
+        random_dids = [did for did, d in zip(dids, assumes) if mdl.t.families[did] in mdl.t.rcs]
+        nodes = [mdl.t.families[did] for did in random_dids]
+        mdl.tape.site_of = lambda key: [i for i, n in enumerate(nodes) if n is key][0]
+        rec = {"values_start": [fl(mdl.value(did)) for did in random_dids], "nodes": []}
+        mdl.tape.sequential = True
+        for k in range(K):
+            mdl.tape.begin(50 + k, 1)
+            rec["nodes"].append(mdl.t.primitive_infer(infer_exp("slice", "default", "one", w, m, 1)))
+        mdl.tape.sequential = False
+        rec["values_slice"] = [fl(mdl.value(did)) for did in random_dids]
+        rec["lj_at"] = fl(mdl.t.log_joint_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
+        out["particles"].append(rec)
+    return out
+
+
 def main():
     fixture = {}
     progs = programs()
     fixture["regression"] = run("regression", progs["regression"], 23, 5, 40, 4)
     fixture["coin"] = run("coin", progs["coin"], 29, 5, 30, 6)
     fixture["hierarchy"] = run("hierarchy", progs["hierarchy"], 31, 5, 60, 3)
+    fixture["regression_slice"] = run_slice(progs["regression2"], 37, 4, 30, 0.7, 8)
+    fixture["chain_slice"] = run_slice(progs["chain"], 41, 4, 40, 1.3, 5)
     fixture["_source"] = ("reference Lite backend (py3 rendering by oracle/lite_py3/build_lite_py3.py) run by "
                           "tests/golden/make_program_chains.py; numpy %s" % np.__version__)
     path = os.path.join(HERE, "program_chains.json")

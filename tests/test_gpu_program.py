@@ -58,6 +58,45 @@ def test_compiled_program_reproduces_lite_on_the_device(name):
     np.testing.assert_allclose(ts2.log_joint_at("default", "all"), [unj(r["lj_at"]) for r in recs], rtol=RTOL)
 
 
+@pytest.mark.parametrize("name", ["regression_slice", "chain_slice"])
+def test_compiled_slice_reproduces_lite_on_the_device(name):
+    """N4 (slice): `(slice default one w m K)` on the device against Lite's StepOutSliceOperator run on the same
+    uniforms (infer/slice_sample.py:39-139; fixture by tests/golden/make_program_chains.py)"""
+    case = golden("program_chains.json")[name]
+    recs = case["particles"]
+    ts = vb.B200TraceSet(CompiledModel([tuple(d) for d in case["program"]]), case["P"], seed=case["seed"])
+    ts.incorporate()
+    start = np.array([[unj(v) for v in r["values_start"]] for r in recs]).T
+    for j in range(ts.num_sites()):
+        ts.write_site(j, start[j])
+    ts.rng_step = case["steps"]["slice"]
+    nodes, moved = ts.slice("default", "one", case["w"], case["m"], case["K"], return_moves=True)
+    np.testing.assert_allclose(sites_of(ts).T, [[unj(v) for v in r["values_slice"]] for r in recs], rtol=1e-11)
+    np.testing.assert_allclose(nodes, [np.mean(r["nodes"]) for r in recs], rtol=1e-14)
+    np.testing.assert_allclose(ts.log_joint_at("default", "all"), [unj(r["lj_at"]) for r in recs], rtol=1e-11)
+    assert moved.min() > 0 and ts.rng_step == case["steps"]["slice"] + case["K"]
+    # through primitive_infer, as the engine hands it down (dispatch.py:190-194)
+    out = ts.primitive_infer(["slice", "default", "each", case["w"], case["m"], 2])
+    assert out.shape == (case["P"],)
+    hand = vb.B200TraceSet(vb.NormalNormalModel(), 4)
+    with pytest.raises(vb.VentureException):
+        hand.primitive_infer(["slice", "default", "one", 1.0, 5, 1])
+
+
+def test_slice_posterior_of_a_normal_mean():
+    """slice sampling leaves the posterior invariant: prior N(10, 1), observation 14 with noise 1 => N(12, sqrt(1/2))
+    (test/inference_quality/micro/test_basic_stats.py:65-76 runs the same model under every operator)"""
+    from stats_policy import report_known_gaussian, statistical_test
+
+    @statistical_test
+    def run(seed):
+        ts = vb.B200TraceSet(CompiledModel([("assume", "x", ["normal", 10.0, 1.0]), ("observe", ["normal", "x", 1.0], 14.0)]), 5000, seed=seed)
+        ts.incorporate()
+        ts.slice("default", "one", 1.0, 20, 30)
+        return report_known_gaussian(12.0, np.sqrt(0.5), ts.read_site(0))
+    run()
+
+
 def test_compiled_normal_normal_equals_the_hand_written_kernels():
     mu0, s0, s, ys = 0.5, 2.0, 1.5, [2.0, 1.0, -0.5]
     P = 3001

@@ -58,6 +58,7 @@ PROTOTYPES = {
     "vk_resample": [_vp, _i64, c.c_int, _vp, _vp],
     "vk_mh": [_vp, _i32, _i32, _i32, _vp, _vp],
     "vk_gibbs": [_vp, _i32, _i32, _i32, _vp, _vp],
+    "vk_slice": [_vp, _i32, _i32, _f64, _f64, _i32, _vp, _vp],
     "vk_p2p_export": [_vp, _vp, _i32, _vp],
     "vk_p2p_open": [_vp, _i32, _i32, _vp, _i32],
     "vk_p2p_resample": [_vp, _i32],

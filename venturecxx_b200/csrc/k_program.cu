@@ -226,6 +226,79 @@ prog_mh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t see
   }
 }
 
+// `(slice scope block w m transitions)`: StepOutSliceOperator under mixMH (infer/slice_sample.py:39-139, dispatch.py:190-194).
+// f(x) = the regen weight of the scaffold with the site forced to x (DeterministicLKernel): the site's own log density
+// + everything absorbing at its border (slice_sample.py:26-37).  Draw layout of a transition: draw 0 block choice, then
+// in call order: the slice height (py_rng.uniform(0,1), :72), the interval position U and the step split V (:98-103),
+// one uniform per shrink step (:49-58), the accept uniform of mixMH (mh.py:85; logAlpha is 0, :85-90).
+template <int LANES>
+__global__ void __launch_bounds__(256)
+prog_slice_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps,
+                  int block_mode, double w, double m, double *nodes_out, long long *moved_out) {
+  double R[VM_MAX_REGS];
+  const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
+  const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
+  const int S = pg.n_sites;
+  for (int64_t p = unit; p < P; p += n_units) {
+    long long moved = 0;
+    double nodes = 0.0;
+    for (int t = 0; t < n_steps; ++t) {
+      Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)t);
+      const double u_sel = r.uniform();
+      int k;
+      if (block_mode == VK_BLOCK_ONE) { k = (int)(u_sel * (double)S); if (k >= S) k = S - 1; }
+      else if (block_mode == VK_BLOCK_EACH) k = t % S;
+      else k = block_mode;
+      double *cell = sites + (int64_t)k * P + p;
+      const int sec_own = __ldg(&pg.site_tab[5 * k + 2]);
+      auto f = [&](double x) -> double {
+        if (LANES == 32) __syncwarp();
+        if (lane == 0) *cell = x;
+        if (LANES == 32) __syncwarp();
+        double v = vm_children<LANES>(pg, k, R, sites, P, p, lane);
+        vm_exec(pg, sec_own, R, sites, P, p, nullptr, nullptr, v, false);
+        return v;
+      };
+      const double x0 = *cell;
+      const double f0 = f(x0);
+      const double logy = f0 + log(r.uniform());
+      const double U = r.uniform();
+      double L = x0 - w * U, Rr = L + w;
+      const double V = r.uniform();
+      double J = floor(m * V), K = (m - 1.0) - J;
+      for (int it = 1; J > 0.0 && it < 10000; ++it) {
+        const double fl = f(L);
+        if (logy >= fl || fl != fl) break;
+        L -= w; J -= 1.0;
+      }
+      for (int it = 1; K > 0.0 && it < 10000; ++it) {
+        const double fr = f(Rr);
+        if (logy >= fr || fr != fr) break;
+        Rr += w; K -= 1.0;
+      }
+      double x1 = x0;
+      for (int it = 1; it < 10000; ++it) {
+        const double Us = r.uniform();
+        const double xc = L + Us * (Rr - L);
+        const double fx = f(xc);
+        if (logy <= fx) { x1 = xc; break; }
+        if (xc < x0) L = xc; else Rr = xc;
+      }
+      const double logu = log(r.uniform());
+      if (!(logu < 0.0)) x1 = x0;                          // alpha = 0 (slice_sample.py:85-90): accepted unless u == 1
+      if (LANES == 32) __syncwarp();
+      if (lane == 0) *cell = x1;
+      if (LANES == 32) __syncwarp();
+      if (x1 != x0) ++moved;
+      nodes += __ldg(&pg.affected[k]);
+    }
+    if (lane == 0) {
+      if (moved_out) moved_out[p] = moved;
+      if (nodes_out && block_mode == VK_BLOCK_ONE) nodes_out[p] = n_steps > 0 ? nodes / (double)n_steps : 0.0;
+    }
+  }
+}
+
 __global__ void prog_fill_kernel(double *out, int64_t n, double v) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = v;
 }
@@ -375,6 +448,27 @@ struct ProgramModel : Model {
       } else if (K > 0) v = affected_host[(size_t)block];
       prog_fill_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, v);
     }
+    VK_CUDA(cudaGetLastError());
+  }
+  void fill_nodes(double *mean_nodes_dev, int block, int K) {
+    if (!mean_nodes_dev || block == VK_BLOCK_ONE) return;
+    double v = 0.0;
+    if (K > 0 && block == VK_BLOCK_EACH) {         // scaffolder_loop: the blocks' counts summed, FLOOR-divided by #blocks (dispatch.py:122-128)
+      double sum = 0.0;
+      for (double a : affected_host) sum += a;
+      v = floor(sum / (double)S);
+    } else if (K > 0) v = affected_host[(size_t)block];
+    prog_fill_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, v);
+  }
+  void slice(int scope, int block, double w, double m, int K, double *mean_nodes_dev, long long *moved_dev) override {
+    block = block_of(scope, block, false);
+    VK_REQUIRE(w > 0.0 && m >= 1.0, VK_EINVAL, "slice: w must be positive and m at least 1");
+    VK_REQUIRE(propagated || G == 0, VK_ESTATE, "slice: unpropagated observations; call vk_make_consistent first");
+    const int n_steps = block == VK_BLOCK_EACH ? K * S : K;
+    const uint32_t step0 = h->next_step((uint32_t)n_steps);
+    if (warp_mode()) prog_slice_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, block, w, m, mean_nodes_dev, moved_dev);
+    else prog_slice_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, block, w, m, mean_nodes_dev, moved_dev);
+    fill_nodes(mean_nodes_dev, block, K);
     VK_CUDA(cudaGetLastError());
   }
   void log_likelihood_at(int scope, int block, bool joint, double *out_dev) override {

@@ -228,6 +228,10 @@ class B200TraceSet(object):
             if len(exp) != 4:
                 raise VentureException("invalid_argument", "gibbs takes (scope block transitions)")
             return self.gibbs(exp[1], exp[2], exp[3])
+        if op == "slice":
+            if len(exp) != 6:
+                raise VentureException("invalid_argument", "slice takes (scope block w m transitions)")
+            return self.slice(exp[1], exp[2], exp[3], exp[4], exp[5])
         if op == "subsampled_mh":
             if len(exp) != 10:
                 raise VentureException(
@@ -258,6 +262,15 @@ class B200TraceSet(object):
         ch = self._out(dtype=np.int64) if return_changes else None
         _lib.call("vk_gibbs", self._h, s, b, int(transitions), _lib.ptr(out), _lib.ptr(ch))
         return (out, ch) if return_changes else out
+
+    def slice(self, scope, block, w, m, transitions, return_moves=False):
+        """(slice scope block w m transitions): slice sampling with stepping out on a continuous site
+        (infer/dispatch.py:190-194 -> infer/slice_sample.py:39-139)."""
+        s, b = self._scope_block(scope, block)
+        out = self._out()
+        mv = self._out(dtype=np.int64) if return_moves else None
+        _lib.call("vk_slice", self._h, s, b, float(w), float(m), int(transitions), _lib.ptr(out), _lib.ptr(mv))
+        return (out, mv) if return_moves else out
 
     def subsampled_mh(self, scope, block, Nbatch, k0, epsilon, useDeltaKernels, deltaKernelArgs,
                       updateValues, transitions):

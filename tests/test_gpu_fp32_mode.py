@@ -59,7 +59,9 @@ def test_fp32_log_density_within_tolerance(N, D, P, K, block):
     ll64 = orc_loglik(w, X, y)
     np.testing.assert_allclose(ll32, ll64, rtol=FP32_RTOL)
     assert np.max(np.abs(ll32 - ll64) / np.abs(ll64)) < 2e-6     # what the kernel achieves; tolerance has slack
-    # an fp64 consumer sees the cache rebuilt from the fp64 weights
+    # in fp32 mode every log density is promised to 1e-5; back in fp64 the cache is rebuilt from the fp64 weights
+    np.testing.assert_allclose(ts.log_likelihood_at("default", "all"), ll64, rtol=FP32_RTOL)
+    ts.precision = "fp64"
     np.testing.assert_allclose(ts.log_likelihood_at("default", "all"), ll64, rtol=1e-12)
     per = D if block == "each" else 1
     assert np.all(nodes == (3 + 2 * N) * per)
@@ -99,8 +101,34 @@ def test_fp32_posterior_moments_match_fp64():
     np.testing.assert_allclose(a.std(axis=1), b.std(axis=1), rtol=0.05)
 
 
+def test_fp32_log_weights_within_tolerance():
+    """north_star: log densities AND log weights within 1e-5 in fp32 mode -- likelihood_weight, incorporate
+    (makeConsistent) and log_likelihood_at of the logistic-regression model run their single-precision variant"""
+    N, D, P = 10000, 16, 512
+    X, y = make_data(N, D, seed=3)
+    ts = vb.B200TraceSet(vb.LogisticRegressionModel(D, N), P, seed=53, precision="fp32")
+    w = read_w(ts, D)
+    ts.observe(X[:6000], y[:6000])
+    inc1 = ts.incorporate()
+    np.testing.assert_allclose(inc1, orc_loglik(w, X, y, 0, 6000), rtol=FP32_RTOL)
+    ts.observe(X[6000:], y[6000:])
+    inc2 = ts.incorporate()
+    np.testing.assert_allclose(inc2, orc_loglik(w, X, y, 6000, N), rtol=FP32_RTOL)
+    np.testing.assert_allclose(ts.log_weights, orc_loglik(w, X, y), rtol=FP32_RTOL)
+    assert np.max(np.abs(ts.log_weights - orc_loglik(w, X, y)) / np.abs(orc_loglik(w, X, y))) < 2e-6
+    ts.likelihood_weight()
+    w2 = read_w(ts, D)
+    assert not np.array_equal(w, w2)
+    np.testing.assert_allclose(ts.log_weights, orc_loglik(w2, X, y), rtol=FP32_RTOL)
+    np.testing.assert_allclose(ts.log_likelihood_at("default", "all"), orc_loglik(w2, X, y), rtol=FP32_RTOL)
+    ts.precision = "fp64"                               # the same handle back in parity mode
+    np.testing.assert_allclose(ts.log_likelihood_at("default", "all"), orc_loglik(w2, X, y), rtol=1e-12)
+    ts.likelihood_weight()
+    np.testing.assert_allclose(ts.log_weights, orc_loglik(read_w(ts, D), X, y), rtol=1e-12)
+
+
 def test_fp32_then_resample_and_incorporate_stay_exact():
-    # fp64 consumers after an fp32 call: resample copies a refreshed cache, incorporate adds to a refreshed ll
+    # after fp32 calls: resample carries the state, incorporate is the fp32 variant; back in fp64 everything is exact
     N, D, P = 600, 4, 256
     X, y = make_data(N, D, seed=6)
     ts = vb.B200TraceSet(vb.LogisticRegressionModel(D, N), P, seed=43, precision="fp32")
@@ -111,9 +139,10 @@ def test_fp32_then_resample_and_incorporate_stay_exact():
     w = read_w(ts, D)
     ts.observe(X[400:], y[400:])
     incr = ts.incorporate()
-    np.testing.assert_allclose(incr, orc_loglik(w, X, y, 400, N), rtol=1e-12)
-    np.testing.assert_allclose(ts.log_likelihood_at("default", "all"), orc_loglik(w, X, y), rtol=1e-12)
+    np.testing.assert_allclose(incr, orc_loglik(w, X, y, 400, N), rtol=FP32_RTOL)
+    np.testing.assert_allclose(ts.log_likelihood_at("default", "all"), orc_loglik(w, X, y), rtol=FP32_RTOL)
     ts.precision = "fp64"                              # and the fp64 kernel picks the chain up exactly
+    np.testing.assert_allclose(ts.log_likelihood_at("default", "all"), orc_loglik(w, X, y), rtol=1e-12)
     step0 = ts.rng_step
     ts.resimulation_mh("default", "one", 8)
     w_ref, _, ll_ref = orc_mh(w, X, y, 43, step0, 8, -1)

@@ -50,6 +50,10 @@ __device__ __forceinline__ double blr_log_alpha(double rho, double xi) {
 // feature values of an observation are read from L2 ONCE and used for all PP particles (one particle per
 // pass made the kernel L2-bound: 8 D bytes of L2 traffic per evaluation, 84 GB per call at C2).
 static const int BLR_ALL_PP = 4;
+// F32 (vk_set_precision(VK_FP32), SURVEY 8 preamble "fp32 (throughput) mode"; north_star: log weights within 1e-5):
+// logits and the log-logistic in single precision (MUFU ex2 / lg2), per-thread sums in single precision, the
+// block sum and everything stored (weights, increments, the logit cache as float-rounded doubles) in double.
+template <bool F32>
 __global__ void __launch_bounds__(256)
 blr_all_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restrict__ ll,
                double *__restrict__ lw, double *__restrict__ incr,
@@ -84,6 +88,42 @@ blr_all_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restr
     double acc[BLR_ALL_PP];
 #pragma unroll
     for (int q = 0; q < BLR_ALL_PP; ++q) acc[q] = 0.0;
+    if (F32) {
+      float *wf_sh = reinterpret_cast<float *>(red + 34);      // PP x D single-precision copies of the weights
+      for (int t = threadIdx.x; t < BLR_ALL_PP * D; t += blockDim.x) wf_sh[t] = (float)w_sh[t];
+      __syncthreads();
+      float accf[BLR_ALL_PP];
+#pragma unroll
+      for (int q = 0; q < BLR_ALL_PP; ++q) accf[q] = 0.0f;
+      int n_in_acc = 0;
+      for (int64_t i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+        float e[BLR_ALL_PP];
+#pragma unroll
+        for (int q = 0; q < BLR_ALL_PP; ++q) e[q] = 0.0f;
+        for (int j = 0; j < D; ++j) {
+          const float x = (float)__ldg(&Xs[(int64_t)j * prm.Xld + i]);
+#pragma unroll
+          for (int q = 0; q < BLR_ALL_PP; ++q) e[q] = fmaf(wf_sh[q * D + j], x, e[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < BLR_ALL_PP; ++q) {
+          if (q < np) {
+            eta[(p0 + q) * prm.Ncap + i] = (double)e[q];
+            // log_logistic(v) = min(v, 0) - log(1 + exp(-|v|))   (utils.py:257-268), MUFU ex2 / lg2
+            const float a = fabsf(e[q]);
+            const float t = __expf(-a);
+            accf[q] += fminf(e[q], 0.0f) - __logf(1.0f + t);
+          }
+        }
+        if (++n_in_acc == 64) {                 // bound the length of a single-precision running sum
+#pragma unroll
+          for (int q = 0; q < BLR_ALL_PP; ++q) { acc[q] += (double)accf[q]; accf[q] = 0.0f; }
+          n_in_acc = 0;
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < BLR_ALL_PP; ++q) acc[q] += (double)accf[q];
+    } else
     for (int64_t i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
       double e[BLR_ALL_PP];
 #pragma unroll
@@ -503,11 +543,17 @@ struct BLRModel : Model {
     int64_t cap = (int64_t)h->sm_count * ctas_per_sm;
     return (int)(h->P < cap ? h->P : cap);
   }
-  void launch_all(int mode, double *incr_dev, uint32_t step) {
-    size_t sm = (size_t)(BLR_ALL_PP * prm.D + 34) * sizeof(double);
+  void launch_all(int mode, double *incr_dev, uint32_t step, bool allow_f32 = true) {
+    const bool f32 = allow_f32 && precision == VK_FP32;
+    size_t sm = (size_t)(BLR_ALL_PP * prm.D + 34) * sizeof(double) + (f32 ? (size_t)BLR_ALL_PP * prm.D * sizeof(float) : 0);
     int64_t groups = (h->P + BLR_ALL_PP - 1) / BLR_ALL_PP, cap = (int64_t)h->sm_count * 8;
-    blr_all_kernel<<<(int)(groups < cap ? groups : cap), 256, sm, h->stream>>>(w, eta, ll, h->lw.p, incr_dev, Xs.p, prm,
-                                                              n_prop, h->P, h->p_base, h->seed, step, mode);
+    const int grid = (int)(groups < cap ? groups : cap);
+    if (f32) {
+      blr_all_kernel<true><<<grid, 256, sm, h->stream>>>(w, eta, ll, h->lw.p, incr_dev, Xs.p, prm, n_prop, h->P, h->p_base, h->seed, step, mode);
+      eta_lowprec = true;          // the cache holds float-rounded logits: an fp64 consumer recomputes it first
+    } else {
+      blr_all_kernel<false><<<grid, 256, sm, h->stream>>>(w, eta, ll, h->lw.p, incr_dev, Xs.p, prm, n_prop, h->P, h->p_base, h->seed, step, mode);
+    }
     VK_CUDA(cudaGetLastError());
   }
   void reset_to_prior() override { launch_all(0, nullptr, h->next_step()); }
@@ -515,10 +561,16 @@ struct BLRModel : Model {
     n_prop = prm.N;
     launch_all(1, nullptr, h->next_step());
   }
-  void refresh() override { launch_all(2, nullptr, 0); eta_dirty = false; eta_lowprec = false; }
+  // recompute the logit cache and ll from the weights -- in DOUBLE unless the caller is the fp32 mode itself
+  void refresh() override { refresh_in(false); }
+  void refresh_in(bool f32) { eta_lowprec = false; launch_all(2, nullptr, 0, f32); eta_dirty = false; }
   // subsampled transitions leave the logit cache stale (subsampled_mh.py:59-73);
   // this is SubsampledInPlaceOperator.makeConsistent (:427-455) done lazily.
-  void ensure_fresh() { if (eta_dirty || eta_lowprec) refresh(); }
+  // fp64 consumers need an fp64 cache; in fp32 mode a float-rounded cache is what the mode promises (1e-5)
+  void ensure_fresh() {
+    if (precision == VK_FP32) { if (eta_dirty) refresh_in(true); }
+    else if (eta_dirty || eta_lowprec) refresh_in(false);
+  }
   void set_observation_shard(int64_t lo, int64_t total) {
     VK_REQUIRE(lo >= 0 && total >= lo, VK_EINVAL, "blr: bad observation shard");
     obs_lo = lo; N_total = total;
@@ -783,7 +835,8 @@ struct BLRModel : Model {
                    (block >= 0 && block < prm.D), VK_EINVAL, "blr: bad block");
     VK_REQUIRE(n_prop == prm.N, VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
     const bool f32 = precision == VK_FP32 && block != VK_BLOCK_ALL && K > 0 && f32_fits();
-    if (f32) { if (eta_dirty) refresh(); } else ensure_fresh();
+    // the fp32 loop converts the cache itself; every other kernel of this entry point is double and wants a double cache
+    if (f32) { if (eta_dirty) refresh(); } else if (eta_dirty || eta_lowprec) refresh_in(false);
     double nodes = 0.0;
     if (K > 0) {
       if (block == VK_BLOCK_ALL) {

@@ -270,8 +270,8 @@ def main():
     ap.add_argument("--dim", type=int, default=16)
     ap.add_argument("--transitions", type=int, default=160)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-configs", action="store_true", help="skip the secondary configs (c1, c3, c4, c5)")
-    ap.add_argument("--configs", default="c1,c3,c4,c5")
+    ap.add_argument("--no-configs", action="store_true", help="skip the secondary configs (c1, c3, c4, c5, c6)")
+    ap.add_argument("--configs", default="c1,c3,c4,c5,c6")
     ap.add_argument("--configs-timeout", type=int, default=420, help="seconds before the secondary configs are abandoned")
     args = ap.parse_args()
     D, N, T, P = args.dim, args.obs, args.transitions, args.particles

@@ -425,7 +425,92 @@ def c5(ctx, N=10 ** 7, P=64, K=100, Nbatch=65536, k0=3, eps=0.01, cpu=False, che
     return out
 
 
-ALL = {"c1": c1, "c3": c3, "c4": c4, "c5": c5}
+# ---------------------------------------------------------------------------------------------- C6 (compiled program)
+def c6_program(n_obs=1000):
+    rng = np.random.default_rng(8)
+    xs = rng.normal(size=n_obs)
+    ys = 1.5 * xs - 0.7 + 0.4 * rng.normal(size=n_obs)
+    return [("assume", "a", ["normal", 0.0, 2.0]), ("assume", "b", ["normal", 0.0, 2.0]), ("assume", "s", ["gamma", 2.0, 2.0])] + \
+           [("observe", ["normal", ["add", ["mul", "a", float(x)], "b"], "s"], float(y)) for x, y in zip(xs, ys)]
+
+
+def c6_cpu_baseline(prog, transitions=6):
+    """THE REFERENCE'S LITE BACKEND on the same program (oracle/_ref, the py3 rendering): one trace, K transitions of
+    (resimulation_mh default one 1) through Trace.primitive_infer -- Lite is single-threaded per trace."""
+    ref = os.path.join(ROOT, "oracle", "_ref")
+    if not os.path.isdir(os.path.join(ref, "venture", "lite")):
+        return None
+    import warnings
+    warnings.simplefilter("ignore")
+    if ref not in sys.path:
+        sys.path.insert(0, ref)
+    import venture.lite.value as vv
+    import venture.value.dicts as vd
+    from venture.lite.trace import Trace
+    t = Trace(1)
+    did = 0
+
+    def sx(e):
+        if isinstance(e, str):
+            return vd.symbol(e)
+        if isinstance(e, (int, float)):
+            return vd.number(e)
+        return [sx(x) for x in e]
+    for d in prog:
+        did += 1
+        if d[0] == "assume":
+            t.eval(did, sx(d[2])); t.bindInGlobalEnv(d[1], did)
+        else:
+            t.eval(did, sx(d[1])); t.observe(did, vd.number(d[2]))
+    t.makeConsistent()
+    exp = ["resimulation_mh", vv.VentureSymbol("default"), vv.VentureSymbol("one"), vv.VentureNumber(1)]
+    t.primitive_infer(exp)
+    t0 = time.perf_counter()
+    for _ in range(transitions):
+        t.primitive_infer(exp)
+    dt = time.perf_counter() - t0
+    return {"value": transitions / dt, "unit": "transitions/s", "cores": 1, "kind": "reference",
+            "sample": "one Lite trace of the same program, %d transitions of (resimulation_mh default one 1) through "
+                      "Trace.primitive_infer (reference Lite backend, py3 rendering), %.1f s" % (transitions, dt)}
+
+
+def c6(ctx, P=65536, n_obs=1000, K=30, cpu=False):
+    """A program nobody wrote a kernel for, through the model compiler (compiler.py -> k_program.cu): Bayesian linear
+    regression with unknown noise, 1000 observations, (resimulation_mh default one K)."""
+    import venturecxx_b200 as vb
+    from venturecxx_b200.compiler import CompiledModel
+    prog = c6_program(n_obs)
+    t0 = time.perf_counter()
+    model = CompiledModel(prog)
+    t_compile = time.perf_counter() - t0
+    ts = vb.B200TraceSet(model, P, seed=12, device=ctx.local, particle_base=ctx.rank * P)
+    ts.use_stream(ctx.stream.cuda_stream)
+    ts.incorporate(return_increments=False)
+    from venturecxx_b200 import _lib
+    run = lambda k: _lib.call("vk_mh", ts._h, 0, _lib.BLOCK_ONE, int(k), None, None)
+    run(3)
+    ts.synchronize()
+    ms = ctx.timed(lambda: run(K), ts.synchronize)
+    a = ts.read_site(0)
+    ts.close()
+    dt = ms * 1e-3
+    tr = P * ctx.world * K / dt
+    # a site's scaffold: a and b absorb at all n_obs observations, s as well: every transition evaluates them twice (rho, xi)
+    evals = tr * 2 * n_obs
+    out = {"workload": "compiled program (model compiler, no hand-written kernel): linear regression a, b ~ normal, s ~ gamma, "
+                       "%d observations normal(a x_i + b, s), %d particles per GPU, (resimulation_mh default one %d)" % (n_obs, P, K),
+           "metric": "particle-site MH transitions/sec", "value": tr, "unit": "transitions/s", "n_gpus": ctx.world, "scaling": "weak",
+           "ms_per_step": ms, "obs_loglik_evals_per_sec": evals, "compile_seconds": t_compile, "posterior_mean_a": float(a.mean()),
+           "gpu_launches_per_step": 1,
+           "roofline": roofline(P * ctx.world * K * (2 * n_obs * 16.0 + 3 * 8.0), dt, ctx.world,
+                                "algorithmic bytes: per transition the group table (x_i, y_i: 16 B per observation, twice) + the sites; "
+                                "the table is shared by all particles (L2), the path is bound by instruction issue of the interpreter")}
+    if cpu and ctx.rank == 0:
+        out["cpu_baseline"] = c6_cpu_baseline(prog)
+    return out
+
+
+ALL = {"c1": c1, "c3": c3, "c4": c4, "c5": c5, "c6": c6}
 
 
 def main():
@@ -442,7 +527,7 @@ def main():
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
     ctx = Ctx(world, rank, local, stream)
-    for w in (args or ["c1", "c3", "c4", "c5"]):
+    for w in (args or ["c1", "c3", "c4", "c5", "c6"]):
         kw = {"cpu": "--cpu" in sys.argv}
         if quick and w == "c5":
             kw.update(N=10 ** 6, K=20)

@@ -433,17 +433,20 @@ __device__ __forceinline__ uint64_t systematic_U0(const double *uniforms, uint64
 }
 
 // pass A': per-tile totals of the fixed-point weights AND of exp(lw - m) (for the LSE)
+// ITEMS particles per thread: 8 for large sets; the peer-memory path uses 2 for small per-GPU sets (four times the
+// CTAs, a quarter of the serial work per thread -- integer sums, so the CDF does not depend on the tiling)
+template <int ITEMS = SCAN_ITEMS>
 __device__ __forceinline__ void
 fixed_tile_sums_exp_body(const double *__restrict__ lw, int64_t n, const double *__restrict__ red,
                          double scale, uint64_t *tile_sums, double *tile_exp) {
   __shared__ uint64_t sh[32];
   __shared__ double shd[33];
   const double m = red[0];
-  int64_t base = (int64_t)blockIdx.x * SCAN_TILE;
+  int64_t base = (int64_t)blockIdx.x * (SCAN_THREADS * ITEMS);
   uint64_t s = 0;
   double se = 0.0;
 #pragma unroll
-  for (int j = 0; j < SCAN_ITEMS; ++j) {
+  for (int j = 0; j < ITEMS; ++j) {
     int64_t i = base + (int64_t)j * SCAN_THREADS + threadIdx.x;
     if (i < n) {
       double v = lw[i];

@@ -78,11 +78,12 @@ static const int P2P_FIXED_HANDLES = 4;          // mailbox, ancestor array, ss 
 // Tile totals against the GLOBAL max (fixed_tile_sums_exp_kernel's work); the last block then scans the tile
 // totals, forms this rank's sum exp (scan_tile_sums_lse_body) and runs exchange 1 -- one launch, no single-CTA
 // kernel of its own.
+template <int ITEMS>
 __global__ void __launch_bounds__(SCAN_THREADS)
 p2p_tile_sums_kernel(const double *__restrict__ lw, int64_t n, double *__restrict__ red, double scale,
                      uint64_t *tile_sums, double *tile_exp, int n_tiles, unsigned int *counter, P2PXchg xchg) {
   if (((volatile P2PParams *)xchg.par)->err) return;
-  fixed_tile_sums_exp_body(lw, n, red, scale, tile_sums, tile_exp);
+  fixed_tile_sums_exp_body<ITEMS>(lw, n, red, scale, tile_sums, tile_exp);
   __shared__ bool last;
   __threadfence();
   __syncthreads();
@@ -99,6 +100,7 @@ p2p_tile_sums_kernel(const double *__restrict__ lw, int64_t n, double *__restric
 // Step C, systematic: as systematic_offspring_kernel, against the GLOBAL mass: this rank's running sum starts at
 // par->offset, thresholds are those of n_total children over par->total, and child k's ancestor goes to the rank
 // that owns slot k (k / P_local) as a GLOBAL particle index.
+template <int ITEMS>
 __global__ void __launch_bounds__(SCAN_THREADS)
 p2p_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__restrict__ red, double scale,
                      const uint64_t *__restrict__ tile_sums, const P2PParams *__restrict__ par,
@@ -109,11 +111,11 @@ p2p_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__r
   const double m = red[0];
   const uint64_t W = par->total;
   const uint64_t U0 = systematic_U0(nullptr, seed, step);
-  int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
-  uint64_t q[SCAN_ITEMS];
+  int64_t base = (int64_t)blockIdx.x * (SCAN_THREADS * ITEMS) + (int64_t)threadIdx.x * ITEMS;
+  uint64_t q[ITEMS];
   uint64_t s = 0;
 #pragma unroll
-  for (int j = 0; j < SCAN_ITEMS; ++j) {
+  for (int j = 0; j < ITEMS; ++j) {
     int64_t i = base + j;
     q[j] = i < n ? fixed_weight(lw[i], m, scale) : 0ull;
     s += q[j];
@@ -134,7 +136,7 @@ p2p_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__r
   int64_t k_lo = first_child_at_least(run, W, n_total, U0, ratio, u0f);
   const int64_t half_off = (int64_t)anc_half * n;
 #pragma unroll
-  for (int j = 0; j < SCAN_ITEMS; ++j) {
+  for (int j = 0; j < ITEMS; ++j) {
     if (q[j] == 0) continue;
     run += q[j];
     int64_t k_hi = first_child_at_least(run, W, n_total, U0, ratio, u0f);
@@ -402,7 +404,12 @@ void p2p_resample(vk_particles *h, int mode) {
   const int half = (int)(++s->n_resamples & 1ull);
   const int S = frac_bits_for(P_total);
   const double scale = ldexp(1.0, S);
-  const int n_tiles = (int)((P + SCAN_TILE - 1) / SCAN_TILE);
+  // small per-GPU sets: 2 particles per thread instead of 8 (each kernel of the step is a single wave whose latency
+  // is the serial work of one thread); the multinomial path shares fixed_cdf_kernel's tiling and keeps 8
+  static const int items_env = getenv("VK_P2P_ITEMS") ? atoi(getenv("VK_P2P_ITEMS")) : 0;
+  const bool small_tiles = mode == VK_RESAMPLE_SYSTEMATIC && (items_env ? items_env == 2 : P <= ((int64_t)1 << 18));
+  const int tile = SCAN_THREADS * (small_tiles ? 2 : SCAN_ITEMS);
+  const int n_tiles = (int)((P + tile - 1) / tile);
   if (h->red_u.n < (size_t)n_tiles + 1) h->red_u.alloc((size_t)n_tiles + 1);
   if (h->tile_exp.n < (size_t)n_tiles) h->tile_exp.alloc((size_t)n_tiles);
   P2PXchg x;
@@ -415,12 +422,20 @@ void p2p_resample(vk_particles *h, int mode) {
   h->lw_minmax_fresh = false; h->lw_x0_done = false;
   p2p_begin_exchange(h, 1, &x);
   x.my_cur_idx = cur_idx;
-  p2p_tile_sums_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p, n_tiles,
-                                                         h->counters.p + 2, x);
+  if (small_tiles)
+    p2p_tile_sums_kernel<2><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p, n_tiles,
+                                                              h->counters.p + 2, x);
+  else
+    p2p_tile_sums_kernel<SCAN_ITEMS><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p,
+                                                                       n_tiles, h->counters.p + 2, x);
   h->prof.mark(st, "p2p_tile_sums+xchg1");
   if (mode == VK_RESAMPLE_SYSTEMATIC) {
-    p2p_offspring_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, s->par.p, s->tab.p,
-                                                           half, P_total, h->p_base, h->seed, step);
+    if (small_tiles)
+      p2p_offspring_kernel<2><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, s->par.p, s->tab.p,
+                                                                half, P_total, h->p_base, h->seed, step);
+    else
+      p2p_offspring_kernel<SCAN_ITEMS><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, s->par.p,
+                                                                         s->tab.p, half, P_total, h->p_base, h->seed, step);
   } else {
     fixed_cdf_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, 0.0, h->red.p, scale, h->red_u.p, h->cdf.p);
     p2p_multinomial_kernel<<<grid_for(P_total, 256, h->sm_count, 8), 256, 0, st>>>(h->cdf.p, P, s->par.p, s->tab.p, half,

@@ -97,7 +97,7 @@ int vk_create_normal_normal(int64_t n_particles, uint64_t seed, int device,
  * straight-line code of a register machine interpreted by ONE pair of kernels
  * (csrc/k_program.cu).  Replaces Trace.eval of the assume / observe directives
  * (lite/trace.py:397-420) for all particles.
- *   code      5 int32 per instruction: op, dst, a, b, c (op codes: compiler.py OP)
+ *   code      4 int32 per instruction: op, dst, a, b (op codes: compiler.py OP)
  *   consts    literals of the assumes
  *   meta      n_sites, n_groups, n_registers, n_sections, PRIOR section, JOINT section;
  *             per site: SIM, CHILD, OWN section, number of observation groups below it;

@@ -17,7 +17,7 @@ import scipy.stats
 
 import oracle
 
-WORDS = 5
+WORDS = 4
 
 
 def _log(x):
@@ -62,7 +62,7 @@ class VM(object):
         first, n = self.dir[sec]
         acc = 0.0
         for i in range(first, first + n):
-            op, d, a, b, _c = [int(x) for x in self.code[i * WORDS:(i + 1) * WORDS]]
+            op, d, a, b = [int(x) for x in self.code[i * WORDS:(i + 1) * WORDS]]
             name = self.op[op]
             if name == "CONST": R[d] = float(self.consts[a])
             elif name == "SITE": R[d] = float(self.sites[a, p])

@@ -50,7 +50,7 @@ OP = dict(
     LD_NORMAL=64, LD_GAMMA=65, LD_BETA=66, LD_UNIFORM=67, LD_EXPON=68, LD_FLIP=69, LD_LOG_FLIP=70,
     LD_LOG_ODDS_FLIP=71,
     STORE=96)
-INSTR_WORDS = 5          # op, dst, a, b, c
+INSTR_WORDS = 4          # op, dst, a, b
 MAX_REGS = 96
 
 DET = {"add": ("fold", "ADD"), "mul": ("fold", "MUL"), "sub": (2, "SUB"), "div": (2, "DIV"), "pow": (2, "POW"),
@@ -275,8 +275,8 @@ class _Code(object):
     def __init__(self, prog):
         self.prog, self.words, self.done = prog, [], set()
 
-    def emit(self, op, dst=0, a=0, b=0, c=0):
-        self.words += [OP[op], dst, a, b, c]
+    def emit(self, op, dst=0, a=0, b=0):
+        self.words += [OP[op], dst, a, b]
 
     def reg(self, nid):
         return self.prog.reg_of(nid)

@@ -51,6 +51,7 @@ struct P2PArrays {                     // by-value kernel argument of the gather
                                             // the 4-byte particle-minor array patch_src (patch_array < 0: none)
   double *lw; const double *red; double log_p_total;   // evened-out weights written by the same kernel
   int32_t *anc_other;                  // the ancestor half of the previous resample: reset to -1 here
+  int world, rank;
   long long timeout_ns;
   volatile int *err_host;
 };
@@ -135,6 +136,10 @@ p2p_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__r
   const double ratio = (double)n_total / (double)W, u0f = (double)U0 * (1.0 / 4294967296.0);
   int64_t k_lo = first_child_at_least(run, W, n_total, U0, ratio, u0f);
   const int64_t half_off = (int64_t)anc_half * n;
+  // the thread's children are one contiguous range of slots: owner rank and offset advance by counting, the owner's
+  // array pointer is fetched when the range crosses into the next rank (no division, no table load per child)
+  int64_t d = k_lo / n, rem = k_lo - d * n;
+  int32_t *dst = k_lo < n_total ? tab->anc[d] + half_off : nullptr;
 #pragma unroll
   for (int j = 0; j < ITEMS; ++j) {
     if (q[j] == 0) continue;
@@ -142,8 +147,8 @@ p2p_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__r
     int64_t k_hi = first_child_at_least(run, W, n_total, U0, ratio, u0f);
     const int32_t g = (int32_t)(p_base + base + j);
     for (int64_t k = k_lo; k < k_hi; ++k) {
-      int64_t d = k / n;
-      tab->anc[d][half_off + k - d * n] = g;
+      dst[rem] = g;
+      if (++rem == n) { rem = 0; ++d; dst = k + 1 < n_total ? tab->anc[d] + half_off : nullptr; }
     }
     k_lo = k_hi;
   }
@@ -198,8 +203,23 @@ __global__ void __launch_bounds__(256)
 p2p_gather_kernel(const int32_t *__restrict__ anc_g, int64_t n, const P2PTables *__restrict__ tab,
                   P2PParams *__restrict__ par, P2PArrays arrs) {
   const int64_t tid0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+  // every rank's LIVE buffer of every array, once per CTA (the tables live in global memory: read per element they
+  // put two dependent loads in front of every peer load)
+  __shared__ const unsigned char *live_sh[P2P_MAX_ARRAYS][P2P_MAX_WORLD];
+  for (int e = threadIdx.x; e < P2P_MAX_ARRAYS * P2P_MAX_WORLD; e += blockDim.x) {
+    const int a = e / P2P_MAX_WORLD, d = e - a * P2P_MAX_WORLD;
+    live_sh[a][d] = (a < arrs.n && d < arrs.world) ? tab->buf[a][d][par->cur_idx[d]] : nullptr;
+  }
+  __syncthreads();
   for (int64_t t = tid0; t < n; t += stride) arrs.anc_other[t] = -1;
   bool failed = ((volatile P2PParams *)par)->err != 0;
+  // owner rank of a global particle index: most ancestors are this rank's own
+  auto owner = [&](int64_t g, int64_t &i) -> int {
+    int d = arrs.rank;
+    i = g - (int64_t)d * n;
+    if (i < 0 || i >= n) { d = (int)(g / n); i = g - (int64_t)d * n; }
+    return d;
+  };
   for (int a = 0; a < arrs.n && !failed; ++a) {
     if (arrs.elem_bytes[a] == 0) {
       const long long rb = arrs.row_bytes[a];
@@ -209,11 +229,12 @@ p2p_gather_kernel(const int32_t *__restrict__ anc_g, int64_t n, const P2PTables 
           int64_t s = t / units, u = t - s * units;
           int64_t g = p2p_wait_ancestor(anc_g, s, par, arrs.timeout_ns, arrs.err_host);
           if (g < 0) { failed = true; break; }
-          int64_t d = g / n, i = g - d * n;
-          const uint4 *src = (const uint4 *)(tab->buf[a][d][par->cur_idx[d]] + i * rb);
+          int64_t i;
+          const int d = owner(g, i);
+          const uint4 *src = (const uint4 *)(live_sh[a][d] + i * rb);
           uint4 v = src[u];
           if (a == arrs.patch_array && u == (arrs.patch_byte >> 4)) {
-            const uint32_t sv = ((const uint32_t *)tab->buf[arrs.patch_src][d][par->cur_idx[d]])[i] & 0xFFu;
+            const uint32_t sv = ((const uint32_t *)live_sh[arrs.patch_src][d])[i] & 0xFFu;
             const int pw = (arrs.patch_byte >> 2) & 3, psh = (arrs.patch_byte & 3) * 8;
             const uint32_t keep = ~(0xFFu << psh), ins = sv << psh;
             if (pw == 0) v.x = (v.x & keep) | ins;
@@ -228,8 +249,9 @@ p2p_gather_kernel(const int32_t *__restrict__ anc_g, int64_t n, const P2PTables 
           int64_t s = t / rb, u = t - s * rb;
           int64_t g = p2p_wait_ancestor(anc_g, s, par, arrs.timeout_ns, arrs.err_host);
           if (g < 0) { failed = true; break; }
-          int64_t d = g / n, i = g - d * n;
-          arrs.alt[a][s * rb + u] = tab->buf[a][d][par->cur_idx[d]][i * rb + u];
+          int64_t i;
+          const int d = owner(g, i);
+          arrs.alt[a][s * rb + u] = live_sh[a][d][i * rb + u];
         }
       }
     } else {
@@ -239,8 +261,9 @@ p2p_gather_kernel(const int32_t *__restrict__ anc_g, int64_t n, const P2PTables 
         int64_t r = t / n, s = t - r * n;
         int64_t g = p2p_wait_ancestor(anc_g, s, par, arrs.timeout_ns, arrs.err_host);
         if (g < 0) { failed = true; break; }
-        int64_t d = g / n, i = g - d * n;
-        const unsigned char *src = tab->buf[a][d][par->cur_idx[d]] + (r * n + i) * eb;
+        int64_t i;
+        const int d = owner(g, i);
+        const unsigned char *src = live_sh[a][d] + (r * n + i) * eb;
         unsigned char *dst = arrs.alt[a] + (r * n + s) * eb;
         if (eb == 8) *(uint64_t *)dst = *(const uint64_t *)src;
         else if (eb == 4) *(uint32_t *)dst = *(const uint32_t *)src;
@@ -449,6 +472,7 @@ void p2p_resample(vk_particles *h, int mode) {
   pa.lw = h->lw.p; pa.red = h->red.p; pa.log_p_total = log((double)P_total);
   pa.anc_other = s->anc_g.p + (int64_t)(1 - half) * P;
   pa.timeout_ns = s->timeout_ns; pa.err_host = s->err_host_dev;
+  pa.world = s->world; pa.rank = s->rank;
   int64_t work = P;
   for (int a = 0; a < s->n_arrays; ++a) {
     pa.alt[a] = (unsigned char *)*arrs[a].alt;

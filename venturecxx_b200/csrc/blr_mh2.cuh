@@ -13,9 +13,9 @@
 //     and each proposal's feature pair one 16-byte L2 read (half the LSU instructions per evaluation).
 //   * exp(-|v|): the |v| <= 700 clamp (3 integer instructions per evaluation) is gone -- the exponent index m
 //     is clamped instead (1 instruction; a huge |v| then yields e ~ 1e-270, i.e. 0 next to 1), the exp table
-//     holds 2^(j/64) with j << 14 pre-subtracted from its high word so that 2^(m>>6) T[j] is ONE integer
-//     multiply-add, and 1 + e = fma(2^n T[j], P(r), 1) with P = e^r of degree 5 (12 fp64 instructions per
-//     evaluation instead of 13).  |v| beyond 2^31 ln2/64 (the index would wrap) or NaN is caught by a test on
+//     holds 2^(j/128) (128 rows x 8 replicas) with j << 13 pre-subtracted from its high word so that
+//     2^(m>>7) T[j] is ONE integer multiply-add, and 1 + e = fma(2^n T[j], P(r), 1) with P = e^r of degree 4 on
+//     |r| <= ln2/256 (11 fp64 instructions per evaluation instead of 13; fit error 1.5e-16).  |v| beyond 2^31 ln2/64 (the index would wrap) or NaN is caught by a test on
 //     the thread's sum of |v| and sends the PASS to the branch-free full-range path (fast_log_logistic).
 // Everything else (neutral padding slots, running products with one logarithm per pass, sum min(v,0) from
 // sum v and sum |v|, recomputed S_eta after an accept, row written back once per launch) is blr_mh_kernel's.
@@ -25,13 +25,14 @@ namespace vk {
 
 static const int MH2_THREADS = 256;
 static const int MH2_TILE = 4 * MH2_THREADS;   // observations per iteration: two 16-byte pairs per thread
-static const int MH2_M_MIN = -64 * 1010;       // smallest exponent index: 2^-1010 is still a normal double
+static const int MH2_M_MIN = -128 * 1010;      // smallest exponent index: 2^-1010 is still a normal double
 
-// exp table for this kernel: entry j = 2^(j/64) with (j << 14) subtracted from the high word, 16 replicas
+// exp table for this kernel: entry j = 2^(j/128) with (j << 13) subtracted from the high word, 128 rows of 8 replicas
+// (the same 8 KB as the 64 x 16 table of fast_math.cuh; |r| <= ln2/256 lets e^r = 1 + r E(r) stop at degree 4)
 __device__ __forceinline__ void mh2_fill_exp_table(unsigned char *exp_tbl) {
-  for (int i = threadIdx.x; i < 64 * 16; i += blockDim.x) {
-    const unsigned long long j = (unsigned long long)(i >> 4);
-    reinterpret_cast<unsigned long long *>(exp_tbl)[i] = FM_EXP_TABLE_DEV[i >> 4] - (j << 46);
+  for (int i = threadIdx.x; i < 128 * 8; i += blockDim.x) {
+    const unsigned long long j = (unsigned long long)(i >> 3);
+    reinterpret_cast<unsigned long long *>(exp_tbl)[i] = FM_EXP128_TABLE_DEV[i >> 3] - (j << 45);
   }
 }
 
@@ -39,21 +40,20 @@ __device__ __forceinline__ void mh2_fill_exp_table(unsigned char *exp_tbl) {
 __device__ __forceinline__ double mh2_one_plus_exp(double v, const FmCoef &cf, uint32_t exp_base) {
   const double MAGIC = 6755399441055744.0;                 // 1.5 * 2^52: ulp 1
   const double a = fabs(v);
-  const double t = fma(a, cf.neg_scale, MAGIC);            // low word = rint(-a 64/ln2)
+  const double t = fma(a, cf.neg_scale128, MAGIC);         // low word = rint(-a 128/ln2)
   const double nf = t - MAGIC;
-  const double r = fma(nf, -cf.c_ln2, -a);
+  const double r = fma(nf, -cf.c_ln2_128, -a);
   const int m = max(__double2loint(t), MH2_M_MIN);
   uint32_t ea, th;
   double T;
-  asm("mad.lo.u32 %0, %1, 128, %2;" : "=r"(ea) : "r"((uint32_t)(m & 63)), "r"(exp_base));
+  asm("mad.lo.u32 %0, %1, 64, %2;" : "=r"(ea) : "r"((uint32_t)(m & 127)), "r"(exp_base));
   asm("ld.shared.f64 %0, [%1];" : "=d"(T) : "r"(ea));
-  asm("mad.lo.u32 %0, %1, 16384, %2;" : "=r"(th) : "r"((uint32_t)m), "r"((uint32_t)__double2hiint(T)));
-  const double Ts = __hiloint2double((int)th, __double2loint(T));   // 2^(m>>6) 2^((m&63)/64)
-  double P = cf.E[4];                                      // e^r = 1 + r E(r)
-  P = fma(P, r, cf.E[3]);
-  P = fma(P, r, cf.E[2]);
-  P = fma(P, r, cf.E[1]);
-  P = fma(P, r, cf.E[0]);
+  asm("mad.lo.u32 %0, %1, 8192, %2;" : "=r"(th) : "r"((uint32_t)m), "r"((uint32_t)__double2hiint(T)));
+  const double Ts = __hiloint2double((int)th, __double2loint(T));   // 2^(m>>7) 2^((m&127)/128)
+  double P = cf.E3[3];                                     // e^r = 1 + r E(r), E of degree 3
+  P = fma(P, r, cf.E3[2]);
+  P = fma(P, r, cf.E3[1]);
+  P = fma(P, r, cf.E3[0]);
   P = fma(P, r, 1.0);
   return fma(Ts, P, 1.0);
 }
@@ -91,7 +91,7 @@ blr_mh2_kernel(double *__restrict__ w, double *__restrict__ eta, double *__restr
   fm_fill_smem_tables(log_tbl, exp_tbl);
   __syncthreads();
   mh2_fill_exp_table(exp_tbl);
-  const uint32_t exp_base = (uint32_t)__cvta_generic_to_shared(exp_tbl) + (uint32_t)(lane & 15) * 8u;
+  const uint32_t exp_base = (uint32_t)__cvta_generic_to_shared(exp_tbl) + (uint32_t)(lane & 7) * 8u;
   const uint32_t log_base = (uint32_t)__cvta_generic_to_shared(log_tbl) + (uint32_t)(lane & 7) * 16u;
   for (int j = 0; j < prm.D; ++j) {          // column sums, once per CTA
     const double *xc = Xs + (int64_t)j * prm.Xld;

@@ -139,7 +139,9 @@ static const uint64_t FM_E_BITS_HOST[5] = {VK_FM_E_COEFFS_BITS};
 static const uint64_t FM_Q_BITS_HOST[6] = {VK_FM_Q_COEFFS_BITS};
 static const uint64_t FM_EXP_TABLE_HOST[64] = {VK_FM_EXP_TABLE_BITS};
 static const uint64_t FM_LOG_TABLE_HOST[2 * 129] = {VK_FM_LOG_TABLE_BITS};
+static const uint64_t FM_E128_BITS_HOST[4] = {VK_FM_E128_COEFFS_BITS};
 #ifdef __CUDACC__
+__device__ const uint64_t FM_EXP128_TABLE_DEV[128] = {VK_FM_EXP128_TABLE_BITS};
 __constant__ uint64_t FM_EQ_BITS_DEV[11] = {VK_FM_E_COEFFS_BITS, VK_FM_Q_COEFFS_BITS};
 __device__ const uint64_t FM_EXP_TABLE_DEV[64] = {VK_FM_EXP_TABLE_BITS};
 __device__ const uint64_t FM_LOG_TABLE_DEV[2 * 129] = {VK_FM_LOG_TABLE_BITS};
@@ -226,6 +228,10 @@ struct FmCoef {
   double neg_scale;   // -64/ln2
   double c_ln2;       // ln2/64
   double k128;        // 128
+  // blr_mh2.cuh: 128-entry exp table, (e^r - 1)/r of degree 3 on |r| <= ln2/256
+  double E3[4];
+  double neg_scale128;   // -128/ln2
+  double c_ln2_128;      // ln2/128
 };
 inline FmCoef fm_coef_host() {
   FmCoef c;
@@ -234,6 +240,9 @@ inline FmCoef fm_coef_host() {
   c.neg_scale = -92.332482616893656;
   c.c_ln2 = 0.010830424696249145;
   c.k128 = 128.0;
+  for (int i = 0; i < 4; ++i) c.E3[i] = fm_from_bits(FM_E128_BITS_HOST[i]);
+  c.neg_scale128 = -184.66496523378731;
+  c.c_ln2_128 = 0.0054152123481245727;
   return c;
 }
 static const int FM_SMEM_LOG_BYTES = 129 * 128;   // 129 rows x 8 replicas x 16 B

@@ -66,6 +66,7 @@ enum vk_model_kind {
 #define VK_BLOCK_ONE  (-1)  /* a uniformly chosen block per transition */
 #define VK_BLOCK_ALL  (-2)  /* all blocks of the scope as one proposal  */
 #define VK_BLOCK_EACH (-3)  /* every block in order, one proposal each  */
+#define VK_BLOCK_ORDERED (-4) /* all blocks of an ordered scope, in order (pgibbs) */
 
 /* arithmetic of the N-observation sums inside the MH hot loop ("fp64 (parity) and fp32
  * (throughput) modes").  State (latent values, logit caches, weights), proposals and accept tests are
@@ -241,6 +242,15 @@ int vk_p2p_export(vk_particles *h, unsigned char *handles_out, int32_t max_handl
 int vk_p2p_open(vk_particles *h, int32_t world, int32_t rank, const unsigned char *all_handles, int32_t n_handles);
 int vk_p2p_resample(vk_particles *h, int mode);
 int vk_p2p_status(vk_particles *h, int32_t *timed_out, double *lse_out);
+
+/* Particle Gibbs, `(pgibbs scope ordered particles transitions)`: infer/dispatch.py:197-212 ->
+ * infer/pgibbs.py:49-126 (PGibbsOperator under mixMH; registered at inference_sps.py:269-300): conditional
+ * SMC over the ordered blocks of the scope inside every trace, `particles` new inner particles next to the
+ * retained path, one MH accept of the chosen path.  Compiled for the HMM model (the state sequence,
+ * hmm.vnt's scope `seq` = scope 0 here; 1..16 inner particles, at most 32 time steps); other model kinds
+ * answer VK_EUNSUPPORTED.  accepted_out_host: NULL or P int64 = transitions that replaced the path. */
+int vk_pgibbs(vk_particles *h, int32_t scope, int32_t block, int32_t particles, int32_t transitions,
+              double *mean_nodes_out_host, int64_t *accepted_out_host);
 
 /* Slice sampling with stepping out, `(slice scope block w m transitions)`: infer/dispatch.py:190-194 ->
  * infer/slice_sample.py:39-139 (StepOutSliceOperator under mixMH; registered at inference_sps.py:500-516).

@@ -25,6 +25,11 @@ HAND = {
         ("pattern = ['let', map(list, zip(syms, vals)), 'body']", "pattern = ['let', list(map(list, zip(syms, vals))), 'body']"),
         ("pattern = ['letrec', map(list, zip(syms, vals)), 'body']", "pattern = ['letrec', list(map(list, zip(syms, vals))), 'body']"),
     ],
+    # py2 ordered objects through __cmp__; py3's sorted() asks for __lt__ (getOrderedSetsInScope sorts block keys,
+    # lite/trace.py:334): the same total order, spelled the py3 way
+    "lite/value.py": [
+        ("  def __cmp__(self, other):", "  def __lt__(self, other):\n    return self.__cmp__(other) < 0\n  def __cmp__(self, other):"),
+    ],
     "sivm/core_sivm.py": [
         ("return map(_modify_expression, expression)", "return list(map(_modify_expression, expression))"),
     ],

@@ -881,6 +881,65 @@ void orc_hmm_gibbs(uint8_t *hist, int Tpad, int T, const double *trans, const do
   }
 }
 
+/* `(pgibbs seq ordered Pi K)` on the HMM: PGibbsOperator under mixMH, infer/pgibbs.py:49-126 (propose: the
+ * conditional SMC; _compute_alpha :109-121), dispatch.py:197-212, with sampleLogCategorical utils.py:170-180 and
+ * normalizeList :93-99.  Border segment 0 is the deterministic state(1): nothing is drawn, every inner particle
+ * starts at the weight of the first emission; every later segment: ancestor, then state, per inner particle;
+ * weights restart after each resampling.  Draws: 0 unused, 1 accept uniform, then in call order. */
+static int sample_log_categorical(orc_stream *r, const double *lw, int n) {
+  double m = -INFINITY, ps[64], tot = 0;
+  for (int i = 0; i < n; ++i) if (lw[i] > m) m = lw[i];
+  for (int i = 0; i < n; ++i) { ps[i] = m > -INFINITY ? exp(lw[i] - m) : 0; tot += ps[i]; }
+  for (int i = 0; i < n; ++i) ps[i] = tot > 0 ? ps[i] / tot : 1.0 / n;
+  return categorical_sim(r, ps, n);
+}
+static double lse_small(const double *v, int n) {
+  double m = -INFINITY, s = 0;
+  for (int i = 0; i < n; ++i) if (v[i] > m) m = v[i];
+  if (isinf(m)) return m;
+  for (int i = 0; i < n; ++i) s += exp(v[i] - m);
+  return m + log(s);
+}
+void orc_hmm_pgibbs(uint8_t *hist, int Tpad, int T, const double *trans, const double *emit, int S, int O,
+                    const int32_t *symbols, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps,
+                    int Pi, int64_t *accepted) {
+  for (int64_t p = 0; p < P; ++p) {
+    uint8_t *h = hist + p * Tpad;
+    static uint8_t path[2][64][256];
+    double xi[65], nw[64], others[65];
+    int64_t acc = 0;
+    for (int k = 0; k < n_steps; ++k) {
+      orc_stream r; st_init(&r, seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
+      (void)st_uniform(&r);
+      double logu = log(st_uniform(&r));
+      int cb = 0;
+      double w0 = categorical_logpmf(symbols[0] - 1, emit + (h[0] - 1) * O, O);
+      for (int i = 0; i < Pi; ++i) { xi[i] = w0; path[0][i][0] = h[0]; }
+      double rho_prev = w0;
+      for (int t = 1; t < T; ++t) {
+        xi[Pi] = rho_prev;
+        for (int i = 0; i < Pi; ++i) {
+          int a = sample_log_categorical(&r, xi, Pi + 1);
+          const uint8_t *src = a == Pi ? h : path[cb][a];
+          for (int u = 0; u < t; ++u) path[cb ^ 1][i][u] = src[u];
+          int s = 1 + categorical_sim(&r, trans + (src[t - 1] - 1) * S, S);
+          path[cb ^ 1][i][t] = (uint8_t)s;
+          nw[i] = categorical_logpmf(symbols[t] - 1, emit + (s - 1) * O, O);
+        }
+        for (int i = 0; i < Pi; ++i) xi[i] = nw[i];
+        cb ^= 1;
+        rho_prev = categorical_logpmf(symbols[t] - 1, emit + (h[t] - 1) * O, O);
+      }
+      int f = sample_log_categorical(&r, xi, Pi), n_o = 0;
+      for (int i = 0; i < Pi; ++i) if (i != f) others[n_o++] = xi[i];
+      others[n_o++] = rho_prev;
+      double alpha = lse_small(xi, Pi) - lse_small(others, n_o);
+      if (logu < alpha) { for (int u = 0; u < T; ++u) h[u] = path[cb][f][u]; ++acc; }
+    }
+    if (accepted) accepted[p] = acc;
+  }
+}
+
 /* ------------------------------------------- C5: subsampled MH (BLR) */
 /* Keyed Feistel bijection on [0,N) shared by the particle batch: the product's
  * stand-in for np_rng.permutation(local_roots) (subsampled_mh.py:103). */

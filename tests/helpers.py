@@ -92,6 +92,15 @@ class OracleHMM(object):
                                    oracle.I32(n_steps), oracle.I32(block_mode), oracle._ptr(ch))
         return ch
 
+    def pgibbs(self, step0, n_steps, particles):
+        sym = np.ascontiguousarray(self.symbols, dtype=np.int32)
+        acc = np.empty(self.P, dtype=np.int64)
+        oracle.lib().orc_hmm_pgibbs(oracle._ptr(self.hist), oracle.I32(self.Tpad), oracle.I32(self.T), oracle._ptr(self.trans),
+                                    oracle._ptr(self.emit), oracle.I32(self.S), oracle.I32(self.O), oracle._ptr(sym),
+                                    oracle.I64(self.P), oracle.I64(self.p_base), oracle.U64(self.seed), oracle.U32(step0),
+                                    oracle.I32(n_steps), oracle.I32(particles), oracle._ptr(acc))
+        return acc
+
     def resample(self, anc):
         self.hist = np.ascontiguousarray(self.hist[anc])
         lse = oracle.logsumexp(self.lw)

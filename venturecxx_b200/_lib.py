@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libventure_b200.so")
 
 VK_OK, VK_EINVAL, VK_ECUDA, VK_EUNSUPPORTED, VK_ESTATE = 0, 1, 2, 3, 4
-BLOCK_ONE, BLOCK_ALL, BLOCK_EACH = -1, -2, -3
+BLOCK_ONE, BLOCK_ALL, BLOCK_EACH, BLOCK_ORDERED = -1, -2, -3, -4
 FP64, FP32 = 0, 1
 RESAMPLE_MULTINOMIAL, RESAMPLE_SYSTEMATIC = 0, 1
 
@@ -59,6 +59,7 @@ PROTOTYPES = {
     "vk_mh": [_vp, _i32, _i32, _i32, _vp, _vp],
     "vk_gibbs": [_vp, _i32, _i32, _i32, _vp, _vp],
     "vk_slice": [_vp, _i32, _i32, _f64, _f64, _i32, _vp, _vp],
+    "vk_pgibbs": [_vp, _i32, _i32, _i32, _i32, _vp, _vp],
     "vk_p2p_export": [_vp, _vp, _i32, _vp],
     "vk_p2p_open": [_vp, _i32, _i32, _vp, _i32],
     "vk_p2p_resample": [_vp, _i32],

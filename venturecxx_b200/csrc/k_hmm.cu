@@ -262,6 +262,84 @@ hmm_gibbs_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad
   }
 }
 
+// `(pgibbs seq ordered Pi K)`: PGibbsOperator under mixMH (infer/pgibbs.py:49-126, dispatch.py:197-212) -- conditional
+// SMC over the time steps inside EVERY outer particle: Pi new inner particles next to the retained path.  Border segment
+// t holds state(t+1) (0-based time t); segment 0 is the deterministic state(1), so nothing is drawn there and every
+// inner particle starts with the weight of the first emission.  At every later segment each inner particle draws an
+// ancestor from sampleLogCategorical over the Pi current weights + the retained path's weight of the previous segment
+// (utils.py:170-180: exp(lw - max), normalizeList, categorical), inherits that path, draws its state from the
+// transition row and is weighted by its emission (weights are NOT accumulated: they restart after the resampling).
+// The final index is drawn from the Pi new weights, alpha = logsumexp(xi) - logsumexp(xi without the chosen one + rho)
+// (:109-121) and mixMH accepts iff log u < alpha.  Draw layout: draw 0 unused (no block choice), draw 1 accept uniform,
+// then the draws above in call order.  One thread per outer particle; paths live in local memory.
+static const int HMM_PG_MAX = 16;    // inner particles
+__device__ __forceinline__ int hmm_sample_log_categorical(Stream &r, const double *lw, int n) {
+  double m = -INFINITY, ps[HMM_PG_MAX + 1], tot = 0.0;
+  for (int i = 0; i < n; ++i) m = fmax(m, lw[i]);
+  for (int i = 0; i < n; ++i) { ps[i] = m > -INFINITY ? exp(lw[i] - m) : 0.0; tot += ps[i]; }
+  for (int i = 0; i < n; ++i) ps[i] = tot > 0.0 ? ps[i] / tot : 1.0 / (double)n;     // normalizeList, utils.py:93-99
+  return categorical_sim(r, ps, n, 1);
+}
+__device__ __forceinline__ double hmm_lse(const double *v, int n) {                  // utils.py:70-91
+  double m = -INFINITY;
+  for (int i = 0; i < n; ++i) m = fmax(m, v[i]);
+  if (isinf(m)) return m;
+  double s = 0.0;
+  for (int i = 0; i < n; ++i) s += exp(v[i] - m);
+  return m + log(s);
+}
+__global__ void __launch_bounds__(128)
+hmm_pgibbs_kernel(int32_t *__restrict__ cur, uint8_t *__restrict__ hist, int Tpad, int T, HMMTables tb,
+                  const int32_t *__restrict__ symbols, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0,
+                  int n_steps, int Pi, long long *__restrict__ acc_out, double *__restrict__ nodes_out) {
+  extern __shared__ double sh[];
+  double *tr = sh;
+  double *em = sh + tb.n_rows * tb.S;
+  for (int i = threadIdx.x; i < tb.n_rows * tb.S; i += blockDim.x) tr[i] = tb.trans[i];
+  for (int i = threadIdx.x; i < tb.S * tb.O; i += blockDim.x) em[i] = tb.emit[i];
+  __syncthreads();
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P; p += (int64_t)gridDim.x * blockDim.x) {
+    uint8_t *h = hist + p * Tpad;
+    uint8_t path[2][HMM_PG_MAX][32];          // [buffer][inner particle][time]
+    double xi[HMM_PG_MAX + 1], nw[HMM_PG_MAX];
+    long long acc = 0;
+    for (int k = 0; k < n_steps; ++k) {
+      Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)k);
+      (void)r.uniform();
+      const double logu = log(r.uniform());
+      int cb = 0;
+      const double w0 = categorical_logpmf(symbols[0] - 1, em + (h[0] - 1) * tb.O, tb.O, 1);
+      for (int i = 0; i < Pi; ++i) { xi[i] = w0; path[0][i][0] = h[0]; }
+      double rho_prev = w0;
+      for (int t = 1; t < T; ++t) {
+        xi[Pi] = rho_prev;
+        for (int i = 0; i < Pi; ++i) {
+          const int a = hmm_sample_log_categorical(r, xi, Pi + 1);
+          const uint8_t *src = a == Pi ? h : path[cb][a];
+          for (int u = 0; u < t; ++u) path[cb ^ 1][i][u] = src[u];
+          const int s = 1 + categorical_sim(r, tr + (src[t - 1] - 1) * tb.S, tb.S, 1);
+          path[cb ^ 1][i][t] = (uint8_t)s;
+          nw[i] = categorical_logpmf(symbols[t] - 1, em + (s - 1) * tb.O, tb.O, 1);
+        }
+        for (int i = 0; i < Pi; ++i) xi[i] = nw[i];
+        cb ^= 1;
+        rho_prev = categorical_logpmf(symbols[t] - 1, em + (h[t] - 1) * tb.O, tb.O, 1);
+      }
+      const int f = hmm_sample_log_categorical(r, xi, Pi);
+      double others[HMM_PG_MAX + 1];
+      int n_o = 0;
+      for (int i = 0; i < Pi; ++i) if (i != f) others[n_o++] = xi[i];
+      others[n_o++] = rho_prev;
+      const double alpha = hmm_lse(xi, Pi) - hmm_lse(others, n_o);
+      if (logu < alpha) { for (int u = 0; u < T; ++u) h[u] = path[cb][f][u]; ++acc; }
+    }
+    if (T > 0) cur[p] = h[T - 1];
+    if (acc_out) acc_out[p] = acc;
+    // one scaffold over every state site: the sites' node counts add up (Lite: 13 per interior state, 9 for the newest)
+    if (nodes_out) nodes_out[p] = (n_steps > 0 && T > 1) ? (double)(HMM_NODES_INTERIOR * (T - 2) + HMM_NODES_LAST) : 0.0;
+  }
+}
+
 __global__ void hmm_loglik_kernel(const uint8_t *__restrict__ hist, int Tpad, int T, HMMTables tb,
                                   const int32_t *__restrict__ symbols, int64_t P, int joint, int t_first,
                                   double *__restrict__ out) {
@@ -451,6 +529,25 @@ struct HMMModel : Model {
   void gibbs(int scope, int block, int K, double *mean_nodes_dev, long long *changed_dev) override {
     VK_REQUIRE(tb.S <= 32, VK_EUNSUPPORTED, "hmm: gibbs is compiled for at most 32 states");
     run_sites(1, scope, block, K, mean_nodes_dev, changed_dev);
+  }
+  void pgibbs(int scope, int block, int particles, int K, double *mean_nodes_dev, long long *acc_dev) override {
+    VK_REQUIRE(scope == 0, VK_EINVAL, "hmm: only the default scope (= the ordered scope `seq` of hmm.vnt) exists");
+    VK_REQUIRE(block == VK_BLOCK_ORDERED, VK_EINVAL, "pgibbs: block must be `ordered`");
+    VK_REQUIRE(particles >= 1 && particles <= HMM_PG_MAX, VK_EUNSUPPORTED, "pgibbs: 1..16 inner particles are compiled");
+    VK_REQUIRE(T <= 32, VK_EUNSUPPORTED, "pgibbs: at most 32 time steps are compiled");
+    VK_REQUIRE(T == (int)symbols_host.size(), VK_ESTATE, "pgibbs: unpropagated observations; call vk_make_consistent first");
+    flush_hist();
+    if (K > 0 && T > 1) {
+      uint32_t step0 = h->next_step((uint32_t)K);
+      upload_symbols();
+      hmm_pgibbs_kernel<<<grid_for(h->P, 128, h->sm_count, 8), 128, smem, h->stream>>>(
+          cur, hist, Tpad, T, tb, symbols.p, h->P, h->p_base, h->seed, step0, K, particles, acc_dev, mean_nodes_dev);
+      VK_CUDA(cudaGetLastError());
+      VK_CUDA(cudaStreamSynchronize(h->stream));
+    } else {
+      if (acc_dev) VK_CUDA(cudaMemsetAsync(acc_dev, 0, (size_t)h->P * sizeof(long long), h->stream));
+      if (mean_nodes_dev) hmm_fill_kernel<<<grid(), 256, 0, h->stream>>>(mean_nodes_dev, h->P, 0.0);
+    }
   }
   void run_sites(int op, int scope, int block, int K, double *mean_nodes_dev, long long *acc_dev) {
     VK_REQUIRE(scope == 0, VK_EINVAL, "hmm: only the default scope exists");

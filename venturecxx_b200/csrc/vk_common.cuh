@@ -160,6 +160,10 @@ struct Model {
   virtual void gibbs(int scope, int block, int K, double *mean_nodes_dev, long long *changed_dev) {
     throw Error(VK_EUNSUPPORTED, "gibbs: this model has no enumerable sites compiled");
   }
+  // particle Gibbs over an ordered scope (infer/pgibbs.py): conditional SMC with `particles` inner particles
+  virtual void pgibbs(int scope, int block, int particles, int K, double *mean_nodes_dev, long long *acc_dev) {
+    throw Error(VK_EUNSUPPORTED, "pgibbs: compiled for the HMM model's ordered state sequence only");
+  }
   // slice sampling with stepping out on a continuous one-dimensional site (infer/slice_sample.py); moved_dev counts
   // transitions that changed the value
   virtual void slice(int scope, int block, double w, double m, int K, double *mean_nodes_dev, long long *moved_dev) {

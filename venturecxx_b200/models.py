@@ -103,6 +103,8 @@ class HMMModel(Model):
     """examples/hmm.vnt:31-60: state(1) = init_state, state(t) ~ categorical(T[state(t-1)-1], 1..S),
     observe categorical(E[state(t)-1], 1..O) = d_t."""
     kind = 3
+    # hmm.vnt tags every state(t) into the ordered scope `seq`, block t: the same random choices as the default scope
+    scopes = {"default": 0, "seq": 0}
 
     def __init__(self, transition_matrix, emission_matrix, init_state=1, T_max=32):
         self.trans = np.ascontiguousarray(transition_matrix, dtype=np.float64)

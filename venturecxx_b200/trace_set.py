@@ -18,7 +18,7 @@ import numpy as np
 from . import _lib
 from .exception import VentureException
 
-_BLOCKS = {"one": _lib.BLOCK_ONE, "all": _lib.BLOCK_ALL, "each": _lib.BLOCK_EACH}
+_BLOCKS = {"one": _lib.BLOCK_ONE, "all": _lib.BLOCK_ALL, "each": _lib.BLOCK_EACH, "ordered": _lib.BLOCK_ORDERED}
 
 
 def _unbox(v):
@@ -228,6 +228,12 @@ class B200TraceSet(object):
             if len(exp) != 4:
                 raise VentureException("invalid_argument", "gibbs takes (scope block transitions)")
             return self.gibbs(exp[1], exp[2], exp[3])
+        if op in ("pgibbs", "func_pgibbs"):
+            if len(exp) == 6 and isinstance(exp[5], bool):      # the trailing in_parallel flag (inference_sps.py:269-300)
+                exp = exp[:5]
+            if len(exp) != 5:
+                raise VentureException("invalid_argument", "%s takes (scope block particles transitions)" % op)
+            return self.pgibbs(exp[1], exp[2], exp[3], exp[4])
         if op == "slice":
             if len(exp) != 6:
                 raise VentureException("invalid_argument", "slice takes (scope block w m transitions)")
@@ -262,6 +268,15 @@ class B200TraceSet(object):
         ch = self._out(dtype=np.int64) if return_changes else None
         _lib.call("vk_gibbs", self._h, s, b, int(transitions), _lib.ptr(out), _lib.ptr(ch))
         return (out, ch) if return_changes else out
+
+    def pgibbs(self, scope, block, particles, transitions, return_accepts=False):
+        """(pgibbs scope ordered particles transitions): particle Gibbs over the ordered blocks of a scope
+        (infer/dispatch.py:197-212 -> infer/pgibbs.py:49-126)."""
+        s, b = self._scope_block(scope, block)
+        out = self._out()
+        acc = self._out(dtype=np.int64) if return_accepts else None
+        _lib.call("vk_pgibbs", self._h, s, b, int(particles), int(transitions), _lib.ptr(out), _lib.ptr(acc))
+        return (out, acc) if return_accepts else out
 
     def slice(self, scope, block, w, m, transitions, return_moves=False):
         """(slice scope block w m transitions): slice sampling with stepping out on a continuous site

@@ -8,7 +8,7 @@ imports the file and calls `__venture_start__(ripl, *args)`
     (ripl.py:938-939 -> engine/engine.py:56-59) whenever the host Venture's
     `venture.lite.inference_sps` is importable: `b200_resample`,
     `b200_likelihood_weight`, `b200_incorporate`, `b200_resimulation_mh` / `b200_mh`,
-    `b200_gibbs`, `b200_subsampled_mh`, `b200_log_likelihood_at`, `b200_log_joint_at`
+    `b200_gibbs`, `b200_slice`, `b200_pgibbs`, `b200_subsampled_mh`, `b200_log_likelihood_at`, `b200_log_joint_at`
     with the SP types of backend/lite/inference_sps.py:234-241, 253-267, 536-551, 602-606,
     678-694 (built with that module's own `sequenced_sp` / `transition_oper_type` /
     `infer_action_maker_type`), so `(b200_resimulation_mh default one 160)` is an
@@ -154,6 +154,10 @@ def inference_sps(plugin):
         "resimulation_mh": inf.sequenced_sp(transition("resimulation_mh"), inf.transition_oper_type()),
         "mh": inf.sequenced_sp(transition("resimulation_mh"), inf.transition_oper_type()),
         "gibbs": inf.sequenced_sp(transition("gibbs"), inf.transition_oper_type()),
+        # :500-516 (slice), :269-300 (pgibbs / func_pgibbs)
+        "slice": inf.sequenced_sp(transition("slice"), inf.transition_oper_type([t.NumberType("w : number"), t.IntegerType("m : int")])),
+        "pgibbs": inf.sequenced_sp(transition("pgibbs"), inf.par_transition_oper_type([t.IntegerType("particles : int")])),
+        "func_pgibbs": inf.sequenced_sp(transition("func_pgibbs"), inf.par_transition_oper_type([t.IntegerType("particles : int")])),
         # :678-694
         "subsampled_mh": inf.sequenced_sp(subsampled, inf.transition_oper_type(subsampled_extra)),
         # :536-551

@@ -220,6 +220,57 @@ p2p_gather_kernel(const int32_t *__restrict__ anc_g, int64_t n, const P2PTables 
     if (i < 0 || i >= n) { d = (int)(g / n); i = g - (int64_t)d * n; }
     return d;
   };
+  // Small state (every array particle-minor, or rows of at most 64 bytes in 16-byte units -- the HMM, the normal
+  // model, compiled programs): ONE THREAD PER CHILD SLOT copies everything that belongs to the slot; the ancestor is
+  // waited for and decoded once per slot instead of once per unit of every array.
+  bool slot_major = true;
+  for (int a = 0; a < arrs.n; ++a)
+    if (arrs.elem_bytes[a] == 0 && ((arrs.row_bytes[a] & 15) != 0 || arrs.row_bytes[a] > 64)) slot_major = false;
+  if (slot_major && !failed) {
+    for (int64_t s = tid0; s < n; s += stride) {
+      const int64_t g = p2p_wait_ancestor(anc_g, s, par, arrs.timeout_ns, arrs.err_host);
+      if (g < 0) { failed = true; break; }
+      int64_t i;
+      const int d = owner(g, i);
+      for (int a = 0; a < arrs.n; ++a) {
+        if (arrs.elem_bytes[a] == 0) {
+          const long long rb = arrs.row_bytes[a];
+          const int units = (int)(rb >> 4);
+          const uint4 *src = (const uint4 *)(live_sh[a][d] + i * rb);
+          uint4 *dst = (uint4 *)(arrs.alt[a] + s * rb);
+          uint4 v[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) if (u < units) v[u] = src[u];
+          if (a == arrs.patch_array) {
+            const uint32_t sv = ((const uint32_t *)live_sh[arrs.patch_src][d])[i] & 0xFFu;
+            const int pu = arrs.patch_byte >> 4, pw = (arrs.patch_byte >> 2) & 3, psh = (arrs.patch_byte & 3) * 8;
+            const uint32_t keep = ~(0xFFu << psh), ins = sv << psh;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              if (u == pu) {
+                if (pw == 0) v[u].x = (v[u].x & keep) | ins;
+                else if (pw == 1) v[u].y = (v[u].y & keep) | ins;
+                else if (pw == 2) v[u].z = (v[u].z & keep) | ins;
+                else v[u].w = (v[u].w & keep) | ins;
+              }
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) if (u < units) dst[u] = v[u];
+        } else {
+          const long long nr = arrs.n_rows[a];
+          const int eb = arrs.elem_bytes[a];
+          for (long long r = 0; r < nr; ++r) {
+            const unsigned char *src = live_sh[a][d] + (r * n + i) * eb;
+            unsigned char *dst = arrs.alt[a] + (r * n + s) * eb;
+            if (eb == 8) *(uint64_t *)dst = *(const uint64_t *)src;
+            else if (eb == 4) *(uint32_t *)dst = *(const uint32_t *)src;
+            else for (int e = 0; e < eb; ++e) dst[e] = src[e];
+          }
+        }
+      }
+    }
+  } else
   for (int a = 0; a < arrs.n && !failed; ++a) {
     if (arrs.elem_bytes[a] == 0) {
       const long long rb = arrs.row_bytes[a];
@@ -482,6 +533,10 @@ void p2p_resample(vk_particles *h, int mode) {
                                     : ((arrs[a].row_bytes & 15) == 0 ? P * (int64_t)(arrs[a].row_bytes >> 4) : P * (int64_t)arrs[a].row_bytes);
     work = wa > work ? wa : work;
   }
+  bool slot_major = true;
+  for (int a = 0; a < s->n_arrays; ++a)
+    if (arrs[a].elem_bytes == 0 && ((arrs[a].row_bytes & 15) != 0 || arrs[a].row_bytes > 64)) slot_major = false;
+  if (slot_major) work = P;
   p2p_gather_kernel<<<grid_for(work, 256, h->sm_count, 8), 256, 0, st>>>(s->anc_g.p + (int64_t)half * P, P, s->tab.p,
                                                                          s->par.p, pa);
   h->prof.mark(st, "p2p_gather");

@@ -104,10 +104,14 @@ int vk_create_normal_normal(int64_t n_particles, uint64_t seed, int device,
  *             per site: SIM, CHILD, OWN section, number of observation groups below it;
  *             the sites' group lists; per group: prologue section, row section, rows,
  *             columns (literals + observed value), offset into data; per section: first
- *             instruction, count
+ *             instruction, count; per site, for subsampled MH (infer/subsampled_mh.py:326-368):
+ *             kind (0 no global border, 1 border found, 2 refused), number of local sections,
+ *             offset into the section list; the local sections as pairs (group, row) |
+ *             (-1, child site), in the order of the border node's children
  *   data      the groups' tables, row-major
- *   affected  per site: Scaffold.numAffectedNodes (scaffold.py:67-68), what
- *             resimulation_mh reports (dispatch.py:109-120)
+ *   affected  2 * n_sites doubles.  Per site: Scaffold.numAffectedNodes (scaffold.py:67-68), what
+ *             resimulation_mh reports (dispatch.py:109-120); then per site the same count for the
+ *             scaffold cut at the global border, what subsampled_mh reports
  * Every index is validated here; the kernels do not re-check. */
 int vk_create_program(int64_t n_particles, uint64_t seed, int device, const int32_t *code,
                       int64_t n_code, const double *consts, int64_t n_consts,
@@ -270,19 +274,27 @@ int vk_slice(vk_particles *h, int32_t scope, int32_t block, double w, double m, 
 int vk_gibbs(vk_particles *h, int32_t scope, int32_t block, int32_t transitions,
              double *mean_nodes_out_host, int64_t *changed_out_host);
 
-/* infer/subsampled_mh.py:76-171 (BLR model only).  stats_out_host: NULL or
- * 3*P doubles per call = (accepted transitions, mean local sections visited
- * per transition, last t statistic).
- * One cooperative, persistent kernel runs every transition of the call (proposal, minibatch rounds,
- * sequential tests, accept) on the device (csrc/blr_subsampled_persistent.cuh; D <= 32, P <= 4096 -- larger
+/* `(subsampled_mh scope block Nbatch k0 epsilon useDeltaKernels deltaKernelArgs updateValues transitions)`:
+ * infer/dispatch.py:149-152, 315-322 -> infer/subsampled_mh.py:76-171 (subsampledMixMH, sequentialTest).
+ * mean_nodes_out_host: NULL or P doubles = transloop's return value, the nodes of the scaffold cut at the global
+ * border (logistic regression: 3).  stats_out_host: NULL or 3*P doubles per call = (accepted transitions, mean local
+ * sections visited per transition, t statistic of the last sequential test, +-inf when it computed none, :170).
+ * Logistic regression: one cooperative, persistent kernel runs every transition of the call (proposal, minibatch
+ * rounds, sequential tests, accept) on the device (csrc/blr_subsampled_persistent.cuh; D <= 32, P <= 4096 -- larger
  * D runs the host-driven round loop).  With observations sharded over peer GPUs
  * (vk_blr_set_observation_shard + vk_p2p_open on replicated particles) the same call exchanges the
- * per-particle partial sums through peer memory and every rank takes identical decisions. */
+ * per-particle partial sums through peer memory and every rank takes identical decisions.
+ * Compiled programs (vk_create_program): the compiler finds each site's global border and local sections
+ * (findGlobalBorder :326-368) -- rows of observation groups and latent children; a site without a border takes a
+ * regular MH step (:91-95); a site whose structure the reference rejects (SubsampledScaffoldError, "Invalid global
+ * border") or mis-handles (overlapping local sections) answers VK_EUNSUPPORTED.  Sections are evaluated from the
+ * current values (no per-section cache): the reference followed by its makeConsistent (:411-441).  block: one or a
+ * site index.  The other model kinds answer VK_EUNSUPPORTED. */
 int vk_subsampled_mh(vk_particles *h, int32_t scope, int32_t block,
                      int64_t Nbatch, int32_t k0, double epsilon,
                      int32_t use_delta_kernels, double delta_sigma,
                      int32_t update_values, int32_t transitions,
-                     double *stats_out_host);
+                     double *mean_nodes_out_host, double *stats_out_host);
 
 /* infer/dispatch.py:331-361 -- non-mutating. out_host: P doubles. */
 int vk_log_likelihood_at(vk_particles *h, int32_t scope, int32_t block,

@@ -53,6 +53,10 @@ class VM(object):
         self.group = [m[at + 5 * g: at + 5 * g + 5] for g in range(self.G)]
         at += 5 * self.G
         self.dir = [(m[at + 2 * s], m[at + 2 * s + 1]) for s in range(self.n_sec)]
+        at += 2 * self.n_sec
+        self.ss = [m[at + 3 * k: at + 3 * k + 3] for k in range(self.S)]          # kind, N, offset into the roots
+        at += 3 * self.S
+        self.roots = [(m[at + 2 * i], m[at + 2 * i + 1]) for i in range((len(m) - at) // 2)]
         self.sites = np.zeros((self.S, P))
         self.lw = np.zeros(P)
         self.step = 0
@@ -228,3 +232,104 @@ class VM(object):
                 self.sites[k, p] = x1
                 nodes[p] += self.affected[k]
         return nodes / max(n_steps, 1)
+
+    def subsampled_mh(self, n_steps, Nbatch, k0, eps, block=-1):
+        """subsampledMixMH + sequentialTest (infer/subsampled_mh.py:76-171) for a compiled program: draw 0 block choice,
+        draw 1 the accept uniform, then the proposal; the minibatch order is the Feistel permutation of (seed, step)
+        (the stand-in behind np_rng.permutation in tests/golden/make_program_chains.py); q = scipy.stats.t.cdf as in
+        the reference.  Returns (accepted, mean sections visited, last t statistic, mean node counts) per particle."""
+        import ctypes
+        step0, self.step = self.step, self.step + n_steps
+        acc, visited, tlast, nodes = np.zeros(self.P), np.zeros(self.P), np.zeros(self.P), np.zeros(self.P)
+        for t in range(n_steps):
+            perms = {}
+            for p in range(self.P):
+                u = oracle.uniforms(self.seed, self.p_base + p, step0 + t, 2)
+                k = min(int(u[0] * self.S), self.S - 1) if block == -1 else (t % self.S if block == -3 else block)
+                kind, N, off = self.ss[k]
+                if kind == 2:
+                    raise ValueError("subsampled_mh: site %d has no valid global border" % k)
+                logu = math.log(u[1])
+                nodes[p] += self.affected[self.S + k]
+                old = float(self.sites[k, p])
+                if kind == 0:                                   # no local sections: regular MH (:91-95)
+                    R = [0.0] * self.n_regs
+                    rho = self.children(k, R, p)
+                    self.run(self.site[k][0], R, p, tape=self._tape(p, step0 + t, 2))
+                    xi = self.children(k, R, p)
+                    with np.errstate(invalid="ignore"):
+                        alpha = np.float64(xi) - np.float64(rho)
+                    if alpha > logu:
+                        acc[p] += 1
+                    else:
+                        self.sites[k, p] = old
+                    continue
+                Rold, Rnew = [0.0] * self.n_regs, [0.0] * self.n_regs
+                for g in self.site_groups[k]:
+                    self.run(self.group[g][0], Rold, p)
+                self.run(self.site[k][0], Rnew, p, tape=self._tape(p, step0 + t, 2))
+                new = float(self.sites[k, p])
+                for g in self.site_groups[k]:
+                    self.run(self.group[g][0], Rnew, p)
+                if N not in perms:
+                    perm = np.empty(N, dtype=np.uint64)
+                    oracle.lib().orc_feistel_perm(ctypes.c_uint64(self.seed), ctypes.c_uint32(step0 + t), ctypes.c_uint64(N),
+                                                  perm.ctypes.data_as(ctypes.c_void_p))
+                    perms[N] = perm
+                perm = perms[N]
+
+                def dllh(q):
+                    g, r = self.roots[off + int(perm[q])]
+                    if g >= 0:
+                        _, row_sec, _, n_cols, doff = self.group[g]
+                        row = self.data[doff + r * n_cols: doff + (r + 1) * n_cols]
+                        return self.run(row_sec, Rnew, p, row=row) - self.run(row_sec, Rold, p, row=row)
+                    self.sites[k, p] = old
+                    lo = self.run(self.site[r][2], [0.0] * self.n_regs, p)
+                    self.sites[k, p] = new
+                    return self.run(self.site[r][2], [0.0] * self.n_regs, p) - lo
+                accept, n, ts = sequential_test((logu - 0.0) / float(N), k0, Nbatch, N, eps, dllh)
+                visited[p] += n
+                if ts is not None:
+                    tlast[p] = ts
+                if accept:
+                    acc[p] += 1
+                else:
+                    self.sites[k, p] = old
+        return acc, visited / max(n_steps, 1), tlast, nodes / max(n_steps, 1)
+
+
+def sequential_test(mu_0, k0, Nbatch, N, epsilon, fun_dllh):
+    """infer/subsampled_mh.py:118-171 (returns the raw t statistic, None when none was computed)"""
+    Nbatch, N = float(Nbatch), float(N)
+    k = n = 0.0
+    cum = cum2 = 0.0
+    tstat = accept = None
+    while n < N:
+        n_end = min(n + Nbatch, N)
+        for i in range(int(n), int(n_end)):
+            d = fun_dllh(i)
+            cum += d
+            cum2 += d * d
+        k += 1
+        n = n_end
+        mx, mx2 = cum / n_end, cum2 / n_end
+        if k < k0 and n < N:
+            continue
+        if n == N:
+            accept = mx >= mu_0
+            break
+        with np.errstate(invalid="ignore", divide="ignore"):
+            sx = np.sqrt((1 - (n - 1) / (N - 1)) * (mx2 - mx * mx) / (n - 1))
+        if sx == 0:
+            q = 1 if mx >= mu_0 else 0
+        else:
+            tstat = (mx - mu_0) / sx
+            q = scipy.stats.t.cdf(tstat, n - 1)
+        if q < epsilon:
+            accept = False
+            break
+        elif q > 1 - epsilon:
+            accept = True
+            break
+    return bool(accept), n, tstat

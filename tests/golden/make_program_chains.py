@@ -47,7 +47,22 @@ def programs():
     chain = [("assume", "mu", ["normal", 1.0, 3.0]), ("assume", "x1", ["normal", "mu", 1.5]), ("assume", "x2", ["normal", "mu", 1.5]),
              ("observe", ["normal", "x1", 0.5], 2.1), ("observe", ["normal", "x2", 0.5], 0.3),
              ("observe", ["log_odds_flip", ["sub", "x1", "x2"]], True)]
-    return {"regression": regression, "coin": coin, "hierarchy": hier, "regression2": regression2, "chain": chain}
+    # subsampled MH: the reference's own pin model (test/inference_language/test_subsampledmh.py:87-99), smaller
+    obs = np.round(rng.normal(10.0, 1.0, size=40), 3).tolist()
+    normal_observes = [("assume", "mu", ["normal", 10.0, 3.0])] + [("observe", ["normal", "mu", 1.0], x) for x in obs]
+    # border below the principal node (mu -> lookup -> mul = z), a latent child among the local sections, a second
+    # site whose border is itself (s), and one without a border (lo: regular MH inside subsampledMixMH)
+    cs = np.round(rng.normal(size=24), 2).tolist()
+    zs = np.round(2.0 * 1.3 + np.array(cs) + 0.8 * rng.normal(size=24), 3).tolist()
+    scaled = [("assume", "mu", ["normal", 1.0, 2.0]), ("assume", "s", ["gamma", 3.0, 3.0]),
+              ("assume", "lo", ["uniform_continuous", -1.0, 1.0]),
+              ("assume", "z", ["mul", 2.0, "mu"]), ("assume", "x", ["normal", "z", 1.5]),
+              ("observe", ["normal", ["add", "lo", 0.3], 0.7], 0.2)] + \
+             [("observe", ["normal", ["add", "z", c], "s"], v) for c, v in zip(cs, zs)]
+    invalid = [("assume", "mu", ["normal", 0.0, 1.0]), ("assume", "x", ["normal", "mu", 1.0]),
+               ("observe", ["normal", "x", 1.0], 0.5), ("observe", ["normal", "x", 1.0], 0.7)]
+    return {"regression": regression, "coin": coin, "hierarchy": hier, "regression2": regression2, "chain": chain,
+            "normal_observes": normal_observes, "scaled": scaled, "invalid_border": invalid}
 
 
 def box(v):
@@ -114,6 +129,71 @@ def run_slice(prog, seed, P, K, w, m):
     return out
 
 
+def run_subsampled(prog, seed, P, K, Nbatch, k0, eps, block="one", make_consistent=False):
+    """(subsampled_mh default <block> Nbatch k0 eps false 0 false 1) K times on Lite (infer/subsampled_mh.py), np_rng.permutation
+    standing in as the kernels' Feistel permutation of (seed, step); records sequentialTest's own return values.
+    make_consistent: SubsampledMHOperator().makeConsistent over every block (what `subsampled_mh_make_consistent default one`
+    is meant to run; its dispatch entry, infer/dispatch.py:158-161, reads an unbound `extra`) after every transition -- an accepted
+    proposal leaves the unvisited local sections stale in Lite (:57-72), and ANOTHER site's transition would then read
+    stale parents; the device keeps no per-section cache, i.e. it is Lite with the sections made consistent."""
+    import ctypes
+    import oracle
+    import venture.lite.infer.subsampled_mh as ss
+    out = {"seed": seed, "P": P, "K": K, "Nbatch": Nbatch, "k0": k0, "eps": eps, "block": block,
+           "program": [list(d) for d in prog], "steps": {"prior": 0, "ssmh": 9}, "particles": []}
+    assumes = [d for d in prog if d[0] == "assume"]
+    observes = [d for d in prog if d[0] == "observe"]
+    tests = []
+    orig = ss.sequentialTest
+
+    def recording(*a):
+        r = orig(*a)
+        tests.append(r)
+        return r
+    ss.sequentialTest = recording
+    for p in range(P):
+        mdl = Model()
+        install(mdl, seed, p)
+        mdl.tape.begin(0, 0)
+        dids = [mdl.assume(d[1], d[2]) for d in assumes]
+        for d in observes:
+            mdl.observe(d[1], box(d[2]))
+        mdl.t.makeConsistent()
+        random_dids = [did for did, d in zip(dids, assumes) if mdl.t.families[did] in mdl.t.rcs]
+        nodes = [mdl.t.families[did] for did in random_dids]
+        tape = mdl.tape
+        tape.site_of = lambda key: [i for i, n in enumerate(nodes) if n is key][0]
+
+        def permutation(items, tape=tape):
+            n = len(items)
+            perm = np.empty(n, dtype=np.uint64)
+            oracle.lib().orc_feistel_perm(ctypes.c_uint64(tape.seed), ctypes.c_uint32(tape.step), ctypes.c_uint64(n),
+                                          perm.ctypes.data_as(ctypes.c_void_p))
+            return [items[int(q)] for q in perm]
+        mdl.t.np_rng.permutation = permutation
+        rec = {"values_prior": [fl(mdl.value(did)) for did in random_dids]}
+        del tests[:]
+        from make_lite_chains import infer_exp
+        rec["nodes"] = []
+        try:
+            for k in range(K):
+                mdl.tape.begin(9 + k, 2)
+                rec["nodes"].append(mdl.t.primitive_infer(infer_exp("subsampled_mh", "default", block, Nbatch, k0, eps, False, 0, False, 1)))
+                if make_consistent:
+                    sc, blk = mdl.t._normalizeEvaluatedScopeAndBlock(vv.VentureSymbol("default"), vv.VentureSymbol("one"))
+                    ss.SubsampledMHOperator().makeConsistent(mdl.t, ss.SubsampledBlockScaffoldIndexer(
+                        sc, blk, useDeltaKernels=False, deltaKernelArgs=0, updateValues=False))
+        except ss.SubsampledScaffoldError as e:
+            rec["error"] = str(e)
+        rec["accept"] = [bool(t[0]) for t in tests]
+        rec["n"] = [float(t[1]) for t in tests]
+        rec["tstat"] = [fl(t[2]) for t in tests]
+        rec["values"] = [fl(mdl.value(did)) for did in random_dids]
+        out["particles"].append(rec)
+    ss.sequentialTest = orig
+    return out
+
+
 def main():
     fixture = {}
     progs = programs()
@@ -122,6 +202,9 @@ def main():
     fixture["hierarchy"] = run("hierarchy", progs["hierarchy"], 31, 5, 60, 3)
     fixture["regression_slice"] = run_slice(progs["regression2"], 37, 4, 30, 0.7, 8)
     fixture["chain_slice"] = run_slice(progs["chain"], 41, 4, 40, 1.3, 5)
+    fixture["normal_observes_ssmh"] = run_subsampled(progs["normal_observes"], 43, 5, 40, 5, 2, 0.05)
+    fixture["scaled_ssmh"] = run_subsampled(progs["scaled"], 47, 5, 60, 4, 2, 0.1, make_consistent=True)
+    fixture["invalid_border_ssmh"] = run_subsampled(progs["invalid_border"], 53, 2, 8, 1, 1, 0.1)
     fixture["_source"] = ("reference Lite backend (py3 rendering by oracle/lite_py3/build_lite_py3.py) run by "
                           "tests/golden/make_program_chains.py; numpy %s" % np.__version__)
     path = os.path.join(HERE, "program_chains.json")

@@ -202,3 +202,92 @@ def test_compiled_particles_restore_into_lite():
         lite = tr.Trace.restore(lambda: Trace(1), ts.dump_particle(i), {})
         got = lite.trace.log_joint_at(vv.VentureSymbol("default"), vv.VentureSymbol("all"))
         assert abs(got - lj[i]) <= 1e-12 * abs(lj[i])
+
+
+@pytest.mark.parametrize("name", ["normal_observes_ssmh", "scaled_ssmh"])
+def test_compiled_subsampled_mh_reproduces_lite_on_the_device(name):
+    """`(subsampled_mh default one Nbatch k0 eps false 0 false 1)` x K on the device against Lite's subsampledMixMH /
+    sequentialTest (infer/subsampled_mh.py:76-171) on the same draws and the same order of local sections: every
+    decision, the sections each test visited, its t statistic, the node counts, the final values"""
+    case = golden("program_chains.json")[name]
+    recs = case["particles"]
+    ts = vb.B200TraceSet(CompiledModel([tuple(d) for d in case["program"]]), case["P"], seed=case["seed"])
+    ts.rng_step = case["steps"]["prior"]
+    ts.reset_to_prior()
+    ts.incorporate()
+    np.testing.assert_allclose(sites_of(ts).T, [[unj(v) for v in r["values_prior"]] for r in recs], rtol=RTOL)
+    ts.rng_step = case["steps"]["ssmh"]
+    acc, visited, tstat, nodes = [], [], [], []
+    for _ in range(case["K"]):
+        st_ = ts.primitive_infer(["subsampled_mh", "default", "one", case["Nbatch"], case["k0"], case["eps"], False, 0, False, 1])
+        acc.append(st_[:, 0]), visited.append(st_[:, 1]), tstat.append(st_[:, 2]), nodes.append(ts.last_mean_nodes)
+    acc, visited, tstat, nodes = [np.array(a).T for a in (acc, visited, tstat, nodes)]
+    for p, r in enumerate(recs):
+        with_border = visited[p] > 0
+        np.testing.assert_array_equal(visited[p][with_border], r["n"])
+        np.testing.assert_array_equal(acc[p][with_border] > 0, r["accept"])
+        np.testing.assert_allclose(tstat[p][with_border], [unj(v) for v in r["tstat"]], rtol=1e-9)
+        np.testing.assert_array_equal(nodes[p], r["nodes"])
+    np.testing.assert_allclose(sites_of(ts).T, [[unj(v) for v in r["values"]] for r in recs], rtol=RTOL)
+    assert ts.rng_step == case["steps"]["ssmh"] + case["K"]
+
+
+def test_compiled_subsampled_mh_refuses_what_lite_rejects():
+    bad = golden("program_chains.json")["invalid_border_ssmh"]
+    ts = vb.B200TraceSet(CompiledModel([tuple(d) for d in bad["program"]]), 4, seed=1)
+    ts.reset_to_prior()
+    ts.incorporate()
+    with pytest.raises(vb.VentureException) as e:
+        ts.subsampled_mh("default", "one", 1, 1, 0.1, False, 0, False, 3)
+    assert "Invalid global border" in str(e.value)
+    ts.subsampled_mh("default", 1, 1, 1, 0.1, False, 0, False, 3)          # x alone has a valid border (itself)
+
+
+def normal_with_observes(N, sigma, seed):
+    """setupNormalWithObserves, test/inference_language/test_subsampledmh.py:87-99"""
+    x = np.random.RandomState(seed).normal(10, 1, N)
+    prog = [("assume", "mu", ["normal", 10.0, sigma])] + [("observe", ["normal", "mu", 1.0], float(v)) for v in x]
+    sigma2 = sigma ** 2
+    post_mean = (sigma2 * x.sum() + 10.0) / (sigma2 * N + 1.0)
+    post_std = np.sqrt(sigma2 / (sigma2 * N + 1.0))
+    return prog, post_mean, post_std
+
+
+@pytest.mark.parametrize("warp", [False, True])
+def test_normal_with_observes_posterior(warp):
+    """The reference's own statistical pin of subsampled MH (testNormalWithObserves1,
+    test/inference_language/test_subsampledmh.py:64-72): `(subsampled_mh default one 2 3 0.01 false 0 false 50)`,
+    the samples of mu against N(post_mean, post_std^2) by reportKnownContinuous under the policy of test/stats.py.
+    warp: 100 observations run one warp per particle (>= 64 rows), 40 one thread per particle."""
+    from stats_policy import report_known_continuous, statistical_test
+
+    @statistical_test
+    def check(seed):
+        prog, mean, std = normal_with_observes(100 if warp else 40, 3.0, 11)
+        # collectSamples continues ONE chain, 50 transitions between samples; here 200 independent chains run the same
+        # command 12 times from the prior (prior proposals are accepted about 3 % of the time: 50 transitions are no burn-in)
+        ts = vb.B200TraceSet(CompiledModel(prog), 200, seed=seed)
+        ts.reset_to_prior()
+        ts.incorporate()
+        for _ in range(12):
+            ts.subsampled_mh("default", "one", 2, 3, 0.01, False, 0, False, 50)
+        return report_known_continuous(st.norm(loc=mean, scale=std).cdf, ts.read_site(0), "N(%f,%f^2)" % (mean, std))
+    check()
+
+
+def test_compiled_subsampled_mh_with_epsilon_zero_is_exact_mh():
+    """epsilon = 0: every local section is visited and the decision is the exact MH one (subsampled_mh.py:66-68):
+    the chain equals resimulation_mh's on the same draws"""
+    prog, _, _ = normal_with_observes(80, 3.0, 5)
+    a = vb.B200TraceSet(CompiledModel(prog), 64, seed=9)
+    b = vb.B200TraceSet(CompiledModel(prog), 64, seed=9)
+    for ts in (a, b):
+        ts.rng_step = 0
+        ts.reset_to_prior()
+        ts.incorporate()
+        ts.rng_step = 100
+    st_ = a.subsampled_mh("default", "one", 7, 2, 0.0, False, 0, False, 30)
+    _, acc = b.resimulation_mh("default", "one", 30, return_accepts=True)
+    np.testing.assert_array_equal(st_[:, 0], acc)
+    np.testing.assert_array_equal(st_[:, 1], 80.0)
+    np.testing.assert_allclose(a.read_site(0), b.read_site(0), rtol=1e-15)

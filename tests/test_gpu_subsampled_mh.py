@@ -63,7 +63,7 @@ def test_drift_kernel_extension_matches_oracle():
     step0 = ts.rng_step
     from venturecxx_b200 import _lib
     st = np.empty((P, 3))
-    _lib.call("vk_subsampled_mh", ts._h, 0, _lib.BLOCK_ONE, 50, 3, 0.05, 2, 0.3, 0, 40, _lib.ptr(st))
+    _lib.call("vk_subsampled_mh", ts._h, 0, _lib.BLOCK_ONE, 50, 3, 0.05, 2, 0.3, 0, 40, None, _lib.ptr(st))
     w_ref, st_ref = orc_ssmh(w0, X, y, 62, step0, 40, -1, 50, 3, 0.05, delta_mode=2, delta_eps=0.3)
     np.testing.assert_allclose(read_w(ts, D), w_ref, rtol=1e-12)
     np.testing.assert_array_equal(st[:, 0], st_ref[:, 0])

@@ -70,6 +70,54 @@ def test_compiled_slice_reproduces_lite(name):
     np.testing.assert_allclose(vm.log_likelihood(joint=True), [unj(r["lj_at"]) for r in recs], rtol=1e-11)
 
 
+@pytest.mark.parametrize("name", ["normal_observes_ssmh", "scaled_ssmh"])
+def test_compiled_subsampled_mh_reproduces_lite(name):
+    """(subsampled_mh default one Nbatch k0 eps false 0 false 1) x K on Lite (infer/subsampled_mh.py:76-171, 326-455) vs the
+    compiled program: the global border and the order of the local sections, every sequential test's decision, the
+    number of sections it visited and its t statistic, the node counts of the cut scaffold"""
+    case = golden("program_chains.json")[name]
+    m = CompiledModel([tuple(d) for d in case["program"]])
+    recs = case["particles"]
+    vm = VM(m.prog.blob(), compiler.OP, case["P"], case["seed"])
+    vm.step = case["steps"]["prior"]
+    vm.reset_to_prior()
+    np.testing.assert_allclose(vm.sites.T, [[unj(v) for v in r["values_prior"]] for r in recs], rtol=RTOL)
+    vm.step = case["steps"]["ssmh"]
+    accs, visited, nodes = [], [], []
+    for _ in range(case["K"]):
+        a, n, _, nd = vm.subsampled_mh(1, case["Nbatch"], case["k0"], case["eps"])
+        accs.append(a), visited.append(n), nodes.append(nd)
+    accs, visited, nodes = np.array(accs).T, np.array(visited).T, np.array(nodes).T
+    for p, r in enumerate(recs):
+        # sequentialTest ran only in the transitions whose site has a border: those report its n, the others 0
+        with_border = visited[p] > 0
+        assert with_border.sum() == len(r["n"])
+        np.testing.assert_array_equal(visited[p][with_border], r["n"])
+        np.testing.assert_array_equal(accs[p][with_border] > 0, r["accept"])
+        np.testing.assert_array_equal(nodes[p], r["nodes"])
+    np.testing.assert_allclose(vm.sites.T, [[unj(v) for v in r["values"]] for r in recs], rtol=RTOL)
+
+
+def test_global_border_rules():
+    """findGlobalBorder (infer/subsampled_mh.py:326-368) on the compiler's graph"""
+    case = golden("program_chains.json")
+    ss = CompiledModel([tuple(d) for d in case["scaled_ssmh"]["program"]]).prog.subsampled
+    # mu: border = z (the mul), local sections = the latent child x, then the 24 observations; s: its own border;
+    # lo and x: one consumer / none -> regular MH
+    assert [s["kind"] for s in ss] == [1, 1, 0, 0]
+    assert ss[0]["roots"] == [(-1, 3)] + [(1, r) for r in range(24)] and ss[0]["nodes"] == 3.0
+    assert ss[1]["roots"] == [(1, r) for r in range(24)] and ss[1]["nodes"] == 1.0
+    # Lite raises SubsampledScaffoldError("Invalid global border.") when the walk passes a random choice (:177-180)
+    bad = case["invalid_border_ssmh"]
+    assert all("Invalid global border" in r["error"] for r in bad["particles"])
+    ss = CompiledModel([tuple(d) for d in bad["program"]]).prog.subsampled
+    assert ss[0]["kind"] == 2 and "Invalid global border" in ss[0]["reason"] and ss[1]["kind"] == 1
+    # an observation that reads the principal node twice: the two local sections would share its nodes
+    ss = CompiledModel([("assume", "mu", ["normal", 0, 1]), ("observe", ["normal", ["mul", "mu", "mu"], 1.0], 0.5),
+                        ("observe", ["normal", ["mul", "mu", "mu"], 1.0], 0.7)]).prog.subsampled
+    assert ss[0]["kind"] == 2 and "overlap" in ss[0]["reason"]
+
+
 def test_node_counts_follow_the_scaffold_rules():
     # scaffold.py:201-218: the site, lookups of resampled nodes, deterministic applications downstream; a variadic
     # add is ONE application; an assume referenced by symbol is ONE node with one lookup per reference
@@ -90,8 +138,10 @@ def test_blob_is_self_consistent():
     code, consts, meta, data, affected = m.prog.blob()
     assert code.dtype == np.int32 and code.size % compiler.INSTR_WORDS == 0 and meta.dtype == np.int32
     S, G, n_regs, n_sec = [int(v) for v in meta[:4]]
-    assert S == 5 and len(affected) == S and n_regs <= compiler.MAX_REGS
-    directory = meta[-2 * n_sec:].reshape(n_sec, 2)
+    assert S == 5 and len(affected) == 2 * S and n_regs <= compiler.MAX_REGS     # regular scaffolds, then the global sections
+    n_roots = sum(len(ss["roots"]) for ss in m.prog.subsampled)
+    tail = 3 * S + 2 * n_roots                                                    # the subsampled-MH block closes the meta words
+    directory = meta[-tail - 2 * n_sec: -tail].reshape(n_sec, 2)
     assert directory[:, 1].sum() == code.size // compiler.INSTR_WORDS
     ops = set(code.reshape(-1, compiler.INSTR_WORDS)[:, 0].tolist())
     assert ops <= set(compiler.OP.values())

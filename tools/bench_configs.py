@@ -376,7 +376,7 @@ def c5(ctx, N=10 ** 7, P=64, K=100, Nbatch=65536, k0=3, eps=0.01, cpu=False, che
         ts.incorporate(return_increments=False)
     from venturecxx_b200 import _lib
     run = lambda k, out=None: _lib.call("vk_subsampled_mh", ts._h, 0, _lib.BLOCK_ONE, int(Nbatch), int(k0), float(eps), 0, 0.0, 0,
-                                        int(k), _lib.ptr(out))
+                                        int(k), None, _lib.ptr(out))
     ts.rng_step = 1000
     run(3)
     ts.synchronize()

@@ -317,7 +317,11 @@ class B200Trace(object):
     def primitive_infer(self, exp):
         """exp = [operator, scope, block, ...extra..., transitions] of VentureValues / stack dicts / python values
         (backend/lite/infer/dispatch.py:50-107)."""
-        return PerParticle(np.asarray(self.ts.primitive_infer([_infer_arg(e) for e in exp]))[..., None].reshape(self.n_particles, -1)[:, 0].tolist())
+        args = [_infer_arg(e) for e in exp]
+        out = np.asarray(self.ts.primitive_infer(args))
+        if args and args[0] == "subsampled_mh" and getattr(self.ts, "last_mean_nodes", None) is not None:
+            out = np.asarray(self.ts.last_mean_nodes)       # the engine gets what Lite returns: node counts, not the test statistics
+        return PerParticle(out[..., None].reshape(self.n_particles, -1)[:, 0].tolist())
 
     def log_likelihood_at(self, scope, block):
         return PerParticle(self.ts.log_likelihood_at(_infer_arg(scope), _infer_arg(block)).tolist())

@@ -119,6 +119,11 @@ class Compiler(object):
         self.group_list = []
         self.directives = []   # the program, for interchange
         self.directive_sites = []   # per directive: the sites its evaluation creates (none for observes)
+        # Lite's child lists, for findGlobalBorder (infer/subsampled_mh.py:326-368): node -> its consumers in
+        # creation order, [consumer node, through a lookup node?, group or None, row]
+        self.uses = {}
+        self.aliased = set()   # nodes some `(assume y x)` renames: their lookups hang off the alias, not off the node
+        self._template_uses = None
 
     # -- building the node graph -------------------------------------------------------------------------
     def _new(self, node):
@@ -150,6 +155,7 @@ class Compiler(object):
         if head in self.env:
             raise VentureException("invalid_argument", "procedure application (%s ...) is outside the fixed-structure subset" % (head,))
         args = [self._expr(a, holes) for a in e[1:]]
+        via = [isinstance(a, str) for a in e[1:]]
         if head in DET:
             arity, op = DET[head]
             if arity == "fold":
@@ -159,17 +165,19 @@ class Compiler(object):
                 for i, a in enumerate(args[1:]):
                     acc = self._finish(Node("det", op, (acc, a)))
                     self.nodes[acc].counted = i == len(args) - 2
+                if len(args) > 1:
+                    self._record_uses(acc, args, via)        # ONE application node in Lite: every operand's consumer
                 return acc
             if len(args) != arity:
                 raise VentureException("invalid_argument", "%s takes %d argument(s)" % (head, arity))
-            return self._finish(Node("det", op, args))
+            return self._record_uses(self._finish(Node("det", op, args)), args, via)
         if head in RANDOM:
             arity, op = RANDOM[head]
             if op == "FLIP" and not args:
                 args = [self._new(Node("const", value=0.5))]           # (flip) = (flip 0.5), discrete.py:98-102
             if len(args) != arity:
                 raise VentureException("invalid_argument", "%s takes %d argument(s)" % (head, arity))
-            nid = self._finish(Node("random", op, args))
+            nid = self._record_uses(self._finish(Node("random", op, args)), args, via)
             if not observed_root:
                 if holes is not None:
                     raise VentureException("invalid_argument", "a latent random choice inside an observed expression is outside the fixed-structure subset")
@@ -178,6 +186,14 @@ class Compiler(object):
                 self.site_names.append(None)
             return nid
         raise VentureException("invalid_argument", "SP %r is outside the model compiler's subset" % (head,))
+
+    def _record_uses(self, consumer, args, via):
+        for a, lookup in zip(args, via):
+            use = [consumer, lookup, None, 0]
+            self.uses.setdefault(a, []).append(use)
+            if self._template_uses is not None:
+                self._template_uses.append((a, use))
+        return consumer
 
     def _finish(self, node):
         deps, rowvar = set(), False
@@ -201,6 +217,8 @@ class Compiler(object):
         n = self.nodes[nid]
         if not isinstance(exp, str) and n.kind == "random":
             self.site_names[n.site] = name          # (an alias's root is the lookup counted in _expr)
+        if isinstance(exp, str):
+            self.aliased.add(nid)
         self.env[name] = nid
         self.directives.append(interchange.define(name, exp))
         self.directive_sites.append(list(range(first, len(self.sites))))
@@ -217,9 +235,14 @@ class Compiler(object):
         if g is None:
             holes = []
             start = len(self.nodes)
+            self._template_uses = []
             root = self._expr_observed(exp, holes)
             g = Group(key, root, len(holes))
             g.own = range(start, len(self.nodes))      # the template's own nodes: one copy per observation in Lite
+            g.symbol_uses = [(a, use[0]) for a, use in self._template_uses if use[1]]
+            for _, use in self._template_uses:
+                use[2] = g
+            self._template_uses = None
             self.groups[key] = g
             self.group_list.append(g)
             g.rows.append(holes + [v])
@@ -228,6 +251,8 @@ class Compiler(object):
             self._literals(exp, lits)
             g.rows.append(lits + [v])
             self._count_template_lookups(exp)
+            for a, consumer in g.symbol_uses:          # this observation's own lookup nodes, in evaluation order
+                self.uses[a].append([consumer, True, g, len(g.rows) - 1])
         boolean = RANDOM[exp[0]][1] in BOOLEAN_VALUED
         self.directives.append(interchange.observe(exp, interchange.boolean(v != 0.0) if boolean else interchange.number(v)))
         self.directive_sites.append([])
@@ -235,11 +260,12 @@ class Compiler(object):
     def _expr_observed(self, exp, holes):
         arity, op = RANDOM[exp[0]]
         args = [self._expr(a, holes) for a in exp[1:]]
+        via = [isinstance(a, str) for a in exp[1:]]
         if op == "FLIP" and not args:
-            args = [self._new(Node("const", value=0.5))]
+            args, via = [self._new(Node("const", value=0.5))], [False]
         if len(args) != arity:
             raise VentureException("invalid_argument", "%s takes %d argument(s)" % (exp[0], arity))
-        return self._finish(Node("random", op, args))
+        return self._record_uses(self._finish(Node("random", op, args)), args, via)
 
     def _template_key(self, e):
         if isinstance(e, bool):
@@ -392,6 +418,86 @@ class Program(object):
                 if n.kind == "det" and k in n.deps:          # deps stop at random nodes: these are k's deterministic descendants
                     cnt += (own.get(nid, 1) if n.counted else 0) + n.lookups
             self.affected.append(float(cnt))
+        self.subsampled = [self._subsample_site(k) for k in range(S)]
+
+    # -- subsampled MH: the global border and the local sections of a site (infer/subsampled_mh.py:326-368, 186-211) --
+    def _subsample_site(self, k):
+        """-> dict(kind, reason, roots, nodes).  kind 0: no global border -- subsampledMixMH is regular MH (:91-95);
+        1: border found, roots = Lite's `trace.childrenAt(globalBorder[0])` in creation order, each one local
+        section given as (group, row) or (-1, child site); 2: a structure Lite rejects or mis-handles
+        (SubsampledScaffoldError / checkApplicability's NotApplicable warning) -- refused at the call.
+        nodes: numAffectedNodes of the scaffold cut at the border (hardBorder, scaffold.py:149-173)."""
+        c = self.c
+        nodes = c.nodes
+        plain = dict(kind=0, reason="", roots=[], nodes=self.affected[k])
+
+        def refuse(why):
+            return dict(kind=2, reason=why, roots=[], nodes=0.0)
+        n, count, random_on_path = c.sites[k], 1, False
+        while True:                                   # P -> single path -> the first node with several children
+            if n in c.aliased:
+                return refuse("an alias of a node between the principal node and its border is outside the compiled subset")
+            uses = c.uses.get(n, [])
+            if not uses:
+                return plain
+            if len(uses) > 1:
+                break
+            consumer, lookup = uses[0][0], uses[0][1]
+            count += 1 if lookup else 0
+            cn = nodes[consumer]
+            if cn.kind == "random":
+                if cn.site is None:
+                    return plain                      # an observed application: it absorbs and has no children
+                random_on_path = True
+            else:
+                count += 1
+            n = consumer
+        if random_on_path:                            # sampleGlobalIndex :177-180 raises: the border is not resampling
+            return refuse("Invalid global border (a random choice between the principal node and the border absorbs)")
+        border, roots, seen = n, [], set()
+        for consumer, lookup, g, row in c.uses[border]:
+            if g is not None:
+                if self._template_entries(g, k) != [border]:
+                    return refuse("local sections overlap: an observation reads the principal node along two paths")
+                roots.append((c.group_list.index(g), row))
+                continue
+            m = consumer
+            while nodes[m].kind == "det":             # the local section: deterministic applications down to one absorber
+                u = c.uses.get(m, [])
+                if len(u) != 1 or m in c.aliased or u[0][2] is not None:
+                    return refuse("a local section that fans out is outside the compiled subset")
+                m = u[0][0]
+            if nodes[m].site is None or m in seen:
+                return refuse("local sections overlap")
+            if k in nodes[m].deps and sum(1 for a in self._entries_of(m, k)) != 1:
+                return refuse("local sections overlap: a child reads the principal node along two paths")
+            seen.add(m)
+            roots.append((-1, nodes[m].site))
+        return dict(kind=1, reason="", roots=roots, nodes=float(count))
+
+    def _depends(self, a, k):
+        n = self.c.nodes[a]
+        return n.site == k if n.kind == "random" else k in n.deps
+
+    def _entries_of(self, root, k):
+        """the occurrences through which site k reaches random node `root`'s parameters (anonymous nodes expanded)"""
+        c = self.c
+        named = set(c.env.values())
+        out = []
+
+        def walk(nid):
+            for a in c.nodes[nid].args:
+                if not self._depends(a, k):
+                    continue
+                if a in named or c.nodes[a].kind == "random":
+                    out.append(a)
+                else:
+                    walk(a)
+        walk(root)
+        return out
+
+    def _template_entries(self, g, k):
+        return self._entries_of(g.root, k)
 
     def _invariant_frontier(self, root):
         """row-independent nodes a group's row program reads: computed once in the group prologue"""
@@ -438,9 +544,17 @@ class Program(object):
             data.append(rows.ravel())
             off += rows.size
         meta += directory
+        # subsampled MH: per site (kind, number of local sections, offset into the root table), then the roots as pairs
+        roots = []
+        for k in range(S):
+            ss = self.subsampled[k]
+            meta += [ss["kind"], len(ss["roots"]), len(roots) // 2]
+            for a, b in ss["roots"]:
+                roots += [a, b]
+        meta += roots
         return (np.asarray(code, dtype=np.int32), np.asarray(self._consts or [0.0], dtype=np.float64),
                 np.asarray(meta, dtype=np.int32), np.concatenate(data) if data else np.zeros(1),
-                np.asarray(self.affected, dtype=np.float64))
+                np.asarray(self.affected + [ss["nodes"] for ss in self.subsampled], dtype=np.float64))
 
 
 # ---- the model object B200TraceSet takes -----------------------------------------------------------------------

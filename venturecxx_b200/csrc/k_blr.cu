@@ -785,8 +785,10 @@ struct BLRModel : Model {
     return !off && prm.D <= 32 && h->P <= 4096 && coop_launch;
   }
   void subsampled_mh(int scope, int block, int64_t Nbatch, int k0, double eps, int use_delta, double delta_arg,
-                     int update_values, int K, double *stats_dev) override {
+                     int update_values, int K, double *mean_nodes_dev, double *stats_dev) override {
     VK_REQUIRE(scope == 0, VK_EINVAL, "blr: only the default scope exists");
+    // the scaffold cut at the global border: the weight, its lookup in `(array w_0 ...)`, the array (3 nodes)
+    if (mean_nodes_dev) blr_fill_const_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, K > 0 ? 3.0 : 0.0);
     VK_REQUIRE(block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || (block >= 0 && block < prm.D), VK_EINVAL, "blr: bad block");
     VK_REQUIRE(n_prop == prm.N, VK_ESTATE, "subsampled_mh: unpropagated observations; call vk_make_consistent first");
     VK_REQUIRE(eps >= 0.0 && eps < 0.5, VK_EINVAL, "subsampled_mh: epsilon must be in [0, 0.5)");

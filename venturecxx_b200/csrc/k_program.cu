@@ -24,6 +24,7 @@
 // The same interpreter restated on the CPU is the oracle (oracle/oracle.c orc_vm_*).
 #include "vk_common.cuh"
 #include "sp_math.cuh"
+#include "subsample_common.cuh"
 
 namespace vk {
 
@@ -50,19 +51,24 @@ struct VMProg {
   const int32_t *site_groups;
   const int32_t *group_tab;  // per group: prologue section, row section, rows, columns, data offset
   const double *affected;    // per site: nodes of Lite's scaffold (scaffold.py:67-68)
+  const int32_t *ss_tab;     // per site: kind (0 no border, 1 border, 2 refused), local sections, offset into ss_roots
+  const int32_t *ss_roots;   // pairs: (group, row) | (-1, child site), in the order of Lite's childrenAt(globalBorder)
+  const double *ss_nodes;    // per site: nodes of the scaffold cut at the global border
   int n_sites, n_groups, sec_prior, sec_joint;
 };
 
 // one straight-line section.  row: the current row of a group table (nullptr outside row programs).
+// ov_site / ov_val: read site ov_site as ov_val instead of from memory (the OLD value of a proposal in flight).
 __device__ __forceinline__ void vm_exec(const VMProg &pg, int section, double *R, double *sites, int64_t P, int64_t p,
-                                        const double *row, Stream *rng, double &acc, bool store) {
+                                        const double *row, Stream *rng, double &acc, bool store,
+                                        int ov_site = -1, double ov_val = 0.0) {
   const int first = __ldg(&pg.dir[2 * section]), n = __ldg(&pg.dir[2 * section + 1]);
   const int32_t *ip = pg.code + (size_t)first * VM_WORDS;
   for (int i = 0; i < n; ++i, ip += VM_WORDS) {
     const int op = __ldg(ip), d = __ldg(ip + 1), a = __ldg(ip + 2), b = __ldg(ip + 3);   // (one int4 load measured 20 % slower)
     switch (op) {
       case VM_CONST: R[d] = __ldg(&pg.consts[a]); break;
-      case VM_SITE: R[d] = sites[(int64_t)a * P + p]; break;
+      case VM_SITE: R[d] = a == ov_site ? ov_val : sites[(int64_t)a * P + p]; break;
       case VM_DATA: R[d] = __ldg(&row[a]); break;
       case VM_ADD: R[d] = R[a] + R[b]; break;
       case VM_SUB: R[d] = R[a] - R[b]; break;
@@ -299,12 +305,117 @@ prog_slice_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t 
   }
 }
 
+// `(subsampled_mh scope block Nbatch k0 epsilon ...)` for a compiled program: subsampledMixMH + sequentialTest
+// (infer/subsampled_mh.py:76-171).  The compiler found every site's global border and local sections
+// (findGlobalBorder :326-368; compiler.py _subsample_site): a section is one row of an observation group or one
+// latent child, and dllh_i = its log density under the proposed value - under the old one (evalOneLocalSection
+// :377-409 refreshes the section to the old value first, so nothing cached is read: Lite followed by makeConsistent).
+// Two register files: Ro holds the groups' row-independent nodes under the old value, Rn under the new one; a row
+// program runs once on each.  Draws: 0 block choice, 1 accept uniform, then the proposal; the sections are visited in
+// the keyed Feistel order of (seed, step) -- the same order for every particle, as in the logistic-regression kernels.
+// LANES = 32: lanes take the positions of a minibatch in turn and the warp adds (sum, sum of squares).
+template <int LANES>
+__global__ void __launch_bounds__(256)
+prog_ssmh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps,
+                 int block_mode, double Nbatch, int k0, double eps, double *nodes_out, double *stats_out) {
+  double Ro[VM_MAX_REGS], Rn[VM_MAX_REGS];
+  const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
+  const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
+  const int S = pg.n_sites;
+  for (int64_t p = unit; p < P; p += n_units) {
+    double accepted = 0.0, visited = 0.0, tlast = 0.0, nodes = 0.0;
+    for (int t = 0; t < n_steps; ++t) {
+      Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)t);
+      const double u_sel = r.uniform();
+      const double logu = log(r.uniform());
+      int k;
+      if (block_mode == VK_BLOCK_ONE) { k = (int)(u_sel * (double)S); if (k >= S) k = S - 1; }
+      else if (block_mode == VK_BLOCK_EACH) k = t % S;
+      else k = block_mode;
+      const int kind = __ldg(&pg.ss_tab[3 * k]), Nloc = __ldg(&pg.ss_tab[3 * k + 1]), off = __ldg(&pg.ss_tab[3 * k + 2]);
+      const int32_t *st = pg.site_tab + 5 * k;
+      nodes += __ldg(&pg.ss_nodes[k]);
+      double *cell = sites + (int64_t)k * P + p;
+      const double old = *cell;
+      double dummy = 0.0;
+      bool accept;
+      if (kind != 1) {                                     // no global border: regular MH, alpha > log u (:91-95)
+        const double rho = vm_children<LANES>(pg, k, Ro, sites, P, p, lane);
+        if (LANES == 32) __syncwarp();
+        vm_exec(pg, __ldg(st), Ro, sites, P, p, nullptr, &r, dummy, lane == 0);
+        if (LANES == 32) __syncwarp();
+        const double xi = vm_children<LANES>(pg, k, Ro, sites, P, p, lane);
+        accept = (xi - rho) > logu;
+      } else {
+        const int ng = __ldg(st + 3), go = __ldg(st + 4);
+        for (int j = 0; j < ng; ++j)
+          vm_exec(pg, __ldg(&pg.group_tab[5 * __ldg(&pg.site_groups[go + j])]), Ro, sites, P, p, nullptr, nullptr, dummy, false);
+        if (LANES == 32) __syncwarp();
+        vm_exec(pg, __ldg(st), Rn, sites, P, p, nullptr, &r, dummy, lane == 0);      // the proposal: SIM_k
+        if (LANES == 32) __syncwarp();
+        for (int j = 0; j < ng; ++j)
+          vm_exec(pg, __ldg(&pg.group_tab[5 * __ldg(&pg.site_groups[go + j])]), Rn, sites, P, p, nullptr, nullptr, dummy, false);
+        const double N = (double)Nloc;
+        const double mu0 = (logu - 0.0) / N;               // alpha of the global section: nothing absorbs in it
+        const FeistelKey key = make_feistel_key(seed, step0 + (uint32_t)t, (uint64_t)Nloc);
+        double n = 0.0, kk = 0.0, cum = 0.0, cum2 = 0.0, ts_t = 0.0;
+        accept = false;
+        while (n < N) {
+          const double n_end = fmin(n + Nbatch, N);
+          double s1 = 0.0, s2 = 0.0;
+          for (int64_t q = (int64_t)n + lane; q < (int64_t)n_end; q += LANES) {
+            const int64_t i = (int64_t)feistel_perm((uint64_t)q, key);
+            const int g = __ldg(&pg.ss_roots[2 * (off + i)]), rr = __ldg(&pg.ss_roots[2 * (off + i) + 1]);
+            double a = 0.0, b = 0.0;
+            if (g >= 0) {
+              const int32_t *gt = pg.group_tab + 5 * g;
+              const double *row = pg.data + __ldg(gt + 4) + (size_t)rr * __ldg(gt + 3);
+              vm_exec(pg, __ldg(gt + 1), Rn, sites, P, p, row, nullptr, a, false);
+              vm_exec(pg, __ldg(gt + 1), Ro, sites, P, p, row, nullptr, b, false);
+            } else {                                       // a latent child: its own density given its parents
+              const int sec = __ldg(&pg.site_tab[5 * rr + 2]);
+              vm_exec(pg, sec, Rn, sites, P, p, nullptr, nullptr, a, false);
+              vm_exec(pg, sec, Ro, sites, P, p, nullptr, nullptr, b, false, k, old);
+            }
+            const double d = a - b;
+            s1 += d; s2 += d * d;
+          }
+          if (LANES == 32) { s1 = warp_sum(s1); s2 = warp_sum(s2); }
+          cum += s1; cum2 += s2; kk += 1.0; n = n_end;
+          const double mx = cum / n, mx2 = cum2 / n;
+          if (kk < (double)k0 && n < N) continue;          // no test during the first k0 minibatches (:146-148)
+          if (n == N) { accept = mx >= mu0; break; }
+          const double sx = sqrt((1.0 - (n - 1.0) / (N - 1.0)) * (mx2 - mx * mx) / (n - 1.0));
+          double q;
+          if (sx == 0.0) q = mx >= mu0 ? 1.0 : 0.0;
+          else { ts_t = (mx - mu0) / sx; q = dev_student_t_cdf(ts_t, n - 1.0); }
+          if (q < eps) { accept = false; break; }
+          if (q > 1.0 - eps) { accept = true; break; }
+        }
+        visited += n;
+        tlast = ts_t != 0.0 ? ts_t : (accept ? INFINITY : -INFINITY);      // :170
+      }
+      if (accept) accepted += 1.0;
+      else { if (LANES == 32) __syncwarp(); if (lane == 0) *cell = old; if (LANES == 32) __syncwarp(); }
+    }
+    if (lane == 0) {
+      if (stats_out) {
+        stats_out[3 * p] = accepted;
+        stats_out[3 * p + 1] = n_steps > 0 ? visited / (double)n_steps : 0.0;
+        stats_out[3 * p + 2] = tlast;
+      }
+      if (nodes_out) nodes_out[p] = n_steps > 0 ? nodes / (double)n_steps : 0.0;
+    }
+  }
+}
+
 __global__ void prog_fill_kernel(double *out, int64_t n, double v) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = v;
 }
 
 struct ProgramModel : Model {
-  std::vector<double> affected_host;
+  std::vector<double> affected_host;   // per site: nodes of the regular scaffold, then of the scaffold cut at the global border
+  std::vector<int> ss_kind;
   DevBuf<int32_t> code, tables;       // tables: dir | site_tab | site_groups | group_tab
   DevBuf<double> consts, data, affected;
   DevBuf<double> sa, sb;
@@ -348,6 +459,25 @@ struct ProgramModel : Model {
     }
     at += 5 * (int64_t)G;
     std::vector<int32_t> dir(meta + at, meta + at + 2 * (int64_t)n_sections);
+    at += 2 * (int64_t)n_sections;
+    // subsampled MH block: per site (kind, local sections, offset), then the sections as pairs
+    VK_REQUIRE(n_meta >= at + 3 * (int64_t)S, VK_EINVAL, "program: truncated subsampled-MH table");
+    std::vector<int32_t> ss_tab(meta + at, meta + at + 3 * (int64_t)S);
+    at += 3 * (int64_t)S;
+    const int64_t n_roots = (n_meta - at) / 2;
+    std::vector<int32_t> ss_roots(meta + at, meta + at + 2 * n_roots);
+    ss_roots.push_back(0);
+    for (int k = 0; k < S; ++k) {
+      const int kind = ss_tab[(size_t)3 * k], n = ss_tab[(size_t)3 * k + 1], off = ss_tab[(size_t)3 * k + 2];
+      VK_REQUIRE(kind >= 0 && kind <= 2 && n >= 0 && off >= 0 && (int64_t)off + n <= n_roots, VK_EINVAL, "program: bad subsampled-MH entry");
+      VK_REQUIRE(kind != 1 || n > 1, VK_EINVAL, "program: a global border has more than one local section");
+      for (int i = off; i < off + n; ++i) {
+        const int g = ss_roots[(size_t)2 * i], r = ss_roots[(size_t)2 * i + 1];
+        if (g >= 0) VK_REQUIRE(g < G && r >= 0 && r < group_tab[(size_t)g * 5 + 2], VK_EINVAL, "program: local section out of range");
+        else VK_REQUIRE(r >= 0 && r < S, VK_EINVAL, "program: local section out of range");
+      }
+      ss_kind.push_back(kind);
+    }
     const int64_t n_instr = n_code / VM_WORDS;
     for (int s = 0; s < n_sections; ++s)
       VK_REQUIRE(dir[2 * s] >= 0 && dir[2 * s + 1] >= 0 && (int64_t)dir[2 * s] + dir[2 * s + 1] <= n_instr, VK_EINVAL,
@@ -386,21 +516,26 @@ struct ProgramModel : Model {
     all.push_back(0);
     const size_t o_gt = all.size();
     all.insert(all.end(), group_tab.begin(), group_tab.end());
+    const size_t o_ss = all.size();
+    all.insert(all.end(), ss_tab.begin(), ss_tab.end());
+    const size_t o_roots = all.size();
+    all.insert(all.end(), ss_roots.begin(), ss_roots.end());
     code.alloc((size_t)(n_code > 0 ? n_code : 1)); tables.alloc(all.size());
-    consts.alloc((size_t)(n_consts > 0 ? n_consts : 1)); data.alloc((size_t)(n_data > 0 ? n_data : 1)); affected.alloc((size_t)S);
+    consts.alloc((size_t)(n_consts > 0 ? n_consts : 1)); data.alloc((size_t)(n_data > 0 ? n_data : 1)); affected.alloc((size_t)2 * S);
     VK_CUDA(cudaMemcpyAsync(code.p, code_h, (size_t)n_code * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
     VK_CUDA(cudaMemcpyAsync(tables.p, all.data(), all.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
     if (n_consts > 0) VK_CUDA(cudaMemcpyAsync(consts.p, consts_h, (size_t)n_consts * sizeof(double), cudaMemcpyHostToDevice, h->stream));
     if (n_data > 0) VK_CUDA(cudaMemcpyAsync(data.p, data_h, (size_t)n_data * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-    VK_CUDA(cudaMemcpyAsync(affected.p, affected_h, (size_t)S * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    VK_CUDA(cudaMemcpyAsync(affected.p, affected_h, (size_t)2 * S * sizeof(double), cudaMemcpyHostToDevice, h->stream));
     VK_CUDA(cudaStreamSynchronize(h->stream));      // the host vectors die with this constructor
     sa.alloc((size_t)S * h->P); sb.alloc((size_t)S * h->P);
     sites = sa.p; sites_alt = sb.p;
     VK_CUDA(cudaMemsetAsync(sites, 0, sa.bytes(), h->stream));
     pg.code = code.p; pg.consts = consts.p; pg.data = data.p;
     pg.dir = tables.p + o_dir; pg.site_tab = tables.p + o_site; pg.site_groups = tables.p + o_sg; pg.group_tab = tables.p + o_gt;
-    pg.affected = affected.p;
-    affected_host.assign(affected_h, affected_h + S);
+    pg.affected = affected.p; pg.ss_nodes = affected.p + S;
+    pg.ss_tab = tables.p + o_ss; pg.ss_roots = tables.p + o_roots;
+    affected_host.assign(affected_h, affected_h + 2 * S);
     pg.n_sites = S; pg.n_groups = G; pg.sec_prior = meta[4]; pg.sec_joint = meta[5];
   }
   bool warp_mode() const { return max_rows >= 64; }
@@ -443,7 +578,7 @@ struct ProgramModel : Model {
       double v = 0.0;
       if (K > 0 && block == VK_BLOCK_EACH) {       // scaffolder_loop: the blocks' counts summed, FLOOR-divided by #blocks (dispatch.py:122-128)
         double sum = 0.0;
-        for (double a : affected_host) sum += a;
+        for (int k = 0; k < S; ++k) sum += affected_host[(size_t)k];
         v = floor(sum / (double)S);
       } else if (K > 0) v = affected_host[(size_t)block];
       prog_fill_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, v);
@@ -455,10 +590,28 @@ struct ProgramModel : Model {
     double v = 0.0;
     if (K > 0 && block == VK_BLOCK_EACH) {         // scaffolder_loop: the blocks' counts summed, FLOOR-divided by #blocks (dispatch.py:122-128)
       double sum = 0.0;
-      for (double a : affected_host) sum += a;
+      for (int k = 0; k < S; ++k) sum += affected_host[(size_t)k];
       v = floor(sum / (double)S);
     } else if (K > 0) v = affected_host[(size_t)block];
     prog_fill_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, v);
+  }
+  // `each` is not a block of subsampled_mh's indexer (BlockScaffoldIndexer: one or a block, dispatch.py:315-322)
+  void subsampled_mh(int scope, int block, int64_t Nbatch, int k0, double eps, int use_delta, double delta_sigma,
+                     int update_values, int K, double *mean_nodes_dev, double *stats_dev) override {
+    (void)use_delta; (void)delta_sigma; (void)update_values;   // none of the compiled SPs has a delta kernel (psp.py:281; continuous.py:352-353)
+    block = block_of(scope, block, false);
+    VK_REQUIRE(block != VK_BLOCK_EACH, VK_EINVAL, "subsampled_mh: block must be one or a site index");
+    VK_REQUIRE(eps >= 0.0 && eps < 0.5, VK_EINVAL, "subsampled_mh: epsilon must be in [0, 0.5)");
+    VK_REQUIRE(propagated || G == 0, VK_ESTATE, "subsampled_mh: unpropagated observations; call vk_make_consistent first");
+    for (int k = 0; k < S; ++k)
+      if (block == VK_BLOCK_ONE || block == k)
+        VK_REQUIRE(ss_kind[(size_t)k] != 2, VK_EUNSUPPORTED,
+                   "subsampled_mh: Invalid global border or overlapping local sections at a site of the block "
+                   "(the reference raises SubsampledScaffoldError / warns NotApplicable)");
+    const uint32_t step0 = h->next_step((uint32_t)K);
+    if (warp_mode()) prog_ssmh_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
+    else prog_ssmh_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
+    VK_CUDA(cudaGetLastError());
   }
   void slice(int scope, int block, double w, double m, int K, double *mean_nodes_dev, long long *moved_dev) override {
     block = block_of(scope, block, false);

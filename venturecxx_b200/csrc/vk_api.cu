@@ -427,13 +427,19 @@ int vk_gibbs(vk_particles *h, int32_t scope, int32_t block, int32_t transitions,
 
 int vk_subsampled_mh(vk_particles *h, int32_t scope, int32_t block, int64_t Nbatch, int32_t k0,
                      double epsilon, int32_t use_delta_kernels, double delta_sigma, int32_t update_values,
-                     int32_t transitions, double *stats_out_host) {
+                     int32_t transitions, double *mean_nodes_out_host, double *stats_out_host) {
   VK_TRY check_handle(h); use_device(h);
   VK_REQUIRE(transitions >= 0 && Nbatch >= 1 && k0 >= 0, VK_EINVAL, "bad subsampled_mh arguments");
-  HostOut o(h, stats_out_host, (size_t)h->P * 3);
+  // both outputs share the handle's one output buffer: statistics in [0, 3P), node counts in [3P, 4P)
+  const size_t P = (size_t)h->P;
+  const bool any = mean_nodes_out_host || stats_out_host;
+  if (any && h->out_d.n < 4 * P) { VK_CUDA(cudaStreamSynchronize(h->stream)); h->out_d.alloc(4 * P); }
+  double *st = stats_out_host ? h->out_d.p : nullptr, *nd = mean_nodes_out_host ? h->out_d.p + 3 * P : nullptr;
   h->model->subsampled_mh(scope, block, Nbatch, k0, epsilon, use_delta_kernels, delta_sigma, update_values,
-                          transitions, o.ptr());
-  o.finish();
+                          transitions, nd, st);
+  if (st) VK_CUDA(cudaMemcpyAsync(stats_out_host, st, 3 * P * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (nd) VK_CUDA(cudaMemcpyAsync(mean_nodes_out_host, nd, P * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (any) { VK_CUDA(cudaStreamSynchronize(h->stream)); vk::p2p_check_error(h); }
   VK_CATCH
 }
 

@@ -174,8 +174,8 @@ struct Model {
   }
   virtual void subsampled_mh(int scope, int block, int64_t Nbatch, int k0, double eps,
                              int use_delta, double delta_sigma, int update_values, int K,
-                             double *stats_dev) {
-    throw Error(VK_EUNSUPPORTED, "subsampled_mh is defined for the BLR model only");
+                             double *mean_nodes_dev, double *stats_dev) {
+    throw Error(VK_EUNSUPPORTED, "subsampled_mh is compiled for the logistic-regression model and for programs of the model compiler");
   }
   virtual void forget_observations(double *w_dev) { throw Error(VK_EUNSUPPORTED, "forget not defined for this model"); }
   virtual int64_t num_sites() const = 0;

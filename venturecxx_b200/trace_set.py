@@ -35,6 +35,7 @@ class B200TraceSet(object):
         self._h = model._create(int(n_particles), int(seed), self.device)
         self.n_particles = int(n_particles)
         self._observed = []
+        self.last_mean_nodes = None
         if particle_base:
             _lib.call("vk_set_particle_base", self._h, int(particle_base))
         # `assume` simulates every latent from its prior (regen.py eval)
@@ -291,9 +292,11 @@ class B200TraceSet(object):
                       updateValues, transitions):
         s, b = self._scope_block(scope, block)
         stats = np.empty((self.n_particles, 3))
+        nodes = self._out()
         _lib.call("vk_subsampled_mh", self._h, s, b, int(Nbatch), int(k0), float(epsilon),
                   int(bool(useDeltaKernels)), float(deltaKernelArgs or 0.0), int(bool(updateValues)),
-                  int(transitions), _lib.ptr(stats))
+                  int(transitions), _lib.ptr(nodes), _lib.ptr(stats))
+        self.last_mean_nodes = nodes       # what the reference's primitive_infer returns (dispatch.py:109-120, 149-152)
         return stats
 
     def log_likelihood_at(self, scope, block):

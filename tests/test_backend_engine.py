@@ -358,3 +358,31 @@ def test_reference_engine_compiles_the_program_from_its_directives():
         e.assume("f", ref_engine.expression("(lambda (x) x)"))
     assert "outside" in str(err.value) or "subset" in str(err.value)
     assert isinstance(ts2.model, CompiledModel) and vb is not None
+
+
+@pytest.mark.gpu
+def test_reference_engine_runs_subsampled_mh_on_a_compiled_program():
+    """The model and the command of test/inference_language/test_subsampledmh.py:64-99 through the reference's
+    Engine: 100 `(observe (normal mu 1.0) x_i)` directives are compiled, `(subsampled_mh default one 2 3 0.01 false
+    0 false 50)` runs on the device, and the engine gets back what Lite returns (the node count of the scaffold cut
+    at the global border: 1 -- mu is its own border)."""
+    from venturecxx_b200 import backend as bk
+    from stats_policy import report_known_continuous, statistical_test
+    import scipy.stats as st
+
+    @statistical_test
+    def check(seed):
+        x = np.random.RandomState(3).normal(10, 1, 100)
+        e = _engine(bk.B200(), seed=seed)
+        e.assume("mu", ref_engine.expression("(normal 10.0 3.0)"))
+        e.infer(ref_engine.program("(resample 128)"))
+        for v in x:
+            e.observe(ref_engine.expression("(normal mu 1.0)"), ref_engine.value(float(v)))
+        nodes = None
+        for _ in range(12):
+            _, nodes = e.infer(ref_engine.program("(subsampled_mh default one 2 3 0.01 false 0 false 50)"))
+        assert nodes is not None
+        mean = (9.0 * x.sum() + 10.0) / (9.0 * 100 + 1.0)
+        std = np.sqrt(9.0 / (9.0 * 100 + 1.0))
+        return report_known_continuous(st.norm(loc=mean, scale=std).cdf, e.model.b200.read_site(0), "N(%f,%f^2)" % (mean, std))
+    check()

@@ -194,6 +194,21 @@ int vk_normalized_probs(vk_particles *h, double *out_host);
 /* stand-alone logsumexp of a host array (n may be 0 -> -inf). */
 int vk_logsumexp_array(const double *in_host, int64_t n, int device,
                        double *out_host);
+/* vk_logsumexp_array for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  No counterpart in the reference.
+ * Allocates nothing and calls no allocating routine: its scratch is a 131 328-byte static __device__ array inside
+ * the library (csrc/k_static.cu; every GPU that loads the library holds it until exit).
+ *   in_dev      n doubles in device memory of the CURRENT device (cudaSetDevice is the caller's)
+ *   n           0 <= n <= 16 777 216 (2^24: one scratch record per 4096 elements, 4096 records); larger n answers
+ *               VK_EINVAL with the limit in vk_last_error(); n = 0 writes -inf
+ *   out_dev     one double in device memory: lite/utils.py:70-91 with its NaN / +-inf cases
+ *   cuda_stream cudaStream_t to enqueue on (NULL = the default stream); stream-ordered, returns without
+ *               synchronising
+ * Every call shares the one scratch array: calls that overlap on the GPU (different streams, threads or processes
+ * on one context) race and give wrong results -- serialise them.  The first call on a device looks up the array's
+ * device address (cudaGetSymbolAddress); make that call outside stream capture. */
+int vk_logsumexp_static(const double *in_dev, int64_t n, double *out_dev,
+                        void *cuda_stream);
 
 /* ---- resample (trace_set.py:202-235, utils.py:93-104,152-157,170-180) ---
  * Draw n_new ancestors proportional to exp(lw); copy ancestor state; all new

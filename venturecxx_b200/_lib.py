@@ -64,6 +64,7 @@ PROTOTYPES = {
     "vk_p2p_open": [_vp, _i32, _i32, _vp, _i32],
     "vk_p2p_resample": [_vp, _i32],
     "vk_p2p_status": [_vp, _vp, _vp],
+    "vk_logsumexp_static": [_vp, _i64, _vp, _vp],
     "vk_subsampled_mh": [_vp, _i32, _i32, _i64, _i32, _f64, _i32, _f64, _i32, _i32, _vp, _vp],
     "vk_log_likelihood_at": [_vp, _i32, _i32, _vp],
     "vk_log_joint_at": [_vp, _i32, _i32, _vp],

@@ -503,7 +503,7 @@ struct HMMModel : Model {
       hmm_step_kernel<<<step_grid(), 256, smem_step, h->stream>>>(cur, hist, Tpad, T, h->lw.p, incr_dev, tb, step_tables.p,
                                                              symbols_host[T], h->P, h->p_base, h->seed, step,
                                                              first ? 0 : 1, h->red.p, h->counters.p, last ? 0 : 1, xchg);
-      h->prof.mark(h->stream, x0 ? "hmm_step+xchg0" : "hmm_step");
+      h->prof.mark(h->stream, x0 ? "hmm_step+send0" : "hmm_step");
       first = false;
     }
     hist_pending = true;
@@ -622,6 +622,7 @@ struct HMMModel : Model {
     if (hist_pending) { patch[0] = 1; patch[1] = 0; patch[2] = T - 1; hist_pending = false; }   // the caller's gather inserts it
     StateArray a{(void **)&cur, (void **)&cur_alt, 0, 1, 4};
     StateArray b{(void **)&hist, (void **)&hist_alt, (size_t)Tpad, 0, 0};
+    b.live_bytes = (size_t)(T > 0 ? T : 1);      // columns T.. of both buffers are still zero (as hmm_gather_kernel's `units`)
     return {a, b};
   }
   int device_buffer(int which, void **p, int64_t *bytes) override {

@@ -437,11 +437,10 @@ __device__ __forceinline__ uint64_t systematic_U0(const double *uniforms, uint64
 // CTAs, a quarter of the serial work per thread -- integer sums, so the CDF does not depend on the tiling)
 template <int ITEMS = SCAN_ITEMS>
 __device__ __forceinline__ void
-fixed_tile_sums_exp_body(const double *__restrict__ lw, int64_t n, const double *__restrict__ red,
+fixed_tile_sums_exp_body(const double *__restrict__ lw, int64_t n, const double m,
                          double scale, uint64_t *tile_sums, double *tile_exp) {
   __shared__ uint64_t sh[32];
   __shared__ double shd[33];
-  const double m = red[0];
   int64_t base = (int64_t)blockIdx.x * (SCAN_THREADS * ITEMS);
   uint64_t s = 0;
   double se = 0.0;
@@ -473,7 +472,7 @@ fixed_tile_sums_exp_body(const double *__restrict__ lw, int64_t n, const double 
 __global__ void __launch_bounds__(SCAN_THREADS)
 fixed_tile_sums_exp_kernel(const double *__restrict__ lw, int64_t n, const double *__restrict__ red,
                            double scale, uint64_t *tile_sums, double *tile_exp) {
-  fixed_tile_sums_exp_body(lw, n, red, scale, tile_sums, tile_exp);
+  fixed_tile_sums_exp_body(lw, n, red[0], scale, tile_sums, tile_exp);
 }
 
 // pass B': scan of tile totals (as scan_tile_sums_kernel) + LSE from the tile exp sums
@@ -812,7 +811,9 @@ void resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms_d
     if (!h->lw_minmax_fresh)
       lse_pass1_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p);
     h->lw_minmax_fresh = false;
+    h->prof.mark(st, "(gap)");
     fixed_tile_sums_exp_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p);
+    h->prof.mark(st, "tile_sums");
     const bool raw_tiles = mode == VK_RESAMPLE_SYSTEMATIC && n_tiles <= 1024;   // each CTA reads all tile totals
     if (!raw_tiles) scan_tile_sums_lse_kernel<<<1, 1024, 0, st>>>(h->red_u.p, h->tile_exp.p, n_tiles, P, h->red.p);
     if (raw_tiles) {
@@ -826,10 +827,12 @@ void resample(vk_particles *h, int64_t n_new, int mode, const double *uniforms_d
       launch_ancestor_search_single(h, n_new, mode, step, uniforms_dev, grid_for(n_new, 256, h->sm_count, 8));
     }
     VK_CUDA(cudaGetLastError());
+    h->prof.mark(st, "offspring / cdf + search");
     const double log_n_new = log((double)n_new);
     if (!(gather_state(h, h->anc.p, n_new, h->lw.p, log_n_new, resize ? &rs_arrs : nullptr) & 2))
       fill_kernel<<<grid_for(n_new, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, n_new, h->red.p, log_n_new);
     VK_CUDA(cudaGetLastError());
+    h->prof.mark(st, "gather");
   }
   if (resize) {
     VK_CUDA(cudaStreamSynchronize(st));          // the gathers read the old buffers, which the model frees now

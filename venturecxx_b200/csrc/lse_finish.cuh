@@ -13,8 +13,9 @@ namespace vk {
 static const int RED_PART = 8;
 
 // every thread of the block calls this with its partial (max, min, nan); block size <= 1024.
-// xchg.tab != nullptr (particle set sharded over peer GPUs, p2p_common.cuh): the last block then runs
-// exchange 0 in its tail, so red[0..2] end up describing the weights of ALL ranks.
+// xchg.tab != nullptr (particle set sharded over peer GPUs, p2p_common.cuh): the last block then SENDS exchange 0
+// in its tail; red[0..2] keep this rank's values until the consumer (p2p_tile_sums_kernel) has collected the
+// peers' and stores the global ones.
 __device__ __forceinline__ void lse_minmax_finish(double mx, double mn, double nanf, double *red,
                                                   unsigned int *counter, const P2PXchg &xchg) {
   __shared__ double sh[3][32];
@@ -62,7 +63,7 @@ __device__ __forceinline__ void lse_minmax_finish(double mx, double mn, double n
     }
     if (xchg.tab) {
       __syncthreads();
-      if (w == 0) p2p_exchange_warp(xchg, red, nullptr, 0, 0);
+      if (w == 0) p2p_send_warp(xchg, 0, red[0], red[1], red[2] != 0.0 ? 1ull : 0ull);
     }
   }
 }

@@ -6,9 +6,11 @@
 // on its own (local) mailbox until every word shows the expected number -- and bulk state moves
 // with plain peer loads / stores over NVLink.  No collective and no host round trip on either path.
 //
-// An exchange is executed by ONE warp, and it runs in the TAIL of the kernel that produced the payload (the
-// "last block" of a grid-wide reduction), not in a kernel of its own: a sharded resample is the same four
-// launches as the single-GPU one.
+// An exchange has two halves, and neither is a kernel of its own (a sharded resample is the same four launches as
+// the single-GPU one).  SEND: one warp, in the TAIL of the kernel that produced the payload (the "last block" of a
+// grid-wide reduction), stores into the peers' mailboxes and returns without waiting.  COLLECT: the first warp of
+// EVERY CTA of the kernel that consumes the values spins on the local mailbox in its prologue, so the peers' stores
+// travel while the producer drains and the consumer launches, and no single CTA's wait serialises a kernel tail.
 //
 // Failure policy: a peer that never arrives trips a wall-clock bound (%globaltimer; VK_P2P_TIMEOUT_S, default
 // 20 s).  The waiting lane then sets the STICKY error word par->err and its mirror in host-mapped pinned
@@ -71,29 +73,31 @@ __device__ __forceinline__ int p2p_mail_index(int parity, int phase, int sender)
   return (parity * P2P_PHASES + phase) * P2P_MAX_WORLD + sender;
 }
 
-// One warp; lane r talks to rank r.  Phase 0 sends (max, min, nan) from red[0..2]; phase 1 sends
-// (sum exp, live-buffer index, mass = tile_sums[n_tiles]).  Results: phase 0 -> red[0..2]; phase 1 -> par
-// (offset, total, cur_idx) and red[3] (global sum exp), red[4] (LSE, utils.py:77-91 edge cases).
-// Returns false (in every lane) when a peer timed out: the results are then NOT written.
-__device__ __forceinline__ bool
-p2p_exchange_warp(const P2PXchg &x, double *red, const uint64_t *tile_sums, int n_tiles, int phase) {
+// SEND half of an exchange: one warp; lane r stores (a, b, c) into this rank's slot of rank r's mailbox.
+__device__ __forceinline__ void p2p_send_warp(const P2PXchg &x, int phase, double a, double b, unsigned long long c) {
   const int lane = threadIdx.x & 31;
   const int parity = (int)(x.seq & 1ull);
-  double a = 0.0, b = 0.0;
-  unsigned long long c = 0ull;
-  if (phase == 0) { a = red[0]; b = red[1]; c = red[2] != 0.0 ? 1ull : 0ull; }
-  else { a = red[3]; b = (double)x.my_cur_idx; c = tile_sums[n_tiles]; }
-  int bad = ((volatile P2PParams *)x.par)->err != 0;
   const unsigned long long flag = (x.seq & 0xffffffffull) << 32;
-  if (lane < x.world && !bad) {
+  if (lane < x.world && !((volatile P2PParams *)x.par)->err) {
     volatile P2PMail *dst = x.tab->mail[lane] + p2p_mail_index(parity, phase, x.rank);
     const unsigned long long ua = (unsigned long long)__double_as_longlong(a), ub = (unsigned long long)__double_as_longlong(b);
     dst->w[0] = (ua & 0xffffffffull) | flag; dst->w[1] = (ua >> 32) | flag;
     dst->w[2] = (ub & 0xffffffffull) | flag; dst->w[3] = (ub >> 32) | flag;
     dst->w[4] = (c & 0xffffffffull) | flag;  dst->w[5] = (c >> 32) | flag;
   }
-  double ra = 0.0, rb = 0.0;
-  unsigned long long rc = 0ull;
+}
+// COLLECT half: one warp; lane r (< world) spins on rank r's slot of the LOCAL mailbox until all six words carry this
+// exchange's number.  Any number of warps (one per CTA of the consuming kernel) may collect the same exchange: a
+// slot is rewritten two exchanges of its phase later, and the sender cannot get there before every kernel of this
+// rank that collects the present one has finished -- to send number seq + 2 of a phase the peer must have collected
+// this rank's seq + 1 of BOTH phases, and this rank sends those after (in stream order) the kernels that collect seq.
+// Returns false in every lane after a timeout (par->err set).
+__device__ __forceinline__ bool p2p_collect_warp(const P2PXchg &x, int phase, double &ra, double &rb, unsigned long long &rc) {
+  const int lane = threadIdx.x & 31;
+  const int parity = (int)(x.seq & 1ull);
+  const unsigned long long flag = (x.seq & 0xffffffffull) << 32;
+  int bad = ((volatile P2PParams *)x.par)->err != 0;
+  ra = 0.0; rb = 0.0; rc = 0ull;
   if (lane < x.world && !bad) {
     volatile P2PMail *src = x.tab->mail[x.rank] + p2p_mail_index(parity, phase, lane);
     const unsigned long long t0 = p2p_now_ns();
@@ -103,7 +107,9 @@ p2p_exchange_warp(const P2PXchg &x, double *red, const uint64_t *tile_sums, int 
 #pragma unroll
       for (int k = 0; k < 6; ++k)
         if (!((have >> k) & 1)) { v[k] = src->w[k]; if ((v[k] & 0xffffffff00000000ull) == flag) have |= 1 << k; }
-      if (have != 0x3f && (++spins & 15) == 0 && (long long)(p2p_now_ns() - t0) > x.timeout_ns) { bad = 1; break; }
+      if (have != 0x3f && (++spins & 15) == 0) {
+        if (((volatile P2PParams *)x.par)->err || (long long)(p2p_now_ns() - t0) > x.timeout_ns) { bad = 1; break; }
+      }
     }
     if (!bad) {
       ra = __longlong_as_double((long long)((v[0] & 0xffffffffull) | (v[1] << 32)));
@@ -112,43 +118,41 @@ p2p_exchange_warp(const P2PXchg &x, double *red, const uint64_t *tile_sums, int 
     }
   }
   bad = __any_sync(0xffffffffu, bad);
-  if (bad) {
-    if (lane == 0) { x.par->err = 1; *x.err_host = 1; __threadfence_system(); }
-    return false;
+  if (bad && lane == 0) { x.par->err = 1; *x.err_host = 1; __threadfence_system(); }
+  return !bad;
+}
+// phase 0 collected: (max, min, NaN flag) over all ranks, in every lane
+__device__ __forceinline__ void p2p_reduce_minmax(const P2PXchg &x, double ra, double rb, unsigned long long rc,
+                                                  double &mx, double &mn, double &nanf) {
+  const int lane = threadIdx.x & 31;
+  mx = lane < x.world ? ra : -INFINITY; mn = lane < x.world ? rb : INFINITY;
+  unsigned long long nf = lane < x.world ? rc : 0ull;
+  for (int o = 16; o > 0; o >>= 1) {
+    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    nf |= __shfl_xor_sync(0xffffffffu, nf, o);
   }
-  if (phase == 0) {
-    double mx = lane < x.world ? ra : -INFINITY, mn = lane < x.world ? rb : INFINITY;
-    unsigned long long nf = lane < x.world ? rc : 0ull;
-    for (int o = 16; o > 0; o >>= 1) {
-      mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-      mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-      nf |= __shfl_xor_sync(0xffffffffu, nf, o);
-    }
-    if (lane == 0) { red[0] = mx; red[1] = mn; red[2] = nf ? 1.0 : 0.0; }
-  } else {
-    // rank-ordered sums (every lane walks the ranks) so that every GPU computes identical values
-    unsigned long long off = 0ull, tot = 0ull;
-    double se = 0.0;
-    for (int r = 0; r < x.world; ++r) {
-      unsigned long long m_r = __shfl_sync(0xffffffffu, rc, r);
-      double se_r = __shfl_sync(0xffffffffu, ra, r);
-      if (r < x.rank) off += m_r;
-      tot += m_r;
-      se += se_r;
-    }
-    if (lane < x.world) x.par->cur_idx[lane] = (int)rb;
-    if (lane == 0) {
-      x.par->offset = off; x.par->total = tot;
-      double m = red[0], mn = red[1], nanf = red[2], lse;
-      if (x.n_total == 0) lse = -INFINITY;
-      else if (nanf != 0.0) lse = NAN;
-      else if (isinf(m) && mn != -m) lse = m;
-      else if (isinf(m)) lse = NAN;
-      else lse = m + log(se);
-      red[3] = se; red[4] = lse;
-    }
+  nanf = nf ? 1.0 : 0.0;
+}
+// phase 1 collected: this rank's mass offset, the global mass and the global sum of exponentials, rank-ordered sums
+// (every lane walks the ranks) so that every GPU computes identical values
+__device__ __forceinline__ void p2p_reduce_mass(const P2PXchg &x, double ra, unsigned long long rc,
+                                                unsigned long long &off, unsigned long long &tot, double &se) {
+  off = 0ull; tot = 0ull; se = 0.0;
+  for (int r = 0; r < x.world; ++r) {
+    const unsigned long long m_r = __shfl_sync(0xffffffffu, rc, r);
+    const double se_r = __shfl_sync(0xffffffffu, ra, r);
+    if (r < x.rank) off += m_r;
+    tot += m_r;
+    se += se_r;
   }
-  return true;
+}
+__device__ __forceinline__ double p2p_lse(long long n_total, double m, double mn, double nanf, double se) {   // utils.py:77-91
+  if (n_total == 0) return -INFINITY;
+  if (nanf != 0.0) return NAN;
+  if (isinf(m) && mn != -m) return m;
+  if (isinf(m)) return NAN;
+  return m + log(se);
 }
 
 }  // namespace vk

@@ -46,6 +46,8 @@ struct P2PArrays {                     // by-value kernel argument of the gather
   long long row_bytes[P2P_MAX_ARRAYS];
   long long n_rows[P2P_MAX_ARRAYS];
   int elem_bytes[P2P_MAX_ARRAYS];
+  int live_units[P2P_MAX_ARRAYS];      // row-major arrays: leading 16-byte units of a row that hold data (StateArray::live_bytes)
+  const unsigned char *own_live[P2P_MAX_ARRAYS];   // this rank's live buffers (most ancestors are this rank's own)
   int patch_array, patch_src, patch_byte;   // Model::state_arrays_patched: byte patch_byte of every row of
                                             // array patch_array := low byte of the ancestor's element of
                                             // the 4-byte particle-minor array patch_src (patch_array < 0: none)
@@ -68,6 +70,8 @@ struct P2P {
   DevBuf<int32_t> anc_g;                         // [2][P]
   DevBuf<P2PTables> tab;
   DevBuf<P2PParams> par;
+  DevBuf<unsigned long long> bar;                // arrival counter of the fused resample kernel's grid barrier (monotone)
+  unsigned long long bar_count = 0;
   DevBuf<double> ss_mail;                        // [2][P2P_MAX_WORLD][ss_stride]
   DevBuf<unsigned long long> ss_seq_words;       // [2][P2P_MAX_WORLD]
   int *err_host = nullptr, *err_host_dev = nullptr;   // mapped pinned word and its device alias
@@ -76,15 +80,27 @@ struct P2P {
 };
 static const int P2P_FIXED_HANDLES = 4;          // mailbox, ancestor array, ss mailbox, ss sequence words
 
-// Tile totals against the GLOBAL max (fixed_tile_sums_exp_kernel's work); the last block then scans the tile
-// totals, forms this rank's sum exp (scan_tile_sums_lse_body) and runs exchange 1 -- one launch, no single-CTA
-// kernel of its own.
+// Tile totals against the GLOBAL max (fixed_tile_sums_exp_kernel's work).  Prologue of every CTA: collect exchange 0
+// (the peers' max / min / NaN flag, sent from the tail of the kernel that wrote the weights).  The last block then
+// stores the global values to red[0..2], scans the tile totals, forms this rank's sum exp (scan_tile_sums_lse_body)
+// and SENDS exchange 1 -- one launch, no single-CTA kernel of its own, no wait in the tail.
 template <int ITEMS>
 __global__ void __launch_bounds__(SCAN_THREADS)
 p2p_tile_sums_kernel(const double *__restrict__ lw, int64_t n, double *__restrict__ red, double scale,
-                     uint64_t *tile_sums, double *tile_exp, int n_tiles, unsigned int *counter, P2PXchg xchg) {
-  if (((volatile P2PParams *)xchg.par)->err) return;
-  fixed_tile_sums_exp_body<ITEMS>(lw, n, red, scale, tile_sums, tile_exp);
+                     uint64_t *__restrict__ tile_sums, double *__restrict__ tile_exp, int n_tiles,
+                     unsigned int *__restrict__ counter, const P2PXchg x0, const P2PXchg xchg) {
+  __shared__ double mm_sh[3];
+  __shared__ int ok_sh;
+  if (threadIdx.x < 32) {
+    double ra, rb, mx, mn, nanf;
+    unsigned long long rc;
+    const bool ok = p2p_collect_warp(x0, 0, ra, rb, rc);
+    p2p_reduce_minmax(x0, ra, rb, rc, mx, mn, nanf);
+    if (threadIdx.x == 0) { mm_sh[0] = mx; mm_sh[1] = mn; mm_sh[2] = nanf; ok_sh = ok ? 1 : 0; }
+  }
+  __syncthreads();
+  if (!ok_sh) return;
+  fixed_tile_sums_exp_body<ITEMS>(lw, n, mm_sh[0], scale, tile_sums, tile_exp);
   __shared__ bool last;
   __threadfence();
   __syncthreads();
@@ -92,10 +108,38 @@ p2p_tile_sums_kernel(const double *__restrict__ lw, int64_t n, double *__restric
   __syncthreads();
   if (!last) return;
   __threadfence();
+  if (threadIdx.x == 0) { red[0] = mm_sh[0]; red[1] = mm_sh[1]; red[2] = mm_sh[2]; }   // every CTA has finished reading
+  __syncthreads();
   scan_tile_sums_lse_body(tile_sums, tile_exp, n_tiles, n, red);
   __syncthreads();
   if (threadIdx.x == 0) *counter = 0;
-  if (threadIdx.x < 32) p2p_exchange_warp(xchg, red, tile_sums, n_tiles, 1);
+  if (threadIdx.x < 32) p2p_send_warp(xchg, 1, red[3], (double)xchg.my_cur_idx, tile_sums[n_tiles]);
+}
+
+// Prologue of the kernels that consume exchange 1: every CTA's first warp collects the ranks' (sum exp, live buffer,
+// mass) and forms this rank's mass offset and the global mass; CTA 0 also stores them (par, red[3..4]) for the gather
+// and for vk_p2p_status.  Returns false (whole CTA) after a timeout.
+__device__ __forceinline__ bool p2p_collect_mass(const P2PXchg &x, double *red, unsigned long long &offset,
+                                                 unsigned long long &total) {
+  __shared__ unsigned long long xm_sh[2];
+  __shared__ int xok_sh;
+  if (threadIdx.x < 32) {
+    double ra, rb, se;
+    unsigned long long rc, off, tot;
+    const bool ok = p2p_collect_warp(x, 1, ra, rb, rc);
+    p2p_reduce_mass(x, ra, rc, off, tot, se);
+    if (threadIdx.x == 0) { xm_sh[0] = off; xm_sh[1] = tot; xok_sh = ok ? 1 : 0; }
+    if (ok && blockIdx.x == 0) {
+      if (threadIdx.x < x.world) x.par->cur_idx[threadIdx.x] = (int)rb;
+      if (threadIdx.x == 0) {
+        x.par->offset = off; x.par->total = tot;
+        red[3] = se; red[4] = p2p_lse(x.n_total, red[0], red[1], red[2], se);
+      }
+    }
+  }
+  __syncthreads();
+  offset = xm_sh[0]; total = xm_sh[1];
+  return xok_sh != 0;
 }
 
 // Step C, systematic: as systematic_offspring_kernel, against the GLOBAL mass: this rank's running sum starts at
@@ -106,11 +150,12 @@ __global__ void __launch_bounds__(SCAN_THREADS)
 p2p_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__restrict__ red, double scale,
                      const uint64_t *__restrict__ tile_sums, const P2PParams *__restrict__ par,
                      P2PTables *__restrict__ tab, int anc_half, int64_t n_total, int64_t p_base, uint64_t seed,
-                     uint32_t step) {
+                     uint32_t step, const P2PXchg x1) {
   __shared__ uint64_t sh[32];
   if (((const volatile P2PParams *)par)->err) return;
+  unsigned long long x_offset, W;
+  if (!p2p_collect_mass(x1, const_cast<double *>(red), x_offset, W)) return;
   const double m = red[0];
-  const uint64_t W = par->total;
   const uint64_t U0 = systematic_U0(nullptr, seed, step);
   int64_t base = (int64_t)blockIdx.x * (SCAN_THREADS * ITEMS) + (int64_t)threadIdx.x * ITEMS;
   uint64_t q[ITEMS];
@@ -132,7 +177,7 @@ p2p_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__r
   }
   __syncthreads();
   if (s == 0) return;
-  uint64_t run = par->offset + tile_sums[blockIdx.x] + (w > 0 ? sh[w - 1] : 0ull) + inc - s;
+  uint64_t run = x_offset + tile_sums[blockIdx.x] + (w > 0 ? sh[w - 1] : 0ull) + inc - s;
   const double ratio = (double)n_total / (double)W, u0f = (double)U0 * (1.0 / 4294967296.0);
   int64_t k_lo = first_child_at_least(run, W, n_total, U0, ratio, u0f);
   const int64_t half_off = (int64_t)anc_half * n;
@@ -160,9 +205,10 @@ p2p_offspring_kernel(const double *__restrict__ lw, int64_t n, const double *__r
 __global__ void __launch_bounds__(256)
 p2p_multinomial_kernel(const uint64_t *__restrict__ cdf, int64_t n, const P2PParams *__restrict__ par,
                        P2PTables *__restrict__ tab, int anc_half, int64_t n_total, int64_t p_base, uint64_t seed,
-                       uint32_t step) {
+                       uint32_t step, double *__restrict__ red, const P2PXchg x1) {
   if (((const volatile P2PParams *)par)->err) return;
-  const uint64_t offset = par->offset, total = par->total;
+  unsigned long long offset, total;
+  if (!p2p_collect_mass(x1, red, offset, total)) return;
   const uint64_t mass = cdf[n - 1];
   const int64_t half_off = (int64_t)anc_half * n;
   for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n_total;
@@ -197,6 +243,292 @@ __device__ __forceinline__ int64_t p2p_wait_ancestor(const int32_t *anc_g, int64
   return g;
 }
 
+// Slot-major gather of small state.  A thread owns GS child slots of a CTA tile: it loads their ancestor indices
+// first, then every row unit and element of all GS slots, then stores -- GS independent chains of dependent loads
+// per thread instead of one.  MAXU: the most 16-byte units any row-major array has live.  Returns false after a
+// timed-out wait.
+template <int GS, int MAXU>
+__device__ __forceinline__ bool p2p_gather_slots(const int32_t *__restrict__ anc_g, int64_t n, P2PParams *__restrict__ par,
+                                                 const P2PArrays &arrs, const P2PTables *__restrict__ tab,
+                                                 const int *cur_idx, double even) {
+  // the live buffer of array a on rank d: this rank's is a kernel argument; a peer's (children at a shard boundary)
+  // costs two dependent loads from the tables.  cur_idx: every rank's live-buffer index (exchange 1)
+  auto live = [&](int a, int d) -> const unsigned char * {
+    return d == arrs.rank ? arrs.own_live[a] : tab->buf[a][d][cur_idx[d]];
+  };
+  const int64_t tile = (int64_t)blockDim.x * GS;
+  const volatile int32_t *anc_v = anc_g;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < n; base += (int64_t)gridDim.x * tile) {
+    int64_t g[GS], i[GS];
+    int d[GS];
+#pragma unroll
+    for (int j = 0; j < GS; ++j) {
+      const int64_t s = base + (int64_t)j * blockDim.x + threadIdx.x;
+      g[j] = s < n ? (int64_t)anc_v[s] : 0;
+    }
+#pragma unroll
+    for (int j = 0; j < GS; ++j) {
+      const int64_t s = base + (int64_t)j * blockDim.x + threadIdx.x;
+      if (s < n && g[j] < 0) {
+        g[j] = p2p_wait_ancestor(anc_g, s, par, arrs.timeout_ns, arrs.err_host);
+        if (g[j] < 0) return false;
+      }
+      // owner rank of a global particle index: most ancestors are this rank's own
+      d[j] = arrs.rank;
+      i[j] = g[j] - (int64_t)d[j] * n;
+      if (i[j] < 0 || i[j] >= n) { d[j] = (int)(g[j] / n); i[j] = g[j] - (int64_t)d[j] * n; }
+    }
+    for (int a = 0; a < arrs.n; ++a) {
+      if (arrs.elem_bytes[a] == 0) {
+        const long long rb = arrs.row_bytes[a];
+        const int units = arrs.live_units[a];
+        uint4 v[GS][MAXU];
+        uint32_t sv[GS];
+        const bool patched = a == arrs.patch_array;
+#pragma unroll
+        for (int j = 0; j < GS; ++j) {
+          const int64_t s = base + (int64_t)j * blockDim.x + threadIdx.x;
+          if (s >= n) continue;
+          const uint4 *src = (const uint4 *)(live(a, d[j]) + i[j] * rb);
+#pragma unroll
+          for (int u = 0; u < MAXU; ++u) if (u < units) v[j][u] = src[u];
+          if (patched) sv[j] = ((const uint32_t *)live(arrs.patch_src, d[j]))[i[j]] & 0xFFu;
+        }
+        const int pu = arrs.patch_byte >> 4, pw = (arrs.patch_byte >> 2) & 3, psh = (arrs.patch_byte & 3) * 8;
+        const uint32_t keep = ~(0xFFu << psh);
+#pragma unroll
+        for (int j = 0; j < GS; ++j) {
+          const int64_t s = base + (int64_t)j * blockDim.x + threadIdx.x;
+          if (s >= n) continue;
+          uint4 *dst = (uint4 *)(arrs.alt[a] + s * rb);
+#pragma unroll
+          for (int u = 0; u < MAXU; ++u) {
+            if (u >= units) continue;
+            if (patched && u == pu) {
+              const uint32_t ins = sv[j] << psh;
+              if (pw == 0) v[j][u].x = (v[j][u].x & keep) | ins;
+              else if (pw == 1) v[j][u].y = (v[j][u].y & keep) | ins;
+              else if (pw == 2) v[j][u].z = (v[j][u].z & keep) | ins;
+              else v[j][u].w = (v[j][u].w & keep) | ins;
+            }
+            dst[u] = v[j][u];
+          }
+        }
+      } else {
+        const long long nr = arrs.n_rows[a];
+        const int eb = arrs.elem_bytes[a];
+        for (long long r = 0; r < nr; ++r) {
+          uint64_t e8[GS];
+#pragma unroll
+          for (int j = 0; j < GS; ++j) {
+            const int64_t s = base + (int64_t)j * blockDim.x + threadIdx.x;
+            if (s >= n) continue;
+            const unsigned char *src = live(a, d[j]) + (r * n + i[j]) * eb;
+            if (eb == 8) e8[j] = *(const uint64_t *)src;
+            else if (eb == 4) e8[j] = *(const uint32_t *)src;
+            else { unsigned char *dst = arrs.alt[a] + (r * n + s) * eb; for (int e = 0; e < eb; ++e) dst[e] = src[e]; }
+          }
+#pragma unroll
+          for (int j = 0; j < GS; ++j) {
+            const int64_t s = base + (int64_t)j * blockDim.x + threadIdx.x;
+            if (s >= n) continue;
+            unsigned char *dst = arrs.alt[a] + (r * n + s) * eb;
+            if (eb == 8) *(uint64_t *)dst = e8[j];
+            else if (eb == 4) *(uint32_t *)dst = (uint32_t)e8[j];
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < GS; ++j) {
+      const int64_t s = base + (int64_t)j * blockDim.x + threadIdx.x;
+      if (s < n) { arrs.anc_other[s] = -1; arrs.lw[s] = even; }
+    }
+  }
+  return true;
+}
+
+// Step D for small state (every array particle-minor, or rows of at most 64 live bytes in 16-byte units -- the HMM, the
+// normal model, compiled programs): ONE THREAD PER CHILD SLOT copies everything that belongs to the slot; the ancestor
+// is waited for and decoded once per slot, and the slot's weight and the other ancestor half are reset by the same
+// thread.  A kernel of its own so that its register count (not the generic path's) sets the occupancy.
+template <int GS, int MAXU>
+__global__ void __launch_bounds__(256, 3)
+p2p_gather_slots_kernel(const int32_t *__restrict__ anc_g, int64_t n, const P2PTables *__restrict__ tab,
+                        P2PParams *__restrict__ par, P2PArrays arrs) {
+  if (!((volatile P2PParams *)par)->err) {
+    const double even = arrs.red[4] - arrs.log_p_total;      // lw := LSE - log P_total (utils.py:152-157)
+    if (p2p_gather_slots<GS, MAXU>(anc_g, n, par, arrs, tab, par->cur_idx, even) && !((volatile P2PParams *)par)->err) return;
+  }
+  // a failed exchange poisons the weights instead
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) {
+    arrs.anc_other[t] = -1; arrs.lw[t] = NAN;
+  }
+}
+
+// Grid barrier of a cooperative launch: a monotone 64-bit counter (never reset; `target` = arrivals expected once this
+// barrier is complete, tracked by the host).  Gives up when the sticky error word is set or the wall-clock bound trips
+// (a CTA that timed out in a collect has left the kernel).
+__device__ __forceinline__ bool p2p_grid_barrier(unsigned long long *bar, unsigned long long target, P2PParams *par,
+                                                 long long timeout_ns, volatile int *err_host) {
+  __shared__ int bar_ok_sh;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(bar, 1ull);
+    const unsigned long long t0 = p2p_now_ns();
+    int ok = 1, spins = 0;
+    while (*(volatile unsigned long long *)bar < target) {
+      if ((++spins & 63) == 0) {
+        if (((volatile P2PParams *)par)->err) { ok = 0; break; }
+        if ((long long)(p2p_now_ns() - t0) > timeout_ns) { par->err = 1; *err_host = 1; __threadfence_system(); ok = 0; break; }
+      }
+    }
+    __threadfence();
+    bar_ok_sh = ok;
+  }
+  __syncthreads();
+  return bar_ok_sh != 0;
+}
+
+// Steps B + C + D of a SYSTEMATIC sharded resample of small state in ONE cooperative launch (one tile per CTA, every CTA
+// resident): collect exchange 0; fixed-point weights of the tile ONCE, kept in registers (the separate kernels compute
+// exp(lw - m) twice and read the weights twice); tile totals -> grid barrier -> every CTA sums the tile totals itself
+// (integers: any order gives the same CDF), CTA 0 sends exchange 1, every CTA collects it; offspring from the registers;
+// then the CTA turns to the gather of ITS child slots, waiting per slot for ancestors that other CTAs and other ranks
+// are still storing (all CTAs are resident, so the wait cannot starve the producers).  Two kernel boundaries and one
+// pass over the weights less than p2p_tile_sums_kernel + p2p_offspring_kernel + p2p_gather_slots_kernel.
+template <int ITEMS, int GS, int MAXU>
+__global__ void __launch_bounds__(SCAN_THREADS, 4)
+p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *__restrict__ red, double scale,
+                          uint64_t *__restrict__ tile_sums, double *__restrict__ tile_exp,
+                          unsigned long long *__restrict__ bar, unsigned long long bar_target, const P2PXchg x0,
+                          const P2PXchg x1, P2PParams *__restrict__ par, P2PTables *__restrict__ tab, int anc_half,
+                          int64_t n_total, int64_t p_base, uint64_t seed, uint32_t step,
+                          const int32_t *__restrict__ anc_mine, P2PArrays arrs) {
+  __shared__ double mm_sh[3];
+  __shared__ int ok_sh;
+  __shared__ uint64_t sh[32];
+  __shared__ double shd[33];
+  __shared__ uint64_t tot_sh[2];
+  __shared__ double se_sh;
+  __shared__ int cur_sh[P2P_MAX_WORLD];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  // ---- exchange 0 (sent from the tail of the kernel that wrote the weights)
+  if (threadIdx.x < 32) {
+    double ra, rb, mx, mn, nanf;
+    unsigned long long rc;
+    const bool ok = p2p_collect_warp(x0, 0, ra, rb, rc);
+    p2p_reduce_minmax(x0, ra, rb, rc, mx, mn, nanf);
+    if (threadIdx.x == 0) { mm_sh[0] = mx; mm_sh[1] = mn; mm_sh[2] = nanf; ok_sh = ok ? 1 : 0; }
+  }
+  __syncthreads();
+  if (!ok_sh) return;
+  const double m = mm_sh[0];
+  // ---- fixed-point weights of this thread's particles (thread-contiguous, as p2p_offspring_kernel)
+  const int64_t base = (int64_t)blockIdx.x * (SCAN_THREADS * ITEMS) + (int64_t)threadIdx.x * ITEMS;
+  uint64_t q[ITEMS];
+  uint64_t s = 0;
+  double se = 0.0;
+#pragma unroll
+  for (int j = 0; j < ITEMS; ++j) {
+    const int64_t i = base + j;
+    q[j] = 0ull;
+    if (i < n) {
+      const double v = lw_in[i];
+      if (!(m > -INFINITY)) q[j] = 1ull;
+      else if (m == INFINITY) q[j] = v == INFINITY ? 1ull : 0ull;
+      else {
+        const double d = v - m;
+        if (d == d) { const double e = exp(d); q[j] = __double2ull_rn(e * scale); se += e; }
+      }
+    }
+    s += q[j];
+  }
+  const uint64_t inc = warp_scan_incl(s, lane);
+  if (lane == 31) sh[w] = inc;
+  se = block_sum(se, shd);                       // (two __syncthreads inside: sh[] is complete after it)
+  if (w == 0) {
+    uint64_t t = lane < (SCAN_THREADS >> 5) ? sh[lane] : 0ull;
+    t = warp_scan_incl(t, lane);
+    sh[lane] = t;
+    if (lane == (SCAN_THREADS >> 5) - 1) tile_sums[blockIdx.x] = t;
+    if (lane == 0) tile_exp[blockIdx.x] = se;
+  }
+  // ---- every tile total is in memory
+  if (!p2p_grid_barrier(bar, bar_target, par, arrs.timeout_ns, arrs.err_host)) return;
+  const int n_tiles = (int)gridDim.x;
+  {
+    uint64_t pre = 0, tot = 0;
+    double te = 0.0;
+    for (int b = threadIdx.x; b < n_tiles; b += SCAN_THREADS) {
+      const uint64_t v = ((const volatile uint64_t *)tile_sums)[b];
+      tot += v;
+      if (b < (int)blockIdx.x) pre += v;
+      te += ((const volatile double *)tile_exp)[b];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { pre += __shfl_xor_sync(0xffffffffu, pre, o); tot += __shfl_xor_sync(0xffffffffu, tot, o); }
+    __shared__ uint64_t pt_sh[2][SCAN_THREADS / 32];
+    if (lane == 0) { pt_sh[0][w] = pre; pt_sh[1][w] = tot; }
+    te = block_sum(te, shd);                     // the same order in every CTA
+    if (threadIdx.x == 0) {
+      pre = 0; tot = 0;
+      for (int k = 0; k < SCAN_THREADS / 32; ++k) { pre += pt_sh[0][k]; tot += pt_sh[1][k]; }
+      tot_sh[0] = pre; tot_sh[1] = tot; se_sh = te;
+    }
+    __syncthreads();
+  }
+  // ---- exchange 1: CTA 0 sends (sum exp, live buffer, mass); every CTA collects
+  if (blockIdx.x == 0 && threadIdx.x < 32) p2p_send_warp(x1, 1, se_sh, (double)x1.my_cur_idx, tot_sh[1]);
+  if (threadIdx.x < 32) {
+    double ra, rb, seg;
+    unsigned long long rc, off, tot;
+    const bool ok = p2p_collect_warp(x1, 1, ra, rb, rc);
+    p2p_reduce_mass(x1, ra, rc, off, tot, seg);
+    if (threadIdx.x < x1.world) cur_sh[threadIdx.x] = (int)rb;
+    if (threadIdx.x == 0) { tot_sh[0] += off; tot_sh[1] = tot; se_sh = seg; ok_sh = ok ? 1 : 0; }
+    if (ok && blockIdx.x == 0) {                 // for vk_p2p_status and the unfused kernels of a later call
+      if (threadIdx.x < x1.world) par->cur_idx[threadIdx.x] = (int)rb;
+      if (threadIdx.x == 0) {
+        par->offset = off; par->total = tot;
+        red[0] = mm_sh[0]; red[1] = mm_sh[1]; red[2] = mm_sh[2];
+        red[3] = seg; red[4] = p2p_lse(x1.n_total, mm_sh[0], mm_sh[1], mm_sh[2], seg);
+      }
+    }
+  }
+  __syncthreads();
+  if (!ok_sh) return;
+  const uint64_t W = tot_sh[1];
+  const double even = p2p_lse(x1.n_total, mm_sh[0], mm_sh[1], mm_sh[2], se_sh) - arrs.log_p_total;
+  // ---- offspring (p2p_offspring_kernel's loop on the registers)
+  if (s != 0) {
+    const uint64_t U0 = systematic_U0(nullptr, seed, step);
+    uint64_t run = tot_sh[0] + (w > 0 ? sh[w - 1] : 0ull) + inc - s;
+    const double ratio = (double)n_total / (double)W, u0f = (double)U0 * (1.0 / 4294967296.0);
+    int64_t k_lo = first_child_at_least(run, W, n_total, U0, ratio, u0f);
+    const int64_t half_off = (int64_t)anc_half * n;
+    int64_t d = k_lo / n, rem = k_lo - d * n;
+    int32_t *dst = k_lo < n_total ? tab->anc[d] + half_off : nullptr;
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+      if (q[j] == 0) continue;
+      run += q[j];
+      const int64_t k_hi = first_child_at_least(run, W, n_total, U0, ratio, u0f);
+      const int32_t g = (int32_t)(p_base + base + j);
+      for (int64_t k = k_lo; k < k_hi; ++k) {
+        dst[rem] = g;
+        if (++rem == n) { rem = 0; ++d; dst = k + 1 < n_total ? tab->anc[d] + half_off : nullptr; }
+      }
+      k_lo = k_hi;
+    }
+  }
+  // ---- gather of this CTA's share of the child slots
+  if (!p2p_gather_slots<GS, MAXU>(anc_mine, n, par, arrs, tab, cur_sh, even)) {
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) arrs.lw[t] = NAN;
+  }
+}
+
 // Step D: slot s copies its ancestor's state from the owning rank's live buffers (NVLink peer loads; rows that
 // are multiples of 16 bytes move as uint4) into the local back buffers.
 __global__ void __launch_bounds__(256)
@@ -220,57 +552,6 @@ p2p_gather_kernel(const int32_t *__restrict__ anc_g, int64_t n, const P2PTables 
     if (i < 0 || i >= n) { d = (int)(g / n); i = g - (int64_t)d * n; }
     return d;
   };
-  // Small state (every array particle-minor, or rows of at most 64 bytes in 16-byte units -- the HMM, the normal
-  // model, compiled programs): ONE THREAD PER CHILD SLOT copies everything that belongs to the slot; the ancestor is
-  // waited for and decoded once per slot instead of once per unit of every array.
-  bool slot_major = true;
-  for (int a = 0; a < arrs.n; ++a)
-    if (arrs.elem_bytes[a] == 0 && ((arrs.row_bytes[a] & 15) != 0 || arrs.row_bytes[a] > 64)) slot_major = false;
-  if (slot_major && !failed) {
-    for (int64_t s = tid0; s < n; s += stride) {
-      const int64_t g = p2p_wait_ancestor(anc_g, s, par, arrs.timeout_ns, arrs.err_host);
-      if (g < 0) { failed = true; break; }
-      int64_t i;
-      const int d = owner(g, i);
-      for (int a = 0; a < arrs.n; ++a) {
-        if (arrs.elem_bytes[a] == 0) {
-          const long long rb = arrs.row_bytes[a];
-          const int units = (int)(rb >> 4);
-          const uint4 *src = (const uint4 *)(live_sh[a][d] + i * rb);
-          uint4 *dst = (uint4 *)(arrs.alt[a] + s * rb);
-          uint4 v[4];
-#pragma unroll
-          for (int u = 0; u < 4; ++u) if (u < units) v[u] = src[u];
-          if (a == arrs.patch_array) {
-            const uint32_t sv = ((const uint32_t *)live_sh[arrs.patch_src][d])[i] & 0xFFu;
-            const int pu = arrs.patch_byte >> 4, pw = (arrs.patch_byte >> 2) & 3, psh = (arrs.patch_byte & 3) * 8;
-            const uint32_t keep = ~(0xFFu << psh), ins = sv << psh;
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              if (u == pu) {
-                if (pw == 0) v[u].x = (v[u].x & keep) | ins;
-                else if (pw == 1) v[u].y = (v[u].y & keep) | ins;
-                else if (pw == 2) v[u].z = (v[u].z & keep) | ins;
-                else v[u].w = (v[u].w & keep) | ins;
-              }
-            }
-          }
-#pragma unroll
-          for (int u = 0; u < 4; ++u) if (u < units) dst[u] = v[u];
-        } else {
-          const long long nr = arrs.n_rows[a];
-          const int eb = arrs.elem_bytes[a];
-          for (long long r = 0; r < nr; ++r) {
-            const unsigned char *src = live_sh[a][d] + (r * n + i) * eb;
-            unsigned char *dst = arrs.alt[a] + (r * n + s) * eb;
-            if (eb == 8) *(uint64_t *)dst = *(const uint64_t *)src;
-            else if (eb == 4) *(uint32_t *)dst = *(const uint32_t *)src;
-            else for (int e = 0; e < eb; ++e) dst[e] = src[e];
-          }
-        }
-      }
-    }
-  } else
   for (int a = 0; a < arrs.n && !failed; ++a) {
     if (arrs.elem_bytes[a] == 0) {
       const long long rb = arrs.row_bytes[a];
@@ -491,31 +772,14 @@ void p2p_resample(vk_particles *h, int mode) {
   if (!(h->lw_minmax_fresh && h->lw_x0_done)) {     // the producer of the weights did not run exchange 0 itself
     p2p_begin_exchange(h, 0, &x);
     lse_pass1_xchg_kernel<<<grid_for(P, 256, h->sm_count, 4), 256, 0, st>>>(h->lw.p, P, h->red.p, h->counters.p, x);
-    h->prof.mark(st, "lse_pass1+xchg0");
+    h->prof.mark(st, "lse_pass1+send0");
   }
   h->lw_minmax_fresh = false; h->lw_x0_done = false;
   p2p_begin_exchange(h, 1, &x);
   x.my_cur_idx = cur_idx;
-  if (small_tiles)
-    p2p_tile_sums_kernel<2><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p, n_tiles,
-                                                              h->counters.p + 2, x);
-  else
-    p2p_tile_sums_kernel<SCAN_ITEMS><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p,
-                                                                       n_tiles, h->counters.p + 2, x);
-  h->prof.mark(st, "p2p_tile_sums+xchg1");
-  if (mode == VK_RESAMPLE_SYSTEMATIC) {
-    if (small_tiles)
-      p2p_offspring_kernel<2><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, s->par.p, s->tab.p,
-                                                                half, P_total, h->p_base, h->seed, step);
-    else
-      p2p_offspring_kernel<SCAN_ITEMS><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, s->par.p,
-                                                                         s->tab.p, half, P_total, h->p_base, h->seed, step);
-  } else {
-    fixed_cdf_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, 0.0, h->red.p, scale, h->red_u.p, h->cdf.p);
-    p2p_multinomial_kernel<<<grid_for(P_total, 256, h->sm_count, 8), 256, 0, st>>>(h->cdf.p, P, s->par.p, s->tab.p, half,
-                                                                                  P_total, h->p_base, h->seed, step);
-  }
-  h->prof.mark(st, mode == VK_RESAMPLE_SYSTEMATIC ? "p2p_offspring" : "cdf+p2p_multinomial");
+  P2PXchg x0 = x;                        // the exchange 0 just sent (by the weights' producer or by lse_pass1_xchg_kernel)
+  x0.seq = s->phase_seq[0];
+  // what the gather needs
   P2PArrays pa;
   memset(&pa, 0, sizeof pa);
   pa.n = s->n_arrays;
@@ -525,20 +789,76 @@ void p2p_resample(vk_particles *h, int mode) {
   pa.timeout_ns = s->timeout_ns; pa.err_host = s->err_host_dev;
   pa.world = s->world; pa.rank = s->rank;
   int64_t work = P;
+  bool slot_major = true;
+  int max_units = 0;
   for (int a = 0; a < s->n_arrays; ++a) {
     pa.alt[a] = (unsigned char *)*arrs[a].alt;
+    pa.own_live[a] = (const unsigned char *)*arrs[a].cur;
     pa.row_bytes[a] = (long long)arrs[a].row_bytes; pa.n_rows[a] = (long long)arrs[a].n_rows;
     pa.elem_bytes[a] = (int)arrs[a].elem_bytes;
     int64_t wa = arrs[a].elem_bytes ? P * (int64_t)arrs[a].n_rows
                                     : ((arrs[a].row_bytes & 15) == 0 ? P * (int64_t)(arrs[a].row_bytes >> 4) : P * (int64_t)arrs[a].row_bytes);
     work = wa > work ? wa : work;
+    const size_t live = arrs[a].live_bytes ? arrs[a].live_bytes : arrs[a].row_bytes;
+    pa.live_units[a] = arrs[a].elem_bytes ? 0 : (int)((live + 15) >> 4);
+    if (arrs[a].elem_bytes == 0) {
+      if ((arrs[a].row_bytes & 15) != 0 || pa.live_units[a] > 4) slot_major = false;
+      max_units = pa.live_units[a] > max_units ? pa.live_units[a] : max_units;
+    }
   }
-  bool slot_major = true;
-  for (int a = 0; a < s->n_arrays; ++a)
-    if (arrs[a].elem_bytes == 0 && ((arrs[a].row_bytes & 15) != 0 || arrs[a].row_bytes > 64)) slot_major = false;
-  if (slot_major) work = P;
-  p2p_gather_kernel<<<grid_for(work, 256, h->sm_count, 8), 256, 0, st>>>(s->anc_g.p + (int64_t)half * P, P, s->tab.p,
-                                                                         s->par.p, pa);
+  const int64_t anc_off = (int64_t)half * P;
+  const int32_t *anc_mine = s->anc_g.p + anc_off;
+  // small state, systematic: steps B + C + D as ONE cooperative launch when a CTA per tile fits on the GPU
+  static const bool unfused_env = getenv("VK_P2P_UNFUSED") != nullptr;
+  const void *fk = nullptr;
+  if (mode == VK_RESAMPLE_SYSTEMATIC && slot_major && !unfused_env) {
+    if (small_tiles) fk = max_units <= 2 ? (const void *)p2p_resample_fused_kernel<2, 2, 2> : (const void *)p2p_resample_fused_kernel<2, 2, 4>;
+    else fk = max_units <= 2 ? (const void *)p2p_resample_fused_kernel<SCAN_ITEMS, 2, 2> : (const void *)p2p_resample_fused_kernel<SCAN_ITEMS, 2, 4>;
+    int coop = 0, per_sm = 0;
+    VK_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device));
+    VK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fk, SCAN_THREADS, 0));
+    if (!coop || (int64_t)per_sm * h->sm_count < n_tiles) fk = nullptr;
+  }
+  if (fk) {
+    if (!s->bar.p) { s->bar.alloc(2); VK_CUDA(cudaMemsetAsync(s->bar.p, 0, s->bar.bytes(), st)); s->bar_count = 0; }
+    s->bar_count += (unsigned long long)n_tiles;
+    const double *lw_in = h->lw.p; double *red_p = h->red.p; uint64_t *ts_p = h->red_u.p; double *te_p = h->tile_exp.p;
+    unsigned long long *bar_p = s->bar.p, bar_target = s->bar_count;
+    P2PParams *par_p = s->par.p; P2PTables *tab_p = s->tab.p;
+    int64_t n_arg = P, n_total_arg = P_total, p_base_arg = h->p_base;
+    uint64_t seed_arg = h->seed; uint32_t step_arg = step; int half_arg = half; double scale_arg = scale;
+    void *args[] = {&lw_in, &n_arg, &red_p, &scale_arg, &ts_p, &te_p, &bar_p, &bar_target, &x0, &x, &par_p, &tab_p, &half_arg,
+                    &n_total_arg, &p_base_arg, &seed_arg, &step_arg, &anc_mine, &pa};
+    VK_CUDA(cudaLaunchCooperativeKernel(fk, dim3(n_tiles), dim3(SCAN_THREADS), args, 0, st));
+    h->prof.mark(st, "p2p_resample_fused");
+  } else {
+  if (small_tiles)
+    p2p_tile_sums_kernel<2><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p, n_tiles,
+                                                              h->counters.p + 2, x0, x);
+  else
+    p2p_tile_sums_kernel<SCAN_ITEMS><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, h->tile_exp.p,
+                                                                       n_tiles, h->counters.p + 2, x0, x);
+  h->prof.mark(st, "collect0+p2p_tile_sums+send1");
+  if (mode == VK_RESAMPLE_SYSTEMATIC) {
+    if (small_tiles)
+      p2p_offspring_kernel<2><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, s->par.p, s->tab.p,
+                                                                half, P_total, h->p_base, h->seed, step, x);
+    else
+      p2p_offspring_kernel<SCAN_ITEMS><<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, h->red.p, scale, h->red_u.p, s->par.p,
+                                                                         s->tab.p, half, P_total, h->p_base, h->seed, step, x);
+  } else {
+    fixed_cdf_kernel<<<n_tiles, SCAN_THREADS, 0, st>>>(h->lw.p, P, 0.0, h->red.p, scale, h->red_u.p, h->cdf.p);
+    p2p_multinomial_kernel<<<grid_for(P_total, 256, h->sm_count, 8), 256, 0, st>>>(h->cdf.p, P, s->par.p, s->tab.p, half,
+                                                                                  P_total, h->p_base, h->seed, step, h->red.p, x);
+  }
+  h->prof.mark(st, mode == VK_RESAMPLE_SYSTEMATIC ? "collect1+p2p_offspring" : "cdf+collect1+p2p_multinomial");
+  if (slot_major && max_units <= 2)
+    p2p_gather_slots_kernel<4, 2><<<grid_for((P + 3) / 4, 256, h->sm_count, 3), 256, 0, st>>>(anc_mine, P, s->tab.p, s->par.p, pa);
+  else if (slot_major)
+    p2p_gather_slots_kernel<2, 4><<<grid_for((P + 1) / 2, 256, h->sm_count, 3), 256, 0, st>>>(anc_mine, P, s->tab.p, s->par.p, pa);
+  else
+    p2p_gather_kernel<<<grid_for(work, 256, h->sm_count, 8), 256, 0, st>>>(anc_mine, P, s->tab.p, s->par.p, pa);
+  }
   h->prof.mark(st, "p2p_gather");
   VK_CUDA(cudaGetLastError());
   for (auto &a : arrs) { void *t = *a.cur; *a.cur = *a.alt; *a.alt = t; }

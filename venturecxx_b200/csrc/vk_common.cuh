@@ -69,6 +69,7 @@ struct StateArray {
   size_t row_bytes;  // bytes per particle when particle-major (rows)
   size_t n_rows;     // SoA: number of particle-minor rows of elem_bytes each
   size_t elem_bytes; // SoA element size (particle-minor layout); 0 => particle-major rows
+  size_t live_bytes = 0;  // particle-major rows: leading bytes that hold data so far (0 => the whole row); a gather may skip the rest
 };
 
 struct Model;

@@ -259,24 +259,26 @@ __device__ __forceinline__ bool p2p_gather_slots(const int32_t *__restrict__ anc
   const int64_t tile = (int64_t)blockDim.x * GS;
   const volatile int32_t *anc_v = anc_g;
   for (int64_t base = (int64_t)blockIdx.x * tile; base < n; base += (int64_t)gridDim.x * tile) {
-    int64_t g[GS], i[GS];
+    int32_t i[GS];                       // global ancestor index, then the index within its owner's shard (P <= 2^30)
     int d[GS];
 #pragma unroll
     for (int j = 0; j < GS; ++j) {
       const int64_t s = base + (int64_t)j * blockDim.x + threadIdx.x;
-      g[j] = s < n ? (int64_t)anc_v[s] : 0;
+      i[j] = s < n ? anc_v[s] : 0;
     }
+    const int32_t n32 = (int32_t)n, mine_lo = (int32_t)(arrs.rank * n);
 #pragma unroll
     for (int j = 0; j < GS; ++j) {
       const int64_t s = base + (int64_t)j * blockDim.x + threadIdx.x;
-      if (s < n && g[j] < 0) {
-        g[j] = p2p_wait_ancestor(anc_g, s, par, arrs.timeout_ns, arrs.err_host);
-        if (g[j] < 0) return false;
+      if (s < n && i[j] < 0) {
+        i[j] = (int32_t)p2p_wait_ancestor(anc_g, s, par, arrs.timeout_ns, arrs.err_host);
+        if (i[j] < 0) return false;
       }
       // owner rank of a global particle index: most ancestors are this rank's own
+      const int32_t g = i[j];
       d[j] = arrs.rank;
-      i[j] = g[j] - (int64_t)d[j] * n;
-      if (i[j] < 0 || i[j] >= n) { d[j] = (int)(g[j] / n); i[j] = g[j] - (int64_t)d[j] * n; }
+      i[j] = g - mine_lo;
+      if (i[j] < 0 || i[j] >= n32) { d[j] = g / n32; i[j] = g - d[j] * n32; }
     }
     for (int a = 0; a < arrs.n; ++a) {
       if (arrs.elem_bytes[a] == 0) {
@@ -289,7 +291,7 @@ __device__ __forceinline__ bool p2p_gather_slots(const int32_t *__restrict__ anc
         for (int j = 0; j < GS; ++j) {
           const int64_t s = base + (int64_t)j * blockDim.x + threadIdx.x;
           if (s >= n) continue;
-          const uint4 *src = (const uint4 *)(live(a, d[j]) + i[j] * rb);
+          const uint4 *src = (const uint4 *)(live(a, d[j]) + (long long)i[j] * rb);
 #pragma unroll
           for (int u = 0; u < MAXU; ++u) if (u < units) v[j][u] = src[u];
           if (patched) sv[j] = ((const uint32_t *)live(arrs.patch_src, d[j]))[i[j]] & 0xFFu;
@@ -395,9 +397,9 @@ __device__ __forceinline__ bool p2p_grid_barrier(unsigned long long *bar, unsign
 // resident): collect exchange 0; fixed-point weights of the tile ONCE, kept in registers (the separate kernels compute
 // exp(lw - m) twice and read the weights twice); tile totals -> grid barrier -> every CTA sums the tile totals itself
 // (integers: any order gives the same CDF), CTA 0 sends exchange 1, every CTA collects it; offspring from the registers;
-// then the CTA turns to the gather of ITS child slots, waiting per slot for ancestors that other CTAs and other ranks
-// are still storing (all CTAs are resident, so the wait cannot starve the producers).  Two kernel boundaries and one
-// pass over the weights less than p2p_tile_sums_kernel + p2p_offspring_kernel + p2p_gather_slots_kernel.
+// a second grid barrier (this rank's ancestors are all stored); then the CTA turns to the gather of ITS child slots,
+// waiting per slot only for ancestors that other RANKS are still storing.  Two kernel boundaries and one pass over the
+// weights less than p2p_tile_sums_kernel + p2p_offspring_kernel + p2p_gather_slots_kernel.
 template <int ITEMS, int GS, int MAXU>
 __global__ void __launch_bounds__(SCAN_THREADS, 4)
 p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *__restrict__ red, double scale,
@@ -456,7 +458,7 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
     if (lane == 0) tile_exp[blockIdx.x] = se;
   }
   // ---- every tile total is in memory
-  if (!p2p_grid_barrier(bar, bar_target, par, arrs.timeout_ns, arrs.err_host)) return;
+  if (!p2p_grid_barrier(bar, bar_target - gridDim.x, par, arrs.timeout_ns, arrs.err_host)) return;
   const int n_tiles = (int)gridDim.x;
   {
     uint64_t pre = 0, tot = 0;
@@ -523,6 +525,10 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
       k_lo = k_hi;
     }
   }
+  // ---- every ancestor this rank produces is stored: the gather below polls only for what peers still owe (spinning
+  // on local ancestors while neighbouring CTAs are still in their offspring loop costs more than this barrier:
+  // 62.7 -> 59.7 us per step at a world of one)
+  if (!p2p_grid_barrier(bar, bar_target, par, arrs.timeout_ns, arrs.err_host)) return;
   // ---- gather of this CTA's share of the child slots
   if (!p2p_gather_slots<GS, MAXU>(anc_mine, n, par, arrs, tab, cur_sh, even)) {
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) arrs.lw[t] = NAN;
@@ -811,17 +817,20 @@ void p2p_resample(vk_particles *h, int mode) {
   // small state, systematic: steps B + C + D as ONE cooperative launch when a CTA per tile fits on the GPU
   static const bool unfused_env = getenv("VK_P2P_UNFUSED") != nullptr;
   const void *fk = nullptr;
+  int fused_tiles = n_tiles;
   if (mode == VK_RESAMPLE_SYSTEMATIC && slot_major && !unfused_env) {
+    // 2 slots per thread and batch in the gather: 4 and 8 were measured slower (68 / 88 us per step against 60 at a
+    // world of one: register spills, and the phases are bound by per-thread serial work, not by memory latency)
     if (small_tiles) fk = max_units <= 2 ? (const void *)p2p_resample_fused_kernel<2, 2, 2> : (const void *)p2p_resample_fused_kernel<2, 2, 4>;
     else fk = max_units <= 2 ? (const void *)p2p_resample_fused_kernel<SCAN_ITEMS, 2, 2> : (const void *)p2p_resample_fused_kernel<SCAN_ITEMS, 2, 4>;
     int coop = 0, per_sm = 0;
     VK_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device));
     VK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fk, SCAN_THREADS, 0));
-    if (!coop || (int64_t)per_sm * h->sm_count < n_tiles) fk = nullptr;
+    if (!coop || (int64_t)per_sm * h->sm_count < fused_tiles) fk = nullptr;
   }
   if (fk) {
     if (!s->bar.p) { s->bar.alloc(2); VK_CUDA(cudaMemsetAsync(s->bar.p, 0, s->bar.bytes(), st)); s->bar_count = 0; }
-    s->bar_count += (unsigned long long)n_tiles;
+    s->bar_count += 2ull * (unsigned long long)fused_tiles;      // two grid barriers per launch
     const double *lw_in = h->lw.p; double *red_p = h->red.p; uint64_t *ts_p = h->red_u.p; double *te_p = h->tile_exp.p;
     unsigned long long *bar_p = s->bar.p, bar_target = s->bar_count;
     P2PParams *par_p = s->par.p; P2PTables *tab_p = s->tab.p;
@@ -829,7 +838,7 @@ void p2p_resample(vk_particles *h, int mode) {
     uint64_t seed_arg = h->seed; uint32_t step_arg = step; int half_arg = half; double scale_arg = scale;
     void *args[] = {&lw_in, &n_arg, &red_p, &scale_arg, &ts_p, &te_p, &bar_p, &bar_target, &x0, &x, &par_p, &tab_p, &half_arg,
                     &n_total_arg, &p_base_arg, &seed_arg, &step_arg, &anc_mine, &pa};
-    VK_CUDA(cudaLaunchCooperativeKernel(fk, dim3(n_tiles), dim3(SCAN_THREADS), args, 0, st));
+    VK_CUDA(cudaLaunchCooperativeKernel(fk, dim3(fused_tiles), dim3(SCAN_THREADS), args, 0, st));
     h->prof.mark(st, "p2p_resample_fused");
   } else {
   if (small_tiles)

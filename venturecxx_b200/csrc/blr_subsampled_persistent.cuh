@@ -40,6 +40,7 @@ static const int SSP_CHUNKS = SSP_ROWS / 32;     // 32-row chunks of a pass (one
 static const int SSP_STAGES = 3;                 // passes in flight (cp.async ring)
 static const int SSP_TILE = 64;                  // undecided particles handled per sweep over the passes
 static const int SSP_GMAX = P2P_SS_MAX_ROUNDS;   // rounds per batch
+static const int SSP_LIST = 256;                 // direct path: local rows a warp lists before it evaluates them
 static const int SSP_DIRECT = 4;                 // at most this many undecided particles: one thread per position, no staging
 static const int SSP_PART = SSP_GMAX * SSP_DIRECT * SSP_WARPS * 2 > SSP_CHUNKS * SSP_TILE * 2
                                 ? SSP_GMAX * SSP_DIRECT * SSP_WARPS * 2 : SSP_CHUNKS * SSP_TILE * 2;   // doubles of scratch
@@ -236,79 +237,98 @@ __global__ void __launch_bounds__(SSP_THREADS, 2) ss_persistent_kernel(const SSP
           site_sh[tid] = tid < nT ? a.S.site[p] : 0;
         }
         __syncthreads();
-        const int ppr2 = (int)((C_full + SSP_THREADS - 1) / SSP_THREADS) > 0 ? (int)((C_full + SSP_THREADS - 1) / SSP_THREADS) : 1;
-        const int n_items = G * ppr2;
-        auto fetch = [&](int it, double (&x)[DT]) -> bool {
-          const int g = it / ppr2, kk = it - g * ppr2;
+        // A ROUND BELONGS TO A WARP (wpr warps share one when the batch has fewer rounds than the CTA has warps).  The
+        // warp turns its positions into local rows first -- Feistel image, this rank's shard only, compacted in
+        // position order into a list -- and then evaluates the list 32 rows at a time.  With the observations sharded
+        // over R ranks only 1/R of the positions are local: evaluating position by position left 1 - 1/R of the
+        // lanes idle through the whole softplus arithmetic (8 GPUs: 2.9 us per round against 5.9 on one).
+        const int wpr = G >= SSP_WARPS ? 1 : SSP_WARPS / G;
+        const int g_stride = SSP_WARPS / wpr, sub = warp % wpr;
+        int *list = reinterpret_cast<int *>(rows_sh) + warp * SSP_LIST;       // the staged ring is idle on this path
+        for (int g = warp / wpr; g < G; g += g_stride) {
           const int64_t q0 = q_done + (int64_t)g * a.Nbatch;
           const int64_t q1 = q0 + a.Nbatch < a.Nt ? q0 + a.Nbatch : a.Nt;
           const int64_t Cg = (q1 - q0 + gridDim.x - 1) / gridDim.x;
-          const int64_t qa = q0 + (int64_t)blockIdx.x * Cg;
-          const int64_t qb = qa + Cg < q1 ? qa + Cg : q1;
-          const int64_t q = qa + (int64_t)kk * SSP_THREADS + tid;
-          int64_t i_loc = -1;
-          if (it < n_items && q < qb) {
-            i_loc = (int64_t)feistel_perm((uint64_t)q, key) - a.obs_lo;
-            if (i_loc < 0 || i_loc >= a.N_local) i_loc = -1;
-          }
-          if (i_loc >= 0) {
-            const double *row = a.Xr + i_loc * D;
-            if ((D & 1) == 0) {          // rows start on 16-byte boundaries
+          const int64_t qa_cta = q0 + (int64_t)blockIdx.x * Cg;
+          const int64_t qb_cta = qa_cta + Cg < q1 ? qa_cta + Cg : q1;
+          const int64_t Cw = (Cg + wpr - 1) / wpr;
+          const int64_t qa = qa_cta + (int64_t)sub * Cw;
+          const int64_t qb = qa + Cw < qb_cta ? qa + Cw : qb_cta;
+          double a1[SSP_DIRECT], a2[SSP_DIRECT];
 #pragma unroll
-              for (int j = 0; j < DT; j += 2) {
-                double2 v = make_double2(0.0, 0.0);
-                if (j < D) v = __ldg(reinterpret_cast<const double2 *>(row + j));
-                x[j] = v.x; x[j + 1] = v.y;
+          for (int sl = 0; sl < SSP_DIRECT; ++sl) { a1[sl] = 0.0; a2[sl] = 0.0; }
+          for (int64_t qs = qa; qs < qb; qs += SSP_LIST) {                     // (warp-uniform loops throughout)
+            const int64_t qe = qs + SSP_LIST < qb ? qs + SSP_LIST : qb;
+            int n_rows = 0;
+            for (int64_t qq = qs; qq < qe; qq += 32) {
+              const int64_t q = qq + lane;
+              int64_t i_loc = -1;
+              if (q < qe) {
+                i_loc = (int64_t)feistel_perm((uint64_t)q, key) - a.obs_lo;
+                if (i_loc < 0 || i_loc >= a.N_local) i_loc = -1;
               }
-            } else {
-#pragma unroll
-              for (int j = 0; j < DT; ++j) x[j] = j < D ? __ldg(row + j) : 0.0;
+              const unsigned bal = __ballot_sync(0xffffffffu, i_loc >= 0);
+              if (i_loc >= 0) list[n_rows + __popc(bal & ((1u << lane) - 1u))] = (int)i_loc;
+              n_rows += __popc(bal);
             }
-          }
-          return i_loc >= 0;
-        };
-        double a1[SSP_DIRECT], a2[SSP_DIRECT];
+            __syncwarp();
+            const int n_chunks = (n_rows + 31) >> 5;
+            auto fetch = [&](int c, double (&x)[DT]) -> bool {
+              const int r = c * 32 + lane;
+              const bool ok = c < n_chunks && r < n_rows;
+              if (ok) {
+                const double *row = a.Xr + (int64_t)list[r] * D;
+                if ((D & 1) == 0) {          // rows start on 16-byte boundaries
 #pragma unroll
-        for (int sl = 0; sl < SSP_DIRECT; ++sl) { a1[sl] = 0.0; a2[sl] = 0.0; }
-        auto consume = [&](int it, bool ok, const double (&x)[DT]) {
-          if (ok) {
+                  for (int j = 0; j < DT; j += 2) {
+                    double2 v = make_double2(0.0, 0.0);
+                    if (j < D) v = __ldg(reinterpret_cast<const double2 *>(row + j));
+                    x[j] = v.x; x[j + 1] = v.y;
+                  }
+                } else {
 #pragma unroll
-            for (int sl = 0; sl < SSP_DIRECT; ++sl) {
-              if (sl < nT) {
-                const double *wv = w_sh + sl * DT;
-                const int site = site_sh[sl];
-                double eta = 0.0, xs = 0.0;
-#pragma unroll
-                for (int j = 0; j < DT; ++j) { eta = fma(wv[j], x[j], eta); xs = (j == site) ? x[j] : xs; }
-                const double v_new = fma(delta_sh[sl], xs, eta);
-                const double d = ssp_dllh(v_new, eta, a.cf, exp_base, log_base);
-                a1[sl] += d; a2[sl] = fma(d, d, a2[sl]);
-              }
-            }
-          }
-          const int g = it / ppr2;
-          if (it - g * ppr2 == ppr2 - 1) {        // the round's last position of this thread: warp sums -> scratch
-#pragma unroll
-            for (int sl = 0; sl < SSP_DIRECT; ++sl) {
-              if (sl < nT) {
-                const double u1 = warp_sum(a1[sl]), u2 = warp_sum(a2[sl]);
-                if (lane == 0) {
-                  double *dst = part_sh + (((size_t)g * SSP_DIRECT + sl) * SSP_WARPS + warp) * 2;
-                  dst[0] = u1; dst[1] = u2;
+                  for (int j = 0; j < DT; ++j) x[j] = j < D ? __ldg(row + j) : 0.0;
                 }
-                a1[sl] = 0.0; a2[sl] = 0.0;
+              }
+              return ok;
+            };
+            auto consume = [&](bool ok, const double (&x)[DT]) {
+              if (!ok) return;
+#pragma unroll
+              for (int sl = 0; sl < SSP_DIRECT; ++sl) {
+                if (sl < nT) {
+                  const double *wv = w_sh + sl * DT;
+                  const int site = site_sh[sl];
+                  double eta = 0.0, xs = 0.0;
+#pragma unroll
+                  for (int j = 0; j < DT; ++j) { eta = fma(wv[j], x[j], eta); xs = (j == site) ? x[j] : xs; }
+                  const double v_new = fma(delta_sh[sl], xs, eta);
+                  const double d = ssp_dllh(v_new, eta, a.cf, exp_base, log_base);
+                  a1[sl] += d; a2[sl] = fma(d, d, a2[sl]);
+                }
+              }
+            };
+            double xa[DT], xb[DT];
+            bool oka = fetch(0, xa), okb = false;
+            for (int c = 0; c < n_chunks; c += 2) {                            // the next chunk's rows are in flight
+              okb = fetch(c + 1, xb);
+              consume(oka, xa);
+              if (c + 1 < n_chunks) {
+                oka = fetch(c + 2, xa);
+                consume(okb, xb);
               }
             }
+            __syncwarp();                                                      // before the list is rewritten
           }
-        };
-        double xa[DT], xb[DT];
-        bool oka = fetch(0, xa), okb = false;
-        for (int it = 0; it < n_items; it += 2) {
-          okb = fetch(it + 1, xb);
-          consume(it, oka, xa);
-          if (it + 1 < n_items) {
-            oka = fetch(it + 2, xa);
-            consume(it + 1, okb, xb);
+#pragma unroll
+          for (int sl = 0; sl < SSP_DIRECT; ++sl) {
+            if (sl < nT) {
+              const double u1 = warp_sum(a1[sl]), u2 = warp_sum(a2[sl]);
+              if (lane == 0) {
+                double *dst = part_sh + (((size_t)g * SSP_DIRECT + sl) * SSP_WARPS + sub) * 2;
+                dst[0] = u1; dst[1] = u2;
+              }
+            }
           }
         }
         __syncthreads();
@@ -316,8 +336,7 @@ __global__ void __launch_bounds__(SSP_THREADS, 2) ss_persistent_kernel(const SSP
           const int comp = e & 1, sl = (e >> 1) % nT, g = (e >> 1) / nT;
           const double *src = part_sh + (((size_t)g * SSP_DIRECT + sl) * SSP_WARPS) * 2 + comp;
           double sum = 0.0;
-#pragma unroll
-          for (int wv = 0; wv < SSP_WARPS; ++wv) sum += src[wv * 2];
+          for (int wv = 0; wv < wpr; ++wv) sum += src[wv * 2];                 // the round's warps, in position order
           a.partial[(((size_t)blockIdx.x * SSP_GMAX + g) * (size_t)P + (size_t)pid_sh[sl]) * 2 + comp] = sum;
         }
         __syncthreads();
@@ -427,11 +446,20 @@ __global__ void __launch_bounds__(SSP_THREADS, 2) ss_persistent_kernel(const SSP
       for (int ai = blockIdx.x; ai < nA; ai += gridDim.x) {          // CTA-uniform loop
         const int64_t p = act_sh[ai];
         // every warp sums the CTAs' partials of some rounds (fixed order: lane-strided, then the shuffle tree)
+        // (a lane's loads of a round are issued together, 12 at a time: one L2 round trip instead of a chain of them)
         for (int g = warp; g < G; g += SSP_WARPS) {
           double s1 = 0.0, s2 = 0.0;
-          for (int bb = lane; bb < (int)gridDim.x; bb += 32) {
-            const double2 v = __ldcg(reinterpret_cast<const double2 *>(a.partial + (((size_t)bb * SSP_GMAX + g) * (size_t)P + (size_t)p) * 2));
-            s1 += v.x; s2 += v.y;
+          for (int b0 = 0; b0 < (int)gridDim.x; b0 += 32 * 12) {
+            double2 v[12];
+#pragma unroll
+            for (int k = 0; k < 12; ++k) {
+              const int bb = b0 + k * 32 + lane;
+              v[k] = make_double2(0.0, 0.0);
+              if (bb < (int)gridDim.x)
+                v[k] = __ldcg(reinterpret_cast<const double2 *>(a.partial + (((size_t)bb * SSP_GMAX + g) * (size_t)P + (size_t)p) * 2));
+            }
+#pragma unroll
+            for (int k = 0; k < 12; ++k) { s1 += v[k].x; s2 += v[k].y; }      // the same order as a lane-strided loop
           }
           s1 = warp_sum(s1); s2 = warp_sum(s2);
           if (lane == 0) { acc_sh[2 * g] = s1; acc_sh[2 * g + 1] = s2; }

@@ -399,7 +399,33 @@ __global__ void __launch_bounds__(SSP_THREADS, 2) ss_persistent_kernel(const SSP
           const int g = i / ppr;
           const int n_rows = cnt_sh[buf * (SSP_WARPS + 1) + SSP_WARPS];
           const int n_chunks = (n_rows + 31) >> 5;
-          if (n_chunks > 0) {
+          if (n_rows > 0 && n_rows <= 16) {
+            // a thin pass (sharded observations: 1/R of a pass's positions are local): the two half-warps take the
+            // same <= 16 rows and DIFFERENT particles.  The 16-lane shuffle tree gives bit for bit what the 32-lane
+            // tree gives with its upper half zero, so the sums do not depend on which mapping a pass used.
+            const int r = lane & 15, hsel = lane >> 4;
+            const bool valid = r < n_rows;
+            const double *row = rows_sh + (size_t)buf * SSP_ROWS * (DT + 1) + (valid ? r : 0) * (DT + 1);
+            double x[DT];
+#pragma unroll
+            for (int j = 0; j < DT; ++j) x[j] = (valid && j < D) ? row[j] : 0.0;
+            for (int slot0 = warp * 2; slot0 < nT; slot0 += SSP_WARPS * 2) {
+              const int slot = slot0 + hsel;
+              const bool live = valid && slot < nT;
+              const double *wv = w_sh + (slot < nT ? slot : 0) * DT;
+              double eta = 0.0;
+#pragma unroll
+              for (int j = 0; j < DT; ++j) eta = fma(wv[j], x[j], eta);
+              const double xs = live ? row[site_sh[slot]] : 0.0;
+              const double v_new = fma(live ? delta_sh[slot] : 0.0, xs, eta);
+              double d = ssp_dllh(v_new, eta, a.cf, exp_base, log_base);
+              if (!live) d = 0.0;
+              double u1 = d, u2 = d * d;
+#pragma unroll
+              for (int o = 8; o > 0; o >>= 1) { u1 += __shfl_xor_sync(0xffffffffu, u1, o); u2 += __shfl_xor_sync(0xffffffffu, u2, o); }
+              if (r == 0 && slot < nT) { part_sh[slot * 2] = u1; part_sh[slot * 2 + 1] = u2; }
+            }
+          } else if (n_chunks > 0) {
             // warps_per_chunk warps share a 32-row chunk and split the tile's particles between them
             const int wpc = SSP_WARPS / n_chunks;
             const int c = warp / wpc, sub = warp - c * wpc;

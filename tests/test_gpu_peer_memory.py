@@ -121,6 +121,62 @@ def _ssmh_worker(rank, world, port, out_q):
     dist.destroy_process_group()
 
 
+def _small_state_worker(rank, world, port, out_q):
+    """models whose whole state is particle-minor (normal-normal; a compiled program with three sites): the fused
+    cooperative resample kernel (default) or, with VK_P2P_UNFUSED=1 in the environment, the separate kernels"""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    os.environ.setdefault("VK_P2P_TIMEOUT_S", "60")
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import venturecxx_b200 as vb
+    from venturecxx_b200.compiler import CompiledModel
+    from venturecxx_b200.distributed import ShardedTraceSet
+    dev = _device_for(rank)
+    torch.cuda.set_device(dev)
+    P_local = 5000 + 3
+    P = world * P_local
+    prog = [("assume", "a", ["normal", 0.0, 2.0]), ("assume", "b", ["normal", "a", 1.0]), ("assume", "s", ["gamma", 2.0, 2.0])] + \
+           [("observe", ["normal", ["add", "a", "b"], "s"], 0.3 * i) for i in range(5)]
+    res = {}
+    for name, make in (("normal", lambda: vb.NormalNormalModel(0.5, 2.0, 1.5, 8)), ("program", lambda: CompiledModel(prog))):
+        model = make()
+        sh = ShardedTraceSet(model, P_local, seed=91, device=dev)
+        sh.enable_peer_memory()
+        ref = vb.B200TraceSet(model, P, seed=91, device=dev)
+        for it in range(4):
+            if name == "normal":
+                sh.observe(1.0 + it); ref.observe(1.0 + it)
+                sh.incorporate(return_increments=False); ref.incorporate()
+            else:
+                sh.likelihood_weight(); ref.likelihood_weight()
+            sh.resample(mode="systematic")
+            timed_out, lse = sh.peer_status()
+            assert not timed_out
+            ref.resample(P, mode="systematic")
+            dist.barrier()
+            for site in range(ref.num_sites()):
+                a = sh.read_site(site)
+                b = ref.read_site(site)[rank * P_local:(rank + 1) * P_local]
+                assert np.array_equal(a, b), (name, it, site, rank)
+            np.testing.assert_allclose(sh.log_weights, ref.log_weights[rank * P_local:(rank + 1) * P_local], rtol=1e-12)
+        res[name] = "bit-identical"
+        dist.barrier()
+        sh.local.close(); ref.close()
+    out_q.put((rank, res))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _unfused_hmm_worker(rank, world, port, out_q):
+    os.environ["VK_P2P_UNFUSED"] = "1"          # read once per process, at the first sharded resample
+    _hmm_worker(rank, world, port, out_q)
+
+
+def _unfused_small_state_worker(rank, world, port, out_q):
+    os.environ["VK_P2P_UNFUSED"] = "1"
+    _small_state_worker(rank, world, port, out_q)
+
+
 def _run(worker, world=2):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
@@ -141,6 +197,20 @@ def _run(worker, world=2):
 def test_peer_memory_resample_two_ranks():
     res = _run(_hmm_worker)
     assert all(r[1] == {"systematic": "bit-identical", "multinomial": "bit-identical"} for r in res)
+
+
+def test_peer_memory_resample_small_state_models():
+    res = _run(_small_state_worker)
+    assert all(r[1] == {"normal": "bit-identical", "program": "bit-identical"} for r in res)
+
+
+def test_peer_memory_resample_separate_kernels():
+    """VK_P2P_UNFUSED=1: tile sums, offspring and gather as three launches (also what multinomial mode, wide rows and
+    very large shards use)"""
+    res = _run(_unfused_hmm_worker)
+    assert all(r[1] == {"systematic": "bit-identical", "multinomial": "bit-identical"} for r in res)
+    res = _run(_unfused_small_state_worker)
+    assert all(r[1] == {"normal": "bit-identical", "program": "bit-identical"} for r in res)
 
 
 def test_peer_memory_subsampled_mh_two_ranks():

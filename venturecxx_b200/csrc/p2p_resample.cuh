@@ -867,8 +867,8 @@ void p2p_resample(vk_particles *h, int mode) {
     p2p_gather_slots_kernel<2, 4><<<grid_for((P + 1) / 2, 256, h->sm_count, 3), 256, 0, st>>>(anc_mine, P, s->tab.p, s->par.p, pa);
   else
     p2p_gather_kernel<<<grid_for(work, 256, h->sm_count, 8), 256, 0, st>>>(anc_mine, P, s->tab.p, s->par.p, pa);
-  }
   h->prof.mark(st, "p2p_gather");
+  }
   VK_CUDA(cudaGetLastError());
   for (auto &a : arrs) { void *t = *a.cur; *a.cur = *a.alt; *a.alt = t; }
   h->model->after_resample();

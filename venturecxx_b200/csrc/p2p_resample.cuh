@@ -56,6 +56,7 @@ struct P2PArrays {                     // by-value kernel argument of the gather
   int world, rank;
   long long timeout_ns;
   volatile int *err_host;
+  unsigned long long *prof;            // VK_P2P_PROFILE=1: phase times of CTA 0 of the fused kernel (ns, accumulated)
 };
 struct P2P {
   int world = 0, rank = 0, n_arrays = 0;
@@ -70,6 +71,7 @@ struct P2P {
   DevBuf<int32_t> anc_g;                         // [2][P]
   DevBuf<P2PTables> tab;
   DevBuf<P2PParams> par;
+  DevBuf<unsigned long long> prof;               // VK_P2P_PROFILE=1
   DevBuf<unsigned long long> bar;                // arrival counter of the fused resample kernel's grid barrier (monotone)
   unsigned long long bar_count = 0;
   DevBuf<double> ss_mail;                        // [2][P2P_MAX_WORLD][ss_stride]
@@ -416,6 +418,9 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
   __shared__ double se_sh;
   __shared__ int cur_sh[P2P_MAX_WORLD];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const bool prof = arrs.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
+  unsigned long long tp = prof ? p2p_now_ns() : 0ull;
+#define P2P_PROF(slot) do { if (prof) { const unsigned long long now_ = p2p_now_ns(); arrs.prof[slot] += now_ - tp; tp = now_; } } while (0)
   // ---- exchange 0 (sent from the tail of the kernel that wrote the weights)
   if (threadIdx.x < 32) {
     double ra, rb, mx, mn, nanf;
@@ -426,6 +431,7 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
   }
   __syncthreads();
   if (!ok_sh) return;
+  P2P_PROF(0);
   const double m = mm_sh[0];
   // ---- fixed-point weights of this thread's particles (thread-contiguous, as p2p_offspring_kernel)
   const int64_t base = (int64_t)blockIdx.x * (SCAN_THREADS * ITEMS) + (int64_t)threadIdx.x * ITEMS;
@@ -458,7 +464,9 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
     if (lane == 0) tile_exp[blockIdx.x] = se;
   }
   // ---- every tile total is in memory
+  P2P_PROF(1);
   if (!p2p_grid_barrier(bar, bar_target - gridDim.x, par, arrs.timeout_ns, arrs.err_host)) return;
+  P2P_PROF(2);
   const int n_tiles = (int)gridDim.x;
   {
     uint64_t pre = 0, tot = 0;
@@ -481,6 +489,7 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
     }
     __syncthreads();
   }
+  P2P_PROF(3);
   // ---- exchange 1: CTA 0 sends (sum exp, live buffer, mass); every CTA collects
   if (blockIdx.x == 0 && threadIdx.x < 32) p2p_send_warp(x1, 1, se_sh, (double)x1.my_cur_idx, tot_sh[1]);
   if (threadIdx.x < 32) {
@@ -501,6 +510,7 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
   }
   __syncthreads();
   if (!ok_sh) return;
+  P2P_PROF(4);
   const uint64_t W = tot_sh[1];
   const double even = p2p_lse(x1.n_total, mm_sh[0], mm_sh[1], mm_sh[2], se_sh) - arrs.log_p_total;
   // ---- offspring (p2p_offspring_kernel's loop on the registers)
@@ -525,14 +535,20 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
       k_lo = k_hi;
     }
   }
+  P2P_PROF(5);
   // ---- every ancestor this rank produces is stored: the gather below polls only for what peers still owe (spinning
   // on local ancestors while neighbouring CTAs are still in their offspring loop costs more than this barrier:
   // 62.7 -> 59.7 us per step at a world of one)
   if (!p2p_grid_barrier(bar, bar_target, par, arrs.timeout_ns, arrs.err_host)) return;
+  P2P_PROF(6);
   // ---- gather of this CTA's share of the child slots
   if (!p2p_gather_slots<GS, MAXU>(anc_mine, n, par, arrs, tab, cur_sh, even)) {
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) arrs.lw[t] = NAN;
   }
+  __syncthreads();
+  P2P_PROF(7);
+  if (prof) arrs.prof[8] += 1;
+#undef P2P_PROF
 }
 
 // Step D: slot s copies its ancestor's state from the owning rank's live buffers (NVLink peer loads; rows that
@@ -829,6 +845,9 @@ void p2p_resample(vk_particles *h, int mode) {
     if (!coop || (int64_t)per_sm * h->sm_count < fused_tiles) fk = nullptr;
   }
   if (fk) {
+    static const bool prof_env = getenv("VK_P2P_PROFILE") != nullptr;
+    if (prof_env && !s->prof.p) { s->prof.alloc(16); VK_CUDA(cudaMemsetAsync(s->prof.p, 0, s->prof.bytes(), st)); }
+    pa.prof = s->prof.p;
     if (!s->bar.p) { s->bar.alloc(2); VK_CUDA(cudaMemsetAsync(s->bar.p, 0, s->bar.bytes(), st)); s->bar_count = 0; }
     s->bar_count += 2ull * (unsigned long long)fused_tiles;      // two grid barriers per launch
     const double *lw_in = h->lw.p; double *red_p = h->red.p; uint64_t *ts_p = h->red_u.p; double *te_p = h->tile_exp.p;
@@ -886,6 +905,13 @@ void p2p_status(vk_particles *h, int *err_out, double *lse_out) {
 }
 
 void p2p_release(vk_particles *h) {
+  if (P2P *sp = p2p_of(h)) if (sp->prof.p) {     // phase times of CTA 0 of the fused resample kernel
+    unsigned long long pr[16];
+    if (cudaMemcpy(pr, sp->prof.p, sizeof pr, cudaMemcpyDeviceToHost) == cudaSuccess && pr[8])
+      fprintf(stderr, "[vk p2p profile rank %d] fused launches %llu | us per launch: collect0 %.2f weights+tile %.2f barrier1 %.2f tile totals %.2f "
+                      "send1+collect1 %.2f offspring %.2f barrier2 %.2f gather %.2f\n", sp->rank, pr[8], pr[0] * 1e-3 / pr[8], pr[1] * 1e-3 / pr[8],
+              pr[2] * 1e-3 / pr[8], pr[3] * 1e-3 / pr[8], pr[4] * 1e-3 / pr[8], pr[5] * 1e-3 / pr[8], pr[6] * 1e-3 / pr[8], pr[7] * 1e-3 / pr[8]);
+  }
   P2P *s = p2p_of(h);
   if (!s) return;
   for (void *p : s->imported) cudaIpcCloseMemHandle(p);

@@ -194,6 +194,26 @@ def run_subsampled(prog, seed, P, K, Nbatch, k0, eps, block="one", make_consiste
     return out
 
 
+def run_check_applicability(prog):
+    """(subsampled_mh_check_applicability default one) on Lite: the warning classes it raises, in order"""
+    import warnings
+    from make_lite_chains import infer_exp
+    assumes = [d for d in prog if d[0] == "assume"]
+    observes = [d for d in prog if d[0] == "observe"]
+    mdl = Model()
+    install(mdl, 3, 0)
+    mdl.tape.begin(0, 0)
+    for d in assumes:
+        mdl.assume(d[1], d[2])
+    for d in observes:
+        mdl.observe(d[1], box(d[2]))
+    mdl.t.makeConsistent()
+    with warnings.catch_warnings(record=True) as caught:
+        warnings.simplefilter("always")
+        mdl.t.primitive_infer(infer_exp("subsampled_mh_check_applicability", "default", "one", 1))
+    return [[type(w.message).__name__, str(w.message)] for w in caught if "Subsampled" in type(w.message).__name__]
+
+
 def main():
     fixture = {}
     progs = programs()
@@ -205,6 +225,7 @@ def main():
     fixture["normal_observes_ssmh"] = run_subsampled(progs["normal_observes"], 43, 5, 40, 5, 2, 0.05)
     fixture["scaled_ssmh"] = run_subsampled(progs["scaled"], 47, 5, 60, 4, 2, 0.1, make_consistent=True)
     fixture["invalid_border_ssmh"] = run_subsampled(progs["invalid_border"], 53, 2, 8, 1, 1, 0.1)
+    fixture["check_applicability"] = dict((k, run_check_applicability(progs[k])) for k in ("normal_observes", "scaled", "invalid_border"))
     fixture["_source"] = ("reference Lite backend (py3 rendering by oracle/lite_py3/build_lite_py3.py) run by "
                           "tests/golden/make_program_chains.py; numpy %s" % np.__version__)
     path = os.path.join(HERE, "program_chains.json")

@@ -291,3 +291,33 @@ def test_compiled_subsampled_mh_with_epsilon_zero_is_exact_mh():
     np.testing.assert_array_equal(st_[:, 0], acc)
     np.testing.assert_array_equal(st_[:, 1], 80.0)
     np.testing.assert_allclose(a.read_site(0), b.read_site(0), rtol=1e-15)
+
+
+def test_subsampled_mh_companion_operators():
+    """`subsampled_mh_check_applicability` warns as the reference does and changes nothing (dispatch.py:153-157);
+    `subsampled_mh_make_consistent` has nothing to refresh on the device and reports the global sections' node counts"""
+    import warnings
+    from venturecxx_b200.exception import SubsampledScaffoldNotApplicableWarning, SubsampledScaffoldNotEffectiveWarning
+    case = golden("program_chains.json")
+    ts = vb.B200TraceSet(CompiledModel([tuple(d) for d in case["invalid_border_ssmh"]["program"]]), 8, seed=2)
+    before = sites_of(ts).copy()
+    with warnings.catch_warnings(record=True) as caught:
+        warnings.simplefilter("always")
+        out = ts.primitive_infer(["subsampled_mh_check_applicability", "default", "one", 1])
+    assert [type(w.message) for w in caught] == [SubsampledScaffoldNotApplicableWarning] and not out.any()
+    np.testing.assert_array_equal(sites_of(ts), before)
+    ts = vb.B200TraceSet(CompiledModel([tuple(d) for d in case["scaled_ssmh"]["program"]]), 8, seed=2)
+    with warnings.catch_warnings(record=True) as caught:
+        warnings.simplefilter("always")
+        ts.primitive_infer(["subsampled_mh_check_applicability", "default", "one", 1])
+        ts.primitive_infer(["subsampled_mh_check_applicability", "default", 0, 1])
+    assert [type(w.message) for w in caught] == [SubsampledScaffoldNotEffectiveWarning]
+    np.testing.assert_array_equal(ts.primitive_infer(["subsampled_mh_make_consistent", "default", "one", False, 0, False, 1]), 4.0)
+    blr = vb.B200TraceSet(vb.LogisticRegressionModel(3, 16), 8, seed=2)
+    with warnings.catch_warnings(record=True) as caught:
+        warnings.simplefilter("always")
+        blr.primitive_infer(["subsampled_mh_check_applicability", "default", "one", 1])
+    assert not caught
+    np.testing.assert_array_equal(blr.primitive_infer(["subsampled_mh_make_consistent", "default", 1, False, 0, False, 1]), 3.0)
+    with pytest.raises(vb.VentureException):
+        vb.B200TraceSet(vb.NormalNormalModel(0.0, 1.0, 1.0, 2), 4).primitive_infer(["subsampled_mh_check_applicability", "default", "one", 1])

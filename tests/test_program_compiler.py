@@ -173,3 +173,25 @@ def test_compiled_model_speaks_the_interchange_format():
     assert [v["value"] for v in vals] == [0.25, True, False]
     np.testing.assert_array_equal(m.sites_from_random_values([], vals), [0.25])
     assert oracle is not None
+
+
+def test_check_applicability_follows_the_reference():
+    """SubsampledBlockScaffoldIndexer.checkApplicability (infer/subsampled_mh.py:222-262): which warning, for which block.
+    The fixture holds what Lite itself warned on the three programs (tests/golden/make_program_chains.py)."""
+    case = golden("program_chains.json")
+    lite = case["check_applicability"]
+    good = CompiledModel([tuple(d) for d in case["normal_observes_ssmh"]["program"]])
+    assert good.subsampled_applicability("one") == (True, None, "") and lite["normal_observes"] == []
+    bad = CompiledModel([tuple(d) for d in case["invalid_border_ssmh"]["program"]])
+    ok, kind, msg = bad.subsampled_applicability("one")
+    assert not ok and [kind, "Invalid global border."] == lite["invalid_border"][0] and "Invalid global border" in msg
+    # `scaled`: mu and s have borders, lo and x have none.  Lite stops at mu with "The scaffold section is not consistent
+    # with the entire scaffold": its OrderedSet.__eq__ (backend/lite/orderedset.py:83-91) also compares the ORDER of the
+    # two node sets, which here hold the same five nodes in different orders -- while subsampled_mh on that block runs
+    # and is pinned decision for decision above.  The compiler reports what the structure says: no border at `lo`.
+    m = CompiledModel([tuple(d) for d in case["scaled_ssmh"]["program"]])
+    assert lite["scaled"] == [["SubsampledScaffoldNotApplicableWarning", "The scaffold section is not consistent with the entire scaffold."]]
+    assert m.subsampled_applicability(0) == (True, None, "") and m.subsampled_applicability(1)[0]
+    ok, kind, msg = m.subsampled_applicability("one")
+    assert not ok and kind == "SubsampledScaffoldNotEffectiveWarning" and "same as mh" in msg
+    assert m.subsampled_global_nodes("one") == 3.0 + 1.0 and m.subsampled_global_nodes(0) == 3.0

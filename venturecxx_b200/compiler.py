@@ -593,6 +593,25 @@ class CompiledModel(object):
         raise VentureException("invalid_argument", "a compiled program holds its observations: extend the directive list "
                                                    "(CompiledModel.extended) instead of observing into the batch")
 
+    # -- subsampled MH ------------------------------------------------------------------------------------------
+    def subsampled_applicability(self, block):
+        """SubsampledBlockScaffoldIndexer.checkApplicability (infer/subsampled_mh.py:222-262) from the compiler's
+        analysis: block "one" walks every block and stops at the first that fails.  -> (ok, warning class name, message)"""
+        sites = range(self.prog.n_sites) if block in ("one", "each", -1, -3) else [int(block)]
+        for k in sites:
+            ss = self.prog.subsampled[k]
+            if ss["kind"] == 0:
+                return False, "SubsampledScaffoldNotEffectiveWarning", "No global border found. subsampled_mh will behave the same as mh."
+            if ss["kind"] == 2:
+                return False, "SubsampledScaffoldNotApplicableWarning", ss["reason"]
+        return True, None, ""
+
+    def subsampled_global_nodes(self, block):
+        """what SubsampledMHOperator.makeConsistent returns for a fresh operator (:411-441): the node counts of the global
+        sections that have a border, summed over the blocks"""
+        sites = range(self.prog.n_sites) if block in ("one", "each", -1, -3) else [int(block)]
+        return float(sum(self.prog.subsampled[k]["nodes"] for k in sites if self.prog.subsampled[k]["kind"] == 1))
+
     # -- interchange.py ---------------------------------------------------------------------------------------
     def program(self, obs):
         return list(self.compiler.directives)

@@ -27,3 +27,16 @@ class VentureException(Exception):
         return "*** %s: %s\n%s" % (self.exception, self.message, self.data)
 
     __repr__ = __str__
+
+
+# infer/subsampled_mh.py:26-28 (python/lib/exception.py in the reference): what subsampled_mh_check_applicability warns with
+class SubsampledScaffoldNotEffectiveWarning(UserWarning):
+    pass
+
+
+class SubsampledScaffoldNotApplicableWarning(UserWarning):
+    pass
+
+
+class SubsampledScaffoldStaleNodesWarning(UserWarning):
+    pass

@@ -75,6 +75,14 @@ class LogisticRegressionModel(Model):
             raise _lib.VentureException("invalid_argument", "X and y disagree on the number of observations")
         _lib.call("vk_blr_observe", h, _lib.ptr(X), _lib.ptr(y), y.size)
 
+    # subsampled MH (backend/lite/infer/subsampled_mh.py:326-368): every weight's global border is the `(array w_0 ...)`
+    # node and its children are the N `vector_dot` applications, one local section per observation
+    def subsampled_applicability(self, block):
+        return True, None, ""
+
+    def subsampled_global_nodes(self, block):
+        return 3.0 * (self.D if block in ("one", "each", -1, -3) else 1)      # per block: the weight, its lookup, the array
+
     def _rows(self, obs):
         for X, y in obs:
             X = np.asarray(X, dtype=np.float64).reshape(-1, self.D)

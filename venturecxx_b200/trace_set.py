@@ -246,6 +246,29 @@ class B200TraceSet(object):
                     "subsampled_mh takes (scope block Nbatch k0 epsilon useDeltaKernels deltaKernelArgs "
                     "updateValues transitions)")
             return self.subsampled_mh(*exp[1:])
+        if op == "subsampled_mh_check_applicability":
+            # dispatch.py:153-157: warns, changes nothing, reports 0 nodes
+            import warnings
+            from . import exception as exc
+            self._scope_block(exp[1], exp[2])
+            check = getattr(self.model, "subsampled_applicability", None)
+            if check is None:
+                raise VentureException("invalid_argument", "subsampled_mh is not compiled for this model")
+            ok, kind, msg = check(exp[2])
+            if not ok:
+                warnings.warn(msg, getattr(exc, kind))
+            return np.zeros(self.n_particles)
+        if op == "subsampled_mh_make_consistent":
+            # SubsampledMHOperator.makeConsistent (infer/subsampled_mh.py:411-441) refreshes the local sections an accepted
+            # proposal left stale.  The device keeps no per-section values (sections are evaluated from the current global
+            # value; the logistic-regression model's logit cache is only MARKED stale and rebuilt by its next reader), so
+            # there is nothing to do but report the node count.  (The reference's own dispatch entry, dispatch.py:158-161,
+            # reads an unbound `extra` and raises NameError.)
+            self._scope_block(exp[1], exp[2])
+            nodes = getattr(self.model, "subsampled_global_nodes", None)
+            if nodes is None:
+                raise VentureException("invalid_argument", "subsampled_mh is not compiled for this model")
+            return np.full(self.n_particles, nodes(exp[2]))
         raise VentureException("invalid_argument", "operator %r is not on the B200 path" % (op,))
 
     def resimulation_mh(self, scope, block, transitions, return_accepts=False, out=None):

@@ -212,6 +212,10 @@ def test_plugin_binds_foreign_inference_sps_with_the_reference_signatures_cpu():
     assert batch.n_particles == 80 and e.num_traces() == 1      # the Lite trace set of the engine is untouched
     _, ans = e.infer(ref_engine.program("(b200_subsampled_mh default one 16 3 0.01 false 0 false 2)"))
     assert batch.calls[-1] == ("primitive_infer", ["subsampled_mh", "default", "one", 16, 3, 0.01, False, 0, False, 2])
+    e.infer(ref_engine.program("(do (b200_subsampled_mh_check_applicability default one 1) "
+                               "(b200_subsampled_mh_make_consistent default one false 0 false 1))"))
+    assert batch.calls[-2] == ("primitive_infer", ["subsampled_mh_check_applicability", "default", "one", 1])
+    assert batch.calls[-1] == ("primitive_infer", ["subsampled_mh_make_consistent", "default", "one", False, 0, False, 1])
     e.infer(ref_engine.program("(do (b200_slice default 0 0.5 10 3) (b200_pgibbs (quote seq) ordered 8 2))"))
     assert batch.calls[-2] == ("primitive_infer", ["slice", "default", 0, 0.5, 10, 3])
     assert batch.calls[-1] == ("primitive_infer", ["pgibbs", "seq", "ordered", 8, 2])

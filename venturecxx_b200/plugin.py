@@ -128,6 +128,9 @@ def inference_sps(plugin):
 
     def subsampled(*operands):
         stats = ts.primitive_infer(["subsampled_mh"] + [_python_value(o) for o in operands])
+        nodes = getattr(ts, "last_mean_nodes", None)          # what the reference returns: nodes touched per transition
+        if nodes is not None:
+            return [float(v) for v in nodes]
         return [float(r[0]) for r in stats] if getattr(stats, "ndim", 1) == 2 else list(stats)
 
     def resample(particles):
@@ -160,6 +163,9 @@ def inference_sps(plugin):
         "func_pgibbs": inf.sequenced_sp(transition("func_pgibbs"), inf.par_transition_oper_type([t.IntegerType("particles : int")])),
         # :678-694
         "subsampled_mh": inf.sequenced_sp(subsampled, inf.transition_oper_type(subsampled_extra)),
+        # :696-720
+        "subsampled_mh_check_applicability": inf.sequenced_sp(transition("subsampled_mh_check_applicability"), inf.transition_oper_type()),
+        "subsampled_mh_make_consistent": inf.sequenced_sp(transition("subsampled_mh_make_consistent"), inf.transition_oper_type(subsampled_extra[3:])),
         # :536-551
         "resample": inf.sequenced_sp(resample, inf.infer_action_maker_type([t.IntegerType("particles : int")])),
         # :602-606

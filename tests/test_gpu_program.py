@@ -321,3 +321,13 @@ def test_subsampled_mh_companion_operators():
     np.testing.assert_array_equal(blr.primitive_infer(["subsampled_mh_make_consistent", "default", 1, False, 0, False, 1]), 3.0)
     with pytest.raises(vb.VentureException):
         vb.B200TraceSet(vb.NormalNormalModel(0.0, 1.0, 1.0, 2), 4).primitive_infer(["subsampled_mh_check_applicability", "default", "one", 1])
+    # mh_kernel_update (dispatch.py:145-148): the same chain as resimulation_mh on the same draws
+    prog = [tuple(d) for d in case["normal_observes_ssmh"]["program"]]
+    a, b = vb.B200TraceSet(CompiledModel(prog), 16, seed=4), vb.B200TraceSet(CompiledModel(prog), 16, seed=4)
+    for t_ in (a, b):
+        t_.incorporate()
+        t_.rng_step = 50
+    na = a.primitive_infer(["mh_kernel_update", "default", "one", False, 0, True, 20])
+    nb = b.primitive_infer(["resimulation_mh", "default", "one", 20])
+    np.testing.assert_array_equal(a.read_site(0), b.read_site(0))
+    np.testing.assert_array_equal(na, nb)

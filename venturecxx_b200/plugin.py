@@ -166,6 +166,8 @@ def inference_sps(plugin):
         # :696-720
         "subsampled_mh_check_applicability": inf.sequenced_sp(transition("subsampled_mh_check_applicability"), inf.transition_oper_type()),
         "subsampled_mh_make_consistent": inf.sequenced_sp(transition("subsampled_mh_make_consistent"), inf.transition_oper_type(subsampled_extra[3:])),
+        # :722-727
+        "mh_kernel_update": inf.sequenced_sp(transition("mh_kernel_update"), inf.transition_oper_type(subsampled_extra[3:])),
         # :536-551
         "resample": inf.sequenced_sp(resample, inf.infer_action_maker_type([t.IntegerType("particles : int")])),
         # :602-606

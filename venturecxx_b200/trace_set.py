@@ -225,6 +225,13 @@ class B200TraceSet(object):
             if len(exp) != 4:
                 raise VentureException("invalid_argument", "%s takes (scope block transitions)" % op)
             return self.resimulation_mh(exp[1], exp[2], exp[3])
+        if op == "mh_kernel_update":
+            # dispatch.py:145-148, 308-313: mh over a scaffold built with (useDeltaKernels deltaKernelArgs updateValues).  None of
+            # the compiled SPs has a delta kernel (only MVNormalOutputPSP does, continuous.py:121-124) and no value on the
+            # device is ever stale, so this is resimulation_mh
+            if len(exp) != 7:
+                raise VentureException("invalid_argument", "mh_kernel_update takes (scope block useDeltaKernels deltaKernelArgs updateValues transitions)")
+            return self.resimulation_mh(exp[1], exp[2], exp[6])
         if op == "gibbs":
             if len(exp) != 4:
                 raise VentureException("invalid_argument", "gibbs takes (scope block transitions)")

@@ -220,6 +220,7 @@ __global__ void __launch_bounds__(SSP_THREADS, 2) ss_persistent_kernel(const SSP
       const int n_pass = G * ppr;
       const bool direct = DT <= 16 && nA <= SSP_DIRECT;
       SSP_PROF(0);
+      const unsigned long long te0 = (a.prof != nullptr && tid == 0) ? p2p_now_ns() : 0ull;
       if (prof) { a.prof[direct ? 9 : 8] += 1; a.prof[direct ? 11 : 10] += (unsigned long long)G; a.prof[12] += (unsigned long long)nA; }
       if (direct) {
         // ---- few stragglers: ONE THREAD PER POSITION.  Rows go from L2/HBM straight into registers (the next
@@ -465,6 +466,7 @@ __global__ void __launch_bounds__(SSP_THREADS, 2) ss_persistent_kernel(const SSP
         }
         __syncthreads();       // before w_sh / pid_sh of the next tile are written
       }
+      if (a.prof != nullptr && tid == 0) a.prof[16 + 2 * blockIdx.x + (direct ? 1 : 0)] += p2p_now_ns() - te0;
       SSP_PROF(direct ? 2 : 1);
       if (!ssp_grid_barrier(a, epoch)) return;
       SSP_PROF(3);

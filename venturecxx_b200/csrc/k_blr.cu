@@ -760,7 +760,7 @@ struct BLRModel : Model {
     VK_CUDA(cudaMemsetAsync(ssp_bar.p, 0, ssp_bar.bytes(), h->stream));
     static const bool profile = getenv("VK_SS_PROFILE") != nullptr;       // phase times of CTA 0, printed per call
     if (profile) {
-      if (!ssp_prof.p) ssp_prof.alloc(16);
+      if (!ssp_prof.p) ssp_prof.alloc(16 + 2 * 1024);
       VK_CUDA(cudaMemsetAsync(ssp_prof.p, 0, ssp_prof.bytes(), h->stream));
       a.prof = ssp_prof.p;
     }
@@ -771,9 +771,19 @@ struct BLRModel : Model {
     VK_CUDA(cudaGetLastError());
     eta_dirty = true;
     if (profile) {
-      unsigned long long pr[16];
+      static unsigned long long pr[16 + 2 * 1024];
       VK_CUDA(cudaMemcpyAsync(pr, ssp_prof.p, sizeof pr, cudaMemcpyDeviceToHost, h->stream));
       VK_CUDA(cudaStreamSynchronize(h->stream));
+      for (int kind = 0; kind < 2; ++kind) {          // spread of the CTAs' evaluation times (the barrier waits for the slowest)
+        unsigned long long mn = ~0ull, mx = 0, sum = 0; int imx = 0, n = 0;
+        for (int b = 0; b < 1024; ++b) {
+          const unsigned long long v = pr[16 + 2 * b + kind];
+          if (!v) continue;
+          ++n; sum += v; if (v < mn) mn = v; if (v > mx) { mx = v; imx = b; }
+        }
+        if (n) fprintf(stderr, "[vk ss profile] eval %s per CTA (us over the call): min %.1f mean %.1f max %.1f (CTA %d), CTA 0 %.1f, %d CTAs\n",
+                       kind ? "direct" : "staged", mn * 1e-3, sum * 1e-3 / n, mx * 1e-3, imx, pr[16 + kind] * 1e-3, n);
+      }
       fprintf(stderr, "[vk ss profile] transitions %d | us: propose+bar %.1f list %.1f eval_staged %.1f eval_direct %.1f bar_eval %.1f decide %.1f "
                       "bar_decide %.1f | batches staged %llu (rounds %llu) direct %llu (rounds %llu) mean undecided %.2f\n", n_steps,
               pr[6] * 1e-3, pr[0] * 1e-3, pr[1] * 1e-3, pr[2] * 1e-3, pr[3] * 1e-3, pr[4] * 1e-3, pr[5] * 1e-3, pr[8], pr[10], pr[9], pr[11],

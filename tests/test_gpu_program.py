@@ -331,3 +331,51 @@ def test_subsampled_mh_companion_operators():
     nb = b.primitive_infer(["resimulation_mh", "default", "one", 20])
     np.testing.assert_array_equal(a.read_site(0), b.read_site(0))
     np.testing.assert_array_equal(na, nb)
+
+
+def test_compiled_logistic_regression_on_the_device():
+    """The C2 / C5 program TEXT (`(array ...)`, `vector_dot`, `log_odds_flip`) through the compiler and the generic kernels:
+    the Lite chains of lite_chains.json c2 / c5 (the fixtures that pin the hand-written logistic-regression kernels) and the
+    hand-written kernels themselves on the same seed."""
+    from test_program_compiler import blr_program
+    c = golden("lite_chains.json")["c2"]
+    D, N, P, K, seed = c["D"], c["N"], c["P"], c["K"], c["seed"]
+    recs = c["particles"]
+    ts = vb.B200TraceSet(CompiledModel(blr_program(c)), P, seed=seed)
+    start = np.array([r["w_lw"] for r in recs]).T
+    for j in range(D):
+        ts.write_site(j, start[j])
+    ts.incorporate()
+    ts.rng_step = c["steps"]["mh_one"]
+    nodes = ts.resimulation_mh("default", "one", K)
+    np.testing.assert_allclose(sites_of(ts).T, [r["w_one"] for r in recs], rtol=RTOL)
+    np.testing.assert_array_equal(nodes, c["untagged_nodes_one"][0])
+    np.testing.assert_allclose(ts.log_likelihood_at("default", "all"), [unj(r["ll_one"]) for r in recs], rtol=RTOL)
+    # the hand-written kernels from the same start on the same Philox steps
+    hand = vb.B200TraceSet(vb.LogisticRegressionModel(D, N), P, seed=seed)
+    hand.observe(np.array(c["X"]), np.array(c["y"]))
+    for j in range(D):
+        hand.write_site(j, start[j])
+    hand.incorporate()
+    hand.rng_step = c["steps"]["mh_one"]
+    hand.resimulation_mh("default", "one", K)
+    np.testing.assert_allclose(sites_of(ts), sites_of(hand), rtol=RTOL)
+    # C5: subsampled MH, the border is the `w` array node
+    c = golden("lite_chains.json")["c5"]
+    recs = c["particles"]
+    ts = vb.B200TraceSet(CompiledModel(blr_program(c)), c["P"], seed=c["seed"])
+    ts.rng_step = c["steps"]["prior"]
+    ts.reset_to_prior()
+    ts.incorporate()
+    np.testing.assert_allclose(sites_of(ts).T, [r["w_prior"] for r in recs], rtol=RTOL)
+    ts.rng_step = c["steps"]["ssmh"]
+    acc, visited = [], []
+    for _ in range(c["K"]):
+        st_ = ts.subsampled_mh("default", "one", c["Nbatch"], c["k0"], c["eps"], False, 0, False, 1)
+        acc.append(st_[:, 0]), visited.append(st_[:, 1])
+        np.testing.assert_array_equal(ts.last_mean_nodes, 3.0)
+    acc, visited = np.array(acc).T, np.array(visited).T
+    for p, r in enumerate(recs):
+        np.testing.assert_array_equal(visited[p], r["n"])
+        np.testing.assert_array_equal(acc[p] > 0, r["accept"])
+    np.testing.assert_allclose(sites_of(ts).T, [r["w"] for r in recs], rtol=RTOL)

@@ -195,3 +195,66 @@ def test_check_applicability_follows_the_reference():
     ok, kind, msg = m.subsampled_applicability("one")
     assert not ok and kind == "SubsampledScaffoldNotEffectiveWarning" and "same as mh" in msg
     assert m.subsampled_global_nodes("one") == 3.0 + 1.0 and m.subsampled_global_nodes(0) == 3.0
+
+
+def blr_program(c, n_obs=None):
+    """the logistic-regression program of SURVEY 8(d) D2 as directives (what tests/golden/make_lite_chains.py ran on Lite)"""
+    D, N = c["D"], c["N"] if n_obs is None else n_obs
+    return [("assume", "w_%d" % j, ["normal", 0.0, 1.0]) for j in range(D)] + \
+           [("assume", "w", ["array"] + ["w_%d" % j for j in range(D)])] + \
+           [("observe", ["log_odds_flip", ["vector_dot", "w", ["array"] + [float(v) for v in c["X"][i]]]], bool(c["y"][i]))
+            for i in range(N)]
+
+
+def test_compiled_logistic_regression_reproduces_lite():
+    """`(array ...)` / `vector_dot` in the compiler: the C2 program text itself, compiled, against the Lite chains that
+    pin the hand-written kernels (lite_chains.json c2): likelihood_weight, the increment, `one` and fixed-block MH"""
+    c = golden("lite_chains.json")["c2"]
+    D, N, P, K, seed = c["D"], c["N"], c["P"], c["K"], c["seed"]
+    h = N // 2
+    first, full = CompiledModel(blr_program(c, h)), CompiledModel(blr_program(c))
+    assert full.prog.affected == c["untagged_nodes_one"][:1] * D and full.prog.n_groups == 1
+    recs = c["particles"]
+    vm = VM(first.prog.blob(), compiler.OP, P, seed)
+    vm.step = c["steps"]["likelihood_weight"]
+    vm.likelihood_weight()
+    np.testing.assert_allclose(vm.lw, [unj(r["lw"]) for r in recs], rtol=RTOL)
+    np.testing.assert_allclose(vm.sites.T, [r["w_lw"] for r in recs], rtol=RTOL)
+    vm2 = VM(full.prog.blob(), compiler.OP, P, seed)
+    vm2.sites[:] = vm.sites
+    np.testing.assert_allclose(vm2.log_likelihood() - vm.log_likelihood(), [unj(r["incr"]) for r in recs], rtol=1e-10)
+    vm2.step = c["steps"]["mh_one"]
+    vm2.mh(K)
+    np.testing.assert_allclose(vm2.sites.T, [r["w_one"] for r in recs], rtol=RTOL)
+    np.testing.assert_allclose(vm2.log_likelihood(), [unj(r["ll_one"]) for r in recs], rtol=RTOL)
+    for k in range(2 * D):                       # (resimulation_mh wts <k mod D> 1), one Philox step each
+        vm2.step = c["steps"]["mh_each"] + k
+        vm2.mh(1, block=k % D)
+    np.testing.assert_allclose(vm2.sites.T, [r["w_each"] for r in recs], rtol=RTOL)
+
+
+def test_compiled_logistic_regression_subsampled_mh_reproduces_lite():
+    """the C5 program text compiled: the global border is the `w` array node, the local sections are the observations;
+    every decision, section count, t statistic and the node count 3 of lite_chains.json c5"""
+    c = golden("lite_chains.json")["c5"]
+    m = CompiledModel(blr_program(c))
+    assert [(s["kind"], len(s["roots"]), s["nodes"]) for s in m.prog.subsampled] == [(1, c["N"], 3.0)] * c["D"]
+    recs = c["particles"]
+    vm = VM(m.prog.blob(), compiler.OP, c["P"], c["seed"])
+    vm.step = c["steps"]["prior"]
+    vm.reset_to_prior()
+    np.testing.assert_allclose(vm.sites.T, [r["w_prior"] for r in recs], rtol=RTOL)
+    vm.step = c["steps"]["ssmh"]
+    acc, visited, ts, nodes = [], [], [], []
+    for _ in range(c["K"]):
+        a, n, t, nd = vm.subsampled_mh(1, c["Nbatch"], c["k0"], c["eps"])
+        acc.append(a), visited.append(n), ts.append(t), nodes.append(nd)
+    acc, visited, ts, nodes = [np.array(v).T for v in (acc, visited, ts, nodes)]
+    for p, r in enumerate(recs):
+        np.testing.assert_array_equal(visited[p], r["n"])
+        np.testing.assert_array_equal(acc[p] > 0, r["accept"])
+        np.testing.assert_array_equal(nodes[p], r["nodes"])
+        want = np.array([unj(v) for v in r["tstat"]])
+        fin = np.isfinite(want)
+        np.testing.assert_allclose(ts[p][fin], want[fin], rtol=1e-9)
+    np.testing.assert_allclose(vm.sites.T, [r["w"] for r in recs], rtol=RTOL)

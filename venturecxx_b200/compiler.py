@@ -9,7 +9,8 @@ ONCE here, per random choice, for programs whose structure cannot change:
 
   expressions   numbers, booleans, symbols bound by earlier assumes, applications of
   deterministic SPs   add sub mul div pow sqrt exp log log1p expm1 logistic log_logistic logit negate abs min max
-                      (venmath.py:101-332; add / mul are variadic left folds)
+                      (venmath.py:101-332; add / mul are variadic left folds); `(array e ...)` and
+                      `(vector_dot a b)` of two such arrays (vectors.py), lowered to scalar multiply-adds
   random SPs          normal gamma beta uniform_continuous expon flip bernoulli log_flip log_bernoulli
                       log_odds_flip log_odds_bernoulli            (continuous.py, discrete.py)
 
@@ -156,6 +157,16 @@ class Compiler(object):
             raise VentureException("invalid_argument", "procedure application (%s ...) is outside the fixed-structure subset" % (head,))
         args = [self._expr(a, holes) for a in e[1:]]
         via = [isinstance(a, str) for a in e[1:]]
+        if head == "array":
+            # `(array e_1 ... e_n)` (vectors.py): ONE deterministic application whose value is the tuple of its operands;
+            # it owns no register -- vector_dot reads the operands' registers
+            return self._record_uses(self._finish(Node("det", "ARRAY", args)), args, via)
+        if head == "vector_dot":
+            if len(args) != 2 or any(self.nodes[a].op != "ARRAY" for a in args):
+                raise VentureException("invalid_argument", "vector_dot takes two arrays built by (array ...) in the compiled subset")
+            if len(self.nodes[args[0]].args) != len(self.nodes[args[1]].args):
+                raise VentureException("invalid_argument", "vector_dot: the arrays differ in length")
+            return self._record_uses(self._finish(Node("det", "VDOT", args)), args, via)
         if head in DET:
             arity, op = DET[head]
             if arity == "fold":
@@ -319,6 +330,21 @@ class _Code(object):
             self.emit("DATA", r, n.hole)
         elif n.kind == "random":
             self.emit("SITE", r, n.site)
+        elif n.op == "ARRAY":
+            for a in n.args:
+                self.need(a)
+        elif n.op == "VDOT":                         # left fold of the products (vectors.py vector_dot = numpy.dot)
+            xs, ys = self.prog.c.nodes[n.args[0]], self.prog.c.nodes[n.args[1]]
+            self.need(n.args[0]), self.need(n.args[1])
+            pairs = [(self.reg(a), self.reg(b)) for a, b in zip(xs.args, ys.args)]
+            if not pairs:
+                self.emit("CONST", r, self.prog.const(0.0))
+            else:
+                self.emit("MUL", r, pairs[0][0], pairs[0][1])
+                tmp = self.prog.reg_of(("vdot-tmp", nid))
+                for ra, rb in pairs[1:]:
+                    self.emit("MUL", tmp, ra, rb)
+                    self.emit("ADD", r, r, tmp)
         else:
             regs = [self.need(a) for a in n.args]
             self.emit(n.op, r, regs[0], regs[1] if len(regs) > 1 else 0)

@@ -106,8 +106,12 @@ int vk_create_normal_normal(int64_t n_particles, uint64_t seed, int device,
  *             columns (literals + observed value), offset into data; per section: first
  *             instruction, count; per site, for subsampled MH (infer/subsampled_mh.py:326-368):
  *             kind (0 no global border, 1 border found, 2 refused), number of local sections,
- *             offset into the section list; the local sections as pairs (group, row) |
- *             (-1, child site), in the order of the border node's children
+ *             offset into the section list; the number of local sections in all, then the local
+ *             sections as pairs (group, row) | (-1, child site), in the order of the border node's
+ *             children; the number of scopes, per scope (blocks, offset into the site list), the
+ *             blocks' sites -- scope 0 is the default scope (every site, in order), the others are
+ *             what `(tag scope block expr)` made (lite/scope.py:25-52; one random choice per block);
+ *             entry points taking (scope, block) read block as an index into the scope's list
  *   data      the groups' tables, row-major
  *   affected  2 * n_sites doubles.  Per site: Scaffold.numAffectedNodes (scaffold.py:67-68), what
  *             resimulation_mh reports (dispatch.py:109-120); then per site the same count for the

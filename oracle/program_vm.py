@@ -56,7 +56,15 @@ class VM(object):
         at += 2 * self.n_sec
         self.ss = [m[at + 3 * k: at + 3 * k + 3] for k in range(self.S)]          # kind, N, offset into the roots
         at += 3 * self.S
-        self.roots = [(m[at + 2 * i], m[at + 2 * i + 1]) for i in range((len(m) - at) // 2)]
+        n_roots = m[at]
+        at += 1
+        self.roots = [(m[at + 2 * i], m[at + 2 * i + 1]) for i in range(n_roots)]
+        at += 2 * n_roots
+        n_scopes = m[at]
+        at += 1
+        tab = [(m[at + 2 * i], m[at + 2 * i + 1]) for i in range(n_scopes)]
+        at += 2 * n_scopes
+        self.scope_sites = [m[at + off: at + off + n] for n, off in tab]       # scope 0 = default: every site
         self.sites = np.zeros((self.S, P))
         self.lw = np.zeros(P)
         self.step = 0
@@ -140,6 +148,15 @@ class VM(object):
     def all_groups(self, R, p):
         return sum(self.group_ll(g, R, p) for g in range(self.G))
 
+    def pick(self, u_sel, t, block, scope):
+        """block -1: one (uniform over the scope's blocks), -3: each (in order), k >= 0: block k of the scope -> site"""
+        sites = self.scope_sites[scope]
+        if block == -1:
+            return sites[min(int(u_sel * len(sites)), len(sites) - 1)]
+        if block == -3:
+            return sites[t % len(sites)]
+        return sites[block]
+
     # -- the operations of the C ABI --------------------------------------------------------------------------
     def likelihood_weight(self):
         step, self.step = self.step, self.step + 1
@@ -160,14 +177,14 @@ class VM(object):
             out[p] = self.all_groups(R, p) + (self.run(self.sec_joint, R, p) if joint else 0.0)
         return out
 
-    def mh(self, n_steps, block=-1):
-        """block -1: one, -3: each, k >= 0: site k.  Returns (accept counts, per-particle mean node counts)."""
+    def mh(self, n_steps, block=-1, scope=0):
+        """block -1: one, -3: each, k >= 0: block k of the scope.  Returns (accept counts, per-particle mean node counts)."""
         step0, self.step = self.step, self.step + n_steps
         acc, nodes = np.zeros(self.P, dtype=np.int64), np.zeros(self.P)
         for p in range(self.P):
             for t in range(n_steps):
                 u = oracle.uniforms(self.seed, self.p_base + p, step0 + t, 2)
-                k = min(int(u[0] * self.S), self.S - 1) if block == -1 else (t % self.S if block == -3 else block)
+                k = self.pick(u[0], t, block, scope)
                 R = [0.0] * self.n_regs
                 rho = self.children(k, R, p)
                 old = self.sites[k, p]
@@ -186,7 +203,7 @@ class VM(object):
                 nodes[p] += self.affected[k]
         return acc, nodes / max(n_steps, 1)
 
-    def slice(self, n_steps, w, m, block=-1):
+    def slice(self, n_steps, w, m, block=-1, scope=0):
         """StepOutSliceOperator under mixMH (infer/slice_sample.py:39-139): draw 0 block choice, then the uniforms in call
         order.  Returns per-particle mean node counts."""
         step0, self.step = self.step, self.step + n_steps
@@ -195,7 +212,7 @@ class VM(object):
             for t in range(n_steps):
                 tape = self._tape(p, step0 + t, 0)
                 u_sel = tape(0, [0.0])
-                k = min(int(u_sel * self.S), self.S - 1) if block == -1 else (t % self.S if block == -3 else block)
+                k = self.pick(u_sel, t, block, scope)
                 R = [0.0] * self.n_regs
 
                 def f(x):
@@ -233,7 +250,7 @@ class VM(object):
                 nodes[p] += self.affected[k]
         return nodes / max(n_steps, 1)
 
-    def subsampled_mh(self, n_steps, Nbatch, k0, eps, block=-1):
+    def subsampled_mh(self, n_steps, Nbatch, k0, eps, block=-1, scope=0):
         """subsampledMixMH + sequentialTest (infer/subsampled_mh.py:76-171) for a compiled program: draw 0 block choice,
         draw 1 the accept uniform, then the proposal; the minibatch order is the Feistel permutation of (seed, step)
         (the stand-in behind np_rng.permutation in tests/golden/make_program_chains.py); q = scipy.stats.t.cdf as in
@@ -245,7 +262,7 @@ class VM(object):
             perms = {}
             for p in range(self.P):
                 u = oracle.uniforms(self.seed, self.p_base + p, step0 + t, 2)
-                k = min(int(u[0] * self.S), self.S - 1) if block == -1 else (t % self.S if block == -3 else block)
+                k = self.pick(u[0], t, block, scope)
                 kind, N, off = self.ss[k]
                 if kind == 2:
                     raise ValueError("subsampled_mh: site %d has no valid global border" % k)

@@ -390,3 +390,27 @@ def test_reference_engine_runs_subsampled_mh_on_a_compiled_program():
         std = np.sqrt(9.0 / (9.0 * 100 + 1.0))
         return report_known_continuous(st.norm(loc=mean, scale=std).cdf, e.model.b200.read_site(0), "N(%f,%f^2)" % (mean, std))
     check()
+
+
+@pytest.mark.gpu
+def test_reference_engine_compiles_tagged_scopes():
+    """`(tag (quote wts) j ...)` directives and `(resimulation_mh (quote wts) j K)` / `each` commands through the reference's
+    Engine: only the tagged block moves"""
+    from venturecxx_b200 import backend as bk
+    e = _engine(bk.B200(), seed=5)
+    e.assume("a", ref_engine.expression("(tag (quote wts) 0 (normal 0 1))"))
+    e.assume("b", ref_engine.expression("(tag (quote wts) 1 (normal a 1))"))
+    e.assume("c", ref_engine.expression("(normal b 1)"))
+    e.infer(ref_engine.program("(resample 64)"))
+    e.observe(ref_engine.expression("(normal c 0.5)"), ref_engine.value(1.5))
+    ts = e.model.b200
+    assert ts.model.scopes == {"default": 0, "wts": 1} and ts.num_sites() == 3
+    before = np.stack([ts.read_site(j) for j in range(3)])
+    _, nodes = e.infer(ref_engine.program("(resimulation_mh (quote wts) 1 30)"))
+    after = np.stack([ts.read_site(j) for j in range(3)])
+    np.testing.assert_array_equal(after[0], before[0]); np.testing.assert_array_equal(after[2], before[2])
+    assert (after[1] != before[1]).any()
+    e.infer(ref_engine.program("(resimulation_mh (quote wts) each 5)"))
+    final = np.stack([ts.read_site(j) for j in range(3)])
+    np.testing.assert_array_equal(final[2], before[2])
+    assert (final[0] != before[0]).any()

@@ -379,3 +379,51 @@ def test_compiled_logistic_regression_on_the_device():
         np.testing.assert_array_equal(visited[p], r["n"])
         np.testing.assert_array_equal(acc[p] > 0, r["accept"])
     np.testing.assert_allclose(sites_of(ts).T, [r["w"] for r in recs], rtol=RTOL)
+
+
+def test_tagged_scopes_on_the_device():
+    """`(tag (quote wts) j (normal 0 1))`: the model lite_chains.json c2 actually ran -- node counts 32, `(resimulation_mh wts
+    <block> 1)` block by block, `each` over the scope; a scope over a subset of the sites leaves the others alone"""
+    from test_program_compiler import tagged_blr_program
+    c = golden("lite_chains.json")["c2"]
+    D, P, K, seed = c["D"], c["P"], c["K"], c["seed"]
+    recs = c["particles"]
+    ts = vb.B200TraceSet(CompiledModel(tagged_blr_program(c)), P, seed=seed)
+    start = np.array([r["w_lw"] for r in recs]).T
+    for j in range(D):
+        ts.write_site(j, start[j])
+    ts.incorporate()
+    ts.rng_step = c["steps"]["mh_one"]
+    nodes = ts.resimulation_mh("default", "one", K)
+    np.testing.assert_allclose(sites_of(ts).T, [r["w_one"] for r in recs], rtol=RTOL)
+    np.testing.assert_array_equal(nodes, [np.mean(r["nodes_one"]) for r in recs])
+    for k in range(2 * D):
+        ts.rng_step = c["steps"]["mh_each"] + k
+        nodes = ts.primitive_infer(["resimulation_mh", "wts", k % D, 1])
+        np.testing.assert_array_equal(nodes, [r["nodes_each"][k] for r in recs])
+    np.testing.assert_allclose(sites_of(ts).T, [r["w_each"] for r in recs], rtol=RTOL)
+    assert ts.numBlocksInScope("default") == D
+    # `each` over the tagged scope = its blocks in order: the same chain as issuing them one by one
+    a, b = [vb.B200TraceSet(CompiledModel(tagged_blr_program(c)), P, seed=seed) for _ in range(2)]
+    for t_ in (a, b):
+        t_.incorporate()
+        t_.rng_step = 300
+    na = a.primitive_infer(["resimulation_mh", "wts", "each", 2])
+    for k in range(2 * D):
+        b.primitive_infer(["resimulation_mh", "wts", float(k % D), 1])
+    np.testing.assert_array_equal(sites_of(a), sites_of(b))
+    np.testing.assert_array_equal(na, 32.0)
+    sub = vb.B200TraceSet(CompiledModel([("assume", "a", ["normal", 0.0, 1.0]),
+                                         ("assume", "b", ["tag", ["quote", "s"], ["quote", "x"], ["normal", "a", 1.0]]),
+                                         ("assume", "c", ["tag", ["quote", "s"], 7, ["normal", "b", 1.0]]),
+                                         ("observe", ["normal", "c", 1.0], 0.4)]), 64, seed=5)
+    sub.incorporate()
+    before = sites_of(sub).copy()
+    _, acc = sub.resimulation_mh("s", "one", 60, return_accepts=True)
+    sub.primitive_infer(["slice", "s", "x", 0.5, 4, 3])
+    after = sites_of(sub)
+    np.testing.assert_array_equal(after[0], before[0])
+    assert acc.sum() > 0 and (after[1] != before[1]).any() and (after[2] != before[2]).any()
+    with pytest.raises(vb.VentureException) as e:
+        sub.resimulation_mh("s", 3, 1)
+    assert "no block" in str(e.value)

@@ -140,7 +140,7 @@ def test_blob_is_self_consistent():
     S, G, n_regs, n_sec = [int(v) for v in meta[:4]]
     assert S == 5 and len(affected) == 2 * S and n_regs <= compiler.MAX_REGS     # regular scaffolds, then the global sections
     n_roots = sum(len(ss["roots"]) for ss in m.prog.subsampled)
-    tail = 3 * S + 2 * n_roots                                                    # the subsampled-MH block closes the meta words
+    tail = 3 * S + 1 + 2 * n_roots + 1 + 2 + S           # subsampled-MH block, then the scopes (here only the default one)
     directory = meta[-tail - 2 * n_sec: -tail].reshape(n_sec, 2)
     assert directory[:, 1].sum() == code.size // compiler.INSTR_WORDS
     ops = set(code.reshape(-1, compiler.INSTR_WORDS)[:, 0].tolist())
@@ -258,3 +258,44 @@ def test_compiled_logistic_regression_subsampled_mh_reproduces_lite():
         fin = np.isfinite(want)
         np.testing.assert_allclose(ts[p][fin], want[fin], rtol=1e-9)
     np.testing.assert_allclose(vm.sites.T, [r["w"] for r in recs], rtol=RTOL)
+
+
+def tagged_blr_program(c, n_obs=None):
+    """blr_model of tests/golden/make_lite_chains.py: every weight tagged into scope `wts`, block j"""
+    prog = blr_program(c, n_obs)
+    return [("assume", d[1], ["tag", ["quote", "wts"], float(j), d[2]]) if j < c["D"] else d for j, d in enumerate(prog)]
+
+
+def test_tagged_scopes_reproduce_lite():
+    """`(tag (quote wts) j (normal 0 1))`: one more deterministic node per weight in the scaffold (32 against 31), and
+    `(resimulation_mh wts <block> 1)` picks the tagged site -- the model lite_chains.json c2 actually ran"""
+    c = golden("lite_chains.json")["c2"]
+    D, P, K, seed = c["D"], c["P"], c["K"], c["seed"]
+    m = CompiledModel(tagged_blr_program(c))
+    assert m.scopes == {"default": 0, "wts": 1} and m.scope_blocks == {1: dict((float(j), j) for j in range(D))}
+    assert m.site_names == ["w_%d" % j for j in range(D)]
+    recs = c["particles"]
+    assert m.prog.affected == [recs[0]["nodes_one"][0]] * D == [32.0] * D
+    vm = VM(m.prog.blob(), compiler.OP, P, seed)
+    vm.sites[:] = np.array([r["w_lw"] for r in recs]).T
+    vm.step = c["steps"]["mh_one"]
+    _, nodes = vm.mh(K)
+    np.testing.assert_allclose(vm.sites.T, [r["w_one"] for r in recs], rtol=RTOL)
+    np.testing.assert_array_equal(nodes, [np.mean(r["nodes_one"]) for r in recs])
+    for k in range(2 * D):
+        vm.step = c["steps"]["mh_each"] + k
+        _, nodes = vm.mh(1, block=m.scope_blocks[1][float(k % D)], scope=1)
+        np.testing.assert_array_equal(nodes, [r["nodes_each"][k] for r in recs])
+    np.testing.assert_allclose(vm.sites.T, [r["w_each"] for r in recs], rtol=RTOL)
+    # a scope over a subset of the sites: `one` and `each` stay inside it
+    sub = CompiledModel([("assume", "a", ["normal", 0.0, 1.0]), ("assume", "b", ["tag", ["quote", "s"], ["quote", "x"], ["normal", "a", 1.0]]),
+                         ("assume", "c", ["tag", ["quote", "s"], 7, ["normal", "b", 1.0]]), ("observe", ["normal", "c", 1.0], 0.4)])
+    assert sub.scope_blocks == {1: {"x": 0, 7.0: 1}} and sub.prog.scope_sites == [[0, 1, 2], [1, 2]]
+    vm = VM(sub.prog.blob(), compiler.OP, 6, 3)
+    vm.reset_to_prior()
+    a0 = vm.sites[0].copy()
+    vm.mh(40, block=-1, scope=1), vm.mh(4, block=-3, scope=1)
+    np.testing.assert_array_equal(vm.sites[0], a0)
+    with pytest.raises(VentureException) as e:
+        CompiledModel([("assume", "a", ["tag", ["quote", "s"], 0, ["add", ["normal", 0.0, 1.0], ["normal", 0.0, 1.0]]])])
+    assert "blocks of one random choice" in str(e.value)

@@ -64,6 +64,19 @@ RANDOM = {"normal": (2, "NORMAL"), "gamma": (2, "GAMMA"), "beta": (2, "BETA"), "
 BOOLEAN_VALUED = ("FLIP", "LOG_FLIP", "LOG_ODDS_FLIP")
 
 
+def _tag_key(e):
+    """scope / block operand of `tag` or of an inference command -> a hashable python value: symbols (quoted or not) as
+    str, numbers as float"""
+    e = _plain(e) if not isinstance(e, (str, float, int, bool, list)) else e
+    if isinstance(e, list):
+        if len(e) == 2 and e[0] == "quote":
+            return _tag_key(e[1])
+        raise VentureException("invalid_argument", "scope / block operands of tag must be literals, not %r" % (e,))
+    if isinstance(e, bool) or isinstance(e, str):
+        return e
+    return float(e)
+
+
 def _plain(e):
     """stack-dict expression / VentureValue -> nested python: str symbols, float numbers, bools, lists"""
     if hasattr(e, "asStackDict"):
@@ -123,6 +136,9 @@ class Compiler(object):
         # Lite's child lists, for findGlobalBorder (infer/subsampled_mh.py:326-368): node -> its consumers in
         # creation order, [consumer node, through a lookup node?, group or None, row]
         self.uses = {}
+        # scopes made by `(tag scope block expr)`: scope -> block -> sites created inside expr, both in order of first
+        # appearance (trace.registerRandomChoiceInScope, lite/trace.py:121-127; regen.py:343-348)
+        self.scopes = {}
         self.aliased = set()   # nodes some `(assume y x)` renames: their lookups hang off the alias, not off the node
         self._template_uses = None
 
@@ -155,6 +171,19 @@ class Compiler(object):
             raise VentureException("invalid_argument", "the model compiler needs a builtin SP in operator position, not %r" % (head,))
         if head in self.env:
             raise VentureException("invalid_argument", "procedure application (%s ...) is outside the fixed-structure subset" % (head,))
+        if head == "tag":
+            # scope.py:25-52: returns its third operand unchanged (ONE deterministic node in the scaffolds) and registers the
+            # random choices made inside it in scope / block
+            if len(e) != 4 or holes is not None or not isinstance(e[3], list):
+                raise VentureException("invalid_argument", "(tag scope block (application ...)) outside an observation is the compiled form")
+            scope, block = _tag_key(e[1]), _tag_key(e[2])
+            if scope == "default":
+                raise VentureException("invalid_argument", "the default scope cannot be tagged into")
+            first = len(self.sites)
+            inner = self._expr(e[3])
+            blocks = self.scopes.setdefault(scope, {})
+            blocks.setdefault(block, []).extend(range(first, len(self.sites)))
+            return self._record_uses(self._finish(Node("det", "TAG", [inner])), [inner], [False])
         args = [self._expr(a, holes) for a in e[1:]]
         via = [isinstance(a, str) for a in e[1:]]
         if head == "array":
@@ -226,6 +255,8 @@ class Compiler(object):
         first = len(self.sites)
         nid = self._expr(exp)
         n = self.nodes[nid]
+        while n.op == "TAG":
+            n = self.nodes[n.args[0]]
         if not isinstance(exp, str) and n.kind == "random":
             self.site_names[n.site] = name          # (an alias's root is the lookup counted in _expr)
         if isinstance(exp, str):
@@ -323,6 +354,11 @@ class _Code(object):
         if nid in self.done:
             return self.reg(nid)
         n = self.prog.c.nodes[nid]
+        if n.op == "TAG":                            # the operand's register under a second name
+            r = self.need(n.args[0])
+            self.prog._regs[nid] = r
+            self.done.add(nid)
+            return r
         r = self.reg(nid)
         if n.kind == "const":
             self.emit("CONST", r, self.prog.const(n.value))
@@ -445,6 +481,17 @@ class Program(object):
                     cnt += (own.get(nid, 1) if n.counted else 0) + n.lookups
             self.affected.append(float(cnt))
         self.subsampled = [self._subsample_site(k) for k in range(S)]
+        # scope 0 = default (one block per site, lite/trace.py:116-119), then the tagged scopes; a block is one site here
+        self.scope_names, self.scope_sites, self.scope_blocks = ["default"], [list(range(S))], [dict((k, k) for k in range(S))]
+        for name, blocks in c.scopes.items():
+            sites, index = [], {}
+            for key, members in blocks.items():
+                if len(members) != 1:
+                    raise VentureException("invalid_argument", "scope %r block %r holds %d random choices: blocks of one random "
+                                           "choice are the compiled subset (single-site proposals)" % (name, key, len(members)))
+                index[key] = len(sites)
+                sites.append(members[0])
+            self.scope_names.append(name), self.scope_sites.append(sites), self.scope_blocks.append(index)
 
     # -- subsampled MH: the global border and the local sections of a site (infer/subsampled_mh.py:326-368, 186-211) --
     def _subsample_site(self, k):
@@ -577,7 +624,15 @@ class Program(object):
             meta += [ss["kind"], len(ss["roots"]), len(roots) // 2]
             for a, b in ss["roots"]:
                 roots += [a, b]
-        meta += roots
+        meta += [len(roots) // 2] + roots
+        # scopes: count; per scope (blocks, offset into the site list); the blocks' sites
+        meta += [len(self.scope_sites)]
+        off = 0
+        for sites in self.scope_sites:
+            meta += [len(sites), off]
+            off += len(sites)
+        for sites in self.scope_sites:
+            meta += sites
         return (np.asarray(code, dtype=np.int32), np.asarray(self._consts or [0.0], dtype=np.float64),
                 np.asarray(meta, dtype=np.int32), np.concatenate(data) if data else np.zeros(1),
                 np.asarray(self.affected + [ss["nodes"] for ss in self.subsampled], dtype=np.float64))
@@ -602,6 +657,8 @@ class CompiledModel(object):
         self.compiler = c
         self.prog = c.compile()
         self.site_names = list(c.site_names)
+        self.scopes = dict((name, i) for i, name in enumerate(self.prog.scope_names))       # B200TraceSet._scope_block
+        self.scope_blocks = dict((i, b) for i, b in enumerate(self.prog.scope_blocks) if i > 0)
         self.n_observations = sum(len(g.rows) for g in c.group_list)
         self.source = list(directives)
 

@@ -54,6 +54,8 @@ struct VMProg {
   const int32_t *ss_tab;     // per site: kind (0 no border, 1 border, 2 refused), local sections, offset into ss_roots
   const int32_t *ss_roots;   // pairs: (group, row) | (-1, child site), in the order of Lite's childrenAt(globalBorder)
   const double *ss_nodes;    // per site: nodes of the scaffold cut at the global border
+  const int32_t *scope_tab;  // per scope: number of blocks, offset into scope_sites (scope 0 = default: every site)
+  const int32_t *scope_sites;   // the blocks' sites (one site per block)
   int n_sites, n_groups, sec_prior, sec_joint;
 };
 
@@ -195,12 +197,13 @@ prog_kernel(VMProg pg, double *sites, double *lw, double *out, int64_t P, int64_
 
 template <int LANES>
 __global__ void __launch_bounds__(256)
-prog_mh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps,
+prog_mh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int scope,
                int block_mode, double *nodes_out, long long *acc_out) {
   double R[VM_MAX_REGS];
   const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
   const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
-  const int S = pg.n_sites;
+  const int S = __ldg(&pg.scope_tab[2 * scope]);                       // blocks of the scope (one site each)
+  const int32_t *sc_sites = pg.scope_sites + __ldg(&pg.scope_tab[2 * scope + 1]);
   for (int64_t p = unit; p < P; p += n_units) {
     long long acc = 0;
     double nodes = 0.0;
@@ -209,8 +212,8 @@ prog_mh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t see
       const double u_sel = r.uniform();                   // draw 0: block choice
       const double logu = log(r.uniform());               // draw 1: accept uniform (mh.py:85)
       int k;
-      if (block_mode == VK_BLOCK_ONE) { k = (int)(u_sel * (double)S); if (k >= S) k = S - 1; }
-      else if (block_mode == VK_BLOCK_EACH) k = t % S;
+      if (block_mode == VK_BLOCK_ONE) { k = (int)(u_sel * (double)S); if (k >= S) k = S - 1; k = __ldg(&sc_sites[k]); }
+      else if (block_mode == VK_BLOCK_EACH) k = __ldg(&sc_sites[t % S]);
       else k = block_mode;
       const double rho = vm_children<LANES>(pg, k, R, sites, P, p, lane);
       const double old = sites[(int64_t)k * P + p];
@@ -239,12 +242,13 @@ prog_mh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t see
 // one uniform per shrink step (:49-58), the accept uniform of mixMH (mh.py:85; logAlpha is 0, :85-90).
 template <int LANES>
 __global__ void __launch_bounds__(256)
-prog_slice_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps,
+prog_slice_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int scope,
                   int block_mode, double w, double m, double *nodes_out, long long *moved_out) {
   double R[VM_MAX_REGS];
   const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
   const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
-  const int S = pg.n_sites;
+  const int S = __ldg(&pg.scope_tab[2 * scope]);                       // blocks of the scope (one site each)
+  const int32_t *sc_sites = pg.scope_sites + __ldg(&pg.scope_tab[2 * scope + 1]);
   for (int64_t p = unit; p < P; p += n_units) {
     long long moved = 0;
     double nodes = 0.0;
@@ -252,8 +256,8 @@ prog_slice_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t 
       Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)t);
       const double u_sel = r.uniform();
       int k;
-      if (block_mode == VK_BLOCK_ONE) { k = (int)(u_sel * (double)S); if (k >= S) k = S - 1; }
-      else if (block_mode == VK_BLOCK_EACH) k = t % S;
+      if (block_mode == VK_BLOCK_ONE) { k = (int)(u_sel * (double)S); if (k >= S) k = S - 1; k = __ldg(&sc_sites[k]); }
+      else if (block_mode == VK_BLOCK_EACH) k = __ldg(&sc_sites[t % S]);
       else k = block_mode;
       double *cell = sites + (int64_t)k * P + p;
       const int sec_own = __ldg(&pg.site_tab[5 * k + 2]);
@@ -316,12 +320,13 @@ prog_slice_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t 
 // LANES = 32: lanes take the positions of a minibatch in turn and the warp adds (sum, sum of squares).
 template <int LANES>
 __global__ void __launch_bounds__(256)
-prog_ssmh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps,
+prog_ssmh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int scope,
                  int block_mode, double Nbatch, int k0, double eps, double *nodes_out, double *stats_out) {
   double Ro[VM_MAX_REGS], Rn[VM_MAX_REGS];
   const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
   const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
-  const int S = pg.n_sites;
+  const int S = __ldg(&pg.scope_tab[2 * scope]);                       // blocks of the scope (one site each)
+  const int32_t *sc_sites = pg.scope_sites + __ldg(&pg.scope_tab[2 * scope + 1]);
   for (int64_t p = unit; p < P; p += n_units) {
     double accepted = 0.0, visited = 0.0, tlast = 0.0, nodes = 0.0;
     for (int t = 0; t < n_steps; ++t) {
@@ -329,8 +334,8 @@ prog_ssmh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t s
       const double u_sel = r.uniform();
       const double logu = log(r.uniform());
       int k;
-      if (block_mode == VK_BLOCK_ONE) { k = (int)(u_sel * (double)S); if (k >= S) k = S - 1; }
-      else if (block_mode == VK_BLOCK_EACH) k = t % S;
+      if (block_mode == VK_BLOCK_ONE) { k = (int)(u_sel * (double)S); if (k >= S) k = S - 1; k = __ldg(&sc_sites[k]); }
+      else if (block_mode == VK_BLOCK_EACH) k = __ldg(&sc_sites[t % S]);
       else k = block_mode;
       const int kind = __ldg(&pg.ss_tab[3 * k]), Nloc = __ldg(&pg.ss_tab[3 * k + 1]), off = __ldg(&pg.ss_tab[3 * k + 2]);
       const int32_t *st = pg.site_tab + 5 * k;
@@ -416,6 +421,8 @@ __global__ void prog_fill_kernel(double *out, int64_t n, double v) {
 struct ProgramModel : Model {
   std::vector<double> affected_host;   // per site: nodes of the regular scaffold, then of the scaffold cut at the global border
   std::vector<int> ss_kind;
+  std::vector<int32_t> scope_tab_host, scope_sites_host;
+  int n_scopes = 1;
   DevBuf<int32_t> code, tables;       // tables: dir | site_tab | site_groups | group_tab
   DevBuf<double> consts, data, affected;
   DevBuf<double> sa, sb;
@@ -464,9 +471,27 @@ struct ProgramModel : Model {
     VK_REQUIRE(n_meta >= at + 3 * (int64_t)S, VK_EINVAL, "program: truncated subsampled-MH table");
     std::vector<int32_t> ss_tab(meta + at, meta + at + 3 * (int64_t)S);
     at += 3 * (int64_t)S;
-    const int64_t n_roots = (n_meta - at) / 2;
+    VK_REQUIRE(n_meta >= at + 1, VK_EINVAL, "program: truncated subsampled-MH table");
+    const int64_t n_roots = meta[at];
+    at += 1;
+    VK_REQUIRE(n_roots >= 0 && n_meta >= at + 2 * n_roots + 1, VK_EINVAL, "program: truncated local-section list");
     std::vector<int32_t> ss_roots(meta + at, meta + at + 2 * n_roots);
     ss_roots.push_back(0);
+    at += 2 * n_roots;
+    // scopes: count; per scope (blocks, offset); the blocks' sites
+    n_scopes = meta[at];
+    at += 1;
+    VK_REQUIRE(n_scopes >= 1 && n_scopes <= 64 && n_meta >= at + 2 * (int64_t)n_scopes, VK_EINVAL, "program: bad scope table");
+    scope_tab_host.assign(meta + at, meta + at + 2 * (int64_t)n_scopes);
+    at += 2 * (int64_t)n_scopes;
+    scope_sites_host.assign(meta + at, meta + n_meta);
+    for (int sc = 0; sc < n_scopes; ++sc) {
+      const int nb = scope_tab_host[(size_t)2 * sc], off = scope_tab_host[(size_t)2 * sc + 1];
+      VK_REQUIRE(nb >= (sc == 0 ? S : 1) && off >= 0 && (size_t)off + (size_t)nb <= scope_sites_host.size(), VK_EINVAL, "program: bad scope entry");
+      for (int i = off; i < off + nb; ++i)
+        VK_REQUIRE(scope_sites_host[(size_t)i] >= 0 && scope_sites_host[(size_t)i] < S, VK_EINVAL, "program: scope site out of range");
+    }
+    for (int k = 0; k < S; ++k) VK_REQUIRE(scope_sites_host[(size_t)scope_tab_host[1] + k] == k, VK_EINVAL, "program: the default scope lists every site in order");
     for (int k = 0; k < S; ++k) {
       const int kind = ss_tab[(size_t)3 * k], n = ss_tab[(size_t)3 * k + 1], off = ss_tab[(size_t)3 * k + 2];
       VK_REQUIRE(kind >= 0 && kind <= 2 && n >= 0 && off >= 0 && (int64_t)off + n <= n_roots, VK_EINVAL, "program: bad subsampled-MH entry");
@@ -520,6 +545,10 @@ struct ProgramModel : Model {
     all.insert(all.end(), ss_tab.begin(), ss_tab.end());
     const size_t o_roots = all.size();
     all.insert(all.end(), ss_roots.begin(), ss_roots.end());
+    const size_t o_sct = all.size();
+    all.insert(all.end(), scope_tab_host.begin(), scope_tab_host.end());
+    const size_t o_scs = all.size();
+    all.insert(all.end(), scope_sites_host.begin(), scope_sites_host.end());
     code.alloc((size_t)(n_code > 0 ? n_code : 1)); tables.alloc(all.size());
     consts.alloc((size_t)(n_consts > 0 ? n_consts : 1)); data.alloc((size_t)(n_data > 0 ? n_data : 1)); affected.alloc((size_t)2 * S);
     VK_CUDA(cudaMemcpyAsync(code.p, code_h, (size_t)n_code * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
@@ -535,6 +564,7 @@ struct ProgramModel : Model {
     pg.dir = tables.p + o_dir; pg.site_tab = tables.p + o_site; pg.site_groups = tables.p + o_sg; pg.group_tab = tables.p + o_gt;
     pg.affected = affected.p; pg.ss_nodes = affected.p + S;
     pg.ss_tab = tables.p + o_ss; pg.ss_roots = tables.p + o_roots;
+    pg.scope_tab = tables.p + o_sct; pg.scope_sites = tables.p + o_scs;
     affected_host.assign(affected_h, affected_h + 2 * S);
     pg.n_sites = S; pg.n_groups = G; pg.sec_prior = meta[4]; pg.sec_joint = meta[5];
   }
@@ -560,77 +590,84 @@ struct ProgramModel : Model {
     launch(VM_MODE_CONSISTENT, incr_dev, 0);
     propagated = true;
   }
+  // blocks of a scope (one site each); scope 0 = default (every site), then the scopes made by `tag`
+  int scope_blocks(int scope) const {
+    VK_REQUIRE(scope >= 0 && scope < n_scopes, VK_EINVAL, "program: scope out of range (scope 0 = default, then the tagged scopes in order of appearance)");
+    return scope_tab_host[(size_t)2 * scope];
+  }
+  int scope_site(int scope, int b) const { return scope_sites_host[(size_t)scope_tab_host[(size_t)2 * scope + 1] + (size_t)b]; }
+  // block: one / each stay as they are (the kernels pick inside the scope); all only in the default scope; an explicit
+  // block index of the scope becomes its SITE index
   int block_of(int scope, int block, bool allow_all) const {
-    VK_REQUIRE(scope == 0, VK_EINVAL, "program: only the default scope is compiled");
+    const int nb = scope_blocks(scope);
     if (block == VK_BLOCK_ONE || block == VK_BLOCK_EACH) return block;
-    if (block == VK_BLOCK_ALL) { VK_REQUIRE(allow_all, VK_EUNSUPPORTED, "program: block 'all' is not compiled for resimulation_mh"); return block; }
-    VK_REQUIRE(block >= 0 && block < S, VK_EINVAL, "program: block must be one / each / a site index");
-    return block;
+    if (block == VK_BLOCK_ALL) {
+      VK_REQUIRE(allow_all && scope == 0, VK_EUNSUPPORTED, "program: block 'all' is compiled for log_likelihood_at / log_joint_at in the default scope only");
+      return block;
+    }
+    VK_REQUIRE(block >= 0 && block < nb, VK_EINVAL, "program: block must be one / each / a block index of the scope");
+    return scope_site(scope, block);
+  }
+  // transloop's value for a particle-independent block choice (dispatch.py:109-128)
+  void fill_nodes(double *mean_nodes_dev, int scope, int block, int K, const double *counts) {
+    if (!mean_nodes_dev || block == VK_BLOCK_ONE) return;
+    double v = 0.0;
+    if (K > 0 && block == VK_BLOCK_EACH) {         // scaffolder_loop: the blocks' counts summed, FLOOR-divided by #blocks (dispatch.py:122-128)
+      const int nb = scope_blocks(scope);
+      double sum = 0.0;
+      for (int b = 0; b < nb; ++b) sum += counts[(size_t)scope_site(scope, b)];
+      v = floor(sum / (double)nb);
+    } else if (K > 0) v = counts[(size_t)block];
+    prog_fill_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, v);
   }
   void mh(int scope, int block, int K, double *mean_nodes_dev, long long *acc_dev) override {
     block = block_of(scope, block, false);
     VK_REQUIRE(propagated || G == 0, VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
-    const int n_steps = block == VK_BLOCK_EACH ? K * S : K;
+    const int n_steps = block == VK_BLOCK_EACH ? K * scope_blocks(scope) : K;
     const uint32_t step0 = h->next_step((uint32_t)n_steps);
-    if (warp_mode()) prog_mh_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, block, mean_nodes_dev, acc_dev);
-    else prog_mh_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, block, mean_nodes_dev, acc_dev);
-    if (mean_nodes_dev && block != VK_BLOCK_ONE) {
-      double v = 0.0;
-      if (K > 0 && block == VK_BLOCK_EACH) {       // scaffolder_loop: the blocks' counts summed, FLOOR-divided by #blocks (dispatch.py:122-128)
-        double sum = 0.0;
-        for (int k = 0; k < S; ++k) sum += affected_host[(size_t)k];
-        v = floor(sum / (double)S);
-      } else if (K > 0) v = affected_host[(size_t)block];
-      prog_fill_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, v);
-    }
+    if (warp_mode()) prog_mh_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, mean_nodes_dev, acc_dev);
+    else prog_mh_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, mean_nodes_dev, acc_dev);
+    fill_nodes(mean_nodes_dev, scope, block, K, affected_host.data());
     VK_CUDA(cudaGetLastError());
-  }
-  void fill_nodes(double *mean_nodes_dev, int block, int K) {
-    if (!mean_nodes_dev || block == VK_BLOCK_ONE) return;
-    double v = 0.0;
-    if (K > 0 && block == VK_BLOCK_EACH) {         // scaffolder_loop: the blocks' counts summed, FLOOR-divided by #blocks (dispatch.py:122-128)
-      double sum = 0.0;
-      for (int k = 0; k < S; ++k) sum += affected_host[(size_t)k];
-      v = floor(sum / (double)S);
-    } else if (K > 0) v = affected_host[(size_t)block];
-    prog_fill_kernel<<<grid_for(h->P, 256, h->sm_count, 4), 256, 0, h->stream>>>(mean_nodes_dev, h->P, v);
   }
   // `each` is not a block of subsampled_mh's indexer (BlockScaffoldIndexer: one or a block, dispatch.py:315-322)
   void subsampled_mh(int scope, int block, int64_t Nbatch, int k0, double eps, int use_delta, double delta_sigma,
                      int update_values, int K, double *mean_nodes_dev, double *stats_dev) override {
     (void)use_delta; (void)delta_sigma; (void)update_values;   // none of the compiled SPs has a delta kernel (psp.py:281; continuous.py:352-353)
     block = block_of(scope, block, false);
-    VK_REQUIRE(block != VK_BLOCK_EACH, VK_EINVAL, "subsampled_mh: block must be one or a site index");
+    VK_REQUIRE(block != VK_BLOCK_EACH, VK_EINVAL, "subsampled_mh: block must be one or a block of the scope");
     VK_REQUIRE(eps >= 0.0 && eps < 0.5, VK_EINVAL, "subsampled_mh: epsilon must be in [0, 0.5)");
     VK_REQUIRE(propagated || G == 0, VK_ESTATE, "subsampled_mh: unpropagated observations; call vk_make_consistent first");
-    for (int k = 0; k < S; ++k)
+    for (int b = 0; b < scope_blocks(scope); ++b) {
+      const int k = scope_site(scope, b);
       if (block == VK_BLOCK_ONE || block == k)
         VK_REQUIRE(ss_kind[(size_t)k] != 2, VK_EUNSUPPORTED,
                    "subsampled_mh: Invalid global border or overlapping local sections at a site of the block "
                    "(the reference raises SubsampledScaffoldError / warns NotApplicable)");
+    }
     const uint32_t step0 = h->next_step((uint32_t)K);
-    if (warp_mode()) prog_ssmh_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
-    else prog_ssmh_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
+    if (warp_mode()) prog_ssmh_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, scope, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
+    else prog_ssmh_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, scope, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
     VK_CUDA(cudaGetLastError());
   }
   void slice(int scope, int block, double w, double m, int K, double *mean_nodes_dev, long long *moved_dev) override {
     block = block_of(scope, block, false);
     VK_REQUIRE(w > 0.0 && m >= 1.0, VK_EINVAL, "slice: w must be positive and m at least 1");
     VK_REQUIRE(propagated || G == 0, VK_ESTATE, "slice: unpropagated observations; call vk_make_consistent first");
-    const int n_steps = block == VK_BLOCK_EACH ? K * S : K;
+    const int n_steps = block == VK_BLOCK_EACH ? K * scope_blocks(scope) : K;
     const uint32_t step0 = h->next_step((uint32_t)n_steps);
-    if (warp_mode()) prog_slice_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, block, w, m, mean_nodes_dev, moved_dev);
-    else prog_slice_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, block, w, m, mean_nodes_dev, moved_dev);
-    fill_nodes(mean_nodes_dev, block, K);
+    if (warp_mode()) prog_slice_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, w, m, mean_nodes_dev, moved_dev);
+    else prog_slice_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, w, m, mean_nodes_dev, moved_dev);
+    fill_nodes(mean_nodes_dev, scope, block, K, affected_host.data());
     VK_CUDA(cudaGetLastError());
   }
   void log_likelihood_at(int scope, int block, bool joint, double *out_dev) override {
     block = block_of(scope, block, true);
-    VK_REQUIRE(block == VK_BLOCK_ALL || block >= 0, VK_EINVAL, "log_likelihood_at: block must be all or a site index");
+    VK_REQUIRE(block == VK_BLOCK_ALL || block >= 0, VK_EINVAL, "log_likelihood_at: block must be all or a block of the scope");
     launch(VM_MODE_LOGLIK, out_dev, 0, block, joint ? 1 : 0);
   }
   int64_t num_sites() const override { return S; }
-  int64_t num_blocks(int) const override { return S; }
+  int64_t num_blocks(int scope) const override { return scope_blocks(scope); }
   void read_site(int64_t site, double *out_dev) override {
     VK_REQUIRE(site >= 0 && site < S, VK_EINVAL, "program: site out of range");
     VK_CUDA(cudaMemcpyAsync(out_dev, sites + site * h->P, (size_t)h->P * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));

@@ -210,6 +210,14 @@ class B200TraceSet(object):
         else:
             raise VentureException("invalid_argument", "scope %r is not compiled for this model (have %s)"
                                    % (scope, sorted(scopes)))
+        # a scope made by `tag` names its blocks by the program's own values (numbers or symbols): -> the block's index
+        tagged = getattr(self.model, "scope_blocks", {}).get(sid)
+        if tagged is not None:
+            key = float(block) if isinstance(block, (int, float)) and not isinstance(block, bool) else block
+            if key in tagged:
+                return sid, tagged[key]
+            if not (isinstance(block, str) and block in _BLOCKS):
+                raise VentureException("invalid_argument", "scope %r has no block %r (have %s)" % (scope, block, sorted(tagged, key=str)))
         if isinstance(block, str):
             if block not in _BLOCKS:
                 raise VentureException("invalid_argument", "unknown block %r" % (block,))

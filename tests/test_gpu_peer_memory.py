@@ -177,6 +177,40 @@ def _unfused_small_state_worker(rank, world, port, out_q):
     _small_state_worker(rank, world, port, out_q)
 
 
+def _absent_peer_worker(rank, world, port, out_q):
+    """rank 1 never calls resample: rank 0's kernel gives up after VK_P2P_TIMEOUT_S, reports it, and the particle set
+    refuses further use (include/venture_b200.h, failure policy of vk_p2p_resample)"""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    os.environ["VK_P2P_TIMEOUT_S"] = "1"
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import venturecxx_b200 as vb
+    from venturecxx_b200.distributed import ShardedTraceSet
+    from helpers import golden
+    H = golden("hmm.json")
+    dev = _device_for(rank)
+    torch.cuda.set_device(dev)
+    sh = ShardedTraceSet(vb.HMMModel(H["transition_matrix"], H["emission_matrix"], 1, 20), 2000, seed=3, device=dev)
+    sh.enable_peer_memory()
+    res = "idle"
+    if rank == 0:
+        sh.observe(H["data"][0])
+        sh.incorporate(return_increments=False)
+        sh.resample(mode="systematic")
+        timed_out, _ = sh.peer_status()
+        raised = False
+        try:
+            sh.log_weights
+        except vb.VentureException:
+            raised = True
+        res = (timed_out, raised)
+    dist.barrier()
+    out_q.put((rank, res))
+    dist.barrier()
+    sh.local.close()
+    dist.destroy_process_group()
+
+
 def _run(worker, world=2):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
@@ -216,3 +250,8 @@ def test_peer_memory_resample_separate_kernels():
 def test_peer_memory_subsampled_mh_two_ranks():
     res = _run(_ssmh_worker)
     assert res[0][1] == res[1][1]
+
+
+def test_peer_memory_absent_peer_is_reported():
+    res = _run(_absent_peer_worker)
+    assert res[0][1] == (True, True) and res[1][1] == "idle"

@@ -418,6 +418,11 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
   __shared__ double se_sh;
   __shared__ int cur_sh[P2P_MAX_WORLD];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  // a timed-out exchange or barrier: the particle set is invalid from here on; the weights say so (the sticky error
+  // word makes the next host-synchronising call fail)
+  auto poison = [&]() {
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) arrs.lw[t] = NAN;
+  };
   const bool prof = arrs.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
   unsigned long long tp = prof ? p2p_now_ns() : 0ull;
 #define P2P_PROF(slot) do { if (prof) { const unsigned long long now_ = p2p_now_ns(); arrs.prof[slot] += now_ - tp; tp = now_; } } while (0)
@@ -430,7 +435,7 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
     if (threadIdx.x == 0) { mm_sh[0] = mx; mm_sh[1] = mn; mm_sh[2] = nanf; ok_sh = ok ? 1 : 0; }
   }
   __syncthreads();
-  if (!ok_sh) return;
+  if (!ok_sh) { poison(); return; }
   P2P_PROF(0);
   const double m = mm_sh[0];
   // ---- fixed-point weights of this thread's particles (thread-contiguous, as p2p_offspring_kernel)
@@ -465,7 +470,7 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
   }
   // ---- every tile total is in memory
   P2P_PROF(1);
-  if (!p2p_grid_barrier(bar, bar_target - gridDim.x, par, arrs.timeout_ns, arrs.err_host)) return;
+  if (!p2p_grid_barrier(bar, bar_target - gridDim.x, par, arrs.timeout_ns, arrs.err_host)) { poison(); return; }
   P2P_PROF(2);
   const int n_tiles = (int)gridDim.x;
   {
@@ -509,7 +514,7 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
     }
   }
   __syncthreads();
-  if (!ok_sh) return;
+  if (!ok_sh) { poison(); return; }
   P2P_PROF(4);
   const uint64_t W = tot_sh[1];
   const double even = p2p_lse(x1.n_total, mm_sh[0], mm_sh[1], mm_sh[2], se_sh) - arrs.log_p_total;
@@ -539,7 +544,7 @@ p2p_resample_fused_kernel(const double *__restrict__ lw_in, int64_t n, double *_
   // ---- every ancestor this rank produces is stored: the gather below polls only for what peers still owe (spinning
   // on local ancestors while neighbouring CTAs are still in their offspring loop costs more than this barrier:
   // 62.7 -> 59.7 us per step at a world of one)
-  if (!p2p_grid_barrier(bar, bar_target, par, arrs.timeout_ns, arrs.err_host)) return;
+  if (!p2p_grid_barrier(bar, bar_target, par, arrs.timeout_ns, arrs.err_host)) { poison(); return; }
   P2P_PROF(6);
   // ---- gather of this CTA's share of the child slots
   if (!p2p_gather_slots<GS, MAXU>(anc_mine, n, par, arrs, tab, cur_sh, even)) {

@@ -414,3 +414,27 @@ def test_reference_engine_compiles_tagged_scopes():
     final = np.stack([ts.read_site(j) for j in range(3)])
     np.testing.assert_array_equal(final[2], before[2])
     assert (final[0] != before[0]).any()
+
+
+@pytest.mark.gpu
+def test_reference_engine_runs_the_logistic_regression_program_text():
+    """INTEGRATION.md's example: tagged weights, `(array ...)`, `vector_dot`, boolean observations, `each` over the tagged
+    scope and `subsampled_mh` -- the reference Engine on the compiled program; the posterior mean of the weight with the
+    most informative column has the data's sign"""
+    from venturecxx_b200 import backend as bk
+    rng = np.random.default_rng(4)
+    X = np.round(rng.normal(size=(80, 2)), 3)
+    y = (X @ np.array([2.0, -1.0]) + 0.3 * rng.normal(size=80)) > 0
+    e = _engine(bk.B200(), seed=6)
+    e.assume("w_0", ref_engine.expression("(tag (quote wts) 0 (normal 0 1))"))
+    e.assume("w_1", ref_engine.expression("(tag (quote wts) 1 (normal 0 1))"))
+    e.assume("w", ref_engine.expression("(array w_0 w_1)"))
+    e.infer(ref_engine.program("(resample 256)"))
+    for x, yi in zip(X, y):
+        e.observe(ref_engine.expression("(log_odds_flip (vector_dot w (array %r %r)))" % (float(x[0]), float(x[1]))),
+                  ref_engine.value(bool(yi)))
+    ts = e.model.b200
+    assert ts.num_sites() == 2 and ts.model.n_observations == 80 and ts.model.prog.subsampled[0]["kind"] == 1
+    e.infer(ref_engine.program("(do (resimulation_mh (quote wts) each 40) (subsampled_mh default one 16 3 0.01 false 0 false 20))"))
+    w0, w1 = ts.read_site(0), ts.read_site(1)
+    assert w0.mean() > 0.5 and w1.mean() < 0.0

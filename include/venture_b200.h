@@ -282,6 +282,11 @@ int vk_pgibbs(vk_particles *h, int32_t scope, int32_t block, int32_t particles, 
  * mean_nodes_out_host as vk_mh; moved_out_host: NULL or P int64 = transitions that changed the value. */
 int vk_slice(vk_particles *h, int32_t scope, int32_t block, double w, double m, int32_t transitions,
              double *mean_nodes_out_host, int64_t *moved_out_host);
+/* Slice sampling with doubling, `(slice_doubling scope block w p transitions)`: infer/dispatch.py:195-199 ->
+ * DoublingSliceOperator, infer/slice_sample.py:148-196 (findInterval: at most p doublings of the interval, one uniform each;
+ * legalProposal: Neal's acceptance test for a point of a doubled interval).  Otherwise as vk_slice. */
+int vk_slice_doubling(vk_particles *h, int32_t scope, int32_t block, double w, int32_t p, int32_t transitions,
+                      double *mean_nodes_out_host, int64_t *moved_out_host);
 
 /* Enumerative Gibbs, `(gibbs scope block transitions)`: infer/dispatch.py:175-179 ->
  * infer/egibbs.py:42-107 (EnumerativeGibbsOperator under mixMH).  For a discrete site every candidate

@@ -203,9 +203,10 @@ class VM(object):
                 nodes[p] += self.affected[k]
         return acc, nodes / max(n_steps, 1)
 
-    def slice(self, n_steps, w, m, block=-1, scope=0):
-        """StepOutSliceOperator under mixMH (infer/slice_sample.py:39-139): draw 0 block choice, then the uniforms in call
-        order.  Returns per-particle mean node counts."""
+    def slice(self, n_steps, w, m, block=-1, scope=0, doubling=False):
+        """StepOutSliceOperator (infer/slice_sample.py:39-139) or, doubling=True, DoublingSliceOperator (:148-196, m = the
+        number of doublings p) under mixMH: draw 0 block choice, then the uniforms in call order.  Returns per-particle
+        mean node counts."""
         step0, self.step = self.step, self.step + n_steps
         nodes = np.zeros(self.P)
         for p in range(self.P):
@@ -222,22 +223,58 @@ class VM(object):
                 logy = f(x0) + math.log(tape(0, [0.0]))
                 L = x0 - w * tape(0, [0.0])
                 Rr = L + w
-                J = math.floor(m * tape(0, [0.0]))
-                K = (m - 1) - J
-                while J > 0:
-                    fl = f(L)
-                    if logy >= fl or math.isnan(fl):
-                        break
-                    L, J = L - w, J - 1
-                while K > 0:
-                    fr = f(Rr)
-                    if logy >= fr or math.isnan(fr):
-                        break
-                    Rr, K = Rr + w, K - 1
+                if doubling:                                     # :155-176
+                    K = m
+                    fl, fr = f(L), f(Rr)
+                    while K > 0:
+                        if logy >= fl and logy >= fr:
+                            break
+                        if math.isnan(fl) or math.isnan(fr):
+                            break
+                        dist = Rr - L
+                        if tape(0, [0.0]) < 0.5:
+                            L = L - dist
+                            fl = f(L)
+                        else:
+                            Rr = Rr + dist
+                            fr = f(Rr)
+                        K -= 1
+                else:
+                    J = math.floor(m * tape(0, [0.0]))
+                    K = (m - 1) - J
+                    while J > 0:
+                        fl = f(L)
+                        if logy >= fl or math.isnan(fl):
+                            break
+                        L, J = L - w, J - 1
+                    while K > 0:
+                        fr = f(Rr)
+                        if logy >= fr or math.isnan(fr):
+                            break
+                        Rr, K = Rr + w, K - 1
+
+                def legal(x1, L, Rr):                            # :178-196 (stepping out: always legal, :146)
+                    if not doubling:
+                        return True
+                    D = False
+                    fr, fl = f(Rr), f(L)
+                    while (Rr - L) > 1.1 * w:
+                        M = (L + Rr) / 2.0
+                        if (x0 < M and x1 >= M) or (x0 >= M and x1 < M):
+                            D = True
+                        if x1 < M:
+                            Rr = M
+                            fr = f(Rr)
+                        else:
+                            L = M
+                            fl = f(L)
+                        if D and logy >= fl and logy >= fr:
+                            return False
+                    return True
                 x1 = x0
                 for _ in range(10000):
                     xc = L + tape(0, [0.0]) * (Rr - L)
-                    if logy <= f(xc):
+                    if logy <= f(xc) and legal(xc, L, Rr):
                         x1 = xc
                         break
                     if xc < x0:

@@ -101,7 +101,7 @@ def run(name, prog, seed, P, K, n_first):
     return out
 
 
-def run_slice(prog, seed, P, K, w, m):
+def run_slice(prog, seed, P, K, w, m, op="slice"):
     """(slice default one w m 1) K times: draw 0 = block choice, then slice_sample.py's uniforms in call order"""
     from make_lite_chains import infer_exp
     out = {"seed": seed, "P": P, "K": K, "w": w, "m": m, "program": [list(d) for d in prog], "steps": {"slice": 50}, "particles": []}
@@ -121,7 +121,7 @@ def run_slice(prog, seed, P, K, w, m):
         mdl.tape.sequential = True
         for k in range(K):
             mdl.tape.begin(50 + k, 1)
-            rec["nodes"].append(mdl.t.primitive_infer(infer_exp("slice", "default", "one", w, m, 1)))
+            rec["nodes"].append(mdl.t.primitive_infer(infer_exp(op, "default", "one", w, m, 1)))
         mdl.tape.sequential = False
         rec["values_slice"] = [fl(mdl.value(did)) for did in random_dids]
         rec["lj_at"] = fl(mdl.t.log_joint_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
@@ -222,6 +222,9 @@ def main():
     fixture["hierarchy"] = run("hierarchy", progs["hierarchy"], 31, 5, 60, 3)
     fixture["regression_slice"] = run_slice(progs["regression2"], 37, 4, 30, 0.7, 8)
     fixture["chain_slice"] = run_slice(progs["chain"], 41, 4, 40, 1.3, 5)
+    # (slice_doubling default one w p 1): DoublingSliceOperator, infer/slice_sample.py:148-196
+    fixture["regression_slice_doubling"] = run_slice(progs["regression2"], 59, 4, 30, 0.4, 5, op="slice_doubling")
+    fixture["chain_slice_doubling"] = run_slice(progs["chain"], 61, 4, 40, 0.9, 3, op="slice_doubling")
     fixture["normal_observes_ssmh"] = run_subsampled(progs["normal_observes"], 43, 5, 40, 5, 2, 0.05)
     fixture["scaled_ssmh"] = run_subsampled(progs["scaled"], 47, 5, 60, 4, 2, 0.1, make_consistent=True)
     fixture["invalid_border_ssmh"] = run_subsampled(progs["invalid_border"], 53, 2, 8, 1, 1, 0.1)

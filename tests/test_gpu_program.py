@@ -58,6 +58,27 @@ def test_compiled_program_reproduces_lite_on_the_device(name):
     np.testing.assert_allclose(ts2.log_joint_at("default", "all"), [unj(r["lj_at"]) for r in recs], rtol=RTOL)
 
 
+@pytest.mark.parametrize("name", ["regression_slice_doubling", "chain_slice_doubling"])
+def test_compiled_slice_doubling_reproduces_lite_on_the_device(name):
+    """`(slice_doubling default one w p K)` on the device against Lite's DoublingSliceOperator run on the same uniforms
+    (infer/slice_sample.py:148-196: doubling of the interval, Neal's acceptance test)"""
+    case = golden("program_chains.json")[name]
+    recs = case["particles"]
+    ts = vb.B200TraceSet(CompiledModel([tuple(d) for d in case["program"]]), case["P"], seed=case["seed"])
+    ts.incorporate()
+    start = np.array([[unj(v) for v in r["values_start"]] for r in recs]).T
+    for j in range(ts.num_sites()):
+        ts.write_site(j, start[j])
+    ts.rng_step = case["steps"]["slice"]
+    nodes, moved = ts.slice_doubling("default", "one", case["w"], case["m"], case["K"], return_moves=True)
+    np.testing.assert_allclose(sites_of(ts).T, [[unj(v) for v in r["values_slice"]] for r in recs], rtol=1e-11)
+    np.testing.assert_allclose(nodes, [np.mean(r["nodes"]) for r in recs], rtol=1e-14)
+    np.testing.assert_allclose(ts.log_joint_at("default", "all"), [unj(r["lj_at"]) for r in recs], rtol=1e-11)
+    assert moved.min() > 0
+    out = ts.primitive_infer(["slice_doubling", "default", "each", case["w"], case["m"], 2])
+    assert out.shape == (case["P"],)
+
+
 @pytest.mark.parametrize("name", ["regression_slice", "chain_slice"])
 def test_compiled_slice_reproduces_lite_on_the_device(name):
     """N4 (slice): `(slice default one w m K)` on the device against Lite's StepOutSliceOperator run on the same

@@ -55,16 +55,17 @@ def test_compiled_program_reproduces_lite(name):
     np.testing.assert_allclose(vm2.log_likelihood(joint=True), [unj(r["lj_at"]) for r in recs], rtol=RTOL)
 
 
-@pytest.mark.parametrize("name", ["regression_slice", "chain_slice"])
+@pytest.mark.parametrize("name", ["regression_slice", "chain_slice", "regression_slice_doubling", "chain_slice_doubling"])
 def test_compiled_slice_reproduces_lite(name):
-    """(slice default one w m 1) x K on Lite (infer/slice_sample.py) vs the compiled program, same uniforms"""
+    """(slice default one w m 1) / (slice_doubling default one w p 1) x K on Lite (infer/slice_sample.py) vs the compiled
+    program, same uniforms"""
     case = golden("program_chains.json")[name]
     m = CompiledModel([tuple(d) for d in case["program"]])
     recs = case["particles"]
     vm = VM(m.prog.blob(), compiler.OP, case["P"], case["seed"])
     vm.sites[:] = np.array([[unj(v) for v in r["values_start"]] for r in recs]).T
     vm.step = case["steps"]["slice"]
-    nodes = vm.slice(case["K"], case["w"], case["m"])
+    nodes = vm.slice(case["K"], case["w"], case["m"], doubling=name.endswith("doubling"))
     np.testing.assert_allclose(vm.sites.T, [[unj(v) for v in r["values_slice"]] for r in recs], rtol=1e-11)
     np.testing.assert_allclose(nodes, [np.mean(r["nodes"]) for r in recs], rtol=1e-14)
     np.testing.assert_allclose(vm.log_likelihood(joint=True), [unj(r["lj_at"]) for r in recs], rtol=1e-11)

@@ -59,6 +59,7 @@ PROTOTYPES = {
     "vk_mh": [_vp, _i32, _i32, _i32, _vp, _vp],
     "vk_gibbs": [_vp, _i32, _i32, _i32, _vp, _vp],
     "vk_slice": [_vp, _i32, _i32, _f64, _f64, _i32, _vp, _vp],
+    "vk_slice_doubling": [_vp, _i32, _i32, _f64, _i32, _i32, _vp, _vp],
     "vk_pgibbs": [_vp, _i32, _i32, _i32, _i32, _vp, _vp],
     "vk_p2p_export": [_vp, _vp, _i32, _vp],
     "vk_p2p_open": [_vp, _i32, _i32, _vp, _i32],

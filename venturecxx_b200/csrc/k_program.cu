@@ -243,7 +243,7 @@ prog_mh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t see
 template <int LANES>
 __global__ void __launch_bounds__(256)
 prog_slice_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int scope,
-                  int block_mode, double w, double m, double *nodes_out, long long *moved_out) {
+                  int block_mode, double w, double m, int doubling, double *nodes_out, long long *moved_out) {
   double R[VM_MAX_REGS];
   const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
   const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
@@ -274,24 +274,47 @@ prog_slice_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t 
       const double logy = f0 + log(r.uniform());
       const double U = r.uniform();
       double L = x0 - w * U, Rr = L + w;
-      const double V = r.uniform();
-      double J = floor(m * V), K = (m - 1.0) - J;
-      for (int it = 1; J > 0.0 && it < 10000; ++it) {
-        const double fl = f(L);
-        if (logy >= fl || fl != fl) break;
-        L -= w; J -= 1.0;
+      if (doubling) {                                      // DoublingSliceOperator.findInterval (:155-176), m = doublings p
+        double fl = f(L), fr = f(Rr);
+        for (double K = m; K > 0.0; K -= 1.0) {
+          if (logy >= fl && logy >= fr) break;
+          if (fl != fl || fr != fr) break;
+          const double dist = Rr - L;
+          if (r.uniform() < 0.5) { L -= dist; fl = f(L); }
+          else { Rr += dist; fr = f(Rr); }
+        }
+      } else {
+        const double V = r.uniform();
+        double J = floor(m * V), K = (m - 1.0) - J;
+        for (int it = 1; J > 0.0 && it < 10000; ++it) {
+          const double fl = f(L);
+          if (logy >= fl || fl != fl) break;
+          L -= w; J -= 1.0;
+        }
+        for (int it = 1; K > 0.0 && it < 10000; ++it) {
+          const double fr = f(Rr);
+          if (logy >= fr || fr != fr) break;
+          Rr += w; K -= 1.0;
+        }
       }
-      for (int it = 1; K > 0.0 && it < 10000; ++it) {
-        const double fr = f(Rr);
-        if (logy >= fr || fr != fr) break;
-        Rr += w; K -= 1.0;
-      }
+      // DoublingSliceOperator.legalProposal (:178-196): would the doubling started at x1 have produced this interval
+      auto legal = [&](double xc, double Ll, double Rl) -> bool {
+        bool D = false;
+        double fr = f(Rl), fl = f(Ll);
+        while ((Rl - Ll) > 1.1 * w) {
+          const double M = (Ll + Rl) / 2.0;
+          if ((x0 < M && xc >= M) || (x0 >= M && xc < M)) D = true;
+          if (xc < M) { Rl = M; fr = f(Rl); } else { Ll = M; fl = f(Ll); }
+          if (D && logy >= fl && logy >= fr) return false;
+        }
+        return true;
+      };
       double x1 = x0;
       for (int it = 1; it < 10000; ++it) {
         const double Us = r.uniform();
         const double xc = L + Us * (Rr - L);
         const double fx = f(xc);
-        if (logy <= fx) { x1 = xc; break; }
+        if (logy <= fx && (!doubling || legal(xc, L, Rr))) { x1 = xc; break; }
         if (xc < x0) L = xc; else Rr = xc;
       }
       const double logu = log(r.uniform());
@@ -650,14 +673,15 @@ struct ProgramModel : Model {
     else prog_ssmh_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, scope, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
     VK_CUDA(cudaGetLastError());
   }
-  void slice(int scope, int block, double w, double m, int K, double *mean_nodes_dev, long long *moved_dev) override {
+  void slice(int scope, int block, double w, double m, int doubling, int K, double *mean_nodes_dev, long long *moved_dev) override {
     block = block_of(scope, block, false);
-    VK_REQUIRE(w > 0.0 && m >= 1.0, VK_EINVAL, "slice: w must be positive and m at least 1");
+    VK_REQUIRE(w > 0.0 && m >= (doubling ? 0.0 : 1.0) && m == floor(m), VK_EINVAL,
+               "slice: w must be positive, m a whole number (at least 1 steps out, at least 0 doublings)");
     VK_REQUIRE(propagated || G == 0, VK_ESTATE, "slice: unpropagated observations; call vk_make_consistent first");
     const int n_steps = block == VK_BLOCK_EACH ? K * scope_blocks(scope) : K;
     const uint32_t step0 = h->next_step((uint32_t)n_steps);
-    if (warp_mode()) prog_slice_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, w, m, mean_nodes_dev, moved_dev);
-    else prog_slice_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, w, m, mean_nodes_dev, moved_dev);
+    if (warp_mode()) prog_slice_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, w, m, doubling, mean_nodes_dev, moved_dev);
+    else prog_slice_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, w, m, doubling, mean_nodes_dev, moved_dev);
     fill_nodes(mean_nodes_dev, scope, block, K, affected_host.data());
     VK_CUDA(cudaGetLastError());
   }

@@ -393,20 +393,28 @@ int vk_pgibbs(vk_particles *h, int32_t scope, int32_t block, int32_t particles, 
   VK_CATCH
 }
 
-int vk_slice(vk_particles *h, int32_t scope, int32_t block, double w, double m, int32_t transitions,
-             double *mean_nodes_out_host, int64_t *moved_out_host) {
+static int slice_call(vk_particles *h, int32_t scope, int32_t block, double w, double m, int doubling, int32_t transitions,
+                      double *mean_nodes_out_host, int64_t *moved_out_host) {
   VK_TRY check_handle(h); use_device(h);
   VK_REQUIRE(transitions >= 0, VK_EINVAL, "transitions must be >= 0");
   HostOut o(h, mean_nodes_out_host, (size_t)h->P);
   if (moved_out_host && h->acc_d.n < (size_t)h->P) { VK_CUDA(cudaStreamSynchronize(h->stream)); h->acc_d.alloc((size_t)h->P); }
   long long *acc = moved_out_host ? h->acc_d.p : nullptr;
   if (acc && transitions == 0) VK_CUDA(cudaMemsetAsync(acc, 0, (size_t)h->P * sizeof(long long), h->stream));
-  h->model->slice(scope, block, w, m, transitions, o.ptr(), acc);
+  h->model->slice(scope, block, w, m, doubling, transitions, o.ptr(), acc);
   if (acc)
     VK_CUDA(cudaMemcpyAsync(moved_out_host, acc, (size_t)h->P * sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
   o.finish();
   if (acc && !mean_nodes_out_host) VK_CUDA(cudaStreamSynchronize(h->stream));
   VK_CATCH
+}
+int vk_slice(vk_particles *h, int32_t scope, int32_t block, double w, double m, int32_t transitions,
+             double *mean_nodes_out_host, int64_t *moved_out_host) {
+  return slice_call(h, scope, block, w, m, 0, transitions, mean_nodes_out_host, moved_out_host);
+}
+int vk_slice_doubling(vk_particles *h, int32_t scope, int32_t block, double w, int32_t p, int32_t transitions,
+                      double *mean_nodes_out_host, int64_t *moved_out_host) {
+  return slice_call(h, scope, block, w, (double)p, 1, transitions, mean_nodes_out_host, moved_out_host);
 }
 
 int vk_gibbs(vk_particles *h, int32_t scope, int32_t block, int32_t transitions, double *mean_nodes_out_host,

@@ -167,7 +167,7 @@ struct Model {
   }
   // slice sampling with stepping out on a continuous one-dimensional site (infer/slice_sample.py); moved_dev counts
   // transitions that changed the value
-  virtual void slice(int scope, int block, double w, double m, int K, double *mean_nodes_dev, long long *moved_dev) {
+  virtual void slice(int scope, int block, double w, double m, int doubling, int K, double *mean_nodes_dev, long long *moved_dev) {
     throw Error(VK_EUNSUPPORTED, "slice: compiled for programs of the model compiler only (vk_create_program)");
   }
   virtual void log_likelihood_at(int scope, int block, bool joint, double *out_dev) {

@@ -159,6 +159,7 @@ def inference_sps(plugin):
         "gibbs": inf.sequenced_sp(transition("gibbs"), inf.transition_oper_type()),
         # :500-516 (slice), :269-300 (pgibbs / func_pgibbs)
         "slice": inf.sequenced_sp(transition("slice"), inf.transition_oper_type([t.NumberType("w : number"), t.IntegerType("m : int")])),
+        "slice_doubling": inf.sequenced_sp(transition("slice_doubling"), inf.transition_oper_type([t.NumberType("w : number"), t.IntegerType("p : int")])),
         "pgibbs": inf.sequenced_sp(transition("pgibbs"), inf.par_transition_oper_type([t.IntegerType("particles : int")])),
         "func_pgibbs": inf.sequenced_sp(transition("func_pgibbs"), inf.par_transition_oper_type([t.IntegerType("particles : int")])),
         # :678-694

@@ -254,6 +254,10 @@ class B200TraceSet(object):
             if len(exp) != 6:
                 raise VentureException("invalid_argument", "slice takes (scope block w m transitions)")
             return self.slice(exp[1], exp[2], exp[3], exp[4], exp[5])
+        if op == "slice_doubling":
+            if len(exp) != 6:
+                raise VentureException("invalid_argument", "slice_doubling takes (scope block w p transitions)")
+            return self.slice_doubling(exp[1], exp[2], exp[3], exp[4], exp[5])
         if op == "subsampled_mh":
             if len(exp) != 10:
                 raise VentureException(
@@ -324,6 +328,15 @@ class B200TraceSet(object):
         out = self._out()
         mv = self._out(dtype=np.int64) if return_moves else None
         _lib.call("vk_slice", self._h, s, b, float(w), float(m), int(transitions), _lib.ptr(out), _lib.ptr(mv))
+        return (out, mv) if return_moves else out
+
+    def slice_doubling(self, scope, block, w, p, transitions, return_moves=False):
+        """(slice_doubling scope block w p transitions): slice sampling with doubling
+        (infer/dispatch.py:195-199 -> DoublingSliceOperator, infer/slice_sample.py:148-196)."""
+        s, b = self._scope_block(scope, block)
+        out = self._out()
+        mv = self._out(dtype=np.int64) if return_moves else None
+        _lib.call("vk_slice_doubling", self._h, s, b, float(w), int(p), int(transitions), _lib.ptr(out), _lib.ptr(mv))
         return (out, mv) if return_moves else out
 
     def subsampled_mh(self, scope, block, Nbatch, k0, epsilon, useDeltaKernels, deltaKernelArgs,

@@ -293,7 +293,8 @@ int vk_slice_doubling(vk_particles *h, int32_t scope, int32_t block, double w, i
  * value is weighted by its regen weight, the new value is drawn proportionally and always accepted.
  * Compiled for the HMM's state sites (scope 0) and the LDA z sites (scope 1 = "z", block = token index,
  * or scope 0 with block = 2 + token index; the default scope's gamma sites cannot be enumerated and
- * give VK_EUNSUPPORTED, as PSP.enumerateValues raises in the reference).  Other models: VK_EUNSUPPORTED.
+ * give VK_EUNSUPPORTED, as PSP.enumerateValues raises in the reference) and for the BOOLEAN sites (flip, log_flip,
+ * log_odds_flip) of compiled programs, in any scope.  Other models and sites: VK_EUNSUPPORTED.
  * mean_nodes_out_host as vk_mh; changed_out_host: NULL or P int64 = transitions that changed the value. */
 int vk_gibbs(vk_particles *h, int32_t scope, int32_t block, int32_t transitions,
              double *mean_nodes_out_host, int64_t *changed_out_host);

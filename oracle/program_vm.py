@@ -96,6 +96,8 @@ class VM(object):
             elif name == "EXPM1": R[d] = math.expm1(R[a])
             elif name == "LOG_LOGISTIC": R[d] = _log_logistic(R[a])
             elif name == "LOGIT": R[d] = math.log(R[a] / (1 - R[a]))
+            elif name == "COND": self._flag = R[a] != 0
+            elif name == "SELECT": R[d] = R[a] if self._flag else R[b]
             elif name == "SIM_NORMAL": R[d] = tape(1, [R[a], R[b]])
             elif name == "SIM_GAMMA": R[d] = tape(2, [R[a], R[b]])
             elif name == "SIM_BETA": R[d] = tape(5, [R[a], R[b]])
@@ -202,6 +204,36 @@ class VM(object):
                     self.sites[k, p] = old
                 nodes[p] += self.affected[k]
         return acc, nodes / max(n_steps, 1)
+
+    def gibbs(self, n_steps, block=-1, scope=0):
+        """EnumerativeGibbsOperator under mixMH (infer/egibbs.py:42-107) on a boolean site: candidates [True, False]
+        (discrete.py:78-86), each weighted by the regen weight with the value forced (its own log density + what absorbs
+        at its border), the new value by sampleLogCategorical (utils.py:170-180; draw 2), always accepted (draw 1 is still
+        drawn).  Returns (changed counts, mean node counts)."""
+        step0, self.step = self.step, self.step + n_steps
+        changed, nodes = np.zeros(self.P, dtype=np.int64), np.zeros(self.P)
+        for p in range(self.P):
+            for t in range(n_steps):
+                u = oracle.uniforms(self.seed, self.p_base + p, step0 + t, 2)
+                k = self.pick(u[0], t, block, scope)
+                old = float(self.sites[k, p])
+                xi = []
+                for v in (1.0, 0.0):
+                    self.sites[k, p] = v
+                    R = [0.0] * self.n_regs
+                    xi.append(self.children(k, R, p) + self.run(self.site[k][2], R, p))
+                mx = max(xi)
+                es = [math.exp(x - mx) for x in xi] if mx > -math.inf else [0.0, 0.0]
+                den = sum(es)
+                ps = [e / den for e in es] if den > 0 else [0.5, 0.5]
+                idx = int(self._tape(p, step0 + t, 2)(3, ps))
+                new = 1.0 if idx == 0 else 0.0
+                if not math.log(u[1]) < 0.0:
+                    new = old
+                self.sites[k, p] = new
+                changed[p] += new != old
+                nodes[p] += self.affected[k]
+        return changed, nodes / max(n_steps, 1)
 
     def slice(self, n_steps, w, m, block=-1, scope=0, doubling=False):
         """StepOutSliceOperator (infer/slice_sample.py:39-139) or, doubling=True, DoublingSliceOperator (:148-196, m = the

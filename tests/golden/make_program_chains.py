@@ -61,7 +61,17 @@ def programs():
              [("observe", ["normal", ["add", "z", c], "s"], v) for c, v in zip(cs, zs)]
     invalid = [("assume", "mu", ["normal", 0.0, 1.0]), ("assume", "x", ["normal", "mu", 1.0]),
                ("observe", ["normal", "x", 1.0], 0.5), ("observe", ["normal", "x", 1.0], 0.7)]
-    return {"regression": regression, "coin": coin, "hierarchy": hier, "regression2": regression2, "chain": chain,
+    # enumerative Gibbs on boolean sites: a two-component mixture with `biplex` (both branches evaluated, no brush), the
+    # three flip SPs, a flip whose probability depends on another flip; the flips are tagged into scope `z`
+    xs5 = [2.3, -0.8, 1.7, -1.4, 0.2]
+    mixture = [("assume", "m0", ["normal", -1.0, 1.0]), ("assume", "m1", ["normal", 2.0, 1.0]),
+               ("assume", "z0", ["tag", ["quote", "z"], 0, ["flip", 0.4]]),
+               ("assume", "z1", ["tag", ["quote", "z"], 1, ["log_flip", -0.7]]),
+               ("assume", "z2", ["tag", ["quote", "z"], 2, ["log_odds_flip", 0.3]]),
+               ("assume", "z3", ["tag", ["quote", "z"], 3, ["flip", ["biplex", "z0", 0.8, 0.2]]]),
+               ("assume", "z4", ["tag", ["quote", "z"], 4, ["flip", 0.5]])] + \
+              [("observe", ["normal", ["biplex", "z%d" % i, "m1", "m0"], 0.7], x) for i, x in enumerate(xs5)]
+    return {"mixture": mixture, "regression": regression, "coin": coin, "hierarchy": hier, "regression2": regression2, "chain": chain,
             "normal_observes": normal_observes, "scaled": scaled, "invalid_border": invalid}
 
 
@@ -194,6 +204,51 @@ def run_subsampled(prog, seed, P, K, Nbatch, k0, eps, block="one", make_consiste
     return out
 
 
+def site_names_of(prog):
+    """the assumes that are random choices (possibly under a tag), by the compiler's own account"""
+    sys.path.insert(0, os.path.join(HERE, "..", ".."))
+    from venturecxx_b200.compiler import CompiledModel
+    return CompiledModel(prog).site_names
+
+
+def run_gibbs(prog, seed, P, K, scope, n_blocks):
+    """(gibbs <scope> one 1) K times, then (gibbs <scope> <block> 1) for every block in order: EnumerativeGibbsOperator,
+    infer/egibbs.py:42-107; draw 0 block choice, draw 1 the accept uniform, draw 2 the categorical over the candidates"""
+    from make_lite_chains import infer_exp
+    out = {"seed": seed, "P": P, "K": K, "scope": scope, "n_blocks": n_blocks, "program": [list(d) for d in prog],
+           "steps": {"prior": 0, "gibbs_one": 20, "gibbs_block": 200}, "particles": []}
+    assumes = [d for d in prog if d[0] == "assume"]
+    observes = [d for d in prog if d[0] == "observe"]
+    for p in range(P):
+        mdl = Model()
+        install(mdl, seed, p)
+        mdl.tape.begin(0, 0)
+        mdl.tape.sequential = True             # the flips' priors draw from py_rng.random(): in call order here
+        dids = [mdl.assume(d[1], d[2]) for d in assumes]
+        mdl.tape.sequential = False            # from now on py_rng.random() is mixMH's accept uniform (draw 1)
+        for d in observes:
+            mdl.observe(d[1], box(d[2]))
+        mdl.t.makeConsistent()
+        site_names = set(site_names_of(prog))
+        random_dids = [did for did, d in zip(dids, assumes) if d[1] in site_names]
+        mdl.tape.site_of = lambda key: int(key.getNumber())          # blocks 0..n-1 of the scope, in order
+
+        def values():
+            return [fl(float(mdl.value(did))) if not isinstance(mdl.value(did), bool) else (1.0 if mdl.value(did) else 0.0) for did in random_dids]
+        rec = {"sites": [d[1] for did, d in zip(dids, assumes) if did in random_dids], "values_prior": values(), "nodes_one": [], "nodes_block": []}
+        for k in range(K):
+            mdl.tape.begin(20 + k, 2)
+            rec["nodes_one"].append(mdl.t.primitive_infer(infer_exp("gibbs", scope, "one", 1)))
+        rec["values_one"] = values()
+        for k in range(2 * n_blocks):
+            mdl.tape.begin(200 + k, 2)
+            rec["nodes_block"].append(mdl.t.primitive_infer(infer_exp("gibbs", scope, k % n_blocks, 1)))
+        rec["values_block"] = values()
+        rec["lj_at"] = fl(mdl.t.log_joint_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
+        out["particles"].append(rec)
+    return out
+
+
 def run_check_applicability(prog):
     """(subsampled_mh_check_applicability default one) on Lite: the warning classes it raises, in order"""
     import warnings
@@ -225,6 +280,7 @@ def main():
     # (slice_doubling default one w p 1): DoublingSliceOperator, infer/slice_sample.py:148-196
     fixture["regression_slice_doubling"] = run_slice(progs["regression2"], 59, 4, 30, 0.4, 5, op="slice_doubling")
     fixture["chain_slice_doubling"] = run_slice(progs["chain"], 61, 4, 40, 0.9, 3, op="slice_doubling")
+    fixture["mixture_gibbs"] = run_gibbs(progs["mixture"], 67, 5, 40, "z", 5)
     fixture["normal_observes_ssmh"] = run_subsampled(progs["normal_observes"], 43, 5, 40, 5, 2, 0.05)
     fixture["scaled_ssmh"] = run_subsampled(progs["scaled"], 47, 5, 60, 4, 2, 0.1, make_consistent=True)
     fixture["invalid_border_ssmh"] = run_subsampled(progs["invalid_border"], 53, 2, 8, 1, 1, 0.1)

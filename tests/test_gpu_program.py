@@ -448,3 +448,39 @@ def test_tagged_scopes_on_the_device():
     with pytest.raises(vb.VentureException) as e:
         sub.resimulation_mh("s", 3, 1)
     assert "no block" in str(e.value)
+
+
+def test_compiled_gibbs_reproduces_lite_on_the_device():
+    """`(gibbs z one 1)` x K and `(gibbs z <block> 1)` on the device against Lite's EnumerativeGibbsOperator on the same
+    draws (infer/egibbs.py:42-107): a mixture with `biplex`, the three flip SPs, a flip whose probability hangs on another"""
+    case = golden("program_chains.json")["mixture_gibbs"]
+    recs = case["particles"]
+    ts = vb.B200TraceSet(CompiledModel([tuple(d) for d in case["program"]]), case["P"], seed=case["seed"])
+    ts.rng_step = case["steps"]["prior"]
+    ts.reset_to_prior()
+    ts.incorporate()
+    np.testing.assert_allclose(sites_of(ts).T, [r["values_prior"] for r in recs], rtol=RTOL)
+    ts.rng_step = case["steps"]["gibbs_one"]
+    nodes = [ts.primitive_infer(["gibbs", "z", "one", 1]) for _ in range(case["K"])]
+    np.testing.assert_array_equal(np.array(nodes).T, [r["nodes_one"] for r in recs])
+    np.testing.assert_array_equal(sites_of(ts).T[:, 2:], np.array([r["values_one"] for r in recs])[:, 2:])     # the assignments
+    np.testing.assert_allclose(sites_of(ts).T[:, :2], np.array([r["values_one"] for r in recs])[:, :2], rtol=RTOL)
+    nodes = []
+    for k in range(2 * case["n_blocks"]):
+        ts.rng_step = case["steps"]["gibbs_block"] + k
+        nodes.append(ts.primitive_infer(["gibbs", "z", k % case["n_blocks"], 1]))
+    np.testing.assert_array_equal(np.array(nodes).T, [r["nodes_block"] for r in recs])
+    np.testing.assert_array_equal(sites_of(ts).T[:, 2:], np.array([r["values_block"] for r in recs])[:, 2:])
+    np.testing.assert_allclose(ts.log_joint_at("default", "all"), [unj(r["lj_at"]) for r in recs], rtol=RTOL)
+    # continuous sites cannot be enumerated (PSP.enumerateValues raises in the reference)
+    with pytest.raises(vb.VentureException) as e:
+        ts.primitive_infer(["gibbs", "default", "one", 1])
+    assert "not boolean" in str(e.value)
+    # the posterior of one assignment by enumeration: z4 given the means (its observation is 0.2, flip 0.5 prior)
+    big = vb.B200TraceSet(CompiledModel([tuple(d) for d in case["program"]]), 4000, seed=8)
+    big.incorporate()
+    big.write_site(0, np.full(4000, -1.0)); big.write_site(1, np.full(4000, 2.0))
+    big.primitive_infer(["gibbs", "z", 4, 3])
+    l1, l0 = st.norm(2.0, 0.7).pdf(0.2), st.norm(-1.0, 0.7).pdf(0.2)
+    want = l1 / (l1 + l0)
+    assert abs(big.read_site(6).mean() - want) < 4 * np.sqrt(want * (1 - want) / 4000) + 1e-3

@@ -50,6 +50,7 @@ OP = dict(
     SIM_LOG_ODDS_FLIP=39,
     LD_NORMAL=64, LD_GAMMA=65, LD_BETA=66, LD_UNIFORM=67, LD_EXPON=68, LD_FLIP=69, LD_LOG_FLIP=70,
     LD_LOG_ODDS_FLIP=71,
+    COND=24, SELECT=25,
     STORE=96)
 INSTR_WORDS = 4          # op, dst, a, b
 MAX_REGS = 96
@@ -57,7 +58,9 @@ MAX_REGS = 96
 DET = {"add": ("fold", "ADD"), "mul": ("fold", "MUL"), "sub": (2, "SUB"), "div": (2, "DIV"), "pow": (2, "POW"),
        "min": (2, "MIN"), "max": (2, "MAX"), "sqrt": (1, "SQRT"), "exp": (1, "EXP"), "log": (1, "LOG"),
        "log1p": (1, "LOG1P"), "expm1": (1, "EXPM1"), "logistic": (1, "LOGISTIC"), "log_logistic": (1, "LOG_LOGISTIC"),
-       "logit": (1, "LOGIT"), "negate": (1, "NEG"), "abs": (1, "ABS")}
+       "logit": (1, "LOGIT"), "negate": (1, "NEG"), "abs": (1, "ABS"),
+       # (biplex pred a b), conditionals.py:27-37: both branches are evaluated, no brush; two instructions: COND, SELECT
+       "biplex": (3, "BIPLEX")}
 RANDOM = {"normal": (2, "NORMAL"), "gamma": (2, "GAMMA"), "beta": (2, "BETA"), "uniform_continuous": (2, "UNIFORM"),
           "expon": (1, "EXPON"), "flip": (1, "FLIP"), "bernoulli": (1, "FLIP"), "log_flip": (1, "LOG_FLIP"),
           "log_bernoulli": (1, "LOG_FLIP"), "log_odds_flip": (1, "LOG_ODDS_FLIP"), "log_odds_bernoulli": (1, "LOG_ODDS_FLIP")}
@@ -366,6 +369,10 @@ class _Code(object):
             self.emit("DATA", r, n.hole)
         elif n.kind == "random":
             self.emit("SITE", r, n.site)
+        elif n.op == "BIPLEX":
+            regs = [self.need(a) for a in n.args]
+            self.emit("COND", 0, regs[0])
+            self.emit("SELECT", r, regs[1], regs[2])
         elif n.op == "ARRAY":
             for a in n.args:
                 self.need(a)

@@ -31,7 +31,7 @@ namespace vk {
 enum VMOp {
   VM_CONST = 0, VM_SITE = 1, VM_DATA = 2, VM_ADD = 3, VM_SUB = 4, VM_MUL = 5, VM_DIV = 6, VM_NEG = 7, VM_EXP = 8,
   VM_LOG = 9, VM_SQRT = 10, VM_POW = 11, VM_LOGISTIC = 12, VM_ABS = 13, VM_MIN = 14, VM_MAX = 15, VM_LOG1P = 16,
-  VM_EXPM1 = 17, VM_LOG_LOGISTIC = 18, VM_LOGIT = 19,
+  VM_EXPM1 = 17, VM_LOG_LOGISTIC = 18, VM_LOGIT = 19, VM_COND = 24, VM_SELECT = 25,
   VM_SIM_NORMAL = 32, VM_SIM_GAMMA = 33, VM_SIM_BETA = 34, VM_SIM_UNIFORM = 35, VM_SIM_EXPON = 36, VM_SIM_FLIP = 37,
   VM_SIM_LOG_FLIP = 38, VM_SIM_LOG_ODDS_FLIP = 39,
   VM_LD_NORMAL = 64, VM_LD_GAMMA = 65, VM_LD_BETA = 66, VM_LD_UNIFORM = 67, VM_LD_EXPON = 68, VM_LD_FLIP = 69,
@@ -66,6 +66,7 @@ __device__ __forceinline__ void vm_exec(const VMProg &pg, int section, double *R
                                         int ov_site = -1, double ov_val = 0.0) {
   const int first = __ldg(&pg.dir[2 * section]), n = __ldg(&pg.dir[2 * section + 1]);
   const int32_t *ip = pg.code + (size_t)first * VM_WORDS;
+  bool flag = false;                      // (biplex p a b) = COND p; SELECT dst a b
   for (int i = 0; i < n; ++i, ip += VM_WORDS) {
     const int op = __ldg(ip), d = __ldg(ip + 1), a = __ldg(ip + 2), b = __ldg(ip + 3);   // (one int4 load measured 20 % slower)
     switch (op) {
@@ -89,6 +90,8 @@ __device__ __forceinline__ void vm_exec(const VMProg &pg, int section, double *R
       case VM_EXPM1: R[d] = expm1(R[a]); break;
       case VM_LOG_LOGISTIC: R[d] = log_logistic(R[a]); break;
       case VM_LOGIT: R[d] = logit(R[a]); break;
+      case VM_COND: flag = R[a] != 0.0; break;
+      case VM_SELECT: R[d] = flag ? R[a] : R[b]; break;
       case VM_SIM_NORMAL: R[d] = normal_sim(*rng, R[a], R[b]); break;
       case VM_SIM_GAMMA: R[d] = gamma_sim(*rng, R[a], R[b]); break;
       case VM_SIM_BETA: R[d] = beta_sim(*rng, R[a], R[b]); break;
@@ -437,13 +440,72 @@ prog_ssmh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t s
   }
 }
 
+// `(gibbs scope block transitions)` on a BOOLEAN site: EnumerativeGibbsOperator under mixMH (infer/egibbs.py:42-107).  The
+// candidates are [true, false] (discrete.py:78-86, 121-125, 156-164; a candidate of probability 0 is left out there and gets
+// weight 0 here: the same choice); each is weighted by the regen weight with the value forced (DeterministicLKernel: the
+// site's own log density + what absorbs at its border), the new value is drawn by sampleLogCategorical (utils.py:170-180:
+// exp(xi - max), normalised, one uniform = draw 2) and always accepted (logAlpha = 0; draw 1 is the accept uniform).
+template <int LANES>
+__global__ void __launch_bounds__(256)
+prog_gibbs_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int scope,
+                  int block_mode, double *nodes_out, long long *changed_out) {
+  double R[VM_MAX_REGS];
+  const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
+  const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
+  const int S = __ldg(&pg.scope_tab[2 * scope]);
+  const int32_t *sc_sites = pg.scope_sites + __ldg(&pg.scope_tab[2 * scope + 1]);
+  for (int64_t p = unit; p < P; p += n_units) {
+    long long changed = 0;
+    double nodes = 0.0;
+    for (int t = 0; t < n_steps; ++t) {
+      Stream r(seed, (uint64_t)(p_base + p), step0 + (uint32_t)t);
+      const double u_sel = r.uniform();
+      const double logu = log(r.uniform());
+      int k;
+      if (block_mode == VK_BLOCK_ONE) { k = (int)(u_sel * (double)S); if (k >= S) k = S - 1; k = __ldg(&sc_sites[k]); }
+      else if (block_mode == VK_BLOCK_EACH) k = __ldg(&sc_sites[t % S]);
+      else k = block_mode;
+      double *cell = sites + (int64_t)k * P + p;
+      const int sec_own = __ldg(&pg.site_tab[5 * k + 2]);
+      const double old = *cell;
+      double xi[2];
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        if (LANES == 32) __syncwarp();
+        if (lane == 0) *cell = c == 0 ? 1.0 : 0.0;
+        if (LANES == 32) __syncwarp();
+        double v = vm_children<LANES>(pg, k, R, sites, P, p, lane);
+        vm_exec(pg, sec_own, R, sites, P, p, nullptr, nullptr, v, false);
+        xi[c] = v;
+      }
+      const double mx = fmax(xi[0], xi[1]);
+      double ps[2] = {0.0, 0.0};
+      if (mx > -INFINITY) { ps[0] = exp(xi[0] - mx); ps[1] = exp(xi[1] - mx); }
+      const double den = ps[0] + ps[1];
+      if (den > 0.0) { ps[0] = ps[0] / den; ps[1] = ps[1] / den; } else { ps[0] = 0.5; ps[1] = 0.5; }
+      const int idx = categorical_sim(r, ps, 2, 1);
+      double nv = idx == 0 ? 1.0 : 0.0;
+      if (!(logu < 0.0)) nv = old;
+      if (LANES == 32) __syncwarp();
+      if (lane == 0) *cell = nv;
+      if (LANES == 32) __syncwarp();
+      if (nv != old) ++changed;
+      nodes += __ldg(&pg.affected[k]);
+    }
+    if (lane == 0) {
+      if (changed_out) changed_out[p] = changed;
+      if (nodes_out && block_mode == VK_BLOCK_ONE) nodes_out[p] = n_steps > 0 ? nodes / (double)n_steps : 0.0;
+    }
+  }
+}
+
 __global__ void prog_fill_kernel(double *out, int64_t n, double v) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = v;
 }
 
 struct ProgramModel : Model {
   std::vector<double> affected_host;   // per site: nodes of the regular scaffold, then of the scaffold cut at the global border
-  std::vector<int> ss_kind;
+  std::vector<int> ss_kind, site_bool;
   std::vector<int32_t> scope_tab_host, scope_sites_host;
   int n_scopes = 1;
   DevBuf<int32_t> code, tables;       // tables: dir | site_tab | site_groups | group_tab
@@ -552,6 +614,17 @@ struct ProgramModel : Model {
     for (int k = 0; k < S; ++k)
       for (int j = 0; j < 3; ++j)
         VK_REQUIRE(site_tab[(size_t)k * 5 + j] >= 0 && site_tab[(size_t)k * 5 + j] < n_sections, VK_EINVAL, "program: bad section id");
+    site_bool.assign((size_t)S, 0);           // a site is boolean when its SIM section simulates it with one of the flip SPs
+    for (int k = 0; k < S; ++k) {
+      const int sec = site_tab[(size_t)k * 5];
+      for (int i = dir[2 * sec]; i < dir[2 * sec] + dir[2 * sec + 1]; ++i) {
+        const int32_t *w = code_h + (int64_t)i * VM_WORDS;
+        if (w[0] == VM_STORE && w[2] == k && i > dir[2 * sec]) {
+          const int prev = code_h[(int64_t)(i - 1) * VM_WORDS];
+          site_bool[(size_t)k] = prev == VM_SIM_FLIP || prev == VM_SIM_LOG_FLIP || prev == VM_SIM_LOG_ODDS_FLIP;
+        }
+      }
+    }
     VK_REQUIRE(meta[4] >= 0 && meta[4] < n_sections && meta[5] >= 0 && meta[5] < n_sections, VK_EINVAL, "program: bad section id");
     // upload
     std::vector<int32_t> all;
@@ -671,6 +744,23 @@ struct ProgramModel : Model {
     const uint32_t step0 = h->next_step((uint32_t)K);
     if (warp_mode()) prog_ssmh_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, scope, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
     else prog_ssmh_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, scope, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
+    VK_CUDA(cudaGetLastError());
+  }
+  void gibbs(int scope, int block, int K, double *mean_nodes_dev, long long *changed_dev) override {
+    block = block_of(scope, block, false);
+    VK_REQUIRE(propagated || G == 0, VK_ESTATE, "gibbs: unpropagated observations; call vk_make_consistent first");
+    for (int b = 0; b < scope_blocks(scope); ++b) {
+      const int k = scope_site(scope, b);
+      if (block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || block == k)
+        VK_REQUIRE(site_bool[(size_t)k], VK_EUNSUPPORTED,
+                   "gibbs: a site of the block is not boolean -- only the flip family is enumerated for compiled programs "
+                   "(the reference's PSP.enumerateValues raises for continuous SPs)");
+    }
+    const int n_steps = block == VK_BLOCK_EACH ? K * scope_blocks(scope) : K;
+    const uint32_t step0 = h->next_step((uint32_t)n_steps);
+    if (warp_mode()) prog_gibbs_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, mean_nodes_dev, changed_dev);
+    else prog_gibbs_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, mean_nodes_dev, changed_dev);
+    fill_nodes(mean_nodes_dev, scope, block, K, affected_host.data());
     VK_CUDA(cudaGetLastError());
   }
   void slice(int scope, int block, double w, double m, int doubling, int K, double *mean_nodes_dev, long long *moved_dev) override {

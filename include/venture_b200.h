@@ -298,6 +298,11 @@ int vk_slice_doubling(vk_particles *h, int32_t scope, int32_t block, double w, i
  * mean_nodes_out_host as vk_mh; changed_out_host: NULL or P int64 = transitions that changed the value. */
 int vk_gibbs(vk_particles *h, int32_t scope, int32_t block, int32_t transitions,
              double *mean_nodes_out_host, int64_t *changed_out_host);
+/* `(emap scope block transitions)`: infer/dispatch.py:180-184 -> EnumerativeMAPOperator, infer/egibbs.py:117-121 -- as
+ * vk_gibbs, but the candidate of largest regen weight (the first of equal ones) is taken instead of a draw.  Compiled
+ * for the boolean sites of compiled programs; other models answer VK_EUNSUPPORTED. */
+int vk_emap(vk_particles *h, int32_t scope, int32_t block, int32_t transitions,
+            double *mean_nodes_out_host, int64_t *changed_out_host);
 
 /* `(subsampled_mh scope block Nbatch k0 epsilon useDeltaKernels deltaKernelArgs updateValues transitions)`:
  * infer/dispatch.py:149-152, 315-322 -> infer/subsampled_mh.py:76-171 (subsampledMixMH, sequentialTest).

@@ -205,7 +205,7 @@ class VM(object):
                 nodes[p] += self.affected[k]
         return acc, nodes / max(n_steps, 1)
 
-    def gibbs(self, n_steps, block=-1, scope=0):
+    def gibbs(self, n_steps, block=-1, scope=0, map=False):
         """EnumerativeGibbsOperator under mixMH (infer/egibbs.py:42-107) on a boolean site: candidates [True, False]
         (discrete.py:78-86), each weighted by the regen weight with the value forced (its own log density + what absorbs
         at its border), the new value by sampleLogCategorical (utils.py:170-180; draw 2), always accepted (draw 1 is still
@@ -226,7 +226,10 @@ class VM(object):
                 es = [math.exp(x - mx) for x in xi] if mx > -math.inf else [0.0, 0.0]
                 den = sum(es)
                 ps = [e / den for e in es] if den > 0 else [0.5, 0.5]
-                idx = int(self._tape(p, step0 + t, 2)(3, ps))
+                if map:                                         # EnumerativeMAPOperator, egibbs.py:117-121: no draw
+                    idx = [i for i, x in enumerate(xi) if x == mx][0]
+                else:
+                    idx = int(self._tape(p, step0 + t, 2)(3, ps))
                 new = 1.0 if idx == 0 else 0.0
                 if not math.log(u[1]) < 0.0:
                     new = old

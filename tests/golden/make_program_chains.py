@@ -211,7 +211,7 @@ def site_names_of(prog):
     return CompiledModel(prog).site_names
 
 
-def run_gibbs(prog, seed, P, K, scope, n_blocks):
+def run_gibbs(prog, seed, P, K, scope, n_blocks, op="gibbs"):
     """(gibbs <scope> one 1) K times, then (gibbs <scope> <block> 1) for every block in order: EnumerativeGibbsOperator,
     infer/egibbs.py:42-107; draw 0 block choice, draw 1 the accept uniform, draw 2 the categorical over the candidates"""
     from make_lite_chains import infer_exp
@@ -238,11 +238,11 @@ def run_gibbs(prog, seed, P, K, scope, n_blocks):
         rec = {"sites": [d[1] for did, d in zip(dids, assumes) if did in random_dids], "values_prior": values(), "nodes_one": [], "nodes_block": []}
         for k in range(K):
             mdl.tape.begin(20 + k, 2)
-            rec["nodes_one"].append(mdl.t.primitive_infer(infer_exp("gibbs", scope, "one", 1)))
+            rec["nodes_one"].append(mdl.t.primitive_infer(infer_exp(op, scope, "one", 1)))
         rec["values_one"] = values()
         for k in range(2 * n_blocks):
             mdl.tape.begin(200 + k, 2)
-            rec["nodes_block"].append(mdl.t.primitive_infer(infer_exp("gibbs", scope, k % n_blocks, 1)))
+            rec["nodes_block"].append(mdl.t.primitive_infer(infer_exp(op, scope, k % n_blocks, 1)))
         rec["values_block"] = values()
         rec["lj_at"] = fl(mdl.t.log_joint_at(vv.VentureSymbol("default"), vv.VentureSymbol("all")))
         out["particles"].append(rec)
@@ -281,6 +281,7 @@ def main():
     fixture["regression_slice_doubling"] = run_slice(progs["regression2"], 59, 4, 30, 0.4, 5, op="slice_doubling")
     fixture["chain_slice_doubling"] = run_slice(progs["chain"], 61, 4, 40, 0.9, 3, op="slice_doubling")
     fixture["mixture_gibbs"] = run_gibbs(progs["mixture"], 67, 5, 40, "z", 5)
+    fixture["mixture_emap"] = run_gibbs(progs["mixture"], 71, 5, 12, "z", 5, op="emap")      # EnumerativeMAPOperator, egibbs.py:117-121
     fixture["normal_observes_ssmh"] = run_subsampled(progs["normal_observes"], 43, 5, 40, 5, 2, 0.05)
     fixture["scaled_ssmh"] = run_subsampled(progs["scaled"], 47, 5, 60, 4, 2, 0.1, make_consistent=True)
     fixture["invalid_border_ssmh"] = run_subsampled(progs["invalid_border"], 53, 2, 8, 1, 1, 0.1)

@@ -450,6 +450,28 @@ def test_tagged_scopes_on_the_device():
     assert "no block" in str(e.value)
 
 
+def test_compiled_emap_reproduces_lite_on_the_device():
+    """`(emap z one 1)` / `(emap z <block> 1)`: EnumerativeMAPOperator (infer/egibbs.py:117-121) on the device vs Lite"""
+    case = golden("program_chains.json")["mixture_emap"]
+    recs = case["particles"]
+    ts = vb.B200TraceSet(CompiledModel([tuple(d) for d in case["program"]]), case["P"], seed=case["seed"])
+    ts.rng_step = case["steps"]["prior"]
+    ts.reset_to_prior()
+    ts.incorporate()
+    ts.rng_step = case["steps"]["gibbs_one"]
+    nodes = [ts.primitive_infer(["emap", "z", "one", 1]) for _ in range(case["K"])]
+    np.testing.assert_array_equal(np.array(nodes).T, [r["nodes_one"] for r in recs])
+    np.testing.assert_array_equal(sites_of(ts).T[:, 2:], np.array([r["values_one"] for r in recs])[:, 2:])
+    for k in range(2 * case["n_blocks"]):
+        ts.rng_step = case["steps"]["gibbs_block"] + k
+        ts.emap("z", k % case["n_blocks"], 1)
+    np.testing.assert_array_equal(sites_of(ts).T[:, 2:], np.array([r["values_block"] for r in recs])[:, 2:])
+    np.testing.assert_allclose(ts.log_joint_at("default", "all"), [unj(r["lj_at"]) for r in recs], rtol=RTOL)
+    # a fixed point: another sweep changes nothing
+    _, ch = ts.emap("z", "each", 1, return_changes=True)
+    assert not ch.any()
+
+
 def test_compiled_gibbs_reproduces_lite_on_the_device():
     """`(gibbs z one 1)` x K and `(gibbs z <block> 1)` on the device against Lite's EnumerativeGibbsOperator on the same
     draws (infer/egibbs.py:42-107): a mixture with `biplex`, the three flip SPs, a flip whose probability hangs on another"""

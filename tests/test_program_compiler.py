@@ -302,10 +302,13 @@ def test_tagged_scopes_reproduce_lite():
     assert "blocks of one random choice" in str(e.value)
 
 
-def test_compiled_gibbs_reproduces_lite():
-    """(gibbs z one 1) x K and (gibbs z <block> 1) on Lite (EnumerativeGibbsOperator, infer/egibbs.py:42-107) vs the compiled
-    program: a mixture with `biplex`, the three flip SPs and a flip whose probability hangs on another flip"""
-    case = golden("program_chains.json")["mixture_gibbs"]
+@pytest.mark.parametrize("name", ["mixture_gibbs", "mixture_emap"])
+def test_compiled_gibbs_reproduces_lite(name):
+    """(gibbs z one 1) x K and (gibbs z <block> 1) on Lite (EnumerativeGibbsOperator, infer/egibbs.py:42-107; emap:
+    EnumerativeMAPOperator :117-121) vs the compiled program: a mixture with `biplex`, the three flip SPs and a flip whose
+    probability hangs on another flip"""
+    case = golden("program_chains.json")[name]
+    is_map = name.endswith("emap")
     m = CompiledModel([tuple(d) for d in case["program"]])
     recs = case["particles"]
     assert m.site_names == recs[0]["sites"] and m.scopes == {"default": 0, "z": 1}
@@ -316,13 +319,13 @@ def test_compiled_gibbs_reproduces_lite():
     vm.step = case["steps"]["gibbs_one"]
     nodes = []
     for _ in range(case["K"]):
-        nodes.append(vm.gibbs(1, block=-1, scope=1)[1])
+        nodes.append(vm.gibbs(1, block=-1, scope=1, map=is_map)[1])
     np.testing.assert_array_equal(np.array(nodes).T, [r["nodes_one"] for r in recs])
     np.testing.assert_array_equal(vm.sites.T, [r["values_one"] for r in recs])
     nodes = []
     for k in range(2 * case["n_blocks"]):
         vm.step = case["steps"]["gibbs_block"] + k
-        nodes.append(vm.gibbs(1, block=k % case["n_blocks"], scope=1)[1])
+        nodes.append(vm.gibbs(1, block=k % case["n_blocks"], scope=1, map=is_map)[1])
     np.testing.assert_array_equal(np.array(nodes).T, [r["nodes_block"] for r in recs])
     np.testing.assert_array_equal(vm.sites.T, [r["values_block"] for r in recs])
     np.testing.assert_allclose(vm.log_likelihood(joint=True), [unj(r["lj_at"]) for r in recs], rtol=RTOL)

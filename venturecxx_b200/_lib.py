@@ -58,6 +58,7 @@ PROTOTYPES = {
     "vk_resample": [_vp, _i64, c.c_int, _vp, _vp],
     "vk_mh": [_vp, _i32, _i32, _i32, _vp, _vp],
     "vk_gibbs": [_vp, _i32, _i32, _i32, _vp, _vp],
+    "vk_emap": [_vp, _i32, _i32, _i32, _vp, _vp],
     "vk_slice": [_vp, _i32, _i32, _f64, _f64, _i32, _vp, _vp],
     "vk_slice_doubling": [_vp, _i32, _i32, _f64, _i32, _i32, _vp, _vp],
     "vk_pgibbs": [_vp, _i32, _i32, _i32, _i32, _vp, _vp],

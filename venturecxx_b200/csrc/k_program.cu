@@ -448,7 +448,7 @@ prog_ssmh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t s
 template <int LANES>
 __global__ void __launch_bounds__(256)
 prog_gibbs_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int scope,
-                  int block_mode, double *nodes_out, long long *changed_out) {
+                  int block_mode, int map, double *nodes_out, long long *changed_out) {
   double R[VM_MAX_REGS];
   const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
   const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
@@ -483,7 +483,8 @@ prog_gibbs_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t 
       if (mx > -INFINITY) { ps[0] = exp(xi[0] - mx); ps[1] = exp(xi[1] - mx); }
       const double den = ps[0] + ps[1];
       if (den > 0.0) { ps[0] = ps[0] / den; ps[1] = ps[1] / den; } else { ps[0] = 0.5; ps[1] = 0.5; }
-      const int idx = categorical_sim(r, ps, 2, 1);
+      // emap (EnumerativeMAPOperator, egibbs.py:117-121): the first candidate of maximal weight, no draw
+      const int idx = map ? (xi[0] >= xi[1] || !(xi[1] == xi[1]) ? 0 : 1) : categorical_sim(r, ps, 2, 1);
       double nv = idx == 0 ? 1.0 : 0.0;
       if (!(logu < 0.0)) nv = old;
       if (LANES == 32) __syncwarp();
@@ -747,6 +748,12 @@ struct ProgramModel : Model {
     VK_CUDA(cudaGetLastError());
   }
   void gibbs(int scope, int block, int K, double *mean_nodes_dev, long long *changed_dev) override {
+    enumerate(scope, block, K, 0, mean_nodes_dev, changed_dev);
+  }
+  void emap(int scope, int block, int K, double *mean_nodes_dev, long long *changed_dev) override {
+    enumerate(scope, block, K, 1, mean_nodes_dev, changed_dev);
+  }
+  void enumerate(int scope, int block, int K, int map, double *mean_nodes_dev, long long *changed_dev) {
     block = block_of(scope, block, false);
     VK_REQUIRE(propagated || G == 0, VK_ESTATE, "gibbs: unpropagated observations; call vk_make_consistent first");
     for (int b = 0; b < scope_blocks(scope); ++b) {
@@ -758,8 +765,8 @@ struct ProgramModel : Model {
     }
     const int n_steps = block == VK_BLOCK_EACH ? K * scope_blocks(scope) : K;
     const uint32_t step0 = h->next_step((uint32_t)n_steps);
-    if (warp_mode()) prog_gibbs_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, mean_nodes_dev, changed_dev);
-    else prog_gibbs_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, mean_nodes_dev, changed_dev);
+    if (warp_mode()) prog_gibbs_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, map, mean_nodes_dev, changed_dev);
+    else prog_gibbs_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, map, mean_nodes_dev, changed_dev);
     fill_nodes(mean_nodes_dev, scope, block, K, affected_host.data());
     VK_CUDA(cudaGetLastError());
   }

@@ -417,20 +417,30 @@ int vk_slice_doubling(vk_particles *h, int32_t scope, int32_t block, double w, i
   return slice_call(h, scope, block, w, (double)p, 1, transitions, mean_nodes_out_host, moved_out_host);
 }
 
-int vk_gibbs(vk_particles *h, int32_t scope, int32_t block, int32_t transitions, double *mean_nodes_out_host,
-             int64_t *changed_out_host) {
+static int gibbs_call(vk_particles *h, int32_t scope, int32_t block, int32_t transitions, double *mean_nodes_out_host,
+                      int64_t *changed_out_host, bool map) {
   VK_TRY check_handle(h); use_device(h);
   VK_REQUIRE(transitions >= 0, VK_EINVAL, "transitions must be >= 0");
   HostOut o(h, mean_nodes_out_host, (size_t)h->P);
   if (changed_out_host && h->acc_d.n < (size_t)h->P) { VK_CUDA(cudaStreamSynchronize(h->stream)); h->acc_d.alloc((size_t)h->P); }
   long long *acc = changed_out_host ? h->acc_d.p : nullptr;
   if (acc && transitions == 0) VK_CUDA(cudaMemsetAsync(acc, 0, (size_t)h->P * sizeof(long long), h->stream));
-  h->model->gibbs(scope, block, transitions, o.ptr(), acc);
+  if (map) h->model->emap(scope, block, transitions, o.ptr(), acc);
+  else h->model->gibbs(scope, block, transitions, o.ptr(), acc);
   if (acc)
     VK_CUDA(cudaMemcpyAsync(changed_out_host, acc, (size_t)h->P * sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
   o.finish();
   if (acc && !mean_nodes_out_host) VK_CUDA(cudaStreamSynchronize(h->stream));
   VK_CATCH
+}
+
+int vk_gibbs(vk_particles *h, int32_t scope, int32_t block, int32_t transitions, double *mean_nodes_out_host,
+             int64_t *changed_out_host) {
+  return gibbs_call(h, scope, block, transitions, mean_nodes_out_host, changed_out_host, false);
+}
+int vk_emap(vk_particles *h, int32_t scope, int32_t block, int32_t transitions, double *mean_nodes_out_host,
+            int64_t *changed_out_host) {
+  return gibbs_call(h, scope, block, transitions, mean_nodes_out_host, changed_out_host, true);
 }
 
 int vk_subsampled_mh(vk_particles *h, int32_t scope, int32_t block, int64_t Nbatch, int32_t k0,

@@ -161,6 +161,10 @@ struct Model {
   virtual void gibbs(int scope, int block, int K, double *mean_nodes_dev, long long *changed_dev) {
     throw Error(VK_EUNSUPPORTED, "gibbs: this model has no enumerable sites compiled");
   }
+  // `(emap scope block K)`: as gibbs, the candidate of largest weight instead of a draw (infer/egibbs.py:117-121)
+  virtual void emap(int scope, int block, int K, double *mean_nodes_dev, long long *changed_dev) {
+    throw Error(VK_EUNSUPPORTED, "emap: compiled for the boolean sites of programs of the model compiler only");
+  }
   // particle Gibbs over an ordered scope (infer/pgibbs.py): conditional SMC with `particles` inner particles
   virtual void pgibbs(int scope, int block, int particles, int K, double *mean_nodes_dev, long long *acc_dev) {
     throw Error(VK_EUNSUPPORTED, "pgibbs: compiled for the HMM model's ordered state sequence only");

@@ -157,6 +157,7 @@ def inference_sps(plugin):
         "resimulation_mh": inf.sequenced_sp(transition("resimulation_mh"), inf.transition_oper_type()),
         "mh": inf.sequenced_sp(transition("resimulation_mh"), inf.transition_oper_type()),
         "gibbs": inf.sequenced_sp(transition("gibbs"), inf.transition_oper_type()),
+        "emap": inf.sequenced_sp(transition("emap"), inf.par_transition_oper_type()),     # :269-280
         # :500-516 (slice), :269-300 (pgibbs / func_pgibbs)
         "slice": inf.sequenced_sp(transition("slice"), inf.transition_oper_type([t.NumberType("w : number"), t.IntegerType("m : int")])),
         "slice_doubling": inf.sequenced_sp(transition("slice_doubling"), inf.transition_oper_type([t.NumberType("w : number"), t.IntegerType("p : int")])),

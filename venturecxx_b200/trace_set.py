@@ -240,10 +240,12 @@ class B200TraceSet(object):
             if len(exp) != 7:
                 raise VentureException("invalid_argument", "mh_kernel_update takes (scope block useDeltaKernels deltaKernelArgs updateValues transitions)")
             return self.resimulation_mh(exp[1], exp[2], exp[6])
-        if op == "gibbs":
+        if op in ("gibbs", "emap"):
+            if len(exp) == 5 and isinstance(exp[4], bool):      # the trailing in_parallel flag (par_transition_oper_type)
+                exp = exp[:4]
             if len(exp) != 4:
-                raise VentureException("invalid_argument", "gibbs takes (scope block transitions)")
-            return self.gibbs(exp[1], exp[2], exp[3])
+                raise VentureException("invalid_argument", "%s takes (scope block transitions)" % op)
+            return getattr(self, op)(exp[1], exp[2], exp[3])
         if op in ("pgibbs", "func_pgibbs"):
             if len(exp) == 6 and isinstance(exp[5], bool):      # the trailing in_parallel flag (inference_sps.py:269-300)
                 exp = exp[:5]
@@ -310,6 +312,15 @@ class B200TraceSet(object):
         out = self._out()
         ch = self._out(dtype=np.int64) if return_changes else None
         _lib.call("vk_gibbs", self._h, s, b, int(transitions), _lib.ptr(out), _lib.ptr(ch))
+        return (out, ch) if return_changes else out
+
+    def emap(self, scope, block, transitions, return_changes=False):
+        """(emap scope block transitions): move to the conditional maximum found by enumeration
+        (infer/dispatch.py:180-184 -> EnumerativeMAPOperator, infer/egibbs.py:117-121)."""
+        s, b = self._scope_block(scope, block)
+        out = self._out()
+        ch = self._out(dtype=np.int64) if return_changes else None
+        _lib.call("vk_emap", self._h, s, b, int(transitions), _lib.ptr(out), _lib.ptr(ch))
         return (out, ch) if return_changes else out
 
     def pgibbs(self, scope, block, particles, transitions, return_accepts=False):

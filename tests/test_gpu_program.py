@@ -470,6 +470,13 @@ def test_compiled_emap_reproduces_lite_on_the_device():
     # a fixed point: another sweep changes nothing
     _, ch = ts.emap("z", "each", 1, return_changes=True)
     assert not ch.any()
+    # gibbs_update (dispatch.py:185-189) is gibbs on the device: the same chain on the same draws
+    a, b = [vb.B200TraceSet(CompiledModel([tuple(d) for d in case["program"]]), 32, seed=3) for _ in range(2)]
+    for t_ in (a, b):
+        t_.incorporate()
+        t_.rng_step = 77
+    a.primitive_infer(["gibbs_update", "z", "one", 25]), b.primitive_infer(["gibbs", "z", "one", 25])
+    np.testing.assert_array_equal(sites_of(a), sites_of(b))
 
 
 def test_compiled_gibbs_reproduces_lite_on_the_device():

@@ -158,6 +158,8 @@ def inference_sps(plugin):
         "mh": inf.sequenced_sp(transition("resimulation_mh"), inf.transition_oper_type()),
         "gibbs": inf.sequenced_sp(transition("gibbs"), inf.transition_oper_type()),
         "emap": inf.sequenced_sp(transition("emap"), inf.par_transition_oper_type()),     # :269-280
+        "gibbs_update": inf.sequenced_sp(transition("gibbs_update"), inf.par_transition_oper_type()),      # :729-732
+        "pgibbs_update": inf.sequenced_sp(transition("pgibbs_update"), inf.par_transition_oper_type([t.IntegerType("particles : int")])),
         # :500-516 (slice), :269-300 (pgibbs / func_pgibbs)
         "slice": inf.sequenced_sp(transition("slice"), inf.transition_oper_type([t.NumberType("w : number"), t.IntegerType("m : int")])),
         "slice_doubling": inf.sequenced_sp(transition("slice_doubling"), inf.transition_oper_type([t.NumberType("w : number"), t.IntegerType("p : int")])),

@@ -240,6 +240,12 @@ class B200TraceSet(object):
             if len(exp) != 7:
                 raise VentureException("invalid_argument", "mh_kernel_update takes (scope block useDeltaKernels deltaKernelArgs updateValues transitions)")
             return self.resimulation_mh(exp[1], exp[2], exp[6])
+        # gibbs_update / pgibbs_update (dispatch.py:185-189, 213-226): the same operators over scaffolds built with
+        # updateValues=True, i.e. tolerating values left stale by subsampled_mh -- nothing is stale on the device
+        if op == "gibbs_update":
+            op = "gibbs"
+        if op == "pgibbs_update":
+            op = "pgibbs"
         if op in ("gibbs", "emap"):
             if len(exp) == 5 and isinstance(exp[4], bool):      # the trailing in_parallel flag (par_transition_oper_type)
                 exp = exp[:4]

@@ -36,6 +36,13 @@ def _logistic(x):
     return math.exp(x) if x <= -37 else 1.0 / (1.0 + math.exp(-x))
 
 
+def _normalize(seq):                                          # normalizeList, utils.py:93-99
+    den = sum(seq)
+    if den > 0:
+        return [float(x) / den for x in seq]
+    return [1.0 / len(seq) for _ in seq]
+
+
 class VM(object):
     def __init__(self, blob, op_table, P, seed, p_base=0):
         self.code, self.consts, meta, self.data, self.affected = [np.asarray(b) for b in blob]
@@ -96,6 +103,20 @@ class VM(object):
             elif name == "EXPM1": R[d] = math.expm1(R[a])
             elif name == "LOG_LOGISTIC": R[d] = _log_logistic(R[a])
             elif name == "LOGIT": R[d] = math.log(R[a] / (1 - R[a]))
+            elif name == "MOV": R[d] = R[a]
+            elif name == "ARGN": self._argn = a
+            elif name == "LOOKUP":
+                j = int(R[b])
+                R[d] = R[a + j] if 0 <= j < self._argn else math.nan
+            elif name == "SIM_CATEGORICAL":                   # simulateCategorical, utils.py:101-104: normalise, one draw
+                k = self._argn
+                ps = _normalize([R[a + j] for j in range(k)])
+                R[d] = R[a + k + int(tape(3, ps))]
+            elif name == "LD_CATEGORICAL":                    # logDensityCategorical, utils.py:106-118
+                k = self._argn
+                ps = _normalize([R[a + j] for j in range(k)])
+                pm = sum(pj for j, pj in enumerate(ps) if R[a + k + j] == R[d])
+                acc += -math.inf if pm == 0 else math.log(pm)
             elif name == "COND": self._flag = R[a] != 0
             elif name == "SELECT": R[d] = R[a] if self._flag else R[b]
             elif name == "SIM_NORMAL": R[d] = tape(1, [R[a], R[b]])

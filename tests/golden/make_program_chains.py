@@ -71,7 +71,15 @@ def programs():
                ("assume", "z3", ["tag", ["quote", "z"], 3, ["flip", ["biplex", "z0", 0.8, 0.2]]]),
                ("assume", "z4", ["tag", ["quote", "z"], 4, ["flip", 0.5]])] + \
               [("observe", ["normal", ["biplex", "z%d" % i, "m1", "m0"], 0.7], x) for i, x in enumerate(xs5)]
-    return {"mixture": mixture, "regression": regression, "coin": coin, "hierarchy": hier, "regression2": regression2, "chain": chain,
+    # categorical sites (weights literal and computed), `simplex`, `lookup` into an array of sites, literal objects
+    xs3 = [0.1, 1.2, 2.2, -0.4]
+    # (Lite's likelihood_weight regenerates the random choices in the order of its scaffold's border, which for this program is
+    # not the order of the assumes: the test starts the chains from the recorded prior values instead of re-drawing them)
+    mixture3 = [("assume", "m%d" % j, ["normal", float(j), 1.0]) for j in range(3)] + [("assume", "q", ["beta", 2.0, 2.0])] + \
+               [("assume", "z%d" % i, ["categorical", ["simplex", 0.2, 0.5, 0.3]]) for i in range(3)] + \
+               [("assume", "z3", ["categorical", ["simplex", "q", ["sub", 1.0, "q"]], ["array", 2.0, 0.0]])] + \
+               [("observe", ["normal", ["lookup", ["array", "m0", "m1", "m2"], "z%d" % i], 0.7], x) for i, x in enumerate(xs3)]
+    return {"mixture3": mixture3, "mixture": mixture, "regression": regression, "coin": coin, "hierarchy": hier, "regression2": regression2, "chain": chain,
             "normal_observes": normal_observes, "scaled": scaled, "invalid_border": invalid}
 
 
@@ -280,6 +288,7 @@ def main():
     # (slice_doubling default one w p 1): DoublingSliceOperator, infer/slice_sample.py:148-196
     fixture["regression_slice_doubling"] = run_slice(progs["regression2"], 59, 4, 30, 0.4, 5, op="slice_doubling")
     fixture["chain_slice_doubling"] = run_slice(progs["chain"], 61, 4, 40, 0.9, 3, op="slice_doubling")
+    fixture["mixture3"] = run("mixture3", progs["mixture3"], 73, 5, 80, 4)
     fixture["mixture_gibbs"] = run_gibbs(progs["mixture"], 67, 5, 40, "z", 5)
     fixture["mixture_emap"] = run_gibbs(progs["mixture"], 71, 5, 12, "z", 5, op="emap")      # EnumerativeMAPOperator, egibbs.py:117-121
     fixture["normal_observes_ssmh"] = run_subsampled(progs["normal_observes"], 43, 5, 40, 5, 2, 0.05)

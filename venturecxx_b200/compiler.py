@@ -50,7 +50,8 @@ OP = dict(
     SIM_LOG_ODDS_FLIP=39,
     LD_NORMAL=64, LD_GAMMA=65, LD_BETA=66, LD_UNIFORM=67, LD_EXPON=68, LD_FLIP=69, LD_LOG_FLIP=70,
     LD_LOG_ODDS_FLIP=71,
-    COND=24, SELECT=25,
+    COND=24, SELECT=25, MOV=26, ARGN=27, LOOKUP=28,
+    SIM_CATEGORICAL=40, LD_CATEGORICAL=72,
     STORE=96)
 INSTR_WORDS = 4          # op, dst, a, b
 MAX_REGS = 96
@@ -63,7 +64,9 @@ DET = {"add": ("fold", "ADD"), "mul": ("fold", "MUL"), "sub": (2, "SUB"), "div":
        "biplex": (3, "BIPLEX")}
 RANDOM = {"normal": (2, "NORMAL"), "gamma": (2, "GAMMA"), "beta": (2, "BETA"), "uniform_continuous": (2, "UNIFORM"),
           "expon": (1, "EXPON"), "flip": (1, "FLIP"), "bernoulli": (1, "FLIP"), "log_flip": (1, "LOG_FLIP"),
-          "log_bernoulli": (1, "LOG_FLIP"), "log_odds_flip": (1, "LOG_ODDS_FLIP"), "log_odds_bernoulli": (1, "LOG_ODDS_FLIP")}
+          "log_bernoulli": (1, "LOG_FLIP"), "log_odds_flip": (1, "LOG_ODDS_FLIP"), "log_odds_bernoulli": (1, "LOG_ODDS_FLIP"),
+          # (categorical <simplex or array> [<array of literal objects>]), discrete.py:208-246; values default to 0..n-1
+          "categorical": ("cat", "CATEGORICAL")}
 BOOLEAN_VALUED = ("FLIP", "LOG_FLIP", "LOG_ODDS_FLIP")
 
 
@@ -189,7 +192,12 @@ class Compiler(object):
             return self._record_uses(self._finish(Node("det", "TAG", [inner])), [inner], [False])
         args = [self._expr(a, holes) for a in e[1:]]
         via = [isinstance(a, str) for a in e[1:]]
-        if head == "array":
+        if head == "lookup":
+            # (lookup <array> <index>), one deterministic application; the index is a value computed on the device
+            if len(args) != 2 or self.nodes[args[0]].op != "ARRAY":
+                raise VentureException("invalid_argument", "lookup takes an array built by (array ...) / (simplex ...) and an index in the compiled subset")
+            return self._record_uses(self._finish(Node("det", "LOOKUP", args)), args, via)
+        if head in ("array", "simplex"):
             # `(array e_1 ... e_n)` (vectors.py): ONE deterministic application whose value is the tuple of its operands;
             # it owns no register -- vector_dot reads the operands' registers
             return self._record_uses(self._finish(Node("det", "ARRAY", args)), args, via)
@@ -216,6 +224,16 @@ class Compiler(object):
             return self._record_uses(self._finish(Node("det", op, args)), args, via)
         if head in RANDOM:
             arity, op = RANDOM[head]
+            if arity == "cat":
+                if len(args) not in (1, 2) or any(self.nodes[a].op != "ARRAY" for a in args):
+                    raise VentureException("invalid_argument", "categorical takes (simplex ...) or (array ...) weights and optionally an array of objects")
+                if len(args) == 2:
+                    objs = [self.nodes[o] for o in self.nodes[args[1]].args]
+                    if len(objs) != len(self.nodes[args[0]].args) or any(o.kind != "const" for o in objs):
+                        raise VentureException("invalid_argument", "categorical: the objects must be as many literal numbers as there are weights")
+                if not 1 <= len(self.nodes[args[0]].args) <= 32:
+                    raise VentureException("invalid_argument", "categorical: 1 to 32 outcomes are compiled")
+                arity = len(args)
             if op == "FLIP" and not args:
                 args = [self._new(Node("const", value=0.5))]           # (flip) = (flip 0.5), discrete.py:98-102
             if len(args) != arity:
@@ -373,6 +391,13 @@ class _Code(object):
             regs = [self.need(a) for a in n.args]
             self.emit("COND", 0, regs[0])
             self.emit("SELECT", r, regs[1], regs[2])
+        elif n.op == "LOOKUP":
+            arr = self.prog.c.nodes[n.args[0]]
+            self.need(n.args[0])
+            idx = self.need(n.args[1])
+            base = self.block([self.reg(a) for a in arr.args], ("lookup", nid))
+            self.emit("ARGN", 0, len(arr.args))
+            self.emit("LOOKUP", r, base, idx)
         elif n.op == "ARRAY":
             for a in n.args:
                 self.need(a)
@@ -394,14 +419,53 @@ class _Code(object):
         self.done.add(nid)
         return r
 
+    def block(self, regs, key):
+        """copies of `regs` in CONSECUTIVE registers (the variadic instructions address a base register); -> base"""
+        dst = [self.prog.reg_of((key, j)) for j in range(len(regs))]
+        assert dst == list(range(dst[0], dst[0] + len(dst))) if dst else True
+        for d, r in zip(dst, regs):
+            self.emit("MOV", d, r)
+        return dst[0] if dst else 0
+
+    def categorical_block(self, nid):
+        """weights then objects of a categorical in consecutive registers; -> (base, n)"""
+        n = self.prog.c.nodes[nid]
+        nodes = self.prog.c.nodes
+        ws = nodes[n.args[0]].args
+        self.need(n.args[0])
+        regs = [self.reg(a) for a in ws]
+        if len(n.args) == 2:
+            self.need(n.args[1])
+            regs += [self.reg(a) for a in nodes[n.args[1]].args]
+        else:
+            for j in range(len(ws)):
+                c = self.prog.reg_of(("cat-obj", nid, j))
+                self.emit("CONST", c, self.prog.const(float(j)))
+                regs.append(c)
+        return self.block(regs, ("cat", nid)), len(ws)
+
     def log_density(self, nid, value_reg=None):
         n = self.prog.c.nodes[nid]
+        if n.op == "CATEGORICAL":
+            base, k = self.categorical_block(nid)
+            x = value_reg if value_reg is not None else self.need(nid)
+            self.emit("ARGN", 0, k)
+            self.emit("LD_CATEGORICAL", x, base)
+            return
         regs = [self.need(a) for a in n.args]
         x = value_reg if value_reg is not None else self.need(nid)
         self.emit("LD_" + n.op, x, regs[0], regs[1] if len(regs) > 1 else 0)
 
     def simulate(self, nid):
         n = self.prog.c.nodes[nid]
+        if n.op == "CATEGORICAL":
+            base, k = self.categorical_block(nid)
+            r = self.reg(nid)
+            self.emit("ARGN", 0, k)
+            self.emit("SIM_CATEGORICAL", r, base)
+            self.emit("STORE", r, n.site)
+            self.done.add(nid)
+            return
         regs = [self.need(a) for a in n.args]
         r = self.reg(nid)
         self.emit("SIM_" + n.op, r, regs[0], regs[1] if len(regs) > 1 else 0)

@@ -31,15 +31,17 @@ namespace vk {
 enum VMOp {
   VM_CONST = 0, VM_SITE = 1, VM_DATA = 2, VM_ADD = 3, VM_SUB = 4, VM_MUL = 5, VM_DIV = 6, VM_NEG = 7, VM_EXP = 8,
   VM_LOG = 9, VM_SQRT = 10, VM_POW = 11, VM_LOGISTIC = 12, VM_ABS = 13, VM_MIN = 14, VM_MAX = 15, VM_LOG1P = 16,
-  VM_EXPM1 = 17, VM_LOG_LOGISTIC = 18, VM_LOGIT = 19, VM_COND = 24, VM_SELECT = 25,
+  VM_EXPM1 = 17, VM_LOG_LOGISTIC = 18, VM_LOGIT = 19, VM_COND = 24, VM_SELECT = 25, VM_MOV = 26,
+  VM_ARGN = 27, VM_LOOKUP = 28,
   VM_SIM_NORMAL = 32, VM_SIM_GAMMA = 33, VM_SIM_BETA = 34, VM_SIM_UNIFORM = 35, VM_SIM_EXPON = 36, VM_SIM_FLIP = 37,
-  VM_SIM_LOG_FLIP = 38, VM_SIM_LOG_ODDS_FLIP = 39,
+  VM_SIM_LOG_FLIP = 38, VM_SIM_LOG_ODDS_FLIP = 39, VM_SIM_CATEGORICAL = 40,
   VM_LD_NORMAL = 64, VM_LD_GAMMA = 65, VM_LD_BETA = 66, VM_LD_UNIFORM = 67, VM_LD_EXPON = 68, VM_LD_FLIP = 69,
-  VM_LD_LOG_FLIP = 70, VM_LD_LOG_ODDS_FLIP = 71,
+  VM_LD_LOG_FLIP = 70, VM_LD_LOG_ODDS_FLIP = 71, VM_LD_CATEGORICAL = 72,
   VM_STORE = 96
 };
 static const int VM_WORDS = 4;      // op, dst, a, b
 static const int VM_MAX_REGS = 96;
+static const int VM_MAX_ARGN = 32;  // outcomes of a categorical
 
 // device-resident program (all pointers into one allocation each)
 struct VMProg {
@@ -67,6 +69,7 @@ __device__ __forceinline__ void vm_exec(const VMProg &pg, int section, double *R
   const int first = __ldg(&pg.dir[2 * section]), n = __ldg(&pg.dir[2 * section + 1]);
   const int32_t *ip = pg.code + (size_t)first * VM_WORDS;
   bool flag = false;                      // (biplex p a b) = COND p; SELECT dst a b
+  int argn = 0;                           // ARGN n: the length of the register block the next variadic instruction reads
   for (int i = 0; i < n; ++i, ip += VM_WORDS) {
     const int op = __ldg(ip), d = __ldg(ip + 1), a = __ldg(ip + 2), b = __ldg(ip + 3);   // (one int4 load measured 20 % slower)
     switch (op) {
@@ -90,6 +93,29 @@ __device__ __forceinline__ void vm_exec(const VMProg &pg, int section, double *R
       case VM_EXPM1: R[d] = expm1(R[a]); break;
       case VM_LOG_LOGISTIC: R[d] = log_logistic(R[a]); break;
       case VM_LOGIT: R[d] = logit(R[a]); break;
+      case VM_MOV: R[d] = R[a]; break;
+      case VM_ARGN: argn = a; break;
+      case VM_LOOKUP: {                     // (lookup <array> i): block R[a .. a + argn), index R[b]
+        const int j = (int)R[b];
+        R[d] = (j >= 0 && j < argn && (double)j == R[b]) ? R[a + j] : NAN;
+        break;
+      }
+      case VM_SIM_CATEGORICAL: {            // simulateCategorical (utils.py:101-104): normalise, one draw; block = weights, objects
+        double den = 0.0;
+        for (int j = 0; j < argn; ++j) den += R[a + j];
+        double ps[VM_MAX_ARGN];
+        for (int j = 0; j < argn; ++j) ps[j] = den > 0.0 ? R[a + j] / den : 1.0 / (double)argn;
+        R[d] = R[a + argn + categorical_sim(*rng, ps, argn, 1)];
+        break;
+      }
+      case VM_LD_CATEGORICAL: {             // logDensityCategorical (utils.py:106-118): the mass of the objects equal to the value
+        double den = 0.0, pm = 0.0;
+        for (int j = 0; j < argn; ++j) den += R[a + j];
+        for (int j = 0; j < argn; ++j)
+          if (R[a + argn + j] == R[d]) pm += den > 0.0 ? R[a + j] / den : 1.0 / (double)argn;
+        acc += pm == 0.0 ? -INFINITY : log(pm);
+        break;
+      }
       case VM_COND: flag = R[a] != 0.0; break;
       case VM_SELECT: R[d] = flag ? R[a] : R[b]; break;
       case VM_SIM_NORMAL: R[d] = normal_sim(*rng, R[a], R[b]); break;
@@ -593,11 +619,20 @@ struct ProgramModel : Model {
     for (int s = 0; s < n_sections; ++s)
       VK_REQUIRE(dir[2 * s] >= 0 && dir[2 * s + 1] >= 0 && (int64_t)dir[2 * s] + dir[2 * s + 1] <= n_instr, VK_EINVAL,
                  "program: section out of range");
+    int argn_seen = 0;
     for (int64_t i = 0; i < n_instr; ++i) {          // every operand index is checked once, here
       const int32_t *w = code_h + i * VM_WORDS;
       const int op = w[0];
       auto reg = [&](int r) { VK_REQUIRE(r >= 0 && r < n_regs, VK_EINVAL, "program: register out of range"); };
       reg(w[1]);
+      if (op == VM_ARGN) { VK_REQUIRE(w[2] >= 1 && w[2] <= VM_MAX_ARGN, VK_EINVAL, "program: block length out of range"); argn_seen = w[2]; continue; }
+      if (op == VM_LOOKUP || op == VM_SIM_CATEGORICAL || op == VM_LD_CATEGORICAL) {     // a register block, announced by ARGN
+        const int len = op == VM_LOOKUP ? argn_seen : 2 * argn_seen;
+        VK_REQUIRE(argn_seen >= 1 && w[2] >= 0 && w[2] + len <= n_regs, VK_EINVAL, "program: register block out of range");
+        if (op == VM_LOOKUP) reg(w[3]);
+        argn_seen = 0;
+        continue;
+      }
       if (op == VM_CONST) VK_REQUIRE(w[2] >= 0 && w[2] < n_consts, VK_EINVAL, "program: constant out of range");
       else if (op == VM_SITE || op == VM_STORE) VK_REQUIRE(w[2] >= 0 && w[2] < S, VK_EINVAL, "program: site out of range");
       else if (op == VM_DATA) VK_REQUIRE(w[2] >= 0, VK_EINVAL, "program: column out of range");

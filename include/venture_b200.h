@@ -111,7 +111,9 @@ int vk_create_normal_normal(int64_t n_particles, uint64_t seed, int device,
  *             children; the number of scopes, per scope (blocks, offset into the site list), the
  *             blocks' sites -- scope 0 is the default scope (every site, in order), the others are
  *             what `(tag scope block expr)` made (lite/scope.py:25-52; one random choice per block);
- *             entry points taking (scope, block) read block as an index into the scope's list
+ *             entry points taking (scope, block) read block as an index into the scope's list;
+ *             per site (enumeration candidates, offset), then the candidates as indices into consts
+ *             ([true, false] for the flip family, the objects of a categorical, none otherwise)
  *   data      the groups' tables, row-major
  *   affected  2 * n_sites doubles.  Per site: Scaffold.numAffectedNodes (scaffold.py:67-68), what
  *             resimulation_mh reports (dispatch.py:109-120); then per site the same count for the
@@ -294,7 +296,7 @@ int vk_slice_doubling(vk_particles *h, int32_t scope, int32_t block, double w, i
  * Compiled for the HMM's state sites (scope 0) and the LDA z sites (scope 1 = "z", block = token index,
  * or scope 0 with block = 2 + token index; the default scope's gamma sites cannot be enumerated and
  * give VK_EUNSUPPORTED, as PSP.enumerateValues raises in the reference) and for the BOOLEAN sites (flip, log_flip,
- * log_odds_flip) of compiled programs, in any scope.  Other models and sites: VK_EUNSUPPORTED.
+ * log_odds_flip) and CATEGORICAL sites of compiled programs, in any scope.  Other models and sites: VK_EUNSUPPORTED.
  * mean_nodes_out_host as vk_mh; changed_out_host: NULL or P int64 = transitions that changed the value. */
 int vk_gibbs(vk_particles *h, int32_t scope, int32_t block, int32_t transitions,
              double *mean_nodes_out_host, int64_t *changed_out_host);

@@ -72,6 +72,10 @@ class VM(object):
         tab = [(m[at + 2 * i], m[at + 2 * i + 1]) for i in range(n_scopes)]
         at += 2 * n_scopes
         self.scope_sites = [m[at + off: at + off + n] for n, off in tab]       # scope 0 = default: every site
+        at += sum(n for n, _ in tab)
+        ctab = [(m[at + 2 * k], m[at + 2 * k + 1]) for k in range(self.S)]
+        at += 2 * self.S
+        self.candidates = [[float(self.consts[m[at + off + j]]) for j in range(n)] for n, off in ctab]
         self.sites = np.zeros((self.S, P))
         self.lw = np.zeros(P)
         self.step = 0
@@ -239,19 +243,22 @@ class VM(object):
                 k = self.pick(u[0], t, block, scope)
                 old = float(self.sites[k, p])
                 xi = []
-                for v in (1.0, 0.0):
+                cand = self.candidates[k]
+                if not cand:
+                    raise ValueError("gibbs: site %d cannot be enumerated" % k)
+                for v in cand:
                     self.sites[k, p] = v
                     R = [0.0] * self.n_regs
                     xi.append(self.children(k, R, p) + self.run(self.site[k][2], R, p))
                 mx = max(xi)
-                es = [math.exp(x - mx) for x in xi] if mx > -math.inf else [0.0, 0.0]
+                es = [math.exp(x - mx) for x in xi] if mx > -math.inf else [0.0] * len(xi)
                 den = sum(es)
-                ps = [e / den for e in es] if den > 0 else [0.5, 0.5]
+                ps = [e / den for e in es] if den > 0 else [1.0 / len(xi)] * len(xi)
                 if map:                                         # EnumerativeMAPOperator, egibbs.py:117-121: no draw
                     idx = [i for i, x in enumerate(xi) if x == mx][0]
                 else:
                     idx = int(self._tape(p, step0 + t, 2)(3, ps))
-                new = 1.0 if idx == 0 else 0.0
+                new = cand[idx]
                 if not math.log(u[1]) < 0.0:
                     new = old
                 self.sites[k, p] = new

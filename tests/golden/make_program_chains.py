@@ -79,7 +79,13 @@ def programs():
                [("assume", "z%d" % i, ["categorical", ["simplex", 0.2, 0.5, 0.3]]) for i in range(3)] + \
                [("assume", "z3", ["categorical", ["simplex", "q", ["sub", 1.0, "q"]], ["array", 2.0, 0.0]])] + \
                [("observe", ["normal", ["lookup", ["array", "m0", "m1", "m2"], "z%d" % i], 0.7], x) for i, x in enumerate(xs3)]
-    return {"mixture3": mixture3, "mixture": mixture, "regression": regression, "coin": coin, "hierarchy": hier, "regression2": regression2, "chain": chain,
+    # the same with the assignments tagged into scope `z`, for enumerative gibbs over categorical sites (with explicit objects:
+    # Lite's CategoricalOutputPSP.enumerateValues returns bare python ints for the default objects and fails to wrap them)
+    mixture3z = [("assume", "m%d" % j, ["normal", float(j), 1.0]) for j in range(3)] + [("assume", "q", ["beta", 2.0, 2.0])] + \
+                [("assume", "z%d" % i, ["tag", ["quote", "z"], i, ["categorical", ["simplex", 0.2, 0.5, 0.3], ["array", 0.0, 1.0, 2.0]]]) for i in range(3)] + \
+                [("assume", "z3", ["tag", ["quote", "z"], 3, ["categorical", ["simplex", "q", ["sub", 1.0, "q"]], ["array", 2.0, 0.0]]])] + \
+                [("observe", ["normal", ["lookup", ["array", "m0", "m1", "m2"], "z%d" % i], 0.7], x) for i, x in enumerate(xs3)]
+    return {"mixture3z": mixture3z, "mixture3": mixture3, "mixture": mixture, "regression": regression, "coin": coin, "hierarchy": hier, "regression2": regression2, "chain": chain,
             "normal_observes": normal_observes, "scaled": scaled, "invalid_border": invalid}
 
 
@@ -290,6 +296,7 @@ def main():
     fixture["chain_slice_doubling"] = run_slice(progs["chain"], 61, 4, 40, 0.9, 3, op="slice_doubling")
     fixture["mixture3"] = run("mixture3", progs["mixture3"], 73, 5, 80, 4)
     fixture["mixture_gibbs"] = run_gibbs(progs["mixture"], 67, 5, 40, "z", 5)
+    fixture["mixture3_gibbs"] = run_gibbs(progs["mixture3z"], 79, 5, 40, "z", 4)
     fixture["mixture_emap"] = run_gibbs(progs["mixture"], 71, 5, 12, "z", 5, op="emap")      # EnumerativeMAPOperator, egibbs.py:117-121
     fixture["normal_observes_ssmh"] = run_subsampled(progs["normal_observes"], 43, 5, 40, 5, 2, 0.05)
     fixture["scaled_ssmh"] = run_subsampled(progs["scaled"], 47, 5, 60, 4, 2, 0.1, make_consistent=True)

@@ -520,3 +520,25 @@ def test_compiled_gibbs_reproduces_lite_on_the_device():
     l1, l0 = st.norm(2.0, 0.7).pdf(0.2), st.norm(-1.0, 0.7).pdf(0.2)
     want = l1 / (l1 + l0)
     assert abs(big.read_site(6).mean() - want) < 4 * np.sqrt(want * (1 - want) / 4000) + 1e-3
+
+
+def test_compiled_gibbs_over_categorical_sites_on_the_device():
+    """`(gibbs z one 1)` x K and per block on categorical assignments (weights literal and hanging on a beta site, explicit
+    objects, `lookup` into the array of means) against Lite's EnumerativeGibbsOperator on the same draws"""
+    case = golden("program_chains.json")["mixture3_gibbs"]
+    recs = case["particles"]
+    ts = vb.B200TraceSet(CompiledModel([tuple(d) for d in case["program"]]), case["P"], seed=case["seed"])
+    ts.rng_step = case["steps"]["prior"]
+    ts.reset_to_prior()
+    ts.incorporate()
+    np.testing.assert_allclose(sites_of(ts).T, [r["values_prior"] for r in recs], rtol=RTOL)
+    zs = [j for j, n in enumerate(recs[0]["sites"]) if n.startswith("z")]
+    ts.rng_step = case["steps"]["gibbs_one"]
+    nodes = [ts.primitive_infer(["gibbs", "z", "one", 1]) for _ in range(case["K"])]
+    np.testing.assert_array_equal(np.array(nodes).T, [r["nodes_one"] for r in recs])
+    np.testing.assert_array_equal(sites_of(ts).T[:, zs], np.array([r["values_one"] for r in recs])[:, zs])
+    for k in range(2 * case["n_blocks"]):
+        ts.rng_step = case["steps"]["gibbs_block"] + k
+        ts.gibbs("z", k % case["n_blocks"], 1)
+    np.testing.assert_array_equal(sites_of(ts).T[:, zs], np.array([r["values_block"] for r in recs])[:, zs])
+    np.testing.assert_allclose(ts.log_joint_at("default", "all"), [unj(r["lj_at"]) for r in recs], rtol=RTOL)

@@ -146,7 +146,8 @@ def test_blob_is_self_consistent():
     S, G, n_regs, n_sec = [int(v) for v in meta[:4]]
     assert S == 5 and len(affected) == 2 * S and n_regs <= compiler.MAX_REGS     # regular scaffolds, then the global sections
     n_roots = sum(len(ss["roots"]) for ss in m.prog.subsampled)
-    tail = 3 * S + 1 + 2 * n_roots + 1 + 2 + S           # subsampled-MH block, then the scopes (here only the default one)
+    n_cand = sum(len(cd) for cd in m.prog.candidates)
+    tail = 3 * S + 1 + 2 * n_roots + 1 + 2 + S + 2 * S + n_cand     # subsampled-MH block, the scopes (only the default one), candidates
     directory = meta[-tail - 2 * n_sec: -tail].reshape(n_sec, 2)
     assert directory[:, 1].sum() == code.size // compiler.INSTR_WORDS
     ops = set(code.reshape(-1, compiler.INSTR_WORDS)[:, 0].tolist())
@@ -307,7 +308,7 @@ def test_tagged_scopes_reproduce_lite():
     assert "blocks of one random choice" in str(e.value)
 
 
-@pytest.mark.parametrize("name", ["mixture_gibbs", "mixture_emap"])
+@pytest.mark.parametrize("name", ["mixture_gibbs", "mixture_emap", "mixture3_gibbs"])
 def test_compiled_gibbs_reproduces_lite(name):
     """(gibbs z one 1) x K and (gibbs z <block> 1) on Lite (EnumerativeGibbsOperator, infer/egibbs.py:42-107; emap:
     EnumerativeMAPOperator :117-121) vs the compiled program: a mixture with `biplex`, the three flip SPs and a flip whose

@@ -54,7 +54,7 @@ OP = dict(
     SIM_CATEGORICAL=40, LD_CATEGORICAL=72,
     STORE=96)
 INSTR_WORDS = 4          # op, dst, a, b
-MAX_REGS = 96
+MAX_REGS = 128
 
 DET = {"add": ("fold", "ADD"), "mul": ("fold", "MUL"), "sub": (2, "SUB"), "div": (2, "DIV"), "pow": (2, "POW"),
        "min": (2, "MIN"), "max": (2, "MAX"), "sqrt": (1, "SQRT"), "exp": (1, "EXP"), "log": (1, "LOG"),
@@ -552,6 +552,18 @@ class Program(object):
                     cnt += (own.get(nid, 1) if n.counted else 0) + n.lookups
             self.affected.append(float(cnt))
         self.subsampled = [self._subsample_site(k) for k in range(S)]
+        # what enumerative gibbs / emap try at a site (PSP.enumerateValues): [true, false] for the flip family
+        # (discrete.py:78-86, 121-125, 156-164), the objects of a categorical (:229-232); nothing for continuous SPs
+        self.candidates = []
+        for nid in c.sites:
+            n = nodes[nid]
+            if n.op in BOOLEAN_VALUED:
+                self.candidates.append([1.0, 0.0])
+            elif n.op == "CATEGORICAL":
+                k = len(nodes[n.args[0]].args)
+                self.candidates.append([float(nodes[o].value) for o in nodes[n.args[1]].args] if len(n.args) == 2 else [float(j) for j in range(k)])
+            else:
+                self.candidates.append([])
         # scope 0 = default (one block per site, lite/trace.py:116-119), then the tagged scopes; a block is one site here
         self.scope_names, self.scope_sites, self.scope_blocks = ["default"], [list(range(S))], [dict((k, k) for k in range(S))]
         for name, blocks in c.scopes.items():
@@ -704,6 +716,13 @@ class Program(object):
             off += len(sites)
         for sites in self.scope_sites:
             meta += sites
+        # enumeration candidates: per site (count, offset), then indices into the constants
+        off = 0
+        for cand in self.candidates:
+            meta += [len(cand), off]
+            off += len(cand)
+        for cand in self.candidates:
+            meta += [self.const(v) for v in cand]
         return (np.asarray(code, dtype=np.int32), np.asarray(self._consts or [0.0], dtype=np.float64),
                 np.asarray(meta, dtype=np.int32), np.concatenate(data) if data else np.zeros(1),
                 np.asarray(self.affected + [ss["nodes"] for ss in self.subsampled], dtype=np.float64))

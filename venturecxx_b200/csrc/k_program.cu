@@ -40,7 +40,7 @@ enum VMOp {
   VM_STORE = 96
 };
 static const int VM_WORDS = 4;      // op, dst, a, b
-static const int VM_MAX_REGS = 96;
+static const int VM_MAX_REGS = 128;
 static const int VM_MAX_ARGN = 32;  // outcomes of a categorical
 
 // device-resident program (all pointers into one allocation each)
@@ -58,6 +58,8 @@ struct VMProg {
   const double *ss_nodes;    // per site: nodes of the scaffold cut at the global border
   const int32_t *scope_tab;  // per scope: number of blocks, offset into scope_sites (scope 0 = default: every site)
   const int32_t *scope_sites;   // the blocks' sites (one site per block)
+  const int32_t *cand_tab;   // per site: enumeration candidates (count, offset into cand_consts); count 0 = not enumerable
+  const int32_t *cand_consts;   // indices into consts
   int n_sites, n_groups, sec_prior, sec_joint;
 };
 
@@ -494,24 +496,27 @@ prog_gibbs_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t 
       double *cell = sites + (int64_t)k * P + p;
       const int sec_own = __ldg(&pg.site_tab[5 * k + 2]);
       const double old = *cell;
-      double xi[2];
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      const int nc = __ldg(&pg.cand_tab[2 * k]);
+      const int32_t *cc = pg.cand_consts + __ldg(&pg.cand_tab[2 * k + 1]);
+      double xi[VM_MAX_ARGN], ps[VM_MAX_ARGN];
+      double mx = -INFINITY;
+      for (int c = 0; c < nc; ++c) {
         if (LANES == 32) __syncwarp();
-        if (lane == 0) *cell = c == 0 ? 1.0 : 0.0;
+        if (lane == 0) *cell = __ldg(&pg.consts[__ldg(&cc[c])]);
         if (LANES == 32) __syncwarp();
         double v = vm_children<LANES>(pg, k, R, sites, P, p, lane);
         vm_exec(pg, sec_own, R, sites, P, p, nullptr, nullptr, v, false);
         xi[c] = v;
+        mx = fmax(mx, v);
       }
-      const double mx = fmax(xi[0], xi[1]);
-      double ps[2] = {0.0, 0.0};
-      if (mx > -INFINITY) { ps[0] = exp(xi[0] - mx); ps[1] = exp(xi[1] - mx); }
-      const double den = ps[0] + ps[1];
-      if (den > 0.0) { ps[0] = ps[0] / den; ps[1] = ps[1] / den; } else { ps[0] = 0.5; ps[1] = 0.5; }
-      // emap (EnumerativeMAPOperator, egibbs.py:117-121): the first candidate of maximal weight, no draw
-      const int idx = map ? (xi[0] >= xi[1] || !(xi[1] == xi[1]) ? 0 : 1) : categorical_sim(r, ps, 2, 1);
-      double nv = idx == 0 ? 1.0 : 0.0;
+      double den = 0.0;
+      for (int c = 0; c < nc; ++c) { ps[c] = mx > -INFINITY ? exp(xi[c] - mx) : 0.0; den += ps[c]; }
+      for (int c = 0; c < nc; ++c) ps[c] = den > 0.0 ? ps[c] / den : 1.0 / (double)nc;
+      int idx = 0;
+      if (map) {                          // emap (EnumerativeMAPOperator, egibbs.py:117-121): the first candidate of maximal weight, no draw
+        for (int c = 0; c < nc; ++c) if (xi[c] == mx) { idx = c; break; }
+      } else idx = categorical_sim(r, ps, nc, 1);
+      double nv = __ldg(&pg.consts[__ldg(&cc[idx])]);
       if (!(logu < 0.0)) nv = old;
       if (LANES == 32) __syncwarp();
       if (lane == 0) *cell = nv;
@@ -533,7 +538,7 @@ __global__ void prog_fill_kernel(double *out, int64_t n, double v) {
 struct ProgramModel : Model {
   std::vector<double> affected_host;   // per site: nodes of the regular scaffold, then of the scaffold cut at the global border
   std::vector<int> ss_kind, site_bool;
-  std::vector<int32_t> scope_tab_host, scope_sites_host;
+  std::vector<int32_t> scope_tab_host, scope_sites_host, cand_tab_host, cand_consts_host;
   int n_scopes = 1;
   DevBuf<int32_t> code, tables;       // tables: dir | site_tab | site_groups | group_tab
   DevBuf<double> consts, data, affected;
@@ -596,7 +601,23 @@ struct ProgramModel : Model {
     VK_REQUIRE(n_scopes >= 1 && n_scopes <= 64 && n_meta >= at + 2 * (int64_t)n_scopes, VK_EINVAL, "program: bad scope table");
     scope_tab_host.assign(meta + at, meta + at + 2 * (int64_t)n_scopes);
     at += 2 * (int64_t)n_scopes;
-    scope_sites_host.assign(meta + at, meta + n_meta);
+    int64_t n_scope_sites = 0;
+    for (int sc = 0; sc < n_scopes; ++sc) n_scope_sites += scope_tab_host[(size_t)2 * sc] > 0 ? scope_tab_host[(size_t)2 * sc] : 0;
+    VK_REQUIRE(n_meta >= at + n_scope_sites + 2 * (int64_t)S, VK_EINVAL, "program: truncated scope / candidate tables");
+    scope_sites_host.assign(meta + at, meta + at + n_scope_sites);
+    at += n_scope_sites;
+    // enumeration candidates: per site (count, offset), then indices into the constants
+    cand_tab_host.assign(meta + at, meta + at + 2 * (int64_t)S);
+    at += 2 * (int64_t)S;
+    cand_consts_host.assign(meta + at, meta + n_meta);
+    cand_consts_host.push_back(0);
+    for (int k = 0; k < S; ++k) {
+      const int nc = cand_tab_host[(size_t)2 * k], off = cand_tab_host[(size_t)2 * k + 1];
+      VK_REQUIRE(nc >= 0 && nc <= VM_MAX_ARGN && off >= 0 && (size_t)off + (size_t)nc < cand_consts_host.size() + (nc == 0), VK_EINVAL,
+                 "program: bad candidate entry");
+      for (int j = 0; j < nc; ++j)
+        VK_REQUIRE(cand_consts_host[(size_t)off + j] >= 0 && cand_consts_host[(size_t)off + j] < n_consts, VK_EINVAL, "program: candidate constant out of range");
+    }
     for (int sc = 0; sc < n_scopes; ++sc) {
       const int nb = scope_tab_host[(size_t)2 * sc], off = scope_tab_host[(size_t)2 * sc + 1];
       VK_REQUIRE(nb >= (sc == 0 ? S : 1) && off >= 0 && (size_t)off + (size_t)nb <= scope_sites_host.size(), VK_EINVAL, "program: bad scope entry");
@@ -681,6 +702,10 @@ struct ProgramModel : Model {
     all.insert(all.end(), scope_tab_host.begin(), scope_tab_host.end());
     const size_t o_scs = all.size();
     all.insert(all.end(), scope_sites_host.begin(), scope_sites_host.end());
+    const size_t o_ct = all.size();
+    all.insert(all.end(), cand_tab_host.begin(), cand_tab_host.end());
+    const size_t o_cc = all.size();
+    all.insert(all.end(), cand_consts_host.begin(), cand_consts_host.end());
     code.alloc((size_t)(n_code > 0 ? n_code : 1)); tables.alloc(all.size());
     consts.alloc((size_t)(n_consts > 0 ? n_consts : 1)); data.alloc((size_t)(n_data > 0 ? n_data : 1)); affected.alloc((size_t)2 * S);
     VK_CUDA(cudaMemcpyAsync(code.p, code_h, (size_t)n_code * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
@@ -697,6 +722,7 @@ struct ProgramModel : Model {
     pg.affected = affected.p; pg.ss_nodes = affected.p + S;
     pg.ss_tab = tables.p + o_ss; pg.ss_roots = tables.p + o_roots;
     pg.scope_tab = tables.p + o_sct; pg.scope_sites = tables.p + o_scs;
+    pg.cand_tab = tables.p + o_ct; pg.cand_consts = tables.p + o_cc;
     affected_host.assign(affected_h, affected_h + 2 * S);
     pg.n_sites = S; pg.n_groups = G; pg.sec_prior = meta[4]; pg.sec_joint = meta[5];
   }
@@ -794,8 +820,8 @@ struct ProgramModel : Model {
     for (int b = 0; b < scope_blocks(scope); ++b) {
       const int k = scope_site(scope, b);
       if (block == VK_BLOCK_ONE || block == VK_BLOCK_EACH || block == k)
-        VK_REQUIRE(site_bool[(size_t)k], VK_EUNSUPPORTED,
-                   "gibbs: a site of the block is not boolean -- only the flip family is enumerated for compiled programs "
+        VK_REQUIRE(cand_tab_host[(size_t)2 * k] > 0, VK_EUNSUPPORTED,
+                   "gibbs: a site of the block is not boolean or categorical -- only those are enumerated for compiled programs "
                    "(the reference's PSP.enumerateValues raises for continuous SPs)");
     }
     const int n_steps = block == VK_BLOCK_EACH ? K * scope_blocks(scope) : K;

@@ -45,14 +45,13 @@ from .exception import VentureException
 # ---- the register machine (mirrored in csrc/k_program.cu and oracle/oracle.c) ----------------------------
 OP = dict(
     CONST=0, SITE=1, DATA=2, ADD=3, SUB=4, MUL=5, DIV=6, NEG=7, EXP=8, LOG=9, SQRT=10, POW=11, LOGISTIC=12,
-    ABS=13, MIN=14, MAX=15, LOG1P=16, EXPM1=17, LOG_LOGISTIC=18, LOGIT=19,
-    SIM_NORMAL=32, SIM_GAMMA=33, SIM_BETA=34, SIM_UNIFORM=35, SIM_EXPON=36, SIM_FLIP=37, SIM_LOG_FLIP=38,
-    SIM_LOG_ODDS_FLIP=39,
-    LD_NORMAL=64, LD_GAMMA=65, LD_BETA=66, LD_UNIFORM=67, LD_EXPON=68, LD_FLIP=69, LD_LOG_FLIP=70,
-    LD_LOG_ODDS_FLIP=71,
-    COND=24, SELECT=25, MOV=26, ARGN=27, LOOKUP=28,
-    SIM_CATEGORICAL=40, LD_CATEGORICAL=72,
-    STORE=96)
+    ABS=13, MIN=14, MAX=15, LOG1P=16, EXPM1=17, LOG_LOGISTIC=18, LOGIT=19, STORE=20,
+    COND=21, SELECT=22, MOV=23, ARGN=24, LOOKUP=25,
+    # (dense numbering: the interpreter's switch is one jump table)
+    SIM_NORMAL=26, SIM_GAMMA=27, SIM_BETA=28, SIM_UNIFORM=29, SIM_EXPON=30, SIM_FLIP=31, SIM_LOG_FLIP=32,
+    SIM_LOG_ODDS_FLIP=33, SIM_CATEGORICAL=34,
+    LD_NORMAL=35, LD_GAMMA=36, LD_BETA=37, LD_UNIFORM=38, LD_EXPON=39, LD_FLIP=40, LD_LOG_FLIP=41,
+    LD_LOG_ODDS_FLIP=42, LD_CATEGORICAL=43)
 INSTR_WORDS = 4          # op, dst, a, b
 MAX_REGS = 128
 

@@ -28,19 +28,19 @@
 
 namespace vk {
 
-enum VMOp {
+enum VMOp {      // dense: the interpreter's switch compiles to one jump table (mirrors compiler.py OP)
   VM_CONST = 0, VM_SITE = 1, VM_DATA = 2, VM_ADD = 3, VM_SUB = 4, VM_MUL = 5, VM_DIV = 6, VM_NEG = 7, VM_EXP = 8,
   VM_LOG = 9, VM_SQRT = 10, VM_POW = 11, VM_LOGISTIC = 12, VM_ABS = 13, VM_MIN = 14, VM_MAX = 15, VM_LOG1P = 16,
-  VM_EXPM1 = 17, VM_LOG_LOGISTIC = 18, VM_LOGIT = 19, VM_COND = 24, VM_SELECT = 25, VM_MOV = 26,
-  VM_ARGN = 27, VM_LOOKUP = 28,
-  VM_SIM_NORMAL = 32, VM_SIM_GAMMA = 33, VM_SIM_BETA = 34, VM_SIM_UNIFORM = 35, VM_SIM_EXPON = 36, VM_SIM_FLIP = 37,
-  VM_SIM_LOG_FLIP = 38, VM_SIM_LOG_ODDS_FLIP = 39, VM_SIM_CATEGORICAL = 40,
-  VM_LD_NORMAL = 64, VM_LD_GAMMA = 65, VM_LD_BETA = 66, VM_LD_UNIFORM = 67, VM_LD_EXPON = 68, VM_LD_FLIP = 69,
-  VM_LD_LOG_FLIP = 70, VM_LD_LOG_ODDS_FLIP = 71, VM_LD_CATEGORICAL = 72,
-  VM_STORE = 96
+  VM_EXPM1 = 17, VM_LOG_LOGISTIC = 18, VM_LOGIT = 19, VM_STORE = 20, VM_COND = 21, VM_SELECT = 22, VM_MOV = 23,
+  VM_ARGN = 24, VM_LOOKUP = 25,
+  VM_SIM_NORMAL = 26, VM_SIM_GAMMA = 27, VM_SIM_BETA = 28, VM_SIM_UNIFORM = 29, VM_SIM_EXPON = 30, VM_SIM_FLIP = 31,
+  VM_SIM_LOG_FLIP = 32, VM_SIM_LOG_ODDS_FLIP = 33, VM_SIM_CATEGORICAL = 34,
+  VM_LD_NORMAL = 35, VM_LD_GAMMA = 36, VM_LD_BETA = 37, VM_LD_UNIFORM = 38, VM_LD_EXPON = 39, VM_LD_FLIP = 40,
+  VM_LD_LOG_FLIP = 41, VM_LD_LOG_ODDS_FLIP = 42, VM_LD_CATEGORICAL = 43
 };
 static const int VM_WORDS = 4;      // op, dst, a, b
 static const int VM_MAX_REGS = 128;
+static const int VM_LEAN_REGS = 32;   // programs with at most this many registers and none of the extended instructions
 static const int VM_MAX_ARGN = 32;  // outcomes of a categorical
 
 // device-resident program (all pointers into one allocation each)
@@ -65,6 +65,7 @@ struct VMProg {
 
 // one straight-line section.  row: the current row of a group table (nullptr outside row programs).
 // ov_site / ov_val: read site ov_site as ov_val instead of from memory (the OLD value of a proposal in flight).
+template <bool FULL>
 __device__ __forceinline__ void vm_exec(const VMProg &pg, int section, double *R, double *sites, int64_t P, int64_t p,
                                         const double *row, Stream *rng, double &acc, bool store,
                                         int ov_site = -1, double ov_val = 0.0) {
@@ -95,22 +96,40 @@ __device__ __forceinline__ void vm_exec(const VMProg &pg, int section, double *R
       case VM_EXPM1: R[d] = expm1(R[a]); break;
       case VM_LOG_LOGISTIC: R[d] = log_logistic(R[a]); break;
       case VM_LOGIT: R[d] = logit(R[a]); break;
-      case VM_MOV: R[d] = R[a]; break;
-      case VM_ARGN: argn = a; break;
-      case VM_LOOKUP: {                     // (lookup <array> i): block R[a .. a + argn), index R[b]
+      case VM_MOV: if (FULL) { R[d] = R[a]; } break;
+      case VM_ARGN: if (FULL) { argn = a; } break;
+      case VM_LOOKUP: if (FULL) {                     // (lookup <array> i): block R[a .. a + argn), index R[b]
         const int j = (int)R[b];
         R[d] = (j >= 0 && j < argn && (double)j == R[b]) ? R[a + j] : NAN;
         break;
       }
-      case VM_SIM_CATEGORICAL: {            // simulateCategorical (utils.py:101-104): normalise, one draw; block = weights, objects
+      case VM_SIM_CATEGORICAL: if (FULL) {            // simulateCategorical (utils.py:101-104): normalise, one draw; block = weights, objects
+        // (categorical_sim of sp_math.cuh on the normalised weights, without materialising them)
         double den = 0.0;
         for (int j = 0; j < argn; ++j) den += R[a + j];
-        double ps[VM_MAX_ARGN];
-        for (int j = 0; j < argn; ++j) ps[j] = den > 0.0 ? R[a + j] / den : 1.0 / (double)argn;
-        R[d] = R[a + argn + categorical_sim(*rng, ps, argn, 1)];
+        const double uni = 1.0 / (double)argn;
+        double den2 = 0.0;
+        for (int j = 0; j < argn; ++j) den2 += den > 0.0 ? R[a + j] / den : uni;
+        const double u = rng->uniform();
+        int idx;
+        if (!(den2 > 0.0)) { idx = (int)(u * (double)argn); if (idx >= argn) idx = argn - 1; }
+        else {
+          const double t = u * den2;
+          double run = 0.0;
+          int last = 0;
+          idx = -1;
+          for (int j = 0; j < argn; ++j) {
+            const double pj = den > 0.0 ? R[a + j] / den : uni;
+            if (pj > 0.0) last = j;
+            run += pj;
+            if (t < run) { idx = j; break; }
+          }
+          if (idx < 0) idx = last;
+        }
+        R[d] = R[a + argn + idx];
         break;
       }
-      case VM_LD_CATEGORICAL: {             // logDensityCategorical (utils.py:106-118): the mass of the objects equal to the value
+      case VM_LD_CATEGORICAL: if (FULL) {             // logDensityCategorical (utils.py:106-118): the mass of the objects equal to the value
         double den = 0.0, pm = 0.0;
         for (int j = 0; j < argn; ++j) den += R[a + j];
         for (int j = 0; j < argn; ++j)
@@ -118,8 +137,8 @@ __device__ __forceinline__ void vm_exec(const VMProg &pg, int section, double *R
         acc += pm == 0.0 ? -INFINITY : log(pm);
         break;
       }
-      case VM_COND: flag = R[a] != 0.0; break;
-      case VM_SELECT: R[d] = flag ? R[a] : R[b]; break;
+      case VM_COND: if (FULL) { flag = R[a] != 0.0; } break;
+      case VM_SELECT: if (FULL) { R[d] = flag ? R[a] : R[b]; } break;
       case VM_SIM_NORMAL: R[d] = normal_sim(*rng, R[a], R[b]); break;
       case VM_SIM_GAMMA: R[d] = gamma_sim(*rng, R[a], R[b]); break;
       case VM_SIM_BETA: R[d] = beta_sim(*rng, R[a], R[b]); break;
@@ -143,34 +162,34 @@ __device__ __forceinline__ void vm_exec(const VMProg &pg, int section, double *R
 }
 
 // log density of group g's observations (prologue once, then the rows); LANES lanes share the rows
-template <int LANES>
+template <int LANES, bool FULL>
 __device__ __forceinline__ double vm_group(const VMProg &pg, int g, double *R, double *sites, int64_t P, int64_t p, int lane) {
   const int32_t *gt = pg.group_tab + 5 * g;
   const int sec_pro = __ldg(gt), sec_row = __ldg(gt + 1), n_rows = __ldg(gt + 2), n_cols = __ldg(gt + 3), off = __ldg(gt + 4);
   double dummy = 0.0;
-  vm_exec(pg, sec_pro, R, sites, P, p, nullptr, nullptr, dummy, false);
+  vm_exec<FULL>(pg, sec_pro, R, sites, P, p, nullptr, nullptr, dummy, false);
   double part = 0.0;
   for (int r = lane; r < n_rows; r += LANES)
-    vm_exec(pg, sec_row, R, sites, P, p, pg.data + off + (size_t)r * n_cols, nullptr, part, false);
+    vm_exec<FULL>(pg, sec_row, R, sites, P, p, pg.data + off + (size_t)r * n_cols, nullptr, part, false);
   if (LANES == 32) part = warp_sum(part);
   return part;
 }
 
 // what absorbs at site k's border: child sites (CHILD section) + the observation groups below k
-template <int LANES>
+template <int LANES, bool FULL>
 __device__ __forceinline__ double vm_children(const VMProg &pg, int k, double *R, double *sites, int64_t P, int64_t p, int lane) {
   const int32_t *st = pg.site_tab + 5 * k;
   double acc = 0.0;
-  vm_exec(pg, __ldg(st + 1), R, sites, P, p, nullptr, nullptr, acc, false);
+  vm_exec<FULL>(pg, __ldg(st + 1), R, sites, P, p, nullptr, nullptr, acc, false);
   const int ng = __ldg(st + 3), go = __ldg(st + 4);
-  for (int j = 0; j < ng; ++j) acc += vm_group<LANES>(pg, __ldg(&pg.site_groups[go + j]), R, sites, P, p, lane);
+  for (int j = 0; j < ng; ++j) acc += vm_group<LANES, FULL>(pg, __ldg(&pg.site_groups[go + j]), R, sites, P, p, lane);
   return acc;
 }
 
-template <int LANES>
+template <int LANES, bool FULL>
 __device__ __forceinline__ double vm_all_groups(const VMProg &pg, double *R, double *sites, int64_t P, int64_t p, int lane) {
   double acc = 0.0;
-  for (int g = 0; g < pg.n_groups; ++g) acc += vm_group<LANES>(pg, g, R, sites, P, p, lane);
+  for (int g = 0; g < pg.n_groups; ++g) acc += vm_group<LANES, FULL>(pg, g, R, sites, P, p, lane);
   return acc;
 }
 
@@ -185,24 +204,24 @@ enum { VM_MODE_PRIOR = 0, VM_MODE_LW = 1, VM_MODE_CONSISTENT = 2, VM_MODE_LOGLIK
 // mode PRIOR: sites from the prior.  LW: the same, lw := log density of the observations.  CONSISTENT: lw += that,
 // increments out.  LOGLIK: out := xi of the scaffold of `block` (VK_BLOCK_ALL: every observation), + the
 // principal nodes' own densities when joint.
-template <int LANES>
-__global__ void __launch_bounds__(256)
+template <int LANES, bool FULL>
+__global__ void __launch_bounds__(256, 4)
 prog_kernel(VMProg pg, double *sites, double *lw, double *out, int64_t P, int64_t p_base, uint64_t seed, uint32_t step,
             int mode, int block, int joint) {
-  double R[VM_MAX_REGS];
+  double R[FULL ? VM_MAX_REGS : VM_LEAN_REGS];
   const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
   const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
   for (int64_t p = unit; p < P; p += n_units) {
     double dummy = 0.0;
     if (mode == VM_MODE_PRIOR || mode == VM_MODE_LW) {
       Stream r(seed, (uint64_t)(p_base + p), step);
-      vm_exec(pg, pg.sec_prior, R, sites, P, p, nullptr, &r, dummy, lane == 0);
+      vm_exec<FULL>(pg, pg.sec_prior, R, sites, P, p, nullptr, &r, dummy, lane == 0);
       if (LANES == 32) __syncwarp();
     }
     if (mode == VM_MODE_RESIM) {              // sites block.. from their priors GIVEN the current values of the earlier ones
       Stream r(seed, (uint64_t)(p_base + p), step);
       for (int k = block; k < pg.n_sites; ++k) {
-        vm_exec(pg, __ldg(&pg.site_tab[5 * k]), R, sites, P, p, nullptr, &r, dummy, lane == 0);
+        vm_exec<FULL>(pg, __ldg(&pg.site_tab[5 * k]), R, sites, P, p, nullptr, &r, dummy, lane == 0);
         if (LANES == 32) __syncwarp();
       }
       continue;
@@ -210,11 +229,11 @@ prog_kernel(VMProg pg, double *sites, double *lw, double *out, int64_t P, int64_
     if (mode == VM_MODE_PRIOR) continue;
     double v;
     if (mode == VM_MODE_LOGLIK && block >= 0) {
-      v = vm_children<LANES>(pg, block, R, sites, P, p, lane);
-      if (joint) vm_exec(pg, __ldg(&pg.site_tab[5 * block + 2]), R, sites, P, p, nullptr, nullptr, v, false);
+      v = vm_children<LANES, FULL>(pg, block, R, sites, P, p, lane);
+      if (joint) vm_exec<FULL>(pg, __ldg(&pg.site_tab[5 * block + 2]), R, sites, P, p, nullptr, nullptr, v, false);
     } else {
-      v = vm_all_groups<LANES>(pg, R, sites, P, p, lane);
-      if (mode == VM_MODE_LOGLIK && joint) vm_exec(pg, pg.sec_joint, R, sites, P, p, nullptr, nullptr, v, false);
+      v = vm_all_groups<LANES, FULL>(pg, R, sites, P, p, lane);
+      if (mode == VM_MODE_LOGLIK && joint) vm_exec<FULL>(pg, pg.sec_joint, R, sites, P, p, nullptr, nullptr, v, false);
     }
     if (lane != 0) continue;
     if (mode == VM_MODE_LW) lw[p] = v;
@@ -226,11 +245,11 @@ prog_kernel(VMProg pg, double *sites, double *lw, double *out, int64_t P, int64_
   }
 }
 
-template <int LANES>
-__global__ void __launch_bounds__(256)
+template <int LANES, bool FULL>
+__global__ void __launch_bounds__(256, 4)
 prog_mh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int scope,
                int block_mode, double *nodes_out, long long *acc_out) {
-  double R[VM_MAX_REGS];
+  double R[FULL ? VM_MAX_REGS : VM_LEAN_REGS];
   const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
   const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
   const int S = __ldg(&pg.scope_tab[2 * scope]);                       // blocks of the scope (one site each)
@@ -246,13 +265,13 @@ prog_mh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t see
       if (block_mode == VK_BLOCK_ONE) { k = (int)(u_sel * (double)S); if (k >= S) k = S - 1; k = __ldg(&sc_sites[k]); }
       else if (block_mode == VK_BLOCK_EACH) k = __ldg(&sc_sites[t % S]);
       else k = block_mode;
-      const double rho = vm_children<LANES>(pg, k, R, sites, P, p, lane);
+      const double rho = vm_children<LANES, FULL>(pg, k, R, sites, P, p, lane);
       const double old = sites[(int64_t)k * P + p];
       if (LANES == 32) __syncwarp();                      // every lane has read the old value
       double dummy = 0.0;
-      vm_exec(pg, __ldg(&pg.site_tab[5 * k]), R, sites, P, p, nullptr, &r, dummy, lane == 0);
+      vm_exec<FULL>(pg, __ldg(&pg.site_tab[5 * k]), R, sites, P, p, nullptr, &r, dummy, lane == 0);
       if (LANES == 32) __syncwarp();                      // the new value is in memory for every lane
-      const double xi = vm_children<LANES>(pg, k, R, sites, P, p, lane);
+      const double xi = vm_children<LANES, FULL>(pg, k, R, sites, P, p, lane);
       if (logu < vm_log_alpha(rho, xi)) ++acc;
       else { if (LANES == 32) __syncwarp(); if (lane == 0) sites[(int64_t)k * P + p] = old; if (LANES == 32) __syncwarp(); }
       nodes += __ldg(&pg.affected[k]);
@@ -271,11 +290,11 @@ prog_mh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t see
 // + everything absorbing at its border (slice_sample.py:26-37).  Draw layout of a transition: draw 0 block choice, then
 // in call order: the slice height (py_rng.uniform(0,1), :72), the interval position U and the step split V (:98-103),
 // one uniform per shrink step (:49-58), the accept uniform of mixMH (mh.py:85; logAlpha is 0, :85-90).
-template <int LANES>
-__global__ void __launch_bounds__(256)
+template <int LANES, bool FULL>
+__global__ void __launch_bounds__(256, 4)
 prog_slice_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int scope,
                   int block_mode, double w, double m, int doubling, double *nodes_out, long long *moved_out) {
-  double R[VM_MAX_REGS];
+  double R[FULL ? VM_MAX_REGS : VM_LEAN_REGS];
   const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
   const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
   const int S = __ldg(&pg.scope_tab[2 * scope]);                       // blocks of the scope (one site each)
@@ -296,8 +315,8 @@ prog_slice_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t 
         if (LANES == 32) __syncwarp();
         if (lane == 0) *cell = x;
         if (LANES == 32) __syncwarp();
-        double v = vm_children<LANES>(pg, k, R, sites, P, p, lane);
-        vm_exec(pg, sec_own, R, sites, P, p, nullptr, nullptr, v, false);
+        double v = vm_children<LANES, FULL>(pg, k, R, sites, P, p, lane);
+        vm_exec<FULL>(pg, sec_own, R, sites, P, p, nullptr, nullptr, v, false);
         return v;
       };
       const double x0 = *cell;
@@ -372,11 +391,11 @@ prog_slice_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t 
 // program runs once on each.  Draws: 0 block choice, 1 accept uniform, then the proposal; the sections are visited in
 // the keyed Feistel order of (seed, step) -- the same order for every particle, as in the logistic-regression kernels.
 // LANES = 32: lanes take the positions of a minibatch in turn and the warp adds (sum, sum of squares).
-template <int LANES>
-__global__ void __launch_bounds__(256)
+template <int LANES, bool FULL>
+__global__ void __launch_bounds__(256, 4)
 prog_ssmh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int scope,
                  int block_mode, double Nbatch, int k0, double eps, double *nodes_out, double *stats_out) {
-  double Ro[VM_MAX_REGS], Rn[VM_MAX_REGS];
+  double Ro[FULL ? VM_MAX_REGS : VM_LEAN_REGS], Rn[FULL ? VM_MAX_REGS : VM_LEAN_REGS];
   const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
   const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
   const int S = __ldg(&pg.scope_tab[2 * scope]);                       // blocks of the scope (one site each)
@@ -399,21 +418,21 @@ prog_ssmh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t s
       double dummy = 0.0;
       bool accept;
       if (kind != 1) {                                     // no global border: regular MH, alpha > log u (:91-95)
-        const double rho = vm_children<LANES>(pg, k, Ro, sites, P, p, lane);
+        const double rho = vm_children<LANES, FULL>(pg, k, Ro, sites, P, p, lane);
         if (LANES == 32) __syncwarp();
-        vm_exec(pg, __ldg(st), Ro, sites, P, p, nullptr, &r, dummy, lane == 0);
+        vm_exec<FULL>(pg, __ldg(st), Ro, sites, P, p, nullptr, &r, dummy, lane == 0);
         if (LANES == 32) __syncwarp();
-        const double xi = vm_children<LANES>(pg, k, Ro, sites, P, p, lane);
+        const double xi = vm_children<LANES, FULL>(pg, k, Ro, sites, P, p, lane);
         accept = (xi - rho) > logu;
       } else {
         const int ng = __ldg(st + 3), go = __ldg(st + 4);
         for (int j = 0; j < ng; ++j)
-          vm_exec(pg, __ldg(&pg.group_tab[5 * __ldg(&pg.site_groups[go + j])]), Ro, sites, P, p, nullptr, nullptr, dummy, false);
+          vm_exec<FULL>(pg, __ldg(&pg.group_tab[5 * __ldg(&pg.site_groups[go + j])]), Ro, sites, P, p, nullptr, nullptr, dummy, false);
         if (LANES == 32) __syncwarp();
-        vm_exec(pg, __ldg(st), Rn, sites, P, p, nullptr, &r, dummy, lane == 0);      // the proposal: SIM_k
+        vm_exec<FULL>(pg, __ldg(st), Rn, sites, P, p, nullptr, &r, dummy, lane == 0);      // the proposal: SIM_k
         if (LANES == 32) __syncwarp();
         for (int j = 0; j < ng; ++j)
-          vm_exec(pg, __ldg(&pg.group_tab[5 * __ldg(&pg.site_groups[go + j])]), Rn, sites, P, p, nullptr, nullptr, dummy, false);
+          vm_exec<FULL>(pg, __ldg(&pg.group_tab[5 * __ldg(&pg.site_groups[go + j])]), Rn, sites, P, p, nullptr, nullptr, dummy, false);
         const double N = (double)Nloc;
         const double mu0 = (logu - 0.0) / N;               // alpha of the global section: nothing absorbs in it
         const FeistelKey key = make_feistel_key(seed, step0 + (uint32_t)t, (uint64_t)Nloc);
@@ -429,12 +448,12 @@ prog_ssmh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t s
             if (g >= 0) {
               const int32_t *gt = pg.group_tab + 5 * g;
               const double *row = pg.data + __ldg(gt + 4) + (size_t)rr * __ldg(gt + 3);
-              vm_exec(pg, __ldg(gt + 1), Rn, sites, P, p, row, nullptr, a, false);
-              vm_exec(pg, __ldg(gt + 1), Ro, sites, P, p, row, nullptr, b, false);
+              vm_exec<FULL>(pg, __ldg(gt + 1), Rn, sites, P, p, row, nullptr, a, false);
+              vm_exec<FULL>(pg, __ldg(gt + 1), Ro, sites, P, p, row, nullptr, b, false);
             } else {                                       // a latent child: its own density given its parents
               const int sec = __ldg(&pg.site_tab[5 * rr + 2]);
-              vm_exec(pg, sec, Rn, sites, P, p, nullptr, nullptr, a, false);
-              vm_exec(pg, sec, Ro, sites, P, p, nullptr, nullptr, b, false, k, old);
+              vm_exec<FULL>(pg, sec, Rn, sites, P, p, nullptr, nullptr, a, false);
+              vm_exec<FULL>(pg, sec, Ro, sites, P, p, nullptr, nullptr, b, false, k, old);
             }
             const double d = a - b;
             s1 += d; s2 += d * d;
@@ -473,11 +492,11 @@ prog_ssmh_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t s
 // weight 0 here: the same choice); each is weighted by the regen weight with the value forced (DeterministicLKernel: the
 // site's own log density + what absorbs at its border), the new value is drawn by sampleLogCategorical (utils.py:170-180:
 // exp(xi - max), normalised, one uniform = draw 2) and always accepted (logAlpha = 0; draw 1 is the accept uniform).
-template <int LANES>
-__global__ void __launch_bounds__(256)
+template <int LANES, bool FULL>
+__global__ void __launch_bounds__(256, 4)
 prog_gibbs_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t seed, uint32_t step0, int n_steps, int scope,
                   int block_mode, int map, double *nodes_out, long long *changed_out) {
-  double R[VM_MAX_REGS];
+  double R[FULL ? VM_MAX_REGS : VM_LEAN_REGS];
   const int lane = LANES == 32 ? (threadIdx.x & 31) : 0;
   const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES, n_units = (int64_t)gridDim.x * blockDim.x / LANES;
   const int S = __ldg(&pg.scope_tab[2 * scope]);
@@ -504,8 +523,8 @@ prog_gibbs_kernel(VMProg pg, double *sites, int64_t P, int64_t p_base, uint64_t 
         if (LANES == 32) __syncwarp();
         if (lane == 0) *cell = __ldg(&pg.consts[__ldg(&cc[c])]);
         if (LANES == 32) __syncwarp();
-        double v = vm_children<LANES>(pg, k, R, sites, P, p, lane);
-        vm_exec(pg, sec_own, R, sites, P, p, nullptr, nullptr, v, false);
+        double v = vm_children<LANES, FULL>(pg, k, R, sites, P, p, lane);
+        vm_exec<FULL>(pg, sec_own, R, sites, P, p, nullptr, nullptr, v, false);
         xi[c] = v;
         mx = fmax(mx, v);
       }
@@ -540,6 +559,7 @@ struct ProgramModel : Model {
   std::vector<int> ss_kind, site_bool;
   std::vector<int32_t> scope_tab_host, scope_sites_host, cand_tab_host, cand_consts_host;
   int n_scopes = 1;
+  bool full = true;        // false: the lean kernels (<= VM_LEAN_REGS registers, core instructions) interpret this program
   DevBuf<int32_t> code, tables;       // tables: dir | site_tab | site_groups | group_tab
   DevBuf<double> consts, data, affected;
   DevBuf<double> sa, sb;
@@ -641,9 +661,12 @@ struct ProgramModel : Model {
       VK_REQUIRE(dir[2 * s] >= 0 && dir[2 * s + 1] >= 0 && (int64_t)dir[2 * s] + dir[2 * s + 1] <= n_instr, VK_EINVAL,
                  "program: section out of range");
     int argn_seen = 0;
+    full = n_regs > VM_LEAN_REGS;
     for (int64_t i = 0; i < n_instr; ++i) {          // every operand index is checked once, here
       const int32_t *w = code_h + i * VM_WORDS;
       const int op = w[0];
+      if (op == VM_MOV || op == VM_ARGN || op == VM_COND || op == VM_SELECT || op == VM_LOOKUP || op == VM_SIM_CATEGORICAL ||
+          op == VM_LD_CATEGORICAL) full = true;
       auto reg = [&](int r) { VK_REQUIRE(r >= 0 && r < n_regs, VK_EINVAL, "program: register out of range"); };
       reg(w[1]);
       if (op == VM_ARGN) { VK_REQUIRE(w[2] >= 1 && w[2] <= VM_MAX_ARGN, VK_EINVAL, "program: block length out of range"); argn_seen = w[2]; continue; }
@@ -730,8 +753,13 @@ struct ProgramModel : Model {
   int grid(bool warp) const { return grid_for(warp ? h->P * 32 : h->P, 256, h->sm_count, 8); }
   void launch(int mode, double *out, uint32_t step, int block = VK_BLOCK_ALL, int joint = 0) {
     const bool wm = warp_mode();
-    if (wm) prog_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->lw.p, out, h->P, h->p_base, h->seed, step, mode, block, joint);
-    else prog_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->lw.p, out, h->P, h->p_base, h->seed, step, mode, block, joint);
+    if (!full) {       // small register file (it lives in local memory: stays in L1), core instruction set only
+      if (wm) prog_kernel<32, false><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->lw.p, out, h->P, h->p_base, h->seed, step, mode, block, joint);
+      else prog_kernel<1, false><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->lw.p, out, h->P, h->p_base, h->seed, step, mode, block, joint);
+    } else {
+      if (wm) prog_kernel<32, true><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->lw.p, out, h->P, h->p_base, h->seed, step, mode, block, joint);
+      else prog_kernel<1, true><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->lw.p, out, h->P, h->p_base, h->seed, step, mode, block, joint);
+    }
     VK_CUDA(cudaGetLastError());
   }
   void reset_to_prior() override { launch(VM_MODE_PRIOR, nullptr, h->next_step()); }
@@ -783,8 +811,13 @@ struct ProgramModel : Model {
     VK_REQUIRE(propagated || G == 0, VK_ESTATE, "mh: unpropagated observations; call vk_make_consistent first");
     const int n_steps = block == VK_BLOCK_EACH ? K * scope_blocks(scope) : K;
     const uint32_t step0 = h->next_step((uint32_t)n_steps);
-    if (warp_mode()) prog_mh_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, mean_nodes_dev, acc_dev);
-    else prog_mh_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, mean_nodes_dev, acc_dev);
+    if (!full) {       // small register file (it lives in local memory: stays in L1), core instruction set only
+      if (warp_mode()) prog_mh_kernel<32, false><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, mean_nodes_dev, acc_dev);
+      else prog_mh_kernel<1, false><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, mean_nodes_dev, acc_dev);
+    } else {
+      if (warp_mode()) prog_mh_kernel<32, true><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, mean_nodes_dev, acc_dev);
+      else prog_mh_kernel<1, true><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, mean_nodes_dev, acc_dev);
+    }
     fill_nodes(mean_nodes_dev, scope, block, K, affected_host.data());
     VK_CUDA(cudaGetLastError());
   }
@@ -804,8 +837,13 @@ struct ProgramModel : Model {
                    "(the reference raises SubsampledScaffoldError / warns NotApplicable)");
     }
     const uint32_t step0 = h->next_step((uint32_t)K);
-    if (warp_mode()) prog_ssmh_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, scope, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
-    else prog_ssmh_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, scope, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
+    if (!full) {       // small register file (it lives in local memory: stays in L1), core instruction set only
+      if (warp_mode()) prog_ssmh_kernel<32, false><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, scope, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
+      else prog_ssmh_kernel<1, false><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, scope, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
+    } else {
+      if (warp_mode()) prog_ssmh_kernel<32, true><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, scope, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
+      else prog_ssmh_kernel<1, true><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, K, scope, block, (double)Nbatch, k0, eps, mean_nodes_dev, stats_dev);
+    }
     VK_CUDA(cudaGetLastError());
   }
   void gibbs(int scope, int block, int K, double *mean_nodes_dev, long long *changed_dev) override {
@@ -826,8 +864,13 @@ struct ProgramModel : Model {
     }
     const int n_steps = block == VK_BLOCK_EACH ? K * scope_blocks(scope) : K;
     const uint32_t step0 = h->next_step((uint32_t)n_steps);
-    if (warp_mode()) prog_gibbs_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, map, mean_nodes_dev, changed_dev);
-    else prog_gibbs_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, map, mean_nodes_dev, changed_dev);
+    if (!full) {       // small register file (it lives in local memory: stays in L1), core instruction set only
+      if (warp_mode()) prog_gibbs_kernel<32, false><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, map, mean_nodes_dev, changed_dev);
+      else prog_gibbs_kernel<1, false><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, map, mean_nodes_dev, changed_dev);
+    } else {
+      if (warp_mode()) prog_gibbs_kernel<32, true><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, map, mean_nodes_dev, changed_dev);
+      else prog_gibbs_kernel<1, true><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, map, mean_nodes_dev, changed_dev);
+    }
     fill_nodes(mean_nodes_dev, scope, block, K, affected_host.data());
     VK_CUDA(cudaGetLastError());
   }
@@ -838,8 +881,13 @@ struct ProgramModel : Model {
     VK_REQUIRE(propagated || G == 0, VK_ESTATE, "slice: unpropagated observations; call vk_make_consistent first");
     const int n_steps = block == VK_BLOCK_EACH ? K * scope_blocks(scope) : K;
     const uint32_t step0 = h->next_step((uint32_t)n_steps);
-    if (warp_mode()) prog_slice_kernel<32><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, w, m, doubling, mean_nodes_dev, moved_dev);
-    else prog_slice_kernel<1><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, w, m, doubling, mean_nodes_dev, moved_dev);
+    if (!full) {       // small register file (it lives in local memory: stays in L1), core instruction set only
+      if (warp_mode()) prog_slice_kernel<32, false><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, w, m, doubling, mean_nodes_dev, moved_dev);
+      else prog_slice_kernel<1, false><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, w, m, doubling, mean_nodes_dev, moved_dev);
+    } else {
+      if (warp_mode()) prog_slice_kernel<32, true><<<grid(true), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, w, m, doubling, mean_nodes_dev, moved_dev);
+      else prog_slice_kernel<1, true><<<grid(false), 256, 0, h->stream>>>(pg, sites, h->P, h->p_base, h->seed, step0, n_steps, scope, block, w, m, doubling, mean_nodes_dev, moved_dev);
+    }
     fill_nodes(mean_nodes_dev, scope, block, K, affected_host.data());
     VK_CUDA(cudaGetLastError());
   }
